@@ -1,0 +1,268 @@
+/*
+ * viabel_b200 — C ABI of the B200-native Monte Carlo variational hot path.
+ *
+ * This header is the drop-in boundary.  The reference (kunalghosh/viabel) has no FFI: its
+ * boundary is a set of Python callables.  Each entry point below sits directly underneath
+ * one of those callables and cites the reference lines it replaces (paths are relative to
+ * the reference checkout).  INTEGRATION.md shows the ctypes stub a maintainer of the
+ * reference would add.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch types.  Every pointer whose name starts with
+ *     d_ is DEVICE memory owned by the caller; h_ is host memory.
+ *   - the library never allocates device memory: every op that needs scratch has a
+ *     *_workspace_bytes query and takes (d_ws, ws_bytes).
+ *   - all work is enqueued on `stream` (a cudaStream_t passed as void*); nothing blocks.
+ *   - return value: 0 ok, > 0 a cudaError_t, < 0 an argument error (VB_ERR_*).
+ *   - scalars are returned through device pointers.
+ *   - float64 everywhere unless a `dtype` argument says otherwise; accumulators are always
+ *     float64.
+ */
+#ifndef VIABEL_B200_H
+#define VIABEL_B200_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VB_OK               0
+#define VB_ERR_ARG         (-1)
+#define VB_ERR_UNSUPPORTED (-2)
+#define VB_ERR_WORKSPACE   (-3)
+#define VB_ERR_ALIGN       (-4)
+
+enum { VB_F32 = 0, VB_F64 = 1 };
+enum { VB_FAMILY_MF_GAUSS = 0, VB_FAMILY_MF_T = 1, VB_FAMILY_FR_T = 2 };
+enum { VB_OBJ_KLVI = 0, VB_OBJ_CHIVI = 1 };
+enum { VB_MODEL_FUNNEL = 0, VB_MODEL_MIXTURE = 1, VB_MODEL_EIGHT_SCHOOLS = 2,
+       VB_MODEL_REGRESSION = 3, VB_MODEL_GAUSS = 4 };
+
+/* Library/ABI version and the SM architecture the kernels were compiled for (100). */
+int vb_abi_version(void);
+int vb_compiled_sm(void);
+const char* vb_error_string(int status);
+
+/* ------------------------------------------------------------------------------------
+ * Model plugins: log p(x) and grad log p(x) on the unconstrained space.
+ * Replaces the `logdensity` argument of black_box_klvi / black_box_chivi
+ * (viabel/vb.py:236,248) and the Stan bridge make_stan_log_density (viabel/vb.py:314-321).
+ *   funnel            notebooks/funnel-distribution.ipynb:48-54
+ *   mixture           notebooks/normal-mixture.ipynb:43
+ *   eight schools ncp notebooks/eight_schools_ncp.stan:1-23 (+log tau Jacobian)
+ *   regression        notebooks/robust-regression.ipynb:73-86
+ *   gauss             BASELINE.json config 3 (not in the reference)
+ * Handles are small host objects; device buffers they reference stay owned by the caller.
+ * ---------------------------------------------------------------------------------- */
+typedef struct vb_model vb_model;
+
+int  vb_model_create_funnel(double log_sigma_stdev, vb_model** out);
+int  vb_model_create_mixture(double loc, vb_model** out);
+int  vb_model_create_eight_schools(const double* h_y, const double* h_sigma, int n_schools,
+                                   vb_model** out);
+/* d_X is (n_rows, dim) row-major, d_y is (n_rows); both of `dtype`. */
+int  vb_model_create_regression(const void* d_X, const void* d_y, long long n_rows, int dim,
+                                double df, double prior_sd, int dtype, vb_model** out);
+/* d_mean (dim) and d_precision (dim, dim) symmetric, float64. */
+int  vb_model_create_gauss(const double* d_mean, const double* d_precision, int dim,
+                           vb_model** out);
+int  vb_model_kind(const vb_model* m);
+int  vb_model_dim(const vb_model* m);
+void vb_model_destroy(vb_model* m);
+
+/* log p (n) [float64] and optionally grad (n, dim) [dtype] for x (n, dim) [dtype].
+ * Plugin contract of viabel/vb.py:314-321. */
+size_t vb_model_logp_grad_workspace_bytes(const vb_model* m, long long n, int dtype);
+int vb_model_logp_grad(const vb_model* m, int dtype, const void* d_x, long long n,
+                       double* d_out_logp, void* d_out_grad_or_null,
+                       void* d_ws, size_t ws_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Base draws.  Philox4x32-10, key = seed, counter = (global sample index, lane, call
+ * offset): results do not depend on the launch geometry or on how samples are split
+ * across GPUs (rank r passes sample_index0 = first global index it owns).
+ *   mean-field Gaussian  eps (n, dim) ~ N(0,1)              viabel/vb.py:57
+ *   mean-field t         eps (n, dim) ~ standard_t(df)      viabel/vb.py:151
+ *   full-rank t          chi2 (n) ~ chisquare(df) first, then z (n, dim) ~ N(0,1)
+ *                                                           viabel/vb.py:204,206
+ * d_out_chi2 is only written for VB_FAMILY_FR_T.
+ * ---------------------------------------------------------------------------------- */
+int vb_base_draws(int family, double df, int dtype, long long n, int dim,
+                  unsigned long long seed, unsigned int call_offset,
+                  unsigned long long sample_index0,
+                  void* d_out_eps, void* d_out_chi2_or_null, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Fused mean-field step: draw/load eps -> x = m + exp(l) eps -> log p, grad log p ->
+ * (log q) -> weighted reductions -> (value, grad).  One launch.
+ * Replaces the objective_and_grad closures of black_box_klvi (viabel/vb.py:236-245) and
+ * black_box_chivi (viabel/vb.py:248-266) for the mean-field families
+ * (viabel/vb.py:48-82, 140-182) and the elementwise model plugins.
+ *
+ *   d_var_param   [2*dim] float64: (mean, log scale)
+ *   n             samples this call (this rank) draws;  n_total = samples over all ranks
+ *   d_base        (n, dim) of `dtype`, or NULL -> Philox(seed, call_offset, sample_index0)
+ *   d_out_partials[VB_MF_NPART(dim)] float64, always written:
+ *                 [0] running max M of the log weights (CHIVI; 0 for KLVI)
+ *                 [1] sum_i w_i            (w = 1 for KLVI, exp(alpha (lw_i - M)) for CHIVI)
+ *                 [2] sum_i log p(x_i)     (KLVI)  /  sum_i lw_i (CHIVI)
+ *                 [3] number of samples
+ *                 [4 .. 4+dim)        sum_i w_i g_ij
+ *                 [4+dim .. 4+2dim)   sum_i w_i g_ij eps_ij
+ *   d_out_value / d_out_grad: if non-NULL the kernel also finalises for n_total == n
+ *                 (single rank); multi-rank callers pass NULL and call vb_mf_finalize
+ *                 on the gathered partials.
+ * ---------------------------------------------------------------------------------- */
+#define VB_MF_NPART(dim) (2 * (dim) + 4)
+
+size_t vb_mf_step_workspace_bytes(int dim);
+int vb_mf_step(int family, double df, const vb_model* model, int objective, double alpha,
+               int dtype, const double* d_var_param, long long n,
+               const void* d_base_or_null,
+               unsigned long long seed, unsigned int call_offset,
+               unsigned long long sample_index0,
+               double* d_out_value_or_null, double* d_out_grad_or_null,
+               double* d_out_partials, void* d_ws, size_t ws_bytes, void* stream);
+
+/* Deterministic fixed-order merge of `n_ranks` partial vectors (laid out
+ * [n_ranks][VB_MF_NPART(dim)]) followed by the (value, grad) formulas. */
+int vb_mf_finalize(int family, int objective, double alpha, const double* d_var_param,
+                   int dim, const double* d_partials, int n_ranks,
+                   double* d_out_value, double* d_out_grad, void* stream);
+
+/* Generic (unfused) mean-field reductions for models whose log p / grad are produced by
+ * vb_model_logp_grad (regression, gauss): same partial layout as vb_mf_step.
+ *   d_eps (n, dim) dtype; d_logp (n) float64; d_grad (n, dim) dtype. */
+size_t vb_mf_reduce_workspace_bytes(long long n, int dim);
+int vb_mf_reduce(int family, double df, int objective, double alpha, int dtype,
+                 const double* d_var_param, long long n, int dim,
+                 const void* d_eps, const double* d_logp, const void* d_grad,
+                 double* d_out_value_or_null, double* d_out_grad_or_null,
+                 double* d_out_partials, void* d_ws, size_t ws_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Variational-family closures (viabel/vb.py:54-79, 148-179, 202-230).
+ *   sample:      x (n, dim) = m + exp(l) * eps                      (mean field)
+ *   logdensity:  log q(x; var_param) (n), all normalising constants kept
+ * entropy / mean_and_cov / pth_moment are O(dim) host arithmetic on var_param and live in
+ * the Python layer.
+ * ---------------------------------------------------------------------------------- */
+int vb_mf_sample(int dtype, const double* d_var_param, long long n, int dim,
+                 const void* d_eps, void* d_out_x, void* stream);
+int vb_mf_logdensity(int family, double df, int dtype, const double* d_var_param,
+                     long long n, int dim, const void* d_x, double* d_out_logq, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Full-rank Student-t family (viabel/vb.py:192-233, viabel/_distributions.py:8-38).
+ * The O(dim^3) parameter chain (fold, eigh, Sylvester) is driven from the Python layer with
+ * the dense kernels below; the per-sample work is:
+ *   vb_fr_sample     x_i = mu + (z_i S) / sqrt(chi2_i/df)          viabel/vb.py:204-208
+ *   vb_fr_rows       lw_i = log p_i - log q_i with q evaluated through the base draw
+ *                    (maha_i = |z_i|^2 / (chi2_i/df)), running max
+ *   vb_fr_weighted   g_mu = sum_i w_i g_i ;  G_S = Ztilde' diag(w) G  (dim x dim)
+ * ---------------------------------------------------------------------------------- */
+int vb_fr_sample(int dtype, const double* d_mu, const void* d_scale /* (dim,dim) dtype */,
+                 double df, long long n, int dim, const void* d_z, const void* d_chi2,
+                 void* d_out_x, void* d_ws, size_t ws_bytes, void* stream);
+/* log q(x; mu, Sigma) for arbitrary x (n, dim): d_U (dim, dim) float64 = u * sqrt(pinv(s)) from
+ * the eigendecomposition Sigma = u diag(s) u', log_pdet = sum log s.  viabel/_distributions.py:8-38. */
+size_t vb_fr_logdensity_workspace_bytes(long long n, int dim);
+int vb_fr_logdensity(int dtype, const double* d_mu, const double* d_U, double log_pdet, double df,
+                     long long n, int dim, const void* d_x, double* d_out_logq,
+                     void* d_ws, size_t ws_bytes, void* stream);
+/* d_out_rows[4]: max lw, sum exp(alpha (lw - max)) (CHIVI) or n (KLVI), sum log p, sum lw.
+ * d_out_lw (n) float64; d_out_w (n) float64 weights (1 or exp(alpha (lw - max))). */
+size_t vb_fr_rows_workspace_bytes(long long n);
+int vb_fr_rows(int objective, double alpha, double df, int dtype, long long n, int dim,
+               const void* d_z, const void* d_chi2, const double* d_logp,
+               double logq_const_minus_entropy,
+               double* d_out_lw, double* d_out_w, double* d_out_rows,
+               void* d_ws, size_t ws_bytes, void* stream);
+/* G_S (dim, dim) float64 = sum_i (w_i / sqrt(chi2_i/df)) z_i' g_i ; g_mu (dim) = sum_i w_i g_i */
+size_t vb_fr_weighted_workspace_bytes(long long n, int dim);
+int vb_fr_weighted(int dtype, double df, long long n, int dim, const void* d_z,
+                   const void* d_chi2, const double* d_w, const void* d_grad,
+                   double* d_out_gmu, double* d_out_GS, void* d_ws, size_t ws_bytes,
+                   void* stream);
+
+/* Dense helper: C (m, n) = alpha * op(A) op(B) + beta * C, row-major, float64 (SIMT) or
+ * float32 storage with 3xTF32 tcgen05 arithmetic.  transa/transb: 0 = as stored, 1 = transposed. */
+size_t vb_gemm_workspace_bytes(int dtype, long long m, long long n, long long k);
+int vb_gemm(int dtype, int transa, int transb, long long m, long long n, long long k,
+            double alpha, const void* d_A, long long lda, const void* d_B, long long ldb,
+            double beta, void* d_C, long long ldc, void* d_ws, size_t ws_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Bounds (viabel/bounds.py).
+ *   vb_bounds_divergence  one streaming pass over lw (n):  max, sum exp(alpha (lw - max)),
+ *                         its second moment, mean/variance of lw.   bounds.py:142-192
+ *     d_out[8]: [0] max  [1] mean w  [2] std(w)/sqrt(n) (ddof 0)  [3] mean lw
+ *               [4] std(lw)/sqrt(n)  [5] cubo  [6] n  [7] reserved
+ *   vb_bounds_moments     two passes over samples (n, dim): column means, then
+ *                         C2 = mean_i sum_j c_ij^2, C4 = mean_i sum_j c_ij^4 and optionally
+ *                         the covariance (ddof 1).              bounds.py:130-135, 55-56
+ * Multi-rank: *_partials variants return mergeable partials, see vb_bounds_merge_*.
+ * ---------------------------------------------------------------------------------- */
+size_t vb_bounds_divergence_workspace_bytes(long long n);
+int vb_bounds_divergence(const double* d_lw, long long n, double alpha, double* d_out,
+                         void* d_ws, size_t ws_bytes, void* stream);
+/* partials[6]: max, sum w, sum w^2 (both relative to max), count, mean lw, M2 lw */
+int vb_bounds_divergence_partials(const double* d_lw, long long n, double alpha,
+                                  double* d_out_partials, void* d_ws, size_t ws_bytes,
+                                  void* stream);
+int vb_bounds_divergence_merge(const double* d_partials, int n_ranks, double alpha,
+                               double* d_out, void* stream);
+
+size_t vb_bounds_moments_workspace_bytes(long long n, int dim);
+int vb_bounds_colsum(int dtype, const void* d_x, long long n, int dim, double* d_out_sum,
+                     void* d_ws, size_t ws_bytes, void* stream);
+/* d_mean (dim): the GLOBAL column means.  d_out[2] = sum_i sum_j c^2, sum_i sum_j c^4 (raw sums);
+ * d_out_scatter_or_null (dim, dim) = sum_i c_i c_i' (raw). */
+int vb_bounds_central(int dtype, const void* d_x, long long n, int dim, const double* d_mean,
+                      double* d_out, double* d_out_scatter_or_null,
+                      void* d_ws, size_t ws_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * PSIS (notebooks/psis.py).
+ *   vb_psis_smooth  psislw for one column (psis.py:112-208): max, exact order-statistic
+ *                   select, tail compaction in index order, tail sort by (value, index),
+ *                   GPD fit (psis.py:211-331), gpinv + log + scatter + clamp
+ *                   (psis.py:187-198), log-sum-exp normalise (psis.py:200).
+ *     d_out_diag[8]: [0] k  [1] sigma  [2] xcutoff  [3] n2 (tail size)  [4] smoothed (0/1)
+ *                    [5] max(lw)  [6] logsumexp after smoothing  [7] candidates gathered
+ *     d_out_tail_idx_or_null: int64, capacity vb_psis_tail_capacity(n, Reff); entry r is the
+ *                    original index of the r-th smallest tail element, i.e. `tailinds[x2si]`
+ *                    of psis.py:174,182,196 (ties broken by ascending index).
+ *   The call synchronises `stream` internally (it reads back candidate counts).
+ *   vb_gpd_fit      gpdfitnew on an ascending-sorted array (psis.py:211-331) -> (k, sigma)
+ *   vb_gpd_inv      gpinv (psis.py:334-376)
+ *   vb_logsumexp    sumlogs (psis.py:379-395)
+ * ---------------------------------------------------------------------------------- */
+long long vb_psis_tail_capacity(long long n, double reff);
+size_t vb_psis_smooth_workspace_bytes(long long n, double reff);
+int vb_psis_smooth(const double* d_lw_in, double* d_lw_out, long long n, double reff,
+                   double* d_out_diag, long long* d_out_tail_idx_or_null,
+                   void* d_ws, size_t ws_bytes, void* stream);
+
+size_t vb_gpd_fit_workspace_bytes(long long n);
+int vb_gpd_fit(const double* d_x_sorted, long long n, double* d_out_k_sigma,
+               void* d_ws, size_t ws_bytes, void* stream);
+int vb_gpd_inv(const double* d_p, long long n, double k, double sigma, double* d_out,
+               void* stream);
+size_t vb_logsumexp_workspace_bytes(long long n);
+int vb_logsumexp(const double* d_x, long long n, double* d_out, void* d_ws, size_t ws_bytes,
+                 void* stream);
+
+/* lw_out -= lse (psis.py:200) for a shard whose log-sum-exp was merged across ranks. */
+int vb_psis_normalise(double* d_lw_out, long long n_local, double lse, void* stream);
+
+/* max of a float64 array (psis.py:165, bounds.py:169) */
+size_t vb_max_workspace_bytes(long long n);
+int vb_max(const double* d_x, long long n, double* d_out, void* d_ws, size_t ws_bytes,
+           void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VIABEL_B200_H */

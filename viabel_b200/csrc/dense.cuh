@@ -1,0 +1,26 @@
+// Entry points of the fp32-storage / 3xTF32 tcgen05 dense path (gemm_tf32x3.cu), used by the
+// full-rank family, the correlated-Gaussian plugin and the Student-t regression plugin.
+#pragma once
+#include "common.cuh"
+
+namespace vb {
+
+struct ModelHost;
+
+size_t gemm_tf32x3_workspace_bytes(long long m, long long n, long long k);
+// C (m, n) = alpha * op(A) op(B) + beta * C, row-major fp32, 3xTF32 on tcgen05 (fp32-accurate).
+int gemm_tf32x3(int transa, int transb, long long m, long long n, long long k, float alpha,
+                const float* A, long long lda, const float* B, long long ldb, float beta,
+                float* C, long long ldc, void* ws, size_t ws_bytes, cudaStream_t st);
+
+int fr_sample_tf32(const double* mu, const float* scale, double df, long long n, int dim, const float* z,
+                   const float* chi2, float* out_x, void* ws, size_t ws_bytes, cudaStream_t st);
+
+int gauss_logp_grad_f32(const double* mean, const double* prec, int dim, const float* x, long long n,
+                        double* out_logp, float* out_grad_or_null, void* ws, size_t ws_bytes, cudaStream_t st);
+
+size_t regression_tf32_workspace_bytes(long long n, long long n_rows, int dim);
+int regression_logp_grad_tf32(const ModelHost* m, const float* b, long long n, double* out_logp,
+                              float* out_grad_or_null, void* ws, size_t ws_bytes, cudaStream_t st);
+
+}  // namespace vb

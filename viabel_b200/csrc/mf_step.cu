@@ -1,0 +1,457 @@
+// Fused mean-field Monte Carlo step (KLVI / CHIVI) for the elementwise model plugins.
+//
+// One persistent launch: each CTA streams tiles of base draws (n, D) through shared memory
+// with the TMA unit's 1-D bulk copy (cp.async.bulk + mbarrier, 3 stages), or generates them
+// with Philox; one thread owns one sample per tile: x = m + exp(l) eps -> log p, grad log p
+// (-> log q for CHIVI) -> fp64 accumulators with online log-sum-exp rescaling.  Block
+// partials go to the workspace; the last CTA to finish merges them in block order
+// (deterministic) and applies the value/gradient formulas of SURVEY.md Appendix A.1.
+//
+// Reference being replaced: viabel/vb.py:236-245 (black_box_klvi), :248-266 (black_box_chivi)
+// on the families of :48-82 and :140-182.
+#include "common.cuh"
+#include "models.cuh"
+#include "philox.cuh"
+
+namespace vb {
+
+constexpr int kMfThreads = 256;
+constexpr int kMfStages = 3;
+
+template <class Model>
+struct MfArgs {
+    typename Model::P mp;
+    const double* var_param;   // [2D]
+    const void* base;          // (n, D) of T or null
+    long long n;
+    double df;
+    double alpha;
+    PhiloxStream rng;
+    unsigned long long sample_index0;
+    double* ws_partials;       // [grid][NP]
+    unsigned int* ws_ticket;
+    double* out_partials;      // [NP]
+    double* out_value;         // or null
+    double* out_grad;          // or null
+    int use_bulk;              // base pointer is 16-byte aligned
+};
+
+// log q(x(lambda); lambda) = D*c0 - sum(l) + core(eps); this returns core(eps).
+template <typename T, int FAM, int D>
+__device__ __forceinline__ T logq_core(const T (&eps)[D], T df) {
+    T s = 0;
+    if (FAM == VB_FAMILY_MF_GAUSS) {
+#pragma unroll
+        for (int j = 0; j < D; ++j) s += eps[j] * eps[j];
+        return (T)-0.5 * s;
+    } else {
+        const T inv_df = Math<T>::rcp(df);
+#pragma unroll
+        for (int j = 0; j < D; ++j) s += Math<T>::log1p(eps[j] * eps[j] * inv_df);
+        return (T)-0.5 * (df + (T)1) * s;
+    }
+}
+
+__host__ __device__ inline double mf_logq_const(int family, double df) {
+    if (family == VB_FAMILY_MF_GAUSS) return -0.9189385332046727;   // -1/2 log 2 pi
+    return lgamma(0.5 * (df + 1.0)) - lgamma(0.5 * df) - 0.5 * log(df * 3.14159265358979323846);
+}
+
+// (value, grad) from merged partials.  Appendix A.1.
+__device__ __forceinline__ void mf_finalize_thread(int family, int objective, double alpha,
+                                                   const double* var_param, int D,
+                                                   const double* part, double n_total,
+                                                   double* out_value, double* out_grad, int j) {
+    const double M = part[0], sw = part[1], s2 = part[2];
+    if (j < D) {
+        const double sig = exp(var_param[D + j]);
+        const double gm = part[4 + j], gl = part[4 + D + j] * sig;
+        if (objective == VB_OBJ_KLVI) {
+            out_grad[j] = -gm / n_total;
+            out_grad[D + j] = -(1.0 + gl / n_total);
+        } else {
+            out_grad[j] = alpha * gm / n_total;
+            out_grad[D + j] = alpha * (gl + sw) / n_total;
+        }
+    }
+    if (j == 0) {
+        if (objective == VB_OBJ_KLVI) {
+            double H = 0.0;
+            for (int k = 0; k < D; ++k) H += var_param[D + k];
+            if (family == VB_FAMILY_MF_GAUSS) H += 0.5 * D * (1.0 + 1.8378770664093453);
+            *out_value = -(H + s2 / n_total);
+        } else {
+            *out_value = log(sw / n_total) / alpha + M;
+        }
+    }
+}
+
+// Merge R partial vectors in index order.  Thread j produces component j.
+__device__ __forceinline__ double mf_merge_component(const double* parts, int R, int NP, int objective,
+                                                     double alpha, double M, int j) {
+    if (j == 0) return M;
+    double acc = 0.0;
+    const bool scaled = (objective == VB_OBJ_CHIVI) && (j == 1 || j >= 4);
+    for (int r = 0; r < R; ++r) {
+        const double f = scaled ? rescale_factor(alpha, parts[(size_t)r * NP], M) : 1.0;
+        acc += parts[(size_t)r * NP + j] * f;
+    }
+    return acc;
+}
+
+template <typename T, int FAM, class Model, int OBJ, bool PHILOX>
+__global__ void __launch_bounds__(kMfThreads)
+mf_step_kernel(const __grid_constant__ MfArgs<Model> a) {
+    constexpr int D = Model::D;
+    constexpr int NP = 2 * D + 4;
+    constexpr int TILE = kMfThreads;
+    constexpr uint32_t kStageBytes = TILE * D * sizeof(T);
+
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ uint64_t full_bar[kMfStages];
+    __shared__ double red[(kMfThreads / 32) * NP];
+    __shared__ double merged[NP];
+    __shared__ unsigned int s_ticket;
+
+    const int tid = threadIdx.x;
+    const long long n = a.n;
+    const long long n_full_tiles = n / TILE;
+    const long long n_tiles = (n + TILE - 1) / TILE;
+
+    T mean[D], sig[D];
+#pragma unroll
+    for (int j = 0; j < D; ++j) {
+        mean[j] = (T)a.var_param[j];
+        sig[j] = (T)exp(a.var_param[D + j]);
+    }
+    const T df = (T)a.df;
+    double sum_l = 0.0;
+#pragma unroll
+    for (int j = 0; j < D; ++j) sum_l += a.var_param[D + j];
+    const double logq0 = D * mf_logq_const(FAM, a.df) - sum_l;
+
+    double M = (OBJ == VB_OBJ_CHIVI) ? -INFINITY : 0.0;
+    double sw = 0.0, s2 = 0.0, cnt = 0.0;
+    double ag[D], age[D];
+#pragma unroll
+    for (int j = 0; j < D; ++j) { ag[j] = 0.0; age[j] = 0.0; }
+
+    const bool bulk = !PHILOX && a.use_bulk;
+    const T* base = reinterpret_cast<const T*>(a.base);
+    T* stage_buf = reinterpret_cast<T*>(smem_raw);
+
+    if (bulk) {
+        if (tid == 0) {
+#pragma unroll
+            for (int s = 0; s < kMfStages; ++s) mbar_init(&full_bar[s], 1);
+            mbar_fence_init();
+        }
+        __syncthreads();
+        if (tid == 0) {
+#pragma unroll
+            for (int s = 0; s < kMfStages; ++s) {
+                const long long t = (long long)blockIdx.x + (long long)s * gridDim.x;
+                if (t < n_full_tiles) {
+                    mbar_expect_tx(&full_bar[s], kStageBytes);
+                    bulk_g2s(stage_buf + (size_t)s * TILE * D, base + (size_t)t * TILE * D, kStageBytes,
+                             &full_bar[s]);
+                }
+            }
+        }
+    }
+
+    int it = 0;
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+        const long long i = tile * TILE + tid;
+        const bool full_tile = tile < n_full_tiles;
+        const bool active = i < n;
+        T eps[D];
+        if (PHILOX) {
+            if (active) {
+                const uint64_t gi = a.sample_index0 + (uint64_t)i;
+                if (FAM == VB_FAMILY_MF_GAUSS) {
+#pragma unroll
+                    for (int q = 0; q < (D + 3) / 4; ++q) {
+                        float z[4];
+                        draw_normal_pair(a.rng, gi, (uint32_t)q, z[0], z[1], z[2], z[3]);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            if (4 * q + k < D) eps[4 * q + k] = (T)z[k];
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < D; ++j) eps[j] = (T)draw_student_t(a.rng, gi, (uint32_t)j, (float)a.df);
+                }
+            }
+        } else if (bulk && full_tile) {
+            const int s = it % kMfStages;
+            const uint32_t parity = (uint32_t)((it / kMfStages) & 1);
+            mbar_wait(&full_bar[s], parity);
+            const T* src = stage_buf + (size_t)s * TILE * D + (size_t)tid * D;
+#pragma unroll
+            for (int j = 0; j < D; ++j) eps[j] = src[j];
+            __syncthreads();   // every thread has drained this stage
+            if (tid == 0) {
+                const long long tn = tile + (long long)kMfStages * gridDim.x;
+                if (tn < n_full_tiles) {
+                    mbar_expect_tx(&full_bar[s], kStageBytes);
+                    bulk_g2s(stage_buf + (size_t)s * TILE * D, base + (size_t)tn * TILE * D, kStageBytes,
+                             &full_bar[s]);
+                }
+            }
+        } else if (active) {
+            const T* src = base + (size_t)i * D;
+#pragma unroll
+            for (int j = 0; j < D; ++j) eps[j] = src[j];
+        }
+        if (!active) continue;
+
+        T x[D], g[D], lp;
+#pragma unroll
+        for (int j = 0; j < D; ++j) x[j] = mean[j] + sig[j] * eps[j];
+        Model::template eval<T>(a.mp, x, lp, g);
+
+        cnt += 1.0;
+        if (OBJ == VB_OBJ_KLVI) {
+            sw += 1.0;
+            s2 += (double)lp;
+#pragma unroll
+            for (int j = 0; j < D; ++j) {
+                ag[j] += (double)g[j];
+                age[j] += (double)(g[j] * eps[j]);
+            }
+        } else {
+            const double lw = (double)lp - (logq0 + (double)logq_core<T, FAM, D>(eps, df));
+            s2 += lw;
+            if (lw > M) {
+                const double f = rescale_factor(a.alpha, M, lw);
+                sw *= f;
+#pragma unroll
+                for (int j = 0; j < D; ++j) { ag[j] *= f; age[j] *= f; }
+                M = lw;
+            }
+            const double w = exp(a.alpha * (lw - M));
+            sw += w;
+#pragma unroll
+            for (int j = 0; j < D; ++j) {
+                const double wg = w * (double)g[j];
+                ag[j] += wg;
+                age[j] += wg * (double)eps[j];
+            }
+        }
+    }
+
+    // ---- block reduction ----
+    const int lane = tid & 31, warp = tid >> 5;
+    constexpr int NW = kMfThreads / 32;
+    if (OBJ == VB_OBJ_CHIVI) {
+        const double Mw = warp_max(M);
+        const double f = rescale_factor(a.alpha, M, Mw);
+        sw *= f;
+#pragma unroll
+        for (int j = 0; j < D; ++j) { ag[j] *= f; age[j] *= f; }
+        M = Mw;
+    }
+    sw = warp_sum(sw); s2 = warp_sum(s2); cnt = warp_sum(cnt);
+#pragma unroll
+    for (int j = 0; j < D; ++j) { ag[j] = warp_sum(ag[j]); age[j] = warp_sum(age[j]); }
+    if (lane == 0) {
+        double* r = red + warp * NP;
+        r[0] = M; r[1] = sw; r[2] = s2; r[3] = cnt;
+#pragma unroll
+        for (int j = 0; j < D; ++j) { r[4 + j] = ag[j]; r[4 + D + j] = age[j]; }
+    }
+    __syncthreads();
+    if (tid < NP) {
+        double Mb = red[0];
+        for (int w = 1; w < NW; ++w) Mb = fmax(Mb, red[w * NP]);
+        const double v = mf_merge_component(red, NW, NP, OBJ, a.alpha, Mb, tid);
+        a.ws_partials[(size_t)blockIdx.x * NP + tid] = v;
+    }
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_ticket = atomicAdd(a.ws_ticket, 1u);
+    __syncthreads();
+    if (s_ticket != gridDim.x - 1) return;
+
+    // ---- last CTA: merge block partials in block order, finalise ----
+    __threadfence();
+    const int G = gridDim.x;
+    const volatile double* parts_v = a.ws_partials;
+    double Mg = -INFINITY;
+    for (int b = tid; b < G; b += kMfThreads) Mg = fmax(Mg, parts_v[(size_t)b * NP]);
+    Mg = block_max(Mg, red);
+    if (OBJ == VB_OBJ_KLVI) Mg = 0.0;
+    if (tid < NP) {
+        const double v = mf_merge_component(const_cast<const double*>(a.ws_partials), G, NP, OBJ, a.alpha, Mg, tid);
+        merged[tid] = v;
+        a.out_partials[tid] = v;
+    }
+    __syncthreads();
+    if (a.out_value != nullptr && tid < NP)
+        mf_finalize_thread(FAM, OBJ, a.alpha, a.var_param, D, merged, merged[3], a.out_value, a.out_grad, tid);
+    if (tid == 0) *a.ws_ticket = 0u;   // ready for the next launch on this stream
+}
+
+// ------------------------------------------------------------------------------------------ dispatch
+static int g_num_sms_cached = 0;
+static int num_sms() {
+    if (g_num_sms_cached == 0) {
+        int dev = 0, v = 0;
+        if (cudaGetDevice(&dev) == cudaSuccess &&
+            cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0)
+            g_num_sms_cached = v;
+        else
+            g_num_sms_cached = kNumSMs;
+    }
+    return g_num_sms_cached;
+}
+
+struct MfCall {
+    int family; double df; int objective; double alpha; int dtype;
+    const double* var_param; long long n; const void* base;
+    unsigned long long seed; unsigned int call_offset; unsigned long long sample_index0;
+    double* out_value; double* out_grad; double* out_partials;
+    void* ws; size_t ws_bytes; cudaStream_t stream;
+};
+
+template <typename T, int FAM, class Model, int OBJ, bool PHILOX>
+static int launch_mf(const MfCall& c, const typename Model::P& mp) {
+    constexpr int D = Model::D;
+    constexpr int NP = 2 * D + 4;
+    auto kern = mf_step_kernel<T, FAM, Model, OBJ, PHILOX>;
+    const size_t smem = PHILOX ? 0 : (size_t)kMfStages * kMfThreads * D * sizeof(T);
+    static bool configured = false;      // per template instantiation
+    static int blocks_per_sm = 1;
+    if (!configured) {
+        VB_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VB_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern, kMfThreads, smem));
+        if (blocks_per_sm < 1) blocks_per_sm = 1;
+        configured = true;
+    }
+    const long long n_tiles = (c.n + kMfThreads - 1) / kMfThreads;
+    long long grid = (long long)num_sms() * blocks_per_sm;
+    if (grid > n_tiles) grid = n_tiles;
+    if (grid < 1) grid = 1;
+    const size_t need = align_up((size_t)grid * NP * sizeof(double), 16) + 16;
+    if (c.ws_bytes < need) return VB_ERR_WORKSPACE;
+
+    MfArgs<Model> a;
+    a.mp = mp;
+    a.var_param = c.var_param;
+    a.base = c.base;
+    a.n = c.n;
+    a.df = c.df;
+    a.alpha = c.alpha;
+    a.rng.k0 = (uint32_t)c.seed;
+    a.rng.k1 = (uint32_t)(c.seed >> 32);
+    a.rng.offset = c.call_offset;
+    a.sample_index0 = c.sample_index0;
+    // ticket lives at the front so its address does not depend on the grid
+    a.ws_ticket = reinterpret_cast<unsigned int*>(c.ws);
+    a.ws_partials = reinterpret_cast<double*>(reinterpret_cast<char*>(c.ws) + 16);
+    a.out_partials = c.out_partials;
+    a.out_value = c.out_value;
+    a.out_grad = c.out_grad;
+    a.use_bulk = (c.base != nullptr) && ((reinterpret_cast<uintptr_t>(c.base) & 15u) == 0);
+    kern<<<(unsigned)grid, kMfThreads, smem, c.stream>>>(a);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+
+template <typename T, int FAM, class Model>
+static int dispatch_obj(const MfCall& c, const typename Model::P& mp) {
+    const bool philox = c.base == nullptr;
+    if (c.objective == VB_OBJ_KLVI)
+        return philox ? launch_mf<T, FAM, Model, VB_OBJ_KLVI, true>(c, mp)
+                      : launch_mf<T, FAM, Model, VB_OBJ_KLVI, false>(c, mp);
+    if (c.objective == VB_OBJ_CHIVI)
+        return philox ? launch_mf<T, FAM, Model, VB_OBJ_CHIVI, true>(c, mp)
+                      : launch_mf<T, FAM, Model, VB_OBJ_CHIVI, false>(c, mp);
+    return VB_ERR_ARG;
+}
+
+template <class Model>
+static int dispatch_family(const MfCall& c, const typename Model::P& mp) {
+    if (c.dtype == VB_F64) {
+        if (c.family == VB_FAMILY_MF_GAUSS) return dispatch_obj<double, VB_FAMILY_MF_GAUSS, Model>(c, mp);
+        if (c.family == VB_FAMILY_MF_T) return dispatch_obj<double, VB_FAMILY_MF_T, Model>(c, mp);
+    } else if (c.dtype == VB_F32) {
+        if (c.family == VB_FAMILY_MF_GAUSS) return dispatch_obj<float, VB_FAMILY_MF_GAUSS, Model>(c, mp);
+        if (c.family == VB_FAMILY_MF_T) return dispatch_obj<float, VB_FAMILY_MF_T, Model>(c, mp);
+    }
+    return VB_ERR_ARG;
+}
+
+// ------------------------------------------------------------------------------------------ finalize (multi-rank)
+__global__ void mf_finalize_kernel(int family, int objective, double alpha, const double* var_param, int D,
+                                   const double* parts, int R, double* out_value, double* out_grad) {
+    extern __shared__ double merged_dyn[];
+    const int NP = 2 * D + 4;
+    double M = 0.0;
+    if (objective == VB_OBJ_CHIVI) {
+        M = -INFINITY;
+        for (int r = 0; r < R; ++r) M = fmax(M, parts[(size_t)r * NP]);
+    }
+    for (int j = threadIdx.x; j < NP; j += blockDim.x)
+        merged_dyn[j] = mf_merge_component(parts, R, NP, objective, alpha, M, j);
+    __syncthreads();
+    for (int j = threadIdx.x; j < NP; j += blockDim.x)
+        mf_finalize_thread(family, objective, alpha, var_param, D, merged_dyn, merged_dyn[3], out_value, out_grad, j);
+}
+
+}  // namespace vb
+
+using namespace vb;
+
+extern "C" size_t vb_mf_step_workspace_bytes(int dim) {
+    if (dim < 1) return 0;
+    // up to 8 resident CTAs per SM on any part this runs on
+    return 16 + align_up((size_t)num_sms() * 8 * VB_MF_NPART(dim) * sizeof(double), 16) + 16;
+}
+
+extern "C" int vb_mf_step(int family, double df, const vb_model* model, int objective, double alpha,
+                          int dtype, const double* d_var_param, long long n,
+                          const void* d_base_or_null,
+                          unsigned long long seed, unsigned int call_offset,
+                          unsigned long long sample_index0,
+                          double* d_out_value_or_null, double* d_out_grad_or_null,
+                          double* d_out_partials, void* d_ws, size_t ws_bytes, void* stream) {
+    if (!model || !d_var_param || !d_out_partials || !d_ws || n < 1) return VB_ERR_ARG;
+    if ((d_out_value_or_null == nullptr) != (d_out_grad_or_null == nullptr)) return VB_ERR_ARG;
+    if (family == VB_FAMILY_MF_T && !(df > 2.0)) return VB_ERR_ARG;
+    if (objective == VB_OBJ_CHIVI && !(alpha > 0.0)) return VB_ERR_ARG;
+    const ModelHost* m = reinterpret_cast<const ModelHost*>(model);
+    MfCall c{family, df, objective, alpha, dtype, d_var_param, n, d_base_or_null, seed, call_offset,
+             sample_index0, d_out_value_or_null, d_out_grad_or_null, d_out_partials, d_ws, ws_bytes,
+             (cudaStream_t)stream};
+    switch (m->kind) {
+        case VB_MODEL_FUNNEL: {
+            Funnel::P p{m->p0};
+            return dispatch_family<Funnel>(c, p);
+        }
+        case VB_MODEL_MIXTURE: {
+            Mixture::P p{m->p0};
+            return dispatch_family<Mixture>(c, p);
+        }
+        case VB_MODEL_EIGHT_SCHOOLS: {
+            if (m->n_schools != 8) return VB_ERR_UNSUPPORTED;
+            EightSchools<8>::P p;
+            for (int j = 0; j < 8; ++j) { p.y[j] = m->y[j]; p.inv_sigma[j] = 1.0 / m->sigma[j]; }
+            return dispatch_family<EightSchools<8>>(c, p);
+        }
+        default:
+            return VB_ERR_UNSUPPORTED;   // regression / gauss go through vb_model_logp_grad + vb_mf_reduce
+    }
+}
+
+extern "C" int vb_mf_finalize(int family, int objective, double alpha, const double* d_var_param,
+                              int dim, const double* d_partials, int n_ranks,
+                              double* d_out_value, double* d_out_grad, void* stream) {
+    if (!d_var_param || !d_partials || !d_out_value || !d_out_grad || dim < 1 || n_ranks < 1) return VB_ERR_ARG;
+    const int NP = VB_MF_NPART(dim);
+    mf_finalize_kernel<<<1, 256, NP * sizeof(double), (cudaStream_t)stream>>>(
+        family, objective, alpha, d_var_param, dim, d_partials, n_ranks, d_out_value, d_out_grad);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}

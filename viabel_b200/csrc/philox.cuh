@@ -1,0 +1,122 @@
+// Counter-based base draws (Philox4x32-10; Salmon et al., SC'11).
+//
+// Counter layout (128 bit): c0,c1 = global sample index (64 bit), c2 = lane (which pair of
+// coordinates / which rejection attempt), c3 = call offset.  Key (64 bit) = family seed.
+// Every variate is a pure function of (seed, call offset, global sample index, coordinate),
+// so results are independent of grid shape and of how the sample axis is split over GPUs.
+//
+// Uniform -> normal by Box-Muller, gamma by Marsaglia-Tsang (2000) with a fixed budget of
+// rejection attempts, all in fp32 arithmetic: the base draws carry fp32 resolution
+// (|z| <= 6.66, spacing 2^-24 relative) and are then promoted to the compute type.
+#pragma once
+#include "common.cuh"
+
+namespace vb {
+
+struct Philox4 { uint32_t x, y, z, w; };
+
+__device__ __forceinline__ Philox4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                                 uint32_t k0, uint32_t k1) {
+    constexpr uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(M0, c0), lo0 = M0 * c0;
+        const uint32_t hi1 = __umulhi(M1, c2), lo1 = M1 * c2;
+        c0 = hi1 ^ c1 ^ k0;
+        c1 = lo1;
+        c2 = hi0 ^ c3 ^ k1;
+        c3 = lo0;
+        k0 += W0;
+        k1 += W1;
+    }
+    return Philox4{c0, c1, c2, c3};
+}
+
+struct PhiloxStream {
+    uint32_t k0, k1;      // seed
+    uint32_t offset;      // call offset
+};
+
+__device__ __forceinline__ Philox4 philox_at(const PhiloxStream& s, uint64_t sample, uint32_t lane) {
+    return philox4x32_10((uint32_t)sample, (uint32_t)(sample >> 32), lane, s.offset, s.k0, s.k1);
+}
+
+// (0,1) open interval, 2^-32 resolution before fp32 rounding; never 0, may round to 1-2^-24.
+__device__ __forceinline__ float u01(uint32_t u) {
+    return fminf(((float)u + 0.5f) * 2.3283064365386963e-10f, 0.99999994f);
+}
+
+// Two independent standard normals from two words.
+__device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& n0, float& n1) {
+    const float r = sqrtf(-2.0f * __logf(u01(a)));
+    float s, c;
+    __sincosf(6.2831853071795865f * ((float)b * 2.3283064365386963e-10f), &s, &c);
+    n0 = r * c;
+    n1 = r * s;
+}
+
+// Lane numbering: coordinates use lanes [0, 2^30); rejection retries use lane | (attempt << 30)... kept
+// disjoint by construction below (coordinate lanes < 2^24, attempt field in bits 24-27, chi2 marker bit 31).
+constexpr uint32_t kLaneChi2 = 0x80000000u;
+constexpr int kGammaAttempts = 6;   // acceptance >= 0.95 per attempt for shape >= 1
+
+// Marsaglia-Tsang acceptance test for Gamma(shape, 1), shape >= 1, given a normal and a uniform.
+__device__ __forceinline__ bool mt_accept(float d, float c, float xn, float un, float& out) {
+    const float t = 1.0f + c * xn;
+    const float v = t * t * t;
+    out = d * v;
+    return (t > 0.0f) && (__logf(un) < 0.5f * xn * xn + d - d * v + d * __logf(v));
+}
+
+// standard_t(df) variate for (sample, coord): z / sqrt(chi2/df), chi2 = 2 Gamma(df/2).
+__device__ __forceinline__ float draw_student_t(const PhiloxStream& s, uint64_t sample, uint32_t coord,
+                                                float df) {
+    const float shape = 0.5f * df;
+    const float d = shape - 1.0f / 3.0f;
+    const float c = rsqrtf(9.0f * d);
+    Philox4 r = philox_at(s, sample, coord);
+    float z, xn;
+    box_muller(r.x, r.y, z, xn);
+    float g;
+    bool ok = mt_accept(d, c, xn, u01(r.z), g);
+#pragma unroll 1
+    for (int a = 1; a < kGammaAttempts && !ok; ++a) {
+        r = philox_at(s, sample, coord | ((uint32_t)a << 24));
+        float x0, x1;
+        box_muller(r.x, r.y, x0, x1);
+        ok = mt_accept(d, c, x0, u01(r.z), g);
+        if (!ok) ok = mt_accept(d, c, x1, u01(r.w), g);
+    }
+    if (!ok) g = d;   // probability < 1e-15; keeps the draw finite
+    // chi2/df = 2 g / df
+    return z * rsqrtf(2.0f * g / df);
+}
+
+// chisquare(df) for one sample (full-rank family, drawn "first": its own lane space).
+__device__ __forceinline__ float draw_chi2(const PhiloxStream& s, uint64_t sample, float df) {
+    const float shape = 0.5f * df;
+    const float d = shape - 1.0f / 3.0f;
+    const float c = rsqrtf(9.0f * d);
+    float g = d;
+    bool ok = false;
+#pragma unroll 1
+    for (int a = 0; a < kGammaAttempts && !ok; ++a) {
+        const Philox4 r = philox_at(s, sample, kLaneChi2 | (uint32_t)a);
+        float x0, x1;
+        box_muller(r.x, r.y, x0, x1);
+        ok = mt_accept(d, c, x0, u01(r.z), g);
+        if (!ok) ok = mt_accept(d, c, x1, u01(r.w), g);
+    }
+    if (!ok) g = d;
+    return 2.0f * g;
+}
+
+// Two standard normals for coordinates (2*pair, 2*pair+1) of a sample.
+__device__ __forceinline__ void draw_normal_pair(const PhiloxStream& s, uint64_t sample, uint32_t pair,
+                                                 float& n0, float& n1, float& n2, float& n3) {
+    const Philox4 r = philox_at(s, sample, pair);
+    box_muller(r.x, r.y, n0, n1);
+    box_muller(r.z, r.w, n2, n3);
+}
+
+}  // namespace vb

@@ -1,0 +1,852 @@
+// Pareto smoothed importance sampling on the device (notebooks/psis.py:112-395).
+//
+// The reference does a full argsort of n log weights only to read ONE order statistic and
+// then works on the <= ceil(min(0.2 n, 3 sqrt(n))) largest values.  Here:
+//   P1  max                                              (8 B/weight read)
+//   P2  prefilter: u = max - x; elements with u <= pivot (a ~1% sample quantile) are
+//       appended as (u, index) candidates, all others contribute exp(-u) to the body sum
+//                                                        (8 B/weight read)
+//       optional refinement of the candidates with a 64 Ki-bin histogram of u
+//   S   bitonic sort of the (few 1e4..1e5) candidates by (u descending, index ascending)
+//       == ascending shifted log weight with ties broken by ascending index
+//   T   exact cutoff = (K+1)-th largest, strict tail, GPD fit, inverse-CDF smoothing
+//   P3  out = (x - max) - logsumexp, tail scattered      (16 B/weight read+write)
+// Selection, tail membership and tail order are exact (bit-level comparisons on the same
+// fp64 values the reference compares); k-hat and the smoothed values differ from numpy only
+// by summation order.
+#include "common.cuh"
+#include <cfloat>
+
+namespace vb {
+
+static inline int grid_for(long long work_items, int threads, int max_blocks) {
+    long long g = (work_items + threads - 1) / threads;
+    if (g > max_blocks) g = max_blocks;
+    if (g < 1) g = 1;
+    return (int)g;
+}
+
+struct __align__(16) Cand { unsigned long long key; unsigned long long idx; };
+// key = ~bits(u), u >= 0: ascending key == descending u == ascending shifted log weight.
+__device__ __forceinline__ unsigned long long u_to_key(double u) {
+    return ~(unsigned long long)__double_as_longlong(u);
+}
+__device__ __forceinline__ double key_to_u(unsigned long long k) {
+    return __longlong_as_double((long long)~k);
+}
+__device__ __forceinline__ bool cand_less(const Cand& a, const Cand& b) {
+    return a.key < b.key || (a.key == b.key && a.idx < b.idx);
+}
+
+constexpr int kSortChunk = 4096;          // elements sorted per CTA in shared memory (64 KiB)
+constexpr int kSortThreads = 1024;
+constexpr int kHistBins = 65536;
+constexpr int kSampleSize = 4096;
+constexpr long long kDirectSortMax = 1ll << 17;
+constexpr double kNegLogTiny = 708.3964185322641;      // -log(DBL_MIN), psis.py:158
+
+// ------------------------------------------------------------------------------------------ bitonic sort
+__device__ __forceinline__ void cmp_swap(Cand& a, Cand& b, bool ascending) {
+    if (cand_less(b, a) == ascending) { const Cand t = a; a = b; b = t; }
+}
+
+// Sort each chunk of kSortChunk elements completely (stages k = 2 .. kSortChunk).
+__global__ void __launch_bounds__(kSortThreads)
+bitonic_chunk_sort_kernel(Cand* __restrict__ data) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    Cand* s = reinterpret_cast<Cand*>(smem_raw);
+    const long long base = (long long)blockIdx.x * kSortChunk;
+    for (int i = threadIdx.x; i < kSortChunk; i += kSortThreads) s[i] = data[base + i];
+    __syncthreads();
+    for (int k = 2; k <= kSortChunk; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int t = threadIdx.x; t < kSortChunk / 2; t += kSortThreads) {
+                const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+                const int p = i | j;
+                const bool asc = (((base + i) & k) == 0);
+                cmp_swap(s[i], s[p], asc);
+            }
+            __syncthreads();
+        }
+    }
+    for (int i = threadIdx.x; i < kSortChunk; i += kSortThreads) data[base + i] = s[i];
+}
+
+// One global compare-exchange step (j >= kSortChunk) of stage k.
+__global__ void bitonic_global_step_kernel(Cand* __restrict__ data, long long n_pad, long long k, long long j) {
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n_pad / 2;
+         t += (long long)gridDim.x * blockDim.x) {
+        const long long i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+        const long long p = i | j;
+        const bool asc = ((i & k) == 0);
+        Cand a = data[i], b = data[p];
+        if (cand_less(b, a) == asc) { data[i] = b; data[p] = a; }
+    }
+}
+
+// Remaining steps j = kSortChunk/2 .. 1 of stage k, inside shared memory.
+__global__ void __launch_bounds__(kSortThreads)
+bitonic_chunk_merge_kernel(Cand* __restrict__ data, long long k) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    Cand* s = reinterpret_cast<Cand*>(smem_raw);
+    const long long base = (long long)blockIdx.x * kSortChunk;
+    for (int i = threadIdx.x; i < kSortChunk; i += kSortThreads) s[i] = data[base + i];
+    __syncthreads();
+    const bool asc = ((base & k) == 0);     // constant inside a chunk because k > kSortChunk
+    for (int j = kSortChunk >> 1; j > 0; j >>= 1) {
+        for (int t = threadIdx.x; t < kSortChunk / 2; t += kSortThreads) {
+            const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+            cmp_swap(s[i], s[i | j], asc);
+        }
+        __syncthreads();
+    }
+    for (int i = threadIdx.x; i < kSortChunk; i += kSortThreads) data[base + i] = s[i];
+}
+
+__global__ void pad_cands_kernel(Cand* __restrict__ data, long long count, long long n_pad) {
+    for (long long i = count + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n_pad;
+         i += (long long)gridDim.x * blockDim.x) {
+        data[i].key = ~0ull;
+        data[i].idx = ~0ull;
+    }
+}
+
+static long long pad_pow2(long long count) {
+    long long p = kSortChunk;
+    while (p < count) p <<= 1;
+    return p;
+}
+
+static bool g_sort_attr_set = false;
+// ascending sort of data[0..n_pad) (n_pad a power of two >= kSortChunk; caller padded the end)
+static int bitonic_sort(Cand* data, long long n_pad, cudaStream_t st) {
+    const size_t smem = (size_t)kSortChunk * sizeof(Cand);
+    if (!g_sort_attr_set) {
+        VB_CUDA_TRY(cudaFuncSetAttribute(bitonic_chunk_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VB_CUDA_TRY(cudaFuncSetAttribute(bitonic_chunk_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        g_sort_attr_set = true;
+    }
+    const int chunks = (int)(n_pad / kSortChunk);
+    bitonic_chunk_sort_kernel<<<chunks, kSortThreads, smem, st>>>(data);
+    VB_LAUNCH_CHECK();
+    for (long long k = 2ll * kSortChunk; k <= n_pad; k <<= 1) {
+        for (long long j = k >> 1; j >= kSortChunk; j >>= 1) {
+            bitonic_global_step_kernel<<<grid_for(n_pad / 2, 256, kNumSMs * 8), 256, 0, st>>>(data, n_pad, k, j);
+            VB_LAUNCH_CHECK();
+        }
+        bitonic_chunk_merge_kernel<<<chunks, kSortThreads, smem, st>>>(data, k);
+        VB_LAUNCH_CHECK();
+    }
+    return VB_OK;
+}
+
+// ------------------------------------------------------------------------------------------ pivot from a strided sample
+// sample[i] = (u of element floor(i * n / S)); sorted ascending by key (descending u).
+__global__ void sample_kernel(const double* __restrict__ lw, long long n, const double* __restrict__ M_ptr,
+                              Cand* __restrict__ sample) {
+    const double M = *M_ptr;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < kSampleSize; i += gridDim.x * blockDim.x) {
+        const long long e = ((long long)i * n) / kSampleSize;   // i < 2^12, n < 2^50
+        Cand c;
+        c.key = u_to_key(M - lw[e]);
+        c.idx = (unsigned long long)e;
+        sample[i] = c;
+    }
+}
+// pivot = the `rank`-th smallest u of the sample (0-based), or +inf when rank >= sample size
+__global__ void pivot_kernel(const Cand* __restrict__ sorted_sample, int rank, double* __restrict__ out_pivot) {
+    if (threadIdx.x == 0 && blockIdx.x == 0)
+        *out_pivot = (rank >= kSampleSize) ? INFINITY : key_to_u(sorted_sample[kSampleSize - 1 - rank].key);
+}
+__global__ void set_double_kernel(double* p, double v) { if (threadIdx.x == 0 && blockIdx.x == 0) *p = v; }
+__global__ void set_counts_kernel(long long* p, long long a, long long b, long long c, long long d) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) { p[0] = a; p[1] = b; p[2] = c; p[3] = d; }
+}
+
+// ------------------------------------------------------------------------------------------ P2: prefilter
+struct PrefilterOut {
+    Cand* cand;
+    long long cap;
+    unsigned long long* counter;     // number of candidates found (may exceed cap)
+    double* block_body;              // [grid] sum of exp(-u) over non-candidates
+};
+
+__device__ __forceinline__ void prefilter_one(double x, bool in, long long gidx, double M, double pivot,
+                                              double& body, const PrefilterOut& o) {
+    // every lane of the warp calls this together (the ballot needs all 32)
+    const double u = M - x;
+    const bool is_cand = in && (u <= pivot);
+    const unsigned mask = __ballot_sync(0xffffffffu, is_cand);
+    if (mask) {
+        const int lane = threadIdx.x & 31;
+        unsigned long long basepos = 0;
+        const int leader = __ffs(mask) - 1;
+        if (lane == leader) basepos = atomicAdd(o.counter, (unsigned long long)__popc(mask));
+        basepos = __shfl_sync(0xffffffffu, basepos, leader);
+        if (is_cand) {
+            const unsigned long long pos = basepos + __popc(mask & ((1u << lane) - 1));
+            if ((long long)pos < o.cap) {
+                Cand c;
+                c.key = u_to_key(u);
+                c.idx = (unsigned long long)gidx;
+                o.cand[pos] = c;
+            }
+        }
+    }
+    if (in && !is_cand) body += exp(-u);
+}
+
+__global__ void __launch_bounds__(256)
+prefilter_kernel(const double* __restrict__ lw, long long n, long long index0, const double* __restrict__ M_ptr,
+                 const double* __restrict__ pivot_ptr, PrefilterOut o) {
+    __shared__ double scratch[32];
+    const double M = *M_ptr, pivot = *pivot_ptr;
+    double body = 0.0;
+    const long long gtid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    const long long gthreads = (long long)gridDim.x * blockDim.x;
+    const long long iters = (n + gthreads - 1) / gthreads;      // uniform trip count
+    long long it = 0;
+    for (; it + 4 <= iters; it += 4) {                           // 4 loads in flight per thread
+        double x[4];
+        bool in[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const long long i = (it + q) * gthreads + gtid;
+            in[q] = i < n;
+            x[q] = in[q] ? ld_stream(lw + i) : 0.0;
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+            prefilter_one(x[q], in[q], index0 + (it + q) * gthreads + gtid, M, pivot, body, o);
+    }
+    for (; it < iters; ++it) {
+        const long long i = it * gthreads + gtid;
+        const bool in = i < n;
+        const double x = in ? ld_stream(lw + i) : 0.0;
+        prefilter_one(x, in, index0 + i, M, pivot, body, o);
+    }
+    body = block_sum(body, scratch);
+    if (threadIdx.x == 0) o.block_body[blockIdx.x] = body;
+}
+
+// ------------------------------------------------------------------------------------------ refinement histogram
+__global__ void hist_kernel(const Cand* __restrict__ cand, long long count, const double* __restrict__ pivot_ptr,
+                            unsigned int* __restrict__ hist) {
+    const double pivot = *pivot_ptr;
+    const double scale = (pivot > 0.0 && isfinite(pivot)) ? (double)kHistBins / pivot : 0.0;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count;
+         i += (long long)gridDim.x * blockDim.x) {
+        const double u = key_to_u(cand[i].key);
+        long long b = (long long)(u * scale);
+        if (b > kHistBins - 1) b = kHistBins - 1;
+        atomicAdd(&hist[b], 1u);
+    }
+}
+// smallest bin b* with cumulative count >= target; out[0] = b*, out[1] = cumulative count through b*
+__global__ void hist_scan_kernel(const unsigned int* __restrict__ hist, long long target, long long* __restrict__ out) {
+    __shared__ long long partial[1024];
+    const int per = kHistBins / 1024;
+    long long s = 0;
+    for (int b = 0; b < per; ++b) s += hist[threadIdx.x * per + b];
+    partial[threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        long long cum = 0;
+        int seg = 0;
+        for (; seg < 1024; ++seg) {
+            if (cum + partial[seg] >= target) break;
+            cum += partial[seg];
+        }
+        if (seg == 1024) { out[0] = kHistBins - 1; out[1] = cum; return; }
+        int b = seg * per;
+        for (;; ++b) {
+            cum += hist[b];
+            if (cum >= target) break;
+        }
+        out[0] = b;
+        out[1] = cum;
+    }
+}
+__global__ void __launch_bounds__(256)
+compact2_kernel(const Cand* __restrict__ cand, long long count, const double* __restrict__ pivot_ptr,
+                const long long* __restrict__ bstar_ptr, Cand* __restrict__ out, unsigned long long* __restrict__ counter,
+                double* __restrict__ block_body) {
+    __shared__ double scratch[32];
+    const double pivot = *pivot_ptr;
+    const double scale = (pivot > 0.0 && isfinite(pivot)) ? (double)kHistBins / pivot : 0.0;
+    const long long bstar = *bstar_ptr;
+    double body = 0.0;
+    const long long gtid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    const long long gthreads = (long long)gridDim.x * blockDim.x;
+    const long long iters = (count + gthreads - 1) / gthreads;
+    for (long long it = 0; it < iters; ++it) {
+        const long long i = it * gthreads + gtid;
+        bool keep = false;
+        Cand c;
+        c.key = 0; c.idx = 0;
+        if (i < count) {
+            c = cand[i];
+            const double u = key_to_u(c.key);
+            long long b = (long long)(u * scale);
+            if (b > kHistBins - 1) b = kHistBins - 1;
+            keep = (b <= bstar);
+            if (!keep) body += exp(-u);
+        }
+        const unsigned mask = __ballot_sync(0xffffffffu, keep);
+        if (mask) {
+            const int lane = threadIdx.x & 31;
+            const int leader = __ffs(mask) - 1;
+            unsigned long long basepos = 0;
+            if (lane == leader) basepos = atomicAdd(counter, (unsigned long long)__popc(mask));
+            basepos = __shfl_sync(0xffffffffu, basepos, leader);
+            if (keep) out[basepos + __popc(mask & ((1u << lane) - 1))] = c;
+        }
+    }
+    body = block_sum(body, scratch);
+    if (threadIdx.x == 0) block_body[blockIdx.x] = body;
+}
+
+// ------------------------------------------------------------------------------------------ tail bookkeeping
+// state[] (doubles): [0] xcutoff  [1] exp(xcutoff)  [2] k  [3] sigma  [4] smoothed  [5] lse  [6] b (GPD)  [7] spare
+// counts[] (long long): [0] n2  [1] first tail position p in the sorted candidates  [2] m (quadrature points)
+//                       [3] 1 when the GPD fit runs (psislw: n2 > 4, psis.py:177)
+__global__ void tail_bounds_kernel(const Cand* __restrict__ sorted, long long count, long long K1,
+                                   double* __restrict__ state, long long* __restrict__ counts) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    // (K1+1)-th largest shifted weight == (K1+1)-th smallest u == sorted[count-1-K1]   (psis.py:157,169)
+    const double u_cut = key_to_u(sorted[count - 1 - K1].key);
+    const double xcut = fmax(-u_cut, -kNegLogTiny);                  // psis.py:169-172
+    const double u_eff = -xcut;
+    // sorted is descending in u: tail = suffix with u < u_eff  (x > xcutoff, strict; psis.py:174)
+    long long lo = 0, hi = count;                                    // first position with u < u_eff
+    while (lo < hi) {
+        const long long mid = (lo + hi) >> 1;
+        if (key_to_u(sorted[mid].key) < u_eff) hi = mid; else lo = mid + 1;
+    }
+    const long long n2 = count - lo;
+    state[0] = xcut;
+    state[1] = exp(xcut);
+    counts[0] = n2;
+    counts[1] = lo;
+    counts[2] = 30 + (long long)sqrt((double)n2);                    // psis.py:268
+    counts[3] = (n2 > 4) ? 1 : 0;                                    // psis.py:177
+}
+
+// x2[r] = exp(x_r) - exp(xcutoff) for the tail in ascending order (psis.py:184-185)
+__global__ void tail_excess_kernel(const Cand* __restrict__ sorted, const double* __restrict__ state,
+                                   const long long* __restrict__ counts, double* __restrict__ x2) {
+    const long long n2 = counts[0], p = counts[1];
+    const double ec = state[1];
+    for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < n2;
+         r += (long long)gridDim.x * blockDim.x)
+        x2[r] = exp(-key_to_u(sorted[p + r].key)) - ec;
+}
+
+// ------------------------------------------------------------------------------------------ GPD fit (psis.py:211-331)
+__device__ __forceinline__ double gpd_b(long long j /*0-based*/, long long m, double x_q, double x_max) {
+    const double jj = (double)(j + 1) - 0.5;
+    double b = 1.0 - sqrt((double)m / jj);          // psis.py:270-274
+    b /= 3.0 * x_q;                                 // PRIOR = 3, psis.py:276/279
+    b += 1.0 / x_max;                               // psis.py:277/280
+    return b;
+}
+// one CTA per quadrature point: ks[j] = mean_r log1p(-b_j x_r), L[j] = n (log(-(b/ks)) - ks - 1)
+__global__ void __launch_bounds__(256)
+gpd_profile_kernel(const double* __restrict__ x, const long long* __restrict__ counts,
+                   double* __restrict__ bs, double* __restrict__ L) {
+    __shared__ double scratch[32];
+    const long long n = counts[0], m = counts[2];
+    const long long j = blockIdx.x;
+    if (counts[3] == 0 || j >= m) return;
+    const double x_q = x[(long long)((double)n / 4.0 + 0.5) - 1];
+    const double x_max = x[n - 1];
+    const double b = gpd_b(j, m, x_q, x_max);
+    double s = 0.0;
+    for (long long r = threadIdx.x; r < n; r += blockDim.x) s += log1p(-b * x[r]);
+    s = block_sum(s, scratch);
+    if (threadIdx.x == 0) {
+        const double ks = s / (double)n;
+        bs[j] = b;
+        L[j] = (double)n * (log(-(b / ks)) - ks - 1.0);
+    }
+}
+// single CTA: quadrature weights, posterior mean of b (psis.py:294-308)
+__global__ void __launch_bounds__(1024)
+gpd_weights_kernel(const long long* __restrict__ counts, const double* __restrict__ bs, const double* __restrict__ L,
+                   double* __restrict__ w_scratch, double* __restrict__ state) {
+    __shared__ double scratch[32];
+    const long long m = counts[2];
+    if (counts[3] == 0) return;
+    // w_j = 1 / sum_i exp(L_i - L_j)
+    for (long long j = threadIdx.x; j < m; j += blockDim.x) {
+        double s = 0.0;
+        const double Lj = L[j];
+        for (long long i = 0; i < m; ++i) s += exp(L[i] - Lj);
+        w_scratch[j] = 1.0 / s;
+    }
+    __syncthreads();
+    double sw = 0.0, sbw = 0.0;
+    for (long long j = threadIdx.x; j < m; j += blockDim.x) {
+        const double w = w_scratch[j];
+        if (w >= 10.0 * DBL_EPSILON) { sw += w; sbw += bs[j] * w; }      // psis.py:300-305
+    }
+    sw = block_sum(sw, scratch);
+    sbw = block_sum(sbw, scratch);
+    if (threadIdx.x == 0) state[6] = sbw / sw;                            // b, psis.py:308
+}
+// partial sums of log1p(-b x_r)
+__global__ void __launch_bounds__(256)
+gpd_k_blocks_kernel(const double* __restrict__ x, const long long* __restrict__ counts, const double* __restrict__ state,
+                    double* __restrict__ block_out) {
+    __shared__ double scratch[32];
+    const long long n = counts[0];
+    const double b = state[6];
+    double s = 0.0;
+    if (counts[3] != 0)
+        for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < n;
+             r += (long long)gridDim.x * blockDim.x)
+            s += log1p(-b * x[r]);
+    s = block_sum(s, scratch);
+    if (threadIdx.x == 0) block_out[blockIdx.x] = s;
+}
+__global__ void gpd_k_finish_kernel(const long long* __restrict__ counts, const double* __restrict__ blocks, int G,
+                                    double* __restrict__ state) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const long long n = counts[0];
+    if (counts[3] == 0) {                                                 // psis.py:177-179
+        state[2] = INFINITY; state[3] = NAN; state[4] = 0.0;
+        return;
+    }
+    double s = 0.0;
+    for (int g = 0; g < G; ++g) s += blocks[g];
+    double k = s / (double)n;                                             // psis.py:311-313
+    const double b = state[6];
+    const double sigma = -k / b * (double)n / (double)(n - 0);            // psis.py:320
+    const double a = 10.0;
+    k = k * (double)n / ((double)n + a) + a * 0.5 / ((double)n + a);      // psis.py:322-323
+    state[2] = k;
+    state[3] = sigma;
+    state[4] = (k >= 1.0 / 3.0 && !isinf(k)) ? 1.0 : 0.0;                 // psis.py:187 (NaN compares false)
+}
+
+// gpinv for p strictly inside (0,1) (psis.py:342-351)
+__device__ __forceinline__ double gpinv_inside(double p, double k, double sigma) {
+    if (!(sigma > 0.0)) return NAN;                                       // psis.py:338-339
+    double t = log1p(-p);
+    if (fabs(k) < DBL_EPSILON) t = -t;
+    else t = expm1(-k * t) / k;
+    return t * sigma;
+}
+
+// new tail values (psis.py:190-198) or the raw ones, and partial sums of exp(value)
+__global__ void __launch_bounds__(256)
+tail_smooth_kernel(const Cand* __restrict__ sorted, const double* __restrict__ state,
+                   const long long* __restrict__ counts, double* __restrict__ tail_new,
+                   long long* __restrict__ tail_idx_or_null, double* __restrict__ block_out) {
+    __shared__ double scratch[32];
+    const long long n2 = counts[0], p = counts[1];
+    const bool smoothed = state[4] != 0.0;
+    const double k = state[2], sigma = state[3], ec = state[1];
+    double s = 0.0;
+    for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < n2;
+         r += (long long)gridDim.x * blockDim.x) {
+        const Cand c = sorted[p + r];
+        double v;
+        if (smoothed) {
+            const double pr = ((double)r + 0.5) / (double)n2;
+            v = log(gpinv_inside(pr, k, sigma) + ec);
+            if (v > 0.0) v = 0.0;                                         // psis.py:198
+        } else {
+            v = -key_to_u(c.key);
+        }
+        tail_new[r] = v;
+        if (tail_idx_or_null) tail_idx_or_null[r] = (long long)c.idx;
+        s += exp(v);
+    }
+    s = block_sum(s, scratch);
+    if (threadIdx.x == 0) block_out[blockIdx.x] = s;
+}
+// body candidates (sorted positions [0, p)) contribute exp(-u)
+__global__ void __launch_bounds__(256)
+cand_body_kernel(const Cand* __restrict__ sorted, const long long* __restrict__ counts, long long skip_idx_lo,
+                 long long skip_idx_hi, double* __restrict__ block_out) {
+    __shared__ double scratch[32];
+    const long long p = counts[1];
+    double s = 0.0;
+    for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < p;
+         r += (long long)gridDim.x * blockDim.x) {
+        const Cand c = sorted[r];
+        const long long gi = (long long)c.idx;
+        if (gi >= skip_idx_lo && gi < skip_idx_hi) s += exp(-key_to_u(c.key));
+    }
+    s = block_sum(s, scratch);
+    if (threadIdx.x == 0) block_out[blockIdx.x] = s;
+}
+
+struct SumList { const double* p[4]; int n[4]; };
+// lse = log(sum of all partial lists) (fixed order); fills the diag vector
+__global__ void psis_finish_kernel(SumList lists, const double* __restrict__ M_ptr, const long long* __restrict__ counts,
+                                   long long n_cand, double* __restrict__ state, double* __restrict__ diag,
+                                   double* __restrict__ lse_partial_or_null) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    double total = 0.0;
+    for (int l = 0; l < 4; ++l)
+        for (int i = 0; i < lists.n[l]; ++i) total += lists.p[l][i];
+    if (lse_partial_or_null) { lse_partial_or_null[0] = 0.0; lse_partial_or_null[1] = total; }
+    const double lse = log(total);
+    state[5] = lse;
+    if (diag) {
+        diag[0] = state[2]; diag[1] = state[3]; diag[2] = state[0]; diag[3] = (double)counts[0];
+        diag[4] = state[4]; diag[5] = *M_ptr; diag[6] = lse; diag[7] = (double)n_cand;
+    }
+}
+
+// P3: out = (x - max) - lse   (psis.py:165, 200)
+__global__ void __launch_bounds__(256)
+normalise_kernel(const double* __restrict__ lw, double* __restrict__ out, long long n, const double* __restrict__ M_ptr,
+                 const double* __restrict__ lse_ptr) {
+    const double M = *M_ptr, lse = *lse_ptr;
+    const long long gtid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    const long long gthreads = (long long)gridDim.x * blockDim.x;
+    if (((reinterpret_cast<uintptr_t>(lw) | reinterpret_cast<uintptr_t>(out)) & 15u) == 0) {
+        const long long n2 = n >> 1;
+        const double2* p = reinterpret_cast<const double2*>(lw);
+        double2* q = reinterpret_cast<double2*>(out);
+        long long i = gtid;
+        for (; i + 3 * gthreads < n2; i += 4 * gthreads) {
+            double2 v0 = ld_stream2(p + i), v1 = ld_stream2(p + i + gthreads);
+            double2 v2 = ld_stream2(p + i + 2 * gthreads), v3 = ld_stream2(p + i + 3 * gthreads);
+            v0.x = (v0.x - M) - lse; v0.y = (v0.y - M) - lse; v1.x = (v1.x - M) - lse; v1.y = (v1.y - M) - lse;
+            v2.x = (v2.x - M) - lse; v2.y = (v2.y - M) - lse; v3.x = (v3.x - M) - lse; v3.y = (v3.y - M) - lse;
+            q[i] = v0; q[i + gthreads] = v1; q[i + 2 * gthreads] = v2; q[i + 3 * gthreads] = v3;
+        }
+        for (; i < n2; i += gthreads) {
+            double2 v = ld_stream2(p + i);
+            v.x = (v.x - M) - lse; v.y = (v.y - M) - lse;
+            q[i] = v;
+        }
+        if ((n & 1) && gtid == 0) out[n - 1] = (lw[n - 1] - M) - lse;
+    } else {
+        for (long long i = gtid; i < n; i += gthreads) out[i] = (lw[i] - M) - lse;
+    }
+}
+__global__ void tail_scatter_kernel(const Cand* __restrict__ sorted, const long long* __restrict__ counts,
+                                    const double* __restrict__ tail_new, const double* __restrict__ state,
+                                    double* __restrict__ out, long long index0, long long n_local) {
+    if (state[4] == 0.0) return;                 // not smoothed: P3 already wrote x - max - lse
+    const long long n2 = counts[0], p = counts[1];
+    const double lse = state[5];
+    for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < n2;
+         r += (long long)gridDim.x * blockDim.x) {
+        const long long li = (long long)sorted[p + r].idx - index0;
+        if (li >= 0 && li < n_local) out[li] = tail_new[r] - lse;
+    }
+}
+
+// ------------------------------------------------------------------------------------------ host orchestration
+static long long psis_K1(long long n, double reff) {
+    return (long long)ceil(fmin(0.2 * (double)n, 3.0 * sqrt((double)n / reff)));     // psis.py:157
+}
+
+struct PsisLayout {
+    long long cap1, cap2;
+    int g_pre, g_small;
+    size_t off_M, off_pivot, off_counters, off_state, off_counts, off_hist, off_sample, off_cand1, off_cand2,
+        off_x2, off_tailnew, off_bs, off_L, off_w, off_blk_pre, off_blk2, off_blk3, off_blk4, off_blk5, total;
+};
+static PsisLayout psis_layout(long long n, double reff) {
+    PsisLayout L;
+    const long long K1 = psis_K1(n, reff);
+    // candidate buffers: the whole array for small n, otherwise max(2 Mi, n/16) pairs
+    L.cap1 = (n <= kDirectSortMax) ? n : ((n / 16 > (1ll << 21)) ? n / 16 : (1ll << 21));
+    if (L.cap1 > n) L.cap1 = n;
+    if (L.cap1 < K1 + 1) L.cap1 = K1 + 1;
+    L.cap2 = pad_pow2(L.cap1);
+    L.g_pre = grid_for(n, 256, kNumSMs * 8);
+    L.g_small = kNumSMs * 2;
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t at = o; o += align_up(bytes, 256); return at; };
+    L.off_M = take(8);
+    L.off_pivot = take(8);
+    L.off_counters = take(4 * 8);
+    L.off_state = take(8 * 8);
+    L.off_counts = take(4 * 8);
+    L.off_hist = take((size_t)kHistBins * 4);
+    L.off_sample = take((size_t)kSampleSize * sizeof(Cand));
+    L.off_cand1 = take((size_t)L.cap1 * sizeof(Cand));
+    L.off_cand2 = take((size_t)L.cap2 * sizeof(Cand));
+    L.off_x2 = take((size_t)(K1 + 1) * 8);
+    L.off_tailnew = take((size_t)(K1 + 1) * 8);
+    const long long m_max = 30 + (long long)sqrt((double)(K1 + 1)) + 1;
+    L.off_bs = take((size_t)m_max * 8);
+    L.off_L = take((size_t)m_max * 8);
+    L.off_w = take((size_t)m_max * 8);
+    L.off_blk_pre = take((size_t)L.g_pre * 8);
+    L.off_blk2 = take((size_t)L.g_small * 8);
+    L.off_blk3 = take((size_t)L.g_small * 8);
+    L.off_blk4 = take((size_t)L.g_small * 8);
+    L.off_blk5 = take((size_t)L.g_small * 8);
+    L.total = o;
+    return L;
+}
+
+// GPD fit on an ascending device array; n2 and m are read from counts[] on the device.
+static int run_gpd_fit(const double* x2, const long long* counts, long long n2_upper, double* bs, double* Lq,
+                       double* wq, double* blk, int g_small, double* state, cudaStream_t st) {
+    const long long m_max = 30 + (long long)sqrt((double)n2_upper) + 1;
+    gpd_profile_kernel<<<(unsigned)m_max, 256, 0, st>>>(x2, counts, bs, Lq);
+    VB_LAUNCH_CHECK();
+    gpd_weights_kernel<<<1, 1024, 0, st>>>(counts, bs, Lq, wq, state);
+    VB_LAUNCH_CHECK();
+    gpd_k_blocks_kernel<<<g_small, 256, 0, st>>>(x2, counts, state, blk);
+    VB_LAUNCH_CHECK();
+    gpd_k_finish_kernel<<<1, 32, 0, st>>>(counts, blk, g_small, state);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+
+extern "C" int vb_max(const double* d_x, long long n, double* d_out, void* d_ws, size_t ws_bytes, void* stream);
+extern "C" size_t vb_max_workspace_bytes(long long n);
+
+}  // namespace vb
+
+using namespace vb;
+
+extern "C" long long vb_psis_tail_capacity(long long n, double reff) {
+    if (n < 2 || !(reff > 0.0)) return 0;
+    return psis_K1(n, reff);
+}
+
+extern "C" size_t vb_psis_smooth_workspace_bytes(long long n, double reff) {
+    if (n < 2 || !(reff > 0.0)) return 0;
+    return psis_layout(n, reff).total + vb_max_workspace_bytes(n) + 256;
+}
+
+extern "C" int vb_psis_smooth(const double* d_lw_in, double* d_lw_out, long long n, double reff,
+                              double* d_out_diag, long long* d_out_tail_idx_or_null,
+                              void* d_ws, size_t ws_bytes, void* stream) {
+    if (!d_lw_in || !d_lw_out || !d_out_diag || !d_ws || !(reff > 0.0)) return VB_ERR_ARG;
+    if (n <= 1) return VB_ERR_ARG;                                    // psis.py:143-144
+    if (d_lw_in == d_lw_out) return VB_ERR_ARG;                       // streaming loads assume no aliasing
+    const PsisLayout L = psis_layout(n, reff);
+    if (ws_bytes < L.total + vb_max_workspace_bytes(n) + 256) return VB_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    char* ws = (char*)d_ws;
+    double* M_ptr = (double*)(ws + L.off_M);
+    double* pivot_ptr = (double*)(ws + L.off_pivot);
+    unsigned long long* counters = (unsigned long long*)(ws + L.off_counters);
+    double* state = (double*)(ws + L.off_state);
+    long long* counts = (long long*)(ws + L.off_counts);
+    unsigned int* hist = (unsigned int*)(ws + L.off_hist);
+    Cand* sample = (Cand*)(ws + L.off_sample);
+    Cand* cand1 = (Cand*)(ws + L.off_cand1);
+    Cand* cand2 = (Cand*)(ws + L.off_cand2);
+    double* x2 = (double*)(ws + L.off_x2);
+    double* tail_new = (double*)(ws + L.off_tailnew);
+    double* bs = (double*)(ws + L.off_bs);
+    double* Lq = (double*)(ws + L.off_L);
+    double* wq = (double*)(ws + L.off_w);
+    double* blk_pre = (double*)(ws + L.off_blk_pre);
+    double* blk2 = (double*)(ws + L.off_blk2);
+    double* blk3 = (double*)(ws + L.off_blk3);
+    double* blk4 = (double*)(ws + L.off_blk4);
+    double* blk5 = (double*)(ws + L.off_blk5);
+    void* max_ws = ws + L.total;
+    const long long K1 = psis_K1(n, reff);
+
+    // P1: max
+    int rc = vb_max(d_lw_in, n, M_ptr, max_ws, vb_max_workspace_bytes(n), stream);
+    if (rc != VB_OK) return rc;
+
+    // P2: prefilter, escalating the sample quantile until the candidates hold the K1+1 largest
+    const bool direct = (n <= kDirectSortMax);
+    if (!direct) {
+        sample_kernel<<<16, 256, 0, st>>>(d_lw_in, n, M_ptr, sample);
+        VB_LAUNCH_CHECK();
+        rc = bitonic_sort(sample, kSampleSize, st);
+        if (rc != VB_OK) return rc;
+    }
+    unsigned long long h_counters[4];
+    long long C1 = 0;
+    double frac = 4.0 * (double)(K1 + 1) / (double)n;
+    if (frac < 0.01) frac = 0.01;
+    for (int attempt = 0;; ++attempt) {
+        if (direct) {
+            set_double_kernel<<<1, 1, 0, st>>>(pivot_ptr, INFINITY);
+        } else {
+            const int rank = (int)ceil(frac * kSampleSize);
+            pivot_kernel<<<1, 1, 0, st>>>(sample, rank, pivot_ptr);
+        }
+        VB_LAUNCH_CHECK();
+        VB_CUDA_TRY(cudaMemsetAsync(counters, 0, 4 * 8, st));
+        PrefilterOut po{cand1, L.cap1, counters, blk_pre};
+        prefilter_kernel<<<L.g_pre, 256, 0, st>>>(d_lw_in, n, 0, M_ptr, pivot_ptr, po);
+        VB_LAUNCH_CHECK();
+        VB_CUDA_TRY(cudaMemcpyAsync(h_counters, counters, 8, cudaMemcpyDeviceToHost, st));
+        VB_CUDA_TRY(cudaStreamSynchronize(st));
+        C1 = (long long)h_counters[0];
+        if (C1 >= K1 + 1 && C1 <= L.cap1) break;
+        if (direct || attempt >= 8) return VB_ERR_UNSUPPORTED;       // cannot happen for direct
+        if (C1 > L.cap1) {
+            // more ties at the top than the candidate buffer holds
+            return VB_ERR_UNSUPPORTED;
+        }
+        frac *= 4.0;                                                  // too few: widen the prefilter
+        if (frac > 1.0) frac = 1.0;
+    }
+
+    // optional refinement so that the sort stays small
+    Cand* sort_buf = cand2;
+    long long C2 = C1;
+    int n_blk2 = 0;
+    if (C1 > kDirectSortMax) {
+        VB_CUDA_TRY(cudaMemsetAsync(hist, 0, (size_t)kHistBins * 4, st));
+        hist_kernel<<<grid_for(C1, 256, kNumSMs * 4), 256, 0, st>>>(cand1, C1, pivot_ptr, hist);
+        VB_LAUNCH_CHECK();
+        hist_scan_kernel<<<1, 1024, 0, st>>>(hist, K1 + 1, counts + 2);
+        VB_LAUNCH_CHECK();
+        compact2_kernel<<<L.g_small, 256, 0, st>>>(cand1, C1, pivot_ptr, counts + 2, cand2, counters + 1, blk2);
+        VB_LAUNCH_CHECK();
+        n_blk2 = L.g_small;
+        VB_CUDA_TRY(cudaMemcpyAsync(h_counters, counters + 1, 8, cudaMemcpyDeviceToHost, st));
+        VB_CUDA_TRY(cudaStreamSynchronize(st));
+        C2 = (long long)h_counters[0];
+        if (C2 < K1 + 1 || C2 > C1) return VB_ERR_UNSUPPORTED;
+    } else {
+        VB_CUDA_TRY(cudaMemcpyAsync(cand2, cand1, (size_t)C1 * sizeof(Cand), cudaMemcpyDeviceToDevice, st));
+    }
+
+    // S: sort candidates ascending by (shifted weight, index)
+    const long long n_pad = pad_pow2(C2);
+    pad_cands_kernel<<<grid_for(n_pad - C2 + 1, 256, kNumSMs * 4), 256, 0, st>>>(sort_buf, C2, n_pad);
+    VB_LAUNCH_CHECK();
+    rc = bitonic_sort(sort_buf, n_pad, st);
+    if (rc != VB_OK) return rc;
+
+    // T: cutoff, tail, GPD fit, smoothing
+    tail_bounds_kernel<<<1, 1, 0, st>>>(sort_buf, C2, K1, state, counts);
+    VB_LAUNCH_CHECK();
+    tail_excess_kernel<<<L.g_small, 256, 0, st>>>(sort_buf, state, counts, x2);
+    VB_LAUNCH_CHECK();
+    rc = run_gpd_fit(x2, counts, K1 + 1, bs, Lq, wq, blk3, L.g_small, state, st);
+    if (rc != VB_OK) return rc;
+    tail_smooth_kernel<<<L.g_small, 256, 0, st>>>(sort_buf, state, counts, tail_new, d_out_tail_idx_or_null, blk4);
+    VB_LAUNCH_CHECK();
+    cand_body_kernel<<<L.g_small, 256, 0, st>>>(sort_buf, counts, 0, n, blk5);
+    VB_LAUNCH_CHECK();
+    SumList lists;
+    lists.p[0] = blk_pre; lists.n[0] = L.g_pre;
+    lists.p[1] = blk2;    lists.n[1] = n_blk2;
+    lists.p[2] = blk5;    lists.n[2] = L.g_small;
+    lists.p[3] = blk4;    lists.n[3] = L.g_small;
+    psis_finish_kernel<<<1, 1, 0, st>>>(lists, M_ptr, counts, C2, state, d_out_diag, nullptr);
+    VB_LAUNCH_CHECK();
+
+    // P3: normalise and scatter the smoothed tail
+    normalise_kernel<<<grid_for((n + 1) / 2, 256, kNumSMs * 8), 256, 0, st>>>(d_lw_in, d_lw_out, n, M_ptr, state + 5);
+    VB_LAUNCH_CHECK();
+    tail_scatter_kernel<<<L.g_small, 256, 0, st>>>(sort_buf, counts, tail_new, state, d_lw_out, 0, n);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+
+// ------------------------------------------------------------------------------------------ standalone ops
+extern "C" size_t vb_gpd_fit_workspace_bytes(long long n) {
+    if (n < 2) return 0;
+    const long long m_max = 30 + (long long)sqrt((double)n) + 1;
+    return 256 + 256 + 3 * align_up((size_t)m_max * 8, 256) + align_up((size_t)kNumSMs * 2 * 8, 256);
+}
+
+extern "C" int vb_gpd_fit(const double* d_x_sorted, long long n, double* d_out_k_sigma,
+                          void* d_ws, size_t ws_bytes, void* stream) {
+    if (!d_x_sorted || !d_out_k_sigma || !d_ws || n <= 1) return VB_ERR_ARG;   // psis.py:250-251
+    if (ws_bytes < vb_gpd_fit_workspace_bytes(n)) return VB_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    char* ws = (char*)d_ws;
+    const long long m_max = 30 + (long long)sqrt((double)n) + 1;
+    const size_t mb = align_up((size_t)m_max * 8, 256);
+    double* state = (double*)ws;
+    long long* counts = (long long*)(ws + 256);
+    double* bs = (double*)(ws + 512);
+    double* Lq = (double*)(ws + 512 + mb);
+    double* wq = (double*)(ws + 512 + 2 * mb);
+    double* blk = (double*)(ws + 512 + 3 * mb);
+    // gpdfitnew itself has no n <= 4 shortcut (that lives in psislw): always fit
+    set_counts_kernel<<<1, 1, 0, st>>>(counts, n, 0, 30 + (long long)sqrt((double)n), 1);
+    VB_LAUNCH_CHECK();
+    int rc = run_gpd_fit(d_x_sorted, counts, n, bs, Lq, wq, blk, kNumSMs * 2, state, st);
+    if (rc != VB_OK) return rc;
+    VB_CUDA_TRY(cudaMemcpyAsync(d_out_k_sigma, state + 2, 16, cudaMemcpyDeviceToDevice, st));
+    return VB_OK;
+}
+
+namespace vb {
+__global__ void gpd_inv_kernel(const double* __restrict__ p, long long n, double k, double sigma, double* __restrict__ out) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const double pi = p[i];
+        double v;
+        if (!(sigma > 0.0)) v = NAN;
+        else if (pi > 0.0 && pi < 1.0) v = gpinv_inside(pi, k, sigma);
+        else if (pi == 0.0) v = 0.0;                                       // psis.py:372
+        else if (pi == 1.0) v = (k >= 0.0) ? INFINITY : -sigma / k;        // psis.py:373-376
+        else v = NAN * sigma;
+        out[i] = v;
+    }
+}
+__global__ void __launch_bounds__(256)
+expsum_blocks_kernel(const double* __restrict__ x, long long n, const double* __restrict__ M_ptr, double* __restrict__ block_out) {
+    __shared__ double scratch[32];
+    const double M = *M_ptr;
+    double s = 0.0;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        s += exp(x[i] - M);
+    s = block_sum(s, scratch);
+    if (threadIdx.x == 0) block_out[blockIdx.x] = s;
+}
+__global__ void lse_finish_kernel(const double* __restrict__ blocks, int G, const double* __restrict__ M_ptr, double* __restrict__ out) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    double s = 0.0;
+    for (int g = 0; g < G; ++g) s += blocks[g];
+    *out = log(s) + *M_ptr;                                                // psis.py:387-394
+}
+__global__ void sub_scalar_kernel(double* __restrict__ x, long long n, double v) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        x[i] -= v;
+}
+}  // namespace vb
+
+extern "C" int vb_gpd_inv(const double* d_p, long long n, double k, double sigma, double* d_out, void* stream) {
+    if (!d_p || !d_out || n < 1) return VB_ERR_ARG;
+    gpd_inv_kernel<<<grid_for(n, 256, kNumSMs * 8), 256, 0, (cudaStream_t)stream>>>(d_p, n, k, sigma, d_out);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+
+extern "C" size_t vb_logsumexp_workspace_bytes(long long n) {
+    return 256 + (size_t)kNumSMs * 8 * 8 + 256 + vb_max_workspace_bytes(n);
+}
+
+extern "C" int vb_logsumexp(const double* d_x, long long n, double* d_out, void* d_ws, size_t ws_bytes, void* stream) {
+    if (!d_x || !d_out || !d_ws || n < 1) return VB_ERR_ARG;
+    if (ws_bytes < vb_logsumexp_workspace_bytes(n)) return VB_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    char* ws = (char*)d_ws;
+    double* M_ptr = (double*)ws;
+    double* blocks = (double*)(ws + 256);
+    void* max_ws = ws + 256 + (size_t)kNumSMs * 8 * 8 + 256;
+    int rc = vb_max(d_x, n, M_ptr, (char*)max_ws, vb_max_workspace_bytes(n), stream);
+    if (rc != VB_OK) return rc;
+    const int G = grid_for(n, 256, kNumSMs * 8);
+    expsum_blocks_kernel<<<G, 256, 0, st>>>(d_x, n, M_ptr, blocks);
+    VB_LAUNCH_CHECK();
+    lse_finish_kernel<<<1, 1, 0, st>>>(blocks, G, M_ptr, d_out);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+
+extern "C" int vb_psis_normalise(double* d_lw_out, long long n_local, double lse, void* stream) {
+    if (!d_lw_out || n_local < 1) return VB_ERR_ARG;
+    sub_scalar_kernel<<<grid_for(n_local, 256, kNumSMs * 8), 256, 0, (cudaStream_t)stream>>>(d_lw_out, n_local, lse);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}

@@ -1,0 +1,147 @@
+"""Drop-in for the PSIS functions of ``notebooks/psis.py`` (``psislw``, ``gpdfitnew``,
+``gpinv``, ``sumlogs``) on the device (``csrc/psis.cu``).
+
+Tie-break contract: where the reference's ``np.argsort`` (default, unstable kind;
+``psis.py:167,182``) leaves the order of equal tail values to the numpy build, this
+implementation orders them by ascending original index (== ``kind='stable'``).
+"""
+import numpy as np
+import torch
+
+from . import _lib
+from ._device import WS, is_host, like_input, ptr, stream_ptr, to_dev
+
+__all__ = ['psislw', 'psislw_detail', 'gpdfitnew', 'gpinv', 'sumlogs']
+
+
+def _smooth_1d(col, Reff, want_tail=False):
+    """col: CUDA f64 (n,) contiguous -> (smoothed (n,), diag (8,) numpy, tail idx or None)."""
+    n = col.numel()
+    out = torch.empty_like(col)
+    diag = torch.empty(8, dtype=torch.float64, device=col.device)
+    tail = None
+    if want_tail:
+        cap = max(int(_lib.lib.vb_psis_tail_capacity(n, float(Reff))), 1)
+        tail = torch.full((cap,), -1, dtype=torch.int64, device=col.device)
+    ws = WS.get('psis', _lib.lib.vb_psis_smooth_workspace_bytes(n, float(Reff)))
+    _lib.check(_lib.lib.vb_psis_smooth(ptr(col), ptr(out), n, float(Reff), ptr(diag), ptr(tail), ptr(ws),
+                                       ws.numel(), stream_ptr()), 'vb_psis_smooth')
+    return out, diag.cpu().numpy(), tail
+
+
+def psislw(lw, Reff=1.0, overwrite_lw=False):
+    """Pareto smoothed importance sampling (``psis.py:112-208``).
+
+    ``lw``: (n,) or (n, m) log weights, numpy or CUDA tensor.  Returns ``(lw_out, kss)`` with
+    ``kss`` a float for 1-D input and an (m,) numpy array otherwise.  ``overwrite_lw`` smooths
+    a CUDA tensor / F-contiguous numpy array in place like the reference does."""
+    if lw.ndim == 2:
+        n, m = lw.shape
+    elif lw.ndim == 1:
+        n, m = len(lw), 1
+    else:
+        raise ValueError("Argument `lw` must be 1 or 2 dimensional.")
+    if n <= 1:
+        raise ValueError("More than one log-weight needed.")
+    dev = to_dev(lw, _lib.F64)
+    kss = np.empty(m)
+    if lw.ndim == 1:
+        out, diag, _ = _smooth_1d(dev.contiguous(), Reff)
+        kss = diag[0]
+    else:
+        cols = dev.t().contiguous()                      # (m, n): one contiguous row per weight set
+        outs = []
+        for i in range(m):
+            o, diag, _ = _smooth_1d(cols[i], Reff)
+            outs.append(o)
+            kss[i] = diag[0]
+        out = torch.stack(outs, dim=1)
+    if is_host(lw):
+        res = out.cpu().numpy()
+        if lw.ndim == 2:
+            res = np.asfortranarray(res)                 # psis.py:151 allocates F-order
+        if overwrite_lw and isinstance(lw, np.ndarray) and lw.flags.f_contiguous:
+            lw[...] = res                                # psis.py:146-148
+            res = lw
+        return res, kss
+    if overwrite_lw:
+        lw.copy_(out)
+        out = lw
+    return out, kss
+
+
+def psislw_detail(lw, Reff=1.0):
+    """1-D ``psislw`` that also returns the tail bookkeeping used by the parity tests:
+    dict(k, sigma, xcutoff, n2, smoothed, max, lse, tail_idx_sorted) where
+    ``tail_idx_sorted[r]`` is the original index of the r-th smallest tail element
+    (``tailinds[x2si]`` in ``psis.py:196``)."""
+    if lw.ndim != 1:
+        raise ValueError('psislw_detail takes a 1-D array')
+    if len(lw) <= 1:
+        raise ValueError("More than one log-weight needed.")
+    dev = to_dev(lw, _lib.F64).contiguous()
+    out, diag, tail = _smooth_1d(dev, Reff, want_tail=True)
+    n2 = int(diag[3])
+    detail = dict(k=diag[0], sigma=diag[1], xcutoff=diag[2], n2=n2, smoothed=bool(diag[4]), max=diag[5],
+                  lse=diag[6], n_candidates=int(diag[7]), tail_idx_sorted=tail[:n2].cpu().numpy())
+    return like_input(out, lw), diag[0], detail
+
+
+def gpdfitnew(x, sort=True, sort_in_place=False, return_quadrature=False):
+    """Zhang–Stephens GPD fit (``psis.py:211-331``): returns ``(k, sigma)``."""
+    if x.ndim != 1 or len(x) <= 1:
+        raise ValueError("Invalid input array.")
+    if return_quadrature:
+        raise NotImplementedError('return_quadrature is not part of the CUDA path')
+    dev = to_dev(x, _lib.F64)
+    if sort is False:
+        xs = dev.contiguous()
+    elif sort is True:
+        xs = torch.sort(dev).values
+        if sort_in_place and isinstance(x, np.ndarray):
+            x.sort()
+    else:
+        idx = torch.as_tensor(np.asarray(sort) if not isinstance(sort, torch.Tensor) else sort, device=dev.device)
+        xs = dev[idx.long()].contiguous()
+    n = xs.numel()
+    if n <= 4:
+        raise NotImplementedError('the CUDA GPD fit needs more than 4 points (psislw never calls it with fewer)')
+    out = torch.empty(2, dtype=torch.float64, device=xs.device)
+    ws = WS.get('gpdfit', _lib.lib.vb_gpd_fit_workspace_bytes(n))
+    _lib.check(_lib.lib.vb_gpd_fit(ptr(xs), n, ptr(out), ptr(ws), ws.numel(), stream_ptr()), 'vb_gpd_fit')
+    k, sigma = out.cpu().numpy()
+    return k, sigma
+
+
+def gpinv(p, k, sigma):
+    """Inverse generalised Pareto CDF (``psis.py:334-376``)."""
+    dev = to_dev(p, _lib.F64).contiguous()
+    out = torch.empty_like(dev)
+    if dev.numel():
+        _lib.check(_lib.lib.vb_gpd_inv(ptr(dev), dev.numel(), float(k), float(sigma), ptr(out), stream_ptr()),
+                   'vb_gpd_inv')
+    return like_input(out, p)
+
+
+def sumlogs(x, axis=None, out=None):
+    """``log(sum(exp(x)))`` (``psis.py:379-395``).  ``axis`` may be None (all elements) or 0 of a
+    2-D array (one value per column)."""
+    if out is not None:
+        raise NotImplementedError('out= is not supported')
+    dev = to_dev(x, _lib.F64)
+
+    def one(v):
+        v = v.contiguous().reshape(-1)
+        res = torch.empty(1, dtype=torch.float64, device=v.device)
+        ws = WS.get('lse', _lib.lib.vb_logsumexp_workspace_bytes(v.numel()))
+        _lib.check(_lib.lib.vb_logsumexp(ptr(v), v.numel(), ptr(res), ptr(ws), ws.numel(), stream_ptr()),
+                   'vb_logsumexp')
+        return res
+
+    if axis is None or dev.ndim == 1:
+        r = one(dev)
+        return float(r.item()) if is_host(x) else r[0]
+    if axis == 0 and dev.ndim == 2:
+        r = torch.cat([one(dev[:, j]) for j in range(dev.shape[1])])
+        return like_input(r, x)
+    raise NotImplementedError('sumlogs supports axis=None or axis=0')

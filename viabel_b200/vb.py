@@ -1,0 +1,575 @@
+"""Drop-in for the Monte Carlo variational path of ``viabel/vb.py``.
+
+Same names, argument order, defaults, return types and error behaviour as the reference for
+
+* ``mean_field_gaussian_variational_family`` (``vb.py:48-82``)
+* ``mean_field_t_variational_family``        (``vb.py:140-182``)
+* ``t_variational_family``                   (``vb.py:192-233``, ``_distributions.py:8-38``)
+* ``black_box_klvi`` / ``black_box_chivi``   (``vb.py:236-266``)
+* ``adagrad_optimize`` / ``learning_rate_schedule`` (``vb.py:324-389``)
+
+What differs by design: ``logdensity`` must be a registered model plugin
+(``viabel_b200.models``) instead of an arbitrary autograd-traceable function, gradients are
+closed-form CUDA reductions instead of an autograd tape, and base draws come from a Philox
+counter stream (seed 0 per family, advancing once per ``seed=None`` call, mirroring the
+reference's persistent ``RandomState(0)``) unless supplied through ``base_draws=``.
+There is no CPU fallback.
+"""
+from collections import namedtuple
+import math
+
+import numpy as np
+import torch
+import tqdm
+
+from . import _lib
+from ._device import WS, Workspace, device, dtype_code, is_host, like_input, ptr, stream_ptr, to_dev, torch_dtype
+from .models import Model
+
+__all__ = [
+    'VariationalFamily',
+    'mean_field_gaussian_variational_family',
+    'mean_field_t_variational_family',
+    't_variational_family',
+    'black_box_klvi',
+    'black_box_chivi',
+    'adagrad_optimize',
+    'learning_rate_schedule',
+]
+
+_Fields = namedtuple('VariationalFamily',
+                     ['sample', 'entropy', 'logdensity', 'mean_and_cov', 'pth_moment', 'var_param_dim'])
+
+
+class VariationalFamily(_Fields):
+    """The reference's namedtuple (``vb.py:42-45``); ``impl`` carries what the fused objectives need."""
+    impl = None
+
+
+_LOG_2PI = math.log(2.0 * math.pi)
+
+
+def _host_param(var_param):
+    if isinstance(var_param, torch.Tensor):
+        return var_param.detach().cpu().numpy().astype(np.float64)
+    return np.asarray(var_param, dtype=np.float64)
+
+
+class _FamilyImpl:
+    """Host-side state of one family instance: kind, shape, compute dtype and the Philox stream."""
+
+    def __init__(self, kind, dim, df, dtype):
+        self.kind, self.dim, self.df = kind, int(dim), (0.0 if df is None else float(df))
+        self.code = dtype_code(dtype)
+        self.seed0, self.offset = 0, 0        # persistent stream, like RandomState(0) at vb.py:49,143,195
+        self.ws = Workspace()
+
+    def next_stream(self, seed):
+        """(seed, call offset) for one draw; ``seed=None`` advances the family's own stream."""
+        if seed is None:
+            off = self.offset
+            self.offset += 1
+            return self.seed0, off
+        return int(seed) & 0xFFFFFFFFFFFFFFFF, 0
+
+    def base_draws(self, n, seed, offset, index0=0):
+        """Philox base draws on the device: dict(eps=...) or dict(z=..., chi2=...)."""
+        dt = torch_dtype(self.code)
+        eps = torch.empty((n, self.dim), dtype=dt, device=device())
+        chi2 = torch.empty(n, dtype=dt, device=device()) if self.kind == _lib.FAMILY_FR_T else None
+        _lib.check(_lib.lib.vb_base_draws(self.kind, self.df, self.code, n, self.dim, seed, offset, index0,
+                                          ptr(eps), ptr(chi2), stream_ptr()), 'vb_base_draws')
+        if self.kind == _lib.FAMILY_FR_T:
+            return {'z': eps, 'chi2': chi2}
+        return {'eps': eps}
+
+    def coerce_base(self, base):
+        """External base draws (numpy or torch) -> device tensors of the compute dtype."""
+        if self.kind == _lib.FAMILY_FR_T:
+            z, c = to_dev(base['z'], self.code), to_dev(base['chi2'], self.code)
+            if z.ndim != 2 or z.shape[1] != self.dim or c.shape != (z.shape[0],):
+                raise ValueError('base draws must be z (n, dim) and chi2 (n,)')
+            return {'z': z, 'chi2': c}
+        eps = base['eps'] if isinstance(base, dict) else base
+        eps = to_dev(eps, self.code)
+        if eps.ndim != 2 or eps.shape[1] != self.dim:
+            raise ValueError('base draws must have shape (n, dim)')
+        return {'eps': eps}
+
+
+# =========================================================================== mean-field families
+def _mean_field_family(dim, df, dtype):
+    kind = _lib.FAMILY_MF_GAUSS if df is None else _lib.FAMILY_MF_T
+    impl = _FamilyImpl(kind, dim, df, dtype)
+
+    def unpack(var_param):
+        lam = _host_param(var_param)
+        return lam[:dim], lam[dim:]
+
+    def sample(var_param, n_samples, seed=None):
+        seed_, off = impl.next_stream(seed)
+        base = impl.base_draws(int(n_samples), seed_, off)
+        vp = to_dev(var_param, _lib.F64)
+        x = torch.empty_like(base['eps'])
+        _lib.check(_lib.lib.vb_mf_sample(impl.code, ptr(vp), int(n_samples), dim, ptr(base['eps']), ptr(x),
+                                         stream_ptr()), 'vb_mf_sample')
+        return like_input(x, var_param)
+
+    def entropy(var_param):
+        _, log_s = unpack(var_param)
+        if df is None:
+            return 0.5 * dim * (1.0 + _LOG_2PI) + np.sum(log_s)          # vb.py:61
+        return np.sum(log_s)                                             # vb.py:156 (df terms dropped)
+
+    def logdensity(x, var_param):
+        host = is_host(x)
+        xd = to_dev(x, impl.code if host else dtype_code(x.dtype))
+        code = dtype_code(xd.dtype)
+        one_d = xd.ndim == 1
+        if one_d:
+            xd = xd[None, :]
+        if xd.ndim != 2 or xd.shape[1] != dim:
+            raise ValueError('expected x of shape (n, %d)' % dim)
+        xd = xd.contiguous()
+        vp = to_dev(var_param, _lib.F64)
+        out = torch.empty(xd.shape[0], dtype=torch.float64, device=xd.device)
+        _lib.check(_lib.lib.vb_mf_logdensity(kind, impl.df, code, ptr(vp), xd.shape[0], dim, ptr(xd), ptr(out),
+                                             stream_ptr()), 'vb_mf_logdensity')
+        if one_d and df is None:          # mvn.logpdf of a single point is a scalar (vb.py:65)
+            out = out[0]
+        return like_input(out, x)
+
+    def mean_and_cov(var_param):
+        mean, log_s = unpack(var_param)
+        c = 1.0 if df is None else df / (df - 2)                        # vb.py:69,166
+        return mean, c * np.diag(np.exp(2 * log_s))
+
+    def pth_moment(p, var_param):
+        if p not in [2, 4]:
+            raise ValueError('only p = 2 or 4 supported')
+        if df is not None and df <= p:
+            raise ValueError('df must be greater than p')
+        _, log_s = unpack(var_param)
+        s2 = np.exp(2 * log_s)
+        if df is None:                                                   # vb.py:76-79
+            return np.sum(s2) if p == 2 else 2 * np.sum(s2 ** 2) + np.sum(s2) ** 2
+        c = df / (df - 2)                                                # vb.py:175-179
+        if p == 2:
+            return c * np.sum(s2)
+        return c ** 2 * (2 * (df - 1) / (df - 4) * np.sum(s2 ** 2) + np.sum(s2) ** 2)
+
+    fam = VariationalFamily(sample, entropy, logdensity, mean_and_cov, pth_moment, 2 * dim)
+    fam.impl = impl
+    return fam
+
+
+def mean_field_gaussian_variational_family(dim, dtype='f64'):
+    return _mean_field_family(dim, None, dtype)
+
+
+def mean_field_t_variational_family(dim, df, dtype='f64'):
+    if df <= 2:
+        raise ValueError('df must be greater than 2')
+    return _mean_field_family(dim, df, dtype)
+
+
+# =========================================================================== full-rank Student t
+class _FullRank(_FamilyImpl):
+    """Parameter chain of paragami's free (mu, Sigma) pattern (vb.py:185-189):
+    flat = [mu (d), row-major lower triangle of chol(Sigma) with log on the diagonal]."""
+
+    def __init__(self, dim, df, dtype, scale):
+        super().__init__(_lib.FAMILY_FR_T, dim, df, dtype)
+        if scale not in ('sqrtm', 'chol'):
+            raise ValueError("scale must be 'sqrtm' (reference) or 'chol'")
+        self.scale = scale
+        self.n_param = dim + dim * (dim + 1) // 2
+        self._tri = None
+
+    def tri(self):
+        if self._tri is None or self._tri[0].device != device():
+            idx = torch.tril_indices(self.dim, self.dim, device=device())
+            diag_pos = torch.cumsum(torch.arange(1, self.dim + 1, device=device()), 0) - 1
+            self._tri = (idx[0], idx[1], diag_pos)
+        return self._tri
+
+    def gemm(self, A, B, transa=False, transb=False):
+        """fp64 d x d product through the library's own GEMM."""
+        m = A.shape[1] if transa else A.shape[0]
+        k = A.shape[0] if transa else A.shape[1]
+        n = B.shape[0] if transb else B.shape[1]
+        Cm = torch.empty((m, n), dtype=torch.float64, device=A.device)
+        _lib.check(_lib.lib.vb_gemm(_lib.F64, int(transa), int(transb), m, n, k, 1.0, ptr(A), A.shape[1],
+                                    ptr(B), B.shape[1], 0.0, ptr(Cm), n, 0, 0, stream_ptr()), 'vb_gemm')
+        return Cm
+
+    def fold(self, vp):
+        """vp: device f64 (P,) -> mu, L, Sigma."""
+        d = self.dim
+        r, c, _ = self.tri()
+        L = torch.zeros((d, d), dtype=torch.float64, device=vp.device)
+        L[r, c] = vp[d:]
+        L.diagonal().exp_()
+        return vp[:d].contiguous(), L, self.gemm(L, L, transb=True)
+
+    def chain(self, vp):
+        """Everything of O(d^3) that a step needs."""
+        mu, L, Sigma = self.fold(vp)
+        out = {'mu': mu, 'L': L, 'Sigma': Sigma}
+        if self.scale == 'sqrtm':
+            # symmetric square root (scipy sqrtm in the reference, vb.py:207); the one library
+            # call on this path: cuSOLVER syevd through torch
+            lam, V = torch.linalg.eigh(Sigma)
+            root = lam.sqrt()
+            out.update(lam=lam, V=V, root=root, S=self.gemm(V * root, V, transb=True))
+        else:
+            out['S'] = L.T.contiguous()          # row form: x = mu + ztilde L'
+        return out
+
+    def scale_matrix(self, ch):
+        S = ch['S']
+        return S if self.code == _lib.F64 else S.to(torch.float32)
+
+    def pack_grad(self, ch, G_S):
+        """d/dphi of sum_i w_i log p(x_i) from G_S = Ztilde' diag(w) G  (SURVEY Appendix A.2)."""
+        r, c, diag_pos = self.tri()
+        L = ch['L']
+        if self.scale == 'sqrtm':
+            V, root = ch['V'], ch['root']
+            inner = self.gemm(self.gemm(V, G_S, transa=True), V) / (root[:, None] + root[None, :])
+            Y = self.gemm(self.gemm(V, inner), V, transb=True)          # Sylvester: S Y + Y S = G_S
+            G_L = self.gemm(Y + Y.T, L)
+        else:
+            G_L = G_S.T
+        phi = G_L[r, c].clone()
+        phi[diag_pos] *= L.diagonal()
+        return phi
+
+
+def t_variational_family(dim, df, dtype='f64', scale='sqrtm'):
+    if df <= 2:
+        raise ValueError('df must be greater than 2')
+    impl = _FullRank(dim, df, dtype, scale)
+
+    def sample_device(vp, base):
+        ch = impl.chain(vp)
+        n = base['z'].shape[0]
+        x = torch.empty_like(base['z'])
+        S = impl.scale_matrix(ch)
+        _lib.check(_lib.lib.vb_fr_sample(impl.code, ptr(ch['mu']), ptr(S), impl.df, n, dim, ptr(base['z']),
+                                         ptr(base['chi2']), ptr(x), 0, 0, stream_ptr()), 'vb_fr_sample')
+        return x, ch
+    impl.sample_device = sample_device
+
+    def sample(var_param, n_samples, seed=None):
+        seed_, off = impl.next_stream(seed)
+        base = impl.base_draws(int(n_samples), seed_, off)
+        x, _ = sample_device(to_dev(var_param, _lib.F64), base)
+        return like_input(x, var_param)
+
+    def entropy(var_param):
+        lam = _host_param(var_param)
+        diag_pos = np.cumsum(np.arange(1, dim + 1)) - 1
+        return np.sum(lam[dim:][diag_pos])               # 1/2 log det Sigma, vb.py:213
+
+    def _fold_host(var_param):
+        lam = _host_param(var_param)
+        L = np.zeros((dim, dim))
+        L[np.tril_indices(dim)] = lam[dim:]
+        L[np.diag_indices(dim)] = np.exp(np.diag(L))
+        return lam[:dim], L @ L.T
+
+    def logdensity(x, var_param):
+        host = is_host(x)
+        xd = to_dev(x, impl.code if host else dtype_code(x.dtype))
+        code = dtype_code(xd.dtype)
+        if xd.ndim == 1:
+            xd = xd[None, :]
+        xd = xd.contiguous()
+        vp = to_dev(var_param, _lib.F64)
+        mu, _, Sigma = impl.fold(vp)
+        s, u = torch.linalg.eigh(Sigma)                                  # _distributions.py:27
+        s_pinv = torch.where(s.abs() <= 1e-10, torch.zeros_like(s), 1.0 / s)
+        U = (u * s_pinv.sqrt()).contiguous()
+        log_pdet = float(torch.log(s).sum())
+        n = xd.shape[0]
+        out = torch.empty(n, dtype=torch.float64, device=xd.device)
+        ws = impl.ws.get('logdensity', _lib.lib.vb_fr_logdensity_workspace_bytes(n, dim))
+        _lib.check(_lib.lib.vb_fr_logdensity(code, ptr(mu), ptr(U), log_pdet, impl.df, n, dim, ptr(xd), ptr(out),
+                                             ptr(ws), ws.numel(), stream_ptr()), 'vb_fr_logdensity')
+        return like_input(out, x)
+
+    def mean_and_cov(var_param):
+        mu, Sigma = _fold_host(var_param)
+        return mu, df / (df - 2.) * Sigma                                # vb.py:217
+
+    def pth_moment(p, var_param):
+        if p not in [2, 4]:
+            raise ValueError('only p = 2 or 4 supported')
+        if df <= p:
+            raise ValueError('df must be greater than p')
+        _, Sigma = _fold_host(var_param)
+        ev = np.linalg.eigvalsh(Sigma)                                   # vb.py:225
+        c = df / (df - 2)
+        if p == 2:
+            return c * np.sum(ev)
+        return c ** 2 * (2 * (df - 1) / (df - 4) * np.sum(ev ** 2) + np.sum(ev) ** 2)
+
+    fam = VariationalFamily(sample, entropy, logdensity, mean_and_cov, pth_moment, impl.n_param)
+    fam.impl = impl
+    return fam
+
+
+# =========================================================================== objectives
+def _require_plugin(logdensity):
+    if not isinstance(logdensity, Model):
+        raise TypeError('logdensity must be a registered viabel_b200.models plugin (Funnel, NormalMixture, '
+                        'EightSchoolsNCP, StudentTRegression, CorrelatedGaussian); arbitrary Python '
+                        'callables have no CUDA path and there is no CPU fallback')
+    return logdensity
+
+
+def _dist_info(group):
+    """(rank, world) of the sample-sharding group, (0, 1) when not distributed."""
+    import torch.distributed as dist
+    if group is False or not dist.is_available() or not dist.is_initialized():
+        return 0, 1, None
+    g = None if group in (None, True) else group
+    return dist.get_rank(g), dist.get_world_size(g), g
+
+
+def _shard(n, rank, world):
+    """Contiguous split of n samples: (first global index, count) of this rank."""
+    base, rem = divmod(n, world)
+    count = base + (1 if rank < rem else 0)
+    start = rank * base + min(rank, rem)
+    return start, count
+
+
+class _Objective:
+    """One KLVI or CHIVI objective bound to (family, model, n_samples)."""
+
+    def __init__(self, objective, alpha, var_family, model, n_samples, group):
+        impl = getattr(var_family, 'impl', None)
+        if not isinstance(impl, _FamilyImpl):
+            raise TypeError('var_family must come from viabel_b200.vb')
+        self.obj, self.alpha = objective, float(alpha)
+        self.impl, self.model, self.n = impl, _require_plugin(model), int(n_samples)
+        if self.model.dim != impl.dim:
+            raise ValueError('model dimension %d != family dimension %d' % (self.model.dim, impl.dim))
+        self.group = group
+        self.P = var_family.var_param_dim
+        self.ws = Workspace()
+        self.last_partials = None
+
+    # ------------------------------------------------------------------ mean field
+    def _mf(self, vp, base, seed, off, index0, n_local, finalize):
+        impl, d = self.impl, self.impl.dim
+        NP = 2 * d + 4
+        out = torch.empty(1 + 2 * d, dtype=torch.float64, device=vp.device)
+        partials = torch.empty(NP, dtype=torch.float64, device=vp.device)
+        val_ptr = ptr(out) if finalize else 0
+        grad_ptr = ptr(out) + 8 if finalize else 0
+        if self.model.fused:
+            ws = self.ws.get('mf_step', _lib.lib.vb_mf_step_workspace_bytes(d))
+            _lib.check(_lib.lib.vb_mf_step(
+                impl.kind, impl.df, self.model.handle, self.obj, self.alpha, impl.code, ptr(vp), n_local,
+                ptr(base['eps']) if base is not None else 0, seed, off, index0,
+                val_ptr, grad_ptr, ptr(partials), ptr(ws), ws.numel(), stream_ptr()), 'vb_mf_step')
+        else:
+            if base is None:
+                base = impl.base_draws(n_local, seed, off, index0)
+            x = torch.empty_like(base['eps'])
+            _lib.check(_lib.lib.vb_mf_sample(impl.code, ptr(vp), n_local, d, ptr(base['eps']), ptr(x),
+                                             stream_ptr()), 'vb_mf_sample')
+            logp, g = self.model.logp_and_grad_device(x, impl.code, True)
+            ws = self.ws.get('mf_reduce', _lib.lib.vb_mf_reduce_workspace_bytes(n_local, d))
+            _lib.check(_lib.lib.vb_mf_reduce(
+                impl.kind, impl.df, self.obj, self.alpha, impl.code, ptr(vp), n_local, d, ptr(base['eps']),
+                ptr(logp), ptr(g), val_ptr, grad_ptr, ptr(partials), ptr(ws), ws.numel(), stream_ptr()),
+                'vb_mf_reduce')
+        return out, partials
+
+    def _mf_merge(self, vp, partials, world, g):
+        import torch.distributed as dist
+        d = self.impl.dim
+        gathered = torch.empty((world, partials.numel()), dtype=torch.float64, device=vp.device)
+        dist.all_gather_into_tensor(gathered, partials, group=g)
+        out = torch.empty(1 + 2 * d, dtype=torch.float64, device=vp.device)
+        _lib.check(_lib.lib.vb_mf_finalize(self.impl.kind, self.obj, self.alpha, ptr(vp), d, ptr(gathered), world,
+                                           ptr(out), ptr(out) + 8, stream_ptr()), 'vb_mf_finalize')
+        return out
+
+    # ------------------------------------------------------------------ full rank
+    def _fr(self, vp, base, n_total, rank, world, g):
+        import torch.distributed as dist
+        impl, d = self.impl, self.impl.dim
+        n = base['z'].shape[0]
+        x, ch = impl.sample_device(vp, base)
+        logp, grad = self.model.logp_and_grad_device(x, impl.code, True)
+        const = (math.lgamma(0.5 * (impl.df + d)) - math.lgamma(0.5 * impl.df)
+                 - 0.5 * d * math.log(math.pi * impl.df))
+        entropy = ch['L'].diagonal().log().sum()
+        lw = torch.empty(n, dtype=torch.float64, device=vp.device)
+        w = torch.empty(n, dtype=torch.float64, device=vp.device)
+        rows = torch.empty(4, dtype=torch.float64, device=vp.device)
+        ws = self.ws.get('fr_rows', _lib.lib.vb_fr_rows_workspace_bytes(n))
+        _lib.check(_lib.lib.vb_fr_rows(self.obj, self.alpha, impl.df, impl.code, n, d, ptr(base['z']),
+                                       ptr(base['chi2']), ptr(logp), float(const) - float(entropy),
+                                       ptr(lw), ptr(w), ptr(rows), ptr(ws), ws.numel(), stream_ptr()), 'vb_fr_rows')
+        if world > 1 and self.obj == _lib.OBJ_CHIVI:
+            # weights must be relative to the GLOBAL max: exchange the local maxima first
+            gm = rows[0:1].clone()
+            dist.all_reduce(gm, op=dist.ReduceOp.MAX, group=g)
+            scale = torch.exp(self.alpha * (rows[0] - gm[0]))
+            w = w * scale
+            rows = torch.stack([gm[0], rows[1] * scale, rows[2], rows[3]])
+        g_mu = torch.empty(d, dtype=torch.float64, device=vp.device)
+        G_S = torch.empty((d, d), dtype=torch.float64, device=vp.device)
+        ws2 = self.ws.get('fr_weighted', _lib.lib.vb_fr_weighted_workspace_bytes(n, d))
+        _lib.check(_lib.lib.vb_fr_weighted(impl.code, impl.df, n, d, ptr(base['z']), ptr(base['chi2']), ptr(w),
+                                           ptr(grad), ptr(g_mu), ptr(G_S), ptr(ws2), ws2.numel(), stream_ptr()),
+                   'vb_fr_weighted')
+        if world > 1:
+            # one exchange: [sum w, sum logp, sum lw, g_mu (d), G_S (d*d)] gathered and summed in rank order
+            pack = torch.cat([rows[1:4], g_mu, G_S.reshape(-1)])
+            gathered = torch.empty((world, pack.numel()), dtype=torch.float64, device=vp.device)
+            dist.all_gather_into_tensor(gathered, pack, group=g)
+            tot = gathered[0].clone()
+            for r in range(1, world):
+                tot += gathered[r]
+            rows = torch.cat([rows[0:1], tot[0:3]])
+            g_mu, G_S = tot[3:3 + d].contiguous(), tot[3 + d:].reshape(d, d).contiguous()
+        phi = impl.pack_grad(ch, G_S)
+        _, _, diag_pos = impl.tri()
+        out = torch.empty(1 + self.P, dtype=torch.float64, device=vp.device)
+        nt = float(n_total)
+        if self.obj == _lib.OBJ_KLVI:
+            out[0] = -(entropy + rows[2] / nt)
+            out[1:1 + d] = -g_mu / nt
+            phi = -phi / nt
+            phi[diag_pos] -= 1.0
+            out[1 + d:] = phi
+        else:
+            out[0] = torch.log(rows[1] / nt) / self.alpha + rows[0]
+            out[1:1 + d] = self.alpha * g_mu / nt
+            phi[diag_pos] += rows[1]
+            out[1 + d:] = self.alpha * phi / nt
+        self.last_log_weights = lw
+        return out
+
+    # ------------------------------------------------------------------ call
+    def __call__(self, var_param, base_draws=None):
+        vp = to_dev(var_param, _lib.F64)
+        if vp.shape != (self.P,):
+            raise ValueError('var_param must have shape (%d,)' % self.P)
+        rank, world, g = _dist_info(self.group)
+        impl = self.impl
+        # base-draw stream: KLVI advances the family's persistent stream (vb.py:239); CHIVI takes a
+        # fresh seed from numpy's global RNG on every call (vb.py:258)
+        if base_draws is not None:
+            base = impl.coerce_base(base_draws)
+            n_local = (base['eps'] if 'eps' in base else base['z']).shape[0]
+            seed = off = index0 = 0
+            n_total = n_local * world if world > 1 else n_local
+        else:
+            base = None
+            if self.obj == _lib.OBJ_KLVI:
+                seed, off = impl.next_stream(None)
+            else:
+                seed, off = int(np.random.randint(2 ** 32)), 0
+                if world > 1:
+                    import torch.distributed as dist
+                    st = torch.tensor([seed], dtype=torch.int64, device=vp.device)
+                    dist.broadcast(st, src=dist.get_global_rank(g, 0) if g is not None else 0, group=g)
+                    seed = int(st.item())
+            index0, n_local = _shard(self.n, rank, world)
+            n_total = self.n
+        if impl.kind == _lib.FAMILY_FR_T:
+            if base is None:
+                base = impl.base_draws(n_local, seed, off, index0)
+            out = self._fr(vp, base, n_total, rank, world, g)
+        else:
+            out, partials = self._mf(vp, base, seed, off, index0, n_local, finalize=(world == 1))
+            self.last_partials = partials
+            if world > 1:
+                out = self._mf_merge(vp, partials, world, g)
+        if is_host(var_param):
+            h = out.cpu().numpy()
+            return h[0], h[1:].copy()
+        return out[0], out[1:]
+
+
+def black_box_klvi(var_family, logdensity, n_samples, group=None):
+    """``vb.py:236-245``.  Returns ``objective_and_grad(var_param) -> (value, grad)`` with
+    value ``-(entropy + mean log p)``.  ``group``: torch.distributed group to shard the sample
+    axis over (default: the world group when torch.distributed is initialised; ``False``: never)."""
+    return _Objective(_lib.OBJ_KLVI, 1.0, var_family, logdensity, n_samples, group)
+
+
+def black_box_chivi(alpha, var_family, logdensity, n_samples, group=None):
+    """``vb.py:248-266``.  Returns a callable giving ``(CUBO_alpha estimate, gradient)`` — a
+    2-tuple, and the gradient is ``(alpha/n) sum_i s_i grad lw_i`` with
+    ``s_i = exp(alpha (lw_i - max lw))`` (not normalised by ``mean s``), as in the reference."""
+    return _Objective(_lib.OBJ_CHIVI, alpha, var_family, logdensity, n_samples, group)
+
+
+# =========================================================================== optimiser
+def learning_rate_schedule(n_iters, learning_rate, learning_rate_end):
+    """``vb.py:324-343``: constant, then a/(b+i) over the middle half, then constant."""
+    if learning_rate <= 0:
+        raise ValueError('learning rate must be positive')
+    decay = learning_rate_end is not None
+    if decay:
+        if learning_rate <= learning_rate_end:
+            raise ValueError('initial learning rate must be greater than final learning rate')
+        b = n_iters * learning_rate_end / (2 * (learning_rate - learning_rate_end))
+        a = learning_rate * b
+        first, last = n_iters // 4, 3 * n_iters // 4
+    for i in range(n_iters):
+        if not decay or i < first:
+            yield learning_rate
+        elif i < last:
+            yield a / (b + i - first + 1)
+        else:
+            yield learning_rate_end
+
+
+def adagrad_optimize(n_iters, objective_and_grad, init_param,
+                     has_log_norm=False, window=10, learning_rate=.01,
+                     epsilon=.1, learning_rate_end=None):
+    """Windowed AdaGrad with iterate averaging over the last quarter (``vb.py:345-389``).
+    Host loop over ``P``-vectors; every iteration makes one call into the CUDA objective."""
+    recent_grads, recent_norms = [], []
+    values, norms, kept = [], [], []
+    param = np.array(init_param, dtype=float, copy=True)
+    keep_from = 3 * n_iters // 4
+    with tqdm.trange(n_iters) as progress:
+        try:
+            rates = learning_rate_schedule(n_iters, learning_rate, learning_rate_end)
+            for i, rate in zip(progress, rates):
+                if has_log_norm:
+                    value, grad, log_norm = objective_and_grad(param)
+                else:
+                    value, grad = objective_and_grad(param)
+                    log_norm = 0
+                values.append(value)
+                norms.append(log_norm)
+                recent_grads.append(grad)
+                recent_norms.append(log_norm)
+                if len(recent_grads) > window:                       # pop after append, vb.py:368-370
+                    del recent_grads[0], recent_norms[0]
+                rescale = np.exp(np.min(recent_norms) - np.array(recent_norms))
+                accum = np.sum((rescale[:, None] * np.array(recent_grads)) ** 2, axis=0)
+                param = param - rate * grad / np.sqrt(epsilon + accum)  # epsilon inside the sqrt
+                if i >= keep_from:
+                    kept.append(param.copy())                        # post-update iterate
+                if i % 10 == 0:
+                    avg_loss = np.mean(values[max(0, i - 1000):i + 1])
+                    progress.set_description('Average Loss = {:,.5g}'.format(avg_loss))
+        except (KeyboardInterrupt, StopIteration):  # pragma: no cover
+            progress.close()
+        finally:
+            progress.close()
+    kept = np.array(kept)
+    return np.mean(kept, axis=0), kept, np.array(values), np.array(norms)
