@@ -1,0 +1,332 @@
+"""Workload definitions for bench.py — the five BASELINE.json configs."""
+import math
+import os
+import time
+
+import numpy as np
+
+METRIC = 'MC grad samples/s (KLVI/CHIVI) & PSIS+bounds weights/s; %HBM/TC roofline'
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def _pool_sum(fn, jobs, procs):
+    """Run fn(job) for every job in a fork pool and return the list of results."""
+    import multiprocessing as mp
+    if procs <= 1 or len(jobs) <= 1:
+        return [fn(j) for j in jobs]
+    ctx = mp.get_context('fork')
+    with ctx.Pool(procs) as pool:
+        return pool.map(fn, jobs)
+
+
+class Workload:
+    default_steps, default_warmup = 20, 3
+    metric, unit, dtype = METRIC, 'samples/s', 'f64'
+    h2d_bytes = d2h_bytes = 0
+    launches_per_step = 1
+
+    def __init__(self, rank, world, n_gpus):
+        self.rank, self.world, self.n_gpus = rank, world, n_gpus
+
+    def extra(self):
+        return {}
+
+
+# ======================================================================================= C4
+EIGHT_SCHOOLS_LAM = np.array(
+    [4.4, 0.8, 0.3, 0.1, -0.1, 0.1, -0.2, -0.1, 0.35, 0.06] +
+    list(np.log([3.2, 0.73, 0.96, 0.94, 0.97, 0.95, 0.92, 0.94, 0.93, 0.98])))
+
+
+def _c4_cpu_job(job):
+    """One shard of the oracle KLVI step: draws its own standard-t base draws like vb.py:151."""
+    seed, n = job
+    from oracle import models_np, vb_np
+    fam = vb_np.mean_field_t_variational_family(10, 40)
+    base = fam.impl.draw_base(np.random.RandomState(seed), n)
+    v, g = vb_np.klvi_value_and_grad(fam.impl, models_np.EightSchoolsNCP(), EIGHT_SCHOOLS_LAM, base)
+    return v, g
+
+
+class C4(Workload):
+    """eight-schools non-centred, mean-field t (df 40), KLVI, 2^22 samples per step per GPU."""
+    name = 'c4'
+    n = 1 << 22
+    d = 10
+    default_steps, default_warmup = 50, 5
+    cpu_sample = 1 << 19
+
+    def setup(self):
+        import torch
+        from viabel_b200 import models, vb, _lib
+        self.torch, self.lib = torch, _lib
+        self.fam = vb.mean_field_t_variational_family(self.d, 40)
+        self.model = models.EightSchoolsNCP()
+        self.obj = vb.black_box_klvi(self.fam, self.model, self.n * self.world)
+        # resident base draws for the streaming (HBM-roofline) mode: this rank's slice of the stream
+        start = self.rank * self.n
+        self.eps = self.fam.impl.base_draws(self.n, 0, 0, index0=start)['eps']
+        self.lam_host = EIGHT_SCHOOLS_LAM.copy()
+        self.lam_dev = torch.from_numpy(self.lam_host).cuda()
+        self.units_per_step = self.n
+        self.h2d_bytes = self.lam_host.nbytes
+        self.d2h_bytes = 8 * (1 + 2 * self.d)
+        # raw C-ABI call for the kernel-only timing
+        from viabel_b200._device import ptr
+        NP = 2 * self.d + 4
+        self._out = torch.empty(1 + 2 * self.d, dtype=torch.float64, device='cuda')
+        self._part = torch.empty(NP, dtype=torch.float64, device='cuda')
+        self._ws = torch.zeros(_lib.lib.vb_mf_step_workspace_bytes(self.d), dtype=torch.uint8, device='cuda')
+        self._args = (_lib.FAMILY_MF_T, 40.0, self.model.handle, _lib.OBJ_KLVI, 1.0, _lib.F64, ptr(self.lam_dev),
+                      self.n, ptr(self.eps), 0, 0, 0, ptr(self._out), ptr(self._out) + 8, ptr(self._part),
+                      ptr(self._ws), self._ws.numel())
+
+    def step_device(self):
+        return self.obj(self.lam_dev, base_draws=self.eps)
+
+    def step_e2e(self):
+        return self.obj(self.lam_host)            # Philox draws inside the fused kernel, host in / host out
+
+    def kernel_only(self):
+        from viabel_b200._device import stream_ptr
+        self.lib.check(self.lib.lib.vb_mf_step(*self._args, stream_ptr()))
+
+    def roofline(self, ms_kernel, hbm_gbs, bf16_tflops):
+        bytes_per_launch = self.n * self.d * 8            # base draws read once, nothing written
+        ach = bytes_per_launch / (ms_kernel * 1e-3) / 1e9
+        return {'bound': 'hbm', 'achieved': ach, 'peak': hbm_gbs, 'unit': 'GB/s', 'frac': ach / hbm_gbs,
+                'traffic': None, 'kernel': 'mf_step_kernel<double, MF_T, EightSchools<8>, KLVI, streaming>',
+                'ms_per_launch': ms_kernel, 'algorithmic_bytes_per_launch': bytes_per_launch}
+
+    def config(self):
+        return {'workload': 'c4: eight-schools ncp (d=10), mean-field Student-t(df=40) KLVI, 2^22 samples/step/GPU',
+                'samples_per_step_per_gpu': self.n, 'value_mode': 'streaming: fp64 base draws resident in HBM',
+                'e2e_mode': 'Philox draws fused in-kernel, host var_param in, host (value, grad) out',
+                'l2': 'inputs (335 MB/step) larger than L2 (126 MB)', 'parallelism': 'sample-sharded x%d' % self.world}
+
+    def _cpu(self, n, procs):
+        per = max(n // max(procs, 1), 1)
+        jobs = [(1000 + i, per) for i in range(max(procs, 1))]
+        t0 = time.perf_counter()
+        _pool_sum(_c4_cpu_job, jobs, procs)
+        return per * len(jobs) / (time.perf_counter() - t0)
+
+    def cpu_baseline(self):
+        rate = self._cpu(self.cpu_sample, 1)
+        return {'value': rate, 'unit': self.unit, 'cores': 1, 'kind': 'port',
+                'sample': 'oracle vb_np KLVI step incl. standard_t draws on %d samples, 1 process' % self.cpu_sample}
+
+    def reference_arm(self, steps, warmup):
+        procs = host_cores()
+        n = self.cpu_sample * min(procs, 8)
+        for _ in range(min(warmup, 1)):
+            self._cpu(n, procs)
+        k = max(1, min(steps, 3))
+        t0 = time.perf_counter()
+        for _ in range(k):
+            self._cpu(n, procs)
+        dt = (time.perf_counter() - t0) / k
+        rate = n / dt
+        sample = 'oracle vb_np KLVI step (draws + log p + grad) on %d samples/step, fork pool of %d processes' % (n, procs)
+        return {'metric': self.metric, 'value': rate, 'unit': self.unit, 'ms_per_step': dt * 1e3, 'dtype': 'f64',
+                'config': {'workload': self.config_name()},
+                'cpu_baseline': {'value': rate, 'unit': self.unit, 'cores': procs, 'kind': 'port', 'sample': sample},
+                'e2e': {'value': rate, 'unit': self.unit, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+
+    def config_name(self):
+        return 'c4: eight-schools ncp (d=10), mean-field Student-t(df=40) KLVI, 2^22 samples/step/GPU'
+
+
+# ======================================================================================= C1
+def _c1_cpu_job(job):
+    seed, iters = job
+    from oracle import models_np, vb_np
+    fam = vb_np.mean_field_gaussian_variational_family(2)
+    obj = vb_np.black_box_klvi(fam, models_np.Funnel(), 1000)
+    lam = np.array([0., -1., 1., 1.])
+    for _ in range(iters):
+        v, g = obj(lam)
+    return v
+
+
+class C1(Workload):
+    """funnel d=2, mean-field Gaussian KLVI, 1000 samples/step (latency-bound; roofline n/a)."""
+    name = 'c1'
+    n = 1000
+    default_steps, default_warmup = 2000, 50
+
+    def setup(self):
+        import torch
+        from viabel_b200 import models, vb, _lib
+        from viabel_b200._device import ptr
+        self.lib = _lib
+        self.fam = vb.mean_field_gaussian_variational_family(2)
+        self.model = models.Funnel()
+        self.obj = vb.black_box_klvi(self.fam, self.model, self.n, group=False)
+        self.lam_host = np.array([0., -1., 1., 1.])
+        self.lam_dev = torch.from_numpy(self.lam_host).cuda()
+        self.units_per_step = self.n
+        self.h2d_bytes, self.d2h_bytes = 32, 40
+        self._out = torch.empty(5, dtype=torch.float64, device='cuda')
+        self._part = torch.empty(8, dtype=torch.float64, device='cuda')
+        self._ws = torch.zeros(_lib.lib.vb_mf_step_workspace_bytes(2), dtype=torch.uint8, device='cuda')
+        self._args = [_lib.FAMILY_MF_GAUSS, 0.0, self.model.handle, _lib.OBJ_KLVI, 1.0, _lib.F64, ptr(self.lam_dev),
+                      self.n, 0, 0, 0, 0, ptr(self._out), ptr(self._out) + 8, ptr(self._part),
+                      ptr(self._ws), self._ws.numel()]
+        self._off = 0
+
+    def step_device(self):
+        return self.obj(self.lam_dev)
+
+    def step_e2e(self):
+        return self.obj(self.lam_host)
+
+    def kernel_only(self):
+        from viabel_b200._device import stream_ptr
+        self._args[10] = self._off
+        self._off += 1
+        self.lib.check(self.lib.lib.vb_mf_step(*self._args, stream_ptr()))
+
+    def roofline(self, ms_kernel, hbm_gbs, bf16_tflops):
+        return {'bound': 'hbm', 'achieved': 0.0, 'peak': hbm_gbs, 'unit': 'GB/s', 'frac': 0.0, 'traffic': None,
+                'kernel': 'mf_step_kernel<double, MF_GAUSS, Funnel, KLVI, philox>', 'ms_per_launch': ms_kernel,
+                'note': 'latency-bound (one CTA-sized problem, ~16 kB touched): roofline fraction not meaningful'}
+
+    def config(self):
+        return {'workload': 'c1: funnel d=2, mean-field Gaussian KLVI, 1000 samples/step (one AdaGrad iteration)',
+                'l2': 'no resident input (Philox in-kernel)', 'parallelism': 'replicas only'}
+
+    config_name = lambda self: self.config()['workload']      # noqa: E731
+
+    def cpu_baseline(self):
+        t0 = time.perf_counter()
+        _c1_cpu_job((0, 3000))
+        rate = 3000 * self.n / (time.perf_counter() - t0)
+        return {'value': rate, 'unit': self.unit, 'cores': 1, 'kind': 'port',
+                'sample': '3000 oracle KLVI steps of 1000 samples (randn + funnel log p + closed-form grad)'}
+
+    def reference_arm(self, steps, warmup):
+        k = max(steps, 1000)
+        t0 = time.perf_counter()
+        _c1_cpu_job((0, k))
+        dt = time.perf_counter() - t0
+        rate = k * self.n / dt
+        cb = {'value': rate, 'unit': self.unit, 'cores': 1, 'kind': 'port',
+              'sample': '%d sequential oracle KLVI steps (the optimiser loop is sequential: 1 process)' % k}
+        return {'metric': self.metric, 'value': rate, 'unit': self.unit, 'ms_per_step': dt / k * 1e3, 'dtype': 'f64',
+                'config': {'workload': self.config_name()}, 'cpu_baseline': cb,
+                'e2e': {'value': rate, 'unit': self.unit, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+
+
+# ======================================================================================= C5
+def c5_log_weights_host(n, seed=7):
+    """lw = log of GPD(k=0.5, sigma=1) variates."""
+    u = np.random.RandomState(seed).rand(n)
+    return np.log(np.expm1(-0.5 * np.log1p(-u)) / 0.5)
+
+
+class C5(Workload):
+    """psislw + all_bounds on 1.25e8 fp64 log weights per GPU (10^9 over 8 GPUs), heavy Pareto tail."""
+    name = 'c5'
+    n = 125_000_000
+    unit = 'weights/s'
+    default_steps, default_warmup = 5, 3
+    cpu_sample = 10_000_000
+
+    def setup(self):
+        import torch
+        import viabel_b200
+        from viabel_b200 import psis, _lib
+        from viabel_b200._device import ptr
+        if self.world > 1:
+            raise NotImplementedError('c5 across ranks needs the distributed PSIS exchange (next round)')
+        self.torch, self.psis, self.vb, self.lib = torch, psis, viabel_b200, _lib
+        g = torch.Generator(device='cuda')
+        g.manual_seed(7 + self.rank)
+        u = torch.rand(self.n, dtype=torch.float64, device='cuda', generator=g)
+        self.lw = torch.log(torch.expm1(-0.5 * torch.log1p(-u)) / 0.5)      # synthetic input, built once
+        del u
+        self.lw_host = None
+        self.units_per_step = self.n
+        self.h2d_bytes = self.n * 8
+        self.d2h_bytes = self.n * 8
+        self.launches_per_step = 60
+        self._out = torch.empty_like(self.lw)
+        self._diag = torch.empty(8, dtype=torch.float64, device='cuda')
+        nb = _lib.lib.vb_psis_smooth_workspace_bytes(self.n, 1.0)
+        self._ws = torch.zeros(nb, dtype=torch.uint8, device='cuda')
+        self._ptr = ptr
+
+    def _bounds(self, lw):
+        return self.vb.all_bounds(lw, moment_bound_fn=lambda p: 3.0 if p == 2 else 27.0, q_var=1.0)
+
+    def step_device(self):
+        out, k = self.psis.psislw(self.lw)
+        res = self._bounds(self.lw)
+        return k, res
+
+    def step_e2e(self):
+        if self.lw_host is None:
+            self.lw_host = self.lw.cpu().numpy()
+        out, k = self.psis.psislw(self.lw_host)
+        res = self._bounds(self.lw_host)
+        return k, res
+
+    def kernel_only(self):
+        from viabel_b200._device import stream_ptr
+        p = self._ptr
+        self.lib.check(self.lib.lib.vb_psis_smooth(p(self.lw), p(self._out), self.n, 1.0, p(self._diag), 0,
+                                                   p(self._ws), self._ws.numel(), stream_ptr()))
+
+    def roofline(self, ms_kernel, hbm_gbs, bf16_tflops):
+        b = 24 * self.n          # read for max/select + read for normalise + write
+        ach = b / (ms_kernel * 1e-3) / 1e9
+        return {'bound': 'hbm', 'achieved': ach, 'peak': hbm_gbs, 'unit': 'GB/s', 'frac': ach / hbm_gbs,
+                'traffic': None, 'kernel': 'vb_psis_smooth (all passes: max, prefilter, normalise + tail work)',
+                'ms_per_launch': ms_kernel, 'algorithmic_bytes_per_launch': b,
+                'note': 'this implementation makes 3 reads + 1 write (32 B/weight): frac <= 0.75 by construction'}
+
+    def config(self):
+        return {'workload': 'c5: psislw + all_bounds on 1.25e8 fp64 log weights per GPU (GPD k=0.5 tail)',
+                'weights_per_gpu': self.n, 'l2': 'input (1 GB) larger than L2 (126 MB)',
+                'parallelism': 'sample-sharded x%d' % self.world}
+
+    config_name = lambda self: self.config()['workload']      # noqa: E731
+
+    def _cpu(self, n):
+        import warnings
+        from oracle import bounds_np, psis_np
+        lw = c5_log_weights_host(n)
+        t0 = time.perf_counter()
+        with warnings.catch_warnings():
+            warnings.simplefilter('ignore')
+            psis_np.psislw(lw)
+            bounds_np.all_bounds(lw, moment_bound_fn=lambda p: 3.0 if p == 2 else 27.0, q_var=1.0)
+        return n / (time.perf_counter() - t0)
+
+    def cpu_baseline(self):
+        rate = self._cpu(self.cpu_sample)
+        return {'value': rate, 'unit': self.unit, 'cores': 1, 'kind': 'port',
+                'sample': 'oracle psislw + all_bounds on %d weights (np.argsort is single-threaded)' % self.cpu_sample}
+
+    def reference_arm(self, steps, warmup):
+        k = max(1, min(steps, 2))
+        t0 = time.perf_counter()
+        rates = [self._cpu(self.cpu_sample) for _ in range(k)]
+        dt = (time.perf_counter() - t0) / k
+        rate = float(np.mean(rates))
+        cb = {'value': rate, 'unit': self.unit, 'cores': 1, 'kind': 'port',
+              'sample': 'oracle psislw + all_bounds on %d weights per step; the reference algorithm is one '
+                        'argsort + numpy ufunc passes, single-threaded' % self.cpu_sample}
+        return {'metric': self.metric, 'value': rate, 'unit': self.unit, 'ms_per_step': dt * 1e3, 'dtype': 'f64',
+                'config': {'workload': self.config_name()}, 'cpu_baseline': cb,
+                'e2e': {'value': rate, 'unit': self.unit, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+
+
+WORKLOADS = {'c1': C1, 'c4': C4, 'c5': C5}

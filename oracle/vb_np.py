@@ -124,8 +124,10 @@ class _FullRankT:
     """paragami ``PatternDict(free_default=True)`` with ``mu`` then ``Sigma`` (vb.py:185-189):
     flat = [mu (d), vec_tril_rowmajor(chol(Sigma) with log on the diagonal)]."""
 
-    def __init__(self, dim, df):
-        self.dim, self.df, self.kind = dim, df, 'fr_t'
+    def __init__(self, dim, df, scale='sqrtm'):
+        # scale='chol' is NOT in the reference: x = mu + L ztilde (same distribution, different
+        # per-draw map); it is the oracle of the product's documented throughput mode.
+        self.dim, self.df, self.kind, self.scale = dim, df, 'fr_t', scale
         self.rs = np.random.RandomState(0)                              # vb.py:195
         self.tri = np.tril_indices(dim)
         self.diag_pos = np.cumsum(np.arange(1, dim + 1)) - 1            # flat slots of L_ii
@@ -156,6 +158,8 @@ class _FullRankT:
 
     def transform(self, lam, base):
         mu, L, Sigma = self.fold(lam)
+        if self.scale == 'chol':
+            return mu + self.ztilde(base) @ L.T
         S, _, _ = self.sqrt_sigma(Sigma)
         return mu + self.ztilde(base) @ S                               # vb.py:207-208
 
@@ -204,10 +208,14 @@ class _FullRankT:
         """d/dlam of sum_i w_i log p(mu + ztilde_i sqrtm(L L'))  (Appendix A.2)."""
         d = self.dim
         mu, L, Sigma = self.fold(lam)
-        S, lamb, V = self.sqrt_sigma(Sigma)
         zt = self.ztilde(base)
         g_mu = w @ g
         G_S = zt.T @ (w[:, None] * g)                                   # d x d
+        if self.scale == 'chol':
+            phi = G_S.T[self.tri].copy()
+            phi[self.diag_pos] *= np.diag(L)
+            return np.concatenate([g_mu, phi])
+        S, lamb, V = self.sqrt_sigma(Sigma)
         # sqrtm VJP: solve S Y + Y S = G_S  (autograd: solve_sylvester(S', S', G))
         r = np.sqrt(lamb)
         Y = V @ ((V.T @ G_S @ V) / (r[:, None] + r[None, :])) @ V.T
@@ -243,10 +251,10 @@ def mean_field_t_variational_family(dim, df):
     return _wrap(_MeanField(dim, df), 2 * dim)
 
 
-def t_variational_family(dim, df):
+def t_variational_family(dim, df, scale='sqrtm'):
     if df <= 2:                                                         # vb.py:193-194
         raise ValueError('df must be greater than 2')
-    impl = _FullRankT(dim, df)
+    impl = _FullRankT(dim, df, scale)
     return _wrap(impl, impl.n_param)
 
 

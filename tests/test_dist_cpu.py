@@ -1,0 +1,147 @@
+"""world_size-2 gloo tests (CPU) of the sample-axis sharding logic: the shard arithmetic the
+product uses (vb._shard / vb._dist_info), the exchange pattern (one all_gather of the
+VB_MF_NPART partial vector per step; one all_gather of 6 doubles for divergence_bound) and the
+fixed-order merge formulas, checked against the unsharded oracle.  The partials themselves are
+produced by the oracle here; on the GPU box the same exchange carries kernel partials
+(tests/test_gpu_multi.py)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from oracle import models_np as mm
+from oracle import vb_np
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(('127.0.0.1', 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def mf_partials(impl, model, objective, alpha, lam, base):
+    """numpy restatement of the partial vector vb_mf_step writes (include/viabel_b200.h)."""
+    d = impl.dim
+    x = impl.transform(lam, base)
+    lp, g = model.logp_and_grad(x)
+    eps = base['eps']
+    out = np.zeros(2 * d + 4)
+    if objective == 'klvi':
+        w = np.ones(len(lp))
+        out[0], out[2] = 0.0, lp.sum()
+    else:
+        lw = lp - impl.logq_of_base(lam, base)
+        out[0] = lw.max()
+        w = np.exp(alpha * (lw - out[0]))
+        out[2] = lw.sum()
+    out[1], out[3] = w.sum(), len(lp)
+    out[4:4 + d] = w @ g
+    out[4 + d:] = w @ (g * eps)
+    return out
+
+
+def mf_finalize(kind, objective, alpha, lam, parts):
+    """numpy restatement of vb_mf_finalize: rescale to the global max, sum in rank order, Appendix A.1."""
+    parts = np.asarray(parts)
+    d = (parts.shape[1] - 4) // 2
+    M = parts[:, 0].max() if objective == 'chivi' else 0.0
+    tot = np.zeros(parts.shape[1])
+    for p in parts:
+        f = np.exp(alpha * (p[0] - M)) if objective == 'chivi' else 1.0
+        tot[1] += p[1] * f
+        tot[2:4] += p[2:4]
+        tot[4:] += p[4:] * f
+    n = tot[3]
+    sig = np.exp(lam[d:])
+    gm, gl = tot[4:4 + d], tot[4 + d:] * sig
+    if objective == 'klvi':
+        H = lam[d:].sum() + (0.5 * d * (1 + np.log(2 * np.pi)) if kind == 'mf_gauss' else 0.0)
+        return -(H + tot[2] / n), np.concatenate([-gm / n, -(1 + gl / n)])
+    return np.log(tot[1] / n) / alpha + M, np.concatenate([alpha * gm / n, alpha * (gl + tot[1]) / n])
+
+
+def _worker(rank, world, port, ret):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        from viabel_b200 import vb
+        from viabel_b200._device import all_gather_rows
+        r, w, g = vb._dist_info(None)
+        assert (r, w) == (rank, world)
+        assert vb._dist_info(False)[:2] == (0, 1)
+        n = 1001
+        start, count = vb._shard(n, rank, world)
+        d = 10
+        fam = vb_np.mean_field_t_variational_family(d, 40)
+        model = mm.EightSchoolsNCP()
+        lam = np.concatenate([0.3 * np.random.RandomState(0).randn(d), np.full(d, -0.1)])
+        full = fam.impl.draw_base(np.random.RandomState(1), n)          # every rank can regenerate it
+        mine = {'eps': full['eps'][start:start + count]}
+        results = {}
+        for objective, alpha in (('klvi', 1.0), ('chivi', 2.0)):
+            part = torch.from_numpy(mf_partials(fam.impl, model, objective, alpha, lam, mine))
+            gathered = all_gather_rows(part, world)        # the product's own exchange helper
+            results[objective] = mf_finalize('mf_t', objective, alpha, lam, gathered.numpy())
+        # divergence_bound partials: [max, sum w, sum w^2, count, mean, M2] merged like bounds.cu
+        lw = np.random.RandomState(2).randn(n) * 1.5 - 3.0
+        x = lw[start:start + count]
+        M = x.max()
+        wv = np.exp(2.0 * (x - M))
+        part = torch.tensor([M, wv.sum(), (wv ** 2).sum(), float(count), x.mean(), ((x - x.mean()) ** 2).sum()])
+        gathered = all_gather_rows(part, world)
+        results['div'] = gathered.numpy().copy()
+        if rank == 0:
+            ret['klvi'], ret['chivi'], ret['div'] = results['klvi'], results['chivi'], results['div']
+            ret['lam'], ret['lw'] = lam, lw
+    finally:
+        dist.destroy_process_group()
+
+
+def test_shard_arithmetic():
+    from viabel_b200 import vb
+    for n, world in [(10, 3), (1001, 2), (8, 8), (5, 8), (2 ** 22, 8)]:
+        spans = [vb._shard(n, r, world) for r in range(world)]
+        assert spans[0][0] == 0 and sum(c for _, c in spans) == n
+        for (s0, c0), (s1, _) in zip(spans, spans[1:]):
+            assert s0 + c0 == s1                                     # contiguous, disjoint, ordered
+        assert max(c for _, c in spans) - min(c for _, c in spans) <= 1
+
+
+def test_two_rank_gloo_merge_equals_unsharded():
+    world, port = 2, _free_port()
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_worker, args=(world, port, ret), nprocs=world, join=True)
+    lam = ret['lam']
+    d = 10
+    fam = vb_np.mean_field_t_variational_family(d, 40)
+    model = mm.EightSchoolsNCP()
+    base = fam.impl.draw_base(np.random.RandomState(1), 1001)
+    v, g = vb_np.klvi_value_and_grad(fam.impl, model, lam, base)
+    np.testing.assert_allclose(ret['klvi'][0], v, rtol=1e-13)
+    np.testing.assert_allclose(ret['klvi'][1], g, rtol=1e-12, atol=1e-14)
+    v, g = vb_np.chivi_value_and_grad(fam.impl, model, 2.0, lam, base)
+    np.testing.assert_allclose(ret['chivi'][0], v, rtol=1e-13)
+    np.testing.assert_allclose(ret['chivi'][1], g, rtol=1e-12, atol=1e-14)
+    # Chan merge of (count, mean, M2) + max-rescaled weight sums reproduce the unsharded statistics
+    parts, lw = ret['div'], ret['lw']
+    M = parts[:, 0].max()
+    sw = sum(p[1] * np.exp(2.0 * (p[0] - M)) for p in parts)
+    cnt, mean, M2 = 0.0, 0.0, 0.0
+    for p in parts:
+        tot = cnt + p[3]
+        delta = p[4] - mean
+        mean += delta * p[3] / tot
+        M2 += p[5] + delta * delta * cnt * p[3] / tot
+        cnt = tot
+    np.testing.assert_allclose(M, lw.max())
+    np.testing.assert_allclose(sw / cnt, np.mean(np.exp(2.0 * (lw - lw.max()))), rtol=1e-13)
+    np.testing.assert_allclose(mean, lw.mean(), rtol=1e-13)
+    np.testing.assert_allclose(np.sqrt(M2 / cnt), lw.std(), rtol=1e-12)

@@ -1,0 +1,202 @@
+"""GPU parity: viabel_b200.bounds / viabel_b200.psis against the committed reference outputs
+(tests/golden, produced by the reference itself) and against the oracle on seeded inputs.
+Tolerances: bounds rtol 1e-10; PSIS tail index set and sort order bit-exact, cutoff bit-exact,
+k-hat rtol 1e-9, smoothed log weights atol 1e-9 (summation order is the only difference)."""
+import warnings
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+import golden_inputs as gi                      # noqa: E402
+from oracle import bounds_np, psis_np           # noqa: E402
+
+
+def _quiet(fn, *a, **k):
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        return fn(*a, **k)
+
+
+# --------------------------------------------------------------------------------------- bounds
+@pytest.mark.parametrize('name', gi.BOUNDS_CASES)
+def test_all_bounds_vs_reference_outputs(golden, name):
+    import viabel_b200
+    lw, samples, kw = gi.bounds_case(name)
+    res = _quiet(viabel_b200.all_bounds, lw, samples, **kw)
+    assert list(res) == ['W1', 'W2', 'mean_error', 'std_error', 'cov_error', 'd2', 'log_norm_bound']
+    for k, v in res.items():
+        np.testing.assert_allclose(v, golden['bounds/%s/%s' % (name, k)], rtol=1e-10, err_msg=k)
+    for alpha in (1.5, 2.0, 3.0):
+        np.testing.assert_allclose(_quiet(viabel_b200.divergence_bound, lw, alpha),
+                                   golden['bounds/%s/d_alpha_%g' % (name, alpha)], rtol=1e-10)
+
+
+def test_reference_known_answer_tests_on_gpu():
+    """tests/test_bounds.py:22-70 of the reference, run against the CUDA backend."""
+    from scipy.stats import norm
+    import viabel_b200
+    MC, TOL = 10000000, 5 / np.sqrt(10000000)
+
+    def a_div(alpha, v1, v2):
+        tmp = alpha * v2 - (alpha - 1) * v1
+        return -0.5 / (alpha - 1) * np.log(tmp) + .5 * alpha / (alpha - 1) * np.log(v2) - .5 * np.log(v1)
+
+    def kl(v1, v2):
+        return .5 * (v1 / v2 + np.log(v2 / v1) - 1)
+    np.random.seed(846)
+    v1, v2 = 4, 16
+    s = norm(scale=np.sqrt(v2)).rvs(MC)
+    lw = norm(scale=np.sqrt(v1)).logpdf(s) - norm(scale=np.sqrt(v2)).logpdf(s)
+    for alpha in [1.5, 2, 3]:
+        for elbo in [None, 0]:
+            exp = a_div(alpha, v1, v2) + (alpha / (alpha - 1) * kl(v2, v1) if elbo is None else 0)
+            np.testing.assert_allclose(_quiet(viabel_b200.divergence_bound, lw, alpha, elbo), exp, atol=TOL, rtol=TOL)
+    np.random.seed(341)
+    d2, sd = 5.0, 3.5
+    s = norm.rvs(scale=sd, size=MC)
+    res = viabel_b200.wasserstein_bounds(d2, s)
+    np.testing.assert_allclose(res['W1'], 2 * sd * np.sqrt(np.expm1(d2)), rtol=TOL)
+    np.testing.assert_allclose(res['W2'], 2 * sd * (3 * np.expm1(d2)) ** 0.25, rtol=TOL)
+    np.random.seed(1639)
+    v1, v2 = 2.5, 9.3
+    s = norm(scale=np.sqrt(v2)).rvs(MC)
+    lw = norm(scale=np.sqrt(v1)).logpdf(s) - norm(scale=np.sqrt(v2)).logpdf(s)
+    res = _quiet(viabel_b200.all_bounds, lw, s, q_var=v2, log_norm_bound=None)
+    np.testing.assert_allclose(res['d2'], a_div(2, v1, v2) + 2 * kl(v2, v1), rtol=TOL)
+    np.testing.assert_allclose(res['W1'], 2 * np.sqrt(v2) * np.sqrt(np.expm1(res['d2'])), rtol=TOL)
+    np.testing.assert_allclose(res['W2'], 2 * np.sqrt(v2) * (3 * np.expm1(res['d2'])) ** 0.25, rtol=TOL)
+
+
+@pytest.mark.parametrize('n', [2, 3, 1000, 1001, 3000001])
+def test_divergence_and_moments_vs_oracle(n):
+    import torch
+    import viabel_b200
+    rs = np.random.RandomState(n)
+    lw = rs.randn(n) * 2.0 - 500.0
+    for alpha in (2.0, 4.0):
+        np.testing.assert_allclose(_quiet(viabel_b200.divergence_bound, lw, alpha),
+                                   _quiet(bounds_np.divergence_bound, lw, alpha), rtol=1e-10)
+    d = 7
+    x = rs.randn(n, d) * np.arange(1, d + 1) + 100.0
+    a = _quiet(viabel_b200.all_bounds, lw, x)
+    b = _quiet(bounds_np.all_bounds, lw, x)
+    for k in b:
+        np.testing.assert_allclose(a[k], b[k], rtol=1e-9, err_msg=k)
+    # CUDA tensors are consumed in place (offset view: misaligned for 16-byte loads)
+    buf = torch.empty(n + 1, dtype=torch.float64, device='cuda')
+    buf[1:].copy_(torch.from_numpy(lw))
+    np.testing.assert_allclose(_quiet(viabel_b200.divergence_bound, buf[1:]),
+                               _quiet(bounds_np.divergence_bound, lw), rtol=1e-10)
+
+
+def test_mc_error_warning_text_matches_reference():
+    import viabel_b200
+    lw = np.array([0.0, 10.0, -10.0, 5.0])
+    with warnings.catch_warnings(record=True) as got:
+        warnings.simplefilter('always')
+        viabel_b200.divergence_bound(lw)
+    with warnings.catch_warnings(record=True) as want:
+        warnings.simplefilter('always')
+        bounds_np.divergence_bound(lw)
+    assert len(got) == len(want) == 2
+    for g, w in zip(got, want):
+        gm, wm = str(g.message), str(w.message)
+        assert gm.split(' (mean')[0] == wm.split(' (mean')[0]          # same sentence, same quantity name
+        gv = [float(t.split(')')[0]) for t in gm.split('= ')[1:]]
+        wv = [float(t.split(')')[0]) for t in wm.split('= ')[1:]]
+        np.testing.assert_allclose(gv, wv, rtol=1e-10)
+
+
+# --------------------------------------------------------------------------------------- PSIS
+@pytest.mark.parametrize('name', gi.PSIS_CASES)
+def test_psislw_vs_reference_outputs(golden, name):
+    from viabel_b200 import psis
+    lw = gi.psis_case(name)
+    out, k, det = psis.psislw_detail(lw)
+    pre = 'psis/%s/' % name
+    gk = golden[pre + 'k']
+    if np.isinf(gk):
+        assert np.isinf(k)
+    else:
+        np.testing.assert_allclose(k, gk, rtol=1e-9)
+    assert det['xcutoff'] == golden[pre + 'xcutoff']                                  # bit-exact order statistic
+    if det['n2'] > 4:
+        assert np.array_equal(det['tail_idx_sorted'], golden[pre + 'tail_idx_sorted'])   # bit-exact set + order
+        np.testing.assert_allclose(out[det['tail_idx_sorted']], golden[pre + 'tail_values'], rtol=0, atol=1e-9)
+    np.testing.assert_allclose(out[gi.probe_indices(len(lw))], golden[pre + 'probe_values'], rtol=0, atol=1e-9)
+    np.testing.assert_allclose(psis.sumlogs(lw), golden[pre + 'sumlogs'], rtol=1e-12)
+    out2, k2 = psis.psislw(lw)
+    assert np.array_equal(out, out2) and (k == k2 or np.isinf(k))
+    np.testing.assert_allclose(np.sum(np.exp(out)), 1.0, rtol=1e-10)                  # normalised weights
+
+
+@pytest.mark.parametrize('n,kk,reff', [(2, 0.5, 1.0), (5, 0.5, 1.0), (26, 0.5, 1.0), (4097, 0.6, 1.0),
+                                        (131072, 0.5, 1.0), (131073, 0.5, 1.0), (300000, 0.4, 0.7),
+                                        (2000003, 0.5, 1.0)])
+def test_psislw_vs_oracle(n, kk, reff):
+    """Includes both sides of the direct-sort threshold (2^17) and the histogram-refined path."""
+    from viabel_b200 import psis
+    lw = gi.gpd_log_weights(n, kk, 4000 + n, offset=-77.0)
+    out, k, det = psis.psislw_detail(lw, Reff=reff)
+    oout, ok, odet = _quiet(psis_np.psislw_detail, lw, Reff=reff, sort_kind='stable')
+    if np.isinf(ok):
+        assert np.isinf(k)
+    else:
+        np.testing.assert_allclose(k, ok, rtol=1e-9)
+    assert det['xcutoff'] == odet['xcutoff'] and det['n2'] == odet['n2']
+    if odet['n2'] > 4:
+        assert np.array_equal(det['tail_idx_sorted'], odet['tailinds'][odet['tail_order']])
+    assert det['smoothed'] == odet['smoothed']
+    np.testing.assert_allclose(out, oout, rtol=0, atol=1e-9)
+
+
+def test_psislw_ties_use_ascending_index():
+    """Heavy ties in the tail: the contract is numpy's kind='stable' order."""
+    from viabel_b200 import psis
+    rs = np.random.RandomState(3)
+    lw = np.round(gi.gpd_log_weights(50000, 0.5, 77), 1)           # many exact duplicates
+    lw[rs.randint(0, 50000, 200)] = lw.max()                        # ties at the very top too
+    out, k, det = psis.psislw_detail(lw)
+    oout, ok, odet = _quiet(psis_np.psislw_detail, lw, sort_kind='stable')
+    assert det['xcutoff'] == odet['xcutoff'] and det['n2'] == odet['n2']
+    assert np.array_equal(det['tail_idx_sorted'], odet['tailinds'][odet['tail_order']])
+    np.testing.assert_allclose(k, ok, rtol=1e-9)
+    np.testing.assert_allclose(out, oout, rtol=0, atol=1e-9)
+
+
+def test_psislw_two_dimensional_and_device_input():
+    import torch
+    from viabel_b200 import psis
+    a, b = gi.psis_case('gpd05_n5000'), gi.psis_case('gpd07_n20000')[:5000]
+    lw2 = np.stack([a, b], axis=1)
+    out, ks = psis.psislw(lw2)
+    oout, oks = _quiet(psis_np.psislw, lw2)
+    assert out.shape == (5000, 2) and out.flags.f_contiguous and ks.shape == (2,)
+    np.testing.assert_allclose(ks, oks, rtol=1e-9)
+    np.testing.assert_allclose(out, oout, rtol=0, atol=1e-9)
+    dev = torch.from_numpy(a).cuda()
+    o, k = psis.psislw(dev)
+    assert o.is_cuda and o.data_ptr() != dev.data_ptr()
+    np.testing.assert_allclose(o.cpu().numpy(), oout[:, 0], rtol=0, atol=1e-9)
+    o2, _ = psis.psislw(dev, overwrite_lw=True)
+    assert o2.data_ptr() == dev.data_ptr()
+    np.testing.assert_allclose(dev.cpu().numpy(), oout[:, 0], rtol=0, atol=1e-9)
+
+
+@pytest.mark.parametrize('name', gi.GPD_CASES)
+def test_gpdfit_gpinv_sumlogs(golden, name):
+    from viabel_b200 import psis
+    xs = gi.gpd_case(name)
+    k, sigma = psis.gpdfitnew(xs, sort=False)
+    np.testing.assert_allclose(k, golden['gpd/%s/k' % name], rtol=1e-9)
+    np.testing.assert_allclose(sigma, golden['gpd/%s/sigma' % name], rtol=1e-9)
+    k2, s2 = psis.gpdfitnew(xs[::-1].copy())                     # unsorted input, sort=True
+    np.testing.assert_allclose([k2, s2], [k, sigma], rtol=1e-12)
+    p = gi.gpinv_probs()
+    for (kk, s) in gi.GPINV_PARAMS:
+        np.testing.assert_allclose(psis.gpinv(p, kk, s), golden['gpinv/%g_%g' % (kk, s)], rtol=1e-12,
+                                   equal_nan=True)
+    x = np.random.RandomState(0).randn(100001) * 30
+    np.testing.assert_allclose(psis.sumlogs(x), psis_np.sumlogs(x), rtol=1e-13)

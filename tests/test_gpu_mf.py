@@ -1,0 +1,195 @@
+"""GPU parity: fused mean-field KLVI / CHIVI step and the family closures against the oracle,
+through the Python surface -> ctypes -> C ABI.  Tolerances (stated per SURVEY 8(d)):
+fp64 kernels rtol 1e-10; fp32-compute / fp64-accumulate rtol 2e-5 (gradient), 1e-5 (value)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+from oracle import models_np as mm          # noqa: E402
+from oracle import vb_np                    # noqa: E402
+
+
+def _models():
+    from viabel_b200 import models
+    return {
+        'funnel': (models.Funnel(), mm.Funnel(), 2),
+        'mixture': (models.NormalMixture(), mm.NormalMixture(), 1),
+        'eight_schools': (models.EightSchoolsNCP(), mm.EightSchoolsNCP(), 10),
+    }
+
+
+def _families(kind, d, dtype):
+    from viabel_b200 import vb
+    if kind == 'gauss':
+        return vb.mean_field_gaussian_variational_family(d, dtype=dtype), \
+            vb_np.mean_field_gaussian_variational_family(d)
+    return vb.mean_field_t_variational_family(d, 40, dtype=dtype), vb_np.mean_field_t_variational_family(d, 40)
+
+
+def _lam(d, seed=0):
+    rs = np.random.RandomState(seed)
+    return np.concatenate([0.3 * rs.randn(d), -0.2 + 0.1 * rs.randn(d)])
+
+
+@pytest.mark.parametrize('model_name', ['funnel', 'mixture', 'eight_schools'])
+@pytest.mark.parametrize('kind', ['gauss', 't'])
+@pytest.mark.parametrize('n', [1, 255, 256, 257, 5000, 70001])
+def test_fused_step_f64_matches_oracle(model_name, kind, n):
+    from viabel_b200 import vb
+    model, omodel, d = _models()[model_name]
+    fam, ofam = _families(kind, d, 'f64')
+    lam = _lam(d)
+    base = ofam.impl.draw_base(np.random.RandomState(n), n)
+    v, g = vb.black_box_klvi(fam, model, n, group=False)(lam, base_draws=base)
+    ov, og = vb_np.klvi_value_and_grad(ofam.impl, omodel, lam, base)
+    np.testing.assert_allclose(v, ov, rtol=1e-10)
+    np.testing.assert_allclose(g, og, rtol=1e-10, atol=1e-12)
+    assert isinstance(g, np.ndarray) and g.shape == (2 * d,)
+    for alpha in (2.0, 1.5):
+        v, g = vb.black_box_chivi(alpha, fam, model, n, group=False)(lam, base_draws=base)
+        ov, og = vb_np.chivi_value_and_grad(ofam.impl, omodel, alpha, lam, base)
+        np.testing.assert_allclose(v, ov, rtol=1e-10)
+        np.testing.assert_allclose(g, og, rtol=1e-9, atol=1e-12)
+
+
+@pytest.mark.parametrize('model_name', ['funnel', 'eight_schools'])
+def test_fused_step_f32_matches_oracle(model_name):
+    from viabel_b200 import vb
+    model, omodel, d = _models()[model_name]
+    fam, ofam = _families('t', d, 'f32')
+    lam = _lam(d)
+    n = 20000
+    base = ofam.impl.draw_base(np.random.RandomState(3), n)
+    base32 = {'eps': base['eps'].astype(np.float32)}
+    base_r = {'eps': base32['eps'].astype(np.float64)}           # the oracle sees the same rounded draws
+    v, g = vb.black_box_klvi(fam, model, n, group=False)(lam, base_draws=base32)
+    ov, og = vb_np.klvi_value_and_grad(ofam.impl, omodel, lam, base_r)
+    np.testing.assert_allclose(v, ov, rtol=1e-5)
+    np.testing.assert_allclose(g, og, rtol=2e-5, atol=2e-6)
+    v, g = vb.black_box_chivi(2.0, fam, model, n, group=False)(lam, base_draws=base32)
+    ov, og = vb_np.chivi_value_and_grad(ofam.impl, omodel, 2.0, lam, base_r)
+    np.testing.assert_allclose(v, ov, rtol=1e-5)
+    np.testing.assert_allclose(g, og, rtol=2e-4, atol=1e-6 * np.abs(og).max())
+
+
+def test_misaligned_base_pointer_takes_the_plain_load_path():
+    """A base-draw view that is only 8-byte aligned cannot use the bulk copy; results must not change."""
+    import torch
+    from viabel_b200 import vb
+    model, omodel, d = _models()['eight_schools']
+    fam, ofam = _families('gauss', d, 'f64')
+    lam = _lam(d)
+    n = 3000
+    base = ofam.impl.draw_base(np.random.RandomState(8), n)
+    buf = torch.empty(n * d + 1, dtype=torch.float64, device='cuda')
+    view = buf[1:].view(n, d)
+    view.copy_(torch.from_numpy(base['eps']))
+    assert view.data_ptr() % 16 == 8
+    v, g = vb.black_box_klvi(fam, model, n, group=False)(lam, base_draws=view)
+    ov, og = vb_np.klvi_value_and_grad(ofam.impl, omodel, lam, base)
+    np.testing.assert_allclose(v, ov, rtol=1e-10)
+    np.testing.assert_allclose(g, og, rtol=1e-10, atol=1e-12)
+
+
+@pytest.mark.parametrize('kind', ['gauss', 't'])
+def test_philox_step_equals_step_on_its_own_draws(kind):
+    """The RNG-fused kernel and the streaming kernel see the same numbers: draw the Philox base
+    draws with vb_base_draws (same seed / offset), feed them to the oracle, compare with the fused
+    Philox step.  Also: sample(seed=k) is x = m + exp(l) * eps of exactly those draws."""
+    from viabel_b200 import vb
+    model, omodel, d = _models()['eight_schools']
+    fam, ofam = _families(kind, d, 'f64')
+    lam = _lam(d)
+    n = 10007
+    obj = vb.black_box_klvi(fam, model, n, group=False)
+    assert fam.impl.offset == 0
+    v, g = obj(lam)                                                  # consumes stream (seed 0, offset 0)
+    assert fam.impl.offset == 1
+    eps = fam.impl.base_draws(n, 0, 0)['eps'].cpu().numpy()
+    ov, og = vb_np.klvi_value_and_grad(ofam.impl, omodel, lam, {'eps': eps})
+    np.testing.assert_allclose(v, ov, rtol=1e-10)
+    np.testing.assert_allclose(g, og, rtol=1e-10, atol=1e-12)
+    v2, _ = obj(lam)                                                 # next call: offset 1, new draws
+    assert v2 != v
+    x = fam.sample(lam, n, seed=5)
+    eps5 = fam.impl.base_draws(n, 5, 0)['eps'].cpu().numpy()
+    np.testing.assert_allclose(x, lam[:d] + np.exp(lam[d:]) * eps5, rtol=1e-14)
+    # CHIVI takes its seed from numpy's global RNG like vb.py:258
+    np.random.seed(123)
+    expect_seed = np.random.randint(2 ** 32)
+    np.random.seed(123)
+    v, g = vb.black_box_chivi(2.0, fam, model, n, group=False)(lam)
+    epsc = fam.impl.base_draws(n, expect_seed, 0)['eps'].cpu().numpy()
+    ov, og = vb_np.chivi_value_and_grad(ofam.impl, omodel, 2.0, lam, {'eps': epsc})
+    np.testing.assert_allclose(v, ov, rtol=1e-10)
+    np.testing.assert_allclose(g, og, rtol=1e-9, atol=1e-12)
+
+
+def test_philox_draws_are_geometry_independent_and_well_distributed():
+    from scipy import stats
+    from viabel_b200 import vb
+    fam = vb.mean_field_t_variational_family(3, 40)
+    a = fam.impl.base_draws(50000, 7, 2)['eps'].cpu().numpy()
+    # a shard starting at global index 20000 reproduces rows 20000.. of the full draw
+    b = fam.impl.base_draws(30000, 7, 2, index0=20000)['eps'].cpu().numpy()
+    np.testing.assert_array_equal(a[20000:], b)
+    assert not np.array_equal(a, fam.impl.base_draws(50000, 7, 3)['eps'].cpu().numpy())
+    assert stats.kstest(a.ravel(), stats.t(40).cdf).pvalue > 1e-3
+    gfam = vb.mean_field_gaussian_variational_family(5)
+    z = gfam.impl.base_draws(200000, 1, 0)['eps'].cpu().numpy()
+    assert stats.kstest(z.ravel(), 'norm').pvalue > 1e-3
+    assert abs(np.corrcoef(z.T)[0, 1]) < 0.01 and abs(z.mean()) < 0.005 and abs(z.std() - 1) < 0.005
+    ffam = vb.t_variational_family(4, 12)
+    bd = ffam.impl.base_draws(200000, 3, 0)
+    assert stats.kstest(bd['chi2'].cpu().numpy(), stats.chi2(12).cdf).pvalue > 1e-3
+    assert stats.kstest(bd['z'].cpu().numpy().ravel(), 'norm').pvalue > 1e-3
+
+
+@pytest.mark.parametrize('kind', ['gauss', 't'])
+def test_family_sample_logdensity(kind):
+    import torch
+    fam, ofam = _families(kind, 6, 'f64')
+    lam = _lam(6, 4)
+    rs = np.random.RandomState(5)
+    x = rs.randn(1000, 6) * 2
+    np.testing.assert_allclose(fam.logdensity(x, lam), ofam.logdensity(x, lam), rtol=1e-12)
+    one = fam.logdensity(x[0], lam)
+    np.testing.assert_allclose(one, ofam.logdensity(x[0], lam), rtol=1e-12)
+    assert np.shape(one) == np.shape(ofam.logdensity(x[0], lam))
+    # device tensors in -> device tensors out, no copy of the input
+    xd = torch.from_numpy(x).cuda()
+    out = fam.logdensity(xd, lam)
+    assert out.is_cuda
+    np.testing.assert_allclose(out.cpu().numpy(), ofam.logdensity(x, lam), rtol=1e-12)
+    s = fam.sample(lam, 1000)
+    assert isinstance(s, np.ndarray) and s.shape == (1000, 6)
+
+
+def test_model_plugins_logp_and_grad():
+    for name, (model, omodel, d) in _models().items():
+        x = np.random.RandomState(1).randn(777, d)
+        lp, g = model.logp_and_grad(x)
+        olp, og = omodel.logp_and_grad(x)
+        np.testing.assert_allclose(lp, olp, rtol=1e-12, atol=1e-12)
+        np.testing.assert_allclose(g, og, rtol=1e-12, atol=1e-12)
+        np.testing.assert_allclose(model(x), olp, rtol=1e-12, atol=1e-12)
+
+
+def test_funnel_adagrad_config1_runs_and_improves():
+    """BASELINE config 1 in miniature: funnel d=2, mean-field Gaussian KLVI, AdaGrad, then all_bounds."""
+    import viabel_b200
+    from viabel_b200 import models, vb
+    fam = vb.mean_field_gaussian_variational_family(2)
+    model = models.Funnel()
+    obj = vb.black_box_klvi(fam, model, 1000, group=False)
+    init = np.array([0., -1., 1., 1.])                 # notebooks/funnel-distribution.ipynb:241-243
+    opt, hist, vals, _ = vb.adagrad_optimize(400, obj, init, learning_rate=.01, learning_rate_end=.001)
+    assert hist.shape == (100, 4) and np.all(np.isfinite(vals))
+    assert vals[-50:].mean() < vals[:50].mean()
+    samples = fam.sample(opt, 100000, seed=1)
+    lw = model(samples) - fam.logdensity(samples, opt)
+    res = viabel_b200.all_bounds(lw, q_var=fam.mean_and_cov(opt)[1],
+                                 moment_bound_fn=lambda p: fam.pth_moment(p, opt))
+    assert set(res) == {'W1', 'W2', 'mean_error', 'std_error', 'cov_error', 'd2', 'log_norm_bound'}
+    assert np.isfinite(res['d2'])

@@ -72,3 +72,13 @@ class Workspace:
 
 
 WS = Workspace()
+
+
+def all_gather_rows(t, world, group=None):
+    """One all_gather of a small vector: returns (world, numel) with row r = rank r's vector.
+    Flat output buffer so that the same call works on NCCL and on gloo (CPU tests)."""
+    import torch.distributed as dist
+    flat = t.contiguous().reshape(-1)
+    out = torch.empty(world * flat.numel(), dtype=flat.dtype, device=flat.device)
+    dist.all_gather_into_tensor(out, flat, group=group)
+    return out.view(world, flat.numel())

@@ -8,7 +8,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._device import WS, dtype_code, is_host, ptr, stream_ptr, to_dev
+from ._device import WS, all_gather_rows, dtype_code, is_host, ptr, stream_ptr, to_dev
 
 __all__ = [
     'all_bounds',
@@ -41,8 +41,7 @@ def _divergence_stats(log_weights, alpha, group=None):
         part = torch.empty(6, dtype=torch.float64, device=lw.device)
         _lib.check(_lib.lib.vb_bounds_divergence_partials(ptr(lw), n, float(alpha), ptr(part), ptr(ws), ws.numel(),
                                                           stream_ptr()), 'vb_bounds_divergence_partials')
-        gathered = torch.empty((world, 6), dtype=torch.float64, device=lw.device)
-        dist.all_gather_into_tensor(gathered, part, group=g)
+        gathered = all_gather_rows(part, world, g)
         _lib.check(_lib.lib.vb_bounds_divergence_merge(ptr(gathered), world, float(alpha), ptr(out), stream_ptr()),
                    'vb_bounds_divergence_merge')
     return out.cpu().numpy()
@@ -100,8 +99,7 @@ def _sample_moments(samples, want_cov, group=None):
     if world > 1:
         import torch.distributed as dist
         pack = torch.cat([colsum, torch.tensor([float(n)], dtype=torch.float64, device=x.device)])
-        gathered = torch.empty((world, d + 1), dtype=torch.float64, device=x.device)
-        dist.all_gather_into_tensor(gathered, pack, group=g)
+        gathered = all_gather_rows(pack, world, g)
         tot = gathered.sum(0)
         colsum, n_total = tot[:d].contiguous(), int(round(float(tot[d])))
     mean = (colsum / n_total).contiguous()
@@ -112,8 +110,7 @@ def _sample_moments(samples, want_cov, group=None):
     if world > 1:
         import torch.distributed as dist
         pack = central if scatter is None else torch.cat([central, scatter.reshape(-1)])
-        gathered = torch.empty((world, pack.numel()), dtype=torch.float64, device=x.device)
-        dist.all_gather_into_tensor(gathered, pack.contiguous(), group=g)
+        gathered = all_gather_rows(pack, world, g)
         tot = gathered.sum(0)
         central = tot[:2]
         if scatter is not None:

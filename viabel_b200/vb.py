@@ -23,7 +23,7 @@ import torch
 import tqdm
 
 from . import _lib
-from ._device import WS, Workspace, device, dtype_code, is_host, like_input, ptr, stream_ptr, to_dev, torch_dtype
+from ._device import WS, Workspace, all_gather_rows, device, dtype_code, is_host, like_input, ptr, stream_ptr, to_dev, torch_dtype
 from .models import Model
 
 __all__ = [
@@ -393,8 +393,7 @@ class _Objective:
     def _mf_merge(self, vp, partials, world, g):
         import torch.distributed as dist
         d = self.impl.dim
-        gathered = torch.empty((world, partials.numel()), dtype=torch.float64, device=vp.device)
-        dist.all_gather_into_tensor(gathered, partials, group=g)
+        gathered = all_gather_rows(partials, world, g)
         out = torch.empty(1 + 2 * d, dtype=torch.float64, device=vp.device)
         _lib.check(_lib.lib.vb_mf_finalize(self.impl.kind, self.obj, self.alpha, ptr(vp), d, ptr(gathered), world,
                                            ptr(out), ptr(out) + 8, stream_ptr()), 'vb_mf_finalize')
@@ -433,8 +432,7 @@ class _Objective:
         if world > 1:
             # one exchange: [sum w, sum logp, sum lw, g_mu (d), G_S (d*d)] gathered and summed in rank order
             pack = torch.cat([rows[1:4], g_mu, G_S.reshape(-1)])
-            gathered = torch.empty((world, pack.numel()), dtype=torch.float64, device=vp.device)
-            dist.all_gather_into_tensor(gathered, pack, group=g)
+            gathered = all_gather_rows(pack, world, g)
             tot = gathered[0].clone()
             for r in range(1, world):
                 tot += gathered[r]
