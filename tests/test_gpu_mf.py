@@ -114,7 +114,7 @@ def test_philox_step_equals_step_on_its_own_draws(kind):
     assert v2 != v
     x = fam.sample(lam, n, seed=5)
     eps5 = fam.impl.base_draws(n, 5, 0)['eps'].cpu().numpy()
-    np.testing.assert_allclose(x, lam[:d] + np.exp(lam[d:]) * eps5, rtol=1e-14)
+    np.testing.assert_allclose(x, lam[:d] + np.exp(lam[d:]) * eps5, rtol=1e-13, atol=1e-15)
     # CHIVI takes its seed from numpy's global RNG like vb.py:258
     np.random.seed(123)
     expect_seed = np.random.randint(2 ** 32)

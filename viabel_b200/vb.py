@@ -195,6 +195,7 @@ class _FullRank(_FamilyImpl):
 
     def gemm(self, A, B, transa=False, transb=False):
         """fp64 d x d product through the library's own GEMM."""
+        A, B = A.contiguous(), B.contiguous()      # eigh returns column-major eigenvectors
         m = A.shape[1] if transa else A.shape[0]
         k = A.shape[0] if transa else A.shape[1]
         n = B.shape[0] if transb else B.shape[1]
