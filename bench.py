@@ -34,6 +34,7 @@ def parse():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--profile-kernel-only', action='store_true',
                     help='run only the dominant-kernel loop (for ncu captures)')
+    ap.add_argument('--profile-step', action='store_true', help='run only the device-resident step loop (for ncu)')
     return ap.parse_args()
 
 
@@ -154,8 +155,8 @@ def main():
             ms = float(t.item())
         return ms
 
-    if args.profile_kernel_only:
-        timed(wl.kernel_only, steps, warmup)
+    if args.profile_kernel_only or args.profile_step:
+        timed(wl.kernel_only if args.profile_kernel_only else wl.step_device, steps, warmup)
         return
 
     sampler = ClockSampler(local_rank)

@@ -140,3 +140,29 @@ def test_full_rank_family_closures():
     mp, Pp = _gauss(d)
     v, g = vb.black_box_chivi(2.0, fam, models.CorrelatedGaussian(mp, Pp), 2000, group=False)(lam)
     assert np.isfinite(v) and g.shape == (fam.var_param_dim,) and np.all(np.isfinite(g))
+
+
+@pytest.mark.parametrize('m,n,k', [(128, 128, 32), (128, 128, 256), (256, 384, 96), (1000, 200, 520), (77, 130, 36)])
+@pytest.mark.parametrize('ta,tb', [(0, 1), (0, 0), (1, 1), (1, 0)])
+def test_gemm_tf32x3(m, n, k, ta, tb):
+    """3xTF32 tcgen05 GEMM against fp64 numpy.  Stated tolerance: 2e-6 * sum_k |a||b| per entry
+    (measured ~3e-7); a single-pass TF32 product would be ~5e-4."""
+    import torch
+    from viabel_b200 import _lib
+    from viabel_b200._device import ptr, stream_ptr
+    rs = np.random.RandomState(m + n + k)
+    A = rs.randn(*((k, m) if ta else (m, k))).astype(np.float32)
+    B = rs.randn(*((n, k) if tb else (k, n))).astype(np.float32)
+    C0 = rs.randn(m, n).astype(np.float32)
+    Ad, Bd, Cd = (torch.from_numpy(x).cuda() for x in (A, B, C0.copy()))
+    nb = _lib.lib.vb_gemm_workspace_bytes(_lib.F32, m, n, k)
+    ws = torch.zeros(nb, dtype=torch.uint8, device='cuda')
+    _lib.check(_lib.lib.vb_gemm(_lib.F32, ta, tb, m, n, k, 0.5, ptr(Ad), A.shape[1], ptr(Bd), B.shape[1],
+                                2.0, ptr(Cd), n, ptr(ws), ws.numel(), stream_ptr()))
+    torch.cuda.synchronize()
+    opA = (A.T if ta else A).astype(np.float64)
+    opB = (B.T if tb else B).astype(np.float64)
+    want = 0.5 * opA @ opB + 2.0 * C0
+    bound = 2e-6 * (np.abs(opA) @ np.abs(opB)) + 1e-6 * np.abs(want)
+    err = np.abs(Cd.cpu().numpy() - want)
+    assert np.all(err <= bound), (err.max(), (err / bound).max())

@@ -28,7 +28,7 @@ struct DivAcc {
             sw2 *= f * f;
             M = x;
         }
-        const double w = exp(alpha * (x - M));
+        const double w = exp_nonpos(alpha * (x - M));
         sw += w;
         sw2 = fma(w, w, sw2);
         const double d = x - K;
@@ -133,19 +133,26 @@ __device__ void divergence_finalize(const double* parts, int R, double alpha, do
     out[7] = 0.0;
 }
 
-__global__ void divergence_finish_kernel(const double* __restrict__ lw, const double* __restrict__ blocks, int G,
-                                         double alpha, double* out_partials, double* out) {
-    if (threadIdx.x != 0) return;
+__global__ void __launch_bounds__(256)
+divergence_finish_kernel(const double* __restrict__ lw, const double* __restrict__ blocks, int G,
+                         double alpha, double* out_partials, double* out) {
+    __shared__ double scratch[32];
+    __shared__ double p[6];
     const double K = lw[0];
     double M = -INFINITY;
-    for (int b = 0; b < G; ++b) M = fmax(M, blocks[(size_t)b * 6]);
-    double p[6] = {M, 0, 0, 0, 0, 0};
-    double sd = 0, sd2 = 0;
-    for (int b = 0; b < G; ++b) {
+    for (int b = threadIdx.x; b < G; b += blockDim.x) M = fmax(M, blocks[(size_t)b * 6]);
+    M = block_max(M, scratch);
+    double acc[5] = {0, 0, 0, 0, 0};
+    for (int b = threadIdx.x; b < G; b += blockDim.x) {          // fixed thread->block map, fixed tree below
         const double* q = blocks + (size_t)b * 6;
         const double f = rescale_factor(alpha, q[0], M);
-        p[1] += q[1] * f; p[2] += q[2] * f * f; p[3] += q[3]; sd += q[4]; sd2 += q[5];
+        acc[0] += q[1] * f; acc[1] += q[2] * f * f; acc[2] += q[3]; acc[3] += q[4]; acc[4] += q[5];
     }
+#pragma unroll
+    for (int k = 0; k < 5; ++k) acc[k] = block_sum(acc[k], scratch);
+    if (threadIdx.x != 0) return;
+    const double sd = acc[3], sd2 = acc[4];
+    p[0] = M; p[1] = acc[0]; p[2] = acc[1]; p[3] = acc[2];
     p[4] = K + sd / p[3];
     p[5] = sd2 - sd * sd / p[3];
     if (out_partials) for (int k = 0; k < 6; ++k) out_partials[k] = p[k];
@@ -296,7 +303,7 @@ static int run_divergence(const double* lw, long long n, double alpha, double* o
     const int grid = grid_for((n + 1) / 2, kDivThreads, kNumSMs * 8);
     divergence_blocks_kernel<<<grid, kDivThreads, 0, st>>>(lw, n, alpha, (double*)ws);
     VB_LAUNCH_CHECK();
-    divergence_finish_kernel<<<1, 32, 0, st>>>(lw, (const double*)ws, grid, alpha, out_partials, out);
+    divergence_finish_kernel<<<1, 256, 0, st>>>(lw, (const double*)ws, grid, alpha, out_partials, out);
     VB_LAUNCH_CHECK();
     return VB_OK;
 }

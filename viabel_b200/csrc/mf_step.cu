@@ -100,7 +100,7 @@ __device__ __forceinline__ double mf_merge_component(const double* parts, int R,
 }
 
 template <typename T, int FAM, class Model, int OBJ, bool PHILOX>
-__global__ void __launch_bounds__(kMfThreads)
+__global__ void __launch_bounds__(kMfThreads, 2)
 mf_step_kernel(const __grid_constant__ MfArgs<Model> a) {
     constexpr int D = Model::D;
     constexpr int NP = 2 * D + 4;
@@ -118,12 +118,13 @@ mf_step_kernel(const __grid_constant__ MfArgs<Model> a) {
     const long long n_full_tiles = n / TILE;
     const long long n_tiles = (n + TILE - 1) / TILE;
 
-    T mean[D], sig[D];
-#pragma unroll
-    for (int j = 0; j < D; ++j) {
-        mean[j] = (T)a.var_param[j];
-        sig[j] = (T)exp(a.var_param[D + j]);
+    // location / scale live in shared memory (broadcast reads) to keep registers for the accumulators
+    __shared__ T mean[D], sig[D];
+    if (tid < D) {
+        mean[tid] = (T)a.var_param[tid];
+        sig[tid] = (T)exp(a.var_param[D + tid]);
     }
+    __syncthreads();
     const T df = (T)a.df;
     double sum_l = 0.0;
 #pragma unroll
@@ -325,6 +326,9 @@ static int launch_mf(const MfCall& c, const typename Model::P& mp) {
     static int blocks_per_sm = 1;
     if (!configured) {
         VB_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        if (smem > 0)
+            VB_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                             (int)cudaSharedmemCarveoutMaxShared));
         VB_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern, kMfThreads, smem));
         if (blocks_per_sm < 1) blocks_per_sm = 1;
         configured = true;

@@ -81,8 +81,8 @@ struct EightSchools {
             s_tt += th * th;
             g[2 + j] = -th + tau * ros;
         }
-        lp = -mu * mu / (T)50 - Math<T>::log1p(tau2 / (T)25) + lt - (T)0.5 * s_tt - (T)0.5 * s_rr;
-        g[0] = -mu / (T)25 + s_ros;
+        lp = -mu * mu * (T)0.02 - Math<T>::log1p(tau2 * (T)0.04) + lt - (T)0.5 * s_tt - (T)0.5 * s_rr;
+        g[0] = -mu * (T)0.04 + s_ros;
         g[1] = (T)1 - (T)2 * tau2 / ((T)25 + tau2) + tau * s_tros;
     }
 };
