@@ -330,3 +330,223 @@ class C5(Workload):
 
 
 WORKLOADS = {'c1': C1, 'c4': C4, 'c5': C5}
+
+
+# ======================================================================================= C3
+def c3_problem(d=512):
+    """Sigma_p = A A'/d + I (seed 4), mu_p (seed 5), var_param = 0.1 N(0,1) (seed 6): SURVEY 8(d) C3."""
+    A = np.random.RandomState(4).randn(d, d)
+    Sp = A @ A.T / d + np.eye(d)
+    mp = np.random.RandomState(5).randn(d)
+    lam = 0.1 * np.random.RandomState(6).randn(d + d * (d + 1) // 2)
+    return mp, np.linalg.inv(Sp), lam
+
+
+class C3(Workload):
+    """CHIVI (alpha 2), full-rank Student-t (df 40), d = 512, correlated-Gaussian target, 2^16 samples/step."""
+    name = 'c3'
+    n, d = 1 << 16, 512
+    dtype = 'f32 storage, 3xTF32 tensor-core products, fp64 accumulation of reductions'
+    default_steps, default_warmup = 10, 3
+    cpu_sample = 1 << 13
+    scale = 'sqrtm'
+
+    def setup(self):
+        import torch
+        from viabel_b200 import models, vb, _lib
+        from viabel_b200._device import ptr
+        self.torch, self.lib = torch, _lib
+        mp, Pp, lam = c3_problem(self.d)
+        self.model = models.CorrelatedGaussian(mp, Pp)
+        self.fam = vb.t_variational_family(self.d, 40, dtype='f32', scale=self.scale)
+        self.obj = vb.black_box_chivi(2.0, self.fam, self.model, self.n * self.world)
+        self.base = self.fam.impl.base_draws(self.n, 0, 0, index0=self.rank * self.n)
+        self.lam_host = lam
+        self.lam_dev = torch.from_numpy(lam).cuda()
+        self.units_per_step = self.n
+        self.h2d_bytes = lam.nbytes
+        self.d2h_bytes = 8 * (1 + lam.size)
+        self.launches_per_step = 40
+        # pre-split operands for the kernel-only timing: X (n, d) = Z (n, d) S (d, d)
+        lib = _lib.lib
+        z = self.base['z']
+        S = torch.randn(self.d, self.d, dtype=torch.float32, device='cuda')
+        self._zs = torch.empty(lib.vb_split_bytes(self.n, self.d) // 4, dtype=torch.float32, device='cuda')
+        self._ss = torch.empty(lib.vb_split_bytes(self.d, self.d) // 4, dtype=torch.float32, device='cuda')
+        _lib.check(lib.vb_split_f32(ptr(z), self.n, self.d, self.d, ptr(self._zs), 0))
+        _lib.check(lib.vb_split_f32(ptr(S), self.d, self.d, self.d, ptr(self._ss), 0))
+        self._c = torch.empty((self.n, self.d), dtype=torch.float32, device='cuda')
+        self._ptr = ptr
+
+    def step_device(self):
+        return self.obj(self.lam_dev, base_draws=self.base)
+
+    def step_e2e(self):
+        return self.obj(self.lam_host)
+
+    def kernel_only(self):
+        from viabel_b200._device import stream_ptr
+        p = self._ptr
+        self.lib.check(self.lib.lib.vb_gemm_tf32x3_split(0, 1, self.n, self.d, self.d, p(self._zs), p(self._ss),
+                                                         p(self._c), self.d, stream_ptr()))
+
+    def roofline(self, ms_kernel, hbm_gbs, bf16_tflops):
+        flops = 2.0 * self.n * self.d * self.d                # algorithmic: counted once, the 3x split is overhead
+        ach = flops / (ms_kernel * 1e-3) / 1e12
+        peak = bf16_tflops / 2.0
+        return {'bound': 'tensor', 'achieved': ach, 'peak': peak, 'unit': 'TFLOP/s', 'frac': ach / peak,
+                'traffic': None, 'kernel': 'gemm_tf32x3_kernel<K-major A, MN-major B> (z S product, 65536x512x512)',
+                'ms_per_launch': ms_kernel, 'algorithmic_flops_per_launch': flops,
+                'note': 'peak = measured dense bf16 / 2 (tf32 runs at half the bf16 rate); three tf32 MMAs are issued '
+                        'per algorithmic product, so frac <= 1/3 by construction; tensor-pipe rate = 3 x achieved'}
+
+    def config(self):
+        return {'workload': self.config_name(), 'samples_per_step_per_gpu': self.n, 'scale': self.scale,
+                'value_mode': 'streaming: fp32 base draws (134 MB) resident in HBM',
+                'e2e_mode': 'Philox draws, host var_param (131840 doubles) in, host (value, grad) out',
+                'l2': 'inputs (134 MB z + intermediates) larger than L2', 'parallelism': 'sample-sharded x%d' % self.world}
+
+    def config_name(self):
+        return 'c3: CHIVI alpha=2, full-rank Student-t(df=40) d=512, correlated-Gaussian target, 2^16 samples/step/GPU'
+
+    def _cpu(self, n):
+        from oracle import models_np, vb_np
+        mp, Pp, lam = c3_problem(self.d)
+        fam = vb_np.t_variational_family(self.d, 40, scale=self.scale)
+        model = models_np.CorrelatedGaussian(mp, Pp)
+        t0 = time.perf_counter()
+        base = fam.impl.draw_base(np.random.RandomState(1), n)
+        vb_np.chivi_value_and_grad(fam.impl, model, 2.0, lam, base)
+        return n / (time.perf_counter() - t0)
+
+    def cpu_baseline(self):
+        rate = self._cpu(self.cpu_sample)
+        return {'value': rate, 'unit': self.unit, 'cores': host_cores(), 'kind': 'port',
+                'sample': 'oracle closed-form CHIVI step on %d samples (numpy + multithreaded BLAS; includes the '
+                          'O(d^3) eigh/sqrtm chain once)' % self.cpu_sample}
+
+    def reference_arm(self, steps, warmup):
+        n = self.cpu_sample * 2
+        self._cpu(1 << 10)
+        k = max(1, min(steps, 3))
+        t0 = time.perf_counter()
+        for _ in range(k):
+            self._cpu(n)
+        dt = (time.perf_counter() - t0) / k
+        rate = n / dt
+        cb = {'value': rate, 'unit': self.unit, 'cores': host_cores(), 'kind': 'port',
+              'sample': 'oracle closed-form CHIVI step on %d samples/step, numpy with BLAS threads on all cores' % n}
+        return {'metric': self.metric, 'value': rate, 'unit': self.unit, 'ms_per_step': dt * 1e3, 'dtype': 'f64',
+                'config': {'workload': self.config_name()}, 'cpu_baseline': cb,
+                'e2e': {'value': rate, 'unit': self.unit, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+
+
+class C3Chol(C3):
+    """Same as c3 with the documented same-distribution fast mode x = mu + L ztilde (no eigh / Sylvester)."""
+    name = 'c3chol'
+    scale = 'chol'
+
+    def config_name(self):
+        return C3.config_name(self) + ' [scale=chol: deviation from the reference per-draw map]'
+
+
+# ======================================================================================= C2
+def c2_problem(N=1 << 20, d=128):
+    """X ~ N(0,1)/sqrt(d) (seed 1), beta* (seed 2), y = X beta* + t_40 centred, var_param (seed 3)."""
+    X = (np.random.RandomState(1).randn(N, d) / np.sqrt(d)).astype(np.float32)
+    bt = np.random.RandomState(2).randn(d)
+    y = X.astype(np.float64) @ bt + np.random.RandomState(12).standard_t(40, N)
+    y = (y - y.mean()).astype(np.float32)
+    lam = np.concatenate([bt + 0.01 * np.random.RandomState(3).randn(d), np.full(d, np.log(1e-3))])
+    return X, y, lam
+
+
+class C2(Workload):
+    """Student-t robust regression N = 2^20 rows, d = 128; KLVI, mean-field Student-t (df 40), 4096 samples/step."""
+    name = 'c2'
+    n, N, d = 4096, 1 << 20, 128
+    dtype = 'f64'
+    compute = 'f64'
+    default_steps, default_warmup = 3, 3
+    cpu_rows = 1 << 16
+
+    def setup(self):
+        import torch
+        from viabel_b200 import models, vb, _lib
+        self.lib = _lib
+        X, y, lam = c2_problem(self.N, self.d)
+        self.model = models.StudentTRegression(X, y, df=40.0, dtype='f32')
+        self.fam = vb.mean_field_t_variational_family(self.d, 40, dtype=self.compute)
+        self.obj = vb.black_box_klvi(self.fam, self.model, self.n * self.world)
+        self.eps = self.fam.impl.base_draws(self.n, 0, 0, index0=self.rank * self.n)['eps']
+        self.lam_host = lam
+        self.lam_dev = torch.from_numpy(lam).cuda()
+        self.units_per_step = self.n
+        self.h2d_bytes, self.d2h_bytes = lam.nbytes, 8 * (1 + lam.size)
+        self.launches_per_step = 3 * 32 + 8
+        self._x = torch.from_numpy(np.tile(lam[:self.d], (self.n, 1))).cuda()
+        if self.compute == 'f32':
+            self._x = self._x.float()
+
+    def step_device(self):
+        return self.obj(self.lam_dev, base_draws=self.eps)
+
+    def step_e2e(self):
+        return self.obj(self.lam_host)
+
+    def kernel_only(self):
+        code = self.lib.F64 if self.compute == 'f64' else self.lib.F32
+        self.model.logp_and_grad_device(self._x, code, True)
+
+    def roofline(self, ms_kernel, hbm_gbs, bf16_tflops):
+        flops = 4.0 * self.N * self.d * self.n
+        ach = flops / (ms_kernel * 1e-3) / 1e12
+        peak = bf16_tflops / 2.0
+        return {'bound': 'tensor', 'achieved': ach, 'peak': peak, 'unit': 'TFLOP/s', 'frac': ach / peak,
+                'traffic': None, 'kernel': 'regression log p + grad pipeline (two GEMMs per row chunk, %s)' % self.compute,
+                'ms_per_launch': ms_kernel, 'algorithmic_flops_per_launch': flops,
+                'note': 'fp64 path runs on the DFMA pipe (SIMT), not the tensor pipe; peak shown is the tf32 tensor peak '
+                        '(measured bf16 / 2) the fp32 path is measured against' if self.compute == 'f64' else
+                        'peak = measured dense bf16 / 2; 3 tf32 MMAs per algorithmic product'}
+
+    def config(self):
+        return {'workload': self.config_name(), 'samples_per_step_per_gpu': self.n, 'rows': self.N, 'compute': self.compute,
+                'l2': 'design matrix (512 MB fp32) larger than L2', 'parallelism': 'sample-sharded x%d' % self.world}
+
+    def config_name(self):
+        return 'c2: Student-t regression N=2^20 rows d=128, KLVI mean-field Student-t(df=40), 4096 samples/step/GPU'
+
+    def _cpu(self, rows):
+        """Full 4096 samples over a bounded number of design-matrix rows; samples/s scaled to N rows."""
+        from oracle import models_np, vb_np
+        X, y, lam = c2_problem(rows, self.d)
+        model = models_np.StudentTRegression(X.astype(np.float64), y.astype(np.float64), 40.0, row_block=1 << 12)
+        fam = vb_np.mean_field_t_variational_family(self.d, 40)
+        base = fam.impl.draw_base(np.random.RandomState(1), self.n)
+        t0 = time.perf_counter()
+        vb_np.klvi_value_and_grad(fam.impl, model, lam, base)
+        dt = time.perf_counter() - t0
+        return self.n / (dt * self.N / rows)
+
+    def cpu_baseline(self):
+        rate = self._cpu(self.cpu_rows)
+        return {'value': rate, 'unit': self.unit, 'cores': host_cores(), 'kind': 'port',
+                'sample': 'oracle KLVI step, 4096 samples x %d of the 2^20 rows (time scaled x%d); numpy + BLAS threads'
+                          % (self.cpu_rows, self.N // self.cpu_rows)}
+
+    def reference_arm(self, steps, warmup):
+        self._cpu(1 << 12)
+        k = max(1, min(steps, 2))
+        t0 = time.perf_counter()
+        rates = [self._cpu(self.cpu_rows) for _ in range(k)]
+        dt = (time.perf_counter() - t0) / k
+        rate = float(np.mean(rates))
+        cb = {'value': rate, 'unit': self.unit, 'cores': host_cores(), 'kind': 'port',
+              'sample': 'oracle KLVI step, 4096 samples x %d of 2^20 rows per step (time scaled x%d), BLAS on all cores'
+                        % (self.cpu_rows, self.N // self.cpu_rows)}
+        return {'metric': self.metric, 'value': rate, 'unit': self.unit, 'ms_per_step': dt * 1e3, 'dtype': 'f64',
+                'config': {'workload': self.config_name()}, 'cpu_baseline': cb,
+                'e2e': {'value': rate, 'unit': self.unit, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+
+
+WORKLOADS.update({'c2': C2, 'c3': C3, 'c3chol': C3Chol})

@@ -162,6 +162,7 @@ int vb_mf_logdensity(int family, double df, int dtype, const double* d_var_param
  *                    (maha_i = |z_i|^2 / (chi2_i/df)), running max
  *   vb_fr_weighted   g_mu = sum_i w_i g_i ;  G_S = Ztilde' diag(w) G  (dim x dim)
  * ---------------------------------------------------------------------------------- */
+size_t vb_fr_sample_workspace_bytes(int dtype, long long n, int dim);
 int vb_fr_sample(int dtype, const double* d_mu, const void* d_scale /* (dim,dim) dtype */,
                  double df, long long n, int dim, const void* d_z, const void* d_chi2,
                  void* d_out_x, void* d_ws, size_t ws_bytes, void* stream);
@@ -192,6 +193,19 @@ size_t vb_gemm_workspace_bytes(int dtype, long long m, long long n, long long k)
 int vb_gemm(int dtype, int transa, int transb, long long m, long long n, long long k,
             double alpha, const void* d_A, long long lda, const void* d_B, long long ldb,
             double beta, void* d_C, long long ldc, void* d_ws, size_t ws_bytes, void* stream);
+
+/* Operands of the 3xTF32 tensor path are "split" matrices: two fp32 planes (tf32 hi part, tf32 lo
+ * part) of shape (rows, pad4(cols)), plane 1 following plane 0.  vb_split_f32 produces them;
+ * vb_gemm_tf32x3_split multiplies pre-split operands: C (m, n) fp32 = A B with
+ *   A planes stored (m, k) [a_mn_major = 0] or (k, m) [a_mn_major = 1],
+ *   B planes stored (n, k) [b_mn_major = 0] or (k, n) [b_mn_major = 1].
+ * Serves the full-rank scale product z S (viabel/vb.py:208) and the design-matrix products. */
+size_t vb_split_bytes(long long rows, long long cols);
+int vb_split_f32(const float* d_src, long long rows, long long cols, long long ld,
+                 float* d_dst_planes, void* stream);
+int vb_gemm_tf32x3_split(int a_mn_major, int b_mn_major, long long m, long long n, long long k,
+                         const float* d_A_planes, const float* d_B_planes,
+                         float* d_C, long long ldc, void* stream);
 
 /* ------------------------------------------------------------------------------------
  * Bounds (viabel/bounds.py).

@@ -166,3 +166,27 @@ def test_gemm_tf32x3(m, n, k, ta, tb):
     bound = 2e-6 * (np.abs(opA) @ np.abs(opB)) + 1e-6 * np.abs(want)
     err = np.abs(Cd.cpu().numpy() - want)
     assert np.all(err <= bound), (err.max(), (err / bound).max())
+
+
+@pytest.mark.parametrize('scale', ['sqrtm', 'chol'])
+@pytest.mark.parametrize('d,n', [(16, 1000), (96, 5000), (200, 4097)])
+def test_full_rank_t_f32_tensor_path(scale, d, n):
+    """fp32 storage + 3xTF32 tcgen05 products + fp64 reductions against the fp64 oracle on the same
+    (fp32-rounded) base draws.  Stated tolerance: value rtol 5e-6 (KLVI) / 2e-5 (CHIVI), gradient 1e-4 / 2e-3 of its max entry."""
+    from viabel_b200 import models, vb
+    mp, Pp = _gauss(d)
+    model, omodel = models.CorrelatedGaussian(mp, Pp), mm.CorrelatedGaussian(mp, Pp)
+    fam = vb.t_variational_family(d, 40, dtype='f32', scale=scale)
+    ofam = vb_np.t_variational_family(d, 40, scale=scale)
+    lam = 0.1 * np.random.RandomState(6).randn(fam.var_param_dim)
+    base = ofam.impl.draw_base(np.random.RandomState(5), n)
+    b32 = {'z': base['z'].astype(np.float32), 'chi2': base['chi2'].astype(np.float32)}
+    br = {'z': b32['z'].astype(np.float64), 'chi2': b32['chi2'].astype(np.float64)}
+    v, g = vb.black_box_klvi(fam, model, n, group=False)(lam, base_draws=b32)
+    ov, og = vb_np.klvi_value_and_grad(ofam.impl, omodel, lam, br)
+    np.testing.assert_allclose(v, ov, rtol=5e-6)
+    assert np.max(np.abs(g - og)) < 1e-4 * np.max(np.abs(og))
+    v, g = vb.black_box_chivi(2.0, fam, model, n, group=False)(lam, base_draws=b32)
+    ov, og = vb_np.chivi_value_and_grad(ofam.impl, omodel, 2.0, lam, br)
+    np.testing.assert_allclose(v, ov, rtol=2e-5)
+    assert np.max(np.abs(g - og)) < 2e-3 * np.max(np.abs(og))

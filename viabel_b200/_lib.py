@@ -39,6 +39,7 @@ SIGNATURES = {
     'vb_mf_reduce': (_i, [_i, _d, _i, _d, _i, _p, _ll, _i, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     'vb_mf_sample': (_i, [_i, _p, _ll, _i, _p, _p, _p]),
     'vb_mf_logdensity': (_i, [_i, _d, _i, _p, _ll, _i, _p, _p, _p]),
+    'vb_fr_sample_workspace_bytes': (_sz, [_i, _ll, _i]),
     'vb_fr_sample': (_i, [_i, _p, _p, _d, _ll, _i, _p, _p, _p, _p, _sz, _p]),
     'vb_fr_logdensity_workspace_bytes': (_sz, [_ll, _i]),
     'vb_fr_logdensity': (_i, [_i, _p, _p, _d, _d, _ll, _i, _p, _p, _p, _sz, _p]),
@@ -48,6 +49,9 @@ SIGNATURES = {
     'vb_fr_weighted': (_i, [_i, _d, _ll, _i, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     'vb_gemm_workspace_bytes': (_sz, [_i, _ll, _ll, _ll]),
     'vb_gemm': (_i, [_i, _i, _i, _ll, _ll, _ll, _d, _p, _ll, _p, _ll, _d, _p, _ll, _p, _sz, _p]),
+    'vb_split_bytes': (_sz, [_ll, _ll]),
+    'vb_split_f32': (_i, [_p, _ll, _ll, _ll, _p, _p]),
+    'vb_gemm_tf32x3_split': (_i, [_i, _i, _ll, _ll, _ll, _p, _p, _p, _ll, _p]),
     'vb_bounds_divergence_workspace_bytes': (_sz, [_ll]),
     'vb_bounds_divergence': (_i, [_p, _ll, _d, _p, _p, _sz, _p]),
     'vb_bounds_divergence_partials': (_i, [_p, _ll, _d, _p, _p, _sz, _p]),

@@ -183,6 +183,11 @@ struct AxpbyStore {
 
 using namespace vb;
 
+extern "C" size_t vb_fr_sample_workspace_bytes(int dtype, long long n, int dim) {
+    if (n < 1 || dim < 1) return 0;
+    return dtype == VB_F32 ? fr_sample_tf32_workspace_bytes(n, dim) : 0;
+}
+
 extern "C" int vb_fr_sample(int dtype, const double* d_mu, const void* d_scale, double df, long long n, int dim,
                             const void* d_z, const void* d_chi2, void* d_out_x, void* d_ws, size_t ws_bytes,
                             void* stream) {
@@ -240,7 +245,8 @@ extern "C" size_t vb_fr_weighted_workspace_bytes(long long n, int dim) {
     if (n < 1 || dim < 1) return 0;
     const size_t a = (size_t)fr_splits(n, dim) * dim * dim * 8;
     const size_t b = (size_t)fr_chunks(n, dim) * dim * 8;
-    return a + b + 512;
+    const size_t t = fr_weighted_tf32_workspace_bytes(n, dim) + b + 256;     // fp32 storage: tensor path
+    return (a + b + 512) > t ? (a + b + 512) : t;
 }
 
 extern "C" int vb_fr_weighted(int dtype, double df, long long n, int dim, const void* d_z,
@@ -265,12 +271,17 @@ extern "C" int vb_fr_weighted(int dtype, double df, long long n, int dim, const 
         fr_wcolsum_kernel<double><<<dim3((dim + 31) / 32, chunks), dim3(32, 8), 0, st>>>(n, dim, (const double*)d_grad,
                                                                                        d_w, rpc, colparts);
     } else {
-        rc = launch_gemm_f64(dim, dim, n, splits,
-                             ScaledZt<float>{(const float*)d_z, dim, d_w, (const float*)d_chi2, df},
-                             RowMajor<float>{(const float*)d_grad, dim}, SplitStoreFr{parts, mn, dim}, st);
+        // fp32 storage: G_S on the tensor path (3xTF32, split-K), g_mu by the fp64-accumulating column sum
+        double* colparts32 = (double*)((char*)d_ws + ((fr_weighted_tf32_workspace_bytes(n, dim) + 255) & ~(size_t)255));
+        rc = fr_weighted_GS_tf32(df, n, dim, (const float*)d_z, (const float*)d_chi2, d_w, (const float*)d_grad,
+                                 d_out_GS, d_ws, fr_weighted_tf32_workspace_bytes(n, dim), st);
         if (rc != VB_OK) return rc;
         fr_wcolsum_kernel<float><<<dim3((dim + 31) / 32, chunks), dim3(32, 8), 0, st>>>(n, dim, (const float*)d_grad,
-                                                                                      d_w, rpc, colparts);
+                                                                                      d_w, rpc, colparts32);
+        VB_LAUNCH_CHECK();
+        fr_split_sum_kernel<<<grid_for(dim, 256, 8), 256, 0, st>>>(colparts32, chunks, dim, d_out_gmu);
+        VB_LAUNCH_CHECK();
+        return VB_OK;
     }
     VB_LAUNCH_CHECK();
     fr_split_sum_kernel<<<grid_for(mn, 256, kNumSMs * 4), 256, 0, st>>>(parts, splits, mn, d_out_GS);

@@ -266,7 +266,8 @@ extern "C" size_t vb_model_logp_grad_workspace_bytes(const vb_model* model, long
         const long long chunk = regression_chunk_rows(n, m->n_rows);
         return align_up((size_t)n * m->dim * 8, 256) + (size_t)n * chunk * 8 + 256;
     }
-    if (m->kind == VB_MODEL_GAUSS) return (size_t)n * m->dim * 8 + 256;    // G when the caller does not want it
+    if (m->kind == VB_MODEL_GAUSS)
+        return dtype == VB_F32 ? gauss_f32_workspace_bytes(n, m->dim) : (size_t)n * m->dim * 8 + 256;    // G when the caller does not want it
     return 256;
 }
 

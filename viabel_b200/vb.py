@@ -257,8 +257,9 @@ def t_variational_family(dim, df, dtype='f64', scale='sqrtm'):
         n = base['z'].shape[0]
         x = torch.empty_like(base['z'])
         S = impl.scale_matrix(ch)
+        ws = impl.ws.get('fr_sample', _lib.lib.vb_fr_sample_workspace_bytes(impl.code, n, dim))
         _lib.check(_lib.lib.vb_fr_sample(impl.code, ptr(ch['mu']), ptr(S), impl.df, n, dim, ptr(base['z']),
-                                         ptr(base['chi2']), ptr(x), 0, 0, stream_ptr()), 'vb_fr_sample')
+                                         ptr(base['chi2']), ptr(x), ptr(ws), ws.numel(), stream_ptr()), 'vb_fr_sample')
         return x, ch
     impl.sample_device = sample_device
 
