@@ -1,0 +1,28 @@
+#!/bin/bash
+# Run on the GPU box (under gpurun):  bash scripts/profile_round.sh <tag> [workloads...]
+# For every workload: a plain run, then the ncu launch list of the device-resident step, then one
+# `ncu --set full` capture of the dominant kernel(s).  Everything lands in gpurun_out/<tag>/.
+# Numbers printed under ncu are never bench values (B200_PROFILING.md).
+set -u
+TAG=${1:-r1}
+shift || true
+WLS=${@:-"c4 c5 c3 c2"}
+OUT=gpurun_out/$TAG
+mkdir -p $OUT
+declare -A KREGEX=( [c4]="mf_step_kernel" [c1]="mf_step_kernel" [c5]="prefilter_kernel|normalise_kernel|max_kernel|divergence"
+                    [c3]="gemm_tf32x3_kernel|fr_" [c3chol]="gemm_tf32x3_kernel" [c2]="regression|gemm" )
+for w in $WLS; do
+  echo "== $w: launch list"
+  python bench.py --workload $w --profile-step --steps 2 --warmup 3 > $OUT/plain_step_$w.log 2>&1 &&
+  ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file $OUT/launches_$w.csv \
+      python bench.py --workload $w --profile-step --steps 2 --warmup 3 > $OUT/ncu_step_$w.log 2>&1
+  echo "   rc=$?"
+  python scripts/launch_summary.py $OUT/launches_$w.csv > $OUT/launches_$w.txt 2>&1
+  echo "== $w: full capture of ${KREGEX[$w]}"
+  SKIP=2; [ "$w" = c5 ] && SKIP=3
+  python bench.py --workload $w --profile-kernel-only --steps 2 --warmup 3 > $OUT/plain_kernel_$w.log 2>&1 &&
+  ncu --set full --clock-control none --import-source on -k "regex:${KREGEX[$w]}" -s $SKIP -c 3 -f -o $OUT/prof_$w \
+      python bench.py --workload $w --profile-kernel-only --steps 2 --warmup 3 > $OUT/ncu_kernel_$w.log 2>&1
+  echo "   rc=$?"
+done
+ls -la $OUT
