@@ -259,6 +259,50 @@ int vb_psis_smooth(const double* d_lw_in, double* d_lw_out, long long n, double 
                    double* d_out_diag, long long* d_out_tail_idx_or_null,
                    void* d_ws, size_t ws_bytes, void* stream);
 
+/* Staged PSIS for log weights sharded by contiguous index ranges (rank r owns global indices
+ * [index0, index0 + n_local)); vb_psis_smooth is the same sequence on one GPU.  Candidates are
+ * 16-byte (key, global index) pairs; between the stages the caller exchanges a few small buffers:
+ *   S1 vb_psis_sample   VB_PSIS_SAMPLE strided (ordered key of x, index) pairs of this shard
+ *      -> all-gather the samples
+ *   S2 vb_psis_pivot    sort them (capacity: power of two >= 4096, >= count); pivot_x = the value
+ *                       with ceil(frac * count) sampled values above it (-inf when frac >= 1)
+ *   S3 vb_psis_filter   ONE pass over the shard: x >= pivot_x -> candidate (raw bits of x, index),
+ *                       otherwise body += exp(x - pivot_x); d_out_body_max = [body, max candidate]
+ *      -> read d_out_count (host), all-reduce(max) the local maxima
+ *   S4 vb_psis_prepare  keys := ~bits(M - x) (the reference sorts the shifted weights,
+ *                       psis.py:165-167); d_out_term0 = body * exp(pivot_x - M)
+ *   S4b vb_psis_refine  keep about `keep` largest local candidates; the rest add exp(-(M - x)) to
+ *                       d_out_term   -> all-gather candidates and the per-rank [term0, term]
+ *   S5 vb_psis_tail     replicated: sort, exact cutoff (psis.py:157,169-176), GPD fit, smoothing,
+ *                       log-sum-exp; fills d_out_diag like vb_psis_smooth
+ *   S6 vb_psis_write    out = (x - M) - lse over the shard + the smoothed tail entries it owns
+ */
+#define VB_PSIS_SAMPLE 4096
+int vb_psis_sample(const double* d_lw, long long n_local, long long index0, void* d_out_sample,
+                   void* stream);
+int vb_psis_pivot(void* d_sample, long long count, long long capacity, double frac,
+                  double* d_out_pivot_x, void* stream);
+size_t vb_psis_filter_workspace_bytes(long long n_local);
+int vb_psis_filter(const double* d_lw, long long n_local, long long index0,
+                   const double* d_pivot_x, void* d_out_cand, long long cap,
+                   unsigned long long* d_out_count, double* d_out_body_max,
+                   void* d_ws, size_t ws_bytes, void* stream);
+int vb_psis_prepare(void* d_cand, long long count, const double* d_M, const double* d_pivot_x,
+                    const double* d_body_pre, double* d_out_term0, void* stream);
+size_t vb_psis_refine_workspace_bytes(void);
+int vb_psis_refine(const void* d_cand, long long count, const double* d_M,
+                   const double* d_pivot_x, long long keep, void* d_out_cand,
+                   unsigned long long* d_out_count, double* d_out_term,
+                   void* d_ws, size_t ws_bytes, void* stream);
+size_t vb_psis_tail_workspace_bytes(long long count, long long K1);
+int vb_psis_tail(const void* d_cands, long long count, long long K1, const double* d_M,
+                 const double* d_pivot_x, const double* d_terms, int n_terms,
+                 double* d_out_diag, long long* d_out_tail_idx_or_null,
+                 void* d_ws, size_t ws_bytes, void* stream);
+int vb_psis_write(const double* d_lw, double* d_out, long long n_local, long long index0,
+                  const double* d_M, long long count, long long K1, const void* d_tail_ws,
+                  void* stream);
+
 size_t vb_gpd_fit_workspace_bytes(long long n);
 int vb_gpd_fit(const double* d_x_sorted, long long n, double* d_out_k_sigma,
                void* d_ws, size_t ws_bytes, void* stream);

@@ -62,6 +62,16 @@ SIGNATURES = {
     'vb_psis_tail_capacity': (_ll, [_ll, _d]),
     'vb_psis_smooth_workspace_bytes': (_sz, [_ll, _d]),
     'vb_psis_smooth': (_i, [_p, _p, _ll, _d, _p, _p, _p, _sz, _p]),
+    'vb_psis_sample': (_i, [_p, _ll, _ll, _p, _p]),
+    'vb_psis_pivot': (_i, [_p, _ll, _ll, _d, _p, _p]),
+    'vb_psis_filter_workspace_bytes': (_sz, [_ll]),
+    'vb_psis_filter': (_i, [_p, _ll, _ll, _p, _p, _ll, _p, _p, _p, _sz, _p]),
+    'vb_psis_prepare': (_i, [_p, _ll, _p, _p, _p, _p, _p]),
+    'vb_psis_refine_workspace_bytes': (_sz, []),
+    'vb_psis_refine': (_i, [_p, _ll, _p, _p, _ll, _p, _p, _p, _p, _sz, _p]),
+    'vb_psis_tail_workspace_bytes': (_sz, [_ll, _ll]),
+    'vb_psis_tail': (_i, [_p, _ll, _ll, _p, _p, _p, _i, _p, _p, _p, _sz, _p]),
+    'vb_psis_write': (_i, [_p, _p, _ll, _ll, _p, _ll, _ll, _p, _p]),
     'vb_gpd_fit_workspace_bytes': (_sz, [_ll]),
     'vb_gpd_fit': (_i, [_p, _ll, _p, _p, _sz, _p]),
     'vb_gpd_inv': (_i, [_p, _ll, _d, _d, _p, _p]),

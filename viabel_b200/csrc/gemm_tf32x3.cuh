@@ -88,7 +88,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         for (long long w = blockIdx.x; w < total; w += gridDim.x) {
             const long long tile = w % (m_tiles * n_tiles);
             const int split = (int)(w / (m_tiles * n_tiles));
-            const int m0 = (int)(tile % m_tiles) * kTBM, n0 = (int)(tile / m_tiles) * kTBN;
+            const int n0 = (int)(tile % n_tiles) * kTBN, m0 = (int)(tile / n_tiles) * kTBM;   // n fastest: CTAs that run together share the A tile in L2
             const long long kt0 = (long long)split * shape.k_tiles_per_split;
             long long kt1 = kt0 + shape.k_tiles_per_split;
             if (kt1 > k_tiles_total) kt1 = k_tiles_total;
@@ -166,7 +166,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         for (long long w = blockIdx.x; w < total; w += gridDim.x, ++it) {
             const long long tile = w % (m_tiles * n_tiles);
             const int split = (int)(w / (m_tiles * n_tiles));
-            const long long m0 = (tile % m_tiles) * kTBM, n0 = (tile / m_tiles) * kTBN;
+            const long long n0 = (tile % n_tiles) * kTBN, m0 = (tile / n_tiles) * kTBM;
             const int as = it & 1;
             mbar_wait(&tmem_full[as], (uint32_t)((it >> 1) & 1));
             tc::fence_after_sync();

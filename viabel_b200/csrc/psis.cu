@@ -141,97 +141,152 @@ static int bitonic_sort(Cand* data, long long n_pad, cudaStream_t st) {
 }
 
 // ------------------------------------------------------------------------------------------ pivot from a strided sample
-// sample[i] = (u of element floor(i * n / S)); sorted ascending by key (descending u).
-__global__ void sample_kernel(const double* __restrict__ lw, long long n, const double* __restrict__ M_ptr,
-                              Cand* __restrict__ sample) {
-    const double M = *M_ptr;
+// The pivot lives in x-space (raw log weights), so neither the sample nor the filter pass needs the
+// maximum: sample[i] = (ordered key of x[floor(i n / S)], index); sorted ascending.
+__global__ void sample_kernel(const double* __restrict__ lw, long long n, long long index0, Cand* __restrict__ sample) {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < kSampleSize; i += gridDim.x * blockDim.x) {
         const long long e = ((long long)i * n) / kSampleSize;   // i < 2^12, n < 2^50
         Cand c;
-        c.key = u_to_key(M - lw[e]);
-        c.idx = (unsigned long long)e;
+        c.key = f64_to_key(lw[e]);
+        c.idx = (unsigned long long)(index0 + e);
         sample[i] = c;
     }
 }
-// pivot = the `rank`-th smallest u of the sample (0-based), or +inf when rank >= sample size
-__global__ void pivot_kernel(const Cand* __restrict__ sorted_sample, int rank, double* __restrict__ out_pivot) {
+// pivot_x = the (rank+1)-th largest sampled value, or -inf when rank >= count (everything is a candidate)
+__global__ void pivot_kernel(const Cand* __restrict__ sorted_sample, long long count, long long rank,
+                             double* __restrict__ out_pivot_x) {
     if (threadIdx.x == 0 && blockIdx.x == 0)
-        *out_pivot = (rank >= kSampleSize) ? INFINITY : key_to_u(sorted_sample[kSampleSize - 1 - rank].key);
+        *out_pivot_x = (rank >= count) ? -INFINITY : key_to_f64(sorted_sample[count - 1 - rank].key);
 }
 __global__ void set_double_kernel(double* p, double v) { if (threadIdx.x == 0 && blockIdx.x == 0) *p = v; }
 __global__ void set_counts_kernel(long long* p, long long a, long long b, long long c, long long d) {
     if (threadIdx.x == 0 && blockIdx.x == 0) { p[0] = a; p[1] = b; p[2] = c; p[3] = d; }
 }
 
-// ------------------------------------------------------------------------------------------ P2: prefilter
-struct PrefilterOut {
+// ------------------------------------------------------------------------------------------ P1: fused filter pass
+// ONE read of the weights: elements with x >= pivot_x are appended as (raw bits of x, global index)
+// candidates, every other element adds exp(x - pivot_x) to the body sum (terms <= 1: no running
+// max needed), and the maximum is taken over the candidates only (it is one of them).
+// Candidates are staged per WARP in shared memory (no block barrier in the loop) and flushed with
+// one global atomic per flush: a per-warp atomic per round on a single counter serialises in L2
+// (measured 1.16 ms at n = 1.25e8).
+struct FilterOut {
     Cand* cand;
     long long cap;
     unsigned long long* counter;     // number of candidates found (may exceed cap)
-    double* block_body;              // [grid] sum of exp(-u) over non-candidates
+    double* block_body;              // [grid]
+    double* block_max;               // [grid]
 };
 
-constexpr int kPreThreads = 256;
-constexpr int kPreUnroll = 4;                       // elements per thread per round
-constexpr int kPreBuf = 2048;                       // candidates staged per CTA (32 KiB)
+constexpr int kFThreads = 256;
+constexpr int kFWarps = kFThreads / 32;
+constexpr int kFPerThread = 8;                          // 4 x 16-byte loads in flight
+constexpr int kFChunk = kFThreads * kFPerThread;        // elements per CTA per round
+constexpr int kFWarpBuf = 512;                          // staged candidates per warp (8 KiB)
+constexpr size_t kFSmem = (size_t)kFWarps * kFWarpBuf * sizeof(Cand);
 
-// Candidates are staged in shared memory and flushed with ONE global atomic per flush (a
-// per-warp atomic on a single global counter serialises in L2: measured 1.16 ms at n = 1.25e8).
-__global__ void __launch_bounds__(kPreThreads)
-prefilter_kernel(const double* __restrict__ lw, long long n, long long index0, const double* __restrict__ M_ptr,
-                 const double* __restrict__ pivot_ptr, PrefilterOut o) {
-    __shared__ Cand buf[kPreBuf];
-    __shared__ unsigned int s_count;
-    __shared__ unsigned long long s_base;
+__device__ __forceinline__ void filter_flush(Cand* mybuf, unsigned int* wcount, unsigned int cnt, int lane,
+                                             const FilterOut& o) {
+    unsigned long long gbase = 0;
+    if (lane == 0) gbase = atomicAdd(o.counter, (unsigned long long)cnt);
+    gbase = __shfl_sync(0xffffffffu, gbase, 0);
+    for (unsigned int k = lane; k < cnt; k += 32)
+        if ((long long)(gbase + k) < o.cap) o.cand[gbase + k] = mybuf[k];
+    __syncwarp();
+    if (lane == 0) *wcount = 0;
+    __syncwarp();
+}
+
+template <bool ALIGNED>
+__global__ void __launch_bounds__(kFThreads)
+filter_kernel(const double* __restrict__ lw, long long n, long long index0, const double* __restrict__ pivot_ptr,
+              FilterOut o) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ unsigned int wcounts[kFWarps];
     __shared__ double scratch[32];
-    const int tid = threadIdx.x;
-    const double M = *M_ptr, pivot = *pivot_ptr;
-    double body = 0.0;
-    if (tid == 0) s_count = 0;
-    __syncthreads();
-    constexpr long long kChunk = (long long)kPreThreads * kPreUnroll;
-    const long long per_round = (long long)gridDim.x * kChunk;
-    const long long rounds = (n + per_round - 1) / per_round;
-    for (long long rd = 0; rd <= rounds; ++rd) {
-        if (rd < rounds) {
-            const long long i0 = rd * per_round + (long long)blockIdx.x * kChunk + tid;
-            double x[kPreUnroll];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    Cand* mybuf = reinterpret_cast<Cand*>(smem_raw) + warp * kFWarpBuf;
+    unsigned int* wcount = &wcounts[warp];
+    if (lane == 0) *wcount = 0;
+    __syncwarp();
+    const double pivot = *pivot_ptr;
+    double body = 0.0, cmax = -INFINITY;
+    const long long n_chunks = (n + kFChunk - 1) / kFChunk;
+    const long long full_chunks = n / kFChunk;
+
+    auto take = [&](double x, long long i) {
+        if (x >= pivot) {
+            const unsigned int pos = atomicAdd(wcount, 1u);
+            Cand c;
+            c.key = (unsigned long long)__double_as_longlong(x);
+            c.idx = (unsigned long long)(index0 + i);
+            mybuf[pos] = c;
+            cmax = fmax(cmax, x);
+        } else {
+            body += exp_nonpos(x - pivot);          // NaN lands here and poisons the sum, like np.exp would
+        }
+    };
+
+    for (long long chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
+        const long long base = chunk * kFChunk;
+        if (ALIGNED && chunk < full_chunks) {
+            const double2* p = reinterpret_cast<const double2*>(lw + base) + tid;
+            double2 v[kFPerThread / 2];
 #pragma unroll
-            for (int q = 0; q < kPreUnroll; ++q) {
-                const long long i = i0 + (long long)q * kPreThreads;
-                x[q] = (i < n) ? ld_stream(lw + i) : NAN;           // NaN: neither candidate nor body
+            for (int q = 0; q < kFPerThread / 2; ++q) v[q] = ld_stream2(p + q * kFThreads);
+#pragma unroll
+            for (int q = 0; q < kFPerThread / 2; ++q) {
+                const long long i = base + 2 * (tid + q * kFThreads);
+                take(v[q].x, i);
+                take(v[q].y, i + 1);
             }
+        } else {
 #pragma unroll
-            for (int q = 0; q < kPreUnroll; ++q) {
-                const long long i = i0 + (long long)q * kPreThreads;
-                const double u = M - x[q];
-                if (u <= pivot) {
-                    const unsigned int pos = atomicAdd(&s_count, 1u);
-                    Cand c;
-                    c.key = u_to_key(u);
-                    c.idx = (unsigned long long)(index0 + i);
-                    buf[pos] = c;
-                } else if (i < n) {
-                    body += exp_nonpos(-u);
-                }
+            for (int q = 0; q < kFPerThread; ++q) {
+                const long long i = base + tid + q * kFThreads;
+                if (i < n) take(lw[i], i);
             }
         }
-        __syncthreads();
-        const unsigned int cnt = s_count;
-        // flush when another round could overflow the staging buffer, and once at the end
-        if (cnt > (unsigned)(kPreBuf - kChunk) || (rd == rounds && cnt > 0)) {
-            if (tid == 0) s_base = atomicAdd(o.counter, (unsigned long long)cnt);
-            __syncthreads();
-            const unsigned long long gbase = s_base;
-            for (unsigned int k = tid; k < cnt; k += kPreThreads)
-                if ((long long)(gbase + k) < o.cap) o.cand[gbase + k] = buf[k];
-            __syncthreads();
-            if (tid == 0) s_count = 0;
-        }
-        __syncthreads();
+        __syncwarp();
+        const unsigned int cnt = *reinterpret_cast<volatile unsigned int*>(wcount);
+        __syncwarp();
+        if (cnt > (unsigned)(kFWarpBuf - 32 * kFPerThread)) filter_flush(mybuf, wcount, cnt, lane, o);
     }
+    __syncwarp();
+    const unsigned int cnt = *reinterpret_cast<volatile unsigned int*>(wcount);
+    __syncwarp();
+    if (cnt > 0) filter_flush(mybuf, wcount, cnt, lane, o);
     body = block_sum(body, scratch);
-    if (tid == 0) o.block_body[blockIdx.x] = body;
+    cmax = block_max(cmax, scratch);
+    if (tid == 0) { o.block_body[blockIdx.x] = body; o.block_max[blockIdx.x] = cmax; }
+}
+// out_body = sum of the block bodies (fixed order), out_max = max of the block maxima
+__global__ void __launch_bounds__(256)
+filter_finish_kernel(const double* __restrict__ block_body, const double* __restrict__ block_max_in, int G,
+                     double* __restrict__ out_body, double* __restrict__ out_max) {
+    __shared__ double scratch[32];
+    double s = 0.0, m = -INFINITY;
+    for (int g = threadIdx.x; g < G; g += blockDim.x) { s += block_body[g]; m = fmax(m, block_max_in[g]); }
+    s = block_sum(s, scratch);
+    m = block_max(m, scratch);
+    if (threadIdx.x == 0) { *out_body = s; *out_max = m; }
+}
+// Once the (global) maximum M is known: candidate keys become ~bits(M - x) (the reference sorts the
+// SHIFTED weights, psis.py:165-167), pivot_u = M - pivot_x, and the body sum is rescaled to M.
+__global__ void rekey_kernel(Cand* __restrict__ cand, long long count, const double* __restrict__ M_ptr) {
+    const double M = *M_ptr;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count;
+         i += (long long)gridDim.x * blockDim.x)
+        cand[i].key = u_to_key(M - __longlong_as_double((long long)cand[i].key));
+}
+// terms[0] = body_pre * exp(pivot_x - M); pivot_u = M - pivot_x
+__global__ void derive_kernel(const double* __restrict__ M_ptr, const double* __restrict__ pivotx_ptr,
+                              const double* __restrict__ body_pre, double* __restrict__ pivot_u,
+                              double* __restrict__ term0) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const double M = *M_ptr, px = *pivotx_ptr, b = *body_pre;
+    if (pivot_u) *pivot_u = M - px;                       // +inf when everything was a candidate
+    *term0 = (b == 0.0) ? 0.0 : b * exp(px - M);
 }
 
 // ------------------------------------------------------------------------------------------ refinement histogram
@@ -577,48 +632,6 @@ static long long psis_K1(long long n, double reff) {
     return (long long)ceil(fmin(0.2 * (double)n, 3.0 * sqrt((double)n / reff)));     // psis.py:157
 }
 
-struct PsisLayout {
-    long long cap1, cap2;
-    int g_pre, g_small;
-    size_t off_M, off_pivot, off_counters, off_state, off_counts, off_hist, off_sample, off_cand1, off_cand2,
-        off_x2, off_tailnew, off_bs, off_L, off_w, off_blk_pre, off_blk2, off_blk3, off_blk4, off_blk5, total;
-};
-static PsisLayout psis_layout(long long n, double reff) {
-    PsisLayout L;
-    const long long K1 = psis_K1(n, reff);
-    // candidate buffers: the whole array for small n, otherwise max(2 Mi, n/16) pairs
-    L.cap1 = (n <= kDirectSortMax) ? n : ((n / 16 > (1ll << 21)) ? n / 16 : (1ll << 21));
-    if (L.cap1 > n) L.cap1 = n;
-    if (L.cap1 < K1 + 1) L.cap1 = K1 + 1;
-    L.cap2 = pad_pow2(L.cap1);
-    L.g_pre = grid_for((n + 3) / 4, 256, kNumSMs * 6);
-    L.g_small = kNumSMs * 2;
-    size_t o = 0;
-    auto take = [&](size_t bytes) { size_t at = o; o += align_up(bytes, 256); return at; };
-    L.off_M = take(8);
-    L.off_pivot = take(8);
-    L.off_counters = take(4 * 8);
-    L.off_state = take(8 * 8);
-    L.off_counts = take(4 * 8);
-    L.off_hist = take((size_t)kHistBins * 4);
-    L.off_sample = take((size_t)kSampleSize * sizeof(Cand));
-    L.off_cand1 = take((size_t)L.cap1 * sizeof(Cand));
-    L.off_cand2 = take((size_t)L.cap2 * sizeof(Cand));
-    L.off_x2 = take((size_t)(K1 + 1) * 8);
-    L.off_tailnew = take((size_t)(K1 + 1) * 8);
-    const long long m_max = 30 + (long long)sqrt((double)(K1 + 1)) + 1;
-    L.off_bs = take((size_t)m_max * 8);
-    L.off_L = take((size_t)m_max * 8);
-    L.off_w = take((size_t)m_max * 8);
-    L.off_blk_pre = take((size_t)L.g_pre * 8);
-    L.off_blk2 = take((size_t)L.g_small * 8);
-    L.off_blk3 = take((size_t)L.g_small * 8);
-    L.off_blk4 = take((size_t)L.g_small * 8);
-    L.off_blk5 = take((size_t)L.g_small * 8);
-    L.total = o;
-    return L;
-}
-
 // GPD fit on an ascending device array; n2 and m are read from counts[] on the device.
 static int run_gpd_fit(const double* x2, const long long* counts, long long n2_upper, double* bs, double* Lq,
                        double* wq, double* blk, int g_small, double* state, cudaStream_t st) {
@@ -634,8 +647,23 @@ static int run_gpd_fit(const double* x2, const long long* counts, long long n2_u
     return VB_OK;
 }
 
-extern "C" int vb_max(const double* d_x, long long n, double* d_out, void* d_ws, size_t ws_bytes, void* stream);
-extern "C" size_t vb_max_workspace_bytes(long long n);
+constexpr int kSmallGrid = kNumSMs * 2;
+static int filter_grid(long long n) { return grid_for((n + kFPerThread - 1) / kFPerThread, kFThreads, kNumSMs * 3); }
+
+__global__ void sum_blocks_kernel(const double* __restrict__ blocks, int G, double* __restrict__ out) {
+    __shared__ double scratch[32];
+    double s = 0.0;
+    for (int g = threadIdx.x; g < G; g += blockDim.x) s += blocks[g];
+    s = block_sum(s, scratch);
+    if (threadIdx.x == 0) *out = s;
+}
+__global__ void set_u64_kernel(unsigned long long* p, unsigned long long v) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) *p = v;
+}
+__global__ void pad_low_kernel(Cand* __restrict__ data, long long count, long long cap) {
+    for (long long i = count + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < cap;
+         i += (long long)gridDim.x * blockDim.x) { data[i].key = 0ull; data[i].idx = 0ull; }
+}
 
 }  // namespace vb
 
@@ -646,9 +674,287 @@ extern "C" long long vb_psis_tail_capacity(long long n, double reff) {
     return psis_K1(n, reff);
 }
 
+// ---- S1: strided sample of the raw weights (VB_PSIS_SAMPLE entries of 16 bytes)
+extern "C" int vb_psis_sample(const double* d_lw, long long n_local, long long index0, void* d_out_sample, void* stream) {
+    if (!d_lw || !d_out_sample || n_local < 1) return VB_ERR_ARG;
+    sample_kernel<<<16, 256, 0, (cudaStream_t)stream>>>(d_lw, n_local, index0, (Cand*)d_out_sample);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+
+// ---- S2: sort the (gathered) sample and pick pivot_x with ceil(frac * count) sampled values above it
+extern "C" int vb_psis_pivot(void* d_sample, long long count, long long capacity, double frac,
+                             double* d_out_pivot_x, void* stream) {
+    if (!d_sample || !d_out_pivot_x || count < 1 || capacity < count || capacity < kSortChunk ||
+        (capacity & (capacity - 1)))
+        return VB_ERR_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (capacity > count) {
+        pad_low_kernel<<<grid_for(capacity - count, 256, kNumSMs), 256, 0, st>>>((Cand*)d_sample, count, capacity);
+        VB_LAUNCH_CHECK();
+    }
+    int rc = bitonic_sort((Cand*)d_sample, capacity, st);
+    if (rc != VB_OK) return rc;
+    long long rank = (long long)ceil(frac * (double)count);
+    // pads (key 0) sort first, so ranks counted from the top are unaffected
+    pivot_kernel<<<1, 1, 0, st>>>((const Cand*)d_sample, capacity, rank >= count ? capacity : rank, d_out_pivot_x);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+
+// ---- S3: the fused filter pass
+extern "C" size_t vb_psis_filter_workspace_bytes(long long n_local) {
+    if (n_local < 1) return 0;
+    return 2 * align_up((size_t)filter_grid(n_local) * 8, 256) + 256;
+}
+extern "C" int vb_psis_filter(const double* d_lw, long long n_local, long long index0, const double* d_pivot_x,
+                              void* d_out_cand, long long cap, unsigned long long* d_out_count,
+                              double* d_out_body_max, void* d_ws, size_t ws_bytes, void* stream) {
+    if (!d_lw || !d_pivot_x || !d_out_cand || !d_out_count || !d_out_body_max || !d_ws || n_local < 1 || cap < 1)
+        return VB_ERR_ARG;
+    if (ws_bytes < vb_psis_filter_workspace_bytes(n_local)) return VB_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    static bool attr = false;
+    if (!attr) {
+        VB_CUDA_TRY(cudaFuncSetAttribute(filter_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFSmem));
+        VB_CUDA_TRY(cudaFuncSetAttribute(filter_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFSmem));
+        attr = true;
+    }
+    const int G = filter_grid(n_local);
+    double* blk_body = (double*)d_ws;
+    double* blk_max = (double*)((char*)d_ws + align_up((size_t)G * 8, 256));
+    VB_CUDA_TRY(cudaMemsetAsync(d_out_count, 0, 8, st));
+    FilterOut fo{(Cand*)d_out_cand, cap, d_out_count, blk_body, blk_max};
+    if ((reinterpret_cast<uintptr_t>(d_lw) & 15u) == 0)
+        filter_kernel<true><<<G, kFThreads, kFSmem, st>>>(d_lw, n_local, index0, d_pivot_x, fo);
+    else
+        filter_kernel<false><<<G, kFThreads, kFSmem, st>>>(d_lw, n_local, index0, d_pivot_x, fo);
+    VB_LAUNCH_CHECK();
+    filter_finish_kernel<<<1, 256, 0, st>>>(blk_body, blk_max, G, d_out_body_max, d_out_body_max + 1);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+
+// ---- S4: keys relative to the (global) maximum; term0 = body sum rescaled to it
+extern "C" int vb_psis_prepare(void* d_cand, long long count, const double* d_M, const double* d_pivot_x,
+                               const double* d_body_pre, double* d_out_term0, void* stream) {
+    if (!d_cand || !d_M || !d_pivot_x || !d_body_pre || !d_out_term0 || count < 0) return VB_ERR_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (count > 0) {
+        rekey_kernel<<<grid_for(count, 256, kNumSMs * 4), 256, 0, st>>>((Cand*)d_cand, count, d_M);
+        VB_LAUNCH_CHECK();
+    }
+    derive_kernel<<<1, 1, 0, st>>>(d_M, d_pivot_x, d_body_pre, nullptr, d_out_term0);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+
+namespace vb {
+struct RefineWs { unsigned int* hist; long long* counts2; double* pivot_u; double* blk; };
+static size_t refine_ws_bytes() { return (size_t)kHistBins * 4 + 256 + 256 + align_up((size_t)kSmallGrid * 8, 256); }
+static RefineWs refine_ws(char* ws) {
+    RefineWs r;
+    r.hist = (unsigned int*)ws;
+    r.counts2 = (long long*)(ws + (size_t)kHistBins * 4);
+    r.pivot_u = (double*)(ws + (size_t)kHistBins * 4 + 256);
+    r.blk = (double*)(ws + (size_t)kHistBins * 4 + 512);
+    return r;
+}
+__global__ void pivot_u_kernel(const double* M, const double* px, double* out) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) *out = *M - *px;
+}
+// keep the ~`keep` largest of `count` re-keyed candidates (histogram of u); the dropped ones add exp(-u) to *out_term
+static int refine_to(const Cand* in, long long count, const double* d_M, const double* d_pivot_x, long long keep,
+                     Cand* out, unsigned long long* d_out_count, double* d_out_term, char* ws, cudaStream_t st) {
+    const RefineWs r = refine_ws(ws);
+    pivot_u_kernel<<<1, 1, 0, st>>>(d_M, d_pivot_x, r.pivot_u);
+    VB_LAUNCH_CHECK();
+    VB_CUDA_TRY(cudaMemsetAsync(r.hist, 0, (size_t)kHistBins * 4, st));
+    VB_CUDA_TRY(cudaMemsetAsync(d_out_count, 0, 8, st));
+    hist_kernel<<<grid_for(count, 256, kNumSMs * 4), 256, 0, st>>>(in, count, r.pivot_u, r.hist);
+    VB_LAUNCH_CHECK();
+    hist_scan_kernel<<<1, 1024, 0, st>>>(r.hist, keep, r.counts2);
+    VB_LAUNCH_CHECK();
+    compact2_kernel<<<kSmallGrid, 256, 0, st>>>(in, count, r.pivot_u, r.counts2, out, d_out_count, r.blk);
+    VB_LAUNCH_CHECK();
+    sum_blocks_kernel<<<1, 256, 0, st>>>(r.blk, kSmallGrid, d_out_term);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+}  // namespace vb
+
+// ---- S4b (sharded callers): shrink the local candidates to about `keep` before the exchange
+extern "C" size_t vb_psis_refine_workspace_bytes(void) { return refine_ws_bytes() + 256; }
+extern "C" int vb_psis_refine(const void* d_cand, long long count, const double* d_M, const double* d_pivot_x,
+                              long long keep, void* d_out_cand, unsigned long long* d_out_count,
+                              double* d_out_term, void* d_ws, size_t ws_bytes, void* stream) {
+    if (!d_cand || !d_M || !d_pivot_x || !d_out_cand || !d_out_count || !d_out_term || !d_ws || count < 0 || keep < 1)
+        return VB_ERR_ARG;
+    if (ws_bytes < vb_psis_refine_workspace_bytes()) return VB_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (count > 2 * keep && count > 8192)
+        return refine_to((const Cand*)d_cand, count, d_M, d_pivot_x, keep, (Cand*)d_out_cand, d_out_count, d_out_term,
+                         (char*)d_ws, st);
+    if (count > 0)
+        VB_CUDA_TRY(cudaMemcpyAsync(d_out_cand, d_cand, (size_t)count * sizeof(Cand), cudaMemcpyDeviceToDevice, st));
+    set_u64_kernel<<<1, 1, 0, st>>>(d_out_count, (unsigned long long)count);
+    VB_LAUNCH_CHECK();
+    set_double_kernel<<<1, 1, 0, st>>>(d_out_term, 0.0);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+
+// ---- S5: replicated tail work on the (gathered) re-keyed candidates
+namespace vb {
+struct TailLayout {
+    long long cap_sort;
+    size_t off_state, off_counts, off_cnt2, off_term, off_refine, off_sort, off_x2, off_tailnew, off_bs, off_L, off_w,
+        off_blk3, off_blk4, off_blk5, total;
+};
+static TailLayout tail_layout(long long count, long long K1) {
+    TailLayout L;
+    L.cap_sort = pad_pow2(count);
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t at = o; o += align_up(bytes, 256); return at; };
+    L.off_state = take(8 * 8);
+    L.off_counts = take(4 * 8);
+    L.off_cnt2 = take(8);
+    L.off_term = take(8);
+    L.off_refine = take(refine_ws_bytes());
+    L.off_sort = take((size_t)L.cap_sort * sizeof(Cand));
+    L.off_x2 = take((size_t)(K1 + 1) * 8);
+    L.off_tailnew = take((size_t)(K1 + 1) * 8);
+    const long long m_max = 30 + (long long)sqrt((double)(K1 + 1)) + 1;
+    L.off_bs = take((size_t)m_max * 8);
+    L.off_L = take((size_t)m_max * 8);
+    L.off_w = take((size_t)m_max * 8);
+    L.off_blk3 = take((size_t)kSmallGrid * 8);
+    L.off_blk4 = take((size_t)kSmallGrid * 8);
+    L.off_blk5 = take((size_t)kSmallGrid * 8);
+    L.total = o;
+    return L;
+}
+}  // namespace vb
+
+extern "C" size_t vb_psis_tail_workspace_bytes(long long count, long long K1) {
+    if (count < 1 || K1 < 0) return 0;
+    return tail_layout(count, K1).total + 256;
+}
+
+extern "C" int vb_psis_tail(const void* d_cands, long long count, long long K1, const double* d_M,
+                            const double* d_pivot_x, const double* d_terms, int n_terms,
+                            double* d_out_diag, long long* d_out_tail_idx_or_null,
+                            void* d_ws, size_t ws_bytes, void* stream) {
+    if (!d_cands || !d_M || !d_pivot_x || !d_terms || !d_out_diag || !d_ws || n_terms < 1 || K1 < 0) return VB_ERR_ARG;
+    if (count < K1 + 1) return VB_ERR_ARG;
+    if (ws_bytes < vb_psis_tail_workspace_bytes(count, K1)) return VB_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    const TailLayout L = tail_layout(count, K1);
+    char* ws = (char*)(((uintptr_t)d_ws + 255) & ~(uintptr_t)255);
+    double* state = (double*)(ws + L.off_state);
+    long long* counts = (long long*)(ws + L.off_counts);
+    unsigned long long* cnt2 = (unsigned long long*)(ws + L.off_cnt2);
+    double* term_ref = (double*)(ws + L.off_term);
+    Cand* sort_buf = (Cand*)(ws + L.off_sort);
+    double* x2 = (double*)(ws + L.off_x2);
+    double* tail_new = (double*)(ws + L.off_tailnew);
+    double* bs = (double*)(ws + L.off_bs);
+    double* Lq = (double*)(ws + L.off_L);
+    double* wq = (double*)(ws + L.off_w);
+    double* blk3 = (double*)(ws + L.off_blk3);
+    double* blk4 = (double*)(ws + L.off_blk4);
+    double* blk5 = (double*)(ws + L.off_blk5);
+
+    long long C2 = count;
+    if (count > kDirectSortMax) {
+        int rc = refine_to((const Cand*)d_cands, count, d_M, d_pivot_x, K1 + 1, sort_buf, cnt2, term_ref,
+                           ws + L.off_refine, st);
+        if (rc != VB_OK) return rc;
+        unsigned long long h = 0;
+        VB_CUDA_TRY(cudaMemcpyAsync(&h, cnt2, 8, cudaMemcpyDeviceToHost, st));
+        VB_CUDA_TRY(cudaStreamSynchronize(st));
+        C2 = (long long)h;
+        if (C2 < K1 + 1 || C2 > count) return VB_ERR_UNSUPPORTED;
+    } else {
+        VB_CUDA_TRY(cudaMemcpyAsync(sort_buf, d_cands, (size_t)count * sizeof(Cand), cudaMemcpyDeviceToDevice, st));
+        set_double_kernel<<<1, 1, 0, st>>>(term_ref, 0.0);
+        VB_LAUNCH_CHECK();
+    }
+    const long long n_pad = pad_pow2(C2);
+    pad_cands_kernel<<<grid_for(n_pad - C2 + 1, 256, kNumSMs * 4), 256, 0, st>>>(sort_buf, C2, n_pad);
+    VB_LAUNCH_CHECK();
+    int rc = bitonic_sort(sort_buf, n_pad, st);
+    if (rc != VB_OK) return rc;
+
+    tail_bounds_kernel<<<1, 1, 0, st>>>(sort_buf, C2, K1, state, counts);
+    VB_LAUNCH_CHECK();
+    tail_excess_kernel<<<kSmallGrid, 256, 0, st>>>(sort_buf, state, counts, x2);
+    VB_LAUNCH_CHECK();
+    rc = run_gpd_fit(x2, counts, K1 + 1, bs, Lq, wq, blk3, kSmallGrid, state, st);
+    if (rc != VB_OK) return rc;
+    tail_smooth_kernel<<<kSmallGrid, 256, 0, st>>>(sort_buf, state, counts, tail_new, d_out_tail_idx_or_null, blk4);
+    VB_LAUNCH_CHECK();
+    cand_body_kernel<<<kSmallGrid, 256, 0, st>>>(sort_buf, counts, 0, 0x7fffffffffffffffll, blk5);
+    VB_LAUNCH_CHECK();
+    SumList lists;
+    lists.p[0] = d_terms;  lists.n[0] = n_terms;          // per-rank body sums, rank order
+    lists.p[1] = term_ref; lists.n[1] = 1;                // dropped by the refinement above
+    lists.p[2] = blk5;     lists.n[2] = kSmallGrid;       // sorted candidates below the cutoff
+    lists.p[3] = blk4;     lists.n[3] = kSmallGrid;       // the (smoothed) tail
+    psis_finish_kernel<<<1, 256, 0, st>>>(lists, d_M, counts, C2, state, d_out_diag, nullptr);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+
+// ---- S6: out = (x - M) - lse over this shard, then the smoothed tail entries it owns
+extern "C" int vb_psis_write(const double* d_lw, double* d_out, long long n_local, long long index0,
+                             const double* d_M, long long count, long long K1, const void* d_tail_ws, void* stream) {
+    if (!d_lw || !d_out || !d_M || !d_tail_ws || n_local < 1 || d_lw == d_out) return VB_ERR_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    const TailLayout L = tail_layout(count, K1);
+    const char* ws = (const char*)(((uintptr_t)d_tail_ws + 255) & ~(uintptr_t)255);
+    const double* state = (const double*)(ws + L.off_state);
+    const long long* counts = (const long long*)(ws + L.off_counts);
+    const Cand* sort_buf = (const Cand*)(ws + L.off_sort);
+    const double* tail_new = (const double*)(ws + L.off_tailnew);
+    normalise_kernel<<<grid_for((n_local + 1) / 2, 256, kNumSMs * 8), 256, 0, st>>>(d_lw, d_out, n_local, d_M, state + 5);
+    VB_LAUNCH_CHECK();
+    tail_scatter_kernel<<<kSmallGrid, 256, 0, st>>>(sort_buf, counts, tail_new, state, d_out, index0, n_local);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+
+// ---- single-GPU composite: psislw for one column
+namespace vb {
+struct SmoothLayout {
+    long long cap1;
+    size_t off_sample, off_pivot, off_count, off_bodymax, off_terms, off_filter, off_cand1, off_tail, total;
+};
+static SmoothLayout smooth_layout(long long n, double reff) {
+    SmoothLayout L;
+    const long long K1 = psis_K1(n, reff);
+    // candidate buffer: the whole array for small n, otherwise max(2 Mi, n/16) pairs
+    L.cap1 = (n <= kDirectSortMax) ? n : ((n / 16 > (1ll << 21)) ? n / 16 : (1ll << 21));
+    if (L.cap1 > n) L.cap1 = n;
+    if (L.cap1 < K1 + 1) L.cap1 = K1 + 1;
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t at = o; o += align_up(bytes, 256); return at; };
+    L.off_sample = take((size_t)kSampleSize * sizeof(Cand));
+    L.off_pivot = take(8);
+    L.off_count = take(8);
+    L.off_bodymax = take(16);
+    L.off_terms = take(16);
+    L.off_filter = take(vb_psis_filter_workspace_bytes(n));
+    L.off_cand1 = take((size_t)L.cap1 * sizeof(Cand));
+    L.off_tail = take(vb_psis_tail_workspace_bytes(L.cap1, K1));
+    L.total = o;
+    return L;
+}
+}  // namespace vb
+
 extern "C" size_t vb_psis_smooth_workspace_bytes(long long n, double reff) {
     if (n < 2 || !(reff > 0.0)) return 0;
-    return psis_layout(n, reff).total + vb_max_workspace_bytes(n) + 256;
+    return smooth_layout(n, reff).total + 256;
 }
 
 extern "C" int vb_psis_smooth(const double* d_lw_in, double* d_lw_out, long long n, double reff,
@@ -657,129 +963,63 @@ extern "C" int vb_psis_smooth(const double* d_lw_in, double* d_lw_out, long long
     if (!d_lw_in || !d_lw_out || !d_out_diag || !d_ws || !(reff > 0.0)) return VB_ERR_ARG;
     if (n <= 1) return VB_ERR_ARG;                                    // psis.py:143-144
     if (d_lw_in == d_lw_out) return VB_ERR_ARG;                       // streaming loads assume no aliasing
-    const PsisLayout L = psis_layout(n, reff);
-    if (ws_bytes < L.total + vb_max_workspace_bytes(n) + 256) return VB_ERR_WORKSPACE;
+    const SmoothLayout L = smooth_layout(n, reff);
+    if (ws_bytes < L.total + 256) return VB_ERR_WORKSPACE;
     cudaStream_t st = (cudaStream_t)stream;
-    char* ws = (char*)d_ws;
-    double* M_ptr = (double*)(ws + L.off_M);
-    double* pivot_ptr = (double*)(ws + L.off_pivot);
-    unsigned long long* counters = (unsigned long long*)(ws + L.off_counters);
-    double* state = (double*)(ws + L.off_state);
-    long long* counts = (long long*)(ws + L.off_counts);
-    unsigned int* hist = (unsigned int*)(ws + L.off_hist);
+    char* ws = (char*)(((uintptr_t)d_ws + 255) & ~(uintptr_t)255);
     Cand* sample = (Cand*)(ws + L.off_sample);
+    double* pivot_x = (double*)(ws + L.off_pivot);
+    unsigned long long* count = (unsigned long long*)(ws + L.off_count);
+    double* body_max = (double*)(ws + L.off_bodymax);
+    double* terms = (double*)(ws + L.off_terms);
     Cand* cand1 = (Cand*)(ws + L.off_cand1);
-    Cand* cand2 = (Cand*)(ws + L.off_cand2);
-    double* x2 = (double*)(ws + L.off_x2);
-    double* tail_new = (double*)(ws + L.off_tailnew);
-    double* bs = (double*)(ws + L.off_bs);
-    double* Lq = (double*)(ws + L.off_L);
-    double* wq = (double*)(ws + L.off_w);
-    double* blk_pre = (double*)(ws + L.off_blk_pre);
-    double* blk2 = (double*)(ws + L.off_blk2);
-    double* blk3 = (double*)(ws + L.off_blk3);
-    double* blk4 = (double*)(ws + L.off_blk4);
-    double* blk5 = (double*)(ws + L.off_blk5);
-    void* max_ws = ws + L.total;
     const long long K1 = psis_K1(n, reff);
-
-    // P1: max
-    int rc = vb_max(d_lw_in, n, M_ptr, max_ws, vb_max_workspace_bytes(n), stream);
-    if (rc != VB_OK) return rc;
-
-    // P2: prefilter, escalating the sample quantile until the candidates hold the K1+1 largest
     const bool direct = (n <= kDirectSortMax);
+    int rc;
     if (!direct) {
-        sample_kernel<<<16, 256, 0, st>>>(d_lw_in, n, M_ptr, sample);
-        VB_LAUNCH_CHECK();
-        rc = bitonic_sort(sample, kSampleSize, st);
+        rc = vb_psis_sample(d_lw_in, n, 0, sample, stream);
         if (rc != VB_OK) return rc;
     }
-    unsigned long long h_counters[4];
+    // filter pass, widening the sample quantile until the candidates hold the K1+1 largest
     long long C1 = 0;
     double frac = 4.0 * (double)(K1 + 1) / (double)n;
     if (frac < 0.01) frac = 0.01;
     for (int attempt = 0;; ++attempt) {
         if (direct) {
-            set_double_kernel<<<1, 1, 0, st>>>(pivot_ptr, INFINITY);
-        } else {
-            const int rank = (int)ceil(frac * kSampleSize);
-            pivot_kernel<<<1, 1, 0, st>>>(sample, rank, pivot_ptr);
+            set_double_kernel<<<1, 1, 0, st>>>(pivot_x, -INFINITY);
+            VB_LAUNCH_CHECK();
+        } else if (attempt == 0) {
+            rc = vb_psis_pivot(sample, kSampleSize, kSampleSize, frac, pivot_x, stream);
+            if (rc != VB_OK) return rc;
+        } else {                                                       // the sample is already sorted
+            const long long rank = (long long)ceil(frac * kSampleSize);
+            pivot_kernel<<<1, 1, 0, st>>>(sample, kSampleSize, rank, pivot_x);
+            VB_LAUNCH_CHECK();
         }
-        VB_LAUNCH_CHECK();
-        VB_CUDA_TRY(cudaMemsetAsync(counters, 0, 4 * 8, st));
-        PrefilterOut po{cand1, L.cap1, counters, blk_pre};
-        prefilter_kernel<<<L.g_pre, 256, 0, st>>>(d_lw_in, n, 0, M_ptr, pivot_ptr, po);
-        VB_LAUNCH_CHECK();
-        VB_CUDA_TRY(cudaMemcpyAsync(h_counters, counters, 8, cudaMemcpyDeviceToHost, st));
+        rc = vb_psis_filter(d_lw_in, n, 0, pivot_x, cand1, L.cap1, count, body_max, ws + L.off_filter,
+                            vb_psis_filter_workspace_bytes(n), stream);
+        if (rc != VB_OK) return rc;
+        unsigned long long h = 0;
+        VB_CUDA_TRY(cudaMemcpyAsync(&h, count, 8, cudaMemcpyDeviceToHost, st));
         VB_CUDA_TRY(cudaStreamSynchronize(st));
-        C1 = (long long)h_counters[0];
+        C1 = (long long)h;
         if (C1 >= K1 + 1 && C1 <= L.cap1) break;
         if (direct || attempt >= 8) return VB_ERR_UNSUPPORTED;       // cannot happen for direct
-        if (C1 > L.cap1) {
-            // more ties at the top than the candidate buffer holds
-            return VB_ERR_UNSUPPORTED;
-        }
-        frac *= 4.0;                                                  // too few: widen the prefilter
+        if (C1 > L.cap1) return VB_ERR_UNSUPPORTED;                  // more ties at the top than the buffer holds
+        frac *= 4.0;                                                  // too few: widen
         if (frac > 1.0) frac = 1.0;
     }
-
-    // optional refinement so that the sort stays small
-    Cand* sort_buf = cand2;
-    long long C2 = C1;
-    int n_blk2 = 0;
-    if (C1 > kDirectSortMax) {
-        VB_CUDA_TRY(cudaMemsetAsync(hist, 0, (size_t)kHistBins * 4, st));
-        hist_kernel<<<grid_for(C1, 256, kNumSMs * 4), 256, 0, st>>>(cand1, C1, pivot_ptr, hist);
-        VB_LAUNCH_CHECK();
-        hist_scan_kernel<<<1, 1024, 0, st>>>(hist, K1 + 1, counts + 2);
-        VB_LAUNCH_CHECK();
-        compact2_kernel<<<L.g_small, 256, 0, st>>>(cand1, C1, pivot_ptr, counts + 2, cand2, counters + 1, blk2);
-        VB_LAUNCH_CHECK();
-        n_blk2 = L.g_small;
-        VB_CUDA_TRY(cudaMemcpyAsync(h_counters, counters + 1, 8, cudaMemcpyDeviceToHost, st));
-        VB_CUDA_TRY(cudaStreamSynchronize(st));
-        C2 = (long long)h_counters[0];
-        if (C2 < K1 + 1 || C2 > C1) return VB_ERR_UNSUPPORTED;
-    } else {
-        VB_CUDA_TRY(cudaMemcpyAsync(cand2, cand1, (size_t)C1 * sizeof(Cand), cudaMemcpyDeviceToDevice, st));
-    }
-
-    // S: sort candidates ascending by (shifted weight, index)
-    const long long n_pad = pad_pow2(C2);
-    pad_cands_kernel<<<grid_for(n_pad - C2 + 1, 256, kNumSMs * 4), 256, 0, st>>>(sort_buf, C2, n_pad);
-    VB_LAUNCH_CHECK();
-    rc = bitonic_sort(sort_buf, n_pad, st);
+    const double* M_ptr = body_max + 1;                               // the maximum is a candidate
+    rc = vb_psis_prepare(cand1, C1, M_ptr, pivot_x, body_max, terms, stream);
     if (rc != VB_OK) return rc;
-
-    // T: cutoff, tail, GPD fit, smoothing
-    tail_bounds_kernel<<<1, 1, 0, st>>>(sort_buf, C2, K1, state, counts);
-    VB_LAUNCH_CHECK();
-    tail_excess_kernel<<<L.g_small, 256, 0, st>>>(sort_buf, state, counts, x2);
-    VB_LAUNCH_CHECK();
-    rc = run_gpd_fit(x2, counts, K1 + 1, bs, Lq, wq, blk3, L.g_small, state, st);
+    rc = vb_psis_tail(cand1, C1, K1, M_ptr, pivot_x, terms, 1, d_out_diag, d_out_tail_idx_or_null,
+                      ws + L.off_tail, vb_psis_tail_workspace_bytes(L.cap1, K1), stream);
     if (rc != VB_OK) return rc;
-    tail_smooth_kernel<<<L.g_small, 256, 0, st>>>(sort_buf, state, counts, tail_new, d_out_tail_idx_or_null, blk4);
-    VB_LAUNCH_CHECK();
-    cand_body_kernel<<<L.g_small, 256, 0, st>>>(sort_buf, counts, 0, n, blk5);
-    VB_LAUNCH_CHECK();
-    SumList lists;
-    lists.p[0] = blk_pre; lists.n[0] = L.g_pre;
-    lists.p[1] = blk2;    lists.n[1] = n_blk2;
-    lists.p[2] = blk5;    lists.n[2] = L.g_small;
-    lists.p[3] = blk4;    lists.n[3] = L.g_small;
-    psis_finish_kernel<<<1, 256, 0, st>>>(lists, M_ptr, counts, C2, state, d_out_diag, nullptr);
-    VB_LAUNCH_CHECK();
-
-    // P3: normalise and scatter the smoothed tail
-    normalise_kernel<<<grid_for((n + 1) / 2, 256, kNumSMs * 8), 256, 0, st>>>(d_lw_in, d_lw_out, n, M_ptr, state + 5);
-    VB_LAUNCH_CHECK();
-    tail_scatter_kernel<<<L.g_small, 256, 0, st>>>(sort_buf, counts, tail_new, state, d_lw_out, 0, n);
-    VB_LAUNCH_CHECK();
-    return VB_OK;
+    return vb_psis_write(d_lw_in, d_lw_out, n, 0, M_ptr, C1, K1, ws + L.off_tail, stream);
 }
 
 // ------------------------------------------------------------------------------------------ standalone ops
+// (vb_max / vb_max_workspace_bytes are declared in include/viabel_b200.h and defined in bounds.cu)
 extern "C" size_t vb_gpd_fit_workspace_bytes(long long n) {
     if (n < 2) return 0;
     const long long m_max = 30 + (long long)sqrt((double)n) + 1;

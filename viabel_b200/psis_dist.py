@@ -1,0 +1,202 @@
+"""``psislw`` for log weights sharded across the ranks of a torch.distributed group.
+
+Rank r holds the contiguous slice ``[index0_r, index0_r + n_r)`` of the global weight vector.  The
+result equals the unsharded ``psislw`` of the concatenation: the tail index set, its order
+(ties by ascending global index) and k-hat are the same on every rank; each rank gets the
+smoothed, normalised weights of its own slice.
+
+Exchange per call (all small; nothing bulk crosses NVLink):
+  all_gather   shard sizes (1 int64), strided samples (4096 x 16 B per rank)
+  all_reduce   candidate counts (sum), local maxima (max)
+  all_gather   refined candidate counts, then <= ~(K+1) (key, index) pairs per rank (K = 94 869 at
+               n = 1e9: 1.5 MB per rank) and two body-sum terms per rank
+The device work is the staged C ABI of ``include/viabel_b200.h`` (``vb_psis_sample`` ... ``vb_psis_write``);
+``stages`` lets the CPU tests drive the same protocol over gloo with a numpy restatement of the stages.
+"""
+import math
+
+import torch
+
+from . import _lib
+
+SAMPLE = 4096
+DIRECT_MAX = 1 << 17
+
+
+def psis_tail_count(n, Reff):
+    """``ceil(min(0.2 n, 3 sqrt(n / Reff)))`` (``psis.py:157``)."""
+    return int(math.ceil(min(0.2 * n, 3.0 * math.sqrt(n / Reff))))
+
+
+def _pow2_at_least(x, lo=SAMPLE):
+    p = lo
+    while p < x:
+        p <<= 1
+    return p
+
+
+class CudaStages:
+    """The staged C ABI on the current CUDA device / stream."""
+
+    def __init__(self):
+        from ._device import Workspace, device
+        self.ws = Workspace()
+        self.device = device()
+
+    def _p(self, t):
+        return 0 if t is None else t.data_ptr()
+
+    def _stream(self):
+        return torch.cuda.current_stream().cuda_stream
+
+    def empty(self, shape, dtype):
+        return torch.empty(shape, dtype=dtype, device=self.device)
+
+    def sample(self, lw, index0):
+        out = self.empty((SAMPLE, 2), torch.int64)
+        _lib.check(_lib.lib.vb_psis_sample(self._p(lw), lw.numel(), index0, self._p(out), self._stream()), 'vb_psis_sample')
+        return out
+
+    def pivot(self, sample_buf, count, frac, out):
+        _lib.check(_lib.lib.vb_psis_pivot(self._p(sample_buf), count, sample_buf.shape[0], float(frac), self._p(out),
+                                          self._stream()), 'vb_psis_pivot')
+
+    def filter(self, lw, index0, pivot, cap):
+        cand = self.empty((cap, 2), torch.int64)
+        count = self.empty((1,), torch.int64)
+        body_max = self.empty((2,), torch.float64)
+        nb = _lib.lib.vb_psis_filter_workspace_bytes(lw.numel())
+        ws = self.ws.get('filter', nb)
+        _lib.check(_lib.lib.vb_psis_filter(self._p(lw), lw.numel(), index0, self._p(pivot), self._p(cand), cap,
+                                           self._p(count), self._p(body_max), self._p(ws), ws.numel(), self._stream()),
+                   'vb_psis_filter')
+        return cand, count, body_max
+
+    def prepare(self, cand, count, M, pivot, body_max, terms):
+        _lib.check(_lib.lib.vb_psis_prepare(self._p(cand), count, self._p(M), self._p(pivot), self._p(body_max),
+                                            self._p(terms), self._stream()), 'vb_psis_prepare')
+
+    def refine(self, cand, count, M, pivot, keep, terms):
+        out = self.empty((max(count, 1), 2), torch.int64)
+        cnt = self.empty((1,), torch.int64)
+        ws = self.ws.get('refine', _lib.lib.vb_psis_refine_workspace_bytes())
+        _lib.check(_lib.lib.vb_psis_refine(self._p(cand), count, self._p(M), self._p(pivot), keep, self._p(out),
+                                           self._p(cnt), self._p(terms) + 8, self._p(ws), ws.numel(), self._stream()),
+                   'vb_psis_refine')
+        return out, cnt
+
+    def tail(self, cands, count, K1, M, pivot, terms, want_tail_idx=False):
+        diag = self.empty((8,), torch.float64)
+        tail_idx = torch.full((K1 + 1,), -1, dtype=torch.int64, device=self.device) if want_tail_idx else None
+        ws = self.ws.get('tail', _lib.lib.vb_psis_tail_workspace_bytes(count, K1))
+        _lib.check(_lib.lib.vb_psis_tail(self._p(cands), count, K1, self._p(M), self._p(pivot), self._p(terms),
+                                         terms.numel(), self._p(diag), self._p(tail_idx), self._p(ws), ws.numel(),
+                                         self._stream()), 'vb_psis_tail')
+        return diag, tail_idx, (ws, count, K1)
+
+    def write(self, lw, index0, M, handle):
+        ws, count, K1 = handle
+        out = torch.empty_like(lw)
+        _lib.check(_lib.lib.vb_psis_write(self._p(lw), self._p(out), lw.numel(), index0, self._p(M), count, K1,
+                                          self._p(ws), self._stream()), 'vb_psis_write')
+        return out
+
+
+class DistComm:
+    """The three collectives the protocol needs, over a torch.distributed group (NCCL on the GPU
+    box, gloo in the CPU tests).  Tests substitute an in-process communicator with the same methods."""
+
+    def __init__(self, group=None):
+        import torch.distributed as dist
+        self.dist, self.group = dist, group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+
+    def all_gather(self, t):
+        """(world, *t.shape): row r = rank r's tensor (equal shapes on every rank)."""
+        flat = t.contiguous().view(-1)
+        out = torch.empty(self.world * flat.numel(), dtype=t.dtype, device=t.device)
+        self.dist.all_gather_into_tensor(out, flat, group=self.group)
+        return out.view((self.world,) + tuple(t.shape))
+
+    def all_reduce_sum(self, t):
+        self.dist.all_reduce(t, group=self.group)
+        return t
+
+    def all_reduce_max(self, t):
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX, group=self.group)
+        return t
+
+
+def psislw_sharded(lw_local, Reff=1.0, group=None, stages=None, want_detail=False, comm=None):
+    """Sharded ``psislw`` (``psis.py:112-208``) of one weight column.
+
+    ``lw_local``: this rank's contiguous slice (float64, on the stages' device).  Returns
+    ``(lw_out_local, k)`` or, with ``want_detail``, ``(lw_out_local, k, detail)`` where detail holds
+    the diag vector and the tail's global indices in ascending tail order."""
+    st = stages if stages is not None else CudaStages()
+    comm = comm if comm is not None else DistComm(group)
+    world, rank = comm.world, comm.rank
+    n_local = int(lw_local.numel())
+    dev = lw_local.device
+    sizes = [int(v) for v in comm.all_gather(torch.tensor([n_local], dtype=torch.int64, device=dev)).cpu().view(-1).tolist()]
+    n = sum(sizes)
+    if n <= 1:
+        raise ValueError("More than one log-weight needed.")
+    if min(sizes) < 1:
+        raise ValueError('every rank needs at least one log weight')
+    index0 = sum(sizes[:rank])
+    K1 = psis_tail_count(n, Reff)
+    direct = n <= DIRECT_MAX
+
+    pivot = st.empty((1,), torch.float64)
+    if direct:
+        pivot.fill_(-math.inf)
+        cap = n_local
+    else:
+        mine = st.sample(lw_local, index0)
+        cap_s = _pow2_at_least(world * SAMPLE)
+        sample_all = st.empty((cap_s, 2), torch.int64)
+        sample_all[:world * SAMPLE] = comm.all_gather(mine).view(world * SAMPLE, 2)
+        cap = min(n_local, max(1 << 21, n_local // 16))
+    frac = max(0.01, 4.0 * (K1 + 1) / n)
+    for attempt in range(10):
+        if not direct:
+            # first call pads [count, capacity) and sorts; later calls see a full, sorted buffer whose
+            # pads (smallest keys) sit at the bottom and do not disturb ranks counted from the top
+            st.pivot(sample_all, world * SAMPLE if attempt == 0 else sample_all.shape[0], frac, pivot)
+        cand, count_t, body_max = st.filter(lw_local, index0, pivot, cap)
+        count = int(count_t.item())
+        tot = comm.all_reduce_sum(torch.tensor([count, 1 if count > cap else 0], dtype=torch.int64, device=dev))
+        total, overflow = (int(v) for v in tot.cpu().tolist())
+        if overflow:
+            raise _lib.ViabelB200Error('psislw: more candidates than the buffer holds (heavy ties at the top)')
+        if total >= K1 + 1:
+            break
+        if direct or frac >= 1.0:
+            raise _lib.ViabelB200Error('psislw: could not collect the tail candidates')
+        frac = min(1.0, frac * 4.0)
+    M = body_max[1:2].clone()
+    comm.all_reduce_max(M)
+    terms = st.empty((2,), torch.float64)
+    st.prepare(cand, count, M, pivot, body_max, terms)
+    cand2, count2_t = st.refine(cand, count, M, pivot, K1 + 1, terms)
+    count2 = int(count2_t.item())
+    counts = [int(v) for v in comm.all_gather(torch.tensor([count2], dtype=torch.int64, device=dev)).cpu().view(-1).tolist()]
+    maxc = max(max(counts), 1)
+    send = st.empty((maxc, 2), torch.int64)
+    send[:count2] = cand2[:count2]
+    if count2 < maxc:
+        send[count2:] = 0
+    recv = comm.all_gather(send)                                      # (world, maxc, 2)
+    all_cands = torch.cat([recv[r, :counts[r]] for r in range(world)], dim=0).contiguous()
+    all_terms = comm.all_gather(terms).view(-1).contiguous()          # rank order: deterministic sum
+    total2 = sum(counts)
+    diag, tail_idx, handle = st.tail(all_cands, total2, K1, M, pivot, all_terms, want_tail_idx=want_detail)
+    out = st.write(lw_local, index0, M, handle)
+    d = diag.cpu().numpy()
+    if not want_detail:
+        return out, d[0]
+    n2 = int(d[3])
+    detail = dict(k=d[0], sigma=d[1], xcutoff=d[2], n2=n2, smoothed=bool(d[4]), max=d[5], lse=d[6],
+                  n_candidates=int(d[7]), tail_idx_sorted=tail_idx[:n2].cpu().numpy(), index0=index0, n=n)
+    return out, d[0], detail
