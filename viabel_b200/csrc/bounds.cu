@@ -21,19 +21,24 @@ constexpr int kDivThreads = 256;
 struct DivAcc {
     double M, sw, sw2, cnt, sd, sd2;
     __device__ __forceinline__ void init() { M = -INFINITY; sw = sw2 = cnt = sd = sd2 = 0.0; }
-    __device__ __forceinline__ void add(double x, double alpha, double K) {
-        if (x > M) {
-            const double f = rescale_factor(alpha, M, x);
-            sw *= f;
-            sw2 *= f * f;
-            M = x;
-        }
-        const double w = exp_nonpos(alpha * (x - M));
+    __device__ __forceinline__ void raise_to(double m, double alpha) {      // rare: a new running maximum
+        const double f = rescale_factor(alpha, M, m);
+        sw *= f;
+        sw2 *= f * f;
+        M = m;
+    }
+    // branch-free accumulation of one element that is known to be <= M
+    __device__ __forceinline__ void add_below(double x, double alpha, double K, const double* table) {
+        const double w = exp_nonpos_flush(alpha * (x - M), table);
         sw += w;
         sw2 = fma(w, w, sw2);
         const double d = x - K;
         sd += d;
         sd2 = fma(d, d, sd2);
+    }
+    __device__ __forceinline__ void add(double x, double alpha, double K, const double* table) {
+        if (x > M) raise_to(x, alpha);
+        add_below(x, alpha, K, table);
         cnt += 1.0;
     }
     __device__ __forceinline__ void rescale_to(double Mn, double alpha) {
@@ -48,9 +53,13 @@ __global__ void __launch_bounds__(kDivThreads)
 divergence_blocks_kernel(const double* __restrict__ lw, long long n, double alpha,
                          double* __restrict__ block_out /* [grid][6] */) {
     __shared__ double red[kDivThreads / 32][6];
+    __shared__ double s_table[64];
+    if (threadIdx.x < 64) s_table[threadIdx.x] = kExp2Table[threadIdx.x];
+    __syncthreads();
     const double K = lw[0];
-    DivAcc a;
+    DivAcc a, b;                        // two independent accumulator sets (same running max)
     a.init();
+    b.init();
     const long long gtid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     const long long gthreads = (long long)gridDim.x * blockDim.x;
     const bool aligned = (reinterpret_cast<uintptr_t>(lw) & 15u) == 0;
@@ -58,23 +67,40 @@ divergence_blocks_kernel(const double* __restrict__ lw, long long n, double alph
         const long long n2 = n >> 1;
         const double2* p = reinterpret_cast<const double2*>(lw);
         long long i = gtid;
-        // 4 independent 16-byte loads in flight per thread
+        // 4 independent 16-byte loads in flight per thread; one (rare) branch per 8 elements
         for (; i + 3 * gthreads < n2; i += 4 * gthreads) {
             const double2 v0 = ld_stream2(p + i), v1 = ld_stream2(p + i + gthreads);
             const double2 v2 = ld_stream2(p + i + 2 * gthreads), v3 = ld_stream2(p + i + 3 * gthreads);
-            a.add(v0.x, alpha, K); a.add(v0.y, alpha, K);
-            a.add(v1.x, alpha, K); a.add(v1.y, alpha, K);
-            a.add(v2.x, alpha, K); a.add(v2.y, alpha, K);
-            a.add(v3.x, alpha, K); a.add(v3.y, alpha, K);
+            const double m8 = fmax(fmax(fmax(v0.x, v0.y), fmax(v1.x, v1.y)), fmax(fmax(v2.x, v2.y), fmax(v3.x, v3.y)));
+            if (m8 > a.M) { a.raise_to(m8, alpha); b.raise_to(m8, alpha); }
+            a.add_below(v0.x, alpha, K, s_table); b.add_below(v0.y, alpha, K, s_table);
+            a.add_below(v1.x, alpha, K, s_table); b.add_below(v1.y, alpha, K, s_table);
+            a.add_below(v2.x, alpha, K, s_table); b.add_below(v2.y, alpha, K, s_table);
+            a.add_below(v3.x, alpha, K, s_table); b.add_below(v3.y, alpha, K, s_table);
+            a.cnt += 8.0;
         }
         for (; i < n2; i += gthreads) {
             const double2 v = ld_stream2(p + i);
-            a.add(v.x, alpha, K); a.add(v.y, alpha, K);
+            const double m2 = fmax(v.x, v.y);
+            if (m2 > a.M) { a.raise_to(m2, alpha); b.raise_to(m2, alpha); }
+            a.add_below(v.x, alpha, K, s_table); b.add_below(v.y, alpha, K, s_table);
+            a.cnt += 2.0;
         }
-        if ((n & 1) && gtid == 0) a.add(lw[n - 1], alpha, K);
+        if ((n & 1) && gtid == 0) {
+            const double x = lw[n - 1];
+            if (x > a.M) { a.raise_to(x, alpha); b.raise_to(x, alpha); }
+            a.add_below(x, alpha, K, s_table);
+            a.cnt += 1.0;
+        }
     } else {
-        for (long long i = gtid; i < n; i += gthreads) a.add(lw[i], alpha, K);
+        for (long long i = gtid; i < n; i += gthreads) {
+            const double x = lw[i];
+            if (x > a.M) { a.raise_to(x, alpha); b.raise_to(x, alpha); }
+            a.add_below(x, alpha, K, s_table);
+            a.cnt += 1.0;
+        }
     }
+    a.sw += b.sw; a.sw2 += b.sw2; a.sd += b.sd; a.sd2 += b.sd2;
     // warp, then block merge
     const double Mw = warp_max(a.M);
     a.rescale_to(Mw, alpha);

@@ -145,6 +145,40 @@ __device__ __forceinline__ double exp_nonpos(double x) {
     return __hiloint2double(__double2hiint(s) + e * 1048576, __double2loint(s));   // * 2^e
 }
 
+// Branch-free variant for streaming sums of weights relative to a maximum / pivot: the same
+// 1-ulp evaluation for -700 <= x <= 0; arguments below -700 (incl. -inf) are clamped, i.e. give
+// e^-700 ~ 1e-304 instead of a smaller number -- invisible in a double-precision sum that holds any
+// term of normal size (every sum here contains exp(0) = 1 for the maximum); NaN stays NaN.
+// `table` is the 64-entry 2^(j/64) table, normally a shared-memory copy of kExp2Table.
+// Coefficients live in the constant bank (not `const`: the compiler must not fold them into
+// immediates, which it would re-materialise with two MOVs in front of every DFMA); DFMA reads
+// c[bank][offset] operands directly.
+static __constant__ double kExpCoef[10] = {
+    0x1.71547652b82fep+6,      // 64 / ln 2
+    6755399441055744.0,        // 1.5 * 2^52
+    -0x1.62e42fee00000p-7,     // -ln2_hi / 64
+    -0x1.a39ef35793c76p-39,    // -ln2_lo / 64
+    1.0 / 720.0, 1.0 / 120.0, 1.0 / 24.0, 1.0 / 6.0, 0.5, -700.0};
+__device__ __forceinline__ double exp_nonpos_flush(double x, const double* __restrict__ table) {
+    const double kMagic = kExpCoef[1];
+    const double xc = !(x <= kExpCoef[9]) ? x : kExpCoef[9];     // unordered compare: NaN passes through
+    const double t = fma(xc, kExpCoef[0], kMagic);
+    const int ki = __double2loint(t);
+    const double kd = t - kMagic;
+    double r = fma(kd, kExpCoef[2], xc);
+    r = fma(kd, kExpCoef[3], r);
+    double q = fma(r, kExpCoef[4], kExpCoef[5]);
+    q = fma(r, q, kExpCoef[6]);
+    q = fma(r, q, kExpCoef[7]);
+    q = fma(r, q, kExpCoef[8]);
+    q = fma(r, q, 1.0);
+    q = q * r;                                      // exp(r) - 1
+    const double T = table[ki & 63];
+    // 2^floor(k/64) folded into the table value (never NaN, stays normal for k >= -64640)
+    const double Ts = __hiloint2double(__double2hiint(T) + ((ki & ~63) << 14), __double2loint(T));
+    return fma(Ts, q, Ts);
+}
+
 // ---------------------------------------------------------------------------- ordered keys
 // Monotone map double -> uint64 (ascending).  -0.0 and +0.0 map to different keys but
 // compare like numpy's sort would order equal values only through the index tie-break.

@@ -40,7 +40,7 @@ __device__ __forceinline__ bool cand_less(const Cand& a, const Cand& b) {
 
 constexpr int kSortChunk = 4096;          // elements sorted per CTA in shared memory (64 KiB)
 constexpr int kSortThreads = 1024;
-constexpr int kHistBins = 65536;
+constexpr int kHistBins = 8192;          // 32 KiB of counters: privatised per CTA in shared memory
 constexpr int kSampleSize = 4096;
 constexpr long long kDirectSortMax = 1ll << 17;
 constexpr double kNegLogTiny = 708.3964185322641;      // -log(DBL_MIN), psis.py:158
@@ -158,6 +158,39 @@ __global__ void pivot_kernel(const Cand* __restrict__ sorted_sample, long long c
     if (threadIdx.x == 0 && blockIdx.x == 0)
         *out_pivot_x = (rank >= count) ? -INFINITY : key_to_f64(sorted_sample[count - 1 - rank].key);
 }
+// The same selection without sorting: one CTA radix-selects the (rank+1)-th largest 64-bit key,
+// eight 8-bit digits from the top (ties in the VALUE do not matter for a pivot).
+__global__ void __launch_bounds__(1024)
+radix_select_kernel(const Cand* __restrict__ sample, int count, int rank, double* __restrict__ out_pivot_x) {
+    __shared__ unsigned int hist[256];
+    __shared__ unsigned long long s_prefix;
+    __shared__ int s_rank;
+    const int tid = threadIdx.x;
+    if (tid == 0) { s_prefix = 0ull; s_rank = rank; }
+    unsigned long long mask = 0ull;
+    for (int shift = 56; shift >= 0; shift -= 8) {
+        if (tid < 256) hist[tid] = 0;
+        __syncthreads();
+        const unsigned long long prefix = s_prefix;
+        const int r = s_rank;
+        for (int i = tid; i < count; i += blockDim.x) {
+            const unsigned long long k = sample[i].key;
+            if ((k & mask) == prefix) atomicAdd(&hist[(unsigned)(k >> shift) & 255u], 1u);
+        }
+        __syncthreads();
+        if (tid < 256) {
+            unsigned int above = 0;
+            for (int d = tid + 1; d < 256; ++d) above += hist[d];
+            if ((int)above <= r && r < (int)(above + hist[tid])) {       // exactly one digit owns rank r
+                s_prefix = prefix | ((unsigned long long)tid << shift);
+                s_rank = r - (int)above;
+            }
+        }
+        mask |= 255ull << shift;
+        __syncthreads();
+    }
+    if (tid == 0) *out_pivot_x = key_to_f64(s_prefix);
+}
 __global__ void set_double_kernel(double* p, double v) { if (threadIdx.x == 0 && blockIdx.x == 0) *p = v; }
 __global__ void set_counts_kernel(long long* p, long long a, long long b, long long c, long long d) {
     if (threadIdx.x == 0 && blockIdx.x == 0) { p[0] = a; p[1] = b; p[2] = c; p[3] = d; }
@@ -182,7 +215,7 @@ constexpr int kFThreads = 256;
 constexpr int kFWarps = kFThreads / 32;
 constexpr int kFPerThread = 8;                          // 4 x 16-byte loads in flight
 constexpr int kFChunk = kFThreads * kFPerThread;        // elements per CTA per round
-constexpr int kFWarpBuf = 512;                          // staged candidates per warp (8 KiB)
+constexpr int kFWarpBuf = 128;                          // staged candidates per warp (2 KiB); overflow goes straight to global
 constexpr size_t kFSmem = (size_t)kFWarps * kFWarpBuf * sizeof(Cand);
 
 __device__ __forceinline__ void filter_flush(Cand* mybuf, unsigned int* wcount, unsigned int cnt, int lane,
@@ -200,7 +233,7 @@ __device__ __forceinline__ void filter_flush(Cand* mybuf, unsigned int* wcount, 
 template <bool ALIGNED>
 __global__ void __launch_bounds__(kFThreads)
 filter_kernel(const double* __restrict__ lw, long long n, long long index0, const double* __restrict__ pivot_ptr,
-              FilterOut o) {
+              const FilterOut o) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ unsigned int wcounts[kFWarps];
     __shared__ double scratch[32];
@@ -209,54 +242,89 @@ filter_kernel(const double* __restrict__ lw, long long n, long long index0, cons
     unsigned int* wcount = &wcounts[warp];
     if (lane == 0) *wcount = 0;
     __syncwarp();
+    __shared__ double s_table[64];
+    if (tid < 64) s_table[tid] = kExp2Table[tid];
+    __syncthreads();
     const double pivot = *pivot_ptr;
     double body = 0.0, cmax = -INFINITY;
     const long long n_chunks = (n + kFChunk - 1) / kFChunk;
     const long long full_chunks = n / kFChunk;
 
-    auto take = [&](double x, long long i) {
-        if (x >= pivot) {
-            const unsigned int pos = atomicAdd(wcount, 1u);
-            Cand c;
-            c.key = (unsigned long long)__double_as_longlong(x);
-            c.idx = (unsigned long long)(index0 + i);
+    auto stage = [&](double x, long long i) {            // rare: x is a candidate
+        const unsigned int pos = atomicAdd(wcount, 1u);
+        Cand c;
+        c.key = (unsigned long long)__double_as_longlong(x);
+        c.idx = (unsigned long long)(index0 + i);
+        if (pos < (unsigned)kFWarpBuf) {
             mybuf[pos] = c;
-            cmax = fmax(cmax, x);
-        } else {
-            body += exp_nonpos(x - pivot);          // NaN lands here and poisons the sum, like np.exp would
+        } else {                                         // dense candidates (tiny n or a widened pivot): unstaged
+            const unsigned long long g = atomicAdd(o.counter, 1ull);
+            if ((long long)g < o.cap) o.cand[g] = c;
         }
+        cmax = fmax(cmax, x);
     };
+    double body2 = 0.0;                                  // second accumulator: two independent add chains
 
+    // software pipeline: the next chunk's four 16-byte loads are in flight while this one is evaluated
+    double2 v[kFPerThread / 2];
+    {
+        const long long c0 = blockIdx.x;
+        if (ALIGNED && c0 < full_chunks) {
+            const double2* p = reinterpret_cast<const double2*>(lw + c0 * kFChunk) + tid;
+#pragma unroll
+            for (int q = 0; q < kFPerThread / 2; ++q) v[q] = ld_stream2(p + q * kFThreads);
+        }
+    }
     for (long long chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
         const long long base = chunk * kFChunk;
         if (ALIGNED && chunk < full_chunks) {
-            const double2* p = reinterpret_cast<const double2*>(lw + base) + tid;
-            double2 v[kFPerThread / 2];
+            double2 nv[kFPerThread / 2];
+            const long long next = chunk + gridDim.x;
+            if (next < full_chunks) {
+                const double2* p = reinterpret_cast<const double2*>(lw + next * kFChunk) + tid;
 #pragma unroll
-            for (int q = 0; q < kFPerThread / 2; ++q) v[q] = ld_stream2(p + q * kFThreads);
+                for (int q = 0; q < kFPerThread / 2; ++q) nv[q] = ld_stream2(p + q * kFThreads);
+            }
+            bool any = false;
 #pragma unroll
             for (int q = 0; q < kFPerThread / 2; ++q) {
-                const long long i = base + 2 * (tid + q * kFThreads);
-                take(v[q].x, i);
-                take(v[q].y, i + 1);
+                // branch-free main path: candidates add e^-700 (nothing); NaN poisons the sum
+                const bool c0 = v[q].x >= pivot, c1 = v[q].y >= pivot;
+                any = any || c0 || c1;
+                body += exp_nonpos_flush(c0 ? -INFINITY : v[q].x - pivot, s_table);
+                body2 += exp_nonpos_flush(c1 ? -INFINITY : v[q].y - pivot, s_table);
             }
-        } else {
+            if (any) {
 #pragma unroll
+                for (int q = 0; q < kFPerThread / 2; ++q) {
+                    const long long i = base + 2 * (tid + q * kFThreads);
+                    if (v[q].x >= pivot) stage(v[q].x, i);
+                    if (v[q].y >= pivot) stage(v[q].y, i + 1);
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < kFPerThread / 2; ++q) v[q] = nv[q];
+        } else {
+#pragma unroll 1
             for (int q = 0; q < kFPerThread; ++q) {
                 const long long i = base + tid + q * kFThreads;
-                if (i < n) take(lw[i], i);
+                if (i < n) {
+                    const double x = lw[i];
+                    if (x >= pivot) stage(x, i);
+                    else body += exp_nonpos_flush(x - pivot, s_table);
+                }
             }
         }
         __syncwarp();
         const unsigned int cnt = *reinterpret_cast<volatile unsigned int*>(wcount);
         __syncwarp();
-        if (cnt > (unsigned)(kFWarpBuf - 32 * kFPerThread)) filter_flush(mybuf, wcount, cnt, lane, o);
+        if (cnt > (unsigned)(kFWarpBuf / 2)) filter_flush(mybuf, wcount, cnt > kFWarpBuf ? kFWarpBuf : cnt, lane, o);
     }
     __syncwarp();
     const unsigned int cnt = *reinterpret_cast<volatile unsigned int*>(wcount);
     __syncwarp();
-    if (cnt > 0) filter_flush(mybuf, wcount, cnt, lane, o);
-    body = block_sum(body, scratch);
+    if (cnt > 0) filter_flush(mybuf, wcount, cnt > kFWarpBuf ? kFWarpBuf : cnt, lane, o);
+    body = block_sum(body + body2, scratch);
     cmax = block_max(cmax, scratch);
     if (tid == 0) { o.block_body[blockIdx.x] = body; o.block_max[blockIdx.x] = cmax; }
 }
@@ -290,8 +358,12 @@ __global__ void derive_kernel(const double* __restrict__ M_ptr, const double* __
 }
 
 // ------------------------------------------------------------------------------------------ refinement histogram
-__global__ void hist_kernel(const Cand* __restrict__ cand, long long count, const double* __restrict__ pivot_ptr,
-                            unsigned int* __restrict__ hist) {
+__global__ void __launch_bounds__(512)
+hist_kernel(const Cand* __restrict__ cand, long long count, const double* __restrict__ pivot_ptr,
+            unsigned int* __restrict__ hist) {
+    __shared__ unsigned int sh[kHistBins];
+    for (int b = threadIdx.x; b < kHistBins; b += blockDim.x) sh[b] = 0;
+    __syncthreads();
     const double pivot = *pivot_ptr;
     const double scale = (pivot > 0.0 && isfinite(pivot)) ? (double)kHistBins / pivot : 0.0;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count;
@@ -299,8 +371,11 @@ __global__ void hist_kernel(const Cand* __restrict__ cand, long long count, cons
         const double u = key_to_u(cand[i].key);
         long long b = (long long)(u * scale);
         if (b > kHistBins - 1) b = kHistBins - 1;
-        atomicAdd(&hist[b], 1u);
+        atomicAdd(&sh[b], 1u);
     }
+    __syncthreads();
+    for (int b = threadIdx.x; b < kHistBins; b += blockDim.x)
+        if (sh[b]) atomicAdd(&hist[b], sh[b]);
 }
 // smallest bin b* with cumulative count >= target; out[0] = b*, out[1] = cumulative count through b*
 __global__ void __launch_bounds__(1024)
@@ -426,10 +501,11 @@ __device__ __forceinline__ double gpd_b(long long j /*0-based*/, long long m, do
     b += 1.0 / x_max;                               // psis.py:277/280
     return b;
 }
-// one CTA per quadrature point: ks[j] = mean_r log1p(-b_j x_r), L[j] = n (log(-(b/ks)) - ks - 1)
+// kGpdSplit CTAs per quadrature point: parts[j][split] = partial sum_r log1p(-b_j x_r)
+// (a single CTA per point leaves the GPU at ~11 warps/SM: latency-bound, 75 us at n2 = 33 541)
+constexpr int kGpdSplit = 8;
 __global__ void __launch_bounds__(256)
-gpd_profile_kernel(const double* __restrict__ x, const long long* __restrict__ counts,
-                   double* __restrict__ bs, double* __restrict__ L) {
+gpd_profile_kernel(const double* __restrict__ x, const long long* __restrict__ counts, double* __restrict__ parts) {
     __shared__ double scratch[32];
     const long long n = counts[0], m = counts[2];
     const long long j = blockIdx.x;
@@ -438,27 +514,38 @@ gpd_profile_kernel(const double* __restrict__ x, const long long* __restrict__ c
     const double x_max = x[n - 1];
     const double b = gpd_b(j, m, x_q, x_max);
     double s = 0.0;
-    for (long long r = threadIdx.x; r < n; r += blockDim.x) s += log1p(-b * x[r]);
+    for (long long r = (long long)blockIdx.y * blockDim.x + threadIdx.x; r < n; r += (long long)kGpdSplit * blockDim.x)
+        s += log1p(-b * x[r]);
     s = block_sum(s, scratch);
-    if (threadIdx.x == 0) {
+    if (threadIdx.x == 0) parts[j * kGpdSplit + blockIdx.y] = s;
+}
+// single CTA: profile log-likelihood L_j = n (log(-(b_j/ks_j)) - ks_j - 1), quadrature weights
+// w_j = 1 / sum_i exp(L_i - L_j) (one warp per j), posterior mean of b (psis.py:287-308)
+__global__ void __launch_bounds__(1024)
+gpd_weights_kernel(const double* __restrict__ x, const long long* __restrict__ counts, const double* __restrict__ parts,
+                   double* __restrict__ bs, double* __restrict__ L, double* __restrict__ w_scratch,
+                   double* __restrict__ state) {
+    __shared__ double scratch[32];
+    const long long n = counts[0], m = counts[2];
+    if (counts[3] == 0) return;
+    const double x_q = x[(long long)((double)n / 4.0 + 0.5) - 1];
+    const double x_max = x[n - 1];
+    for (long long j = threadIdx.x; j < m; j += blockDim.x) {
+        double s = 0.0;
+        for (int k = 0; k < kGpdSplit; ++k) s += parts[j * kGpdSplit + k];      // fixed order
         const double ks = s / (double)n;
+        const double b = gpd_b(j, m, x_q, x_max);
         bs[j] = b;
         L[j] = (double)n * (log(-(b / ks)) - ks - 1.0);
     }
-}
-// single CTA: quadrature weights, posterior mean of b (psis.py:294-308)
-__global__ void __launch_bounds__(1024)
-gpd_weights_kernel(const long long* __restrict__ counts, const double* __restrict__ bs, const double* __restrict__ L,
-                   double* __restrict__ w_scratch, double* __restrict__ state) {
-    __shared__ double scratch[32];
-    const long long m = counts[2];
-    if (counts[3] == 0) return;
-    // w_j = 1 / sum_i exp(L_i - L_j)
-    for (long long j = threadIdx.x; j < m; j += blockDim.x) {
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    for (long long j = warp; j < m; j += nw) {
         double s = 0.0;
         const double Lj = L[j];
-        for (long long i = 0; i < m; ++i) s += exp(L[i] - Lj);
-        w_scratch[j] = 1.0 / s;
+        for (long long i = lane; i < m; i += 32) s += exp(L[i] - Lj);
+        s = warp_sum(s);
+        if (lane == 0) w_scratch[j] = 1.0 / s;
     }
     __syncthreads();
     double sw = 0.0, sbw = 0.0;
@@ -636,9 +723,10 @@ static long long psis_K1(long long n, double reff) {
 static int run_gpd_fit(const double* x2, const long long* counts, long long n2_upper, double* bs, double* Lq,
                        double* wq, double* blk, int g_small, double* state, cudaStream_t st) {
     const long long m_max = 30 + (long long)sqrt((double)n2_upper) + 1;
-    gpd_profile_kernel<<<(unsigned)m_max, 256, 0, st>>>(x2, counts, bs, Lq);
+    double* parts = Lq + m_max;                     // the L region holds L[m_max] then parts[m_max][kGpdSplit]
+    gpd_profile_kernel<<<dim3((unsigned)m_max, kGpdSplit), 256, 0, st>>>(x2, counts, parts);
     VB_LAUNCH_CHECK();
-    gpd_weights_kernel<<<1, 1024, 0, st>>>(counts, bs, Lq, wq, state);
+    gpd_weights_kernel<<<1, 1024, 0, st>>>(x2, counts, parts, bs, Lq, wq, state);
     VB_LAUNCH_CHECK();
     gpd_k_blocks_kernel<<<g_small, 256, 0, st>>>(x2, counts, state, blk);
     VB_LAUNCH_CHECK();
@@ -689,15 +777,25 @@ extern "C" int vb_psis_pivot(void* d_sample, long long count, long long capacity
         (capacity & (capacity - 1)))
         return VB_ERR_ARG;
     cudaStream_t st = (cudaStream_t)stream;
+    const long long rank = (long long)ceil(frac * (double)count);
+    if (rank >= count) {
+        set_double_kernel<<<1, 1, 0, st>>>(d_out_pivot_x, -INFINITY);
+        VB_LAUNCH_CHECK();
+        return VB_OK;
+    }
+    if (count <= 16 * kSampleSize) {                // 8 counting passes in one CTA beat a full sort here
+        radix_select_kernel<<<1, 1024, 0, st>>>((const Cand*)d_sample, (int)count, (int)rank, d_out_pivot_x);
+        VB_LAUNCH_CHECK();
+        return VB_OK;
+    }
     if (capacity > count) {
         pad_low_kernel<<<grid_for(capacity - count, 256, kNumSMs), 256, 0, st>>>((Cand*)d_sample, count, capacity);
         VB_LAUNCH_CHECK();
     }
     int rc = bitonic_sort((Cand*)d_sample, capacity, st);
     if (rc != VB_OK) return rc;
-    long long rank = (long long)ceil(frac * (double)count);
     // pads (key 0) sort first, so ranks counted from the top are unaffected
-    pivot_kernel<<<1, 1, 0, st>>>((const Cand*)d_sample, capacity, rank >= count ? capacity : rank, d_out_pivot_x);
+    pivot_kernel<<<1, 1, 0, st>>>((const Cand*)d_sample, capacity, rank, d_out_pivot_x);
     VB_LAUNCH_CHECK();
     return VB_OK;
 }
@@ -771,7 +869,7 @@ static int refine_to(const Cand* in, long long count, const double* d_M, const d
     VB_LAUNCH_CHECK();
     VB_CUDA_TRY(cudaMemsetAsync(r.hist, 0, (size_t)kHistBins * 4, st));
     VB_CUDA_TRY(cudaMemsetAsync(d_out_count, 0, 8, st));
-    hist_kernel<<<grid_for(count, 256, kNumSMs * 4), 256, 0, st>>>(in, count, r.pivot_u, r.hist);
+    hist_kernel<<<grid_for(count, 512 * 8, kNumSMs), 512, 0, st>>>(in, count, r.pivot_u, r.hist);
     VB_LAUNCH_CHECK();
     hist_scan_kernel<<<1, 1024, 0, st>>>(r.hist, keep, r.counts2);
     VB_LAUNCH_CHECK();
@@ -826,7 +924,7 @@ static TailLayout tail_layout(long long count, long long K1) {
     L.off_tailnew = take((size_t)(K1 + 1) * 8);
     const long long m_max = 30 + (long long)sqrt((double)(K1 + 1)) + 1;
     L.off_bs = take((size_t)m_max * 8);
-    L.off_L = take((size_t)m_max * 8);
+    L.off_L = take((size_t)m_max * 8 * (1 + kGpdSplit));
     L.off_w = take((size_t)m_max * 8);
     L.off_blk3 = take((size_t)kSmallGrid * 8);
     L.off_blk4 = take((size_t)kSmallGrid * 8);
@@ -988,13 +1086,9 @@ extern "C" int vb_psis_smooth(const double* d_lw_in, double* d_lw_out, long long
         if (direct) {
             set_double_kernel<<<1, 1, 0, st>>>(pivot_x, -INFINITY);
             VB_LAUNCH_CHECK();
-        } else if (attempt == 0) {
+        } else {
             rc = vb_psis_pivot(sample, kSampleSize, kSampleSize, frac, pivot_x, stream);
             if (rc != VB_OK) return rc;
-        } else {                                                       // the sample is already sorted
-            const long long rank = (long long)ceil(frac * kSampleSize);
-            pivot_kernel<<<1, 1, 0, st>>>(sample, kSampleSize, rank, pivot_x);
-            VB_LAUNCH_CHECK();
         }
         rc = vb_psis_filter(d_lw_in, n, 0, pivot_x, cand1, L.cap1, count, body_max, ws + L.off_filter,
                             vb_psis_filter_workspace_bytes(n), stream);
@@ -1023,7 +1117,7 @@ extern "C" int vb_psis_smooth(const double* d_lw_in, double* d_lw_out, long long
 extern "C" size_t vb_gpd_fit_workspace_bytes(long long n) {
     if (n < 2) return 0;
     const long long m_max = 30 + (long long)sqrt((double)n) + 1;
-    return 256 + 256 + 3 * align_up((size_t)m_max * 8, 256) + align_up((size_t)kNumSMs * 2 * 8, 256);
+    return 256 + 256 + (3 + kGpdSplit) * align_up((size_t)m_max * 8, 256) + align_up((size_t)kNumSMs * 2 * 8, 256);
 }
 
 extern "C" int vb_gpd_fit(const double* d_x_sorted, long long n, double* d_out_k_sigma,
@@ -1038,8 +1132,8 @@ extern "C" int vb_gpd_fit(const double* d_x_sorted, long long n, double* d_out_k
     long long* counts = (long long*)(ws + 256);
     double* bs = (double*)(ws + 512);
     double* Lq = (double*)(ws + 512 + mb);
-    double* wq = (double*)(ws + 512 + 2 * mb);
-    double* blk = (double*)(ws + 512 + 3 * mb);
+    double* wq = (double*)(ws + 512 + (2 + kGpdSplit) * mb);
+    double* blk = (double*)(ws + 512 + (3 + kGpdSplit) * mb);
     // gpdfitnew itself has no n <= 4 shortcut (that lives in psislw): always fit
     set_counts_kernel<<<1, 1, 0, st>>>(counts, n, 0, 30 + (long long)sqrt((double)n), 1);
     VB_LAUNCH_CHECK();

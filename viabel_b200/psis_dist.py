@@ -161,9 +161,7 @@ def psislw_sharded(lw_local, Reff=1.0, group=None, stages=None, want_detail=Fals
     frac = max(0.01, 4.0 * (K1 + 1) / n)
     for attempt in range(10):
         if not direct:
-            # first call pads [count, capacity) and sorts; later calls see a full, sorted buffer whose
-            # pads (smallest keys) sit at the bottom and do not disturb ranks counted from the top
-            st.pivot(sample_all, world * SAMPLE if attempt == 0 else sample_all.shape[0], frac, pivot)
+            st.pivot(sample_all.clone(), world * SAMPLE, frac, pivot)    # the stage may sort / pad its input
         cand, count_t, body_max = st.filter(lw_local, index0, pivot, cap)
         count = int(count_t.item())
         tot = comm.all_reduce_sum(torch.tensor([count, 1 if count > cap else 0], dtype=torch.int64, device=dev))
