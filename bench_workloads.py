@@ -244,8 +244,6 @@ class C5(Workload):
         import viabel_b200
         from viabel_b200 import psis, _lib
         from viabel_b200._device import ptr
-        if self.world > 1:
-            raise NotImplementedError('c5 across ranks needs the distributed PSIS exchange (next round)')
         self.torch, self.psis, self.vb, self.lib = torch, psis, viabel_b200, _lib
         g = torch.Generator(device='cuda')
         g.manual_seed(7 + self.rank)
@@ -263,18 +261,22 @@ class C5(Workload):
         self._ws = torch.zeros(nb, dtype=torch.uint8, device='cuda')
         self._ptr = ptr
 
+    @property
+    def _group(self):
+        return True if self.world > 1 else None
+
     def _bounds(self, lw):
-        return self.vb.all_bounds(lw, moment_bound_fn=lambda p: 3.0 if p == 2 else 27.0, q_var=1.0)
+        return self.vb.all_bounds(lw, moment_bound_fn=lambda p: 3.0 if p == 2 else 27.0, q_var=1.0, group=self._group)
 
     def step_device(self):
-        out, k = self.psis.psislw(self.lw)
+        out, k = self.psis.psislw(self.lw, group=self._group)
         res = self._bounds(self.lw)
         return k, res
 
     def step_e2e(self):
         if self.lw_host is None:
             self.lw_host = self.lw.cpu().numpy()
-        out, k = self.psis.psislw(self.lw_host)
+        out, k = self.psis.psislw(self.lw_host, group=self._group)
         res = self._bounds(self.lw_host)
         return k, res
 

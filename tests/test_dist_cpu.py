@@ -145,3 +145,46 @@ def test_two_rank_gloo_merge_equals_unsharded():
     np.testing.assert_allclose(sw / cnt, np.mean(np.exp(2.0 * (lw - lw.max()))), rtol=1e-13)
     np.testing.assert_allclose(mean, lw.mean(), rtol=1e-13)
     np.testing.assert_allclose(np.sqrt(M2 / cnt), lw.std(), rtol=1e-12)
+
+
+# ------------------------------------------------------------------------------------------ sharded PSIS protocol
+def _psis_worker(rank, world, port, n, ret):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        from viabel_b200 import psis_dist, vb
+        from psis_stages_np import NumpyStages
+        u = np.random.RandomState(9).rand(n)
+        lw = np.log(np.expm1(-0.5 * np.log1p(-u)) / 0.5)
+        start, count = vb._shard(n, rank, world)
+        mine = torch.from_numpy(lw[start:start + count].copy())
+        out, k, det = psis_dist.psislw_sharded(mine, stages=NumpyStages(), want_detail=True)
+        ret[rank] = (out.numpy(), k, det['tail_idx_sorted'], det['n2'])
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize('n', [5000, 300000])
+def test_two_rank_gloo_sharded_psis_equals_unsharded(n):
+    """The exchange protocol of viabel_b200/psis_dist.py over real gloo collectives (stages restated in
+    numpy): both sides of the direct threshold; tail order exact, weights to summation order."""
+    import warnings
+    from oracle import psis_np
+    sys_path_tests = os.path.dirname(os.path.abspath(__file__))
+    os.environ['PYTHONPATH'] = sys_path_tests + os.pathsep + os.environ.get('PYTHONPATH', '')
+    world, port = 2, _free_port()
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_psis_worker, args=(world, port, n, ret), nprocs=world, join=True)
+    u = np.random.RandomState(9).rand(n)
+    lw = np.log(np.expm1(-0.5 * np.log1p(-u)) / 0.5)
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        oout, ok, odet = psis_np.psislw_detail(lw, sort_kind='stable')
+    out = np.concatenate([ret[0][0], ret[1][0]])
+    for r in range(world):
+        assert ret[r][3] == odet['n2']
+        np.testing.assert_array_equal(ret[r][2], odet['tailinds'][odet['tail_order']])
+        np.testing.assert_allclose(ret[r][1], ok, rtol=1e-10)
+    np.testing.assert_allclose(out, oout, rtol=1e-10, atol=1e-10)

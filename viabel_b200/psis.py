@@ -29,8 +29,12 @@ def _smooth_1d(col, Reff, want_tail=False):
     return out, diag.cpu().numpy(), tail
 
 
-def psislw(lw, Reff=1.0, overwrite_lw=False):
+def psislw(lw, Reff=1.0, overwrite_lw=False, group=None):
     """Pareto smoothed importance sampling (``psis.py:112-208``).
+
+    ``group``: torch.distributed group (or ``True`` for the world group) over which a 1-D ``lw`` is
+    sharded by contiguous index ranges; every rank passes its slice and gets its slice back, k-hat is
+    the global one (``viabel_b200/psis_dist.py``).  Default: not sharded.
 
     ``lw``: (n,) or (n, m) log weights, numpy or CUDA tensor.  Returns ``(lw_out, kss)`` with
     ``kss`` a float for 1-D input and an (m,) numpy array otherwise.  ``overwrite_lw`` smooths
@@ -41,11 +45,17 @@ def psislw(lw, Reff=1.0, overwrite_lw=False):
         n, m = len(lw), 1
     else:
         raise ValueError("Argument `lw` must be 1 or 2 dimensional.")
-    if n <= 1:
+    sharded = group is not None and group is not False
+    if n <= 1 and not sharded:                           # a shard may hold one weight; the global check is in psis_dist
         raise ValueError("More than one log-weight needed.")
     dev = to_dev(lw, _lib.F64)
     kss = np.empty(m)
-    if lw.ndim == 1:
+    if sharded:
+        if lw.ndim != 1:
+            raise ValueError('sharded psislw takes one weight column')
+        from .psis_dist import psislw_sharded
+        out, kss = psislw_sharded(dev.contiguous(), Reff, group=None if group is True else group)
+    elif lw.ndim == 1:
         out, diag, _ = _smooth_1d(dev.contiguous(), Reff)
         kss = diag[0]
     else:
