@@ -467,9 +467,9 @@ class C2(Workload):
     """Student-t robust regression N = 2^20 rows, d = 128; KLVI, mean-field Student-t (df 40), 4096 samples/step."""
     name = 'c2'
     n, N, d = 4096, 1 << 20, 128
-    dtype = 'f64'
-    compute = 'f64'
-    default_steps, default_warmup = 3, 3
+    dtype = 'f32 storage, 3xTF32 tensor-core products, fp64 accumulation across row chunks'
+    compute = 'f32'
+    default_steps, default_warmup = 5, 3
     cpu_rows = 1 << 16
 
     def setup(self):
@@ -485,7 +485,7 @@ class C2(Workload):
         self.lam_dev = torch.from_numpy(lam).cuda()
         self.units_per_step = self.n
         self.h2d_bytes, self.d2h_bytes = lam.nbytes, 8 * (1 + lam.size)
-        self.launches_per_step = 3 * 32 + 8
+        self.launches_per_step = 4 * ((self.N + 8191) // 8192) + 10
         self._x = torch.from_numpy(np.tile(lam[:self.d], (self.n, 1))).cuda()
         if self.compute == 'f32':
             self._x = self._x.float()
@@ -551,4 +551,15 @@ class C2(Workload):
                 'e2e': {'value': rate, 'unit': self.unit, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
 
 
-WORKLOADS.update({'c2': C2, 'c3': C3, 'c3chol': C3Chol})
+class C2F64(C2):
+    """Same as c2 in full fp64 (SIMT DFMA path): the parity instrument, not the throughput path."""
+    name = 'c2f64'
+    dtype = 'f64'
+    compute = 'f64'
+    default_steps, default_warmup = 2, 3
+
+    def config_name(self):
+        return C2.config_name(self) + ' [fp64 SIMT parity path]'
+
+
+WORKLOADS.update({'c2': C2, 'c2f64': C2F64, 'c3': C3, 'c3chol': C3Chol})

@@ -71,6 +71,43 @@ def test_regression_plugin(N, d, n):
     assert rel(lp, olp) < 1e-12 and rel(g, og) < 1e-11
 
 
+@pytest.mark.parametrize('N,d,n', [(300, 8, 40), (5000, 32, 129), (40000, 128, 512), (70001, 64, 300)])
+def test_regression_plugin_tensor_path(N, d, n):
+    """fp32 storage: both design-matrix products on tcgen05 (3xTF32), fused residual / psi epilogue,
+    fp64 accumulation across row chunks.  Stated tolerance: 1e-5 relative (gradient, log p)."""
+    from viabel_b200 import models
+    X, y, bt = _regression(N, d)
+    X32, y32 = X.astype(np.float32), y.astype(np.float32)
+    model = models.StudentTRegression(X32, y32, df=40.0, dtype='f32')
+    omodel = mm.StudentTRegression(X32.astype(np.float64), y32.astype(np.float64), 40.0)
+    b = (bt + 0.1 * np.random.RandomState(3).randn(n, d)).astype(np.float32)
+    lp, g = model.logp_and_grad(b, dtype='f32')
+    olp, og = omodel.logp_and_grad(b.astype(np.float64))
+    assert rel(lp, olp) < 1e-5, rel(lp, olp)
+    assert rel(g, og) < 1e-5, rel(g, og)
+    np.testing.assert_allclose(lp, olp, rtol=2e-5)
+    lp_only = model(b, dtype='f32')
+    np.testing.assert_allclose(lp_only, lp, rtol=1e-12)
+
+
+def test_mean_field_regression_tensor_path_klvi():
+    """Config-2 in miniature through the public objective with fp32 storage."""
+    from viabel_b200 import models, vb
+    N, d, n = 20000, 128, 256
+    X, y, bt = _regression(N, d)
+    X32, y32 = X.astype(np.float32), y.astype(np.float32)
+    model = models.StudentTRegression(X32, y32, df=40.0, dtype='f32')
+    omodel = mm.StudentTRegression(X32.astype(np.float64), y32.astype(np.float64), 40.0)
+    fam, ofam = vb.mean_field_t_variational_family(d, 40, dtype='f32'), vb_np.mean_field_t_variational_family(d, 40)
+    lam = np.concatenate([bt + 0.01 * np.random.RandomState(3).randn(d), np.full(d, np.log(1e-2))])
+    base = ofam.impl.draw_base(np.random.RandomState(9), n)
+    base32 = {'eps': base['eps'].astype(np.float32)}
+    v, g = vb.black_box_klvi(fam, model, n, group=False)(lam, base_draws=base32)
+    ov, og = vb_np.klvi_value_and_grad(ofam.impl, omodel, lam, {'eps': base32['eps'].astype(np.float64)})
+    np.testing.assert_allclose(v, ov, rtol=1e-6)
+    assert rel(g, og) < 2e-5, rel(g, og)
+
+
 @pytest.mark.parametrize('kind', ['gauss', 't'])
 def test_mean_field_with_regression_plugin(kind):
     """Config-2 shape in miniature: the unfused path sample -> plugin -> vb_mf_reduce."""

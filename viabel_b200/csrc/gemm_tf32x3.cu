@@ -2,6 +2,7 @@
 // entry (vb_gemm with dtype f32) and the fused pipelines built on the kernel in gemm_tf32x3.cuh.
 #include "gemm_tf32x3.cuh"
 #include "dense.cuh"
+#include "models.cuh"
 
 namespace vb {
 
@@ -71,13 +72,51 @@ __global__ void split_kernel(const float* __restrict__ src, long long rows, long
 static inline long long pad4(long long x) { return (x + 3) / 4 * 4; }
 
 // ------------------------------------------------------------------------------------------ plain GEMM epilogue
-struct AxpbyEpi {
-    float* c; long long ldc; float alpha, beta;
-    __device__ __forceinline__ void operator()(long long row, long long col0, float (&v)[32], int ncols, int) const {
-        float* p = c + row * ldc + col0;
+// 256-bit global accesses (sm_100: STG/LDG.E.ENL2.256); addresses 32-byte aligned.  Each thread of an
+// epilogue warp owns one row, so a warp-wide store touches 32 different lines: with 256-bit accesses
+// every request is at least a full 32-byte sector (scalar stores were the bottleneck of every epilogue).
+__device__ __forceinline__ void st_global_v8(float* dst, const float (&a)[8]) {
+    asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                 :: "l"(dst), "f"(a[0]), "f"(a[1]), "f"(a[2]), "f"(a[3]), "f"(a[4]), "f"(a[5]), "f"(a[6]), "f"(a[7])
+                 : "memory");
+}
+__device__ __forceinline__ void ld_global_v8(const float* src, float (&a)[8]) {
+    asm volatile("ld.global.nc.v8.f32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=f"(a[0]), "=f"(a[1]), "=f"(a[2]), "=f"(a[3]), "=f"(a[4]), "=f"(a[5]), "=f"(a[6]), "=f"(a[7])
+                 : "l"(src));
+}
+__device__ __forceinline__ bool aligned32(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 31u) == 0; }
+// p[0..ncols) = w[0..ncols): four 256-bit stores for a full, aligned block, scalar otherwise
+__device__ __forceinline__ void store_row32(float* p, const float (&w)[32], int ncols) {
+    if (ncols == 32 && aligned32(p)) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 8) {
+            const float t[8] = {w[j], w[j + 1], w[j + 2], w[j + 3], w[j + 4], w[j + 5], w[j + 6], w[j + 7]};
+            st_global_v8(p + j, t);
+        }
+    } else {
 #pragma unroll
         for (int j = 0; j < 32; ++j)
-            if (j < ncols) p[j] = alpha * v[j] + (beta == 0.f ? 0.f : beta * p[j]);
+            if (j < ncols) p[j] = w[j];
+    }
+}
+
+struct AxpbyEpi {
+    struct Pre {};
+    __device__ __forceinline__ Pre prefetch(long long, long long, int) const { return Pre{}; }
+    float* c; long long ldc; float alpha, beta;
+    __device__ __forceinline__ void operator()(long long row, long long col0, float (&v)[32], int ncols, int, const Pre&) const {
+        float* p = c + row * ldc + col0;
+        if (beta == 0.f) {
+            float w[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) w[j] = alpha * v[j];
+            store_row32(p, w, ncols);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (j < ncols) p[j] = alpha * v[j] + beta * p[j];
+        }
     }
 };
 
@@ -118,13 +157,16 @@ int gemm_tf32x3(int transa, int transb, long long m, long long n, long long k, f
 // ------------------------------------------------------------------------------------------ full-rank sample
 // x_i = mu + (z_i S) / sqrt(chi2_i / df)            (viabel/vb.py:204-208), S given as stored (k, n)
 struct FrSampleEpi {
+    struct Pre {};
+    __device__ __forceinline__ Pre prefetch(long long, long long, int) const { return Pre{}; }
     float* x; long long ld; const double* mu; const float* chi2; float df;
-    __device__ __forceinline__ void operator()(long long row, long long col0, float (&v)[32], int ncols, int) const {
+    __device__ __forceinline__ void operator()(long long row, long long col0, float (&v)[32], int ncols, int, const Pre&) const {
         const float s = rsqrtf(chi2[row] / df);
         float* p = x + row * ld + col0;
+        float w[32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
-            if (j < ncols) p[j] = (float)mu[col0 + j] + v[j] * s;
+        for (int j = 0; j < 32; ++j) w[j] = (j < ncols) ? (float)mu[col0 + j] + v[j] * s : 0.f;
+        store_row32(p, w, ncols);
     }
 };
 
@@ -173,17 +215,36 @@ __global__ void gauss_prep_kernel(const double* __restrict__ mean, const double*
 }
 struct GaussEpi {
     float* g; long long ld; const float* bias; const float* x; const double* mean; float* rowpart; int n_chunks;
-    __device__ __forceinline__ void operator()(long long row, long long col0, float (&v)[32], int ncols, int) const {
-        float* gp = g + row * ld + col0;
+    struct Pre { float x[32]; };
+    __device__ __forceinline__ Pre prefetch(long long row, long long col0, int ncols) const {
+        Pre p;
         const float* xp = x + row * ld + col0;
+        if (ncols == 32 && aligned32(xp)) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+                float t[8];
+                ld_global_v8(xp + j, t);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) p.x[j + q] = t[q];
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) p.x[j] = (j < ncols) ? xp[j] : 0.f;
+        }
+        return p;
+    }
+    __device__ __forceinline__ void operator()(long long row, long long col0, float (&v)[32], int ncols, int,
+                                               const Pre& pre) const {
+        float w[32];
         float dot = 0.f;
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
-            if (j < ncols) {
-                const float gv = bias[col0 + j] - v[j];
-                gp[j] = gv;
-                dot = fmaf(gv, xp[j] - (float)mean[col0 + j], dot);
-            }
+        for (int j = 0; j < 32; ++j) {
+            const bool ok = j < ncols;
+            const float gv = ok ? bias[col0 + j] - v[j] : 0.f;
+            w[j] = gv;
+            dot = fmaf(gv, ok ? pre.x[j] - (float)mean[col0 + j] : 0.f, dot);
+        }
+        store_row32(g + row * ld + col0, w, ncols);
         rowpart[row * n_chunks + (col0 >> 5)] = dot;
     }
 };
@@ -249,12 +310,11 @@ __global__ void split_rowscaled_kernel(const float* __restrict__ src, long long 
     }
 }
 struct SplitKEpi {
+    struct Pre {};
+    __device__ __forceinline__ Pre prefetch(long long, long long, int) const { return Pre{}; }
     float* parts; long long mn; long long ld;
-    __device__ __forceinline__ void operator()(long long row, long long col0, float (&v)[32], int ncols, int split) const {
-        float* p = parts + (size_t)split * mn + row * ld + col0;
-#pragma unroll
-        for (int j = 0; j < 32; ++j)
-            if (j < ncols) p[j] = v[j];
+    __device__ __forceinline__ void operator()(long long row, long long col0, float (&v)[32], int ncols, int split, const Pre&) const {
+        store_row32(parts + (size_t)split * mn + row * ld + col0, v, ncols);
     }
 };
 __global__ void splitk_sum_f64_kernel(const float* __restrict__ parts, int splits, long long mn, double* __restrict__ out) {
@@ -325,9 +385,192 @@ extern "C" int vb_gemm_tf32x3_split(int a_mn_major, int b_mn_major, long long m,
 }
 
 namespace vb {
-// ------------------------------------------------------------------------------------------ not yet on the tensor path
-size_t regression_tf32_workspace_bytes(long long, long long, int) { return 0; }
-int regression_logp_grad_tf32(const ModelHost*, const float*, long long, double*, float*, void*, size_t,
-                              cudaStream_t) { return VB_ERR_UNSUPPORTED; }
+// ------------------------------------------------------------------------------------------ Student-t regression
+// log p(b) = -|b|^2 / (2 sd^2) - (df+1)/2 sum_r log1p(r_r^2/df),  r = y - X b
+// grad     = -b / sd^2 + psi' X,  psi_r = (df+1) r_r / (df + r_r^2)                  
+// Batched over S samples and tiled over chunks of C design-matrix rows:
+//   GEMM1  acc (S x C) = B (S x d) X_chunk'  with the fused epilogue below: r, the log1p partial sums and
+//          psi written straight into split (hi, lo) planes -- the S x N residual matrix is never stored
+//   GEMM2  G (S x d) += Psi (S x C) X_chunk  (split-K over the chunk, partials summed into fp64)
+// The same split copy of X serves both products: K-major B operand in GEMM1, MN-major B operand in GEMM2.
+struct PsiEpi {
+    float* __restrict__ psi; long long ldp, plane;   // split planes of Psi, (S, C) with leading dimension ldp
+    const float* __restrict__ y;                     // y + r0
+    float* __restrict__ rowpart; int n_blocks;       // (S, C/32) partial sums of log1p(r^2/df)
+    float df, inv_df, dfp1;
+    struct Pre { float y[32]; };
+    __device__ __forceinline__ Pre prefetch(long long, long long col0, int ncols) const {
+        Pre p;
+        const float* yy = y + col0;
+        if (ncols == 32) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+                const float4 t = __ldg(reinterpret_cast<const float4*>(yy + j));
+                p.y[j] = t.x; p.y[j + 1] = t.y; p.y[j + 2] = t.z; p.y[j + 3] = t.w;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) p.y[j] = (j < ncols) ? __ldg(yy + j) : 0.f;
+        }
+        return p;
+    }
+    __device__ __forceinline__ void operator()(long long row, long long col0, float (&v)[32], int ncols, int,
+                                               const Pre& pre) const {
+        float* ph = psi + row * ldp + col0;
+        float* pl = ph + plane;
+        float acc = 0.f;
+        if (ncols == 32) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+                float hi[8], lo[8];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    const float r = pre.y[j + q] - v[j + q];
+                    const float r2 = r * r;
+                    acc += log1pf(r2 * inv_df);
+                    const float ps = dfp1 * r * __frcp_rn(df + r2);
+                    tc::split_tf32(ps, hi[q], lo[q]);
+                }
+                st_global_v8(ph + j, hi);          // one full 32-byte sector per request
+                st_global_v8(pl + j, lo);
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                if (j < ncols) {
+                    const float r = pre.y[j] - v[j];
+                    const float r2 = r * r;
+                    acc += log1pf(r2 * inv_df);
+                    float hi, lo;
+                    tc::split_tf32(dfp1 * r * __frcp_rn(df + r2), hi, lo);
+                    ph[j] = hi;
+                    pl[j] = lo;
+                }
+            }
+        }
+        rowpart[row * n_blocks + (col0 >> 5)] = acc;
+    }
+};
+// logp[s] -= (df+1)/2 * sum_blocks rowpart[s][.]   (fp64 accumulation across blocks and chunks)
+__global__ void reg_rowpart_acc_kernel(const float* __restrict__ rowpart, long long S, int n_blocks, int used_blocks,
+                                       double scale, double* __restrict__ logp) {
+    const int lane = threadIdx.x & 31;
+    const long long warp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long s = warp; s < S; s += nwarps) {
+        double a = 0.0;
+        for (int b = lane; b < used_blocks; b += 32) a += (double)rowpart[s * n_blocks + b];
+        a = warp_sum(a);
+        if (lane == 0) logp[s] -= scale * a;
+    }
+}
+// logp[s] = -|b_s|^2 / (2 sd^2);  gacc[s, j] = -b_sj / sd^2
+__global__ void reg_init_kernel(const float* __restrict__ b, long long S, int D, double inv_var,
+                                double* __restrict__ logp, double* __restrict__ gacc) {
+    const int lane = threadIdx.x & 31;
+    const long long warp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long s = warp; s < S; s += nwarps) {
+        double a = 0.0;
+        for (int j = lane; j < D; j += 32) {
+            const double v = (double)b[s * D + j];
+            a = fma(v, v, a);
+            gacc[s * D + j] = -v * inv_var;
+        }
+        a = warp_sum(a);
+        if (lane == 0) logp[s] = -0.5 * a * inv_var;
+    }
+}
+// gacc[e] += sum_k parts[k][e]
+__global__ void reg_parts_acc_kernel(const float* __restrict__ parts, int splits, long long mn, double* __restrict__ gacc) {
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < mn; e += (long long)gridDim.x * blockDim.x) {
+        double a = 0.0;
+        for (int k = 0; k < splits; ++k) a += (double)parts[(size_t)k * mn + e];
+        gacc[e] += a;
+    }
+}
+__global__ void reg_cast_kernel(const double* __restrict__ src, long long total, float* __restrict__ dst) {
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x)
+        dst[e] = (float)src[e];
+}
+
+static long long reg_chunk_rows(long long S, long long N) {
+    long long c = (1ll << 25) / (S > 0 ? S : 1);          // Psi planes <= 2 x 128 MiB
+    c = c / 128 * 128;
+    if (c < 128) c = 128;
+    if (c > 16384) c = 16384;
+    if (c > N) c = (N + 31) / 32 * 32;
+    return c;
+}
+struct RegLayout { long long C; int splits; size_t off_xs, off_bs, off_psi, off_rowpart, off_parts, off_gacc, total; };
+static RegLayout reg_layout(long long S, long long N, int D) {
+    RegLayout L;
+    L.C = reg_chunk_rows(S, N);
+    L.splits = plan_gemm(S, D, L.C, auto_splits(S, D, L.C)).splits;
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t at = o; o += (bytes + 255) & ~(size_t)255; return at; };
+    L.off_xs = take(split_bytes(N, D));
+    L.off_bs = take(split_bytes(S, D));
+    L.off_psi = take((size_t)2 * S * L.C * 4);
+    L.off_rowpart = take((size_t)S * (L.C / 32 + 1) * 4);
+    L.off_parts = take((size_t)L.splits * S * D * 4);
+    L.off_gacc = take((size_t)S * D * 8);
+    L.total = o;
+    return L;
+}
+
+size_t regression_tf32_workspace_bytes(long long n, long long n_rows, int dim) {
+    return reg_layout(n, n_rows, dim).total + 512;
+}
+
+int regression_logp_grad_tf32(const ModelHost* m, const float* b, long long S, double* out_logp,
+                              float* out_grad_or_null, void* ws, size_t ws_bytes, cudaStream_t st) {
+    const int D = m->dim;
+    const long long N = m->n_rows;
+    if (D % 4) return VB_ERR_ALIGN;                       // TMA rows must be 16-byte multiples
+    const RegLayout L = reg_layout(S, N, D);
+    if (!ws || ws_bytes < L.total + 512) return VB_ERR_WORKSPACE;
+    char* w = (char*)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
+    float* psi = (float*)(w + L.off_psi);
+    float* rowpart = (float*)(w + L.off_rowpart);
+    float* parts = (float*)(w + L.off_parts);
+    double* gacc = (double*)(w + L.off_gacc);
+    const float* X = (const float*)m->d_X;
+    const float* y = (const float*)m->d_y;
+    SplitMat xs, bs;
+    int rc = split_into(X, N, D, D, (float*)(w + L.off_xs), st, &xs);
+    if (rc != VB_OK) return rc;
+    rc = split_into(b, S, D, D, (float*)(w + L.off_bs), st, &bs);
+    if (rc != VB_OK) return rc;
+    const double inv_var = 1.0 / (m->prior_sd * m->prior_sd);
+    reg_init_kernel<<<grid_for(S * 32, 256, kNumSMs * 8), 256, 0, st>>>(b, S, D, inv_var, out_logp, gacc);
+    VB_LAUNCH_CHECK();
+    const int n_blocks = (int)(L.C / 32 + 1);
+    const long long mn = S * D;
+    for (long long r0 = 0; r0 < N; r0 += L.C) {
+        const long long cols = (r0 + L.C <= N) ? L.C : (N - r0);
+        const SplitMat xc{xs.base + r0 * xs.ld, cols, D, xs.ld, xs.plane_stride};
+        // GEMM1 + fused elementwise epilogue
+        PsiEpi e1{psi, L.C, S * L.C, y + r0, rowpart, n_blocks, (float)m->df, (float)(1.0 / m->df), (float)(m->df + 1.0)};
+        rc = launch_tf32x3<false, false, PsiEpi, 16>(bs, xc, plan_gemm(S, cols, D, 1), e1, st);
+        if (rc != VB_OK) return rc;
+        reg_rowpart_acc_kernel<<<grid_for(S * 32, 256, kNumSMs * 8), 256, 0, st>>>(
+            rowpart, S, n_blocks, (int)((cols + 31) / 32), 0.5 * (m->df + 1.0), out_logp);
+        VB_LAUNCH_CHECK();
+        if (out_grad_or_null) {
+            const SplitMat ps{psi, S, cols, L.C, S * L.C};
+            const GemmShape shape = plan_gemm(S, D, cols, auto_splits(S, D, cols));
+            rc = launch_tf32x3<false, true>(ps, xc, shape, SplitKEpi{parts, mn, D}, st);
+            if (rc != VB_OK) return rc;
+            reg_parts_acc_kernel<<<grid_for(mn, 256, kNumSMs * 4), 256, 0, st>>>(parts, shape.splits, mn, gacc);
+            VB_LAUNCH_CHECK();
+        }
+    }
+    if (out_grad_or_null) {
+        reg_cast_kernel<<<grid_for(mn, 256, kNumSMs * 4), 256, 0, st>>>(gacc, mn, out_grad_or_null);
+        VB_LAUNCH_CHECK();
+    }
+    return VB_OK;
+}
 
 }  // namespace vb

@@ -47,8 +47,11 @@ struct OperandLayout {
     static constexpr uint32_t k_step = MN_MAJOR ? 1024u : 32u;     // per UMMA_K = 8 fp32
 };
 
-template <bool A_MN, bool B_MN, class Epi>
-__global__ void __launch_bounds__(kTThreads, 1)
+// EW = number of epilogue warps (4, 8 or 16): warp (q, h) drains TMEM lane quarter q = warp % 4 and the
+// column blocks h, h + EW/4, ... of the 128-column accumulator.  Heavy epilogues (transcendentals per
+// element) need 16 warps to hide their latency; a plain store is fine with 4.
+template <bool A_MN, bool B_MN, class Epi, int EW = 4>
+__global__ void __launch_bounds__(64 + 32 * EW, 1)
 gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                    const GemmShape shape, const Epi epi) {
     extern __shared__ unsigned char smem_dyn[];
@@ -72,7 +75,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
 #pragma unroll
         for (int s = 0; s < kTStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
         mbar_init(&tmem_full[0], 1); mbar_init(&tmem_full[1], 1);
-        mbar_init(&tmem_empty[0], 128); mbar_init(&tmem_empty[1], 128);
+        mbar_init(&tmem_empty[0], 32 * EW); mbar_init(&tmem_empty[1], 32 * EW);
         mbar_fence_init();
     }
     if (warp == 1) tc::tmem_alloc<256>(tmem_ptr);      // 2 accumulator stages x 128 columns
@@ -162,6 +165,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     } else {
         // ===================================================== epilogue (warps 2..5)
         const int q = warp & 3;                      // TMEM lane quarter this warp may access
+        const int h = (warp - 2) >> 2;               // which column blocks of the quarter this warp takes
         int it = 0;
         for (long long w = blockIdx.x; w < total; w += gridDim.x, ++it) {
             const long long tile = w % (m_tiles * n_tiles);
@@ -172,13 +176,17 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
             tc::fence_after_sync();
             const long long row = m0 + q * 32 + lane;
 #pragma unroll 1
-            for (int c = 0; c < kTBN / 32; ++c) {
-                float v[32];
-                tc::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * kTBN + c * 32), v);
+            for (int c = h; c < kTBN / 32; c += EW / 4) {
                 const long long col0 = n0 + c * 32;
                 long long ncols = shape.N - col0;
                 if (ncols > 32) ncols = 32;
-                if (row < shape.M && ncols > 0) epi(row, col0, v, (int)ncols, split);
+                const bool live = row < shape.M && ncols > 0;
+                // operands the epilogue needs from global memory are requested before the TMEM read
+                typename Epi::Pre pre;
+                if (live) pre = epi.prefetch(row, col0, (int)ncols);
+                float v[32];
+                tc::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * kTBN + c * 32), v);
+                if (live) epi(row, col0, v, (int)ncols, split, pre);
             }
             tc::fence_before_sync();
             mbar_arrive(&tmem_empty[as]);
@@ -212,7 +220,7 @@ inline int auto_splits(long long M, long long N, long long K) {
 
 int tf32x3_num_sms();
 
-template <bool A_MN, bool B_MN, class Epi>
+template <bool A_MN, bool B_MN, class Epi, int EW = 4>
 static int launch_tf32x3(const SplitMat& A, const SplitMat& B, const GemmShape& shape, const Epi& epi,
                          cudaStream_t st) {
     CUtensorMap ta, tb;
@@ -220,7 +228,7 @@ static int launch_tf32x3(const SplitMat& A, const SplitMat& B, const GemmShape& 
     if (rc != VB_OK) return rc;
     rc = make_split_tmap(&tb, B.base, B.rows, B.cols, B.ld, B.plane_stride, B_MN ? kTBK : kTBN, B_MN);
     if (rc != VB_OK) return rc;
-    auto kern = gemm_tf32x3_kernel<A_MN, B_MN, Epi>;
+    auto kern = gemm_tf32x3_kernel<A_MN, B_MN, Epi, EW>;
     static bool configured = false;
     if (!configured) {
         VB_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTSmemBytes));
@@ -229,7 +237,7 @@ static int launch_tf32x3(const SplitMat& A, const SplitMat& B, const GemmShape& 
     const long long total = ((shape.M + kTBM - 1) / kTBM) * ((shape.N + kTBN - 1) / kTBN) * shape.splits;
     long long grid = tf32x3_num_sms();
     if (grid > total) grid = total;
-    kern<<<(unsigned)grid, kTThreads, kTSmemBytes, st>>>(ta, tb, shape, epi);
+    kern<<<(unsigned)grid, 64 + 32 * EW, kTSmemBytes, st>>>(ta, tb, shape, epi);
     VB_LAUNCH_CHECK();
     return VB_OK;
 }
