@@ -1,5 +1,6 @@
 // Host side of the 3xTF32 tcgen05 path: tensor-map creation, operand splitting, the plain GEMM
 // entry (vb_gemm with dtype f32) and the fused pipelines built on the kernel in gemm_tf32x3.cuh.
+#include <cstdlib>
 #include "gemm_tf32x3.cuh"
 #include "dense.cuh"
 #include "models.cuh"
@@ -495,10 +496,18 @@ __global__ void reg_cast_kernel(const double* __restrict__ src, long long total,
 }
 
 static long long reg_chunk_rows(long long S, long long N) {
-    long long c = (1ll << 25) / (S > 0 ? S : 1);          // Psi planes <= 2 x 128 MiB
+    // Psi planes of 2 x 256 MiB per chunk: larger chunks amortise the per-launch host work (two tensor-map
+    // encodes per GEMM), smaller ones would keep Psi in L2 but leave the GPU waiting for launches
+    // (measured at S = 4096: 33 ms with 2048-row chunks, 24.0 with 8192, 22.7 with 16384).  VB_REG_CHUNK overrides (tuning).
+    static long long forced = -1;
+    if (forced < 0) {
+        const char* e = getenv("VB_REG_CHUNK");
+        forced = e ? atoll(e) : 0;
+    }
+    long long c = forced > 0 ? forced : (1ll << 26) / (S > 0 ? S : 1);
     c = c / 128 * 128;
     if (c < 128) c = 128;
-    if (c > 16384) c = 16384;
+    if (c > 32768) c = 32768;
     if (c > N) c = (N + 31) / 32 * 32;
     return c;
 }
