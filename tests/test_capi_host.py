@@ -92,7 +92,7 @@ def test_python_surface_matches_reference_signatures():
                                                    ('return_log_norm_bound', False)]
     assert params(bounds.wasserstein_bounds)[:3] == [('d2', E), ('samples', None), ('moment_bound_fn', None)]
     assert params(bounds.error_bounds) == [('W1', np.inf), ('W2', np.inf), ('q_var', np.inf), ('p_var', np.inf)]
-    assert params(psis.psislw) == [('lw', E), ('Reff', 1.0), ('overwrite_lw', False)]
+    assert params(psis.psislw)[:3] == [('lw', E), ('Reff', 1.0), ('overwrite_lw', False)]      # + group=None
     assert params(vb.adagrad_optimize) == [('n_iters', E), ('objective_and_grad', E), ('init_param', E),
                                            ('has_log_norm', False), ('window', 10), ('learning_rate', .01),
                                            ('epsilon', .1), ('learning_rate_end', None)]
@@ -174,3 +174,14 @@ def test_bounds_and_psis_argument_errors_without_gpu():
     assert res == {'mean_error': 1.0, 'std_error': 2.0, 'cov_error': 2 * (3.0 * 2.0 + 4.0)}
     res = bounds.wasserstein_bounds(0.5, moment_bound_fn=lambda p: 2.0 ** p)
     np.testing.assert_allclose(res['W1'], 2 * 2.0 * np.sqrt(np.expm1(0.5)))
+
+
+def test_torch_custom_ops_registered_cuda_only():
+    """torch.ops.viabel_b200.* exist and have no CPU kernel (no CPU fallback)."""
+    import torch
+    import viabel_b200
+    from viabel_b200 import _ops
+    for name in _ops.OPS:
+        assert hasattr(torch.ops.viabel_b200, name)
+    with pytest.raises((NotImplementedError, RuntimeError)):
+        torch.ops.viabel_b200.logsumexp(torch.zeros(4, dtype=torch.float64))

@@ -193,3 +193,32 @@ def test_funnel_adagrad_config1_runs_and_improves():
                                  moment_bound_fn=lambda p: fam.pth_moment(p, opt))
     assert set(res) == {'W1', 'W2', 'mean_error', 'std_error', 'cov_error', 'd2', 'log_norm_bound'}
     assert np.isfinite(res['d2'])
+
+
+def test_torch_custom_ops_match_python_surface():
+    """torch.ops.viabel_b200.* forward to the same C ABI as the Python closures."""
+    import torch
+    from viabel_b200 import models, vb, psis, _lib
+    d = 10
+    rs = np.random.RandomState(0)
+    lam = np.concatenate([rs.randn(d) * 0.3, np.full(d, -0.1)])
+    fam = vb.mean_field_t_variational_family(d, 40)
+    model = models.EightSchoolsNCP()
+    base = rs.standard_t(40, (2048, d))
+    v, g = vb.black_box_klvi(fam, model, 2048, group=False)(lam, base_draws=base)
+    out, partials = torch.ops.viabel_b200.mf_step(_lib.FAMILY_MF_T, 40.0, model.handle.value, _lib.OBJ_KLVI, 1.0,
+                                                  torch.from_numpy(lam).cuda(), 2048, torch.from_numpy(base).cuda(),
+                                                  0, 0, 0)
+    np.testing.assert_allclose(out[0].item(), v, rtol=1e-14)
+    np.testing.assert_allclose(out[1:].cpu().numpy(), g, rtol=1e-14)
+    fin = torch.ops.viabel_b200.mf_finalize(_lib.FAMILY_MF_T, _lib.OBJ_KLVI, 1.0, torch.from_numpy(lam).cuda(), partials)
+    np.testing.assert_allclose(fin.cpu().numpy(), out.cpu().numpy(), rtol=1e-13)
+    lw = torch.from_numpy(np.log(rs.rand(50000))).cuda()
+    o, diag = torch.ops.viabel_b200.psis_smooth(lw, 1.0)
+    o2, k2 = psis.psislw(lw)
+    assert torch.equal(o, o2) and diag[0].item() == k2
+    np.testing.assert_allclose(torch.ops.viabel_b200.logsumexp(lw).item(), psis.sumlogs(lw.cpu().numpy()), rtol=1e-13)
+    a, b = torch.randn(300, 200, device='cuda'), torch.randn(200, 100, device='cuda')
+    c = torch.ops.viabel_b200.gemm_tf32x3(a, b)
+    ref = a.double() @ b.double()
+    assert ((c.double() - ref).norm() / ref.norm()).item() < 1e-6

@@ -10,3 +10,4 @@ from .bounds import *          # noqa: F401,F403
 from . import bounds, models, psis, vb   # noqa: F401
 
 __version__ = '0.1.0'
+from . import _ops             # noqa: F401,E402  (registers torch.ops.viabel_b200.*)
