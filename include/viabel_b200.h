@@ -141,6 +141,23 @@ int vb_mf_reduce(int family, double df, int objective, double alpha, int dtype,
                  double* d_out_value_or_null, double* d_out_grad_or_null,
                  double* d_out_partials, void* d_ws, size_t ws_bytes, void* stream);
 
+/* get_samples_and_log_weights (notebooks/experiments.py:60-63) in one pass for the mean-field families and
+ * the elementwise plugins: samples (n, dim) [dtype], log p (n) (optional) and
+ * lw = log p(x) - log q(x; var_param) (n) float64, all left on the device for all_bounds / psislw. */
+int vb_mf_samples_logweights(int family, double df, const vb_model* model, int dtype,
+                             const double* d_var_param, long long n, const void* d_base_or_null,
+                             unsigned long long seed, unsigned int call_offset,
+                             unsigned long long sample_index0, void* d_out_samples,
+                             double* d_out_logp_or_null, double* d_out_lw, void* stream);
+
+/* Importance-weighted mean and covariance (notebooks/experiments.py:81-86, improve_with_psis):
+ * w = exp(lw - max lw); mean = sum w x / sum w; cov = sum w (x - mean)(x - mean)' / sum w
+ * (== np.cov(samples.T, aweights=w, ddof=0)).  d_x (n, dim) of `dtype`, d_log_weights (n) float64. */
+size_t vb_weighted_moments_workspace_bytes(long long n, int dim);
+int vb_weighted_moments(int dtype, const void* d_x, const double* d_log_weights, long long n, int dim,
+                        double* d_out_mean, double* d_out_cov_or_null,
+                        void* d_ws, size_t ws_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------
  * Variational-family closures (viabel/vb.py:54-79, 148-179, 202-230).
  *   sample:      x (n, dim) = m + exp(l) * eps                      (mean field)

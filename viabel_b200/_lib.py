@@ -37,6 +37,9 @@ SIGNATURES = {
     'vb_mf_finalize': (_i, [_i, _i, _d, _p, _i, _p, _i, _p, _p, _p]),
     'vb_mf_reduce_workspace_bytes': (_sz, [_ll, _i]),
     'vb_mf_reduce': (_i, [_i, _d, _i, _d, _i, _p, _ll, _i, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    'vb_mf_samples_logweights': (_i, [_i, _d, _p, _i, _p, _ll, _p, _ull, _u, _ull, _p, _p, _p, _p]),
+    'vb_weighted_moments_workspace_bytes': (_sz, [_ll, _i]),
+    'vb_weighted_moments': (_i, [_i, _p, _p, _ll, _i, _p, _p, _p, _sz, _p]),
     'vb_mf_sample': (_i, [_i, _p, _ll, _i, _p, _p, _p]),
     'vb_mf_logdensity': (_i, [_i, _d, _i, _p, _ll, _i, _p, _p, _p]),
     'vb_fr_sample_workspace_bytes': (_sz, [_i, _ll, _i]),

@@ -387,6 +387,93 @@ static int dispatch_family(const MfCall& c, const typename Model::P& mp) {
     return VB_ERR_ARG;
 }
 
+// ------------------------------------------------------------------------------------------ samples + log weights
+// get_samples_and_log_weights of notebooks/experiments.py:60-63 as ONE pass for the mean-field families and
+// the elementwise plugins: draw (or load) eps -> x = m + exp(l) eps -> lw = log p(x) - log q(x; lambda).
+// Outputs stay on the device and feed all_bounds / psislw without a host round trip.
+template <typename T, int FAM, class Model, bool PHILOX>
+__global__ void __launch_bounds__(256)
+mf_samples_lw_kernel(const __grid_constant__ MfArgs<Model> a, T* __restrict__ out_x, double* __restrict__ out_logp,
+                     double* __restrict__ out_lw) {
+    constexpr int D = Model::D;
+    __shared__ T mean[D], sig[D];
+    if (threadIdx.x < D) {
+        mean[threadIdx.x] = (T)a.var_param[threadIdx.x];
+        sig[threadIdx.x] = (T)exp(a.var_param[D + threadIdx.x]);
+    }
+    __syncthreads();
+    double sum_l = 0.0;
+#pragma unroll
+    for (int j = 0; j < D; ++j) sum_l += a.var_param[D + j];
+    const double logq0 = D * mf_logq_const(FAM, a.df) - sum_l;
+    const T df = (T)a.df;
+    const T* base = reinterpret_cast<const T*>(a.base);
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < a.n; i += (long long)gridDim.x * blockDim.x) {
+        T eps[D];
+        if (PHILOX) {
+            const uint64_t gi = a.sample_index0 + (uint64_t)i;
+            if (FAM == VB_FAMILY_MF_GAUSS) {
+#pragma unroll
+                for (int q = 0; q < (D + 3) / 4; ++q) {
+                    float z[4];
+                    draw_normal_pair(a.rng, gi, (uint32_t)q, z[0], z[1], z[2], z[3]);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        if (4 * q + k < D) eps[4 * q + k] = (T)z[k];
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < D; ++j) eps[j] = (T)draw_student_t(a.rng, gi, (uint32_t)j, (float)a.df);
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < D; ++j) eps[j] = base[(size_t)i * D + j];
+        }
+        T x[D], g[D], lp;
+#pragma unroll
+        for (int j = 0; j < D; ++j) x[j] = mean[j] + sig[j] * eps[j];
+        Model::template eval<T>(a.mp, x, lp, g);
+#pragma unroll
+        for (int j = 0; j < D; ++j) out_x[(size_t)i * D + j] = x[j];
+        if (out_logp) out_logp[i] = (double)lp;
+        out_lw[i] = (double)lp - (logq0 + (double)logq_core<T, FAM, D>(eps, df));
+    }
+}
+
+template <typename T, int FAM, class Model>
+static int launch_samples_lw(const MfCall& c, const typename Model::P& mp, void* out_x, double* out_logp, double* out_lw) {
+    MfArgs<Model> a{};
+    a.mp = mp;
+    a.var_param = c.var_param;
+    a.base = c.base;
+    a.n = c.n;
+    a.df = c.df;
+    a.alpha = 1.0;
+    a.rng.k0 = (uint32_t)c.seed;
+    a.rng.k1 = (uint32_t)(c.seed >> 32);
+    a.rng.offset = c.call_offset;
+    a.sample_index0 = c.sample_index0;
+    long long grid = (c.n + 255) / 256;
+    if (grid > (long long)num_sms() * 8) grid = (long long)num_sms() * 8;
+    if (c.base == nullptr)
+        mf_samples_lw_kernel<T, FAM, Model, true><<<(unsigned)grid, 256, 0, c.stream>>>(a, (T*)out_x, out_logp, out_lw);
+    else
+        mf_samples_lw_kernel<T, FAM, Model, false><<<(unsigned)grid, 256, 0, c.stream>>>(a, (T*)out_x, out_logp, out_lw);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+template <class Model>
+static int dispatch_samples_lw(const MfCall& c, const typename Model::P& mp, void* out_x, double* out_logp, double* out_lw) {
+    if (c.dtype == VB_F64) {
+        if (c.family == VB_FAMILY_MF_GAUSS) return launch_samples_lw<double, VB_FAMILY_MF_GAUSS, Model>(c, mp, out_x, out_logp, out_lw);
+        if (c.family == VB_FAMILY_MF_T) return launch_samples_lw<double, VB_FAMILY_MF_T, Model>(c, mp, out_x, out_logp, out_lw);
+    } else if (c.dtype == VB_F32) {
+        if (c.family == VB_FAMILY_MF_GAUSS) return launch_samples_lw<float, VB_FAMILY_MF_GAUSS, Model>(c, mp, out_x, out_logp, out_lw);
+        if (c.family == VB_FAMILY_MF_T) return launch_samples_lw<float, VB_FAMILY_MF_T, Model>(c, mp, out_x, out_logp, out_lw);
+    }
+    return VB_ERR_ARG;
+}
+
 // ------------------------------------------------------------------------------------------ finalize (multi-rank)
 __global__ void mf_finalize_kernel(int family, int objective, double alpha, const double* var_param, int D,
                                    const double* parts, int R, double* out_value, double* out_grad) {
@@ -458,4 +545,34 @@ extern "C" int vb_mf_finalize(int family, int objective, double alpha, const dou
         family, objective, alpha, d_var_param, dim, d_partials, n_ranks, d_out_value, d_out_grad);
     VB_LAUNCH_CHECK();
     return VB_OK;
+}
+
+extern "C" int vb_mf_samples_logweights(int family, double df, const vb_model* model, int dtype,
+                                        const double* d_var_param, long long n, const void* d_base_or_null,
+                                        unsigned long long seed, unsigned int call_offset,
+                                        unsigned long long sample_index0, void* d_out_samples,
+                                        double* d_out_logp_or_null, double* d_out_lw, void* stream) {
+    if (!model || !d_var_param || !d_out_samples || !d_out_lw || n < 1) return VB_ERR_ARG;
+    if (family == VB_FAMILY_MF_T && !(df > 2.0)) return VB_ERR_ARG;
+    const ModelHost* m = reinterpret_cast<const ModelHost*>(model);
+    MfCall c{family, df, VB_OBJ_KLVI, 1.0, dtype, d_var_param, n, d_base_or_null, seed, call_offset,
+             sample_index0, nullptr, nullptr, nullptr, nullptr, 0, (cudaStream_t)stream};
+    switch (m->kind) {
+        case VB_MODEL_FUNNEL: {
+            Funnel::P p{m->p0};
+            return dispatch_samples_lw<Funnel>(c, p, d_out_samples, d_out_logp_or_null, d_out_lw);
+        }
+        case VB_MODEL_MIXTURE: {
+            Mixture::P p{m->p0};
+            return dispatch_samples_lw<Mixture>(c, p, d_out_samples, d_out_logp_or_null, d_out_lw);
+        }
+        case VB_MODEL_EIGHT_SCHOOLS: {
+            if (m->n_schools != 8) return VB_ERR_UNSUPPORTED;
+            EightSchools<8>::P p;
+            for (int j = 0; j < 8; ++j) { p.y[j] = m->y[j]; p.inv_sigma[j] = 1.0 / m->sigma[j]; }
+            return dispatch_samples_lw<EightSchools<8>>(c, p, d_out_samples, d_out_logp_or_null, d_out_lw);
+        }
+        default:
+            return VB_ERR_UNSUPPORTED;   // regression / gauss / full rank: composed from sample + plugin + logdensity
+    }
 }
