@@ -55,6 +55,20 @@ int make_split_tmap(CUtensorMap* out, const float* base, long long rows, long lo
     return r == CUDA_SUCCESS ? VB_OK : VB_ERR_ARG;
 }
 
+int make_raw_tmap(CUtensorMap* out, const float* base, long long rows, long long cols, long long ld, int box_rows) {
+    EncodeTiledFn enc = get_encode_tiled();
+    if (!enc) return VB_ERR_UNSUPPORTED;
+    if ((reinterpret_cast<uintptr_t>(base) & 15u) || (ld % 4)) return VB_ERR_ALIGN;
+    const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+    const cuuint32_t box[2] = {32, (cuuint32_t)box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                           CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? VB_OK : VB_ERR_ARG;
+}
+
 // ------------------------------------------------------------------------------------------ operand splitting
 // src (rows, cols) with leading dimension lds -> dst planes (rows, ldd): hi at dst, lo at dst + plane
 __global__ void split_kernel(const float* __restrict__ src, long long rows, long long cols, long long lds,
@@ -394,11 +408,15 @@ namespace vb {
 //          psi written straight into split (hi, lo) planes -- the S x N residual matrix is never stored
 //   GEMM2  G (S x d) += Psi (S x C) X_chunk  (split-K over the chunk, partials summed into fp64)
 // The same split copy of X serves both products: K-major B operand in GEMM1, MN-major B operand in GEMM2.
+__device__ __noinline__ float log1p_sum4_slow(float r0, float r1, float r2, float r3, float inv_df) {
+    return (log1pf(r0 * r0 * inv_df) + log1pf(r1 * r1 * inv_df)) + (log1pf(r2 * r2 * inv_df) + log1pf(r3 * r3 * inv_df));
+}
 struct PsiEpi {
-    float* __restrict__ psi; long long ldp, plane;   // split planes of Psi, (S, C) with leading dimension ldp
+    static constexpr bool kStaged = true;
+    alignas(64) CUtensorMap tmap;                    // Psi / c as a plain fp32 (S, cols) matrix, 32 x 32 store box
     const float* __restrict__ y;                     // y + r0
     float* __restrict__ rowpart; int n_blocks;       // (S, C/32) partial sums of log1p(r^2/df)
-    float df, inv_df, dfp1;
+    float inv_df;
     struct Pre { float y[32]; };
     __device__ __forceinline__ Pre prefetch(long long, long long col0, int ncols) const {
         Pre p;
@@ -415,38 +433,72 @@ struct PsiEpi {
         }
         return p;
     }
-    __device__ __forceinline__ void operator()(long long row, long long col0, float (&v)[32], int ncols, int,
-                                               const Pre& pre) const {
-        float* ph = psi + row * ldp + col0;
-        float* pl = ph + plane;
+    // Four elements at a time: u_i = 1 + r_i^2/df, sum_i log1p(r_i^2/df) = log(u_0 u_1 u_2 u_3) (one log per four
+    // elements; the rare product overflow falls back to log1pf per element), psi_i / c = r_i / u_i with the
+    // approximate reciprocal (1 ulp; u >= 1) -- the constant c = (df+1)/df is applied once to the accumulated
+    // gradient.  Psi is stored as plain fp32; the consumer GEMM splits it into tf32 hi / lo in shared memory.
+    static __device__ __forceinline__ float log_ge1(float p) {
+        // p in [1, 3e38): p = 2^e m, m in [2/3, 4/3); log m = f - f^2/2 + f^3 Q(f), f = m - 1, Q = degree-6 minimax
+        // fit (max abs error 3.4e-8 over the interval, fitted in scripts/fit_log_poly.py)
+        const uint32_t bits = __float_as_uint(p);
+        const uint32_t e = (bits - 0x3f2aaaabu) & 0xff800000u;
+        const float f = __uint_as_float(bits - e) - 1.f;
+        float q = 0.1440092772245407f;
+        q = fmaf(q, f, -0.15269480645656586f);
+        q = fmaf(q, f, 0.13915356993675232f);
+        q = fmaf(q, f, -0.1644672304391861f);
+        q = fmaf(q, f, 0.20016367733478546f);
+        q = fmaf(q, f, -0.2500529885292053f);
+        q = fmaf(q, f, 0.33333104848861694f);
+        q = fmaf(q, f, -0.5f);
+        q = fmaf(f, q * f, f);
+        return fmaf((float)(int)e, 8.262958294867817e-08f, q);     // e * 2^-23 * ln 2
+    }
+    __device__ __forceinline__ float4 quad(const float* yv, const float* av, float& acc) const {
+        float r[4], u[4], o[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            r[q] = yv[q] - av[q];
+            u[q] = fmaf(r[q] * r[q], inv_df, 1.f);
+        }
+        const float p = (u[0] * u[1]) * (u[2] * u[3]);
+        if (p < 3.0e38f) {
+            acc += log_ge1(p);
+        } else {
+            acc += log1p_sum4_slow(r[0], r[1], r[2], r[3], inv_df);
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            float inv;
+            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(u[q]));
+            o[q] = r[q] * inv;
+        }
+        return make_float4(o[0], o[1], o[2], o[3]);
+    }
+    // Thread = one row of the warp's 32 x 32 block.  The block is written in the 128-byte-swizzled layout the
+    // TMA store expects: 16-byte unit j of row r lives at r*128 + ((j ^ (r & 7)) << 4) (conflict-free STS.128).
+    __device__ __forceinline__ void staged(long long row, long long col0, float (&v)[32], int ncols, int,
+                                           const Pre& pre, unsigned char* staging, int lane) const {
         float acc = 0.f;
+        unsigned char* my = staging + lane * 128;
         if (ncols == 32) {
 #pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-                float hi[8], lo[8];
-#pragma unroll
-                for (int q = 0; q < 8; ++q) {
-                    const float r = pre.y[j + q] - v[j + q];
-                    const float r2 = r * r;
-                    acc += log1pf(r2 * inv_df);
-                    const float ps = dfp1 * r * __frcp_rn(df + r2);
-                    tc::split_tf32(ps, hi[q], lo[q]);
-                }
-                st_global_v8(ph + j, hi);          // one full 32-byte sector per request
-                st_global_v8(pl + j, lo);
+            for (int j = 0; j < 8; ++j) {
+                const float4 o = quad(pre.y + 4 * j, v + 4 * j, acc);
+                *reinterpret_cast<float4*>(my + ((j ^ (lane & 7)) << 4)) = o;
             }
         } else {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                if (j < ncols) {
-                    const float r = pre.y[j] - v[j];
-                    const float r2 = r * r;
-                    acc += log1pf(r2 * inv_df);
-                    float hi, lo;
-                    tc::split_tf32(dfp1 * r * __frcp_rn(df + r2), hi, lo);
-                    ph[j] = hi;
-                    pl[j] = lo;
+            for (int j = 0; j < 8; ++j) {
+                float yy[4], aa[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {      // masked columns: r = 0 -> u = 1 -> no contribution; the store clips them
+                    const bool on = 4 * j + q < ncols;
+                    yy[q] = on ? pre.y[4 * j + q] : 0.f;
+                    aa[q] = on ? v[4 * j + q] : 0.f;
                 }
+                const float4 o = quad(yy, aa, acc);
+                *reinterpret_cast<float4*>(my + ((j ^ (lane & 7)) << 4)) = o;
             }
         }
         rowpart[row * n_blocks + (col0 >> 5)] = acc;
@@ -482,12 +534,13 @@ __global__ void reg_init_kernel(const float* __restrict__ b, long long S, int D,
         if (lane == 0) logp[s] = -0.5 * a * inv_var;
     }
 }
-// gacc[e] += sum_k parts[k][e]
-__global__ void reg_parts_acc_kernel(const float* __restrict__ parts, int splits, long long mn, double* __restrict__ gacc) {
+// gacc[e] += scale * sum_k parts[k][e]
+__global__ void reg_parts_acc_kernel(const float* __restrict__ parts, int splits, long long mn, double scale,
+                                     double* __restrict__ gacc) {
     for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < mn; e += (long long)gridDim.x * blockDim.x) {
         double a = 0.0;
         for (int k = 0; k < splits; ++k) a += (double)parts[(size_t)k * mn + e];
-        gacc[e] += a;
+        gacc[e] = fma(scale, a, gacc[e]);
     }
 }
 __global__ void reg_cast_kernel(const double* __restrict__ src, long long total, float* __restrict__ dst) {
@@ -520,7 +573,7 @@ static RegLayout reg_layout(long long S, long long N, int D) {
     auto take = [&](size_t bytes) { size_t at = o; o += (bytes + 255) & ~(size_t)255; return at; };
     L.off_xs = take(split_bytes(N, D));
     L.off_bs = take(split_bytes(S, D));
-    L.off_psi = take((size_t)2 * S * L.C * 4);
+    L.off_psi = take((size_t)S * L.C * 4);
     L.off_rowpart = take((size_t)S * (L.C / 32 + 1) * 4);
     L.off_parts = take((size_t)L.splits * S * D * 4);
     L.off_gacc = take((size_t)S * D * 8);
@@ -559,19 +612,24 @@ int regression_logp_grad_tf32(const ModelHost* m, const float* b, long long S, d
     for (long long r0 = 0; r0 < N; r0 += L.C) {
         const long long cols = (r0 + L.C <= N) ? L.C : (N - r0);
         const SplitMat xc{xs.base + r0 * xs.ld, cols, D, xs.ld, xs.plane_stride};
-        // GEMM1 + fused elementwise epilogue
-        PsiEpi e1{psi, L.C, S * L.C, y + r0, rowpart, n_blocks, (float)m->df, (float)(1.0 / m->df), (float)(m->df + 1.0)};
-        rc = launch_tf32x3<false, false, PsiEpi, 16>(bs, xc, plan_gemm(S, cols, D, 1), e1, st);
+        // GEMM1 + fused elementwise epilogue; Psi / c leaves through a TMA store as one fp32 plane (S, cols), ld = C
+        PsiEpi e1;
+        rc = make_raw_tmap(&e1.tmap, psi, S, cols, L.C, 32);
+        if (rc != VB_OK) return rc;
+        e1.y = y + r0; e1.rowpart = rowpart; e1.n_blocks = n_blocks; e1.inv_df = (float)(1.0 / m->df);
+        // d <= 128: the 128-sample tile of B stays in shared memory while the CTA walks the chunk's row tiles
+        rc = (D <= kTResKTiles * kTBK) ? launch_tf32x3<false, false, PsiEpi, 8, true>(bs, xc, plan_gemm(S, cols, D, 1), e1, st)
+                                       : launch_tf32x3<false, false, PsiEpi, 8>(bs, xc, plan_gemm(S, cols, D, 1), e1, st);
         if (rc != VB_OK) return rc;
         reg_rowpart_acc_kernel<<<grid_for(S * 32, 256, kNumSMs * 8), 256, 0, st>>>(
             rowpart, S, n_blocks, (int)((cols + 31) / 32), 0.5 * (m->df + 1.0), out_logp);
         VB_LAUNCH_CHECK();
         if (out_grad_or_null) {
-            const SplitMat ps{psi, S, cols, L.C, S * L.C};
+            const SplitMat ps{psi, S, cols, L.C, 0};                 // raw fp32: split in shared memory by the GEMM
             const GemmShape shape = plan_gemm(S, D, cols, auto_splits(S, D, cols));
-            rc = launch_tf32x3<false, true>(ps, xc, shape, SplitKEpi{parts, mn, D}, st);
+            rc = launch_tf32x3<false, true, SplitKEpi, 4, false, true>(ps, xc, shape, SplitKEpi{parts, mn, D}, st);
             if (rc != VB_OK) return rc;
-            reg_parts_acc_kernel<<<grid_for(mn, 256, kNumSMs * 4), 256, 0, st>>>(parts, shape.splits, mn, gacc);
+            reg_parts_acc_kernel<<<grid_for(mn, 256, kNumSMs * 4), 256, 0, st>>>(parts, shape.splits, mn, (m->df + 1.0) / m->df, gacc);
             VB_LAUNCH_CHECK();
         }
     }

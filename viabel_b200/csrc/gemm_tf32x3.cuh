@@ -2,28 +2,40 @@
 //   A B ~= A_hi B_hi + A_hi B_lo + A_lo B_hi        (lo*lo dropped: 2^-22 relative)
 // accumulated in fp32 in tensor memory.  Operands are "split" matrices (see tc05.cuh):
 // producers write the hi/lo planes once, the GEMM streams them with TMA (SWIZZLE_128B) into a
-// 3-stage shared-memory ring, a single thread issues tcgen05.mma (kind::tf32, 128x128x8), and four
+// shared-memory ring, a single thread issues tcgen05.mma (kind::tf32, 128x128x8), and the
 // epilogue warps drain double-buffered TMEM accumulators through a fused epilogue functor.
 //
-// Warp roles (192 threads): warp 0 TMA producer, warp 1 TMEM owner + MMA issuer, warps 2-5 epilogue.
-// Persistent CTAs walk (m tile, n tile, k split) work items round-robin.
+// Warp roles: warp 0 TMA producer, warp 1 TMEM owner + MMA issuer, warps 2 .. 2+EW-1 epilogue,
+// (A_RAW only) four more warps that split a raw fp32 A tile into its hi / lo planes in shared memory.
+// Persistent CTAs walk (m tile, n tile, k split) work items.
 //
 // Layouts: A is either K-major (rows = M, cols = K) or MN-major (rows = K, cols = M); same for B
 // with N.  K-major tiles are one (32 x 128 x 2) box; MN-major tiles are four (32 x 32 x 2) boxes.
+//
+// Variants (template flags):
+//   A_RES  (K <= 128, K-major A, splits == 1): the whole K extent of the A tile stays in shared memory while
+//          the CTA walks a contiguous run of n tiles; only B is streamed.  A 128x128 3xTF32 tile that reloads
+//          both operands needs 59 B/clk/SM from L2 against ~43 available (B300_MICROARCH: ~6300 B/clk chip).
+//   A_RAW  (K-major A): A is a plain fp32 matrix (one plane in HBM, half the traffic of a split operand);
+//          the tile is split into hi / lo in place in shared memory by four converter warps.
+//   Epi::kStaged: the epilogue writes its 32x32 output blocks to a per-warp swizzled shared-memory buffer and
+//          stores them with TMA (full lines, no LSU pressure) instead of 32 scattered sectors per warp store.
 #pragma once
+#include <type_traits>
 #include "tc05.cuh"
 
 namespace vb {
 
 constexpr int kTBM = 128, kTBN = 128, kTBK = 32, kTStages = 3;
-constexpr int kTThreads = 192;
 constexpr uint32_t kTPlaneBytes = 128 * 32 * 4;             // one 128 x 32 fp32 tile
 constexpr uint32_t kTOperandBytes = 2 * kTPlaneBytes;       // hi + lo
 constexpr uint32_t kTStageBytes = 2 * kTOperandBytes;       // A + B
-constexpr size_t kTSmemBytes = (size_t)kTStages * kTStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int kTResKTiles = 4;
+constexpr size_t kTResABytes = (size_t)kTResKTiles * kTOperandBytes;
+constexpr uint32_t kTStagingBytes = 32 * 32 * 4;            // one 32 x 32 fp32 block per epilogue warp
 
 struct SplitMat {
-    const float* base;          // plane 0 (hi); plane 1 (lo) at base + plane_stride
+    const float* base;          // plane 0 (hi); plane 1 (lo) at base + plane_stride (ignored for a raw operand)
     long long rows, cols, ld, plane_stride;
 };
 
@@ -47,35 +59,64 @@ struct OperandLayout {
     static constexpr uint32_t k_step = MN_MAJOR ? 1024u : 32u;     // per UMMA_K = 8 fp32
 };
 
+template <class E, class = void> struct epi_staged : std::false_type {};
+template <class E> struct epi_staged<E, std::void_t<decltype(E::kStaged)>> : std::bool_constant<E::kStaged> {};
+
+// Shared-memory plan of one instantiation
+template <class Epi, int EW, bool A_RES, bool A_RAW>
+struct GemmCfg {
+    static constexpr bool kStaged = epi_staged<Epi>::value;
+    static constexpr int kStages = (A_RES && kStaged) ? 2 : kTStages;
+    static constexpr size_t kSlot = A_RES ? kTOperandBytes : kTStageBytes;      // ring slot: [A | B] or [B]
+    static constexpr size_t kRingOff = A_RES ? kTResABytes : 0;
+    static constexpr size_t kStagingOff = kRingOff + (size_t)kStages * kSlot;
+    static constexpr size_t kBarOff = kStagingOff + (kStaged ? (size_t)EW * kTStagingBytes : 0);
+    static constexpr size_t kSmemBytes = kBarOff + 256 /*barriers*/ + 1024 /*align*/;
+    static constexpr int kThreads = 64 + 32 * EW + (A_RAW ? 128 : 0);
+    static_assert(kSmemBytes <= 232448, "exceeds the 227 KB of shared memory a CTA may use");
+};
+
 // EW = number of epilogue warps (4, 8 or 16): warp (q, h) drains TMEM lane quarter q = warp % 4 and the
-// column blocks h, h + EW/4, ... of the 128-column accumulator.  Heavy epilogues (transcendentals per
-// element) need 16 warps to hide their latency; a plain store is fine with 4.
-template <bool A_MN, bool B_MN, class Epi, int EW = 4>
-__global__ void __launch_bounds__(64 + 32 * EW, 1)
+// column blocks h, h + EW/4, ... of the 128-column accumulator.
+template <bool A_MN, bool B_MN, class Epi, int EW = 4, bool A_RES = false, bool A_RAW = false>
+__global__ void __launch_bounds__(GemmCfg<Epi, EW, A_RES, A_RAW>::kThreads, 1)
 gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                   const GemmShape shape, const Epi epi) {
+                   const GemmShape shape, const __grid_constant__ Epi epi) {
+    using Cfg = GemmCfg<Epi, EW, A_RES, A_RAW>;
+    static_assert(!(A_RES && A_MN) && !(A_RAW && A_MN) && !(A_RES && A_RAW), "unsupported variant combination");
+    constexpr int kStages = Cfg::kStages;
+    constexpr size_t kSlot = Cfg::kSlot;
     extern __shared__ unsigned char smem_dyn[];
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) &
                                                            ~(uintptr_t)1023);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)kTStages * kTStageBytes);
-    uint64_t* full_bar = bars;                      // [stages]
-    uint64_t* empty_bar = bars + kTStages;          // [stages]
-    uint64_t* tmem_full = bars + 2 * kTStages;      // [2]
-    uint64_t* tmem_empty = bars + 2 * kTStages + 2; // [2]
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * kTStages + 4);
+    unsigned char* ring = smem + Cfg::kRingOff;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kBarOff);
+    uint64_t* full_bar = bars;                      // [3] TMA bytes of the slot landed
+    uint64_t* empty_bar = bars + 3;                 // [3] MMAs reading the slot retired
+    uint64_t* tmem_full = bars + 6;                 // [2]
+    uint64_t* tmem_empty = bars + 8;                // [2]
+    uint64_t* a_full = bars + 10;                   // A_RES: resident A tile landed / all MMAs on it retired
+    uint64_t* a_empty = bars + 11;
+    uint64_t* conv_bar = bars + 12;                 // [3] A_RAW: slot's A tile split into hi / lo
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 15);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const long long m_tiles = (shape.M + kTBM - 1) / kTBM, n_tiles = (shape.N + kTBN - 1) / kTBN;
     const long long total = m_tiles * n_tiles * shape.splits;
     const long long k_tiles_total = (shape.K + kTBK - 1) / kTBK;
+    // work items: round-robin over the grid, or (A_RES) one contiguous run of n tiles per CTA
+    const long long w_begin = A_RES ? total * blockIdx.x / gridDim.x : blockIdx.x;
+    const long long w_end = A_RES ? total * (blockIdx.x + 1) / gridDim.x : total;
+    const long long w_step = A_RES ? 1 : gridDim.x;
 
     if (threadIdx.x == 0) {
         tc::prefetch_tmap(&tmap_a);
         tc::prefetch_tmap(&tmap_b);
 #pragma unroll
-        for (int s = 0; s < kTStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        for (int s = 0; s < 3; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); mbar_init(&conv_bar[s], 128); }
         mbar_init(&tmem_full[0], 1); mbar_init(&tmem_full[1], 1);
         mbar_init(&tmem_empty[0], 32 * EW); mbar_init(&tmem_empty[1], 32 * EW);
+        mbar_init(a_full, 1); mbar_init(a_empty, 1);
         mbar_fence_init();
     }
     if (warp == 1) tc::tmem_alloc<256>(tmem_ptr);      // 2 accumulator stages x 128 columns
@@ -87,22 +128,37 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     if (warp == 0) {
         // ===================================================== TMA producer (whole warp loops, lane 0 issues)
         int stage = 0;
-        uint32_t phase = 0;
-        for (long long w = blockIdx.x; w < total; w += gridDim.x) {
+        uint32_t phase = 0, a_phase = 0;
+        int cur_m0 = -1;
+        for (long long w = w_begin; w < w_end; w += w_step) {
             const long long tile = w % (m_tiles * n_tiles);
             const int split = (int)(w / (m_tiles * n_tiles));
-            const int n0 = (int)(tile % n_tiles) * kTBN, m0 = (int)(tile / n_tiles) * kTBM;   // n fastest: CTAs that run together share the A tile in L2
+            // n fastest: CTAs that run together share the A tile in L2
+            const int n0 = (int)(tile % n_tiles) * kTBN, m0 = (int)(tile / n_tiles) * kTBM;
             const long long kt0 = (long long)split * shape.k_tiles_per_split;
             long long kt1 = kt0 + shape.k_tiles_per_split;
             if (kt1 > k_tiles_total) kt1 = k_tiles_total;
+            if (A_RES && m0 != cur_m0) {
+                if (cur_m0 >= 0) { mbar_wait(a_empty, a_phase); a_phase ^= 1; }
+                if (lane == 0) {
+                    mbar_expect_tx(a_full, (uint32_t)(k_tiles_total * kTOperandBytes));
+                    for (int kt = 0; kt < (int)k_tiles_total; ++kt)
+                        tc::tma_load_3d(smem + (size_t)kt * kTOperandBytes, &tmap_a, a_full, kt * kTBK, m0, 0);
+                }
+                __syncwarp();
+                cur_m0 = m0;
+            }
             for (long long kt = kt0; kt < kt1; ++kt) {
                 mbar_wait(&empty_bar[stage], phase ^ 1);
                 if (lane == 0) {
-                    unsigned char* sa = smem + (size_t)stage * kTStageBytes;
-                    unsigned char* sb = sa + kTOperandBytes;
-                    mbar_expect_tx(&full_bar[stage], kTStageBytes);
+                    unsigned char* sa = ring + (size_t)stage * kSlot;
+                    unsigned char* sb = A_RES ? sa : sa + kTOperandBytes;
+                    mbar_expect_tx(&full_bar[stage], A_RES ? kTOperandBytes : (A_RAW ? kTPlaneBytes + kTOperandBytes : kTStageBytes));
                     const int k0 = (int)kt * kTBK;
-                    if (A_MN) {
+                    if (A_RES) {
+                    } else if (A_RAW) {
+                        tc::tma_load_2d(sa, &tmap_a, &full_bar[stage], k0, m0);          // lands in the hi plane
+                    } else if (A_MN) {
 #pragma unroll
                         for (int b = 0; b < 4; ++b) tc::tma_load_3d(sa + b * 8192, &tmap_a, &full_bar[stage], m0 + 32 * b, k0, 0);
                     } else {
@@ -116,7 +172,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
                     }
                 }
                 __syncwarp();
-                if (++stage == kTStages) { stage = 0; phase ^= 1; }
+                if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
         }
     } else if (warp == 1) {
@@ -125,13 +181,19 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         using LA = OperandLayout<A_MN>;
         using LB = OperandLayout<B_MN>;
         int stage = 0;
-        uint32_t phase = 0;
+        uint32_t phase = 0, a_phase = 0;
         int it = 0;
-        for (long long w = blockIdx.x; w < total; w += gridDim.x, ++it) {
+        long long cur_m = -1;
+        for (long long w = w_begin; w < w_end; w += w_step, ++it) {
             const int split = (int)(w / (m_tiles * n_tiles));
             const long long kt0 = (long long)split * shape.k_tiles_per_split;
             long long kt1 = kt0 + shape.k_tiles_per_split;
             if (kt1 > k_tiles_total) kt1 = k_tiles_total;
+            if (A_RES && w / n_tiles != cur_m) {
+                cur_m = w / n_tiles;
+                mbar_wait(a_full, a_phase);
+                a_phase ^= 1;
+            }
             const int as = it & 1;
             mbar_wait(&tmem_empty[as], (uint32_t)(((it >> 1) & 1) ^ 1));
             tc::fence_after_sync();
@@ -139,10 +201,12 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
             bool first = true;
             for (long long kt = kt0; kt < kt1; ++kt) {
                 mbar_wait(&full_bar[stage], phase);
+                if (A_RAW) mbar_wait(&conv_bar[stage], phase);
                 tc::fence_after_sync();
                 if (lane == 0) {
-                    const uint32_t a_addr = smem_u32(smem + (size_t)stage * kTStageBytes);
-                    const uint32_t b_addr = a_addr + kTOperandBytes;
+                    const uint32_t slot = smem_u32(ring + (size_t)stage * kSlot);
+                    const uint32_t a_addr = A_RES ? smem_u32(smem + (size_t)kt * kTOperandBytes) : slot;
+                    const uint32_t b_addr = A_RES ? slot : slot + kTOperandBytes;
 #pragma unroll
                     for (int k = 0; k < kTBK / 8; ++k) {
                         const uint64_t a_hi = tc::smem_desc_sw128(a_addr + k * LA::k_step, LA::lbo, LA::sbo, LA::layout_type);
@@ -157,17 +221,52 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
                 }
                 __syncwarp();
                 first = false;
-                if (++stage == kTStages) { stage = 0; phase ^= 1; }
+                if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
-            if (lane == 0) tc::mma_commit(&tmem_full[as]);    // accumulator ready for the epilogue
+            if (lane == 0) {
+                tc::mma_commit(&tmem_full[as]);               // accumulator ready for the epilogue
+                if (A_RES && w + 1 < w_end && (w + 1) / n_tiles != cur_m) tc::mma_commit(a_empty);   // last use of this A tile
+            }
             __syncwarp();
         }
+    } else if (A_RAW && warp >= 2 + EW) {
+        // ===================================================== converter warps: raw fp32 A tile -> hi / lo planes
+        // The split is element-wise, so it is independent of the swizzle TMA applied: every 16-byte unit is
+        // rewritten in place (hi) and mirrored at +kTPlaneBytes (lo), which is the split-tile layout.
+        const int tid_c = (int)threadIdx.x - (64 + 32 * EW);
+        int stage = 0;
+        uint32_t phase = 0;
+        for (long long w = w_begin; w < w_end; w += w_step) {
+            const int split = (int)(w / (m_tiles * n_tiles));
+            const long long kt0 = (long long)split * shape.k_tiles_per_split;
+            long long kt1 = kt0 + shape.k_tiles_per_split;
+            if (kt1 > k_tiles_total) kt1 = k_tiles_total;
+            for (long long kt = kt0; kt < kt1; ++kt) {
+                mbar_wait(&full_bar[stage], phase);
+                float4* hi_p = reinterpret_cast<float4*>(ring + (size_t)stage * kSlot);
+                float4* lo_p = reinterpret_cast<float4*>(ring + (size_t)stage * kSlot + kTPlaneBytes);
+#pragma unroll
+                for (int i = 0; i < (int)(kTPlaneBytes / 16 / 128); ++i) {
+                    const int u = tid_c + i * 128;
+                    const float4 x = hi_p[u];
+                    float4 h, l;
+                    tc::split_tf32(x.x, h.x, l.x); tc::split_tf32(x.y, h.y, l.y);
+                    tc::split_tf32(x.z, h.z, l.z); tc::split_tf32(x.w, h.w, l.w);
+                    hi_p[u] = h;
+                    lo_p[u] = l;
+                }
+                tc::fence_proxy_async_smem();
+                mbar_arrive(&conv_bar[stage]);
+                if (++stage == kStages) { stage = 0; phase ^= 1; }
+            }
+        }
     } else {
-        // ===================================================== epilogue (warps 2..5)
+        // ===================================================== epilogue (warps 2 .. 2+EW-1)
         const int q = warp & 3;                      // TMEM lane quarter this warp may access
         const int h = (warp - 2) >> 2;               // which column blocks of the quarter this warp takes
+        unsigned char* staging = smem + Cfg::kStagingOff + (size_t)(warp - 2) * kTStagingBytes;
         int it = 0;
-        for (long long w = blockIdx.x; w < total; w += gridDim.x, ++it) {
+        for (long long w = w_begin; w < w_end; w += w_step, ++it) {
             const long long tile = w % (m_tiles * n_tiles);
             const int split = (int)(w / (m_tiles * n_tiles));
             const long long n0 = (tile % n_tiles) * kTBN, m0 = (tile / n_tiles) * kTBM;
@@ -186,11 +285,24 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
                 if (live) pre = epi.prefetch(row, col0, (int)ncols);
                 float v[32];
                 tc::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * kTBN + c * 32), v);
-                if (live) epi(row, col0, v, (int)ncols, split, pre);
+                if constexpr (Cfg::kStaged) {
+                    if (lane == 0) tc::bulk_wait_read0();      // the previous store has finished reading the buffer
+                    __syncwarp();
+                    if (live) epi.staged(row, col0, v, (int)ncols, split, pre, staging, lane);
+                    tc::fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0 && ncols > 0 && m0 + q * 32 < shape.M) {   // rows / columns past the edge are clipped by the map
+                        tc::tma_store_2d(&epi.tmap, staging, (int)col0, (int)(m0 + q * 32));
+                        tc::bulk_commit();
+                    }
+                } else {
+                    if (live) epi(row, col0, v, (int)ncols, split, pre);
+                }
             }
             tc::fence_before_sync();
             mbar_arrive(&tmem_empty[as]);
         }
+        if (Cfg::kStaged && lane == 0) tc::bulk_wait0();
     }
     tc::fence_before_sync();
     __syncthreads();
@@ -220,24 +332,27 @@ inline int auto_splits(long long M, long long N, long long K) {
 
 int tf32x3_num_sms();
 
-template <bool A_MN, bool B_MN, class Epi, int EW = 4>
+template <bool A_MN, bool B_MN, class Epi, int EW = 4, bool A_RES = false, bool A_RAW = false>
 static int launch_tf32x3(const SplitMat& A, const SplitMat& B, const GemmShape& shape, const Epi& epi,
                          cudaStream_t st) {
+    using Cfg = GemmCfg<Epi, EW, A_RES, A_RAW>;
+    if (A_RES && (shape.splits != 1 || shape.K > (long long)kTResKTiles * kTBK)) return VB_ERR_ARG;
     CUtensorMap ta, tb;
-    int rc = make_split_tmap(&ta, A.base, A.rows, A.cols, A.ld, A.plane_stride, A_MN ? kTBK : kTBM, A_MN);
+    int rc = A_RAW ? make_raw_tmap(&ta, A.base, A.rows, A.cols, A.ld, kTBM)
+                   : make_split_tmap(&ta, A.base, A.rows, A.cols, A.ld, A.plane_stride, A_MN ? kTBK : kTBM, A_MN);
     if (rc != VB_OK) return rc;
     rc = make_split_tmap(&tb, B.base, B.rows, B.cols, B.ld, B.plane_stride, B_MN ? kTBK : kTBN, B_MN);
     if (rc != VB_OK) return rc;
-    auto kern = gemm_tf32x3_kernel<A_MN, B_MN, Epi, EW>;
+    auto kern = gemm_tf32x3_kernel<A_MN, B_MN, Epi, EW, A_RES, A_RAW>;
     static bool configured = false;
     if (!configured) {
-        VB_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTSmemBytes));
+        VB_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::kSmemBytes));
         configured = true;
     }
     const long long total = ((shape.M + kTBM - 1) / kTBM) * ((shape.N + kTBN - 1) / kTBN) * shape.splits;
     long long grid = tf32x3_num_sms();
     if (grid > total) grid = total;
-    kern<<<(unsigned)grid, 64 + 32 * EW, kTSmemBytes, st>>>(ta, tb, shape, epi);
+    kern<<<(unsigned)grid, Cfg::kThreads, Cfg::kSmemBytes, st>>>(ta, tb, shape, epi);
     VB_LAUNCH_CHECK();
     return VB_OK;
 }

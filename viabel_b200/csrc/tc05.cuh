@@ -25,6 +25,24 @@ __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* m
            "r"(c0), "r"(c1), "r"(c2) : "memory");
 }
 
+// 2-D tiled load global -> shared (plain fp32 matrix)
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        :: "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+// 2-D tiled store shared -> global (bulk async group of the issuing thread); out-of-range box elements are clipped
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* smem_src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 :: "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// all bulk groups of this thread have finished READING their shared-memory source
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+// generic-proxy shared-memory writes -> visible to the async proxy (TMA store, tcgen05.mma operand reads)
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
 // ---------------------------------------------------------------------------- TMEM
 template <uint32_t kCols>
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_result) {      // one full warp
@@ -124,5 +142,9 @@ EncodeTiledFn get_encode_tiled();
 // mn_major operands use the 32-byte-atom flavour of the 128-byte swizzle (see smem_desc_sw128).
 int make_split_tmap(CUtensorMap* out, const float* base, long long rows, long long cols, long long ld,
                     long long plane_stride_elems, int box_rows, bool mn_major);
+// A plain fp32 (rows, cols) row-major matrix: 2-D map, (32, box_rows) box, 128-byte swizzle.  Loaded tiles have
+// the layout of ONE plane of a K-major split tile (so a tile can be split into hi / lo in shared memory);
+// the same map stores (32 x box_rows) tiles staged in shared memory.
+int make_raw_tmap(CUtensorMap* out, const float* base, long long rows, long long cols, long long ld, int box_rows);
 
 }  // namespace vb
