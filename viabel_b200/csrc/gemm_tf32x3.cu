@@ -55,7 +55,8 @@ int make_split_tmap(CUtensorMap* out, const float* base, long long rows, long lo
     return r == CUDA_SUCCESS ? VB_OK : VB_ERR_ARG;
 }
 
-int make_raw_tmap(CUtensorMap* out, const float* base, long long rows, long long cols, long long ld, int box_rows) {
+int make_raw_tmap(CUtensorMap* out, const float* base, long long rows, long long cols, long long ld, int box_rows,
+                  bool atom32) {
     EncodeTiledFn enc = get_encode_tiled();
     if (!enc) return VB_ERR_UNSUPPORTED;
     if ((reinterpret_cast<uintptr_t>(base) & 15u) || (ld % 4)) return VB_ERR_ALIGN;
@@ -64,7 +65,8 @@ int make_raw_tmap(CUtensorMap* out, const float* base, long long rows, long long
     const cuuint32_t box[2] = {32, (cuuint32_t)box_rows};
     const cuuint32_t estr[2] = {1, 1};
     const CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
-                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
                            CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS ? VB_OK : VB_ERR_ARG;
 }
@@ -417,22 +419,10 @@ struct PsiEpi {
     const float* __restrict__ y;                     // y + r0
     float* __restrict__ rowpart; int n_blocks;       // (S, C/32) partial sums of log1p(r^2/df)
     float inv_df;
-    struct Pre { float y[32]; };
-    __device__ __forceinline__ Pre prefetch(long long, long long col0, int ncols) const {
-        Pre p;
-        const float* yy = y + col0;
-        if (ncols == 32) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-                const float4 t = __ldg(reinterpret_cast<const float4*>(yy + j));
-                p.y[j] = t.x; p.y[j + 1] = t.y; p.y[j + 2] = t.z; p.y[j + 3] = t.w;
-            }
-        } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) p.y[j] = (j < ncols) ? __ldg(yy + j) : 0.f;
-        }
-        return p;
-    }
+    // y is indexed by the column: every lane of the warp reads the same address (one sector per request, L1
+    // hits), so it is read where it is used instead of being held in 32 registers across the TMEM load.
+    struct Pre {};
+    __device__ __forceinline__ Pre prefetch(long long, long long, int) const { return Pre{}; }
     // Four elements at a time: u_i = 1 + r_i^2/df, sum_i log1p(r_i^2/df) = log(u_0 u_1 u_2 u_3) (one log per four
     // elements; the rare product overflow falls back to log1pf per element), psi_i / c = r_i / u_i with the
     // approximate reciprocal (1 ulp; u >= 1) -- the constant c = (df+1)/df is applied once to the accumulated
@@ -481,10 +471,13 @@ struct PsiEpi {
                                            const Pre& pre, unsigned char* staging, int lane) const {
         float acc = 0.f;
         unsigned char* my = staging + lane * 128;
+        const float* yc = y + col0;
         if (ncols == 32) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-                const float4 o = quad(pre.y + 4 * j, v + 4 * j, acc);
+                const float4 t = __ldg(reinterpret_cast<const float4*>(yc + 4 * j));
+                const float yy[4] = {t.x, t.y, t.z, t.w};
+                const float4 o = quad(yy, v + 4 * j, acc);
                 *reinterpret_cast<float4*>(my + ((j ^ (lane & 7)) << 4)) = o;
             }
         } else {
@@ -494,7 +487,7 @@ struct PsiEpi {
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {      // masked columns: r = 0 -> u = 1 -> no contribution; the store clips them
                     const bool on = 4 * j + q < ncols;
-                    yy[q] = on ? pre.y[4 * j + q] : 0.f;
+                    yy[q] = on ? __ldg(yc + 4 * j + q) : 0.f;
                     aa[q] = on ? v[4 * j + q] : 0.f;
                 }
                 const float4 o = quad(yy, aa, acc);
@@ -571,8 +564,9 @@ static RegLayout reg_layout(long long S, long long N, int D) {
     L.splits = plan_gemm(S, D, L.C, auto_splits(S, D, L.C)).splits;
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t at = o; o += (bytes + 255) & ~(size_t)255; return at; };
+    const bool resident = D <= kTResKTiles * kTBK;     // no pre-split operands needed
     L.off_xs = take(split_bytes(N, D));
-    L.off_bs = take(split_bytes(S, D));
+    L.off_bs = take(resident ? 0 : split_bytes(S, D));
     L.off_psi = take((size_t)S * L.C * 4);
     L.off_rowpart = take((size_t)S * (L.C / 32 + 1) * 4);
     L.off_parts = take((size_t)L.splits * S * D * 4);
@@ -599,11 +593,22 @@ int regression_logp_grad_tf32(const ModelHost* m, const float* b, long long S, d
     double* gacc = (double*)(w + L.off_gacc);
     const float* X = (const float*)m->d_X;
     const float* y = (const float*)m->d_y;
-    SplitMat xs, bs;
-    int rc = split_into(X, N, D, D, (float*)(w + L.off_xs), st, &xs);
-    if (rc != VB_OK) return rc;
-    rc = split_into(b, S, D, D, (float*)(w + L.off_bs), st, &bs);
-    if (rc != VB_OK) return rc;
+    // d <= 128: both GEMMs read X and the coefficient draws as plain fp32 and split them on chip; wider models fall
+    // back to pre-split operands for GEMM1
+    const bool resident = D <= kTResKTiles * kTBK;
+    static int raw_mask = -1;                              // experiments: bit 0 = GEMM1 reads X raw, bit 1 = GEMM2
+    if (raw_mask < 0) { const char* e = getenv("VB_REG_RAW"); raw_mask = e ? atoi(e) : 3; }
+    const bool raw1 = resident && (raw_mask & 1), raw2 = (raw_mask & 2) != 0;
+    SplitMat xs{}, bs{};
+    int rc = VB_OK;
+    if (!raw1 || !raw2) {
+        rc = split_into(X, N, D, D, (float*)(w + L.off_xs), st, &xs);
+        if (rc != VB_OK) return rc;
+    }
+    if (!resident) {
+        rc = split_into(b, S, D, D, (float*)(w + L.off_bs), st, &bs);
+        if (rc != VB_OK) return rc;
+    }
     const double inv_var = 1.0 / (m->prior_sd * m->prior_sd);
     reg_init_kernel<<<grid_for(S * 32, 256, kNumSMs * 8), 256, 0, st>>>(b, S, D, inv_var, out_logp, gacc);
     VB_LAUNCH_CHECK();
@@ -611,15 +616,21 @@ int regression_logp_grad_tf32(const ModelHost* m, const float* b, long long S, d
     const long long mn = S * D;
     for (long long r0 = 0; r0 < N; r0 += L.C) {
         const long long cols = (r0 + L.C <= N) ? L.C : (N - r0);
-        const SplitMat xc{xs.base + r0 * xs.ld, cols, D, xs.ld, xs.plane_stride};
+        const SplitMat xraw{X + r0 * D, cols, D, D, 0};
         // GEMM1 + fused elementwise epilogue; Psi / c leaves through a TMA store as one fp32 plane (S, cols), ld = C
         PsiEpi e1;
         rc = make_raw_tmap(&e1.tmap, psi, S, cols, L.C, 32);
         if (rc != VB_OK) return rc;
         e1.y = y + r0; e1.rowpart = rowpart; e1.n_blocks = n_blocks; e1.inv_df = (float)(1.0 / m->df);
-        // d <= 128: the 128-sample tile of B stays in shared memory while the CTA walks the chunk's row tiles
-        rc = (D <= kTResKTiles * kTBK) ? launch_tf32x3<false, false, PsiEpi, 8, true>(bs, xc, plan_gemm(S, cols, D, 1), e1, st)
-                                       : launch_tf32x3<false, false, PsiEpi, 8>(bs, xc, plan_gemm(S, cols, D, 1), e1, st);
+        // d <= 128: the 128-sample tile of draws stays in tensor memory while the CTA walks the chunk's row tiles
+        const SplitMat xc{xs.base + r0 * xs.ld, cols, D, xs.ld, xs.plane_stride};
+        if (raw1) {
+            rc = launch_tf32x3<false, false, PsiEpi, 16, true, false, true>(SplitMat{b, S, D, D, 0}, xraw, plan_gemm(S, cols, D, 1), e1, st);
+        } else if (resident) {
+            rc = launch_tf32x3<false, false, PsiEpi, 16, true, false, false>(SplitMat{b, S, D, D, 0}, xc, plan_gemm(S, cols, D, 1), e1, st);
+        } else {
+            rc = launch_tf32x3<false, false, PsiEpi, 8>(bs, xc, plan_gemm(S, cols, D, 1), e1, st);
+        }
         if (rc != VB_OK) return rc;
         reg_rowpart_acc_kernel<<<grid_for(S * 32, 256, kNumSMs * 8), 256, 0, st>>>(
             rowpart, S, n_blocks, (int)((cols + 31) / 32), 0.5 * (m->df + 1.0), out_logp);
@@ -627,7 +638,8 @@ int regression_logp_grad_tf32(const ModelHost* m, const float* b, long long S, d
         if (out_grad_or_null) {
             const SplitMat ps{psi, S, cols, L.C, 0};                 // raw fp32: split in shared memory by the GEMM
             const GemmShape shape = plan_gemm(S, D, cols, auto_splits(S, D, cols));
-            rc = launch_tf32x3<false, true, SplitKEpi, 4, false, true>(ps, xc, shape, SplitKEpi{parts, mn, D}, st);
+            rc = raw2 ? launch_tf32x3<false, true, SplitKEpi, 4, false, true, true>(ps, xraw, shape, SplitKEpi{parts, mn, D}, st)
+                      : launch_tf32x3<false, true, SplitKEpi, 4, false, true, false>(ps, xc, shape, SplitKEpi{parts, mn, D}, st);
             if (rc != VB_OK) return rc;
             reg_parts_acc_kernel<<<grid_for(mn, 256, kNumSMs * 4), 256, 0, st>>>(parts, shape.splits, mn, (m->df + 1.0) / m->df, gacc);
             VB_LAUNCH_CHECK();

@@ -23,6 +23,7 @@
 //   Epi::kStaged: the epilogue writes its 32x32 output blocks to a per-warp swizzled shared-memory buffer and
 //          stores them with TMA (full lines, no LSU pressure) instead of 32 scattered sectors per warp store.
 #pragma once
+#include <cstdlib>
 #include <type_traits>
 #include "tc05.cuh"
 
@@ -45,6 +46,7 @@ struct GemmShape {
     long long M, N, K;
     int splits;                 // k splits (>= 1), every split non-empty
     int k_tiles_per_split;
+    int debug = 0;              // experiments only (VB_GEMM_DEBUG): 1 = epilogue body skipped, 2 = MMAs skipped
 };
 
 // Smem offsets of the hi / lo planes and descriptor strides for an operand tile
@@ -65,37 +67,45 @@ template <class E, class = void> struct epi_staged : std::false_type {};
 template <class E> struct epi_staged<E, std::void_t<decltype(E::kStaged)>> : std::bool_constant<E::kStaged> {};
 
 // Shared-memory / tensor-memory plan of one instantiation
-template <class Epi, int EW, bool A_RES, bool A_RAW>
+template <class Epi, int EW, bool A_RES, bool A_RAW, bool B_RAW>
 struct GemmCfg {
     static constexpr bool kStaged = epi_staged<Epi>::value;
     static constexpr bool kATmem = A_RES || A_RAW;                 // A operand read from tensor memory
-    static constexpr int kStages = kATmem ? 4 : kTStages;
-    // ring slot: [A hi+lo | B hi+lo], or [B] (A_RES), or [A raw | B] (A_RAW)
-    static constexpr size_t kSlot = A_RES ? kTOperandBytes : (A_RAW ? kTPlaneBytes + kTOperandBytes : kTStageBytes);
+    static constexpr bool kConvert = A_RAW || B_RAW;               // auxiliary warps touch every k tile
+    // ring slot: [A hi+lo | B hi+lo], or [B] (A_RES), or [A raw | B] (A_RAW); a raw B tile lands in the hi part
+    // of its [hi | lo] region and is split in place
     static constexpr size_t kBOff = A_RES ? 0 : (A_RAW ? kTPlaneBytes : kTOperandBytes);
-    static constexpr uint32_t kSlotTx = (uint32_t)kSlot;           // bytes TMA delivers per slot
+    static constexpr size_t kSlot = kBOff + kTOperandBytes;
+    static constexpr uint32_t kSlotTx = (uint32_t)kBOff + (B_RAW ? kTPlaneBytes : kTOperandBytes);   // bytes TMA delivers per slot
+    static constexpr size_t kStagingBytes = kStaged ? (size_t)EW * kTStagingBytes : 0;
+    // as many ring slots as fit (a 128-wide K is only four k tiles: the ring must hold more than one output tile's
+    // worth of operands or the loads of the next tile cannot start before the current one retires)
+    static constexpr int kFit = (int)((232448 - 1280 - kStagingBytes) / kSlot);
+    static constexpr int kStages = kATmem ? (kFit > 8 ? 8 : kFit) : kTStages;
     static constexpr size_t kStagingOff = (size_t)kStages * kSlot;
-    static constexpr size_t kBarOff = kStagingOff + (kStaged ? (size_t)EW * kTStagingBytes : 0);
+    static constexpr size_t kBarOff = kStagingOff + kStagingBytes;
     static constexpr size_t kSmemBytes = kBarOff + 256 /*barriers*/ + 1024 /*align*/;
     static constexpr int kThreads = 64 + 32 * EW + (kATmem ? 128 : 0);
     static constexpr uint32_t kTmemCols = kATmem ? 512 : 256;      // accumulators 0..255, A operand 256..511
     static constexpr uint32_t kTmemA = 256;
+    static_assert(!A_RAW || kStages <= 4, "TMEM holds four staged A tiles");
     static_assert(kSmemBytes <= 232448, "exceeds the 227 KB of shared memory a CTA may use");
 };
 
-// The A operand as the loader warps of the A_RES variant read it (split planes in global memory)
+// The A operand as the loader warps of the A_RES variant read it (plain fp32 in global memory, split in registers)
 struct AGlobal {
-    const float* base; long long ld, plane_stride;
+    const float* base; long long ld;
 };
 
 // EW = number of epilogue warps (4, 8 or 16): warp (q, h) drains TMEM lane quarter q = warp % 4 and the
 // column blocks h, h + EW/4, ... of the 128-column accumulator.
-template <bool A_MN, bool B_MN, class Epi, int EW = 4, bool A_RES = false, bool A_RAW = false>
-__global__ void __launch_bounds__(GemmCfg<Epi, EW, A_RES, A_RAW>::kThreads, 1)
+template <bool A_MN, bool B_MN, class Epi, int EW = 4, bool A_RES = false, bool A_RAW = false, bool B_RAW = false>
+__global__ void __launch_bounds__(GemmCfg<Epi, EW, A_RES, A_RAW, B_RAW>::kThreads, 1)
 gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                    const GemmShape shape, const AGlobal ag, const __grid_constant__ Epi epi) {
-    using Cfg = GemmCfg<Epi, EW, A_RES, A_RAW>;
-    static_assert(!(A_RES && A_MN) && !(A_RAW && A_MN) && !(A_RES && A_RAW), "unsupported variant combination");
+    using Cfg = GemmCfg<Epi, EW, A_RES, A_RAW, B_RAW>;
+    static_assert(!(A_RES && A_MN) && !(A_RAW && A_MN) && !(A_RES && A_RAW) && !(B_RAW && !Cfg::kATmem),
+                  "unsupported variant combination");
     constexpr int kStages = Cfg::kStages;
     constexpr size_t kSlot = Cfg::kSlot;
     extern __shared__ unsigned char smem_dyn[];
@@ -103,14 +113,14 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
                                                            ~(uintptr_t)1023);
     unsigned char* ring = smem;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kBarOff);
-    uint64_t* full_bar = bars;                      // [4] TMA bytes of the slot landed
-    uint64_t* empty_bar = bars + 4;                 // [4] MMAs reading the slot (and its TMEM A stage) retired
-    uint64_t* conv_bar = bars + 8;                  // [4] A_RAW: the slot's A tile is split and sits in its TMEM stage
-    uint64_t* tmem_full = bars + 12;                // [2]
-    uint64_t* tmem_empty = bars + 14;               // [2]
-    uint64_t* a_full = bars + 16;                   // A_RES: resident A tile written / all MMAs on it retired
-    uint64_t* a_empty = bars + 17;
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 18);
+    uint64_t* full_bar = bars;                      // [8] TMA bytes of the slot landed
+    uint64_t* empty_bar = bars + 8;                 // [8] MMAs reading the slot (and its TMEM A stage) retired
+    uint64_t* conv_bar = bars + 16;                 // [8] raw operands of the slot are split (A in its TMEM stage)
+    uint64_t* tmem_full = bars + 24;                // [2]
+    uint64_t* tmem_empty = bars + 26;               // [2]
+    uint64_t* a_full = bars + 28;                   // A_RES: resident A tile written / all MMAs on it retired
+    uint64_t* a_empty = bars + 29;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 30);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const long long m_tiles = (shape.M + kTBM - 1) / kTBM, n_tiles = (shape.N + kTBN - 1) / kTBN;
@@ -125,7 +135,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         if (!Cfg::kATmem || A_RAW) tc::prefetch_tmap(&tmap_a);
         tc::prefetch_tmap(&tmap_b);
 #pragma unroll
-        for (int s = 0; s < 4; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); mbar_init(&conv_bar[s], 128); }
+        for (int s = 0; s < 8; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); mbar_init(&conv_bar[s], 128); }
         mbar_init(&tmem_full[0], 1); mbar_init(&tmem_full[1], 1);
         mbar_init(&tmem_empty[0], 32 * EW); mbar_init(&tmem_empty[1], 32 * EW);
         mbar_init(a_full, 128); mbar_init(a_empty, 1);
@@ -165,7 +175,12 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
                     } else {
                         tc::tma_load_3d(sa, &tmap_a, &full_bar[stage], k0, m0, 0);
                     }
-                    if (B_MN) {
+                    if (B_RAW && B_MN) {
+#pragma unroll
+                        for (int b = 0; b < 4; ++b) tc::tma_load_2d(sb + b * 8192, &tmap_b, &full_bar[stage], n0 + 32 * b, k0);
+                    } else if (B_RAW) {
+                        tc::tma_load_2d(sb, &tmap_b, &full_bar[stage], k0, n0);
+                    } else if (B_MN) {
 #pragma unroll
                         for (int b = 0; b < 4; ++b) tc::tma_load_3d(sb + b * 8192, &tmap_b, &full_bar[stage], n0 + 32 * b, k0, 0);
                     } else {
@@ -185,6 +200,9 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         uint32_t phase = 0, a_phase = 0;
         int it = 0;
         long long cur_m = -1;
+        const uint32_t tmem_u = __reduce_or_sync(0xffffffffu, tmem_base);      // same value, now provably uniform
+        const uint32_t ring_u = smem_u32(ring);
+        const uint32_t bars_u = smem_u32(bars);
         for (long long w = w_begin; w < w_end; w += w_step, ++it) {
             const int split = (int)(w / (m_tiles * n_tiles));
             const long long kt0 = (long long)split * shape.k_tiles_per_split;
@@ -198,111 +216,133 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
             const int as = it & 1;
             mbar_wait(&tmem_empty[as], (uint32_t)(((it >> 1) & 1) ^ 1));
             tc::fence_after_sync();
-            const uint32_t d_addr = tmem_base + (uint32_t)as * kTBN;
+            const uint32_t d_addr = tmem_u + (uint32_t)as * kTBN;
             bool first = true;
             for (long long kt = kt0; kt < kt1; ++kt) {
                 mbar_wait(&full_bar[stage], phase);
-                if (A_RAW) mbar_wait(&conv_bar[stage], phase);
+                if (Cfg::kConvert) mbar_wait(&conv_bar[stage], phase);
                 tc::fence_after_sync();
-                if (lane == 0) {
-                    const uint32_t slot = smem_u32(ring + (size_t)stage * kSlot);
-                    const uint32_t b_addr = slot + (uint32_t)Cfg::kBOff;
-                    // TMEM A: resident tile = [hi: 128 cols | lo: 128 cols]; staged tile = [hi: 32 | lo: 32] per stage
-                    const uint32_t ta_hi = tmem_base + Cfg::kTmemA + (A_RES ? (uint32_t)kt * kTBK : (uint32_t)stage * 2 * kTBK);
-                    const uint32_t ta_lo = ta_hi + (A_RES ? (uint32_t)kTResKTiles * kTBK : (uint32_t)kTBK);
+                // All 32 lanes run this code converged; one lane is elected inside each MMA / commit asm.  Issuing
+                // under `if (lane == 0)` makes the compiler wrap every MMA in an elect / R2UR.BROADCAST / branch loop
+                // (~100 clk per MMA: longer than the ~90 clk the 128x128x8 MMA itself takes).
+                const uint32_t slot = ring_u + (uint32_t)stage * (uint32_t)kSlot;
+                const uint32_t b_addr = slot + (uint32_t)Cfg::kBOff;
+                // TMEM A: resident tile = [hi: 128 cols | lo: 128 cols]; staged tile = [hi: 32 | lo: 32] per stage
+                const uint32_t ta_hi = tmem_u + Cfg::kTmemA + (A_RES ? (uint32_t)kt * kTBK : (uint32_t)stage * 2 * kTBK);
+                const uint32_t ta_lo = ta_hi + (A_RES ? (uint32_t)kTResKTiles * kTBK : (uint32_t)kTBK);
+                if (!(shape.debug & 2)) {
 #pragma unroll
                     for (int k = 0; k < kTBK / 8; ++k) {
                         const uint64_t b_hi = tc::smem_desc_sw128(b_addr + k * LB::k_step, LB::lbo, LB::sbo, LB::layout_type);
                         const uint64_t b_lo = tc::smem_desc_sw128(b_addr + LB::lo_offset + k * LB::k_step, LB::lbo, LB::sbo, LB::layout_type);
                         const bool acc0 = !(first && k == 0);
                         if constexpr (Cfg::kATmem) {
-                            tc::mma_tf32_ts(d_addr, ta_lo + k * 8, b_hi, idesc, acc0);         // small terms first
-                            tc::mma_tf32_ts(d_addr, ta_hi + k * 8, b_lo, idesc, true);
-                            tc::mma_tf32_ts(d_addr, ta_hi + k * 8, b_hi, idesc, true);
+                            tc::mma_tf32_ts_warp(d_addr, ta_lo + k * 8, b_hi, idesc, acc0);    // small terms first
+                            tc::mma_tf32_ts_warp(d_addr, ta_hi + k * 8, b_lo, idesc, true);
+                            tc::mma_tf32_ts_warp(d_addr, ta_hi + k * 8, b_hi, idesc, true);
                         } else {
                             const uint64_t a_hi = tc::smem_desc_sw128(slot + k * LA::k_step, LA::lbo, LA::sbo, LA::layout_type);
                             const uint64_t a_lo = tc::smem_desc_sw128(slot + LA::lo_offset + k * LA::k_step, LA::lbo, LA::sbo, LA::layout_type);
-                            tc::mma_tf32(d_addr, a_lo, b_hi, idesc, acc0);
-                            tc::mma_tf32(d_addr, a_hi, b_lo, idesc, true);
-                            tc::mma_tf32(d_addr, a_hi, b_hi, idesc, true);
+                            tc::mma_tf32_warp(d_addr, a_lo, b_hi, idesc, acc0);
+                            tc::mma_tf32_warp(d_addr, a_hi, b_lo, idesc, true);
+                            tc::mma_tf32_warp(d_addr, a_hi, b_hi, idesc, true);
                         }
                     }
-                    tc::mma_commit(&empty_bar[stage]);        // frees the smem slot when these MMAs retire
                 }
-                __syncwarp();
+                tc::mma_commit_warp(bars_u + (uint32_t)(8 + stage) * 8);        // empty_bar[stage]: frees the slot when these MMAs retire
                 first = false;
                 if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
-            if (lane == 0) {
-                tc::mma_commit(&tmem_full[as]);               // accumulator ready for the epilogue
-                if (A_RES && w + 1 < w_end && (w + 1) / n_tiles != cur_m) tc::mma_commit(a_empty);   // last use of this A tile
-            }
-            __syncwarp();
+            tc::mma_commit_warp(bars_u + (uint32_t)(24 + as) * 8);            // tmem_full[as]: accumulator ready
+            if (A_RES && w + 1 < w_end && (w + 1) / n_tiles != cur_m) tc::mma_commit_warp(bars_u + 29 * 8);   // a_empty: last use of this A tile
         }
     } else if (Cfg::kATmem && warp >= 2 + EW) {
-        // ===================================================== auxiliary warps: A operand -> tensor memory
+        // ===================================================== auxiliary warps: operand preparation
         // Four warps, one per TMEM lane quarter (a warp may only touch lanes 32 (warp % 4) ..+31): thread = A row.
+        //   A_RES: at every change of m tile, read this thread's raw fp32 A row, split it and write hi / lo to TMEM
+        //   A_RAW: per k tile, the raw A tile TMA put into the slot (128-byte swizzle: 16-byte unit j of row r at
+        //          r*128 + ((j ^ (r & 7)) << 4)) -> tf32 hi / lo -> the slot's TMEM stage
+        //   B_RAW: per k tile, split the raw B tile in place (element-wise, so independent of the swizzle: every
+        //          16-byte unit is rewritten as hi and mirrored as lo at the plane offset of the layout)
         const int qa = warp & 3;
         const uint32_t lane_base = (uint32_t)(qa * 32) << 16;
-        if constexpr (A_RES) {
-            // resident tile: read the split planes of this thread's row from global memory (K <= 128 floats per plane)
-            uint32_t a_phase = 0;
-            long long cur_m = -1;
-            for (long long w = w_begin; w < w_end; w += w_step) {
+        const int tid_c = (int)threadIdx.x - (64 + 32 * EW);
+        using LB = OperandLayout<B_MN>;
+        int stage = 0;
+        uint32_t phase = 0, a_phase = 0;
+        long long cur_m = -1;
+        for (long long w = w_begin; w < w_end; w += w_step) {
+            if constexpr (A_RES) {
                 const long long m = w / n_tiles;
-                if (m == cur_m) continue;
-                if (cur_m >= 0) { mbar_wait(a_empty, a_phase); a_phase ^= 1; tc::fence_after_sync(); }
-                cur_m = m;
-                const long long row = m * kTBM + qa * 32 + lane;
-                const bool live = row < shape.M;
-#pragma unroll 1
-                for (int plane = 0; plane < 2; ++plane) {
-                    const float* src = ag.base + (size_t)plane * ag.plane_stride + row * ag.ld;
+                if (m != cur_m) {
+                    if (cur_m >= 0) { mbar_wait(a_empty, a_phase); a_phase ^= 1; tc::fence_after_sync(); }
+                    cur_m = m;
+                    const long long row = m * kTBM + qa * 32 + lane;
+                    const bool live = row < shape.M;
+                    const float* src = ag.base + row * ag.ld;
 #pragma unroll 1
                     for (int kt = 0; kt < kTResKTiles; ++kt) {
-                        float v[32];
+                        float hi[32], lo[32];
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
                             const int c = kt * kTBK + 4 * j;
                             float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
                             if (live && c < shape.K) t = __ldg(reinterpret_cast<const float4*>(src + c));
-                            v[4 * j] = t.x; v[4 * j + 1] = t.y; v[4 * j + 2] = t.z; v[4 * j + 3] = t.w;
+                            tc::split_tf32_fast(t.x, hi[4 * j], lo[4 * j]);
+                            tc::split_tf32_fast(t.y, hi[4 * j + 1], lo[4 * j + 1]);
+                            tc::split_tf32_fast(t.z, hi[4 * j + 2], lo[4 * j + 2]);
+                            tc::split_tf32_fast(t.w, hi[4 * j + 3], lo[4 * j + 3]);
                         }
-                        tc::tmem_st_32x32(tmem_base + lane_base + Cfg::kTmemA + (uint32_t)(plane * kTResKTiles * kTBK + kt * kTBK), v);
+                        const uint32_t ta = tmem_base + lane_base + Cfg::kTmemA + (uint32_t)(kt * kTBK);
+                        tc::tmem_st_32x32(ta, hi);
+                        tc::tmem_st_32x32(ta + kTResKTiles * kTBK, lo);
                     }
+                    tc::tmem_st_wait();
+                    tc::fence_before_sync();
+                    mbar_arrive(a_full);
                 }
-                tc::tmem_st_wait();
-                tc::fence_before_sync();
-                mbar_arrive(a_full);
             }
-        } else {
-            // staged tile: the raw fp32 tile TMA put into the slot (128-byte swizzle: 16-byte unit j of row r at
-            // r*128 + ((j ^ (r & 7)) << 4)) -> tf32 hi / lo -> this slot's TMEM stage
-            int stage = 0;
-            uint32_t phase = 0;
-            const int r = qa * 32 + lane;
-            for (long long w = w_begin; w < w_end; w += w_step) {
+            if constexpr (Cfg::kConvert) {
                 const int split = (int)(w / (m_tiles * n_tiles));
                 const long long kt0 = (long long)split * shape.k_tiles_per_split;
                 long long kt1 = kt0 + shape.k_tiles_per_split;
                 if (kt1 > k_tiles_total) kt1 = k_tiles_total;
                 for (long long kt = kt0; kt < kt1; ++kt) {
                     mbar_wait(&full_bar[stage], phase);
-                    const unsigned char* my = ring + (size_t)stage * kSlot + r * 128;
-                    float hi[32], lo[32];
+                    unsigned char* slot = ring + (size_t)stage * kSlot;
+                    if constexpr (A_RAW) {
+                        const unsigned char* my = slot + (qa * 32 + lane) * 128;
+                        float hi[32], lo[32];
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        const float4 x = *reinterpret_cast<const float4*>(my + ((j ^ (lane & 7)) << 4));
-                        tc::split_tf32(x.x, hi[4 * j], lo[4 * j]);
-                        tc::split_tf32(x.y, hi[4 * j + 1], lo[4 * j + 1]);
-                        tc::split_tf32(x.z, hi[4 * j + 2], lo[4 * j + 2]);
-                        tc::split_tf32(x.w, hi[4 * j + 3], lo[4 * j + 3]);
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 x = *reinterpret_cast<const float4*>(my + ((j ^ (lane & 7)) << 4));
+                            tc::split_tf32_fast(x.x, hi[4 * j], lo[4 * j]);
+                            tc::split_tf32_fast(x.y, hi[4 * j + 1], lo[4 * j + 1]);
+                            tc::split_tf32_fast(x.z, hi[4 * j + 2], lo[4 * j + 2]);
+                            tc::split_tf32_fast(x.w, hi[4 * j + 3], lo[4 * j + 3]);
+                        }
+                        const uint32_t ta = tmem_base + lane_base + Cfg::kTmemA + (uint32_t)stage * 2 * kTBK;
+                        tc::tmem_st_32x32(ta, hi);
+                        tc::tmem_st_32x32(ta + kTBK, lo);
                     }
-                    const uint32_t ta = tmem_base + lane_base + Cfg::kTmemA + (uint32_t)stage * 2 * kTBK;
-                    tc::tmem_st_32x32(ta, hi);
-                    tc::tmem_st_32x32(ta + kTBK, lo);
-                    tc::tmem_st_wait();
-                    tc::fence_before_sync();
+                    if (B_RAW && !(shape.debug & 8)) {
+                        unsigned char* sb = slot + Cfg::kBOff;
+#pragma unroll
+                        for (int i = 0; i < (int)(kTPlaneBytes / 16 / 128); ++i) {
+                            const int u = tid_c + i * 128;
+                            // K-major: [hi 16 KB | lo 16 KB]; MN-major: four 8 KB blocks of [hi 4 KB | lo 4 KB]
+                            const uint32_t off = B_MN ? (uint32_t)((u >> 8) * 8192 + (u & 255) * 16) : (uint32_t)u * 16;
+                            float4* hp = reinterpret_cast<float4*>(sb + off);
+                            const float4 x = *hp;
+                            float4 hv, lv;
+                            tc::split_tf32_fast(x.x, hv.x, lv.x); tc::split_tf32_fast(x.y, hv.y, lv.y);
+                            tc::split_tf32_fast(x.z, hv.z, lv.z); tc::split_tf32_fast(x.w, hv.w, lv.w);
+                            *hp = hv;
+                            *reinterpret_cast<float4*>(sb + off + LB::lo_offset) = lv;
+                        }
+                        if (!(shape.debug & 4)) tc::fence_proxy_async_smem();
+                    }
+                    if constexpr (A_RAW) { tc::tmem_st_wait(); tc::fence_before_sync(); }
                     mbar_arrive(&conv_bar[stage]);
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
@@ -333,6 +373,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
                 if (live) pre = epi.prefetch(row, col0, (int)ncols);
                 float v[32];
                 tc::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * kTBN + c * 32), v);
+                if (shape.debug & 1) continue;
                 if constexpr (Cfg::kStaged) {
                     if (lane == 0) tc::bulk_wait_read0();      // the previous store has finished reading the buffer
                     __syncwarp();
@@ -380,22 +421,23 @@ inline int auto_splits(long long M, long long N, long long K) {
 
 int tf32x3_num_sms();
 
-template <bool A_MN, bool B_MN, class Epi, int EW = 4, bool A_RES = false, bool A_RAW = false>
+template <bool A_MN, bool B_MN, class Epi, int EW = 4, bool A_RES = false, bool A_RAW = false, bool B_RAW = false>
 static int launch_tf32x3(const SplitMat& A, const SplitMat& B, const GemmShape& shape, const Epi& epi,
                          cudaStream_t st) {
-    using Cfg = GemmCfg<Epi, EW, A_RES, A_RAW>;
-    if (A_RES && (shape.splits != 1 || shape.K > (long long)kTResKTiles * kTBK || (shape.K % 4) || (A.ld % 4) || (A.plane_stride % 4) ||
+    using Cfg = GemmCfg<Epi, EW, A_RES, A_RAW, B_RAW>;
+    if (A_RES && (shape.splits != 1 || shape.K > (long long)kTResKTiles * kTBK || (shape.K % 4) || (A.ld % 4) ||
                   (reinterpret_cast<uintptr_t>(A.base) & 15u)))
         return VB_ERR_ARG;
     CUtensorMap ta, tb;
     int rc = VB_OK;
     if (A_RES) memset(&ta, 0, sizeof(ta));               // A is read by the loader warps, not by TMA
-    else if (A_RAW) rc = make_raw_tmap(&ta, A.base, A.rows, A.cols, A.ld, kTBM);
+    else if (A_RAW) rc = make_raw_tmap(&ta, A.base, A.rows, A.cols, A.ld, kTBM, false);
     else rc = make_split_tmap(&ta, A.base, A.rows, A.cols, A.ld, A.plane_stride, A_MN ? kTBK : kTBM, A_MN);
     if (rc != VB_OK) return rc;
-    rc = make_split_tmap(&tb, B.base, B.rows, B.cols, B.ld, B.plane_stride, B_MN ? kTBK : kTBN, B_MN);
+    rc = B_RAW ? make_raw_tmap(&tb, B.base, B.rows, B.cols, B.ld, B_MN ? kTBK : kTBN, B_MN)
+               : make_split_tmap(&tb, B.base, B.rows, B.cols, B.ld, B.plane_stride, B_MN ? kTBK : kTBN, B_MN);
     if (rc != VB_OK) return rc;
-    auto kern = gemm_tf32x3_kernel<A_MN, B_MN, Epi, EW, A_RES, A_RAW>;
+    auto kern = gemm_tf32x3_kernel<A_MN, B_MN, Epi, EW, A_RES, A_RAW, B_RAW>;
     static bool configured = false;
     if (!configured) {
         VB_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::kSmemBytes));
@@ -404,7 +446,9 @@ static int launch_tf32x3(const SplitMat& A, const SplitMat& B, const GemmShape& 
     const long long total = ((shape.M + kTBM - 1) / kTBM) * ((shape.N + kTBN - 1) / kTBN) * shape.splits;
     long long grid = tf32x3_num_sms();
     if (grid > total) grid = total;
-    kern<<<(unsigned)grid, Cfg::kThreads, Cfg::kSmemBytes, st>>>(ta, tb, shape, AGlobal{A.base, A.ld, A.plane_stride}, epi);
+    GemmShape sh = shape;
+    { const char* e = getenv("VB_GEMM_DEBUG"); if (e && Cfg::kStaged) sh.debug = atoi(e); }
+    kern<<<(unsigned)grid, Cfg::kThreads, Cfg::kSmemBytes, st>>>(ta, tb, sh, AGlobal{A.base, A.ld}, epi);
     VB_LAUNCH_CHECK();
     return VB_OK;
 }

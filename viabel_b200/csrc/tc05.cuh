@@ -134,6 +134,40 @@ __device__ __forceinline__ void mma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, ui
         "}\n"
         :: "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"((uint32_t)accumulate) : "memory");
 }
+// Warp-collective forms: called by ALL 32 converged lanes with warp-uniform operands; one elected lane issues.
+// Keeping the election inside the asm leaves the C++ control flow convergent, so the compiler holds the operands
+// in uniform registers instead of handing each one over from a vector register before every MMA.
+__device__ __forceinline__ void mma_tf32_ts_warp(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                                 bool accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p, e;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "elect.sync _|e, 0xffffffff;\n"
+        "@e tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n"
+        "}\n"
+        :: "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"((uint32_t)accumulate) : "memory");
+}
+__device__ __forceinline__ void mma_tf32_warp(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                              bool accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p, e;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "elect.sync _|e, 0xffffffff;\n"
+        "@e tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
+        "}\n"
+        :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"((uint32_t)accumulate) : "memory");
+}
+__device__ __forceinline__ void mma_commit_warp(uint32_t bar_smem_addr) {
+    asm volatile(
+        "{\n"
+        ".reg .pred e;\n"
+        "elect.sync _|e, 0xffffffff;\n"
+        "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n"
+        "}\n"
+        :: "r"(bar_smem_addr) : "memory");
+}
 // mbarrier arrive once all previously issued tcgen05.mma of this thread have completed
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
@@ -145,6 +179,12 @@ __device__ __forceinline__ float to_tf32(float x) {
     uint32_t r;
     asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
     return __uint_as_float(r);
+}
+// Cheap split for finite data: hi = round-half-away to tf32 by integer add + mask, lo = x - hi left unrounded
+// (the tensor core reads only the upper 19 bits of a tf32 operand, i.e. truncates lo: error 2^-22 |x|)
+__device__ __forceinline__ void split_tf32_fast(float x, float& hi, float& lo) {
+    hi = __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
+    lo = x - hi;
 }
 // x = hi + lo + O(2^-22 |x|), both exactly representable in tf32
 __device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
@@ -171,6 +211,7 @@ int make_split_tmap(CUtensorMap* out, const float* base, long long rows, long lo
 // A plain fp32 (rows, cols) row-major matrix: 2-D map, (32, box_rows) box, 128-byte swizzle.  Loaded tiles have
 // the layout of ONE plane of a K-major split tile (so a tile can be split into hi / lo in shared memory);
 // the same map stores (32 x box_rows) tiles staged in shared memory.
-int make_raw_tmap(CUtensorMap* out, const float* base, long long rows, long long cols, long long ld, int box_rows);
+int make_raw_tmap(CUtensorMap* out, const float* base, long long rows, long long cols, long long ld, int box_rows,
+                  bool atom32 = false);
 
 }  // namespace vb
