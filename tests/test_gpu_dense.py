@@ -91,6 +91,39 @@ def test_regression_plugin_tensor_path(N, d, n):
     np.testing.assert_allclose(lp_only, lp, rtol=1e-12)
 
 
+@pytest.mark.parametrize('raw', ['1', '2', '3'])
+def test_regression_tensor_path_raw_operand_variants(raw, monkeypatch):
+    """VB_REG_RAW selects the GEMM variants that read X as plain fp32 and split it into tf32 hi / lo on chip
+    (converter warps; GEMM1 bit 0, GEMM2 bit 1).  Same stated tolerance as the default pre-split path."""
+    from viabel_b200 import models
+    monkeypatch.setenv('VB_REG_RAW', raw)
+    N, d, n = 5000, 64, 200
+    X, y, bt = _regression(N, d)
+    X32, y32 = X.astype(np.float32), y.astype(np.float32)
+    model = models.StudentTRegression(X32, y32, df=40.0, dtype='f32')
+    omodel = mm.StudentTRegression(X32.astype(np.float64), y32.astype(np.float64), 40.0)
+    b = (bt + 0.1 * np.random.RandomState(3).randn(n, d)).astype(np.float32)
+    lp, g = model.logp_and_grad(b, dtype='f32')
+    olp, og = omodel.logp_and_grad(b.astype(np.float64))
+    assert rel(lp, olp) < 1e-5, rel(lp, olp)
+    assert rel(g, og) < 2e-5, rel(g, og)
+
+
+def test_regression_tensor_path_wide_model():
+    """d > 128: the coefficient tile no longer fits tensor memory, GEMM1 falls back to streamed split operands."""
+    from viabel_b200 import models
+    N, d, n = 3000, 160, 130
+    X, y, bt = _regression(N, d)
+    X32, y32 = X.astype(np.float32), y.astype(np.float32)
+    model = models.StudentTRegression(X32, y32, df=40.0, dtype='f32')
+    omodel = mm.StudentTRegression(X32.astype(np.float64), y32.astype(np.float64), 40.0)
+    b = (bt + 0.1 * np.random.RandomState(3).randn(n, d)).astype(np.float32)
+    lp, g = model.logp_and_grad(b, dtype='f32')
+    olp, og = omodel.logp_and_grad(b.astype(np.float64))
+    assert rel(lp, olp) < 1e-5, rel(lp, olp)
+    assert rel(g, og) < 2e-5, rel(g, og)
+
+
 def test_mean_field_regression_tensor_path_klvi():
     """Config-2 in miniature through the public objective with fp32 storage."""
     from viabel_b200 import models, vb

@@ -419,8 +419,11 @@ struct PsiEpi {
     const float* __restrict__ y;                     // y + r0
     float* __restrict__ rowpart; int n_blocks;       // (S, C/32) partial sums of log1p(r^2/df)
     float inv_df;
-    // y is indexed by the column: every lane of the warp reads the same address (one sector per request, L1
-    // hits), so it is read where it is used instead of being held in 32 registers across the TMEM load.
+    // y is indexed by the column: the kernel stages the tile's 128-float segment of it in shared memory (bulk copy
+    // issued when the accumulator stage frees up), so the epilogue reads it with broadcast LDS instead of waiting
+    // for L2 in the middle of the arithmetic.
+    static constexpr bool kColVec = true;
+    __device__ __forceinline__ const float* colvec() const { return y; }
     struct Pre {};
     __device__ __forceinline__ Pre prefetch(long long, long long, int) const { return Pre{}; }
     // Four elements at a time: u_i = 1 + r_i^2/df, sum_i log1p(r_i^2/df) = log(u_0 u_1 u_2 u_3) (one log per four
@@ -444,57 +447,85 @@ struct PsiEpi {
         q = fmaf(f, q * f, f);
         return fmaf((float)(int)e, 8.262958294867817e-08f, q);     // e * 2^-23 * ln 2
     }
-    __device__ __forceinline__ float4 quad(const float* yv, const float* av, float& acc) const {
-        float r[4], u[4], o[4];
+    // packed fp32x2 arithmetic (sm_100 FADD2 / FMUL2 / FFMA2): the epilogue is issue-bound, not pipe-bound
+    static __device__ __forceinline__ float2 log_ge1_x2(float2 p) {
+        const uint32_t bx = __float_as_uint(p.x), by = __float_as_uint(p.y);
+        const uint32_t ex = (bx - 0x3f2aaaabu) & 0xff800000u, ey = (by - 0x3f2aaaabu) & 0xff800000u;
+        const float2 f = __fadd2_rn(make_float2(__uint_as_float(bx - ex), __uint_as_float(by - ey)), make_float2(-1.f, -1.f));
+        float2 q = make_float2(0.1440092772245407f, 0.1440092772245407f);
+        q = __ffma2_rn(q, f, make_float2(-0.15269480645656586f, -0.15269480645656586f));
+        q = __ffma2_rn(q, f, make_float2(0.13915356993675232f, 0.13915356993675232f));
+        q = __ffma2_rn(q, f, make_float2(-0.1644672304391861f, -0.1644672304391861f));
+        q = __ffma2_rn(q, f, make_float2(0.20016367733478546f, 0.20016367733478546f));
+        q = __ffma2_rn(q, f, make_float2(-0.2500529885292053f, -0.2500529885292053f));
+        q = __ffma2_rn(q, f, make_float2(0.33333104848861694f, 0.33333104848861694f));
+        q = __ffma2_rn(q, f, make_float2(-0.5f, -0.5f));
+        q = __ffma2_rn(f, __fmul2_rn(q, f), f);
+        return __ffma2_rn(make_float2((float)(int)ex, (float)(int)ey), make_float2(8.262958294867817e-08f, 8.262958294867817e-08f), q);
+    }
+    // eight elements: two products of four, one packed log
+    __device__ __forceinline__ void oct(const float* yv, const float* av, float2& acc, float4& o0, float4& o1) const {
+        const float2 neg1 = make_float2(-1.f, -1.f), one = make_float2(1.f, 1.f), idf = make_float2(inv_df, inv_df);
+        float2 r[4], u[4];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            r[q] = yv[q] - av[q];
-            u[q] = fmaf(r[q] * r[q], inv_df, 1.f);
+        for (int i = 0; i < 4; ++i) {
+            r[i] = __ffma2_rn(make_float2(av[2 * i], av[2 * i + 1]), neg1, make_float2(yv[2 * i], yv[2 * i + 1]));
+            u[i] = __ffma2_rn(__fmul2_rn(r[i], r[i]), idf, one);
         }
-        const float p = (u[0] * u[1]) * (u[2] * u[3]);
-        if (p < 3.0e38f) {
-            acc += log_ge1(p);
+        const float2 pa = __fmul2_rn(u[0], u[1]), pb = __fmul2_rn(u[2], u[3]);
+        const float2 p = __fmul2_rn(make_float2(pa.x, pb.x), make_float2(pa.y, pb.y));
+        if (p.x < 3.0e38f && p.y < 3.0e38f) {
+            acc = __fadd2_rn(acc, log_ge1_x2(p));
         } else {
-            acc += log1p_sum4_slow(r[0], r[1], r[2], r[3], inv_df);
+            acc.x += log1p_sum4_slow(r[0].x, r[0].y, r[1].x, r[1].y, inv_df);
+            acc.y += log1p_sum4_slow(r[2].x, r[2].y, r[3].x, r[3].y, inv_df);
         }
+        float2 o[4];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            float inv;
-            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(u[q]));
-            o[q] = r[q] * inv;
+        for (int i = 0; i < 4; ++i) {
+            float ix, iy;
+            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ix) : "f"(u[i].x));
+            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(iy) : "f"(u[i].y));
+            o[i] = __fmul2_rn(r[i], make_float2(ix, iy));
         }
-        return make_float4(o[0], o[1], o[2], o[3]);
+        o0 = make_float4(o[0].x, o[0].y, o[1].x, o[1].y);
+        o1 = make_float4(o[2].x, o[2].y, o[3].x, o[3].y);
     }
     // Thread = one row of the warp's 32 x 32 block.  The block is written in the 128-byte-swizzled layout the
     // TMA store expects: 16-byte unit j of row r lives at r*128 + ((j ^ (r & 7)) << 4) (conflict-free STS.128).
     __device__ __forceinline__ void staged(long long row, long long col0, float (&v)[32], int ncols, int,
-                                           const Pre& pre, unsigned char* staging, int lane) const {
-        float acc = 0.f;
+                                           const Pre& pre, unsigned char* staging, int lane, const float* ysm) const {
+        float2 acc = make_float2(0.f, 0.f);
         unsigned char* my = staging + lane * 128;
         const float* yc = y + col0;
         if (ncols == 32) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const float4 t = __ldg(reinterpret_cast<const float4*>(yc + 4 * j));
-                const float yy[4] = {t.x, t.y, t.z, t.w};
-                const float4 o = quad(yy, v + 4 * j, acc);
-                *reinterpret_cast<float4*>(my + ((j ^ (lane & 7)) << 4)) = o;
+            for (int j = 0; j < 8; j += 2) {
+                const float4 t0 = *reinterpret_cast<const float4*>(ysm + 4 * j);
+                const float4 t1 = *reinterpret_cast<const float4*>(ysm + 4 * j + 4);
+                const float yy[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
+                float4 o0, o1;
+                oct(yy, v + 4 * j, acc, o0, o1);
+                *reinterpret_cast<float4*>(my + ((j ^ (lane & 7)) << 4)) = o0;
+                *reinterpret_cast<float4*>(my + (((j + 1) ^ (lane & 7)) << 4)) = o1;
             }
         } else {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                float yy[4], aa[4];
+            for (int j = 0; j < 8; j += 2) {
+                float yy[8], aa[8];
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {      // masked columns: r = 0 -> u = 1 -> no contribution; the store clips them
+                for (int q = 0; q < 8; ++q) {      // masked columns: r = 0 -> u = 1 -> no contribution; the store clips them
                     const bool on = 4 * j + q < ncols;
                     yy[q] = on ? __ldg(yc + 4 * j + q) : 0.f;
                     aa[q] = on ? v[4 * j + q] : 0.f;
                 }
-                const float4 o = quad(yy, aa, acc);
-                *reinterpret_cast<float4*>(my + ((j ^ (lane & 7)) << 4)) = o;
+                float4 o0, o1;
+                oct(yy, aa, acc, o0, o1);
+                *reinterpret_cast<float4*>(my + ((j ^ (lane & 7)) << 4)) = o0;
+                *reinterpret_cast<float4*>(my + (((j + 1) ^ (lane & 7)) << 4)) = o1;
             }
         }
-        rowpart[row * n_blocks + (col0 >> 5)] = acc;
+        rowpart[row * n_blocks + (col0 >> 5)] = acc.x + acc.y;
     }
 };
 // logp[s] -= (df+1)/2 * sum_blocks rowpart[s][.]   (fp64 accumulation across blocks and chunks)
@@ -596,8 +627,11 @@ int regression_logp_grad_tf32(const ModelHost* m, const float* b, long long S, d
     // d <= 128: both GEMMs read X and the coefficient draws as plain fp32 and split them on chip; wider models fall
     // back to pre-split operands for GEMM1
     const bool resident = D <= kTResKTiles * kTBK;
-    static int raw_mask = -1;                              // experiments: bit 0 = GEMM1 reads X raw, bit 1 = GEMM2
-    if (raw_mask < 0) { const char* e = getenv("VB_REG_RAW"); raw_mask = e ? atoi(e) : 3; }
+    // VB_REG_RAW: bit 0 = GEMM1 reads X as plain fp32 and splits it in shared memory, bit 1 = same for GEMM2.
+    // Default 0: measured on B200 the pre-split X planes are faster (14.0 vs 16.1 ms / step at N = 2^20, d = 128):
+    // halving the L2 -> SM traffic does not pay for the extra shared-memory pass of the converter warps.
+    int raw_mask = 0;
+    { const char* e = getenv("VB_REG_RAW"); if (e) raw_mask = atoi(e); }
     const bool raw1 = resident && (raw_mask & 1), raw2 = (raw_mask & 2) != 0;
     SplitMat xs{}, bs{};
     int rc = VB_OK;

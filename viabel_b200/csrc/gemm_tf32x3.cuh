@@ -63,6 +63,8 @@ struct OperandLayout {
     static constexpr uint32_t k_step = MN_MAJOR ? 1024u : 32u;     // per UMMA_K = 8 fp32
 };
 
+template <class E, class = void> struct epi_colvec : std::false_type {};
+template <class E> struct epi_colvec<E, std::void_t<decltype(E::kColVec)>> : std::bool_constant<E::kColVec> {};
 template <class E, class = void> struct epi_staged : std::false_type {};
 template <class E> struct epi_staged<E, std::void_t<decltype(E::kStaged)>> : std::bool_constant<E::kStaged> {};
 
@@ -70,6 +72,7 @@ template <class E> struct epi_staged<E, std::void_t<decltype(E::kStaged)>> : std
 template <class Epi, int EW, bool A_RES, bool A_RAW, bool B_RAW>
 struct GemmCfg {
     static constexpr bool kStaged = epi_staged<Epi>::value;
+    static constexpr bool kColVec = epi_colvec<Epi>::value;     // the epilogue reads a per-column vector (staged per tile)
     static constexpr bool kATmem = A_RES || A_RAW;                 // A operand read from tensor memory
     static constexpr bool kConvert = A_RAW || B_RAW;               // auxiliary warps touch every k tile
     // ring slot: [A hi+lo | B hi+lo], or [B] (A_RES), or [A raw | B] (A_RAW); a raw B tile lands in the hi part
@@ -77,14 +80,15 @@ struct GemmCfg {
     static constexpr size_t kBOff = A_RES ? 0 : (A_RAW ? kTPlaneBytes : kTOperandBytes);
     static constexpr size_t kSlot = kBOff + kTOperandBytes;
     static constexpr uint32_t kSlotTx = (uint32_t)kBOff + (B_RAW ? kTPlaneBytes : kTOperandBytes);   // bytes TMA delivers per slot
-    static constexpr size_t kStagingBytes = kStaged ? (size_t)EW * kTStagingBytes : 0;
+    static constexpr size_t kColVecBytes = kColVec ? 2 * kTBN * 4 : 0;          // one 128-float segment per accumulator stage
+    static constexpr size_t kStagingBytes = (kStaged ? (size_t)EW * kTStagingBytes : 0) + kColVecBytes;
     // as many ring slots as fit (a 128-wide K is only four k tiles: the ring must hold more than one output tile's
     // worth of operands or the loads of the next tile cannot start before the current one retires)
-    static constexpr int kFit = (int)((232448 - 1280 - kStagingBytes) / kSlot);
+    static constexpr int kFit = (int)((232448 - 1344 - kStagingBytes) / kSlot);
     static constexpr int kStages = kATmem ? (kFit > 8 ? 8 : kFit) : kTStages;
     static constexpr size_t kStagingOff = (size_t)kStages * kSlot;
     static constexpr size_t kBarOff = kStagingOff + kStagingBytes;
-    static constexpr size_t kSmemBytes = kBarOff + 256 /*barriers*/ + 1024 /*align*/;
+    static constexpr size_t kSmemBytes = kBarOff + 320 /*barriers*/ + 1024 /*align*/;
     static constexpr int kThreads = 64 + 32 * EW + (kATmem ? 128 : 0);
     static constexpr uint32_t kTmemCols = kATmem ? 512 : 256;      // accumulators 0..255, A operand 256..511
     static constexpr uint32_t kTmemA = 256;
@@ -120,7 +124,9 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     uint64_t* tmem_empty = bars + 26;               // [2]
     uint64_t* a_full = bars + 28;                   // A_RES: resident A tile written / all MMAs on it retired
     uint64_t* a_empty = bars + 29;
-    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 30);
+    uint64_t* vec_full = bars + 30;                 // [2] kColVec: the tile's column-vector segment landed
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 32);
+    float* colvec_sm = reinterpret_cast<float*>(smem + Cfg::kBarOff - Cfg::kColVecBytes);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const long long m_tiles = (shape.M + kTBM - 1) / kTBM, n_tiles = (shape.N + kTBN - 1) / kTBN;
@@ -139,6 +145,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
         mbar_init(&tmem_full[0], 1); mbar_init(&tmem_full[1], 1);
         mbar_init(&tmem_empty[0], 32 * EW); mbar_init(&tmem_empty[1], 32 * EW);
         mbar_init(a_full, 128); mbar_init(a_empty, 1);
+        mbar_init(&vec_full[0], 1); mbar_init(&vec_full[1], 1);
         mbar_fence_init();
     }
     if (warp == 1) tc::tmem_alloc<Cfg::kTmemCols>(tmem_ptr);
@@ -216,6 +223,18 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
             const int as = it & 1;
             mbar_wait(&tmem_empty[as], (uint32_t)(((it >> 1) & 1) ^ 1));
             tc::fence_after_sync();
+            if constexpr (Cfg::kColVec) {
+                // the epilogue of the tile that used this accumulator stage is done, so its vector buffer is free
+                const long long n0v = ((w % (m_tiles * n_tiles)) % n_tiles) * kTBN;
+                long long nv = shape.N - n0v;
+                if (nv > kTBN) nv = kTBN;
+                const uint32_t vbytes = (uint32_t)(nv / 4) * 16;
+                if (lane == 0 && vbytes) {
+                    mbar_expect_tx(&vec_full[as], vbytes);
+                    bulk_g2s(colvec_sm + as * kTBN, epi.colvec() + n0v, vbytes, &vec_full[as]);
+                }
+                __syncwarp();
+            }
             const uint32_t d_addr = tmem_u + (uint32_t)as * kTBN;
             bool first = true;
             for (long long kt = kt0; kt < kt1; ++kt) {
@@ -361,6 +380,9 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
             const int as = it & 1;
             mbar_wait(&tmem_full[as], (uint32_t)((it >> 1) & 1));
             tc::fence_after_sync();
+            if constexpr (Cfg::kColVec) {
+                if (shape.N - n0 >= 4) mbar_wait(&vec_full[as], (uint32_t)((it >> 1) & 1));
+            }
             const long long row = m0 + q * 32 + lane;
 #pragma unroll 1
             for (int c = h; c < kTBN / 32; c += EW / 4) {
@@ -377,7 +399,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
                 if constexpr (Cfg::kStaged) {
                     if (lane == 0) tc::bulk_wait_read0();      // the previous store has finished reading the buffer
                     __syncwarp();
-                    if (live) epi.staged(row, col0, v, (int)ncols, split, pre, staging, lane);
+                    if (live) epi.staged(row, col0, v, (int)ncols, split, pre, staging, lane, colvec_sm + as * kTBN + c * 32);
                     tc::fence_proxy_async_smem();
                     __syncwarp();
                     if (lane == 0 && ncols > 0 && m0 + q * 32 < shape.M) {   // rows / columns past the edge are clipped by the map
