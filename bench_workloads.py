@@ -485,7 +485,7 @@ class C2(Workload):
         self.lam_dev = torch.from_numpy(lam).cuda()
         self.units_per_step = self.n
         self.h2d_bytes, self.d2h_bytes = lam.nbytes, 8 * (1 + lam.size)
-        self.launches_per_step = 4 * ((self.N + 16383) // 16384) + 10
+        self.launches_per_step = 2 * ((self.N + 16383) // 16384) + 12     # two GEMMs per 16384-row chunk
         self._x = torch.from_numpy(np.tile(lam[:self.d], (self.n, 1))).cuda()
         if self.compute == 'f32':
             self._x = self._x.float()
@@ -509,8 +509,9 @@ class C2(Workload):
                     '(measured bf16 / 2) the fp32 path is measured against')
         else:
             note = ('timed unit = the whole plugin call vb_model_logp_grad (per 16384-row chunk: GEMM1 B X\' with the '
-                    'fused residual/psi epilogue, GEMM2 Psi X, two fp64 accumulation kernels); peak = measured dense '
-                    'bf16 / 2 (tf32 rate); 3 tf32 MMAs per algorithmic product, so frac <= 1/3 by construction')
+                    'fused residual/psi epilogue and TMA-stored Psi, GEMM2 Psi X accumulating in fp64 in its epilogue; '
+                    'A operands in tensor memory); peak = measured dense bf16 / 2 (tf32 rate); 3 tf32 MMAs per '
+                    'algorithmic product, so frac <= 1/3 by construction')
         return {'bound': 'tensor', 'achieved': ach, 'peak': peak, 'unit': 'TFLOP/s', 'frac': ach / peak,
                 'traffic': None, 'kernel': 'gemm_tf32x3_kernel<PsiEpi> + gemm_tf32x3_kernel<SplitKEpi> (regression '
                 'log p + grad pipeline, %s)' % self.compute,

@@ -124,6 +124,26 @@ def test_regression_tensor_path_wide_model():
     assert rel(g, og) < 2e-5, rel(g, og)
 
 
+def test_regression_tensor_path_long_accumulation_chains():
+    """Half a million rows, draws close to the optimum (the gradient is a small difference of large sums): the
+    production regime.  GEMM2's split-K chains reach their cap (256 k tiles = 8192 rows per tensor-memory
+    accumulation).  The tensor core's fp32 accumulate truncates (round toward zero), which biases GEMM1's X b by
+    about 7e-7 relative; near the optimum that bias is amplified by |b| / |b - b*| in the gradient.  Measured on
+    B200: 4.6e-5 (3.7e-5 with 16-k-tile chains, 5.6e-5 with 1024).  Stated tolerance here: 1e-4 on the gradient,
+    1e-5 on log p -- far below the Monte Carlo noise of the objective these gradients feed."""
+    from viabel_b200 import models
+    N, d, n = 1 << 19, 128, 128
+    X, y, bt = _regression(N, d)
+    X32, y32 = X.astype(np.float32), y.astype(np.float32)
+    model = models.StudentTRegression(X32, y32, df=40.0, dtype='f32')
+    omodel = mm.StudentTRegression(X32.astype(np.float64), y32.astype(np.float64), 40.0)
+    b = (bt + 0.02 * np.random.RandomState(3).randn(n, d)).astype(np.float32)
+    lp, g = model.logp_and_grad(b, dtype='f32')
+    olp, og = omodel.logp_and_grad(b.astype(np.float64))
+    assert rel(lp, olp) < 1e-5, rel(lp, olp)
+    assert rel(g, og) < 1e-4, rel(g, og)
+
+
 def test_mean_field_regression_tensor_path_klvi():
     """Config-2 in miniature through the public objective with fp32 storage."""
     from viabel_b200 import models, vb

@@ -334,6 +334,28 @@ struct SplitKEpi {
         store_row32(parts + (size_t)split * mn + row * ld + col0, v, ncols);
     }
 };
+// Split-K partials accumulated in fp64 across launches: every (tile, split) work item owns its slice of
+// acc[split][M][N], so the read-modify-write needs no atomics and the summation order is fixed.
+struct SplitKAccEpi {
+    struct Pre {};
+    __device__ __forceinline__ Pre prefetch(long long, long long, int) const { return Pre{}; }
+    double* acc; long long mn; long long ld;
+    __device__ __forceinline__ void operator()(long long row, long long col0, float (&v)[32], int ncols, int split, const Pre&) const {
+        double* p = acc + (size_t)split * mn + row * ld + col0;
+        if (ncols == 32 && ((reinterpret_cast<uintptr_t>(p) & 15u) == 0)) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 2) {
+                double2 t = *reinterpret_cast<double2*>(p + j);
+                t.x += (double)v[j]; t.y += (double)v[j + 1];
+                *reinterpret_cast<double2*>(p + j) = t;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (j < ncols) p[j] += (double)v[j];
+        }
+    }
+};
 __global__ void splitk_sum_f64_kernel(const float* __restrict__ parts, int splits, long long mn, double* __restrict__ out) {
     for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < mn; e += (long long)gridDim.x * blockDim.x) {
         double s = 0.0;
@@ -496,6 +518,10 @@ struct PsiEpi {
     __device__ __forceinline__ void staged(long long row, long long col0, float (&v)[32], int ncols, int,
                                            const Pre& pre, unsigned char* staging, int lane, const float* ysm) const {
         float2 acc = make_float2(0.f, 0.f);
+        // running sum of this (row, column block of the chunk) over the chunks: the slot belongs to this thread for
+        // the whole launch, so a plain read-modify-write keeps the order fixed (chunk by chunk)
+        float* slot = rowpart + row * n_blocks + (col0 >> 5);
+        const float prev = *slot;
         unsigned char* my = staging + lane * 128;
         const float* yc = y + col0;
         if (ncols == 32) {
@@ -525,7 +551,7 @@ struct PsiEpi {
                 *reinterpret_cast<float4*>(my + (((j + 1) ^ (lane & 7)) << 4)) = o1;
             }
         }
-        rowpart[row * n_blocks + (col0 >> 5)] = acc.x + acc.y;
+        *slot = prev + (acc.x + acc.y);
     }
 };
 // logp[s] -= (df+1)/2 * sum_blocks rowpart[s][.]   (fp64 accumulation across blocks and chunks)
@@ -558,41 +584,43 @@ __global__ void reg_init_kernel(const float* __restrict__ b, long long S, int D,
         if (lane == 0) logp[s] = -0.5 * a * inv_var;
     }
 }
-// gacc[e] += scale * sum_k parts[k][e]
-__global__ void reg_parts_acc_kernel(const float* __restrict__ parts, int splits, long long mn, double scale,
-                                     double* __restrict__ gacc) {
-    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < mn; e += (long long)gridDim.x * blockDim.x) {
+// grad[e] = prior part + scale * sum_k acc[k][e]
+__global__ void reg_final_kernel(const double* __restrict__ prior, const double* __restrict__ acc, int splits, long long total,
+                                 double scale, float* __restrict__ dst) {
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
         double a = 0.0;
-        for (int k = 0; k < splits; ++k) a += (double)parts[(size_t)k * mn + e];
-        gacc[e] = fma(scale, a, gacc[e]);
+        for (int k = 0; k < splits; ++k) a += acc[(size_t)k * total + e];
+        dst[e] = (float)fma(scale, a, prior[e]);
     }
-}
-__global__ void reg_cast_kernel(const double* __restrict__ src, long long total, float* __restrict__ dst) {
-    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x)
-        dst[e] = (float)src[e];
 }
 
 static long long reg_chunk_rows(long long S, long long N) {
-    // Psi planes of 2 x 256 MiB per chunk: larger chunks amortise the per-launch host work (two tensor-map
-    // encodes per GEMM), smaller ones would keep Psi in L2 but leave the GPU waiting for launches
-    // (measured at S = 4096: 33 ms with 2048-row chunks, 24.0 with 8192, 22.7 with 16384).  VB_REG_CHUNK overrides (tuning).
-    static long long forced = -1;
-    if (forced < 0) {
-        const char* e = getenv("VB_REG_CHUNK");
-        forced = e ? atoll(e) : 0;
-    }
-    long long c = forced > 0 ? forced : (1ll << 26) / (S > 0 ? S : 1);
+    // Psi (S x chunk fp32) of at most 1 GiB per chunk.  Every chunk costs two kernel boundaries (pipeline fill,
+    // tail imbalance, launch latency: ~20 us), so larger chunks are faster even though Psi then streams through HBM:
+    // measured at S = 4096, N = 2^20: 14.9 ms with 16384-row chunks, 13.5 with 32768, 13.15 with 65536, 12.9 with
+    // 262144.  VB_REG_CHUNK overrides (tuning).
+    long long forced = 0;
+    { const char* e = getenv("VB_REG_CHUNK"); if (e) forced = atoll(e); }
+    long long c = forced > 0 ? forced : (1ll << 28) / (S > 0 ? S : 1);
     c = c / 128 * 128;
     if (c < 128) c = 128;
-    if (c > 32768) c = 32768;
+    if (c > 262144) c = 262144;
     if (c > N) c = (N + 31) / 32 * 32;
     return c;
 }
+// at most 256 k tiles (8192 rows) per TMEM accumulation chain of GEMM2: the truncating fp32 accumulate of the
+// tensor core costs about 1e-9 of the gradient per row of the chain (measured 1.1e-5 at 10 000 rows); stated
+// tolerance 2e-5
+static long long reg_max_chain() {
+    const char* e = getenv("VB_REG_CHAIN");        // tuning / experiments
+    return e ? atoll(e) : 256;
+}
+#define kRegMaxChain reg_max_chain()
 struct RegLayout { long long C; int splits; size_t off_xs, off_bs, off_psi, off_rowpart, off_parts, off_gacc, total; };
 static RegLayout reg_layout(long long S, long long N, int D) {
     RegLayout L;
     L.C = reg_chunk_rows(S, N);
-    L.splits = plan_gemm(S, D, L.C, auto_splits(S, D, L.C)).splits;
+    L.splits = plan_gemm(S, D, L.C, auto_splits(S, D, L.C, kRegMaxChain)).splits;
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t at = o; o += (bytes + 255) & ~(size_t)255; return at; };
     const bool resident = D <= kTResKTiles * kTBK;     // no pre-split operands needed
@@ -600,7 +628,7 @@ static RegLayout reg_layout(long long S, long long N, int D) {
     L.off_bs = take(resident ? 0 : split_bytes(S, D));
     L.off_psi = take((size_t)S * L.C * 4);
     L.off_rowpart = take((size_t)S * (L.C / 32 + 1) * 4);
-    L.off_parts = take((size_t)L.splits * S * D * 4);
+    L.off_parts = take((size_t)L.splits * S * D * 8);
     L.off_gacc = take((size_t)S * D * 8);
     L.total = o;
     return L;
@@ -620,7 +648,7 @@ int regression_logp_grad_tf32(const ModelHost* m, const float* b, long long S, d
     char* w = (char*)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
     float* psi = (float*)(w + L.off_psi);
     float* rowpart = (float*)(w + L.off_rowpart);
-    float* parts = (float*)(w + L.off_parts);
+    double* parts = (double*)(w + L.off_parts);
     double* gacc = (double*)(w + L.off_gacc);
     const float* X = (const float*)m->d_X;
     const float* y = (const float*)m->d_y;
@@ -648,6 +676,8 @@ int regression_logp_grad_tf32(const ModelHost* m, const float* b, long long S, d
     VB_LAUNCH_CHECK();
     const int n_blocks = (int)(L.C / 32 + 1);
     const long long mn = S * D;
+    VB_CUDA_TRY(cudaMemsetAsync(rowpart, 0, (size_t)S * n_blocks * 4, st));
+    if (out_grad_or_null) VB_CUDA_TRY(cudaMemsetAsync(parts, 0, (size_t)L.splits * mn * 8, st));
     for (long long r0 = 0; r0 < N; r0 += L.C) {
         const long long cols = (r0 + L.C <= N) ? L.C : (N - r0);
         const SplitMat xraw{X + r0 * D, cols, D, D, 0};
@@ -666,21 +696,23 @@ int regression_logp_grad_tf32(const ModelHost* m, const float* b, long long S, d
             rc = launch_tf32x3<false, false, PsiEpi, 8>(bs, xc, plan_gemm(S, cols, D, 1), e1, st);
         }
         if (rc != VB_OK) return rc;
-        reg_rowpart_acc_kernel<<<grid_for(S * 32, 256, kNumSMs * 8), 256, 0, st>>>(
-            rowpart, S, n_blocks, (int)((cols + 31) / 32), 0.5 * (m->df + 1.0), out_logp);
-        VB_LAUNCH_CHECK();
         if (out_grad_or_null) {
             const SplitMat ps{psi, S, cols, L.C, 0};                 // raw fp32: split in shared memory by the GEMM
-            const GemmShape shape = plan_gemm(S, D, cols, auto_splits(S, D, cols));
-            rc = raw2 ? launch_tf32x3<false, true, SplitKEpi, 4, false, true, true>(ps, xraw, shape, SplitKEpi{parts, mn, D}, st)
-                      : launch_tf32x3<false, true, SplitKEpi, 4, false, true, false>(ps, xc, shape, SplitKEpi{parts, mn, D}, st);
+            const GemmShape shape = plan_gemm(S, D, cols, auto_splits(S, D, cols, kRegMaxChain));
+            if (shape.splits > L.splits) return VB_ERR_WORKSPACE;
+            rc = raw2 ? launch_tf32x3<false, true, SplitKAccEpi, 4, false, true, true>(ps, xraw, shape, SplitKAccEpi{parts, mn, D}, st)
+                      : launch_tf32x3<false, true, SplitKAccEpi, 4, false, true, false>(ps, xc, shape, SplitKAccEpi{parts, mn, D}, st);
             if (rc != VB_OK) return rc;
-            reg_parts_acc_kernel<<<grid_for(mn, 256, kNumSMs * 4), 256, 0, st>>>(parts, shape.splits, mn, (m->df + 1.0) / m->df, gacc);
-            VB_LAUNCH_CHECK();
         }
     }
+    // one reduction per call instead of one per chunk: log p from the per-(row, block) running sums, the gradient
+    // from the per-split fp64 accumulators
+    reg_rowpart_acc_kernel<<<grid_for(S * 32, 256, kNumSMs * 8), 256, 0, st>>>(
+        rowpart, S, n_blocks, (int)(((N < L.C ? N : L.C) + 31) / 32), 0.5 * (m->df + 1.0), out_logp);
+    VB_LAUNCH_CHECK();
     if (out_grad_or_null) {
-        reg_cast_kernel<<<grid_for(mn, 256, kNumSMs * 4), 256, 0, st>>>(gacc, mn, out_grad_or_null);
+        reg_final_kernel<<<grid_for(mn, 256, kNumSMs * 4), 256, 0, st>>>(gacc, parts, L.splits, mn, (m->df + 1.0) / m->df,
+                                                                        out_grad_or_null);
         VB_LAUNCH_CHECK();
     }
     return VB_OK;

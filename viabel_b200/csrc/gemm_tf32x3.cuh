@@ -432,13 +432,26 @@ inline GemmShape plan_gemm(long long M, long long N, long long K, int want_split
     s.splits = (int)((kt + per - 1) / per);
     return s;
 }
-inline int auto_splits(long long M, long long N, long long K) {
+// k splits for a GEMM with fewer output tiles than SMs: minimise (waves of work items) x (k tiles per item) with
+// at least 8 k tiles per split; among schedules within 3 % of the best, the fewest splits (fewer partial tiles).  max_chain bounds the k
+// tiles accumulated in one TMEM chain (the tensor core's fp32 accumulate truncates: the relative error grows
+// by about 7e-9 per unit of K), 0 = unbounded.
+inline int auto_splits(long long M, long long N, long long K, long long max_chain = 0) {
     const long long tiles = ((M + kTBM - 1) / kTBM) * ((N + kTBN - 1) / kTBN);
-    if (tiles >= kNumSMs) return 1;
-    long long sp = kNumSMs / tiles;
     const long long kt = (K + kTBK - 1) / kTBK;
-    if (sp > kt / 8) sp = kt / 8;          // keep >= 8 k tiles per split
-    return sp < 1 ? 1 : (int)sp;
+    const long long sp_min = (max_chain > 0) ? (kt + max_chain - 1) / max_chain : 1;
+    if (tiles >= kNumSMs && sp_min <= 1) return 1;
+    const long long sp0 = sp_min < 1 ? 1 : sp_min;
+    auto cost_of = [&](long long sp) {
+        const long long per = (kt + sp - 1) / sp;
+        const long long items = tiles * ((kt + per - 1) / per);
+        return ((items + kNumSMs - 1) / kNumSMs) * per;
+    };
+    long long best_cost = cost_of(sp0);
+    for (long long sp = sp0 + 1; sp <= sp0 + 32 && sp * 8 <= kt; ++sp) best_cost = cost_of(sp) < best_cost ? cost_of(sp) : best_cost;
+    long long best = sp0;                                   // fewest splits within 3 % of the best schedule
+    while (cost_of(best) * 100 > best_cost * 103) ++best;
+    return (int)best;
 }
 
 int tf32x3_num_sms();

@@ -38,8 +38,9 @@ class Model:
 
     def __del__(self):
         h = getattr(self, '_handle', None)
-        if h:
-            _lib.lib.vb_model_destroy(h)
+        lib = getattr(_lib, 'lib', None) if _lib is not None else None     # module globals may be gone at exit
+        if h and lib is not None:
+            lib.vb_model_destroy(h)
             self._handle = None
 
     @property
