@@ -186,6 +186,15 @@ def test_psislw_two_dimensional_and_device_input():
     o2, _ = psis.psislw(dev, overwrite_lw=True)
     assert o2.data_ptr() == dev.data_ptr()
     np.testing.assert_allclose(dev.cpu().numpy(), oout[:, 0], rtol=0, atol=1e-11)
+    # out=: the result lands in a caller-owned (here pinned) host buffer
+    pin_in = torch.empty(5000, dtype=torch.float64, pin_memory=True)
+    pin_in.copy_(torch.from_numpy(a))
+    pin_out = torch.empty(5000, dtype=torch.float64, pin_memory=True)
+    res, k3 = psis.psislw(pin_in.numpy(), out=pin_out.numpy())
+    assert res is not None and np.shares_memory(res, pin_out.numpy()) and k3 == k
+    np.testing.assert_array_equal(res, o.cpu().numpy())
+    with pytest.raises(ValueError):
+        psis.psislw(a, out=np.empty(4999))
 
 
 @pytest.mark.parametrize('name', gi.GPD_CASES)

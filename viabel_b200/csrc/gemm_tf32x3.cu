@@ -208,12 +208,15 @@ int fr_sample_tf32(const double* mu, const float* scale, double df, long long n,
     if (!ws || ws_bytes < fr_sample_tf32_workspace_bytes(n, dim)) return VB_ERR_WORKSPACE;
     char* w = (char*)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
     SplitMat zs, ss;
-    int rc = split_into(z, n, dim, dim, (float*)w, st, &zs);
-    if (rc != VB_OK) return rc;
-    rc = split_into(scale, dim, dim, dim, (float*)(w + split_bytes(n, dim)), st, &ss);
+    int rc = split_into(scale, dim, dim, dim, (float*)(w + split_bytes(n, dim)), st, &ss);
     if (rc != VB_OK) return rc;
     const GemmShape shape = plan_gemm(n, dim, dim, 1);
-    return launch_tf32x3<false, true>(zs, ss, shape, FrSampleEpi{out_x, dim, mu, chi2, (float)df}, st);
+    const FrSampleEpi epi{out_x, dim, mu, chi2, (float)df};
+    if (dim % 4 == 0 && (reinterpret_cast<uintptr_t>(z) & 15u) == 0)    // z read as plain fp32, split on chip into TMEM
+        return launch_tf32x3<false, true, FrSampleEpi, 4, false, true, false>(SplitMat{z, n, dim, dim, 0}, ss, shape, epi, st);
+    rc = split_into(z, n, dim, dim, (float*)w, st, &zs);
+    if (rc != VB_OK) return rc;
+    return launch_tf32x3<false, true>(zs, ss, shape, epi, st);
 }
 
 // ------------------------------------------------------------------------------------------ correlated Gaussian
@@ -295,12 +298,17 @@ int gauss_logp_grad_f32(const double* mean, const double* prec, int dim, const f
     gauss_prep_kernel<<<grid_for((long long)dim * dim, 256, kNumSMs * 2), 256, 0, st>>>(mean, prec, dim, p32, bias);
     VB_LAUNCH_CHECK();
     SplitMat xs, ps;
-    int rc = split_into(x, n, dim, dim, xs_buf, st, &xs);
-    if (rc != VB_OK) return rc;
-    rc = split_into(p32, dim, dim, dim, ps_buf, st, &ps);
+    int rc = split_into(p32, dim, dim, dim, ps_buf, st, &ps);
     if (rc != VB_OK) return rc;
     const GemmShape shape = plan_gemm(n, dim, dim, 1);
-    rc = launch_tf32x3<false, true>(xs, ps, shape, GaussEpi{g, dim, bias, x, mean, rowpart, chunks}, st);
+    const GaussEpi epi{g, dim, bias, x, mean, rowpart, chunks};
+    if (dim % 4 == 0 && (reinterpret_cast<uintptr_t>(x) & 15u) == 0) {  // x read as plain fp32, split on chip into TMEM
+        rc = launch_tf32x3<false, true, GaussEpi, 4, false, true, false>(SplitMat{x, n, dim, dim, 0}, ps, shape, epi, st);
+    } else {
+        rc = split_into(x, n, dim, dim, xs_buf, st, &xs);
+        if (rc != VB_OK) return rc;
+        rc = launch_tf32x3<false, true>(xs, ps, shape, epi, st);
+    }
     if (rc != VB_OK) return rc;
     rowpart_sum_kernel<<<grid_for(n, 256, kNumSMs * 8), 256, 0, st>>>(rowpart, n, chunks, 0.5, out_logp);
     VB_LAUNCH_CHECK();

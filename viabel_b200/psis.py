@@ -29,7 +29,7 @@ def _smooth_1d(col, Reff, want_tail=False):
     return out, diag.cpu().numpy(), tail
 
 
-def psislw(lw, Reff=1.0, overwrite_lw=False, group=None):
+def psislw(lw, Reff=1.0, overwrite_lw=False, group=None, out=None):
     """Pareto smoothed importance sampling (``psis.py:112-208``).
 
     ``group``: torch.distributed group (or ``True`` for the world group) over which a 1-D ``lw`` is
@@ -38,7 +38,9 @@ def psislw(lw, Reff=1.0, overwrite_lw=False, group=None):
 
     ``lw``: (n,) or (n, m) log weights, numpy or CUDA tensor.  Returns ``(lw_out, kss)`` with
     ``kss`` a float for 1-D input and an (m,) numpy array otherwise.  ``overwrite_lw`` smooths
-    a CUDA tensor / F-contiguous numpy array in place like the reference does."""
+    a CUDA tensor / F-contiguous numpy array in place like the reference does.  ``out`` (1-D host input only): a
+    float64 C-contiguous numpy array of the same length that receives the result; when it lives in pinned memory
+    the device-to-host copy runs at link speed instead of through the driver's pageable staging."""
     if lw.ndim == 2:
         n, m = lw.shape
     elif lw.ndim == 1:
@@ -46,6 +48,7 @@ def psislw(lw, Reff=1.0, overwrite_lw=False, group=None):
     else:
         raise ValueError("Argument `lw` must be 1 or 2 dimensional.")
     sharded = group is not None and group is not False
+    out_host, out = out, None
     if n <= 1 and not sharded:                           # a shard may hold one weight; the global check is in psis_dist
         raise ValueError("More than one log-weight needed.")
     dev = to_dev(lw, _lib.F64)
@@ -67,6 +70,12 @@ def psislw(lw, Reff=1.0, overwrite_lw=False, group=None):
             kss[i] = diag[0]
         out = torch.stack(outs, dim=1)
     if is_host(lw):
+        if out_host is not None:
+            if lw.ndim != 1 or not isinstance(out_host, np.ndarray) or out_host.dtype != np.float64 \
+                    or out_host.shape != (n,) or not out_host.flags.c_contiguous:
+                raise ValueError('`out` must be a C-contiguous float64 numpy array of shape (n,) for 1-D host input')
+            torch.from_numpy(out_host).copy_(out)
+            return out_host, kss
         res = out.cpu().numpy()
         if lw.ndim == 2:
             res = np.asfortranarray(res)                 # psis.py:151 allocates F-order
