@@ -144,48 +144,71 @@ class C4(Workload):
 
 
 # ======================================================================================= C1
+C1_ITERS = 500          # AdaGrad iterations per bench step (10 CUDA-graph replays of 50 iterations)
+
+
 def _c1_cpu_job(job):
     seed, iters = job
     from oracle import models_np, vb_np
     fam = vb_np.mean_field_gaussian_variational_family(2)
     obj = vb_np.black_box_klvi(fam, models_np.Funnel(), 1000)
-    lam = np.array([0., -1., 1., 1.])
-    for _ in range(iters):
-        v, g = obj(lam)
-    return v
+    vb_np.adagrad_optimize(iters, obj, np.array([0., -1., 1., 1.]), learning_rate=.01, learning_rate_end=.001)
+    return iters
 
 
 class C1(Workload):
-    """funnel d=2, mean-field Gaussian KLVI, 1000 samples/step (latency-bound; roofline n/a)."""
+    """funnel d=2, mean-field Gaussian KLVI, 1000 samples per AdaGrad iteration (latency-bound; roofline n/a).
+    One bench step = 500 iterations of adagrad_optimize on the device-resident loop (vb_mf_adagrad_*)."""
     name = 'c1'
     n = 1000
-    default_steps, default_warmup = 2000, 50
+    default_steps, default_warmup = 10, 3
 
     def setup(self):
+        import ctypes
         import torch
         from viabel_b200 import models, vb, _lib
-        from viabel_b200._device import ptr
-        self.lib = _lib
+        from viabel_b200._device import ptr, stream_ptr
+        self.lib, self.vb, self.torch = _lib, vb, torch
         self.fam = vb.mean_field_gaussian_variational_family(2)
         self.model = models.Funnel()
         self.obj = vb.black_box_klvi(self.fam, self.model, self.n, group=False)
-        self.lam_host = np.array([0., -1., 1., 1.])
-        self.lam_dev = torch.from_numpy(self.lam_host).cuda()
-        self.units_per_step = self.n
-        self.h2d_bytes, self.d2h_bytes = 32, 40
-        self._out = torch.empty(5, dtype=torch.float64, device='cuda')
-        self._part = torch.empty(8, dtype=torch.float64, device='cuda')
-        self._ws = torch.zeros(_lib.lib.vb_mf_step_workspace_bytes(2), dtype=torch.uint8, device='cuda')
-        self._args = [_lib.FAMILY_MF_GAUSS, 0.0, self.model.handle, _lib.OBJ_KLVI, 1.0, _lib.F64, ptr(self.lam_dev),
+        self.init = np.array([0., -1., 1., 1.])                 # notebooks/funnel-distribution.ipynb:241-243
+        self.units_per_step = self.n * C1_ITERS
+        self.h2d_bytes = 32 + C1_ITERS * (8 + 8 + 4)            # init_param + schedule + Philox (seed, offset) arrays
+        self.d2h_bytes = 8 * C1_ITERS + 8 * 4 * (C1_ITERS - 3 * C1_ITERS // 4)   # value history + kept iterates
+        self.launches_per_step = C1_ITERS                       # one fused (step + update) launch per iteration
+        # device-resident plan for `value` / the kernel-only timing: a long run the timed steps are slices of
+        total = 1 << 18
+        dev = 'cuda'
+        self._param = torch.from_numpy(self.init.copy()).to(dev)
+        self._rates = torch.full((total,), 0.001, dtype=torch.float64, device=dev)
+        self._seeds = torch.zeros(total, dtype=torch.int64, device=dev)
+        self._offsets = torch.arange(total, dtype=torch.int32, device=dev)
+        self._values = torch.zeros(total, dtype=torch.float64, device=dev)
+        self._kept = torch.zeros((total - 3 * total // 4, 4), dtype=torch.float64, device=dev)
+        self._state = torch.zeros(_lib.lib.vb_mf_adagrad_state_bytes(2, 10), dtype=torch.uint8, device=dev)
+        self._ws = torch.zeros(_lib.lib.vb_mf_step_workspace_bytes(2), dtype=torch.uint8, device=dev)
+        self._plan = ctypes.c_void_p()
+        _lib.check(_lib.lib.vb_mf_adagrad_create(
+            _lib.FAMILY_MF_GAUSS, 0.0, self.model.handle, _lib.OBJ_KLVI, 1.0, _lib.F64, ptr(self._param), self.n, 0,
+            total, 10, 0.1, ptr(self._rates), ptr(self._seeds), ptr(self._offsets), ptr(self._values),
+            ptr(self._kept), ptr(self._state), self._state.numel(), ptr(self._ws), self._ws.numel(), 50, 1,
+            stream_ptr(), ctypes.byref(self._plan)), 'vb_mf_adagrad_create')
+        # single fused step (no update) for the kernel-only line
+        self._out = torch.empty(5, dtype=torch.float64, device=dev)
+        self._part = torch.empty(8, dtype=torch.float64, device=dev)
+        self._args = [_lib.FAMILY_MF_GAUSS, 0.0, self.model.handle, _lib.OBJ_KLVI, 1.0, _lib.F64, ptr(self._param),
                       self.n, 0, 0, 0, 0, ptr(self._out), ptr(self._out) + 8, ptr(self._part),
                       ptr(self._ws), self._ws.numel()]
         self._off = 0
 
     def step_device(self):
-        return self.obj(self.lam_dev)
+        from viabel_b200._device import stream_ptr
+        self.lib.check(self.lib.lib.vb_mf_adagrad_run(self._plan, C1_ITERS, stream_ptr()), 'vb_mf_adagrad_run')
 
     def step_e2e(self):
-        return self.obj(self.lam_host)
+        # the public call: host init_param in, (averaged iterate, kept iterates, value history) out
+        return self.vb.adagrad_optimize(C1_ITERS, self.obj, self.init, learning_rate=.01, learning_rate_end=.001)
 
     def kernel_only(self):
         from viabel_b200._device import stream_ptr
@@ -199,28 +222,34 @@ class C1(Workload):
                 'note': 'latency-bound (one CTA-sized problem, ~16 kB touched): roofline fraction not meaningful'}
 
     def config(self):
-        return {'workload': 'c1: funnel d=2, mean-field Gaussian KLVI, 1000 samples/step (one AdaGrad iteration)',
+        return {'workload': self.config_name(), 'iterations_per_step': C1_ITERS,
+                'value_mode': 'device-resident AdaGrad loop: CUDA-graph replays of 50 iterations, one launch per iteration '
+                              '(the step kernel\'s last CTA applies the update)',
+                'e2e_mode': 'adagrad_optimize(500, objective, host init_param) -> host histories, plan built per call',
                 'l2': 'no resident input (Philox in-kernel)', 'parallelism': 'replicas only'}
 
-    config_name = lambda self: self.config()['workload']      # noqa: E731
+    def config_name(self):
+        return ('c1: funnel d=2, mean-field Gaussian KLVI, 1000 samples/iteration, adagrad_optimize '
+                '(%d iterations per bench step)' % C1_ITERS)
 
     def cpu_baseline(self):
         t0 = time.perf_counter()
         _c1_cpu_job((0, 3000))
         rate = 3000 * self.n / (time.perf_counter() - t0)
         return {'value': rate, 'unit': self.unit, 'cores': 1, 'kind': 'port',
-                'sample': '3000 oracle KLVI steps of 1000 samples (randn + funnel log p + closed-form grad)'}
+                'sample': '3000 oracle adagrad_optimize iterations of 1000 samples (randn + funnel log p + '
+                          'closed-form grad + windowed update)'}
 
     def reference_arm(self, steps, warmup):
-        k = max(steps, 1000)
+        k = max(steps, 2) * C1_ITERS
         t0 = time.perf_counter()
         _c1_cpu_job((0, k))
         dt = time.perf_counter() - t0
         rate = k * self.n / dt
         cb = {'value': rate, 'unit': self.unit, 'cores': 1, 'kind': 'port',
-              'sample': '%d sequential oracle KLVI steps (the optimiser loop is sequential: 1 process)' % k}
-        return {'metric': self.metric, 'value': rate, 'unit': self.unit, 'ms_per_step': dt / k * 1e3, 'dtype': 'f64',
-                'config': {'workload': self.config_name()}, 'cpu_baseline': cb,
+              'sample': '%d sequential oracle adagrad_optimize iterations (the optimiser loop is sequential: 1 process)' % k}
+        return {'metric': self.metric, 'value': rate, 'unit': self.unit, 'ms_per_step': dt / k * C1_ITERS * 1e3,
+                'dtype': 'f64', 'config': {'workload': self.config_name()}, 'cpu_baseline': cb,
                 'e2e': {'value': rate, 'unit': self.unit, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
 
 

@@ -64,6 +64,11 @@ int  vb_model_create_eight_schools(const double* h_y, const double* h_sigma, int
 /* d_X is (n_rows, dim) row-major, d_y is (n_rows); both of `dtype`. */
 int  vb_model_create_regression(const void* d_X, const void* d_y, long long n_rows, int dim,
                                 double df, double prior_sd, int dtype, vb_model** out);
+/* The design matrix is model data: attach its tf32 (hi, lo) planes, made ONCE with
+ * vb_split_f32(d_X, n_rows, dim, dim, d_X_planes) into vb_split_bytes(n_rows, dim) bytes that outlive the
+ * model, so that the fp32 / 3xTF32 path (vb_model_logp_grad, dtype VB_F32) does not re-split X on every call
+ * and its workspace shrinks by that amount.  NULL detaches.  fp32 data only. */
+int  vb_model_regression_attach_split(vb_model* model, const float* d_X_planes);
 /* d_mean (dim) and d_precision (dim, dim) symmetric, float64. */
 int  vb_model_create_gauss(const double* d_mean, const double* d_precision, int dim,
                            vb_model** out);
@@ -124,6 +129,43 @@ int vb_mf_step(int family, double df, const vb_model* model, int objective, doub
                unsigned long long sample_index0,
                double* d_out_value_or_null, double* d_out_grad_or_null,
                double* d_out_partials, void* d_ws, size_t ws_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Device-resident AdaGrad loop over the fused mean-field step.
+ * Replaces the Python loop of adagrad_optimize (viabel/vb.py:345-389, has_log_norm=False):
+ * windowed sum of squared gradients (vb.py:368-373), the update
+ * `param - rate * grad / sqrt(epsilon + accum)` (vb.py:374), the value history (vb.py:364) and
+ * the iterates kept from iteration 3*n_iters/4 on (vb.py:375-376).  The iterate, the
+ * gradient window and the histories stay in HBM; groups of `graph_iters` iterations are
+ * replayed as one CUDA graph.  The update is evaluated with individually rounded fp64
+ * operations in numpy's order, so for equal gradients it is bit-identical to vb.py:371-374.
+ *
+ *   d_var_param      [2*dim] float64, in: init_param, updated in place every iteration
+ *   d_base_or_null   NULL -> Philox stream (d_seeds[i], d_offsets[i]) for iteration i;
+ *                    else (n_iters, n_samples, dim) external base draws of `dtype`
+ *   d_rates          [n_iters] float64 learning-rate schedule (viabel/vb.py:324-343)
+ *   d_seeds/d_offsets[n_iters] per-iteration Philox (seed, call offset)
+ *   d_value_history  [n_iters] float64;  d_param_history [n_iters - 3*n_iters/4][2*dim]
+ *   d_state          vb_mf_adagrad_state_bytes(dim, window) bytes, 16-byte aligned, owned by
+ *                    the plan until vb_mf_adagrad_destroy
+ *   d_ws             vb_mf_step_workspace_bytes(dim)
+ *   graph_iters      0: plain launches; k > 0: k iterations per CUDA graph replay
+ *   fused            1: the last CTA of each step launch applies the update (one launch per iteration);
+ *                    0: separate update launch (two launches per iteration)
+ * vb_mf_adagrad_run enqueues the next `n_steps` iterations on `stream` (no host sync).
+ * ---------------------------------------------------------------------------------- */
+typedef struct vb_adagrad_plan vb_adagrad_plan;
+size_t vb_mf_adagrad_state_bytes(int dim, int window);
+int vb_mf_adagrad_create(int family, double df, const vb_model* model, int objective, double alpha,
+                         int dtype, double* d_var_param, long long n_samples,
+                         const void* d_base_or_null, int n_iters, int window, double epsilon,
+                         const double* d_rates, const unsigned long long* d_seeds,
+                         const unsigned int* d_offsets, double* d_value_history,
+                         double* d_param_history, void* d_state, size_t state_bytes,
+                         void* d_ws, size_t ws_bytes, int graph_iters, int fused, void* stream,
+                         vb_adagrad_plan** out_plan);
+int vb_mf_adagrad_run(vb_adagrad_plan* plan, int n_steps, void* stream);
+int vb_mf_adagrad_destroy(vb_adagrad_plan* plan);
 
 /* Deterministic fixed-order merge of `n_ranks` partial vectors (laid out
  * [n_ranks][VB_MF_NPART(dim)]) followed by the (value, grad) formulas. */

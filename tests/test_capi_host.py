@@ -93,9 +93,10 @@ def test_python_surface_matches_reference_signatures():
     assert params(bounds.wasserstein_bounds)[:3] == [('d2', E), ('samples', None), ('moment_bound_fn', None)]
     assert params(bounds.error_bounds) == [('W1', np.inf), ('W2', np.inf), ('q_var', np.inf), ('p_var', np.inf)]
     assert params(psis.psislw)[:3] == [('lw', E), ('Reff', 1.0), ('overwrite_lw', False)]      # + group=None
-    assert params(vb.adagrad_optimize) == [('n_iters', E), ('objective_and_grad', E), ('init_param', E),
-                                           ('has_log_norm', False), ('window', 10), ('learning_rate', .01),
-                                           ('epsilon', .1), ('learning_rate_end', None)]
+    # + device_loop=None, base_draws=None, graph_iters=None (extensions after the reference's parameters)
+    assert params(vb.adagrad_optimize)[:8] == [('n_iters', E), ('objective_and_grad', E), ('init_param', E),
+                                               ('has_log_norm', False), ('window', 10), ('learning_rate', .01),
+                                               ('epsilon', .1), ('learning_rate_end', None)]
     assert params(vb.black_box_klvi)[:3] == [('var_family', E), ('logdensity', E), ('n_samples', E)]
     assert params(vb.black_box_chivi)[:4] == [('alpha', E), ('var_family', E), ('logdensity', E), ('n_samples', E)]
     assert vb.VariationalFamily._fields == ('sample', 'entropy', 'logdensity', 'mean_and_cov', 'pth_moment',

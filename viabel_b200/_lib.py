@@ -25,6 +25,7 @@ SIGNATURES = {
     'vb_model_create_mixture': (_i, [_d, C.POINTER(_p)]),
     'vb_model_create_eight_schools': (_i, [C.POINTER(_d), C.POINTER(_d), _i, C.POINTER(_p)]),
     'vb_model_create_regression': (_i, [_p, _p, _ll, _i, _d, _d, _i, C.POINTER(_p)]),
+    'vb_model_regression_attach_split': (_i, [_p, _p]),
     'vb_model_create_gauss': (_i, [_p, _p, _i, C.POINTER(_p)]),
     'vb_model_kind': (_i, [_p]),
     'vb_model_dim': (_i, [_p]),
@@ -34,6 +35,11 @@ SIGNATURES = {
     'vb_base_draws': (_i, [_i, _d, _i, _ll, _i, _ull, _u, _ull, _p, _p, _p]),
     'vb_mf_step_workspace_bytes': (_sz, [_i]),
     'vb_mf_step': (_i, [_i, _d, _p, _i, _d, _i, _p, _ll, _p, _ull, _u, _ull, _p, _p, _p, _p, _sz, _p]),
+    'vb_mf_adagrad_state_bytes': (_sz, [_i, _i]),
+    'vb_mf_adagrad_create': (_i, [_i, _d, _p, _i, _d, _i, _p, _ll, _p, _i, _i, _d, _p, _p, _p, _p, _p, _p, _sz,
+                                  _p, _sz, _i, _i, _p, C.POINTER(_p)]),
+    'vb_mf_adagrad_run': (_i, [_p, _i, _p]),
+    'vb_mf_adagrad_destroy': (_i, [_p]),
     'vb_mf_finalize': (_i, [_i, _i, _d, _p, _i, _p, _i, _p, _p, _p]),
     'vb_mf_reduce_workspace_bytes': (_sz, [_ll, _i]),
     'vb_mf_reduce': (_i, [_i, _d, _i, _d, _i, _p, _ll, _i, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),

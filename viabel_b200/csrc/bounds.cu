@@ -4,6 +4,7 @@
 //   wasserstein_bounds / np.cov (bounds.py:130-135, 55-56): column sums, then central
 //     2nd/4th moments and the scatter matrix in a second pass.
 // HBM-bound: 8 B/weight, 16 d B/sample.  All cross-block merges are in fixed order.
+#include <cstdlib>
 #include "common.cuh"
 #include "gemm_f64.cuh"
 
@@ -28,8 +29,9 @@ struct DivAcc {
         M = m;
     }
     // branch-free accumulation of one element that is known to be <= M
+    template <int MIXED = 0>
     __device__ __forceinline__ void add_below(double x, double alpha, double K, const double* table) {
-        const double w = exp_nonpos_flush(alpha * (x - M), table);
+        const double w = exp_nonpos_flush_v<MIXED>(alpha * (x - M), table);
         sw += w;
         sw2 = fma(w, w, sw2);
         const double d = x - K;
@@ -49,6 +51,7 @@ struct DivAcc {
     }
 };
 
+template <int MIXED>
 __global__ void __launch_bounds__(kDivThreads)
 divergence_blocks_kernel(const double* __restrict__ lw, long long n, double alpha,
                          double* __restrict__ block_out /* [grid][6] */) {
@@ -73,23 +76,23 @@ divergence_blocks_kernel(const double* __restrict__ lw, long long n, double alph
             const double2 v2 = ld_stream2(p + i + 2 * gthreads), v3 = ld_stream2(p + i + 3 * gthreads);
             const double m8 = fmax(fmax(fmax(v0.x, v0.y), fmax(v1.x, v1.y)), fmax(fmax(v2.x, v2.y), fmax(v3.x, v3.y)));
             if (m8 > a.M) { a.raise_to(m8, alpha); b.raise_to(m8, alpha); }
-            a.add_below(v0.x, alpha, K, s_table); b.add_below(v0.y, alpha, K, s_table);
-            a.add_below(v1.x, alpha, K, s_table); b.add_below(v1.y, alpha, K, s_table);
-            a.add_below(v2.x, alpha, K, s_table); b.add_below(v2.y, alpha, K, s_table);
-            a.add_below(v3.x, alpha, K, s_table); b.add_below(v3.y, alpha, K, s_table);
+            a.add_below<MIXED>(v0.x, alpha, K, s_table); b.add_below<MIXED>(v0.y, alpha, K, s_table);
+            a.add_below<MIXED>(v1.x, alpha, K, s_table); b.add_below<MIXED>(v1.y, alpha, K, s_table);
+            a.add_below<MIXED>(v2.x, alpha, K, s_table); b.add_below<MIXED>(v2.y, alpha, K, s_table);
+            a.add_below<MIXED>(v3.x, alpha, K, s_table); b.add_below<MIXED>(v3.y, alpha, K, s_table);
             a.cnt += 8.0;
         }
         for (; i < n2; i += gthreads) {
             const double2 v = ld_stream2(p + i);
             const double m2 = fmax(v.x, v.y);
             if (m2 > a.M) { a.raise_to(m2, alpha); b.raise_to(m2, alpha); }
-            a.add_below(v.x, alpha, K, s_table); b.add_below(v.y, alpha, K, s_table);
+            a.add_below<MIXED>(v.x, alpha, K, s_table); b.add_below<MIXED>(v.y, alpha, K, s_table);
             a.cnt += 2.0;
         }
         if ((n & 1) && gtid == 0) {
             const double x = lw[n - 1];
             if (x > a.M) { a.raise_to(x, alpha); b.raise_to(x, alpha); }
-            a.add_below(x, alpha, K, s_table);
+            a.add_below<MIXED>(x, alpha, K, s_table);
             a.cnt += 1.0;
         }
     } else {
@@ -327,7 +330,10 @@ static int run_divergence(const double* lw, long long n, double alpha, double* o
     if (!lw || n < 1 || !ws || !(alpha > 0.0)) return VB_ERR_ARG;
     if (ws_bytes < vb_bounds_divergence_workspace_bytes(n)) return VB_ERR_WORKSPACE;
     const int grid = grid_for((n + 1) / 2, kDivThreads, kNumSMs * 8);
-    divergence_blocks_kernel<<<grid, kDivThreads, 0, st>>>(lw, n, alpha, (double*)ws);
+    // VB_EXP_MIXED=1 (experiment): series tail of the exp in fp32 (7 instead of 12 fp64 operations per weight)
+    static const bool mixed = getenv("VB_EXP_MIXED") != nullptr && atoi(getenv("VB_EXP_MIXED")) != 0;
+    if (mixed) divergence_blocks_kernel<1><<<grid, kDivThreads, 0, st>>>(lw, n, alpha, (double*)ws);
+    else divergence_blocks_kernel<0><<<grid, kDivThreads, 0, st>>>(lw, n, alpha, (double*)ws);
     VB_LAUNCH_CHECK();
     divergence_finish_kernel<<<1, 256, 0, st>>>(lw, (const double*)ws, grid, alpha, out_partials, out);
     VB_LAUNCH_CHECK();

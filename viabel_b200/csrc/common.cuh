@@ -4,6 +4,7 @@
 #include <stdint.h>
 #include <math.h>
 #include "../../include/viabel_b200.h"
+#include "log_table.cuh"
 
 #define VB_CUDA_TRY(expr)                                   \
     do {                                                    \
@@ -145,6 +146,59 @@ __device__ __forceinline__ double exp_nonpos(double x) {
     return __hiloint2double(__double2hiint(s) + e * 1048576, __double2loint(s));   // * 2^e
 }
 
+// General-range version of the same evaluation (|x| < 700; everything else, incl. NaN, takes the library path).
+__device__ __forceinline__ double fast_exp(double x) {
+    if (!(fabs(x) < 700.0)) return ::exp(x);
+    const double kMagic = 6755399441055744.0;
+    const double t = fma(x, 0x1.71547652b82fep+6, kMagic);
+    const int ki = __double2loint(t);
+    const double kd = t - kMagic;
+    double r = fma(kd, -0x1.62e42fee00000p-7, x);
+    r = fma(kd, -0x1.a39ef35793c76p-39, r);
+    double q = fma(r, 1.0 / 720.0, 1.0 / 120.0);
+    q = fma(r, q, 1.0 / 24.0);
+    q = fma(r, q, 1.0 / 6.0);
+    q = fma(r, q, 0.5);
+    q = fma(r, q, 1.0);
+    q = q * r;
+    const double T = __ldg(&kExp2Table[ki & 63]);
+    const double s = fma(T, q, T);
+    return __hiloint2double(__double2hiint(s) + (ki >> 6) * 1048576, __double2loint(s));
+}
+
+// ---------------------------------------------------------------------------- fast fp64 log
+// log(y) = k ln2 + log(c_i) + log1p(r), r = z / c_i - 1 with z = y / 2^k in [0.6875, 1.375) and c_i the midpoint of
+// the i-th of 128 bit-pattern intervals (|r| <= 2^-8, degree-6 series); table and a pure-Python check of the
+// algorithm: scripts/gen_log_table.py (max error 1 ulp of max(|log y|, 1e-16 absolute near y = 1)).  11 fp64
+// operations instead of the ~35 of the library log1p.  Non-positive, subnormal, inf and NaN arguments take the
+// library path.
+__device__ __forceinline__ double fast_log(double y) {
+    const long long ix = __double_as_longlong(y);
+    if ((unsigned long long)(ix - 0x0010000000000000ll) >= 0x7fe0000000000000ull) return ::log(y);
+    const long long tmp = ix - 0x3fe6000000000000ll;
+    const int i = (int)(tmp >> 45) & 127;
+    const int k = (int)(tmp >> 52);
+    const double z = __longlong_as_double(ix - (tmp & (long long)0xfff0000000000000ull));
+    const double2 t = __ldg(reinterpret_cast<const double2*>(&kLogTable[i][0]));
+    const double r = fma(z, t.x, -1.0);
+    const double kd = (double)k;
+    const double hi = fma(kd, 0x1.62e42fefa3800p-1, t.y);
+    double p = fma(r, -1.0 / 6.0, 0.2);
+    p = fma(r, p, -0.25);
+    p = fma(r, p, 1.0 / 3.0);
+    p = fma(r, p, -0.5);
+    const double lo = fma(kd, 0x1.ef35793c76730p-45, fma(r * r, p, r));
+    return hi + lo;
+}
+// log(1 + v) for v >= 0 with ABSOLUTE accuracy ~1e-16 (the argument is rounded to 1 + v): for sums of O(1) terms
+// (log densities), not for callers that need the relative accuracy of log1p near 0.
+__device__ __forceinline__ double fast_log1p_abs(double v) { return fast_log(1.0 + v); }
+// type-dispatched forms for the templated model / family code (fp32 keeps the library intrinsics)
+__device__ __forceinline__ double vexp(double x) { return fast_exp(x); }
+__device__ __forceinline__ float vexp(float x) { return ::expf(x); }
+__device__ __forceinline__ double vlog1p_abs(double v) { return fast_log1p_abs(v); }
+__device__ __forceinline__ float vlog1p_abs(float v) { return ::log1pf(v); }
+
 // Branch-free variant for streaming sums of weights relative to a maximum / pivot: the same
 // 1-ulp evaluation for -700 <= x <= 0; arguments below -700 (incl. -inf) are clamped, i.e. give
 // e^-700 ~ 1e-304 instead of a smaller number -- invisible in a double-precision sum that holds any
@@ -159,7 +213,10 @@ static __constant__ double kExpCoef[10] = {
     -0x1.62e42fee00000p-7,     // -ln2_hi / 64
     -0x1.a39ef35793c76p-39,    // -ln2_lo / 64
     1.0 / 720.0, 1.0 / 120.0, 1.0 / 24.0, 1.0 / 6.0, 0.5, -700.0};
-__device__ __forceinline__ double exp_nonpos_flush(double x, const double* __restrict__ table) {
+// MIXED = 1 evaluates the tail of the series, h = exp(r) - 1 - r (|h| <= 1.5e-5), in fp32 on the FMA pipe and adds
+// it back in fp64: 7 fp64-pipe operations instead of 12, relative error <= 2e-12 (h carries fp32 rounding, 6e-8 * h).
+template <int MIXED>
+__device__ __forceinline__ double exp_nonpos_flush_v(double x, const double* __restrict__ table) {
     const double kMagic = kExpCoef[1];
     const double xc = !(x <= kExpCoef[9]) ? x : kExpCoef[9];     // unordered compare: NaN passes through
     const double t = fma(xc, kExpCoef[0], kMagic);
@@ -167,16 +224,29 @@ __device__ __forceinline__ double exp_nonpos_flush(double x, const double* __res
     const double kd = t - kMagic;
     double r = fma(kd, kExpCoef[2], xc);
     r = fma(kd, kExpCoef[3], r);
-    double q = fma(r, kExpCoef[4], kExpCoef[5]);
-    q = fma(r, q, kExpCoef[6]);
-    q = fma(r, q, kExpCoef[7]);
-    q = fma(r, q, kExpCoef[8]);
-    q = fma(r, q, 1.0);
-    q = q * r;                                      // exp(r) - 1
+    double q;
+    if (MIXED) {
+        const float rf = (float)r;
+        float h = fmaf(rf, 1.0f / 120.0f, 1.0f / 24.0f);
+        h = fmaf(rf, h, 1.0f / 6.0f);
+        h = fmaf(rf, h, 0.5f);
+        h = h * rf * rf;
+        q = r + (double)h;                          // exp(r) - 1
+    } else {
+        q = fma(r, kExpCoef[4], kExpCoef[5]);
+        q = fma(r, q, kExpCoef[6]);
+        q = fma(r, q, kExpCoef[7]);
+        q = fma(r, q, kExpCoef[8]);
+        q = fma(r, q, 1.0);
+        q = q * r;                                  // exp(r) - 1
+    }
     const double T = table[ki & 63];
     // 2^floor(k/64) folded into the table value (never NaN, stays normal for k >= -64640)
     const double Ts = __hiloint2double(__double2hiint(T) + ((ki & ~63) << 14), __double2loint(T));
     return fma(Ts, q, Ts);
+}
+__device__ __forceinline__ double exp_nonpos_flush(double x, const double* __restrict__ table) {
+    return exp_nonpos_flush_v<0>(x, table);
 }
 
 // ---------------------------------------------------------------------------- ordered keys

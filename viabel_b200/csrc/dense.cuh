@@ -26,7 +26,7 @@ size_t fr_weighted_tf32_workspace_bytes(long long n, int dim);
 int fr_weighted_GS_tf32(double df, long long n, int dim, const float* z, const float* chi2, const double* w,
                         const float* grad, double* out_GS, void* ws, size_t ws_bytes, cudaStream_t st);
 
-size_t regression_tf32_workspace_bytes(long long n, long long n_rows, int dim);
+size_t regression_tf32_workspace_bytes(long long n, long long n_rows, int dim, bool have_planes);
 int regression_logp_grad_tf32(const ModelHost* m, const float* b, long long n, double* out_logp,
                               float* out_grad_or_null, void* ws, size_t ws_bytes, cudaStream_t st);
 

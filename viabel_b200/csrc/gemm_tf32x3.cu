@@ -625,14 +625,14 @@ static long long reg_max_chain() {
 }
 #define kRegMaxChain reg_max_chain()
 struct RegLayout { long long C; int splits; size_t off_xs, off_bs, off_psi, off_rowpart, off_parts, off_gacc, total; };
-static RegLayout reg_layout(long long S, long long N, int D) {
+static RegLayout reg_layout(long long S, long long N, int D, bool have_planes) {
     RegLayout L;
     L.C = reg_chunk_rows(S, N);
     L.splits = plan_gemm(S, D, L.C, auto_splits(S, D, L.C, kRegMaxChain)).splits;
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t at = o; o += (bytes + 255) & ~(size_t)255; return at; };
     const bool resident = D <= kTResKTiles * kTBK;     // no pre-split operands needed
-    L.off_xs = take(split_bytes(N, D));
+    L.off_xs = take(have_planes ? 0 : split_bytes(N, D));     // X planes attached to the model: nothing to stage
     L.off_bs = take(resident ? 0 : split_bytes(S, D));
     L.off_psi = take((size_t)S * L.C * 4);
     L.off_rowpart = take((size_t)S * (L.C / 32 + 1) * 4);
@@ -642,8 +642,8 @@ static RegLayout reg_layout(long long S, long long N, int D) {
     return L;
 }
 
-size_t regression_tf32_workspace_bytes(long long n, long long n_rows, int dim) {
-    return reg_layout(n, n_rows, dim).total + 512;
+size_t regression_tf32_workspace_bytes(long long n, long long n_rows, int dim, bool have_planes) {
+    return reg_layout(n, n_rows, dim, have_planes).total + 512;
 }
 
 int regression_logp_grad_tf32(const ModelHost* m, const float* b, long long S, double* out_logp,
@@ -651,7 +651,7 @@ int regression_logp_grad_tf32(const ModelHost* m, const float* b, long long S, d
     const int D = m->dim;
     const long long N = m->n_rows;
     if (D % 4) return VB_ERR_ALIGN;                       // TMA rows must be 16-byte multiples
-    const RegLayout L = reg_layout(S, N, D);
+    const RegLayout L = reg_layout(S, N, D, m->d_X_planes != nullptr);
     if (!ws || ws_bytes < L.total + 512) return VB_ERR_WORKSPACE;
     char* w = (char*)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
     float* psi = (float*)(w + L.off_psi);
@@ -671,7 +671,10 @@ int regression_logp_grad_tf32(const ModelHost* m, const float* b, long long S, d
     const bool raw1 = resident && (raw_mask & 1), raw2 = (raw_mask & 2) != 0;
     SplitMat xs{}, bs{};
     int rc = VB_OK;
-    if (!raw1 || !raw2) {
+    if (m->d_X_planes != nullptr) {
+        // the design matrix is model data: its tf32 planes were made once (vb_model_regression_attach_split)
+        xs = SplitMat{m->d_X_planes, N, D, pad4(D), N * pad4(D)};
+    } else if (!raw1 || !raw2) {
         rc = split_into(X, N, D, D, (float*)(w + L.off_xs), st, &xs);
         if (rc != VB_OK) return rc;
     }

@@ -9,6 +9,7 @@
 //
 // Reference being replaced: viabel/vb.py:236-245 (black_box_klvi), :248-266 (black_box_chivi)
 // on the families of :48-82 and :140-182.
+#include <new>
 #include "common.cuh"
 #include "models.cuh"
 #include "philox.cuh"
@@ -17,6 +18,63 @@ namespace vb {
 
 constexpr int kMfThreads = 256;
 constexpr int kMfStages = 3;
+constexpr long long kMfSingleCtaMax = 2048;   // samples: at most 8 tiles on one CTA
+
+// Philox stream record kept in device memory by the device-resident optimiser loop: every launch of an
+// iteration has identical kernel arguments (so a CUDA graph can replay it) and picks its stream up from here.
+struct MfDynStream {
+    unsigned long long seed;
+    unsigned int offset;
+    unsigned int step;
+};
+
+struct AdagradArgs {
+    int P, window, n_iters, keep_from;
+    double epsilon;
+    double* var_param;          // [P] in/out
+    const double* out;          // [1 + P]: (value, grad) written by the step
+    double* ring;               // [window][P]
+    const double* rates;        // [n_iters]
+    const unsigned long long* seeds;   // [n_iters]
+    const unsigned int* offsets;       // [n_iters]
+    double* value_history;      // [n_iters]
+    double* param_history;      // [n_iters - keep_from][P]
+    MfDynStream* dyn;
+};
+
+// One AdaGrad update by one CTA (vb.py:368-376): called from the last CTA of a fused step launch, or from the
+// stand-alone update kernel.  Not inlined: keeps the step kernel's register allocation untouched.
+__device__ __noinline__ void adagrad_update_block(const AdagradArgs& g) {
+    const unsigned int step = g.dyn->step;
+    __syncthreads();
+    if (step >= (unsigned int)g.n_iters) return;
+    const int P = g.P, W = g.window;
+    const int cnt = (int)min(step + 1u, (unsigned int)W);
+    const unsigned int oldest = step + 1u - (unsigned int)cnt;
+    const double rate = g.rates[step];
+    for (int j = threadIdx.x; j < P; j += blockDim.x) {
+        const double gr = g.out[1 + j];
+        g.ring[(size_t)(step % W) * P + j] = gr;
+        double acc = 0.0;
+        for (int k = 0; k < cnt; ++k) {
+            const double v = (k == cnt - 1) ? gr : g.ring[(size_t)((oldest + k) % W) * P + j];
+            acc = __dadd_rn(acc, __dmul_rn(v, v));
+        }
+        const double pn = __dsub_rn(g.var_param[j],
+                                    __ddiv_rn(__dmul_rn(rate, gr), __dsqrt_rn(__dadd_rn(g.epsilon, acc))));
+        g.var_param[j] = pn;
+        if (step >= (unsigned int)g.keep_from) g.param_history[(size_t)(step - g.keep_from) * P + j] = pn;
+    }
+    if (threadIdx.x == 0) {
+        g.value_history[step] = g.out[0];
+        const unsigned int next = step + 1u;
+        g.dyn->step = next;
+        if (next < (unsigned int)g.n_iters) {
+            g.dyn->seed = g.seeds[next];
+            g.dyn->offset = g.offsets[next];
+        }
+    }
+}
 
 template <class Model>
 struct MfArgs {
@@ -34,6 +92,9 @@ struct MfArgs {
     double* out_value;         // or null
     double* out_grad;          // or null
     int use_bulk;              // base pointer is 16-byte aligned
+    const MfDynStream* dyn;    // or null: Philox (seed, offset) read from device memory (device-resident optimiser)
+    const AdagradArgs* opt;    // or null: AdaGrad update applied by the last CTA after the finalise (fused iteration)
+    int iters;                 // > 1 (single-CTA Philox launches with opt): optimiser iterations run inside this launch
 };
 
 // log q(x(lambda); lambda) = D*c0 - sum(l) + core(eps); this returns core(eps).
@@ -47,7 +108,7 @@ __device__ __forceinline__ T logq_core(const T (&eps)[D], T df) {
     } else {
         const T inv_df = Math<T>::rcp(df);
 #pragma unroll
-        for (int j = 0; j < D; ++j) s += Math<T>::log1p(eps[j] * eps[j] * inv_df);
+        for (int j = 0; j < D; ++j) s += vlog1p_abs(eps[j] * eps[j] * inv_df);
         return (T)-0.5 * (df + (T)1) * s;
     }
 }
@@ -120,16 +181,22 @@ mf_step_kernel(const __grid_constant__ MfArgs<Model> a) {
 
     // location / scale live in shared memory (broadcast reads) to keep registers for the accumulators
     __shared__ T mean[D], sig[D];
+    const T df = (T)a.df;
+    // Small problems (one CTA) of the device-resident optimiser run `iters` whole iterations inside one launch:
+    // step -> finalise -> AdaGrad update -> reload the iterate, with no kernel boundary in between.
+    const int reps = (PHILOX && a.opt != nullptr && gridDim.x == 1) ? a.iters : 1;
+    const double logq_c = D * mf_logq_const(FAM, a.df);
+    for (int rep = 0; rep < reps; ++rep) {
+    if (rep > 0) __syncthreads();      // the previous iteration's update and shared-memory reads are complete
     if (tid < D) {
         mean[tid] = (T)a.var_param[tid];
         sig[tid] = (T)exp(a.var_param[D + tid]);
     }
     __syncthreads();
-    const T df = (T)a.df;
     double sum_l = 0.0;
 #pragma unroll
     for (int j = 0; j < D; ++j) sum_l += a.var_param[D + j];
-    const double logq0 = D * mf_logq_const(FAM, a.df) - sum_l;
+    const double logq0 = logq_c - sum_l;
 
     double M = (OBJ == VB_OBJ_CHIVI) ? -INFINITY : 0.0;
     double sw = 0.0, s2 = 0.0, cnt = 0.0;
@@ -140,6 +207,17 @@ mf_step_kernel(const __grid_constant__ MfArgs<Model> a) {
     const bool bulk = !PHILOX && a.use_bulk;
     const T* base = reinterpret_cast<const T*>(a.base);
     T* stage_buf = reinterpret_cast<T*>(smem_raw);
+    PhiloxStream rng = a.rng;
+    if (a.dyn != nullptr) {
+        if (PHILOX) {
+            const unsigned long long sd = a.dyn->seed;
+            rng.k0 = (uint32_t)sd;
+            rng.k1 = (uint32_t)(sd >> 32);
+            rng.offset = a.dyn->offset;
+        } else {
+            base += (size_t)a.dyn->step * (size_t)n * D;     // external draws: one (n, D) block per iteration
+        }
+    }
 
     if (bulk) {
         if (tid == 0) {
@@ -174,14 +252,14 @@ mf_step_kernel(const __grid_constant__ MfArgs<Model> a) {
 #pragma unroll
                     for (int q = 0; q < (D + 3) / 4; ++q) {
                         float z[4];
-                        draw_normal_pair(a.rng, gi, (uint32_t)q, z[0], z[1], z[2], z[3]);
+                        draw_normal_pair(rng, gi, (uint32_t)q, z[0], z[1], z[2], z[3]);
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
                             if (4 * q + k < D) eps[4 * q + k] = (T)z[k];
                     }
                 } else {
 #pragma unroll
-                    for (int j = 0; j < D; ++j) eps[j] = (T)draw_student_t(a.rng, gi, (uint32_t)j, (float)a.df);
+                    for (int j = 0; j < D; ++j) eps[j] = (T)draw_student_t(rng, gi, (uint32_t)j, (float)a.df);
                 }
             }
         } else if (bulk && full_tile) {
@@ -263,35 +341,49 @@ mf_step_kernel(const __grid_constant__ MfArgs<Model> a) {
         for (int j = 0; j < D; ++j) { r[4 + j] = ag[j]; r[4 + D + j] = age[j]; }
     }
     __syncthreads();
+    double v = 0.0;
     if (tid < NP) {
         double Mb = red[0];
         for (int w = 1; w < NW; ++w) Mb = fmax(Mb, red[w * NP]);
-        const double v = mf_merge_component(red, NW, NP, OBJ, a.alpha, Mb, tid);
-        a.ws_partials[(size_t)blockIdx.x * NP + tid] = v;
+        v = mf_merge_component(red, NW, NP, OBJ, a.alpha, Mb, tid);
     }
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) s_ticket = atomicAdd(a.ws_ticket, 1u);
-    __syncthreads();
-    if (s_ticket != gridDim.x - 1) return;
+    if (gridDim.x == 1) {
+        // one CTA: its partial IS the merged vector (the cross-CTA merge multiplies by exp(0) = 1: same bits)
+        if (tid < NP) {
+            merged[tid] = v;
+            a.out_partials[tid] = v;
+        }
+    } else {
+        if (tid < NP) a.ws_partials[(size_t)blockIdx.x * NP + tid] = v;
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) s_ticket = atomicAdd(a.ws_ticket, 1u);
+        __syncthreads();
+        if (s_ticket != gridDim.x - 1) return;
 
-    // ---- last CTA: merge block partials in block order, finalise ----
-    __threadfence();
-    const int G = gridDim.x;
-    const volatile double* parts_v = a.ws_partials;
-    double Mg = -INFINITY;
-    for (int b = tid; b < G; b += kMfThreads) Mg = fmax(Mg, parts_v[(size_t)b * NP]);
-    Mg = block_max(Mg, red);
-    if (OBJ == VB_OBJ_KLVI) Mg = 0.0;
-    if (tid < NP) {
-        const double v = mf_merge_component(const_cast<const double*>(a.ws_partials), G, NP, OBJ, a.alpha, Mg, tid);
-        merged[tid] = v;
-        a.out_partials[tid] = v;
+        // ---- last CTA: merge block partials in block order, finalise ----
+        __threadfence();
+        const int G = gridDim.x;
+        const volatile double* parts_v = a.ws_partials;
+        double Mg = -INFINITY;
+        for (int b = tid; b < G; b += kMfThreads) Mg = fmax(Mg, parts_v[(size_t)b * NP]);
+        Mg = block_max(Mg, red);
+        if (OBJ == VB_OBJ_KLVI) Mg = 0.0;
+        if (tid < NP) {
+            const double vm = mf_merge_component(const_cast<const double*>(a.ws_partials), G, NP, OBJ, a.alpha, Mg, tid);
+            merged[tid] = vm;
+            a.out_partials[tid] = vm;
+        }
+        if (tid == 0) *a.ws_ticket = 0u;   // ready for the next launch on this stream
     }
     __syncthreads();
     if (a.out_value != nullptr && tid < NP)
         mf_finalize_thread(FAM, OBJ, a.alpha, a.var_param, D, merged, merged[3], a.out_value, a.out_grad, tid);
-    if (tid == 0) *a.ws_ticket = 0u;   // ready for the next launch on this stream
+    if (a.opt != nullptr) {            // every other CTA has retired its reads of var_param (ticket order)
+        __syncthreads();
+        adagrad_update_block(*a.opt);
+    }
+    }   // rep
 }
 
 // ------------------------------------------------------------------------------------------ dispatch
@@ -314,6 +406,9 @@ struct MfCall {
     unsigned long long seed; unsigned int call_offset; unsigned long long sample_index0;
     double* out_value; double* out_grad; double* out_partials;
     void* ws; size_t ws_bytes; cudaStream_t stream;
+    const MfDynStream* dyn = nullptr;
+    const AdagradArgs* opt = nullptr;
+    int iters = 1;
 };
 
 template <typename T, int FAM, class Model, int OBJ, bool PHILOX>
@@ -336,6 +431,9 @@ static int launch_mf(const MfCall& c, const typename Model::P& mp) {
     const long long n_tiles = (c.n + kMfThreads - 1) / kMfThreads;
     long long grid = (long long)num_sms() * blocks_per_sm;
     if (grid > n_tiles) grid = n_tiles;
+    // Small problems run on ONE CTA (a few tiles in sequence cost less than the cross-CTA ticket / fence / merge
+    // round trips).  The rule depends on n only, so every path (single step, optimiser loop) sums in the same order.
+    if (c.n <= kMfSingleCtaMax) grid = 1;
     if (grid < 1) grid = 1;
     const size_t need = align_up((size_t)grid * NP * sizeof(double), 16) + 16;
     if (c.ws_bytes < need) return VB_ERR_WORKSPACE;
@@ -357,7 +455,11 @@ static int launch_mf(const MfCall& c, const typename Model::P& mp) {
     a.out_partials = c.out_partials;
     a.out_value = c.out_value;
     a.out_grad = c.out_grad;
-    a.use_bulk = (c.base != nullptr) && ((reinterpret_cast<uintptr_t>(c.base) & 15u) == 0);
+    a.use_bulk = (c.base != nullptr) && ((reinterpret_cast<uintptr_t>(c.base) & 15u) == 0) &&
+                 (c.dyn == nullptr || ((size_t)c.n * D * sizeof(T)) % 16 == 0);
+    a.dyn = c.dyn;
+    a.opt = c.opt;
+    a.iters = (PHILOX && c.opt != nullptr && grid == 1 && c.iters > 1) ? c.iters : 1;
     kern<<<(unsigned)grid, kMfThreads, smem, c.stream>>>(a);
     VB_LAUNCH_CHECK();
     return VB_OK;
@@ -491,6 +593,78 @@ __global__ void mf_finalize_kernel(int family, int objective, double alpha, cons
         mf_finalize_thread(family, objective, alpha, var_param, D, merged_dyn, merged_dyn[3], out_value, out_grad, j);
 }
 
+// Model dispatch shared by vb_mf_step and the device-resident optimiser.
+static int mf_step_call(const MfCall& c, const ModelHost* m) {
+    switch (m->kind) {
+        case VB_MODEL_FUNNEL: {
+            const Funnel::P p = Funnel::make(m->p0);
+            return dispatch_family<Funnel>(c, p);
+        }
+        case VB_MODEL_MIXTURE: {
+            Mixture::P p{m->p0};
+            return dispatch_family<Mixture>(c, p);
+        }
+        case VB_MODEL_EIGHT_SCHOOLS: {
+            if (m->n_schools != 8) return VB_ERR_UNSUPPORTED;
+            EightSchools<8>::P p;
+            for (int j = 0; j < 8; ++j) { p.y[j] = m->y[j]; p.inv_sigma[j] = 1.0 / m->sigma[j]; }
+            return dispatch_family<EightSchools<8>>(c, p);
+        }
+        default:
+            return VB_ERR_UNSUPPORTED;   // regression / gauss go through vb_model_logp_grad + vb_mf_reduce
+    }
+}
+
+// ------------------------------------------------------------------------------------------ device-resident AdaGrad
+// adagrad_optimize of viabel/vb.py:345-389 with the whole loop on the device: per iteration one fused step
+// launch (above) and one update launch; the iterate, the window of recent gradients, the value history and the
+// kept iterates never leave HBM, and groups of iterations replay as one CUDA graph.  The update uses explicitly
+// rounded fp64 operations (no FMA contraction) in the reference's evaluation order, so for the same gradients
+// it is bit-identical to the numpy expression at vb.py:371-374.
+__global__ void adagrad_init_kernel(AdagradArgs g) {
+    if (threadIdx.x == 0) {
+        g.dyn->seed = g.seeds[0];
+        g.dyn->offset = g.offsets[0];
+        g.dyn->step = 0u;
+    }
+}
+
+__global__ void __launch_bounds__(128) adagrad_update_kernel(AdagradArgs g) { adagrad_update_block(g); }
+
+}  // namespace vb
+
+struct vb_adagrad_plan {
+    vb::MfCall call;
+    const vb::ModelHost* model;
+    vb::AdagradArgs upd;
+    int graph_iters;
+    int fused;
+    cudaGraph_t graph;
+    cudaGraphExec_t exec;
+};
+
+namespace vb {
+
+static int adagrad_enqueue_one(const vb_adagrad_plan* p, cudaStream_t stream) {
+    MfCall c = p->call;
+    c.stream = stream;
+    const int rc = mf_step_call(c, p->model);
+    if (rc != VB_OK || p->fused) return rc;
+    adagrad_update_kernel<<<1, 128, 0, stream>>>(p->upd);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+// fused single-CTA Philox problems: `iters` iterations inside ONE launch
+static bool adagrad_persistent(const vb_adagrad_plan* p) {
+    return p->fused && p->call.base == nullptr && p->call.n <= kMfSingleCtaMax;
+}
+static int adagrad_enqueue_many(const vb_adagrad_plan* p, int iters, cudaStream_t stream) {
+    MfCall c = p->call;
+    c.stream = stream;
+    c.iters = iters;
+    return mf_step_call(c, p->model);
+}
+
 }  // namespace vb
 
 using namespace vb;
@@ -516,24 +690,7 @@ extern "C" int vb_mf_step(int family, double df, const vb_model* model, int obje
     MfCall c{family, df, objective, alpha, dtype, d_var_param, n, d_base_or_null, seed, call_offset,
              sample_index0, d_out_value_or_null, d_out_grad_or_null, d_out_partials, d_ws, ws_bytes,
              (cudaStream_t)stream};
-    switch (m->kind) {
-        case VB_MODEL_FUNNEL: {
-            Funnel::P p{m->p0};
-            return dispatch_family<Funnel>(c, p);
-        }
-        case VB_MODEL_MIXTURE: {
-            Mixture::P p{m->p0};
-            return dispatch_family<Mixture>(c, p);
-        }
-        case VB_MODEL_EIGHT_SCHOOLS: {
-            if (m->n_schools != 8) return VB_ERR_UNSUPPORTED;
-            EightSchools<8>::P p;
-            for (int j = 0; j < 8; ++j) { p.y[j] = m->y[j]; p.inv_sigma[j] = 1.0 / m->sigma[j]; }
-            return dispatch_family<EightSchools<8>>(c, p);
-        }
-        default:
-            return VB_ERR_UNSUPPORTED;   // regression / gauss go through vb_model_logp_grad + vb_mf_reduce
-    }
+    return mf_step_call(c, m);
 }
 
 extern "C" int vb_mf_finalize(int family, int objective, double alpha, const double* d_var_param,
@@ -544,6 +701,122 @@ extern "C" int vb_mf_finalize(int family, int objective, double alpha, const dou
     mf_finalize_kernel<<<1, 256, NP * sizeof(double), (cudaStream_t)stream>>>(
         family, objective, alpha, d_var_param, dim, d_partials, n_ranks, d_out_value, d_out_grad);
     VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+
+
+/* ---- device-resident AdaGrad loop (viabel/vb.py:345-389) ---- */
+static size_t adagrad_state_layout(int dim, int window, size_t* off_out, size_t* off_part, size_t* off_ring) {
+    const size_t P = 2 * (size_t)dim;
+    size_t o = 16;                                             // MfDynStream
+    o += align_up(sizeof(AdagradArgs), 16);                    // device copy of the update arguments (fused mode)
+    *off_out = o;  o += align_up((1 + P) * sizeof(double), 16);
+    *off_part = o; o += align_up((size_t)VB_MF_NPART(dim) * sizeof(double), 16);
+    *off_ring = o; o += align_up((size_t)window * P * sizeof(double), 16);
+    return o;
+}
+
+extern "C" size_t vb_mf_adagrad_state_bytes(int dim, int window) {
+    if (dim < 1 || window < 1) return 0;
+    size_t a, b, c;
+    return adagrad_state_layout(dim, window, &a, &b, &c);
+}
+
+extern "C" int vb_mf_adagrad_create(int family, double df, const vb_model* model, int objective, double alpha,
+                                    int dtype, double* d_var_param, long long n_samples,
+                                    const void* d_base_or_null, int n_iters, int window, double epsilon,
+                                    const double* d_rates, const unsigned long long* d_seeds,
+                                    const unsigned int* d_offsets, double* d_value_history,
+                                    double* d_param_history, void* d_state, size_t state_bytes,
+                                    void* d_ws, size_t ws_bytes, int graph_iters, int fused, void* stream,
+                                    vb_adagrad_plan** out_plan) {
+    if (!model || !d_var_param || !d_rates || !d_seeds || !d_offsets || !d_value_history || !d_param_history ||
+        !d_state || !d_ws || !out_plan || n_samples < 1 || n_iters < 1 || window < 1 || graph_iters < 0)
+        return VB_ERR_ARG;
+    if (family == VB_FAMILY_MF_T && !(df > 2.0)) return VB_ERR_ARG;
+    if (objective == VB_OBJ_CHIVI && !(alpha > 0.0)) return VB_ERR_ARG;
+    const ModelHost* m = reinterpret_cast<const ModelHost*>(model);
+    const int dim = m->dim;
+    size_t off_out, off_part, off_ring;
+    if (state_bytes < adagrad_state_layout(dim, window, &off_out, &off_part, &off_ring)) return VB_ERR_WORKSPACE;
+    if ((reinterpret_cast<uintptr_t>(d_state) & 15u) != 0) return VB_ERR_ALIGN;
+    char* st = reinterpret_cast<char*>(d_state);
+    cudaStream_t s = (cudaStream_t)stream;
+
+    vb_adagrad_plan* p = new (std::nothrow) vb_adagrad_plan();
+    if (!p) return VB_ERR_ARG;
+    double* out = reinterpret_cast<double*>(st + off_out);
+    MfDynStream* dyn = reinterpret_cast<MfDynStream*>(st);
+    p->call = MfCall{family, df, objective, alpha, dtype, d_var_param, n_samples, d_base_or_null, 0ull, 0u, 0ull,
+                     out, out + 1, reinterpret_cast<double*>(st + off_part), d_ws, ws_bytes, s, dyn};
+    p->model = m;
+    p->upd = AdagradArgs{2 * dim, window, n_iters, 3 * n_iters / 4, epsilon, d_var_param, out,
+                         reinterpret_cast<double*>(st + off_ring), d_rates, d_seeds, d_offsets, d_value_history,
+                         d_param_history, dyn};
+    p->graph_iters = graph_iters;
+    p->fused = fused != 0;
+    p->graph = nullptr;
+    p->exec = nullptr;
+
+    adagrad_init_kernel<<<1, 32, 0, s>>>(p->upd);
+    int rc = (int)cudaGetLastError();
+    AdagradArgs* d_upd = reinterpret_cast<AdagradArgs*>(st + 16);
+    if (rc == VB_OK) rc = (int)cudaMemcpyAsync(d_upd, &p->upd, sizeof(AdagradArgs), cudaMemcpyHostToDevice, s);
+    // one step outside any capture: configures the kernel (attributes, occupancy) and validates the arguments; it
+    // only writes the (value, grad) scratch, which every iteration overwrites before reading
+    if (rc == VB_OK) rc = mf_step_call(p->call, m);
+    if (p->fused) p->call.opt = d_upd;
+    if (rc == VB_OK && graph_iters > 0 && !adagrad_persistent(p)) {
+        cudaStream_t cs = nullptr;
+        rc = (int)cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking);
+        if (rc == VB_OK) {
+            rc = (int)cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal);
+            if (rc == VB_OK) {
+                int rc_body = VB_OK;
+                for (int k = 0; k < graph_iters && rc_body == VB_OK; ++k) rc_body = adagrad_enqueue_one(p, cs);
+                rc = (int)cudaStreamEndCapture(cs, &p->graph);
+                if (rc_body != VB_OK) rc = rc_body;
+            }
+            if (rc == VB_OK) rc = (int)cudaGraphInstantiate(&p->exec, p->graph, 0ull);
+            cudaStreamDestroy(cs);
+        }
+    }
+    if (rc != VB_OK) {
+        if (p->exec) cudaGraphExecDestroy(p->exec);
+        if (p->graph) cudaGraphDestroy(p->graph);
+        delete p;
+        return rc;
+    }
+    *out_plan = p;
+    return VB_OK;
+}
+
+extern "C" int vb_mf_adagrad_run(vb_adagrad_plan* plan, int n_steps, void* stream) {
+    if (!plan || n_steps < 0) return VB_ERR_ARG;
+    cudaStream_t s = (cudaStream_t)stream;
+    int left = n_steps;
+    while (adagrad_persistent(plan) && left > 0) {          // no graph needed: the loop lives inside the kernel
+        const int k = left < 512 ? left : 512;
+        const int rc = adagrad_enqueue_many(plan, k, s);
+        if (rc != VB_OK) return rc;
+        left -= k;
+    }
+    while (plan->exec != nullptr && left >= plan->graph_iters) {
+        VB_CUDA_TRY(cudaGraphLaunch(plan->exec, s));
+        left -= plan->graph_iters;
+    }
+    for (; left > 0; --left) {
+        const int rc = adagrad_enqueue_one(plan, s);
+        if (rc != VB_OK) return rc;
+    }
+    return VB_OK;
+}
+
+extern "C" int vb_mf_adagrad_destroy(vb_adagrad_plan* plan) {
+    if (!plan) return VB_OK;
+    if (plan->exec) cudaGraphExecDestroy(plan->exec);
+    if (plan->graph) cudaGraphDestroy(plan->graph);
+    delete plan;
     return VB_OK;
 }
 
@@ -559,7 +832,7 @@ extern "C" int vb_mf_samples_logweights(int family, double df, const vb_model* m
              sample_index0, nullptr, nullptr, nullptr, nullptr, 0, (cudaStream_t)stream};
     switch (m->kind) {
         case VB_MODEL_FUNNEL: {
-            Funnel::P p{m->p0};
+            const Funnel::P p = Funnel::make(m->p0);
             return dispatch_samples_lw<Funnel>(c, p, d_out_samples, d_out_logp_or_null, d_out_lw);
         }
         case VB_MODEL_MIXTURE: {

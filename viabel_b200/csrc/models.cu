@@ -241,6 +241,15 @@ extern "C" int vb_model_create_regression(const void* d_X, const void* d_y, long
     int rc = new_model(VB_MODEL_REGRESSION, dim, out, &m);
     if (rc) return rc;
     m->d_X = d_X; m->d_y = d_y; m->n_rows = n_rows; m->df = df; m->prior_sd = prior_sd; m->data_dtype = dtype;
+    m->d_X_planes = nullptr;
+    return VB_OK;
+}
+
+extern "C" int vb_model_regression_attach_split(vb_model* model, const float* d_X_planes) {
+    if (!model) return VB_ERR_ARG;
+    ModelHost* m = reinterpret_cast<ModelHost*>(model);
+    if (m->kind != VB_MODEL_REGRESSION || m->data_dtype != VB_F32) return VB_ERR_UNSUPPORTED;
+    m->d_X_planes = d_X_planes;
     return VB_OK;
 }
 
@@ -262,7 +271,7 @@ extern "C" size_t vb_model_logp_grad_workspace_bytes(const vb_model* model, long
     const ModelHost* m = reinterpret_cast<const ModelHost*>(model);
     if (m->kind == VB_MODEL_REGRESSION) {
         if (dtype == VB_F32 && m->data_dtype == VB_F32)
-            return regression_tf32_workspace_bytes(n, m->n_rows, m->dim);
+            return regression_tf32_workspace_bytes(n, m->n_rows, m->dim, m->d_X_planes != nullptr);
         const long long chunk = regression_chunk_rows(n, m->n_rows);
         return align_up((size_t)n * m->dim * 8, 256) + (size_t)n * chunk * 8 + 256;
     }
@@ -280,7 +289,7 @@ extern "C" int vb_model_logp_grad(const vb_model* model, int dtype, const void* 
     cudaStream_t st = (cudaStream_t)stream;
     switch (m->kind) {
         case VB_MODEL_FUNNEL: {
-            Funnel::P p{m->p0};
+            const Funnel::P p = Funnel::make(m->p0);
             return run_elementwise<Funnel>(p, dtype, d_x, n, d_out_logp, d_out_grad_or_null, st);
         }
         case VB_MODEL_MIXTURE: {

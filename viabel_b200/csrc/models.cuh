@@ -24,6 +24,7 @@ struct ModelHost {
     double df;
     double prior_sd;
     int data_dtype;
+    const float* d_X_planes;   // or null: tf32 hi/lo planes of X made once by vb_split_f32 (vb_model_regression_attach_split)
     // gauss
     const double* d_mean;
     const double* d_prec;
@@ -31,17 +32,18 @@ struct ModelHost {
 
 struct Funnel {
     static constexpr int D = 2;
-    struct P { double a; };
+    struct P { double inv_a, inv_a2, lp0; };       // 1/a, 1/a^2, -log(2 pi) - log a: hoisted to the host
+    static inline P make(double a) { return P{1.0 / a, 1.0 / (a * a), -1.8378770664093453 - log(a)}; }
     template <typename T>
     static __device__ __forceinline__ void eval(const P& p, const T (&x)[D], T& lp, T (&g)[D]) {
         const T mu = x[0], ls = x[1];
-        const T a = (T)p.a;
-        const T e = Math<T>::exp((T)-2 * ls);
+        const T e = vexp((T)-2 * ls);
         const T mu2e = mu * mu * e;
+        const T t = ls * (T)p.inv_a;
         // norm.logpdf(ls, 0, a) + norm.logpdf(mu, 0, exp(ls))
-        lp = (T)(-1.8378770664093453) - Math<T>::log(a) - (T)0.5 * (ls / a) * (ls / a) - ls - (T)0.5 * mu2e;
+        lp = (T)p.lp0 - (T)0.5 * t * t - ls - (T)0.5 * mu2e;
         g[0] = -mu * e;
-        g[1] = -ls / (a * a) - (T)1 + mu2e;
+        g[1] = -ls * (T)p.inv_a2 - (T)1 + mu2e;
     }
 };
 
@@ -66,7 +68,7 @@ struct EightSchools {
     template <typename T>
     static __device__ __forceinline__ void eval(const P& p, const T (&u)[D], T& lp, T (&g)[D]) {
         const T mu = u[0], lt = u[1];
-        const T tau = Math<T>::exp(lt);
+        const T tau = vexp(lt);
         const T tau2 = tau * tau;
         T s_rr = 0, s_ros = 0, s_tros = 0, s_tt = 0;
 #pragma unroll
@@ -81,7 +83,7 @@ struct EightSchools {
             s_tt += th * th;
             g[2 + j] = -th + tau * ros;
         }
-        lp = -mu * mu * (T)0.02 - Math<T>::log1p(tau2 * (T)0.04) + lt - (T)0.5 * s_tt - (T)0.5 * s_rr;
+        lp = -mu * mu * (T)0.02 - vlog1p_abs(tau2 * (T)0.04) + lt - (T)0.5 * s_tt - (T)0.5 * s_rr;
         g[0] = -mu * (T)0.04 + s_ros;
         g[1] = (T)1 - (T)2 * tau2 / ((T)25 + tau2) + tau * s_tros;
     }

@@ -14,6 +14,7 @@
 // Selection, tail membership and tail order are exact (bit-level comparisons on the same
 // fp64 values the reference compares); k-hat and the smoothed values differ from numpy only
 // by summation order.
+#include <cstdlib>
 #include "common.cuh"
 #include <cfloat>
 
@@ -230,8 +231,8 @@ __device__ __forceinline__ void filter_flush(Cand* mybuf, unsigned int* wcount, 
     __syncwarp();
 }
 
-template <bool ALIGNED>
-__global__ void __launch_bounds__(kFThreads)
+template <bool ALIGNED, int MIXED, int MINB>
+__global__ void __launch_bounds__(kFThreads, MINB)
 filter_kernel(const double* __restrict__ lw, long long n, long long index0, const double* __restrict__ pivot_ptr,
               const FilterOut o) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -291,8 +292,8 @@ filter_kernel(const double* __restrict__ lw, long long n, long long index0, cons
                 // branch-free main path: candidates add e^-700 (nothing); NaN poisons the sum
                 const bool c0 = v[q].x >= pivot, c1 = v[q].y >= pivot;
                 any = any || c0 || c1;
-                body += exp_nonpos_flush(c0 ? -INFINITY : v[q].x - pivot, s_table);
-                body2 += exp_nonpos_flush(c1 ? -INFINITY : v[q].y - pivot, s_table);
+                body += exp_nonpos_flush_v<MIXED>(c0 ? -INFINITY : v[q].x - pivot, s_table);
+                body2 += exp_nonpos_flush_v<MIXED>(c1 ? -INFINITY : v[q].y - pivot, s_table);
             }
             if (any) {
 #pragma unroll
@@ -736,7 +737,10 @@ static int run_gpd_fit(const double* x2, const long long* counts, long long n2_u
 }
 
 constexpr int kSmallGrid = kNumSMs * 2;
-static int filter_grid(long long n) { return grid_for((n + kFPerThread - 1) / kFPerThread, kFThreads, kNumSMs * 3); }
+static int filter_grid(long long n) {
+    static const int per_sm = (getenv("VB_FILTER_OCC4") != nullptr && atoi(getenv("VB_FILTER_OCC4")) != 0) ? 4 : 3;
+    return grid_for((n + kFPerThread - 1) / kFPerThread, kFThreads, kNumSMs * per_sm);
+}
 
 __global__ void sum_blocks_kernel(const double* __restrict__ blocks, int G, double* __restrict__ out) {
     __shared__ double scratch[32];
@@ -812,21 +816,31 @@ extern "C" int vb_psis_filter(const double* d_lw, long long n_local, long long i
         return VB_ERR_ARG;
     if (ws_bytes < vb_psis_filter_workspace_bytes(n_local)) return VB_ERR_WORKSPACE;
     cudaStream_t st = (cudaStream_t)stream;
-    static bool attr = false;
-    if (!attr) {
-        VB_CUDA_TRY(cudaFuncSetAttribute(filter_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFSmem));
-        VB_CUDA_TRY(cudaFuncSetAttribute(filter_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFSmem));
-        attr = true;
-    }
+    // experiment knobs: VB_EXP_MIXED=1 (fp32 series tail in the exp), VB_FILTER_OCC4=1 (64 registers, 4 CTAs per SM)
+    static const bool mixed = getenv("VB_EXP_MIXED") != nullptr && atoi(getenv("VB_EXP_MIXED")) != 0;
+    static const bool occ4 = getenv("VB_FILTER_OCC4") != nullptr && atoi(getenv("VB_FILTER_OCC4")) != 0;
     const int G = filter_grid(n_local);
     double* blk_body = (double*)d_ws;
     double* blk_max = (double*)((char*)d_ws + align_up((size_t)G * 8, 256));
     VB_CUDA_TRY(cudaMemsetAsync(d_out_count, 0, 8, st));
     FilterOut fo{(Cand*)d_out_cand, cap, d_out_count, blk_body, blk_max};
-    if ((reinterpret_cast<uintptr_t>(d_lw) & 15u) == 0)
-        filter_kernel<true><<<G, kFThreads, kFSmem, st>>>(d_lw, n_local, index0, d_pivot_x, fo);
-    else
-        filter_kernel<false><<<G, kFThreads, kFSmem, st>>>(d_lw, n_local, index0, d_pivot_x, fo);
+    const bool aligned = (reinterpret_cast<uintptr_t>(d_lw) & 15u) == 0;
+#define VB_FILTER_LAUNCH(AL, MX, MB)                                                                              \
+    do {                                                                                                          \
+        static bool attr = false;                                                                                 \
+        if (!attr) {                                                                                              \
+            VB_CUDA_TRY(cudaFuncSetAttribute(filter_kernel<AL, MX, MB>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                             (int)kFSmem));                                                       \
+            attr = true;                                                                                          \
+        }                                                                                                         \
+        filter_kernel<AL, MX, MB><<<G, kFThreads, kFSmem, st>>>(d_lw, n_local, index0, d_pivot_x, fo);            \
+    } while (0)
+    if (!aligned) VB_FILTER_LAUNCH(false, 0, 3);
+    else if (mixed && occ4) VB_FILTER_LAUNCH(true, 1, 4);
+    else if (mixed) VB_FILTER_LAUNCH(true, 1, 3);
+    else if (occ4) VB_FILTER_LAUNCH(true, 0, 4);
+    else VB_FILTER_LAUNCH(true, 0, 3);
+#undef VB_FILTER_LAUNCH
     VB_LAUNCH_CHECK();
     filter_finish_kernel<<<1, 256, 0, st>>>(blk_body, blk_max, G, d_out_body_max, d_out_body_max + 1);
     VB_LAUNCH_CHECK();

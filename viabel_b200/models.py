@@ -14,6 +14,7 @@ reference passes to ``black_box_klvi`` / ``black_box_chivi`` (``viabel/vb.py:236
 import ctypes as C
 
 import numpy as np
+import torch
 
 from . import _lib
 from ._device import WS, dtype_code, is_host, like_input, ptr, stream_ptr, to_dev, torch_dtype
@@ -132,6 +133,13 @@ class StudentTRegression(Model):
         self.df, self.prior_sd, self.data_dtype = float(df), float(prior_sd), code
         _lib.check(_lib.lib.vb_model_create_regression(ptr(Xd), ptr(yd), Xd.shape[0], Xd.shape[1], self.df,
                                                        self.prior_sd, code, C.byref(self._handle)), 'regression')
+        if code == _lib.F32 and Xd.shape[1] % 4 == 0:
+            # tensor path: X feeds tcgen05 as tf32 (hi, lo) planes; it is model data, so split it once here
+            N, d = Xd.shape
+            planes = torch.empty(_lib.lib.vb_split_bytes(N, d) // 4, dtype=torch.float32, device=Xd.device)
+            _lib.check(_lib.lib.vb_split_f32(ptr(Xd), N, d, d, ptr(planes), stream_ptr()), 'vb_split_f32')
+            _lib.check(_lib.lib.vb_model_regression_attach_split(self._handle, ptr(planes)), 'attach_split')
+            self._keep.append(planes)
 
 
 class CorrelatedGaussian(Model):

@@ -16,6 +16,7 @@ reference's persistent ``RandomState(0)``) unless supplied through ``base_draws=
 There is no CPU fallback.
 """
 from collections import namedtuple
+import ctypes
 import math
 
 import numpy as np
@@ -535,11 +536,108 @@ def learning_rate_schedule(n_iters, learning_rate, learning_rate_end):
             yield learning_rate_end
 
 
+def _device_loop_ok(objective_and_grad, has_log_norm):
+    """The device-resident loop serves single-rank objectives of the fused mean-field path."""
+    o = objective_and_grad
+    if has_log_norm or not isinstance(o, _Objective):
+        return False
+    if o.impl.kind == _lib.FAMILY_FR_T or not o.model.fused:
+        return False
+    return _dist_info(o.group)[1] == 1
+
+
+def _adagrad_device(n_iters, o, init_param, window, learning_rate, epsilon, learning_rate_end, base_draws,
+                    graph_iters, progress, fused=True):
+    """``vb.py:345-389`` with the loop on the device (``vb_mf_adagrad_*``): one fused step launch and one
+    update launch per iteration, replayed in CUDA graphs of ``graph_iters`` iterations; the host only reads
+    the value history back between groups of iterations to refresh the progress bar."""
+    impl, d = o.impl, o.impl.dim
+    P = 2 * d
+    rates = np.fromiter(learning_rate_schedule(n_iters, learning_rate, learning_rate_end), dtype=np.float64,
+                        count=n_iters)
+    if base_draws is not None:
+        base = impl.coerce_base(base_draws.reshape(-1, d) if hasattr(base_draws, 'reshape') else base_draws)['eps']
+        if base.shape[0] % n_iters != 0 or base.shape[0] // n_iters < 1:
+            raise ValueError('base_draws must have shape (n_iters, n_samples, dim)')
+        n_samples = base.shape[0] // n_iters
+        seeds, offsets = np.zeros(n_iters, dtype=np.uint64), np.zeros(n_iters, dtype=np.uint32)
+    else:
+        base, n_samples = None, o.n
+        if o.obj == _lib.OBJ_KLVI:                      # the family's persistent stream, one call offset per step
+            seeds = np.full(n_iters, impl.seed0, dtype=np.uint64)
+            offsets = (impl.offset + np.arange(n_iters)).astype(np.uint32)
+            impl.offset += n_iters
+        else:                                           # CHIVI: a fresh global-RNG seed per call (vb.py:258)
+            seeds = np.array([np.random.randint(2 ** 32) for _ in range(n_iters)], dtype=np.uint64)
+            offsets = np.zeros(n_iters, dtype=np.uint32)
+    dev = device()
+    param = torch.from_numpy(np.array(init_param, dtype=np.float64, copy=True)).to(dev)
+    if param.shape != (P,):
+        raise ValueError('init_param must have shape (%d,)' % P)
+    keep_from = 3 * n_iters // 4
+    d_rates = torch.from_numpy(rates).to(dev)
+    d_seeds = torch.from_numpy(seeds.view(np.int64)).to(dev)
+    d_offsets = torch.from_numpy(offsets.view(np.int32)).to(dev)
+    values = torch.zeros(n_iters, dtype=torch.float64, device=dev)
+    kept = torch.zeros((n_iters - keep_from, P), dtype=torch.float64, device=dev)
+    state = torch.zeros(_lib.lib.vb_mf_adagrad_state_bytes(d, window), dtype=torch.uint8, device=dev)
+    ws = torch.zeros(_lib.lib.vb_mf_step_workspace_bytes(d), dtype=torch.uint8, device=dev)
+    plan = ctypes.c_void_p()
+    _lib.check(_lib.lib.vb_mf_adagrad_create(
+        impl.kind, impl.df, o.model.handle, o.obj, o.alpha, impl.code, ptr(param), n_samples, ptr(base), n_iters,
+        window, float(epsilon), ptr(d_rates), ptr(d_seeds), ptr(d_offsets), ptr(values), ptr(kept), ptr(state),
+        state.numel(), ptr(ws), ws.numel(), int(graph_iters), int(bool(fused)), stream_ptr(), ctypes.byref(plan)),
+        'vb_mf_adagrad_create')
+    try:
+        group = max(int(graph_iters), 1) * max(1, 500 // max(int(graph_iters), 1))
+        done = 0
+        while done < n_iters:
+            k = min(group, n_iters - done)
+            _lib.check(_lib.lib.vb_mf_adagrad_run(plan, k, stream_ptr()), 'vb_mf_adagrad_run')
+            done += k
+            if progress is not None:
+                i = (done - 1) // 10 * 10                # last iteration of this group that refreshes the bar
+                host = values[max(0, i - 1000):i + 1].cpu().numpy()
+                progress.update(k)
+                progress.set_description('Average Loss = {:,.5g}'.format(np.mean(host)))
+        kept_host = kept.cpu().numpy()
+        values_host = values.cpu().numpy()
+    finally:
+        torch.cuda.current_stream().synchronize()
+        _lib.lib.vb_mf_adagrad_destroy(plan)
+    return np.mean(kept_host, axis=0), kept_host, values_host, np.array([0] * n_iters)
+
+
 def adagrad_optimize(n_iters, objective_and_grad, init_param,
                      has_log_norm=False, window=10, learning_rate=.01,
-                     epsilon=.1, learning_rate_end=None):
+                     epsilon=.1, learning_rate_end=None, device_loop=None, base_draws=None, graph_iters=None):
     """Windowed AdaGrad with iterate averaging over the last quarter (``vb.py:345-389``).
-    Host loop over ``P``-vectors; every iteration makes one call into the CUDA objective."""
+
+    ``device_loop`` (extension): ``None`` runs the whole loop on the device when the objective is a single-rank
+    fused mean-field objective of this package (same iterates as the host loop, bit for bit, because both consume
+    the same Philox streams and the update is evaluated in the same order), ``False`` forces the host loop of the
+    reference, ``True`` raises if the device loop does not apply; ``'two-launch'`` is ``True`` with the update in its
+    own kernel instead of the step kernel's last CTA (ablation).  ``base_draws`` (n_iters, n_samples, dim):
+    external base draws, one block per iteration (validation against the CPU oracle).  ``graph_iters``:
+    iterations per CUDA-graph replay (default 50; 0 = plain launches)."""
+    if device_loop is None:
+        device_loop = _device_loop_ok(objective_and_grad, has_log_norm)
+    elif device_loop and not _device_loop_ok(objective_and_grad, has_log_norm):
+        raise TypeError('device_loop=True needs a single-rank fused mean-field objective of viabel_b200.vb and '
+                        'has_log_norm=False')
+    if device_loop:
+        # learning-rate validation errors surface before the progress bar opens, as in the reference (vb.py:356)
+        if graph_iters is None:
+            graph_iters = 50 if n_iters >= 100 else 0
+        with tqdm.trange(n_iters) as progress:
+            try:
+                return _adagrad_device(n_iters, objective_and_grad, init_param, window, learning_rate, epsilon,
+                                       learning_rate_end, base_draws, graph_iters, progress,
+                                       fused=device_loop != 'two-launch')
+            finally:
+                progress.close()
+    if base_draws is not None:
+        base_draws = np.asarray(base_draws)
     recent_grads, recent_norms = [], []
     values, norms, kept = [], [], []
     param = np.array(init_param, dtype=float, copy=True)
@@ -548,10 +646,11 @@ def adagrad_optimize(n_iters, objective_and_grad, init_param,
         try:
             rates = learning_rate_schedule(n_iters, learning_rate, learning_rate_end)
             for i, rate in zip(progress, rates):
+                extra = {} if base_draws is None else {'base_draws': base_draws[i]}
                 if has_log_norm:
-                    value, grad, log_norm = objective_and_grad(param)
+                    value, grad, log_norm = objective_and_grad(param, **extra)
                 else:
-                    value, grad = objective_and_grad(param)
+                    value, grad = objective_and_grad(param, **extra)
                     log_norm = 0
                 values.append(value)
                 norms.append(log_norm)
