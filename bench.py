@@ -186,6 +186,12 @@ def main():
         units_total = wl.units_per_step * world * steps
         roof = wl.roofline(ms_kernel, hbm, tf)
         roof['peak_source'] = src
+        tpath = os.path.join(ROOT, 'profiles', 'traffic.json')      # measured DRAM bytes of the same kernel(s) (ncu)
+        if os.path.exists(tpath):
+            with open(tpath) as fh:
+                t = json.load(fh).get(args.workload)
+            if t:
+                roof['traffic'], roof['traffic_unit'], roof['traffic_source'] = t['bytes'], 'bytes/launch', t['source']
         line = {
             'metric': wl.metric, 'value': units_total / (ms_dev / 1e3), 'unit': wl.unit,
             'n_gpus': world, 'steps': steps, 'warmup': warmup, 'ms_per_step': ms_dev / steps,
