@@ -365,7 +365,102 @@ class C5(Workload):
                 'e2e': {'value': rate, 'unit': self.unit, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
 
 
-WORKLOADS = {'c1': C1, 'c4': C4, 'c5': C5}
+# ======================================================================================= N3
+def n3_log_lik(n, m, seed=31):
+    """(n, m) log-likelihood draws whose importance ratios -log_lik have GPD(k = 0.5) right tails."""
+    u = np.random.RandomState(seed).rand(n, m)
+    return -np.log(np.expm1(-0.5 * np.log1p(-u)) / 0.5)
+
+
+class N3(Workload):
+    """psisloo (notebooks/psis.py:68-109) on 4000 posterior draws x 8192 observations: one CTA per column."""
+    name = 'n3'
+    n, m = 4000, 8192
+    unit = 'weights/s'
+    default_steps, default_warmup = 20, 3
+    cpu_cols = 256
+
+    def setup(self):
+        import torch
+        from viabel_b200 import psis, _lib
+        from viabel_b200._device import ptr
+        self.torch, self.psis, self.lib, self._ptr = torch, psis, _lib, ptr
+        g = torch.Generator(device='cuda')
+        g.manual_seed(31 + self.rank)
+        u = torch.rand((self.n, self.m), dtype=torch.float64, device='cuda', generator=g)
+        self.ll = -torch.log(torch.expm1(-0.5 * torch.log1p(-u)) / 0.5)          # (n, m), as the reference takes it
+        del u
+        self.units_per_step = self.n * self.m
+        self.h2d_bytes, self.d2h_bytes = self.n * self.m * 8, 8 * (1 + 2 * self.m)
+        self.launches_per_step = 3                                                # negate+transpose, smooth, sum
+        self._cols = (-self.ll).t().contiguous()
+        self._out = torch.empty_like(self._cols)
+        self._ks = torch.empty(self.m, dtype=torch.float64, device='cuda')
+        self._loo = torch.empty(self.m, dtype=torch.float64, device='cuda')
+        self._pin = None
+
+    def step_device(self):
+        return self.psis.psisloo(self.ll)
+
+    def step_e2e(self):
+        if self._pin is None:
+            self._pin = self.torch.empty((self.n, self.m), dtype=self.torch.float64, pin_memory=True)
+            self._pin.copy_(self.ll)
+        return self.psis.psisloo(self._pin.numpy())
+
+    def kernel_only(self):
+        from viabel_b200._device import stream_ptr
+        p = self._ptr
+        self.lib.check(self.lib.lib.vb_psis_smooth_columns(p(self._cols), p(self._out), self.n, self.m, 1.0,
+                                                           p(self._ks), p(self._loo), stream_ptr()))
+
+    def roofline(self, ms_kernel, hbm_gbs, bf16_tflops):
+        b = 16 * self.n * self.m         # each weight read once and written once (the second read for loo hits L2)
+        ach = b / (ms_kernel * 1e-3) / 1e9
+        return {'bound': 'hbm', 'achieved': ach, 'peak': hbm_gbs, 'unit': 'GB/s', 'frac': ach / hbm_gbs,
+                'traffic': None, 'kernel': 'psis_columns_kernel (one CTA per column: sort + GPD fit + smoothing + loo)',
+                'ms_per_launch': ms_kernel, 'algorithmic_bytes_per_launch': b,
+                'note': 'per column the CTA sorts 4096 (key, index) pairs in shared memory (78 compare-exchange '
+                        'steps): the kernel is bound by shared-memory sort latency, not by HBM'}
+
+    def config(self):
+        return {'workload': self.config_name(), 'draws': self.n, 'columns': self.m,
+                'l2': 'input + output (524 MB) larger than L2', 'parallelism': 'columns sharded x%d' % self.world}
+
+    def config_name(self):
+        return 'n3: psisloo on 4000 draws x 8192 observations (GPD k=0.5 ratios), one CTA per column'
+
+    def _cpu(self, cols):
+        import warnings
+        from oracle import psis_np
+        ll = n3_log_lik(self.n, cols)
+        t0 = time.perf_counter()
+        with warnings.catch_warnings():
+            warnings.simplefilter('ignore')
+            psis_np.psisloo(ll)
+        return self.n * cols / (time.perf_counter() - t0)
+
+    def cpu_baseline(self):
+        rate = self._cpu(self.cpu_cols)
+        return {'value': rate, 'unit': self.unit, 'cores': 1, 'kind': 'port',
+                'sample': 'oracle psisloo on %d of the %d columns (4000 draws each), single-threaded numpy'
+                          % (self.cpu_cols, self.m)}
+
+    def reference_arm(self, steps, warmup):
+        k = max(1, min(steps, 3))
+        t0 = time.perf_counter()
+        rates = [self._cpu(self.cpu_cols) for _ in range(k)]
+        dt = (time.perf_counter() - t0) / k
+        rate = float(np.mean(rates))
+        cb = {'value': rate, 'unit': self.unit, 'cores': 1, 'kind': 'port',
+              'sample': 'oracle psisloo on %d columns x 4000 draws per step (argsort + GPD fit per column)' % self.cpu_cols}
+        return {'metric': self.metric, 'value': rate, 'unit': self.unit, 'ms_per_step': dt * 1e3, 'dtype': 'f64',
+                'config': {'workload': self.config_name()}, 'cpu_baseline': cb,
+                'e2e': {'value': rate, 'unit': self.unit, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+
+
+WORKLOADS = {'c1': C1, 'c4': C4, 'c5': C5, 'n3': N3}
+
 
 
 # ======================================================================================= C3

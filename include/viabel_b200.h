@@ -318,6 +318,20 @@ int vb_psis_smooth(const double* d_lw_in, double* d_lw_out, long long n, double 
                    double* d_out_diag, long long* d_out_tail_idx_or_null,
                    void* d_ws, size_t ws_bytes, void* stream);
 
+/* ------------------------------------------------------------------------------------
+ * Batched columns: psislw on an (n, m) matrix (notebooks/psis.py:136-137,163 -- one independent
+ * smoothing per column) and the leave-one-out reduction of psisloo (notebooks/psis.py:68-109).
+ * One CTA per column, the whole column in shared memory (n <= vb_psis_columns_max_n() = 8192;
+ * longer columns: call vb_psis_smooth per column).
+ *   d_lw_cols / d_out_cols   (m, n) float64: column j of the reference's (n, m) array is row j here
+ *   d_out_k[m]               k-hat per column (inf where the tail has <= 4 points, psis.py:177-179)
+ *   d_out_loo_or_null[m]     log sum_i exp(out_ij - lw_ij): with lw = -log_lik this is `loos` of
+ *                            psisloo (psis.py:104-107)
+ * ---------------------------------------------------------------------------------- */
+long long vb_psis_columns_max_n(void);
+int vb_psis_smooth_columns(const double* d_lw_cols, double* d_out_cols, long long n, long long m,
+                           double reff, double* d_out_k, double* d_out_loo_or_null, void* stream);
+
 /* Staged PSIS for log weights sharded by contiguous index ranges (rank r owns global indices
  * [index0, index0 + n_local)); vb_psis_smooth is the same sequence on one GPU.  Candidates are
  * 16-byte (key, global index) pairs; between the stages the caller exchanges a few small buffers:

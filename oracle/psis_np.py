@@ -11,7 +11,7 @@ of the CUDA path (ascending original index); on tie-free input both kinds agree 
 """
 import numpy as np
 
-__all__ = ['psislw', 'psislw_detail', 'gpdfitnew', 'gpinv', 'sumlogs']
+__all__ = ['psislw', 'psislw_detail', 'psisloo', 'gpdfitnew', 'gpinv', 'sumlogs']
 
 _K_MIN = 1.0 / 3.0                                       # psis.py:160
 _LOG_TINY = np.log(np.finfo(float).tiny)                 # psis.py:158
@@ -170,3 +170,14 @@ def psislw(lw, Reff=1.0, overwrite_lw=False, sort_kind='default'):
     if lw_out.ndim == 1:                                 # psis.py:205-206
         kss = kss[0]
     return lw_out, kss
+
+
+def psisloo(log_lik, **kwargs):
+    """psis.py:68-109 -- PSIS leave-one-out log predictive densities from an (n, m) matrix of log-likelihood
+    draws: ``lw = -log_lik`` smoothed column by column, ``loos = sumlogs(lw + log_lik, axis=0)``."""
+    kwargs['overwrite_lw'] = True                        # psis.py:100
+    lw = -log_lik                                        # psis.py:102
+    lw, ks = psislw(lw, **kwargs)                        # psis.py:104
+    lw += log_lik                                        # psis.py:106
+    loos = sumlogs(lw, axis=0)                           # psis.py:107
+    return loos.sum(), loos, ks                          # psis.py:108-109

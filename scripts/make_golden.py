@@ -64,6 +64,16 @@ def main():
             k, sigma = rp.gpdfitnew(xs, sort=False)
             out['gpd/%s/k' % name] = np.float64(k)
             out['gpd/%s/sigma' % name] = np.float64(sigma)
+        # ---- psisloo and 2-D psislw (psis.py:68-109, 136-137)
+        for name in gi.LOO_CASES:
+            ll = gi.loo_case(name)
+            loo, loos, ks = rp.psisloo(ll.copy())
+            out['loo/%s/loo' % name] = np.float64(loo)
+            out['loo/%s/loos' % name] = loos
+            out['loo/%s/ks' % name] = ks
+            lw2, ks2 = rp.psislw(-ll)
+            out['loo/%s/lw_probe' % name] = np.ascontiguousarray(lw2[gi.probe_indices(ll.shape[0])])
+            assert np.array_equal(ks, ks2)
         p = gi.gpinv_probs()
         for (k, s) in gi.GPINV_PARAMS:
             out['gpinv/%g_%g' % (k, s)] = rp.gpinv(p, k, s)

@@ -7,6 +7,7 @@ BOUNDS_CASES = ['mixture_nb', 'mixture_nb_known', 'gauss3d', 'offset1d']
 PSIS_CASES = ['gpd05_n10', 'gpd05_n100', 'gpd05_n5000', 'gpd07_n20000', 'gauss_n3000', 'gpd05_n200000',
               'offset_n1000', 'gpd05_reff_n4000']
 GPD_CASES = ['gpd05_2000', 'gpd02_500', 'exp_50']
+LOO_CASES = ['regression_n2000_m9', 'mixed_n300_m5', 'tiny_n12_m3']
 GPINV_PARAMS = [(0.5, 1.0), (-0.3, 2.0), (0.0, 1.5), (0.7, -1.0)]
 
 
@@ -79,3 +80,26 @@ def gpd_case(name):
 
 def gpinv_probs():
     return np.concatenate([[0.0], (np.arange(0.5, 64) / 64), [1.0]])
+
+
+def loo_case(name):
+    """(n, m) log-likelihood draws for psisloo: n posterior draws of m pointwise terms.  Columns mix heavy tails
+    (an outlying observation: -log_lik has a GPD-like right tail), light tails (no smoothing) and ties."""
+    if name == 'regression_n2000_m9':
+        rs = np.random.RandomState(21)
+        n, m = 2000, 9
+        beta = 1.0 + 0.3 * rs.randn(n)                                  # posterior draws of a slope
+        sd = np.exp(0.1 * rs.randn(n))
+        xs = np.linspace(-2.0, 2.0, m)
+        ys = xs + np.array([0.1, -0.2, 0.05, 0.0, 3.5, -0.1, 0.2, -4.0, 0.3])     # two outliers
+        r = (ys[None, :] - beta[:, None] * xs[None, :]) / sd[:, None]
+        return -0.5 * r * r - np.log(sd)[:, None] - 0.9189385332046727
+    if name == 'mixed_n300_m5':
+        rs = np.random.RandomState(22)
+        ll = -gpd_log_weights(300 * 5, 0.6, 23).reshape(300, 5)
+        ll[:, 1] = 0.2 * rs.randn(300)                                  # light tail
+        ll[:, 3] = np.round(ll[:, 3], 1)                                # ties
+        return ll
+    if name == 'tiny_n12_m3':
+        return np.random.RandomState(24).randn(12, 3)
+    raise KeyError(name)

@@ -197,6 +197,58 @@ def test_psislw_two_dimensional_and_device_input():
         psis.psislw(a, out=np.empty(4999))
 
 
+@pytest.mark.parametrize('name', gi.LOO_CASES)
+def test_psisloo_vs_reference_outputs(golden, name):
+    """Batched-column kernel (one CTA per column) against the real reference's psisloo / 2-D psislw outputs.
+    Tolerances: k-hat and weights 1e-11 (summation order), loo terms rtol 1e-12."""
+    import torch
+    from viabel_b200 import psis
+    ll = gi.loo_case(name)
+    pre = 'loo/%s/' % name
+    loo, loos, ks = psis.psisloo(ll)
+    finite = np.isfinite(golden[pre + 'ks'])
+    assert np.array_equal(np.isinf(ks), ~finite)
+    np.testing.assert_allclose(ks[finite], golden[pre + 'ks'][finite], rtol=1e-11)
+    np.testing.assert_allclose(loos, golden[pre + 'loos'], rtol=1e-12)
+    np.testing.assert_allclose(loo, golden[pre + 'loo'], rtol=1e-12)
+    out, ks2 = psis.psislw(-ll)
+    assert out.shape == ll.shape and out.flags.f_contiguous
+    np.testing.assert_array_equal(ks2, ks)
+    probe = out[gi.probe_indices(ll.shape[0])]
+    cols = [j for j in range(ll.shape[1]) if not (name == 'mixed_n300_m5' and j == 3)]   # column 3: ties, see below
+    np.testing.assert_allclose(probe[:, cols], golden[pre + 'lw_probe'][:, cols], rtol=0, atol=1e-11)
+    # tie-break contract (numpy kind='stable'): the whole matrix against the stable-sort oracle
+    oout, oks = _quiet(psis_np.psislw, -ll, sort_kind='stable')
+    np.testing.assert_allclose(out, oout, rtol=0, atol=1e-11)
+    # device input stays on the device
+    dloo, dloos, dks = psis.psisloo(torch.from_numpy(ll).cuda())
+    assert dloos.is_cuda and dks.is_cuda
+    np.testing.assert_array_equal(dloos.cpu().numpy(), loos)
+
+
+@pytest.mark.parametrize('n,m', [(2, 3), (5, 2), (257, 33), (4096, 5), (8192, 3), (8193, 2)])
+def test_psislw_columns_match_single_column_path(n, m):
+    """Every column of the batched kernel equals the single-column pipeline (tail set and order are exact in both,
+    so the values agree to summation order); n = 8193 exceeds the shared-memory kernel and takes the column loop."""
+    from viabel_b200 import psis
+    lw = gi.gpd_log_weights(n * m, 0.6, 500 + n).reshape(n, m)
+    lw[:, 0] = np.random.RandomState(n).randn(n) * 0.3              # a light-tailed column
+    out, ks = psis.psislw(lw)
+    for j in range(m):
+        o1, k1 = psis.psislw(np.ascontiguousarray(lw[:, j]))
+        assert (np.isinf(k1) and np.isinf(ks[j])) or abs(k1 - ks[j]) <= 1e-11 * max(1.0, abs(k1))
+        np.testing.assert_allclose(out[:, j], o1, rtol=0, atol=1e-11)
+    oout, oks = _quiet(psis_np.psislw, lw, sort_kind='stable')
+    np.testing.assert_allclose(out, oout, rtol=0, atol=1e-11)
+    loo, loos, ks3 = psis.psisloo(-lw)
+    oloo, oloos, _ = _quiet(psis_np.psisloo, -lw, sort_kind='stable')
+    np.testing.assert_allclose(loos, oloos, rtol=1e-11, atol=1e-11)
+    with pytest.raises(ValueError):
+        psis.psisloo(lw[:, 0])
+    with pytest.raises(ValueError):
+        psis.psisloo(lw[:1])
+
+
 @pytest.mark.parametrize('name', gi.GPD_CASES)
 def test_gpdfit_gpinv_sumlogs(golden, name):
     from viabel_b200 import psis

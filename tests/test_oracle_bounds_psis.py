@@ -142,6 +142,21 @@ def test_psis_edge_cases():
     np.testing.assert_allclose(ks[0], ks[1], rtol=1e-10)
 
 
+@pytest.mark.parametrize('name', gi.LOO_CASES)
+def test_psisloo_matches_reference_outputs(golden, name):
+    """psisloo / 2-D psislw (psis.py:68-109,136-137) against outputs of the real reference (scripts/make_golden.py)."""
+    ll = gi.loo_case(name)
+    keep = ll.copy()
+    loo, loos, ks = _quiet(psis_np.psisloo, ll)
+    assert np.array_equal(ll, keep)                                   # the input is not modified (lw = -log_lik copy)
+    pre = 'loo/%s/' % name
+    assert loo == golden[pre + 'loo'] and np.array_equal(loos, golden[pre + 'loos'])
+    assert np.array_equal(ks, golden[pre + 'ks'])
+    lw2, ks2 = _quiet(psis_np.psislw, -ll)
+    assert lw2.flags.f_contiguous and np.array_equal(ks2, golden[pre + 'ks'])
+    assert np.array_equal(lw2[gi.probe_indices(ll.shape[0])], golden[pre + 'lw_probe'])
+
+
 def test_live_reference_agrees(reference_modules):
     """A/B against the imported reference on fresh random inputs (build container only)."""
     rb, rp = reference_modules
@@ -155,3 +170,6 @@ def test_live_reference_agrees(reference_modules):
         o1, k1 = _quiet(rp.psislw, w)
         o2, k2 = _quiet(psis_np.psislw, w)
         assert np.array_equal(o1, o2) and k1 == k2
+    ll = -gi.gpd_log_weights(1500 * 6, 0.55, 4242).reshape(1500, 6)
+    a, b = _quiet(rp.psisloo, ll.copy()), _quiet(psis_np.psisloo, ll.copy())
+    assert a[0] == b[0] and np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])

@@ -1227,3 +1227,196 @@ extern "C" int vb_psis_normalise(double* d_lw_out, long long n_local, double lse
     VB_LAUNCH_CHECK();
     return VB_OK;
 }
+
+// ------------------------------------------------------------------------------------------ batched columns (N3)
+// psislw on an (n, m) matrix (psis.py:136-137,163: one independent smoothing per column) and the psisloo
+// reduction (psis.py:68-109) for the shapes PSIS-LOO has: a few thousand draws per column, many columns.
+// ONE CTA per column, everything in shared memory: max -> (key, index) pairs -> bitonic sort of the whole column
+// -> exact cutoff / strict tail -> GPD fit (one warp per quadrature point) -> inverse-CDF smoothing -> log-sum-exp
+// -> out = value - lse scattered back by index.  Same comparisons and formulas as the single-column path above
+// (tail set and order are bit-exact; k-hat and the weights differ from it by summation order only).
+namespace vb {
+
+constexpr int kColThreads = 256;
+constexpr int kColMaxN = 8192;                 // 64 KiB of keys + 16 KiB of 16-bit indices: 2 CTAs per SM at the
+                                               // maximum, 4-5 at the usual 4096 draws (the sort is barrier-latency bound)
+constexpr int kColMaxQ = 128;                  // quadrature points: 30 + sqrt(n2) <= 30 + sqrt(0.2 * 8192) = 70
+
+struct ColSmem {
+    double scratch[32];
+    double bs[kColMaxQ], L[kColMaxQ], w[kColMaxQ];
+    double st[8];                              // xcut, exp(xcut), k, sigma, smoothed, lse, b, spare
+    long long cnt[4];                          // n2, first tail position, quadrature points, fit runs
+};
+
+__global__ void __launch_bounds__(kColThreads)
+psis_columns_kernel(const double* __restrict__ lw_cols, double* __restrict__ out_cols, int n, int n_pad, int K1,
+                    double* __restrict__ out_k, double* __restrict__ out_loo_or_null) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    ColSmem& S = *reinterpret_cast<ColSmem*>(smem_raw);
+    unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem_raw + ((sizeof(ColSmem) + 15) & ~(size_t)15));
+    double* x2 = reinterpret_cast<double*>(keys + n_pad);       // [K1]: tail excesses, ascending; later the new values
+    unsigned short* idxs = reinterpret_cast<unsigned short*>(x2 + (K1 > 0 ? K1 : 1));
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = kColThreads / 32;
+    const double* x = lw_cols + (size_t)blockIdx.x * n;
+    double* out = out_cols + (size_t)blockIdx.x * n;
+
+    // max, keys relative to it (psis.py:165-167)
+    double M = -INFINITY;
+    for (int i = tid; i < n; i += kColThreads) M = fmax(M, x[i]);
+    M = block_max(M, S.scratch);
+    for (int i = tid; i < n_pad; i += kColThreads) {
+        keys[i] = (i < n) ? u_to_key(M - x[i]) : ~0ull;
+        idxs[i] = (i < n) ? (unsigned short)i : (unsigned short)0xffff;
+    }
+    __syncthreads();
+    // ascending (key, index) == ascending shifted weight, ties by ascending index
+    for (int k = 2; k <= n_pad; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int t = tid; t < n_pad / 2; t += kColThreads) {
+                const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1)), q = i | j;
+                const unsigned long long ka = keys[i], kb = keys[q];
+                const unsigned short ia = idxs[i], ib = idxs[q];
+                const bool b_less = kb < ka || (kb == ka && ib < ia);
+                if (b_less == ((i & k) == 0)) { keys[i] = kb; keys[q] = ka; idxs[i] = ib; idxs[q] = ia; }
+            }
+            __syncthreads();
+        }
+    }
+    // cutoff and strict tail (psis.py:157,169-176), as tail_bounds_kernel
+    if (tid == 0) {
+        const double u_cut = key_to_u(keys[n - 1 - K1]);
+        const double xcut = fmax(-u_cut, -kNegLogTiny);
+        const double u_eff = -xcut;
+        int lo = 0, hi = n;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (key_to_u(keys[mid]) < u_eff) hi = mid; else lo = mid + 1;
+        }
+        const int n2 = n - lo;
+        S.st[0] = xcut;
+        S.st[1] = exp(xcut);
+        S.cnt[0] = n2;
+        S.cnt[1] = lo;
+        S.cnt[2] = 30 + (long long)sqrt((double)n2);
+        S.cnt[3] = (n2 > 4) ? 1 : 0;
+    }
+    __syncthreads();
+    const int n2 = (int)S.cnt[0], p0 = (int)S.cnt[1], mq = (int)S.cnt[2];
+    const bool fit = S.cnt[3] != 0;
+    const double ec = S.st[1];
+    for (int r = tid; r < n2; r += kColThreads) x2[r] = exp(-key_to_u(keys[p0 + r])) - ec;     // psis.py:184-185
+    __syncthreads();
+    if (fit) {                                                                                  // psis.py:266-323
+        const double x_q = x2[(int)((double)n2 / 4.0 + 0.5) - 1], x_max = x2[n2 - 1];
+        for (int j = warp; j < mq; j += nw) {
+            const double b = gpd_b(j, mq, x_q, x_max);
+            double a = 0.0;
+            for (int r = lane; r < n2; r += 32) a += log1p(-b * x2[r]);
+            a = warp_sum(a);
+            if (lane == 0) {
+                const double ks = a / (double)n2;
+                S.bs[j] = b;
+                S.L[j] = (double)n2 * (log(-(b / ks)) - ks - 1.0);
+            }
+        }
+        __syncthreads();
+        for (int j = warp; j < mq; j += nw) {
+            double a = 0.0;
+            const double Lj = S.L[j];
+            for (int i = lane; i < mq; i += 32) a += exp(S.L[i] - Lj);
+            a = warp_sum(a);
+            if (lane == 0) S.w[j] = 1.0 / a;
+        }
+        __syncthreads();
+        double sw = 0.0, sbw = 0.0;
+        for (int j = tid; j < mq; j += kColThreads) {
+            const double w = S.w[j];
+            if (w >= 10.0 * DBL_EPSILON) { sw += w; sbw += S.bs[j] * w; }
+        }
+        sw = block_sum(sw, S.scratch);
+        sbw = block_sum(sbw, S.scratch);
+        const double b = sbw / sw;
+        double a = 0.0;
+        for (int r = tid; r < n2; r += kColThreads) a += log1p(-b * x2[r]);
+        a = block_sum(a, S.scratch);
+        if (tid == 0) {
+            double k = a / (double)n2;
+            const double sigma = -k / b;
+            k = k * (double)n2 / ((double)n2 + 10.0) + 5.0 / ((double)n2 + 10.0);
+            S.st[2] = k;
+            S.st[3] = sigma;
+            S.st[4] = (k >= 1.0 / 3.0 && !isinf(k)) ? 1.0 : 0.0;
+        }
+    } else if (tid == 0) {
+        S.st[2] = INFINITY; S.st[3] = NAN; S.st[4] = 0.0;                                       // psis.py:177-179
+    }
+    __syncthreads();
+    const bool smoothed = S.st[4] != 0.0;
+    const double kh = S.st[2], sigma = S.st[3];
+    // new tail values (psis.py:190-198); x2 is reused for them
+    __syncthreads();
+    double se = 0.0;
+    for (int r = tid; r < n2; r += kColThreads) {
+        double v;
+        if (smoothed) {
+            v = log(gpinv_inside(((double)r + 0.5) / (double)n2, kh, sigma) + ec);
+            if (v > 0.0) v = 0.0;
+        } else {
+            v = -key_to_u(keys[p0 + r]);
+        }
+        x2[r] = v;
+        se += exp(v);
+    }
+    for (int r = tid; r < p0; r += kColThreads) se += exp(-key_to_u(keys[r]));
+    se = block_sum(se, S.scratch);
+    const double lse = log(se);                                                                  // psis.py:200
+    // write back by index; optional leave-one-out term log sum_i exp(out_i - lw_i) (psis.py:104-107, lw = -log_lik)
+    double lmax = -INFINITY;
+    for (int r = tid; r < n; r += kColThreads) {
+        const int i = (int)idxs[r];
+        const double v = ((r >= p0) ? x2[r - p0] : -key_to_u(keys[r])) - lse;
+        out[i] = v;
+        if (out_loo_or_null) lmax = fmax(lmax, v - x[i]);
+    }
+    if (tid == 0) out_k[blockIdx.x] = kh;
+    if (out_loo_or_null) {
+        lmax = block_max(lmax, S.scratch);
+        double a = 0.0;
+        for (int r = tid; r < n; r += kColThreads) {
+            const int i = (int)idxs[r];
+            const double v = ((r >= p0) ? x2[r - p0] : -key_to_u(keys[r])) - lse;
+            a += exp((v - x[i]) - lmax);
+        }
+        a = block_sum(a, S.scratch);
+        if (tid == 0) out_loo_or_null[blockIdx.x] = log(a) + lmax;                               // psis.py:390-395
+    }
+}
+
+}  // namespace vb
+
+extern "C" long long vb_psis_columns_max_n(void) { return vb::kColMaxN; }
+
+extern "C" int vb_psis_smooth_columns(const double* d_lw_cols, double* d_out_cols, long long n, long long m,
+                                      double reff, double* d_out_k, double* d_out_loo_or_null, void* stream) {
+    using namespace vb;
+    if (!d_lw_cols || !d_out_cols || !d_out_k || m < 1 || !(reff > 0.0)) return VB_ERR_ARG;
+    if (n <= 1) return VB_ERR_ARG;                                    // psis.py:143-144
+    if (n > kColMaxN) return VB_ERR_UNSUPPORTED;
+    if (d_lw_cols == d_out_cols) return VB_ERR_ARG;
+    long long n_pad = 2;
+    while (n_pad < n) n_pad <<= 1;
+    const long long K1 = psis_K1(n, reff);
+    if (K1 + 1 > n) return VB_ERR_UNSUPPORTED;                        // Reff so small that the cutoff leaves the column
+    const size_t smem = ((sizeof(ColSmem) + 15) & ~(size_t)15) + (size_t)n_pad * 8 +
+                        (size_t)(K1 > 0 ? K1 : 1) * sizeof(double) + (size_t)n_pad * 2;
+    static size_t configured = 0;
+    if (smem > configured) {
+        VB_CUDA_TRY(cudaFuncSetAttribute(psis_columns_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    psis_columns_kernel<<<(unsigned)m, kColThreads, smem, (cudaStream_t)stream>>>(
+        d_lw_cols, d_out_cols, (int)n, (int)n_pad, (int)K1, d_out_k, d_out_loo_or_null);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}

@@ -11,7 +11,7 @@ import torch
 from . import _lib
 from ._device import WS, is_host, like_input, ptr, stream_ptr, to_dev
 
-__all__ = ['psislw', 'psislw_detail', 'gpdfitnew', 'gpinv', 'sumlogs']
+__all__ = ['psislw', 'psislw_detail', 'psisloo', 'gpdfitnew', 'gpinv', 'sumlogs']
 
 
 def _smooth_1d(col, Reff, want_tail=False):
@@ -27,6 +27,48 @@ def _smooth_1d(col, Reff, want_tail=False):
     _lib.check(_lib.lib.vb_psis_smooth(ptr(col), ptr(out), n, float(Reff), ptr(diag), ptr(tail), ptr(ws),
                                        ws.numel(), stream_ptr()), 'vb_psis_smooth')
     return out, diag.cpu().numpy(), tail
+
+
+def _smooth_columns(cols, Reff, want_loo=False):
+    """cols: CUDA f64 (m, n) contiguous, one weight set per row -> (smoothed (m, n), k (m,) device, loo (m,) or None).
+    One launch for all columns (``vb_psis_smooth_columns``); columns longer than the kernel holds in shared memory
+    go through the single-column path one by one."""
+    m, n = cols.shape
+    if n <= int(_lib.lib.vb_psis_columns_max_n()):
+        out = torch.empty_like(cols)
+        ks = torch.empty(m, dtype=torch.float64, device=cols.device)
+        loo = torch.empty(m, dtype=torch.float64, device=cols.device) if want_loo else None
+        _lib.check(_lib.lib.vb_psis_smooth_columns(ptr(cols), ptr(out), n, m, float(Reff), ptr(ks), ptr(loo),
+                                                   stream_ptr()), 'vb_psis_smooth_columns')
+        return out, ks, loo
+    outs, ks = [], np.empty(m)
+    for i in range(m):
+        o, diag, _ = _smooth_1d(cols[i], Reff)
+        outs.append(o)
+        ks[i] = diag[0]
+    out = torch.stack(outs, dim=0)
+    loo = torch.logsumexp(out - cols, dim=1) if want_loo else None
+    return out, torch.from_numpy(ks).to(cols.device), loo
+
+
+def psisloo(log_lik, **kwargs):
+    """PSIS leave-one-out log predictive densities (``psis.py:68-109``): ``log_lik`` is (n, m) -- n posterior
+    draws of m log-likelihood terms; returns ``(loo, loos (m,), ks (m,))``.  Keyword arguments go to ``psislw``
+    (``Reff``).  The smoothing of all columns and the leave-one-out sums run in one launch."""
+    if log_lik.ndim != 2:
+        raise ValueError("Argument `log_lik` must be 2 dimensional.")
+    Reff = kwargs.pop('Reff', 1.0)
+    kwargs.pop('overwrite_lw', None)                     # psis.py:100 forces it; the input is never touched here
+    if kwargs:
+        raise TypeError('unexpected keyword arguments: %s' % sorted(kwargs))
+    if log_lik.shape[0] <= 1:
+        raise ValueError("More than one log-weight needed.")
+    cols = (-to_dev(log_lik, _lib.F64)).t().contiguous()            # lw = -log_lik, one column per row
+    _, ks, loos = _smooth_columns(cols, Reff, want_loo=True)
+    loo = loos.sum()
+    if is_host(log_lik):
+        return float(loo.item()), loos.cpu().numpy(), ks.cpu().numpy()
+    return loo, loos, ks
 
 
 def psislw(lw, Reff=1.0, overwrite_lw=False, group=None, out=None):
@@ -63,12 +105,9 @@ def psislw(lw, Reff=1.0, overwrite_lw=False, group=None, out=None):
         kss = diag[0]
     else:
         cols = dev.t().contiguous()                      # (m, n): one contiguous row per weight set
-        outs = []
-        for i in range(m):
-            o, diag, _ = _smooth_1d(cols[i], Reff)
-            outs.append(o)
-            kss[i] = diag[0]
-        out = torch.stack(outs, dim=1)
+        out_cols, ks_dev, _ = _smooth_columns(cols, Reff)
+        kss = ks_dev.cpu().numpy()
+        out = out_cols.t().contiguous()
     if is_host(lw):
         if out_host is not None:
             if lw.ndim != 1 or not isinstance(out_host, np.ndarray) or out_host.dtype != np.float64 \
