@@ -367,6 +367,17 @@ int vb_psis_refine(const void* d_cand, long long count, const double* d_M,
                    const double* d_pivot_x, long long keep, void* d_out_cand,
                    unsigned long long* d_out_count, double* d_out_term,
                    void* d_ws, size_t ws_bytes, void* stream);
+/* Global refinement for world > 1 (the bins depend only on the all-reduced maximum and the common pivot):
+ * vb_psis_refine_hist counts this rank's candidates into d_hist[vb_psis_hist_bins()], the caller all-reduces
+ * (sum) the counters, vb_psis_refine_select keeps the candidates above the ONE threshold that leaves
+ * >= keep_global of them over all ranks; the dropped ones add exp(-u) to *d_out_term. */
+int vb_psis_hist_bins(void);
+int vb_psis_refine_hist(const void* d_cand, long long count, const double* d_M, const double* d_pivot_x,
+                        unsigned int* d_hist, void* d_ws, size_t ws_bytes, void* stream);
+int vb_psis_refine_select(const void* d_cand, long long count, const double* d_M, const double* d_pivot_x,
+                          const unsigned int* d_hist_global, long long keep_global, void* d_out_cand,
+                          unsigned long long* d_out_count, double* d_out_term, void* d_ws, size_t ws_bytes,
+                          void* stream);
 size_t vb_psis_tail_workspace_bytes(long long count, long long K1);
 int vb_psis_tail(const void* d_cands, long long count, long long K1, const double* d_M,
                  const double* d_pivot_x, const double* d_terms, int n_terms,

@@ -76,6 +76,30 @@ class NumpyStages:
         out = torch.from_numpy(np.ascontiguousarray(c).copy()) if len(c) else torch.zeros((1, 2), dtype=torch.int64)
         return out, torch.tensor([len(c)])
 
+    BINS = 8192
+
+    def _bins(self, cand, count, M, pivot):
+        c = cand.numpy()[:count]
+        u = (~c[:, 0].view(np.uint64)).view(np.float64)
+        pu = float(M[0]) - float(pivot[0])
+        scale = self.BINS / pu if (pu > 0.0 and math.isfinite(pu)) else 0.0
+        return c, u, np.minimum((u * scale).astype(np.int64), self.BINS - 1)
+
+    def refine_hist(self, cand, count, M, pivot):
+        _, _, b = self._bins(cand, count, M, pivot)
+        return torch.from_numpy(np.bincount(b, minlength=self.BINS).astype(np.int32))
+
+    def refine_select(self, cand, count, M, pivot, hist_global, keep, terms):
+        c, u, b = self._bins(cand, count, M, pivot)
+        cum = np.cumsum(hist_global.numpy().astype(np.int64))
+        hit = np.nonzero(cum >= keep)[0]
+        bstar = int(hit[0]) if len(hit) else self.BINS - 1
+        sel = b <= bstar
+        terms[1] = float(np.exp(-u[~sel]).sum())
+        c = c[sel]
+        out = torch.from_numpy(np.ascontiguousarray(c).copy()) if len(c) else torch.zeros((1, 2), dtype=torch.int64)
+        return out, torch.tensor([len(c)])
+
     def tail(self, cands, count, K1, M, pivot, terms, want_tail_idx=False):
         c = cands.numpy()[:count]
         keys, idx = c[:, 0].view(np.uint64), c[:, 1]

@@ -165,7 +165,7 @@ def _psis_worker(rank, world, port, n, ret):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize('n', [5000, 300000])
+@pytest.mark.parametrize('n', [5000, 40000, 300000])      # 40000: the global (all-reduced histogram) refinement
 def test_two_rank_gloo_sharded_psis_equals_unsharded(n):
     """The exchange protocol of viabel_b200/psis_dist.py over real gloo collectives (stages restated in
     numpy): both sides of the direct threshold; tail order exact, weights to summation order."""

@@ -78,6 +78,9 @@ SIGNATURES = {
     'vb_psis_prepare': (_i, [_p, _ll, _p, _p, _p, _p, _p]),
     'vb_psis_refine_workspace_bytes': (_sz, []),
     'vb_psis_refine': (_i, [_p, _ll, _p, _p, _ll, _p, _p, _p, _p, _sz, _p]),
+    'vb_psis_hist_bins': (_i, []),
+    'vb_psis_refine_hist': (_i, [_p, _ll, _p, _p, _p, _p, _sz, _p]),
+    'vb_psis_refine_select': (_i, [_p, _ll, _p, _p, _p, _ll, _p, _p, _p, _p, _sz, _p]),
     'vb_psis_tail_workspace_bytes': (_sz, [_ll, _ll]),
     'vb_psis_tail': (_i, [_p, _ll, _ll, _p, _p, _p, _i, _p, _p, _p, _sz, _p]),
     'vb_psis_write': (_i, [_p, _p, _ll, _ll, _p, _ll, _ll, _p, _p]),

@@ -916,6 +916,49 @@ extern "C" int vb_psis_refine(const void* d_cand, long long count, const double*
     return VB_OK;
 }
 
+// ---- S4c (sharded callers, world > 1): GLOBAL refinement.  The histogram bins are the same on every rank (they
+// depend on the all-reduced maximum and the common pivot only), so the ranks all-reduce the 8192 counters between
+// these two calls and keep what lies above ONE global threshold: the gathered candidate set is ~keep in total
+// instead of ~keep per rank, and the replicated sort does not grow with the number of ranks.
+extern "C" int vb_psis_hist_bins(void) { return kHistBins; }
+extern "C" int vb_psis_refine_hist(const void* d_cand, long long count, const double* d_M, const double* d_pivot_x,
+                                   unsigned int* d_hist, void* d_ws, size_t ws_bytes, void* stream) {
+    if (!d_cand || !d_M || !d_pivot_x || !d_hist || !d_ws || count < 0) return VB_ERR_ARG;
+    if (ws_bytes < vb_psis_refine_workspace_bytes()) return VB_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    const RefineWs r = refine_ws((char*)d_ws);
+    pivot_u_kernel<<<1, 1, 0, st>>>(d_M, d_pivot_x, r.pivot_u);
+    VB_LAUNCH_CHECK();
+    VB_CUDA_TRY(cudaMemsetAsync(d_hist, 0, (size_t)kHistBins * 4, st));
+    if (count > 0) {
+        hist_kernel<<<grid_for(count, 512 * 8, kNumSMs), 512, 0, st>>>((const Cand*)d_cand, count, r.pivot_u, d_hist);
+        VB_LAUNCH_CHECK();
+    }
+    return VB_OK;
+}
+extern "C" int vb_psis_refine_select(const void* d_cand, long long count, const double* d_M, const double* d_pivot_x,
+                                     const unsigned int* d_hist_global, long long keep_global, void* d_out_cand,
+                                     unsigned long long* d_out_count, double* d_out_term, void* d_ws, size_t ws_bytes,
+                                     void* stream) {
+    if (!d_cand || !d_M || !d_pivot_x || !d_hist_global || !d_out_cand || !d_out_count || !d_out_term || !d_ws ||
+        count < 0 || keep_global < 1)
+        return VB_ERR_ARG;
+    if (ws_bytes < vb_psis_refine_workspace_bytes()) return VB_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    const RefineWs r = refine_ws((char*)d_ws);
+    pivot_u_kernel<<<1, 1, 0, st>>>(d_M, d_pivot_x, r.pivot_u);
+    VB_LAUNCH_CHECK();
+    VB_CUDA_TRY(cudaMemsetAsync(d_out_count, 0, 8, st));
+    hist_scan_kernel<<<1, 1024, 0, st>>>(d_hist_global, keep_global, r.counts2);
+    VB_LAUNCH_CHECK();
+    compact2_kernel<<<kSmallGrid, 256, 0, st>>>((const Cand*)d_cand, count, r.pivot_u, r.counts2, (Cand*)d_out_cand,
+                                                d_out_count, r.blk);
+    VB_LAUNCH_CHECK();
+    sum_blocks_kernel<<<1, 256, 0, st>>>(r.blk, kSmallGrid, d_out_term);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+
 // ---- S5: replicated tail work on the (gathered) re-keyed candidates
 namespace vb {
 struct TailLayout {

@@ -7,7 +7,7 @@ smoothed, normalised weights of its own slice.
 
 Exchange per call (all small; nothing bulk crosses NVLink):
   all_gather   shard sizes (1 int64), strided samples (4096 x 16 B per rank)
-  all_reduce   candidate counts (sum), local maxima (max)
+  all_gather   candidate counts;  all_reduce  local maxima (max), refinement histogram (sum, 8192 x int32)
   all_gather   refined candidate counts, then <= ~(K+1) (key, index) pairs per rank (K = 94 869 at
                n = 1e9: 1.5 MB per rank) and two body-sum terms per rank
 The device work is the staged C ABI of ``include/viabel_b200.h`` (``vb_psis_sample`` ... ``vb_psis_write``);
@@ -83,6 +83,24 @@ class CudaStages:
         _lib.check(_lib.lib.vb_psis_refine(self._p(cand), count, self._p(M), self._p(pivot), keep, self._p(out),
                                            self._p(cnt), self._p(terms) + 8, self._p(ws), ws.numel(), self._stream()),
                    'vb_psis_refine')
+        return out, cnt
+
+    def refine_hist(self, cand, count, M, pivot):
+        """This rank's histogram of candidate keys (int32 [bins]); summed over ranks it selects ONE threshold."""
+        hist = self.empty((int(_lib.lib.vb_psis_hist_bins()),), torch.int32)
+        ws = self.ws.get('refine', _lib.lib.vb_psis_refine_workspace_bytes())
+        _lib.check(_lib.lib.vb_psis_refine_hist(self._p(cand), count, self._p(M), self._p(pivot), self._p(hist),
+                                                self._p(ws), ws.numel(), self._stream()), 'vb_psis_refine_hist')
+        return hist
+
+    def refine_select(self, cand, count, M, pivot, hist_global, keep, terms):
+        out = self.empty((max(count, 1), 2), torch.int64)
+        cnt = self.empty((1,), torch.int64)
+        ws = self.ws.get('refine', _lib.lib.vb_psis_refine_workspace_bytes())
+        _lib.check(_lib.lib.vb_psis_refine_select(self._p(cand), count, self._p(M), self._p(pivot),
+                                                  self._p(hist_global), keep, self._p(out), self._p(cnt),
+                                                  self._p(terms) + 8, self._p(ws), ws.numel(), self._stream()),
+                   'vb_psis_refine_select')
         return out, cnt
 
     def tail(self, cands, count, K1, M, pivot, terms, want_tail_idx=False):
@@ -163,10 +181,12 @@ def psislw_sharded(lw_local, Reff=1.0, group=None, stages=None, want_detail=Fals
         if not direct:
             st.pivot(sample_all.clone(), world * SAMPLE, frac, pivot)    # the stage may sort / pad its input
         cand, count_t, body_max = st.filter(lw_local, index0, pivot, cap)
-        count = int(count_t.item())
-        tot = comm.all_reduce_sum(torch.tensor([count, 1 if count > cap else 0], dtype=torch.int64, device=dev))
-        total, overflow = (int(v) for v in tot.cpu().tolist())
-        if overflow:
+        # one collective + one host read: every rank's candidate count (its own among them)
+        pair = torch.cat([count_t.view(1).to(torch.int64), torch.tensor([cap], dtype=torch.int64, device=dev)])
+        gathered = comm.all_gather(pair).cpu().view(-1, 2).tolist()
+        all_counts = [int(c) for c, _ in gathered]
+        count, total = all_counts[rank], sum(all_counts)
+        if any(int(c) > int(k) for c, k in gathered):
             raise _lib.ViabelB200Error('psislw: more candidates than the buffer holds (heavy ties at the top)')
         if total >= K1 + 1:
             break
@@ -177,9 +197,15 @@ def psislw_sharded(lw_local, Reff=1.0, group=None, stages=None, want_detail=Fals
     comm.all_reduce_max(M)
     terms = st.empty((2,), torch.float64)
     st.prepare(cand, count, M, pivot, body_max, terms)
-    cand2, count2_t = st.refine(cand, count, M, pivot, K1 + 1, terms)
-    count2 = int(count2_t.item())
-    counts = [int(v) for v in comm.all_gather(torch.tensor([count2], dtype=torch.int64, device=dev)).cpu().view(-1).tolist()]
+    if world > 1 and total > 2 * (K1 + 1) and total > 8192:
+        # global refinement: ONE threshold for all ranks from the summed histogram (32 KB all-reduce), so the
+        # gathered candidate set is ~K+1 in total and the replicated sort does not grow with the world size
+        hist = comm.all_reduce_sum(st.refine_hist(cand, count, M, pivot))
+        cand2, count2_t = st.refine_select(cand, count, M, pivot, hist, K1 + 1, terms)
+    else:
+        cand2, count2_t = st.refine(cand, count, M, pivot, K1 + 1, terms)
+    counts = [int(v) for v in comm.all_gather(count2_t.view(1).to(torch.int64)).cpu().view(-1).tolist()]
+    count2 = counts[rank]
     maxc = max(max(counts), 1)
     send = st.empty((maxc, 2), torch.int64)
     send[:count2] = cand2[:count2]
