@@ -224,3 +224,23 @@ def test_torch_custom_ops_match_python_surface():
     # 3xTF32 with fp32 accumulation in TMEM: the tensor core's accumulate truncates, so the relative Frobenius error
     # grows ~7e-9 per unit of K (measured 1.4e-6 at K=200, 3.6e-6 at K=512); stated tolerance 5e-6 at K=200
     assert ((c.double() - ref).norm() / ref.norm()).item() < 5e-6
+    # batched columns + leave-one-out sums, and the device-resident AdaGrad loop
+    ll = torch.from_numpy(-np.log(rs.rand(700, 6))).cuda()
+    cols = (-ll).t().contiguous()
+    sm, ks, loos = torch.ops.viabel_b200.psis_smooth_columns(cols, 1.0, True)
+    loo2, loos2, ks2 = psis.psisloo(ll)
+    assert torch.equal(loos, loos2) and torch.equal(ks, ks2)
+    fam2 = vb.mean_field_gaussian_variational_family(2)
+    funnel = models.Funnel()
+    init = np.array([0., -1., 1., 1.])
+    n_iters = 60
+    want = vb.adagrad_optimize(n_iters, vb.black_box_klvi(fam2, funnel, 500, group=False), init, learning_rate=.02)
+    rates = torch.full((n_iters,), 0.02, dtype=torch.float64, device='cuda')
+    seeds = torch.zeros(n_iters, dtype=torch.int64, device='cuda')
+    offsets = torch.arange(n_iters, dtype=torch.int32, device='cuda')
+    last, kept, vals = torch.ops.viabel_b200.mf_adagrad(_lib.FAMILY_MF_GAUSS, 0.0, funnel.handle.value, _lib.OBJ_KLVI,
+                                                        1.0, torch.from_numpy(init).cuda(), 500, rates, seeds, offsets,
+                                                        10, 0.1)
+    np.testing.assert_array_equal(kept.cpu().numpy(), want[1])
+    np.testing.assert_array_equal(vals.cpu().numpy(), want[2])
+    np.testing.assert_array_equal(last.cpu().numpy(), want[1][-1])

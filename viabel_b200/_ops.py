@@ -20,6 +20,9 @@ _lib_def.define('mf_finalize(int family, int objective, float alpha, Tensor var_
 _lib_def.define('model_logp_grad(int model, Tensor x, bool want_grad) -> (Tensor, Tensor)')
 _lib_def.define('bounds_divergence(Tensor lw, float alpha) -> Tensor')
 _lib_def.define('psis_smooth(Tensor lw, float reff) -> (Tensor, Tensor)')
+_lib_def.define('psis_smooth_columns(Tensor lw_cols, float reff, bool want_loo) -> (Tensor, Tensor, Tensor)')
+_lib_def.define('mf_adagrad(int family, float df, int model, int objective, float alpha, Tensor init_param, int n, '
+                'Tensor rates, Tensor seeds, Tensor offsets, int window, float epsilon) -> (Tensor, Tensor, Tensor)')
 _lib_def.define('logsumexp(Tensor x) -> Tensor')
 _lib_def.define('gemm_tf32x3(Tensor a, Tensor b) -> Tensor')
 
@@ -82,6 +85,43 @@ def _psis_smooth(lw, reff):
     return out, diag
 
 
+def _psis_smooth_columns(lw_cols, reff, want_loo):
+    """(smoothed (m, n), k-hat (m,), loo (m,) or empty): one CTA per row of lw_cols (vb_psis_smooth_columns)."""
+    m, n = lw_cols.shape
+    out = torch.empty_like(lw_cols)
+    ks = torch.empty(m, dtype=torch.float64, device=lw_cols.device)
+    loo = torch.empty(m if want_loo else 0, dtype=torch.float64, device=lw_cols.device)
+    _lib.check(_lib.lib.vb_psis_smooth_columns(ptr(lw_cols), ptr(out), n, m, reff, ptr(ks), ptr(loo) if want_loo else 0,
+                                               stream_ptr()), 'vb_psis_smooth_columns')
+    return out, ks, loo
+
+
+def _mf_adagrad(family, df, model, objective, alpha, init_param, n, rates, seeds, offsets, window, epsilon):
+    """Device-resident AdaGrad (vb_mf_adagrad_*): (final iterate (2d,), kept iterates (n_iters - 3 n_iters // 4, 2d),
+    value history (n_iters,)).  rates float64, seeds int64, offsets int32, all (n_iters,) on the device."""
+    import ctypes
+    P, n_iters = init_param.numel(), rates.numel()
+    d = P // 2
+    dev = init_param.device
+    param = init_param.to(torch.float64).clone()
+    values = torch.zeros(n_iters, dtype=torch.float64, device=dev)
+    kept = torch.zeros((n_iters - 3 * n_iters // 4, P), dtype=torch.float64, device=dev)
+    state = torch.zeros(_lib.lib.vb_mf_adagrad_state_bytes(d, window), dtype=torch.uint8, device=dev)
+    ws = torch.zeros(_lib.lib.vb_mf_step_workspace_bytes(d), dtype=torch.uint8, device=dev)
+    plan = ctypes.c_void_p()
+    _lib.check(_lib.lib.vb_mf_adagrad_create(family, df, model, objective, alpha, _lib.F64, ptr(param), n, 0, n_iters,
+                                             window, epsilon, ptr(rates), ptr(seeds), ptr(offsets), ptr(values),
+                                             ptr(kept), ptr(state), state.numel(), ptr(ws), ws.numel(),
+                                             50 if n_iters >= 100 else 0, 1, stream_ptr(), ctypes.byref(plan)),
+               'vb_mf_adagrad_create')
+    try:
+        _lib.check(_lib.lib.vb_mf_adagrad_run(plan, n_iters, stream_ptr()), 'vb_mf_adagrad_run')
+        torch.cuda.current_stream().synchronize()        # the plan owns graph / state until the work has drained
+    finally:
+        _lib.lib.vb_mf_adagrad_destroy(plan)
+    return param, kept, values
+
+
 def _logsumexp(x):
     out = torch.empty(1, dtype=torch.float64, device=x.device)
     ws = _WS.get('lse', _lib.lib.vb_logsumexp_workspace_bytes(x.numel()))
@@ -102,7 +142,9 @@ def _gemm_tf32x3(a, b):
 
 for _name, _fn in (('mf_step', _mf_step), ('mf_finalize', _mf_finalize), ('model_logp_grad', _model_logp_grad),
                    ('bounds_divergence', _bounds_divergence), ('psis_smooth', _psis_smooth),
+                   ('psis_smooth_columns', _psis_smooth_columns), ('mf_adagrad', _mf_adagrad),
                    ('logsumexp', _logsumexp), ('gemm_tf32x3', _gemm_tf32x3)):
     _lib_def.impl(_name, _fn, 'CUDA')
 
-OPS = ('mf_step', 'mf_finalize', 'model_logp_grad', 'bounds_divergence', 'psis_smooth', 'logsumexp', 'gemm_tf32x3')
+OPS = ('mf_step', 'mf_finalize', 'model_logp_grad', 'bounds_divergence', 'psis_smooth', 'psis_smooth_columns',
+       'mf_adagrad', 'logsumexp', 'gemm_tf32x3')
