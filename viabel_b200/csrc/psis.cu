@@ -458,6 +458,105 @@ compact2_kernel(const Cand* __restrict__ cand, long long count, const double* __
     if (threadIdx.x == 0) block_body[blockIdx.x] = body;
 }
 
+// ------------------------------------------------------------------------------------------ counting sort by bin
+// The refinement bins are monotone in u, so the kept candidates can be ordered bin by bin: an exclusive scan of
+// the counters gives every bin its segment (largest u first == ascending key), a scatter fills the segments, and
+// one warp per bin ranks its few elements by (key, index).  Replaces the 17-stage bitonic network over the padded
+// candidate array (150 us at 65 536 entries, barrier-latency bound) when no bin is large; heavy ties or a
+// degenerate pivot (everything in one bin) fall back to the bitonic sort.
+constexpr int kBinSortMax = 512;               // largest bin the per-warp ranking takes
+// offsets[b] = number of kept candidates in bins < b (b = 0 .. kHistBins); meta = [largest bin, total]
+__global__ void __launch_bounds__(1024)
+bin_scan_kernel(const unsigned int* __restrict__ hist, const long long* __restrict__ bstar_ptr,
+                unsigned int* __restrict__ offsets, long long* __restrict__ meta) {
+    __shared__ unsigned int warp_tot[32];
+    __shared__ unsigned int warp_max[32];
+    constexpr int per = kHistBins / 1024;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const long long bstar = bstar_ptr ? *bstar_ptr : (long long)kHistBins - 1;
+    unsigned int c[per];
+    unsigned int mine = 0, mx = 0;
+#pragma unroll
+    for (int b = 0; b < per; ++b) {
+        const int bin = tid * per + b;
+        c[b] = (bin <= bstar) ? hist[bin] : 0u;
+        mine += c[b];
+        mx = max(mx, c[b]);
+    }
+    unsigned int incl = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const unsigned int v = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += v;
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+    if (lane == 31) warp_tot[warp] = incl;
+    if (lane == 0) warp_max[warp] = mx;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned int w = warp_tot[lane], m = warp_max[lane];
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned int v = __shfl_up_sync(0xffffffffu, w, d);
+            if (lane >= d) w += v;
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, d));
+        warp_tot[lane] = w;
+        if (lane == 0) { meta[0] = (long long)m; }
+        if (lane == 31) { meta[1] = (long long)w; offsets[kHistBins] = w; }
+    }
+    __syncthreads();
+    unsigned int run = incl - mine + ((warp == 0) ? 0u : warp_tot[warp - 1]);
+#pragma unroll
+    for (int b = 0; b < per; ++b) {
+        offsets[tid * per + b] = run;
+        run += c[b];
+    }
+}
+__device__ __forceinline__ int cand_bin(const Cand& c, double scale) {
+    long long b = (long long)(key_to_u(c.key) * scale);         // same expression as hist_kernel
+    return (int)(b > kHistBins - 1 ? kHistBins - 1 : b);
+}
+// dst[total - offsets[b + 1] + slot]: bins in descending order, arbitrary order inside a bin
+__global__ void __launch_bounds__(256)
+bin_scatter_kernel(const Cand* __restrict__ src, const long long* __restrict__ meta, const double* __restrict__ pivot_ptr,
+                   const unsigned int* __restrict__ offsets, unsigned int* __restrict__ cursor, Cand* __restrict__ dst) {
+    const double pivot = *pivot_ptr;
+    const double scale = (pivot > 0.0 && isfinite(pivot)) ? (double)kHistBins / pivot : 0.0;
+    const long long total = meta[1];
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const Cand c = src[i];
+        const int b = cand_bin(c, scale);
+        const unsigned int slot = atomicAdd(&cursor[b], 1u);
+        dst[total - (long long)offsets[b + 1] + slot] = c;
+    }
+}
+// one warp per bin: rank of every element among the bin's elements by (key, index)
+__global__ void __launch_bounds__(256)
+bin_rank_kernel(const Cand* __restrict__ src, const long long* __restrict__ meta, const long long* __restrict__ bstar_ptr,
+                const unsigned int* __restrict__ offsets, Cand* __restrict__ dst) {
+    const long long total = meta[1];
+    const int n_bins = (int)((bstar_ptr ? *bstar_ptr : (long long)kHistBins - 1) + 1);
+    const int lane = threadIdx.x & 31;
+    const int warps = (gridDim.x * blockDim.x) >> 5;
+    for (int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < n_bins; b += warps) {
+        const unsigned int lo = offsets[b], hi = offsets[b + 1];
+        const int c = (int)(hi - lo);
+        if (c == 0) continue;
+        const long long base = total - (long long)hi;
+        const Cand* seg = src + base;
+        for (int i = lane; i < c; i += 32) {
+            const Cand e = seg[i];
+            int rank = 0;
+            for (int j = 0; j < c; ++j) rank += cand_less(seg[j], e) ? 1 : 0;
+            dst[base + rank] = e;
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------ tail bookkeeping
 // state[] (doubles): [0] xcutoff  [1] exp(xcutoff)  [2] k  [3] sigma  [4] smoothed  [5] lse  [6] b (GPD)  [7] spare
 // counts[] (long long): [0] n2  [1] first tail position p in the sorted candidates  [2] m (quadrature points)
@@ -964,7 +1063,7 @@ namespace vb {
 struct TailLayout {
     long long cap_sort;
     size_t off_state, off_counts, off_cnt2, off_term, off_refine, off_sort, off_x2, off_tailnew, off_bs, off_L, off_w,
-        off_blk3, off_blk4, off_blk5, total;
+        off_blk3, off_blk4, off_blk5, off_sort2, off_binoff, off_cursor, off_meta, total;
 };
 static TailLayout tail_layout(long long count, long long K1) {
     TailLayout L;
@@ -986,6 +1085,10 @@ static TailLayout tail_layout(long long count, long long K1) {
     L.off_blk3 = take((size_t)kSmallGrid * 8);
     L.off_blk4 = take((size_t)kSmallGrid * 8);
     L.off_blk5 = take((size_t)kSmallGrid * 8);
+    L.off_sort2 = take((size_t)L.cap_sort * sizeof(Cand));       // scatter target of the counting sort
+    L.off_binoff = take((size_t)(kHistBins + 1) * 4);
+    L.off_cursor = take((size_t)kHistBins * 4);
+    L.off_meta = take(16);
     L.total = o;
     return L;
 }
@@ -1020,26 +1123,61 @@ extern "C" int vb_psis_tail(const void* d_cands, long long count, long long K1, 
     double* blk4 = (double*)(ws + L.off_blk4);
     double* blk5 = (double*)(ws + L.off_blk5);
 
+    Cand* sort2 = (Cand*)(ws + L.off_sort2);
+    unsigned int* binoff = (unsigned int*)(ws + L.off_binoff);
+    unsigned int* cursor = (unsigned int*)(ws + L.off_cursor);
+    long long* meta = (long long*)(ws + L.off_meta);
+    const RefineWs rw = refine_ws(ws + L.off_refine);
+    static const bool no_binsort = getenv("VB_PSIS_BITONIC") != nullptr && atoi(getenv("VB_PSIS_BITONIC")) != 0;
+
     long long C2 = count;
+    long long h[3] = {0, 0, 0};          // kept candidates, largest bin, total over the kept bins
+    bool binned = false;
     if (count > kDirectSortMax) {
         int rc = refine_to((const Cand*)d_cands, count, d_M, d_pivot_x, K1 + 1, sort_buf, cnt2, term_ref,
                            ws + L.off_refine, st);
         if (rc != VB_OK) return rc;
-        unsigned long long h = 0;
-        VB_CUDA_TRY(cudaMemcpyAsync(&h, cnt2, 8, cudaMemcpyDeviceToHost, st));
+        bin_scan_kernel<<<1, 1024, 0, st>>>(rw.hist, rw.counts2, binoff, meta);      // kept == bins <= b*
+        VB_LAUNCH_CHECK();
+        VB_CUDA_TRY(cudaMemcpyAsync(&h[0], cnt2, 8, cudaMemcpyDeviceToHost, st));
+        VB_CUDA_TRY(cudaMemcpyAsync(&h[1], meta, 16, cudaMemcpyDeviceToHost, st));
         VB_CUDA_TRY(cudaStreamSynchronize(st));
-        C2 = (long long)h;
+        C2 = h[0];
         if (C2 < K1 + 1 || C2 > count) return VB_ERR_UNSUPPORTED;
+        binned = true;
     } else {
         VB_CUDA_TRY(cudaMemcpyAsync(sort_buf, d_cands, (size_t)count * sizeof(Cand), cudaMemcpyDeviceToDevice, st));
         set_double_kernel<<<1, 1, 0, st>>>(term_ref, 0.0);
         VB_LAUNCH_CHECK();
+        if (count > 8192 && !no_binsort) {
+            // (sharded callers hand over an already refined set): bin the candidates as the refinement would
+            pivot_u_kernel<<<1, 1, 0, st>>>(d_M, d_pivot_x, rw.pivot_u);
+            VB_LAUNCH_CHECK();
+            VB_CUDA_TRY(cudaMemsetAsync(rw.hist, 0, (size_t)kHistBins * 4, st));
+            hist_kernel<<<grid_for(count, 512 * 8, kNumSMs), 512, 0, st>>>(sort_buf, count, rw.pivot_u, rw.hist);
+            VB_LAUNCH_CHECK();
+            bin_scan_kernel<<<1, 1024, 0, st>>>(rw.hist, nullptr, binoff, meta);
+            VB_LAUNCH_CHECK();
+            VB_CUDA_TRY(cudaMemcpyAsync(&h[1], meta, 16, cudaMemcpyDeviceToHost, st));
+            VB_CUDA_TRY(cudaStreamSynchronize(st));
+            binned = true;
+        }
     }
-    const long long n_pad = pad_pow2(C2);
-    pad_cands_kernel<<<grid_for(n_pad - C2 + 1, 256, kNumSMs * 4), 256, 0, st>>>(sort_buf, C2, n_pad);
-    VB_LAUNCH_CHECK();
-    int rc = bitonic_sort(sort_buf, n_pad, st);
-    if (rc != VB_OK) return rc;
+    int rc = VB_OK;
+    if (binned && !no_binsort && C2 > 8192 && h[1] <= kBinSortMax && h[2] == C2) {
+        const long long* bstar = (count > kDirectSortMax) ? rw.counts2 : nullptr;
+        VB_CUDA_TRY(cudaMemsetAsync(cursor, 0, (size_t)kHistBins * 4, st));
+        bin_scatter_kernel<<<grid_for(C2, 256, kNumSMs * 4), 256, 0, st>>>(sort_buf, meta, rw.pivot_u, binoff, cursor, sort2);
+        VB_LAUNCH_CHECK();
+        bin_rank_kernel<<<kNumSMs * 4, 256, 0, st>>>(sort2, meta, bstar, binoff, sort_buf);
+        VB_LAUNCH_CHECK();
+    } else {
+        const long long n_pad = pad_pow2(C2);
+        pad_cands_kernel<<<grid_for(n_pad - C2 + 1, 256, kNumSMs * 4), 256, 0, st>>>(sort_buf, C2, n_pad);
+        VB_LAUNCH_CHECK();
+        rc = bitonic_sort(sort_buf, n_pad, st);
+        if (rc != VB_OK) return rc;
+    }
 
     tail_bounds_kernel<<<1, 1, 0, st>>>(sort_buf, C2, K1, state, counts);
     VB_LAUNCH_CHECK();
