@@ -4,10 +4,14 @@ Tolerances: bounds rtol 1e-10; PSIS tail index set and sort order bit-exact, cut
 k-hat rtol 1e-9, smoothed log weights atol 1e-9 (summation order is the only difference)."""
 import warnings
 
+import os
+
 import numpy as np
 import pytest
 
 pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 import golden_inputs as gi                      # noqa: E402
 from oracle import bounds_np, psis_np           # noqa: E402
@@ -167,6 +171,38 @@ def test_psislw_ties_use_ascending_index():
     assert np.array_equal(det['tail_idx_sorted'], odet['tailinds'][odet['tail_order']])
     np.testing.assert_allclose(k, ok, rtol=1e-11)
     np.testing.assert_allclose(out, oout, rtol=0, atol=1e-11)
+
+
+@pytest.mark.parametrize('decimals,forced', [(3, False), (1, False), (3, True)])
+def test_psislw_ties_in_the_counting_sort_path(decimals, forced, monkeypatch):
+    """n above the direct-sort threshold: the candidates are ordered by the counting sort over the refinement bins
+    (ties share a bin and are ranked by index); coarse rounding makes bins larger than the per-warp ranking takes and
+    must fall back to the bitonic network; VB_PSIS_BITONIC=1 forces the fallback.  All three agree with the
+    stable-sort oracle exactly in tail membership and order."""
+    import subprocess
+    import sys
+    lw = np.round(gi.gpd_log_weights(400000, 0.5, 78), decimals)
+    oout, ok, odet = _quiet(psis_np.psislw_detail, lw, sort_kind='stable')
+    if forced:                                   # the switch is read once per process: run in a child
+        code = ("import numpy as np, sys; sys.path.insert(0, %r); sys.path.insert(0, %r); import golden_inputs as gi;"
+                "from viabel_b200 import psis; lw = np.round(gi.gpd_log_weights(400000, 0.5, 78), %d);"
+                "out, k, det = psis.psislw_detail(lw); np.save(sys.argv[1], det['tail_idx_sorted']); print(repr(k))"
+                % (ROOT, os.path.join(ROOT, 'tests'), decimals))
+        import tempfile
+        with tempfile.TemporaryDirectory() as td:
+            path = os.path.join(td, 't.npy')
+            env = dict(os.environ, VB_PSIS_BITONIC='1')
+            res = subprocess.run([sys.executable, '-c', code, path], env=env, capture_output=True, text=True, check=True)
+            tail = np.load(path)
+        k = float(res.stdout.strip().splitlines()[-1].replace('np.float64(', '').rstrip(')'))
+    else:
+        from viabel_b200 import psis
+        out, k, det = psis.psislw_detail(lw)
+        tail = det['tail_idx_sorted']
+        assert det['xcutoff'] == odet['xcutoff'] and det['n2'] == odet['n2']
+        np.testing.assert_allclose(out, oout, rtol=0, atol=1e-11)
+    assert np.array_equal(tail, odet['tailinds'][odet['tail_order']])
+    np.testing.assert_allclose(k, ok, rtol=1e-11)
 
 
 def test_psislw_two_dimensional_and_device_input():
