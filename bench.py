@@ -104,8 +104,8 @@ def main():
     args = parse()
     # the image exports NCCL_DEBUG=VERSION, which makes NCCL print its banner on stdout next to the ONE JSON line;
     # set before torch / NCCL are loaded
-    if os.environ.get('NCCL_DEBUG', '').upper() in ('', 'VERSION'):
-        os.environ['NCCL_DEBUG'] = 'WARN'
+    if os.environ.get('NCCL_DEBUG', '').upper() == 'VERSION':      # (WARN prints the banner too)
+        os.environ.pop('NCCL_DEBUG', None)
     import bench_workloads as W
     wl_cls = W.WORKLOADS[args.workload]
     steps = args.steps if args.steps is not None else wl_cls.default_steps

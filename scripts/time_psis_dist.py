@@ -16,8 +16,8 @@ sys.path.insert(0, ROOT)
 def main():
     rank, world = int(os.environ['RANK']), int(os.environ['WORLD_SIZE'])
     torch.cuda.set_device(int(os.environ['LOCAL_RANK']))
-    if os.environ.get('NCCL_DEBUG', '').upper() in ('', 'VERSION'):
-        os.environ['NCCL_DEBUG'] = 'WARN'
+    if os.environ.get('NCCL_DEBUG', '').upper() == 'VERSION':      # (WARN prints the banner too)
+        os.environ.pop('NCCL_DEBUG', None)
     dist.init_process_group('nccl', device_id=torch.device('cuda', int(os.environ['LOCAL_RANK'])))
     import viabel_b200
     from viabel_b200 import psis_dist, psis

@@ -160,7 +160,11 @@ def _psis_worker(rank, world, port, n, ret):
         start, count = vb._shard(n, rank, world)
         mine = torch.from_numpy(lw[start:start + count].copy())
         out, k, det = psis_dist.psislw_sharded(mine, stages=NumpyStages(), want_detail=True)
-        ret[rank] = (out.numpy(), k, det['tail_idx_sorted'], det['n2'])
+        # same group, different shard sizes: the cached sizes must be detected as stale and gathered again
+        cut = n // 3
+        mine2 = torch.from_numpy((lw[:cut] if rank == 0 else lw[cut:]).copy())
+        out2, k2, det2 = psis_dist.psislw_sharded(mine2, stages=NumpyStages(), want_detail=True)
+        ret[rank] = (out.numpy(), k, det['tail_idx_sorted'], det['n2'], out2.numpy(), k2, det2['tail_idx_sorted'])
     finally:
         dist.destroy_process_group()
 
@@ -183,7 +187,11 @@ def test_two_rank_gloo_sharded_psis_equals_unsharded(n):
         warnings.simplefilter('ignore')
         oout, ok, odet = psis_np.psislw_detail(lw, sort_kind='stable')
     out = np.concatenate([ret[0][0], ret[1][0]])
+    out2 = np.concatenate([ret[0][4], ret[1][4]])
+    np.testing.assert_allclose(out2, oout, rtol=1e-10, atol=1e-10)
     for r in range(world):
+        np.testing.assert_array_equal(ret[r][6], odet['tailinds'][odet['tail_order']])
+        np.testing.assert_allclose(ret[r][5], ok, rtol=1e-10)
         assert ret[r][3] == odet['n2']
         np.testing.assert_array_equal(ret[r][2], odet['tailinds'][odet['tail_order']])
         np.testing.assert_allclose(ret[r][1], ok, rtol=1e-10)

@@ -6,10 +6,11 @@ result equals the unsharded ``psislw`` of the concatenation: the tail index set,
 smoothed, normalised weights of its own slice.
 
 Exchange per call (all small; nothing bulk crosses NVLink):
-  all_gather   shard sizes (1 int64), strided samples (4096 x 16 B per rank)
-  all_gather   candidate counts;  all_reduce  local maxima (max), refinement histogram (sum, 8192 x int32)
-  all_gather   refined candidate counts, then <= ~(K+1) (key, index) pairs per rank (K = 94 869 at
-               n = 1e9: 1.5 MB per rank) and two body-sum terms per rank
+  all_gather   shard sizes (1 int64, first call only: cached and re-validated), strided samples (4096 x 16 B per rank)
+  all_gather   (candidate count, buffer capacity, shard size) per rank;  all_reduce  local maxima (max)
+  all_gather   refinement histograms (8192 x int32 per rank): one global threshold, and every rank's kept count
+  all_gather   the kept (key, index) pairs (~K+1 in TOTAL; K = 94 869 at n = 1e9: ~1.5 MB) with the two body-sum
+               terms of each rank in the last row
 The device work is the staged C ABI of ``include/viabel_b200.h`` (``vb_psis_sample`` ... ``vb_psis_write``);
 ``stages`` lets the CPU tests drive the same protocol over gloo with a numpy restatement of the stages.
 """
@@ -128,6 +129,7 @@ class DistComm:
         import torch.distributed as dist
         self.dist, self.group = dist, group
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.cache_key = ('dist', id(group) if group is not None else 0, self.world)
 
     def all_gather(self, t):
         """(world, *t.shape): row r = rank r's tensor (equal shapes on every rank)."""
@@ -156,7 +158,31 @@ def psislw_sharded(lw_local, Reff=1.0, group=None, stages=None, want_detail=Fals
     world, rank = comm.world, comm.rank
     n_local = int(lw_local.numel())
     dev = lw_local.device
-    sizes = [int(v) for v in comm.all_gather(torch.tensor([n_local], dtype=torch.int64, device=dev)).cpu().view(-1).tolist()]
+    # shard sizes: gathered once per communicator and re-used; every call re-validates them inside the candidate
+    # count exchange below (each rank's n_local rides along), and starts over with a fresh gather if any changed
+    key = getattr(comm, 'cache_key', None)
+    sizes = _SIZES.get(key) if key is not None else None
+    for _round in range(2):
+        if sizes is None:
+            sizes = [int(v) for v in comm.all_gather(torch.tensor([n_local], dtype=torch.int64, device=dev)).cpu().view(-1).tolist()]
+            if key is not None:
+                _SIZES[key] = sizes
+        res = _sharded_with_sizes(st, comm, lw_local, Reff, sizes, want_detail)
+        if res is not None:
+            return res
+        sizes = None                       # some rank's shard changed since the sizes were cached
+        if key is not None:
+            _SIZES.pop(key, None)
+    raise _lib.ViabelB200Error('psislw: shard sizes changed during the call')
+
+
+_SIZES = {}
+
+
+def _sharded_with_sizes(st, comm, lw_local, Reff, sizes, want_detail):
+    world, rank = comm.world, comm.rank
+    n_local = int(lw_local.numel())
+    dev = lw_local.device
     n = sum(sizes)
     if n <= 1:
         raise ValueError("More than one log-weight needed.")
@@ -181,12 +207,14 @@ def psislw_sharded(lw_local, Reff=1.0, group=None, stages=None, want_detail=Fals
         if not direct:
             st.pivot(sample_all.clone(), world * SAMPLE, frac, pivot)    # the stage may sort / pad its input
         cand, count_t, body_max = st.filter(lw_local, index0, pivot, cap)
-        # one collective + one host read: every rank's candidate count (its own among them)
-        pair = torch.cat([count_t.view(1).to(torch.int64), torch.tensor([cap], dtype=torch.int64, device=dev)])
-        gathered = comm.all_gather(pair).cpu().view(-1, 2).tolist()
-        all_counts = [int(c) for c, _ in gathered]
+        # one collective + one host read: every rank's candidate count, buffer capacity and shard size
+        trip = torch.cat([count_t.view(1).to(torch.int64), torch.tensor([cap, n_local], dtype=torch.int64, device=dev)])
+        gathered = comm.all_gather(trip).cpu().view(-1, 3).tolist()
+        if [int(g[2]) for g in gathered] != list(sizes):
+            return None
+        all_counts = [int(g[0]) for g in gathered]
         count, total = all_counts[rank], sum(all_counts)
-        if any(int(c) > int(k) for c, k in gathered):
+        if any(int(g[0]) > int(g[1]) for g in gathered):
             raise _lib.ViabelB200Error('psislw: more candidates than the buffer holds (heavy ties at the top)')
         if total >= K1 + 1:
             break
@@ -198,25 +226,34 @@ def psislw_sharded(lw_local, Reff=1.0, group=None, stages=None, want_detail=Fals
     terms = st.empty((2,), torch.float64)
     st.prepare(cand, count, M, pivot, body_max, terms)
     if world > 1 and total > 2 * (K1 + 1) and total > 8192:
-        # global refinement: ONE threshold for all ranks from the summed histogram (32 KB all-reduce), so the
-        # gathered candidate set is ~K+1 in total and the replicated sort does not grow with the world size
-        hist = comm.all_reduce_sum(st.refine_hist(cand, count, M, pivot))
-        cand2, count2_t = st.refine_select(cand, count, M, pivot, hist, K1 + 1, terms)
+        # global refinement: the bins are the same on every rank, so the ranks exchange their 8192 counters (one
+        # all-gather, 32 KB per rank) and cut at ONE threshold: ~K+1 candidates in total, independent of the world
+        # size -- and every rank also knows how many each rank keeps, so no second count exchange is needed
+        hist_all = comm.all_gather(st.refine_hist(cand, count, M, pivot))                     # (world, bins) int32
+        cand2, _ = st.refine_select(cand, count, M, pivot, hist_all.sum(0, dtype=torch.int32), K1 + 1, terms)
+        h = hist_all.cpu().numpy().astype('int64')            # the one host read of this exchange
+        cum = h.sum(0).cumsum()
+        hit = (cum >= K1 + 1).nonzero()[0]
+        bstar = int(hit[0]) if len(hit) else h.shape[1] - 1   # same rule as the device scan (hist_scan_kernel)
+        counts = [int(v) for v in h[:, :bstar + 1].sum(1)]
     else:
         cand2, count2_t = st.refine(cand, count, M, pivot, K1 + 1, terms)
-    counts = [int(v) for v in comm.all_gather(count2_t.view(1).to(torch.int64)).cpu().view(-1).tolist()]
+        counts = [int(v) for v in comm.all_gather(count2_t.view(1).to(torch.int64)).cpu().view(-1).tolist()]
     count2 = counts[rank]
     maxc = max(max(counts), 1)
-    send = st.empty((maxc, 2), torch.int64)
+    # candidates and the two body-sum terms travel in ONE all-gather: row maxc of the send buffer holds the terms
+    send = st.empty((maxc + 1, 2), torch.int64)
     send[:count2] = cand2[:count2]
     if count2 < maxc:
-        send[count2:] = 0
-    recv = comm.all_gather(send)                                      # (world, maxc, 2)
+        send[count2:maxc] = 0
+    send[maxc] = terms.view(torch.int64)
+    recv = comm.all_gather(send)                                      # (world, maxc + 1, 2)
     all_cands = torch.cat([recv[r, :counts[r]] for r in range(world)], dim=0).contiguous()
-    all_terms = comm.all_gather(terms).view(-1).contiguous()          # rank order: deterministic sum
+    all_terms = recv[:, maxc, :].contiguous().view(torch.float64).view(-1)     # rank order: deterministic sum
     total2 = sum(counts)
     diag, tail_idx, handle = st.tail(all_cands, total2, K1, M, pivot, all_terms, want_tail_idx=want_detail)
     out = st.write(lw_local, index0, M, handle)
+    n = sum(sizes)
     d = diag.cpu().numpy()
     if not want_detail:
         return out, d[0]
