@@ -1,0 +1,106 @@
+// Micro-benchmark: what limits a streaming sum of exp(x - pivot) over 1.25e8 doubles on B200?
+// Variants isolate the table lookup, the clamp, the fp64 operation count and the reduction arithmetic.
+//   nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -o exp_bench exp_bench.cu && ./exp_bench
+#include <cstdio>
+#include <cstdlib>
+#include <cuda_runtime.h>
+#include "../../viabel_b200/csrc/common.cuh"
+using namespace vb;
+
+template <int V>
+__device__ __forceinline__ double f(double x, const double* table) {
+    if (V == 0) return exp_nonpos_flush(x, table);                       // production routine
+    if (V == 6) return x;                                                // pure read + add
+    if (V == 4) return (double)__expf((float)x);                         // fp32 reference point
+    const double kMagic = kExpCoef[1];
+    double xc = x;
+    if (V != 2) xc = !(x <= kExpCoef[9]) ? x : kExpCoef[9];              // V2: no clamp
+    const double t = fma(xc, kExpCoef[0], kMagic);
+    const int ki = __double2loint(t);
+    const double kd = t - kMagic;
+    double r = fma(kd, kExpCoef[2], xc);
+    r = fma(kd, kExpCoef[3], r);
+    double q;
+    if (V == 3) {                                                        // V3: half the polynomial
+        q = fma(r, kExpCoef[8], 1.0);
+        q = q * r;
+    } else {
+        q = fma(r, kExpCoef[4], kExpCoef[5]);
+        q = fma(r, q, kExpCoef[6]);
+        q = fma(r, q, kExpCoef[7]);
+        q = fma(r, q, kExpCoef[8]);
+        q = fma(r, q, 1.0);
+        q = q * r;
+    }
+    double T = 1.0;
+    if (V != 1) T = table[ki & 63];                                      // V1: no table lookup
+    if (V == 5) T = __ldg(&kExp2Table[ki & 63]);                         // V5: table through L1 instead of smem
+    const double Ts = __hiloint2double(__double2hiint(T) + ((ki & ~63) << 14), __double2loint(T));
+    return fma(Ts, q, Ts);
+}
+
+template <int V>
+__global__ void __launch_bounds__(256) sum_kernel(const double* __restrict__ x, long long n, double pivot, double* out) {
+    __shared__ double s_table[64];
+    __shared__ double scratch[32];
+    if (threadIdx.x < 64) s_table[threadIdx.x] = kExp2Table[threadIdx.x];
+    __syncthreads();
+    const long long n2 = n >> 1;
+    const double2* p = reinterpret_cast<const double2*>(x);
+    const long long gt = blockIdx.x * (long long)blockDim.x + threadIdx.x, gs = (long long)gridDim.x * blockDim.x;
+    double a = 0.0, b = 0.0;
+    long long i = gt;
+    for (; i + 3 * gs < n2; i += 4 * gs) {
+        const double2 v0 = ld_stream2(p + i), v1 = ld_stream2(p + i + gs), v2 = ld_stream2(p + i + 2 * gs), v3 = ld_stream2(p + i + 3 * gs);
+        a += f<V>(v0.x - pivot, s_table); b += f<V>(v0.y - pivot, s_table);
+        a += f<V>(v1.x - pivot, s_table); b += f<V>(v1.y - pivot, s_table);
+        a += f<V>(v2.x - pivot, s_table); b += f<V>(v2.y - pivot, s_table);
+        a += f<V>(v3.x - pivot, s_table); b += f<V>(v3.y - pivot, s_table);
+    }
+    for (; i < n2; i += gs) { const double2 v = ld_stream2(p + i); a += f<V>(v.x - pivot, s_table); b += f<V>(v.y - pivot, s_table); }
+    a = block_sum(a + b, scratch);
+    if (threadIdx.x == 0) out[blockIdx.x] = a;
+}
+
+template <int V>
+static void run(const char* name, const double* x, long long n, double* out, int grid) {
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    for (int w = 0; w < 3; ++w) sum_kernel<V><<<grid, 256>>>(x, n, 10.0, out);
+    cudaEventRecord(e0);
+    const int reps = 20;
+    for (int r = 0; r < reps; ++r) sum_kernel<V><<<grid, 256>>>(x, n, 10.0, out);
+    cudaEventRecord(e1);
+    cudaEventSynchronize(e1);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    ms /= reps;
+    printf("%-44s grid %5d  %7.3f ms  %7.1f GB/s  (%s)\n", name, grid, ms, 8.0 * n / ms / 1e6, cudaGetErrorString(cudaGetLastError()));
+}
+
+__global__ void fill(double* x, long long n) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        unsigned long long h = (unsigned long long)i * 0x9E3779B97F4A7C15ull;
+        h ^= h >> 29;
+        x[i] = 10.0 - 12.0 * (double)(h >> 11) * (1.0 / 9007199254740992.0);     // uniform in (-2, 10]: x - pivot in (-12, 0]
+    }
+}
+
+int main() {
+    const long long n = 125000000;
+    double *x, *out;
+    cudaMalloc(&x, n * 8);
+    cudaMalloc(&out, 1 << 20);
+    fill<<<1184, 256>>>(x, n);
+    cudaDeviceSynchronize();
+    for (int grid : {148 * 4, 148 * 8}) {
+        run<6>("V6 read + add (no exp)", x, n, out, grid);
+        run<0>("V0 production exp (table in smem)", x, n, out, grid);
+        run<1>("V1 no table lookup", x, n, out, grid);
+        run<5>("V5 table through L1 (__ldg)", x, n, out, grid);
+        run<2>("V2 no clamp", x, n, out, grid);
+        run<3>("V3 polynomial cut to 2 operations", x, n, out, grid);
+        run<4>("V4 fp32 __expf (cvt both ways)", x, n, out, grid);
+    }
+    return 0;
+}
