@@ -1461,7 +1461,10 @@ psis_columns_kernel(const double* __restrict__ lw_cols, double* __restrict__ out
                 const bool b_less = kb < ka || (kb == ka && ib < ia);
                 if (b_less == ((i & k) == 0)) { keys[i] = kb; keys[q] = ka; idxs[i] = ib; idxs[q] = ia; }
             }
-            __syncthreads();
+            // steps with j <= 32 stay inside the 64-element block a warp owns (t = tid + 256 m -> elements
+            // [64 (t / 32), +64)), so they only need a warp barrier; a block barrier precedes every wider step
+            const int next_j = (j > 1) ? (j >> 1) : k;
+            if (next_j > 32 || (j == 1 && k == n_pad)) __syncthreads(); else __syncwarp();
         }
     }
     // cutoff and strict tail (psis.py:157,169-176), as tail_bounds_kernel
