@@ -397,6 +397,7 @@ class N3(Workload):
         self._out = torch.empty_like(self._cols)
         self._ks = torch.empty(self.m, dtype=torch.float64, device='cuda')
         self._loo = torch.empty(self.m, dtype=torch.float64, device='cuda')
+        self._status = torch.empty(self.m, dtype=torch.int32, device='cuda')
         self._pin = None
 
     def step_device(self):
@@ -412,7 +413,7 @@ class N3(Workload):
         from viabel_b200._device import stream_ptr
         p = self._ptr
         self.lib.check(self.lib.lib.vb_psis_smooth_columns(p(self._cols), p(self._out), self.n, self.m, 1.0,
-                                                           p(self._ks), p(self._loo), stream_ptr()))
+                                                           p(self._ks), p(self._loo), p(self._status), stream_ptr()))
 
     def roofline(self, ms_kernel, hbm_gbs, bf16_tflops):
         b = 16 * self.n * self.m         # each weight read once and written once (the second read for loo hits L2)

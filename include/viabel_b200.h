@@ -327,10 +327,14 @@ int vb_psis_smooth(const double* d_lw_in, double* d_lw_out, long long n, double 
  *   d_out_k[m]               k-hat per column (inf where the tail has <= 4 points, psis.py:177-179)
  *   d_out_loo_or_null[m]     log sum_i exp(out_ij - lw_ij): with lw = -log_lik this is `loos` of
  *                            psisloo (psis.py:104-107)
+ *   d_status_or_null[m]      scratch ints; when given, columns longer than 2048 draws first try the selection
+ *                            mode (sample pivot -> <= 2048 candidates sorted instead of the whole column) and
+ *                            only the columns it flags are redone with the full in-CTA sort
  * ---------------------------------------------------------------------------------- */
 long long vb_psis_columns_max_n(void);
 int vb_psis_smooth_columns(const double* d_lw_cols, double* d_out_cols, long long n, long long m,
-                           double reff, double* d_out_k, double* d_out_loo_or_null, void* stream);
+                           double reff, double* d_out_k, double* d_out_loo_or_null, int* d_status_or_null,
+                           void* stream);
 
 /* Staged PSIS for log weights sharded by contiguous index ranges (rank r owns global indices
  * [index0, index0 + n_local)); vb_psis_smooth is the same sequence on one GPU.  Candidates are

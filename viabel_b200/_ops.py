@@ -91,8 +91,9 @@ def _psis_smooth_columns(lw_cols, reff, want_loo):
     out = torch.empty_like(lw_cols)
     ks = torch.empty(m, dtype=torch.float64, device=lw_cols.device)
     loo = torch.empty(m if want_loo else 0, dtype=torch.float64, device=lw_cols.device)
+    status = torch.empty(m, dtype=torch.int32, device=lw_cols.device)
     _lib.check(_lib.lib.vb_psis_smooth_columns(ptr(lw_cols), ptr(out), n, m, reff, ptr(ks), ptr(loo) if want_loo else 0,
-                                               stream_ptr()), 'vb_psis_smooth_columns')
+                                               ptr(status), stream_ptr()), 'vb_psis_smooth_columns')
     return out, ks, loo
 
 

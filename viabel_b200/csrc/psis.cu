@@ -1412,46 +1412,34 @@ extern "C" int vb_psis_normalise(double* d_lw_out, long long n_local, double lse
 // ------------------------------------------------------------------------------------------ batched columns (N3)
 // psislw on an (n, m) matrix (psis.py:136-137,163: one independent smoothing per column) and the psisloo
 // reduction (psis.py:68-109) for the shapes PSIS-LOO has: a few thousand draws per column, many columns.
-// ONE CTA per column, everything in shared memory: max -> (key, index) pairs -> bitonic sort of the whole column
-// -> exact cutoff / strict tail -> GPD fit (one warp per quadrature point) -> inverse-CDF smoothing -> log-sum-exp
-// -> out = value - lse scattered back by index.  Same comparisons and formulas as the single-column path above
+// ONE CTA per column.  Like the single-column pipeline it never sorts the column: a 256-entry strided sample gives
+// a pivot with ~3 (K+1) elements above it, those are compacted into shared memory and sorted there (<= 2048
+// (key, index) pairs instead of the 4096-8192 of the column), then exact cutoff / strict tail -> GPD fit (one warp
+// per quadrature point) -> inverse-CDF smoothing -> log-sum-exp -> out = value - lse, with the body read from
+// global memory (L2) in index order.  A column whose candidate set does not fit (heavy ties) or falls short is
+// flagged and redone by a second launch of the same kernel in FULL mode (every element a candidate); short
+// columns (n <= 1024) go straight to FULL mode.  Same comparisons and formulas as the single-column path above
 // (tail set and order are bit-exact; k-hat and the weights differ from it by summation order only).
 namespace vb {
 
 constexpr int kColThreads = 256;
-constexpr int kColMaxN = 8192;                 // 64 KiB of keys + 16 KiB of 16-bit indices: 2 CTAs per SM at the
-                                               // maximum, 4-5 at the usual 4096 draws (the sort is barrier-latency bound)
+constexpr int kColMaxN = 8192;                 // FULL mode: 64 KiB of keys + 16 KiB of 16-bit indices
 constexpr int kColMaxQ = 128;                  // quadrature points: 30 + sqrt(n2) <= 30 + sqrt(0.2 * 8192) = 70
+constexpr int kColSelCap = 2048;               // candidate capacity of the selection mode (20 KiB)
+constexpr int kColSample = 256;
 
 struct ColSmem {
     double scratch[32];
     double bs[kColMaxQ], L[kColMaxQ], w[kColMaxQ];
     double st[8];                              // xcut, exp(xcut), k, sigma, smoothed, lse, b, spare
     long long cnt[4];                          // n2, first tail position, quadrature points, fit runs
+    unsigned long long pivot_key;
+    unsigned int ncand;
+    int bail;
 };
 
-__global__ void __launch_bounds__(kColThreads)
-psis_columns_kernel(const double* __restrict__ lw_cols, double* __restrict__ out_cols, int n, int n_pad, int K1,
-                    double* __restrict__ out_k, double* __restrict__ out_loo_or_null) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    ColSmem& S = *reinterpret_cast<ColSmem*>(smem_raw);
-    unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem_raw + ((sizeof(ColSmem) + 15) & ~(size_t)15));
-    double* x2 = reinterpret_cast<double*>(keys + n_pad);       // [K1]: tail excesses, ascending; later the new values
-    unsigned short* idxs = reinterpret_cast<unsigned short*>(x2 + (K1 > 0 ? K1 : 1));
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = kColThreads / 32;
-    const double* x = lw_cols + (size_t)blockIdx.x * n;
-    double* out = out_cols + (size_t)blockIdx.x * n;
-
-    // max, keys relative to it (psis.py:165-167)
-    double M = -INFINITY;
-    for (int i = tid; i < n; i += kColThreads) M = fmax(M, x[i]);
-    M = block_max(M, S.scratch);
-    for (int i = tid; i < n_pad; i += kColThreads) {
-        keys[i] = (i < n) ? u_to_key(M - x[i]) : ~0ull;
-        idxs[i] = (i < n) ? (unsigned short)i : (unsigned short)0xffff;
-    }
-    __syncthreads();
-    // ascending (key, index) == ascending shifted weight, ties by ascending index
+// ascending bitonic sort of (keys, idxs)[0, n_pad) by (key, index); n_pad a power of two
+__device__ __forceinline__ void col_bitonic(unsigned long long* keys, unsigned short* idxs, int n_pad, int tid) {
     for (int k = 2; k <= n_pad; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
             for (int t = tid; t < n_pad / 2; t += kColThreads) {
@@ -1461,23 +1449,95 @@ psis_columns_kernel(const double* __restrict__ lw_cols, double* __restrict__ out
                 const bool b_less = kb < ka || (kb == ka && ib < ia);
                 if (b_less == ((i & k) == 0)) { keys[i] = kb; keys[q] = ka; idxs[i] = ib; idxs[q] = ia; }
             }
-            // steps with j <= 32 stay inside the 64-element block a warp owns (t = tid + 256 m -> elements
-            // [64 (t / 32), +64)), so they only need a warp barrier; a block barrier precedes every wider step
-            const int next_j = (j > 1) ? (j >> 1) : k;
-            if (next_j > 32 || (j == 1 && k == n_pad)) __syncthreads(); else __syncwarp();
+            __syncthreads();
         }
     }
-    // cutoff and strict tail (psis.py:157,169-176), as tail_bounds_kernel
+}
+
+
+// cap: capacity (power of two) of the candidate arrays in shared memory.  SELECT: candidates = elements at or above
+// a sample pivot; otherwise every element.  status (or null): SELECT launches set status[col] = 1 when the column
+// must be redone; FULL launches that receive status skip the columns whose status is 0.
+template <bool SELECT>
+__global__ void __launch_bounds__(kColThreads)
+psis_columns_kernel(const double* __restrict__ lw_cols, double* __restrict__ out_cols, int n, int cap, int K1,
+                    double* __restrict__ out_k, double* __restrict__ out_loo_or_null, int* __restrict__ status) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    ColSmem& S = *reinterpret_cast<ColSmem*>(smem_raw);
+    unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem_raw + ((sizeof(ColSmem) + 15) & ~(size_t)15));
+    double* x2 = reinterpret_cast<double*>(keys + cap);         // [K1]: tail excesses, ascending; later the new values
+    unsigned short* idxs = reinterpret_cast<unsigned short*>(x2 + (K1 > 0 ? K1 : 1));
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = kColThreads / 32;
+    if (!SELECT && status != nullptr && status[blockIdx.x] == 0) return;
+    const double* x = lw_cols + (size_t)blockIdx.x * n;
+    double* out = out_cols + (size_t)blockIdx.x * n;
+
+    // max (psis.py:165)
+    double M = -INFINITY;
+    for (int i = tid; i < n; i += kColThreads) M = fmax(M, x[i]);
+    M = block_max(M, S.scratch);
+
+    int C, C_pad;
+    if (SELECT) {
+        // pivot from a strided sample: about 3 (K1 + 1) + 64 elements are expected at or above it
+        for (int s = tid; s < kColSample; s += kColThreads) {
+            keys[s] = u_to_key(M - x[(long long)s * n / kColSample]);
+            idxs[s] = (unsigned short)s;
+        }
+        if (tid == 0) { S.ncand = 0u; S.bail = 0; }
+        __syncthreads();
+        col_bitonic(keys, idxs, kColSample, tid);
+        if (tid == 0) {
+            long long rank_top = ((long long)kColSample * (3ll * (K1 + 1) + 64) + n - 1) / n;
+            if (rank_top < 4) rank_top = 4;
+            if (rank_top >= kColSample) S.bail = 1;                   // the candidates would be most of the column
+            else S.pivot_key = keys[kColSample - rank_top];
+        }
+        __syncthreads();
+        if (!S.bail) {
+            const unsigned long long pk = S.pivot_key;
+            __syncthreads();                                          // everyone holds the pivot: the arrays are free
+            for (int i = tid; i < n; i += kColThreads) {
+                const unsigned long long key = u_to_key(M - x[i]);
+                if (key >= pk) {                                      // larger key == larger weight
+                    const unsigned int pos = atomicAdd(&S.ncand, 1u);
+                    if (pos < (unsigned int)cap) { keys[pos] = key; idxs[pos] = (unsigned short)i; }
+                }
+            }
+            __syncthreads();
+            if (tid == 0 && (S.ncand > (unsigned int)cap || S.ncand < (unsigned int)(K1 + 1))) S.bail = 1;
+            __syncthreads();
+        }
+        if (S.bail) {
+            if (tid == 0) status[blockIdx.x] = 1;
+            return;
+        }
+        C = (int)S.ncand;
+        C_pad = 2;
+        while (C_pad < C) C_pad <<= 1;
+        for (int i = C + tid; i < C_pad; i += kColThreads) { keys[i] = ~0ull; idxs[i] = (unsigned short)0xffff; }
+    } else {
+        C = n;
+        C_pad = cap;
+        for (int i = tid; i < C_pad; i += kColThreads) {
+            keys[i] = (i < n) ? u_to_key(M - x[i]) : ~0ull;
+            idxs[i] = (i < n) ? (unsigned short)i : (unsigned short)0xffff;
+        }
+    }
+    __syncthreads();
+    // ascending (key, index) == ascending shifted weight, ties by ascending index (psis.py:167 with kind='stable')
+    col_bitonic(keys, idxs, C_pad, tid);
+    // cutoff and strict tail (psis.py:157,169-176), as tail_bounds_kernel: the K1 + 1 largest are all candidates
     if (tid == 0) {
-        const double u_cut = key_to_u(keys[n - 1 - K1]);
+        const double u_cut = key_to_u(keys[C - 1 - K1]);
         const double xcut = fmax(-u_cut, -kNegLogTiny);
         const double u_eff = -xcut;
-        int lo = 0, hi = n;
+        int lo = 0, hi = C;
         while (lo < hi) {
             const int mid = (lo + hi) >> 1;
             if (key_to_u(keys[mid]) < u_eff) hi = mid; else lo = mid + 1;
         }
-        const int n2 = n - lo;
+        const int n2 = C - lo;
         S.st[0] = xcut;
         S.st[1] = exp(xcut);
         S.cnt[0] = n2;
@@ -1488,7 +1548,7 @@ psis_columns_kernel(const double* __restrict__ lw_cols, double* __restrict__ out
     __syncthreads();
     const int n2 = (int)S.cnt[0], p0 = (int)S.cnt[1], mq = (int)S.cnt[2];
     const bool fit = S.cnt[3] != 0;
-    const double ec = S.st[1];
+    const double ec = S.st[1], u_eff = -S.st[0];
     for (int r = tid; r < n2; r += kColThreads) x2[r] = exp(-key_to_u(keys[p0 + r])) - ec;     // psis.py:184-185
     __syncthreads();
     if (fit) {                                                                                  // psis.py:266-323
@@ -1539,7 +1599,6 @@ psis_columns_kernel(const double* __restrict__ lw_cols, double* __restrict__ out
     const bool smoothed = S.st[4] != 0.0;
     const double kh = S.st[2], sigma = S.st[3];
     // new tail values (psis.py:190-198); x2 is reused for them
-    __syncthreads();
     double se = 0.0;
     for (int r = tid; r < n2; r += kColThreads) {
         double v;
@@ -1552,26 +1611,38 @@ psis_columns_kernel(const double* __restrict__ lw_cols, double* __restrict__ out
         x2[r] = v;
         se += exp(v);
     }
-    for (int r = tid; r < p0; r += kColThreads) se += exp(-key_to_u(keys[r]));
+    // the body: every element at or below the cutoff, read back from global memory (L2) in index order
+    for (int i = tid; i < n; i += kColThreads) {
+        const double u = M - x[i];
+        if (!(u < u_eff)) se += exp(-u);
+    }
     se = block_sum(se, S.scratch);
     const double lse = log(se);                                                                  // psis.py:200
-    // write back by index; optional leave-one-out term log sum_i exp(out_i - lw_i) (psis.py:104-107, lw = -log_lik)
+    // write back; optional leave-one-out term log sum_i exp(out_i - lw_i) (psis.py:104-107, lw = -log_lik)
     double lmax = -INFINITY;
-    for (int r = tid; r < n; r += kColThreads) {
-        const int i = (int)idxs[r];
-        const double v = ((r >= p0) ? x2[r - p0] : -key_to_u(keys[r])) - lse;
+    for (int i = tid; i < n; i += kColThreads) {
+        const double u = M - x[i];
+        if (!(u < u_eff)) {
+            const double v = -u - lse;
+            out[i] = v;
+            lmax = fmax(lmax, v - x[i]);
+        }
+    }
+    for (int r = tid; r < n2; r += kColThreads) {
+        const int i = (int)idxs[p0 + r];
+        const double v = x2[r] - lse;
         out[i] = v;
-        if (out_loo_or_null) lmax = fmax(lmax, v - x[i]);
+        lmax = fmax(lmax, v - x[i]);
     }
     if (tid == 0) out_k[blockIdx.x] = kh;
     if (out_loo_or_null) {
         lmax = block_max(lmax, S.scratch);
         double a = 0.0;
-        for (int r = tid; r < n; r += kColThreads) {
-            const int i = (int)idxs[r];
-            const double v = ((r >= p0) ? x2[r - p0] : -key_to_u(keys[r])) - lse;
-            a += exp((v - x[i]) - lmax);
+        for (int i = tid; i < n; i += kColThreads) {
+            const double u = M - x[i];
+            if (!(u < u_eff)) a += exp(((-u - lse) - x[i]) - lmax);
         }
+        for (int r = tid; r < n2; r += kColThreads) a += exp(((x2[r] - lse) - x[(int)idxs[p0 + r]]) - lmax);
         a = block_sum(a, S.scratch);
         if (tid == 0) out_loo_or_null[blockIdx.x] = log(a) + lmax;                               // psis.py:390-395
     }
@@ -1582,7 +1653,8 @@ psis_columns_kernel(const double* __restrict__ lw_cols, double* __restrict__ out
 extern "C" long long vb_psis_columns_max_n(void) { return vb::kColMaxN; }
 
 extern "C" int vb_psis_smooth_columns(const double* d_lw_cols, double* d_out_cols, long long n, long long m,
-                                      double reff, double* d_out_k, double* d_out_loo_or_null, void* stream) {
+                                      double reff, double* d_out_k, double* d_out_loo_or_null, int* d_status,
+                                      void* stream) {
     using namespace vb;
     if (!d_lw_cols || !d_out_cols || !d_out_k || m < 1 || !(reff > 0.0)) return VB_ERR_ARG;
     if (n <= 1) return VB_ERR_ARG;                                    // psis.py:143-144
@@ -1592,15 +1664,35 @@ extern "C" int vb_psis_smooth_columns(const double* d_lw_cols, double* d_out_col
     while (n_pad < n) n_pad <<= 1;
     const long long K1 = psis_K1(n, reff);
     if (K1 + 1 > n) return VB_ERR_UNSUPPORTED;                        // Reff so small that the cutoff leaves the column
-    const size_t smem = ((sizeof(ColSmem) + 15) & ~(size_t)15) + (size_t)n_pad * 8 +
-                        (size_t)(K1 > 0 ? K1 : 1) * sizeof(double) + (size_t)n_pad * 2;
-    static size_t configured = 0;
-    if (smem > configured) {
-        VB_CUDA_TRY(cudaFuncSetAttribute(psis_columns_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
+    cudaStream_t st = (cudaStream_t)stream;
+    auto smem_for = [&](long long cap) {
+        return ((sizeof(ColSmem) + 15) & ~(size_t)15) + (size_t)cap * 8 + (size_t)(K1 > 0 ? K1 : 1) * sizeof(double) +
+               (size_t)cap * 2;
+    };
+    static size_t configured[2] = {0, 0};
+    // selection mode when it can pay: the column is longer than the candidate buffer and the expected candidate
+    // count (3 (K1 + 1) + 64) fits it with room to spare; d_status (m ints) is required for it
+    static const bool no_select = getenv("VB_PSIS_COLUMNS_FULL") != nullptr && atoi(getenv("VB_PSIS_COLUMNS_FULL")) != 0;
+    const bool select = !no_select && d_status != nullptr && n > kColSelCap && 3 * (K1 + 1) + 64 <= kColSelCap / 2;
+    if (select) {
+        const size_t smem = smem_for(kColSelCap);
+        if (smem > configured[1]) {
+            VB_CUDA_TRY(cudaFuncSetAttribute(psis_columns_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            configured[1] = smem;
+        }
+        VB_CUDA_TRY(cudaMemsetAsync(d_status, 0, (size_t)m * sizeof(int), st));
+        psis_columns_kernel<true><<<(unsigned)m, kColThreads, smem, st>>>(
+            d_lw_cols, d_out_cols, (int)n, kColSelCap, (int)K1, d_out_k, d_out_loo_or_null, d_status);
+        VB_LAUNCH_CHECK();
     }
-    psis_columns_kernel<<<(unsigned)m, kColThreads, smem, (cudaStream_t)stream>>>(
-        d_lw_cols, d_out_cols, (int)n, (int)n_pad, (int)K1, d_out_k, d_out_loo_or_null);
+    const size_t smem = smem_for(n_pad);
+    if (smem > configured[0]) {
+        VB_CUDA_TRY(cudaFuncSetAttribute(psis_columns_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured[0] = smem;
+    }
+    // FULL mode: every column, or (after a selection launch) only the flagged ones -- the other CTAs exit at once
+    psis_columns_kernel<false><<<(unsigned)m, kColThreads, smem, st>>>(
+        d_lw_cols, d_out_cols, (int)n, (int)n_pad, (int)K1, d_out_k, d_out_loo_or_null, select ? d_status : nullptr);
     VB_LAUNCH_CHECK();
     return VB_OK;
 }

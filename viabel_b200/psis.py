@@ -38,8 +38,9 @@ def _smooth_columns(cols, Reff, want_loo=False):
         out = torch.empty_like(cols)
         ks = torch.empty(m, dtype=torch.float64, device=cols.device)
         loo = torch.empty(m, dtype=torch.float64, device=cols.device) if want_loo else None
+        status = torch.empty(m, dtype=torch.int32, device=cols.device)
         _lib.check(_lib.lib.vb_psis_smooth_columns(ptr(cols), ptr(out), n, m, float(Reff), ptr(ks), ptr(loo),
-                                                   stream_ptr()), 'vb_psis_smooth_columns')
+                                                   ptr(status), stream_ptr()), 'vb_psis_smooth_columns')
         return out, ks, loo
     outs, ks = [], np.empty(m)
     for i in range(m):
