@@ -103,3 +103,102 @@ def loo_case(name):
     if name == 'tiny_n12_m3':
         return np.random.RandomState(24).randn(12, 3)
     raise KeyError(name)
+
+
+# ------------------------------------------------------------------------------------------ R-hat / optimisers (N4)
+RHAT_CASES = ['c4_t400_p6', 'c1_t64_p3', 'c3_t1000_p40_warm', 'const_param']
+RHAT_WINDOW_CASES = ['c2_t600_p8', 'c3_t1200_p10']
+AVERAGING_CASES = ['n50_k4', 'n400_k7_start100']
+OPTIM_CASES = ['adagrad_const', 'adagrad_decay_lognorm', 'rmsprop_1opt', 'rmsprop_2opt_avgnorm', 'adam_1opt',
+               'adam_2opt_lognorm']
+
+
+def _ar_chains(n_chains, n_iters, p, seed, drift=0.0):
+    """Autocorrelated chains around chain-specific levels (so R-hat is neither 1 nor huge)."""
+    rs = np.random.RandomState(seed)
+    x = np.zeros((n_chains, n_iters, p))
+    level = 0.3 * rs.randn(n_chains, p)
+    e = rs.randn(n_chains, n_iters, p)
+    for t in range(1, n_iters):
+        x[:, t] = 0.8 * x[:, t - 1] + e[:, t]
+    return x + level[:, None, :] + drift * np.linspace(1.0, 0.0, n_iters)[None, :, None] ** 4
+
+
+def rhat_case(name):
+    """(chains (n_chains, n_iters, p), kwargs of compute_R_hat)."""
+    if name == 'c4_t400_p6':
+        return _ar_chains(4, 400, 6, 31), {'warmup': 0}
+    if name == 'c1_t64_p3':
+        return _ar_chains(1, 64, 3, 32), {'warmup': 0}
+    if name == 'c3_t1000_p40_warm':
+        return _ar_chains(3, 1000, 40, 33, drift=5.0), {}           # default warmup = 500
+    if name == 'const_param':
+        x = _ar_chains(2, 100, 4, 34)
+        x[:, :, 2] = 1.5                                              # zero variance: only the jitter keeps W > 0
+        return x, {'warmup': 20}
+    raise KeyError(name)
+
+
+def rhat_window_case(name):
+    """(chains, window_size, interval, start) for compute_R_hat_adaptive_numpy / compute_R_hat_halfway."""
+    if name == 'c2_t600_p8':
+        return _ar_chains(2, 600, 8, 35, drift=3.0), 100, 100, 200
+    if name == 'c3_t1200_p10':
+        return _ar_chains(3, 1200, 10, 36, drift=8.0), 200, 100, 1000     # start + k*interval runs past the end
+    raise KeyError(name)
+
+
+def averaging_case(name):
+    if name == 'n50_k4':
+        return np.random.RandomState(37).randn(50, 4), 0
+    if name == 'n400_k7_start100':
+        return np.cumsum(np.random.RandomState(38).randn(400, 7), axis=0) * 0.05, 100
+    raise KeyError(name)
+
+
+class NoisyQuadratic:
+    """Deterministic stand-in for a Monte Carlo objective: value 1/2 sum a (x - c)^2 + noise, gradient
+    a (x - c) + noise, drawn from the objective's OWN RandomState so that the reference optimiser and the one
+    under test see the same sequence (call k gets draw k).  With has_log_norm the third return value is a
+    per-call log normaliser, as CHIVI-style objectives give."""
+
+    def __init__(self, dim, seed, has_log_norm=False):
+        rs = np.random.RandomState(seed)
+        self.a = np.exp(0.5 * rs.randn(dim))
+        self.c = rs.randn(dim)
+        self.rs = np.random.RandomState(seed + 1000)
+        self.has_log_norm = has_log_norm
+        self.calls = 0
+
+    def __call__(self, x):
+        x = np.asarray(x, dtype=np.float64)
+        self.calls += 1
+        r = x - self.c
+        value = 0.5 * np.sum(self.a * r * r) + 0.05 * self.rs.randn()
+        grad = self.a * r + 0.1 * self.rs.randn(len(x))
+        if self.has_log_norm:
+            return value, grad, -0.3 * value + 0.2 * self.rs.randn()
+        return value, grad
+
+
+def optim_case(name):
+    """(kind, n_iters, init_param, kwargs, objective seed)."""
+    init6 = np.array([1.5, -0.5, 0.25, 0.0, -1.0, 0.5])
+    if name == 'adagrad_const':
+        return 'adagrad', 60, init6, {}, 41
+    if name == 'adagrad_decay_lognorm':
+        return 'adagrad', 80, init6, {'has_log_norm': True, 'window': 5, 'learning_rate': .05, 'epsilon': .2,
+                                      'learning_rate_end': .005}, 42
+    if name == 'rmsprop_1opt':
+        return 'rmsprop', 400, init6, {'rhat_window': 100, 'tail_avg_iters': 150, 'learning_rate': .02}, 43
+    if name == 'rmsprop_2opt_avgnorm':
+        return 'rmsprop', 400, init6, {'rhat_window': 50, 'n_optimisers': 2, 'avg_grad_norm': True, 'window': 5,
+                                       'tail_avg_iters': 100, 'learning_rate': .05, 'learning_rate_end': .01,
+                                       'r_mean_threshold': 1.6, 'r_sigma_threshold': 1.7}, 44
+    if name == 'adam_1opt':
+        return 'adam', 400, init6, {'rhat_window': 100, 'tail_avg_iters': 150, 'learning_rate': .02}, 45
+    if name == 'adam_2opt_lognorm':
+        return 'adam', 400, init6, {'rhat_window': 50, 'n_optimisers': 2, 'has_log_norm': True, 'window': 4,
+                                    'tail_avg_iters': 120, 'learning_rate': .05, 'learning_rate_end': .01,
+                                    'r_mean_threshold': 1.6, 'r_sigma_threshold': 1.7}, 46
+    raise KeyError(name)
