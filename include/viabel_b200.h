@@ -408,6 +408,29 @@ size_t vb_max_workspace_bytes(long long n);
 int vb_max(const double* d_x, long long n, double* d_out, void* d_ws, size_t ws_bytes,
            void* stream);
 
+/* ------------------------------------------------------------------------------------
+ * Convergence diagnostics of the R-hat-monitored optimisers (viabel/functions.py, called from
+ * rmsprop_IA_optimize_with_rhat / adam_IA_optimize_with_rhat, viabel/vb.py:486-522).
+ *   vb_rhat_windows     compute_R_hat (functions.py:8-31) on n_windows iteration windows of a
+ *                       (n_chains, n_iters, n_params) fp64 history at once: window w covers the
+ *                       iterations [d_windows[2w], d_windows[2w] + d_windows[2w+1]) of every chain
+ *                       (the caller guarantees even lengths >= 2 inside the history), each chain
+ *                       cut in two halves.  One call serves compute_R_hat (1 window),
+ *                       compute_R_hat_adaptive_numpy (functions.py:44-52: consecutive windows) and
+ *                       compute_R_hat_halfway (functions.py:54-65: second halves of growing
+ *                       prefixes).  Outputs (n_windows, n_params): var_hat and R-hat = sqrt(var_hat).
+ *   vb_iterate_average  stochastic_iterate_averaging (functions.py:68-77): out[t - start] =
+ *                       mean(est[start..t]) for t in [start, n_iters); est has row stride ld, so a
+ *                       column block of the history (the means, or the log scales) is passed in
+ *                       place.  Summation order is that of numpy's cumsum.
+ * ---------------------------------------------------------------------------------- */
+size_t vb_rhat_workspace_bytes(int n_chains, long long n_params, int n_windows);
+int vb_rhat_windows(const double* d_chains, int n_chains, long long n_iters, long long n_params,
+                    const long long* d_windows, int n_windows, double* d_out_var_hat,
+                    double* d_out_rhat, void* d_ws, size_t ws_bytes, void* stream);
+int vb_iterate_average(const double* d_est, long long n_iters, long long n_params, long long ld,
+                       long long start, double* d_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

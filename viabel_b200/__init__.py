@@ -7,7 +7,7 @@ Importing needs the compiled ``libviabel_b200.so`` (``python -m viabel_b200.buil
 CPU fallback.
 """
 from .bounds import *          # noqa: F401,F403
-from . import bounds, models, psis, vb   # noqa: F401
+from . import bounds, functions, models, psis, vb   # noqa: F401
 
 __version__ = '0.1.0'
 from . import _ops             # noqa: F401,E402  (registers torch.ops.viabel_b200.*)

@@ -94,6 +94,9 @@ SIGNATURES = {
     'vb_psis_normalise': (_i, [_p, _ll, _d, _p]),
     'vb_max_workspace_bytes': (_sz, [_ll]),
     'vb_max': (_i, [_p, _ll, _p, _p, _sz, _p]),
+    'vb_rhat_workspace_bytes': (_sz, [_i, _ll, _i]),
+    'vb_rhat_windows': (_i, [_p, _i, _ll, _ll, _p, _i, _p, _p, _p, _sz, _p]),
+    'vb_iterate_average': (_i, [_p, _ll, _ll, _ll, _ll, _p, _p]),
 }
 
 

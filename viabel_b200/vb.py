@@ -35,6 +35,8 @@ __all__ = [
     'black_box_klvi',
     'black_box_chivi',
     'adagrad_optimize',
+    'rmsprop_IA_optimize_with_rhat',
+    'adam_IA_optimize_with_rhat',
     'learning_rate_schedule',
 ]
 
@@ -672,3 +674,116 @@ def adagrad_optimize(n_iters, objective_and_grad, init_param,
             progress.close()
     kept = np.array(kept)
     return np.mean(kept, axis=0), kept, np.array(values), np.array(norms)
+
+
+# --------------------------------------------------------------------------- R-hat-monitored optimisers (fork)
+def _first_converged_window(rhat_windows, threshold, rhat_window, default):
+    """First window that, together with its successor, has every R-hat below the threshold (``vb.py:499-515``)."""
+    for ee in range(rhat_windows.shape[0] - 1):
+        if (rhat_windows[ee] < threshold).all() and (rhat_windows[ee + 1] < threshold).all():
+            return ee * rhat_window
+    return default
+
+
+def _optimize_with_rhat(rule, n_iters, objective_and_grad, init_param, K, has_log_norm, window, learning_rate,
+                        epsilon, rhat_window, n_optimisers, r_mean_threshold, r_sigma_threshold, tail_avg_iters,
+                        avg_grad_norm, learning_rate_end):
+    """Shared body of ``rmsprop_IA_optimize_with_rhat`` (``vb.py:392-548``) and ``adam_IA_optimize_with_rhat``
+    (``vb.py:554-712``): n_optimisers restarts of the update rule, the iterate history of every restart, then the
+    windowed / halfway split R-hat of that history and the iterate averages from the first converged window on.
+    The objective is this package's CUDA step; the diagnostics run on the device over the uploaded history
+    (``functions.py``).  The reference's windowed-gradient bookkeeping (``vb.py:456-459``) feeds nothing and is
+    not restated."""
+    import scipy.stats as stats
+    from . import functions as fn
+    init_param = np.array(init_param, dtype=float, copy=True)
+    param = init_param.copy()
+    values, norms, chains = [], [], []
+    decay, beta1, beta2 = 0.9, 0.9, 0.999
+    spread = 0.5 if rule == 'rmsprop' else 0.2                       # vb.py:425, :592
+    for o in range(n_optimisers):
+        history = []
+        np.random.seed(seed=o)                                       # the reference reseeds the GLOBAL numpy stream
+        if o >= 1:
+            param = init_param + stats.norm.rvs(size=len(init_param)) * (o + 1) * spread
+        with tqdm.trange(n_iters) as progress:
+            try:
+                rates = learning_rate_schedule(n_iters, learning_rate, learning_rate_end)
+                for i, rate in zip(progress, rates):
+                    if has_log_norm:
+                        value, grad, log_norm = objective_and_grad(param)
+                    else:
+                        value, grad = objective_and_grad(param)
+                        log_norm = 0
+                    grad = np.asarray(grad, dtype=float)
+                    values.append(value)
+                    norms.append(log_norm)
+                    if rule == 'rmsprop':
+                        grad_norm = np.exp(log_norm) if has_log_norm else np.sum(grad ** 2, axis=0)
+                        if i == 0:
+                            second = grad_norm if avg_grad_norm else grad ** 2
+                        elif avg_grad_norm:
+                            second = grad_norm * decay + (1. - decay) * grad_norm      # vb.py:452, as written
+                        else:
+                            second = second * decay + (1. - decay) * grad ** 2
+                        step = rate * grad / np.sqrt(epsilon + second)
+                    else:
+                        if i == 0:
+                            second, first = 0.9 * grad ** 2, 0.9 * grad               # vb.py:617-618
+                        else:
+                            second = second * beta2 + (1. - beta2) * grad ** 2
+                            first = first * beta1 + (1. - beta1) * grad
+                        m_hat = first / (1 - np.power(beta1, i + 2))
+                        v_hat = second / (1 - np.power(beta2, i + 2))
+                        step = rate * m_hat / np.sqrt(epsilon + v_hat)
+                    history.append(param.copy())                     # pre-update iterate, vb.py:464
+                    param = param - step
+                    if len(history) > 100 * window:
+                        del history[0]
+                    if i % 100 == 0:
+                        progress.set_description('Average Loss = {:,.6g}'.format(np.mean(values[max(0, i - 1000):i + 1])))
+            except (KeyboardInterrupt, StopIteration):  # pragma: no cover
+                progress.close()
+            finally:
+                progress.close()
+        chains.append(np.array(history))
+    chains = np.stack(chains, axis=0)
+    chains_dev = to_dev(chains, _lib.F64)                             # one upload; every diagnostic reads it in place
+    rhats = fn.compute_R_hat_adaptive_numpy(chains_dev, window_size=rhat_window).cpu().numpy()
+    halfway = fn.compute_R_hat_halfway(chains_dev, interval=100, start=200).cpu().numpy()
+    start_m = _first_converged_window(rhats[:, :K], r_mean_threshold, rhat_window, n_iters - tail_avg_iters)
+    start_s = _first_converged_window(rhats[:, K:], r_sigma_threshold, rhat_window, n_iters - tail_avg_iters)
+    avg_means, avg_sigmas = [], []
+    for o in range(n_optimisers):
+        avg_means.append(fn.stochastic_iterate_averaging(chains_dev[o, :, :K], start_m)[0].cpu().numpy())
+        avg_sigmas.append(fn.stochastic_iterate_averaging(chains_dev[o, :, K:], start_s)[0].cpu().numpy())
+    log = {'start_avg_mean_iters': start_m, 'start_avg_sigma_iters': start_s,
+           'r_hat_mean': rhats[:, :K], 'r_hat_sigma': rhats[:, K:],
+           'r_hat_mean_halfway': halfway[:, :K], 'r_hat_sigma_halfway': halfway[:, K:]}
+    return param, chains, avg_means, avg_sigmas, np.array(values), np.array(norms), log
+
+
+def rmsprop_IA_optimize_with_rhat(n_iters, objective_and_grad, init_param, K,
+                                  has_log_norm=False, window=500, learning_rate=.01,
+                                  epsilon=.000001, rhat_window=500, averaging=True, n_optimisers=1,
+                                  r_mean_threshold=1.15, r_sigma_threshold=1.20, tail_avg_iters=2000,
+                                  avg_grad_norm=False, learning_rate_end=None):
+    """RMSProp with iterate averaging started where the windowed split R-hat says the iterates are stationary
+    (``vb.py:392-548``).  ``K`` = number of location parameters (the first K entries of the variational parameter;
+    the rest are log scales).  Returns ``(param, history (n_optimisers, kept, P), averaged means per optimiser,
+    averaged log scales per optimiser, value_history, log_norm_history, optimisation_log)``."""
+    return _optimize_with_rhat('rmsprop', n_iters, objective_and_grad, init_param, K, has_log_norm, window,
+                               learning_rate, epsilon, rhat_window, n_optimisers, r_mean_threshold,
+                               r_sigma_threshold, tail_avg_iters, avg_grad_norm, learning_rate_end)
+
+
+def adam_IA_optimize_with_rhat(n_iters, objective_and_grad, init_param, K,
+                               has_log_norm=False, window=500, learning_rate=.01,
+                               epsilon=.000001, rhat_window=500, averaging=True, n_optimisers=1,
+                               r_mean_threshold=1.15, r_sigma_threshold=1.20, tail_avg_iters=2000,
+                               learning_rate_end=None):
+    """Adam (bias correction with exponent i + 2, first step seeded with 0.9 g, as ``vb.py:617-629``) with the same
+    R-hat-triggered iterate averaging (``vb.py:554-712``); same return tuple as the RMSProp variant."""
+    return _optimize_with_rhat('adam', n_iters, objective_and_grad, init_param, K, has_log_norm, window,
+                               learning_rate, epsilon, rhat_window, n_optimisers, r_mean_threshold,
+                               r_sigma_threshold, tail_avg_iters, False, learning_rate_end)
