@@ -30,7 +30,7 @@ def parse():
     ap.add_argument('--steps', type=int, default=None)
     ap.add_argument('--warmup', type=int, default=None)
     ap.add_argument('--workload', default=os.environ.get('VB_BENCH_WORKLOAD', 'c2'),
-                    help='c2 (default: BASELINE.json configs[1]), c1, c3, c3chol, c4, c5, c2f64, n3 (psisloo)')
+                    help='c2 (default: BASELINE.json configs[1]), c1, c3, c3chol, c4, c5, c2f64, n3 (psisloo), n4r (R-hat diagnostics)')
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--profile-kernel-only', action='store_true',

@@ -460,7 +460,113 @@ class N3(Workload):
                 'e2e': {'value': rate, 'unit': self.unit, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
 
 
-WORKLOADS = {'c1': C1, 'c4': C4, 'c5': C5, 'n3': N3}
+class N4R(Workload):
+    """Convergence diagnostics of the R-hat optimisers (viabel/functions.py) over a C3-sized iterate history:
+    2 restarts x 2000 iterates x 131 840 parameters (4.2 GB fp64): windowed split R-hat (8 windows of 250),
+    halfway R-hat of the whole history, iterate averages of the last 500 iterates of both restarts."""
+    name = 'n4r'
+    chains, iters, params = 2, 2000, 131840
+    window = 250
+    unit = 'iterate values/s'
+    default_steps, default_warmup = 5, 3
+    cpu_params = 4096
+
+    def setup(self):
+        import torch
+        from viabel_b200 import functions, _lib
+        from viabel_b200._device import ptr
+        self.torch, self.fn, self.lib, self._ptr = torch, functions, _lib, ptr
+        g = torch.Generator(device='cuda')
+        g.manual_seed(41 + self.rank)
+        self.hist = torch.randn((self.chains, self.iters, self.params), dtype=torch.float64, device='cuda', generator=g)
+        self.hist += torch.linspace(1.0, 0.0, self.iters, dtype=torch.float64, device='cuda')[None, :, None] ** 4
+        self.units_per_step = self.chains * self.iters * self.params
+        self.h2d_bytes = self.units_per_step * 8
+        self.d2h_bytes = 8 * self.params * (self.iters // self.window + 1)
+        self.launches_per_step = 2 + 2 + 2 * self.chains
+        nw = self.iters // self.window
+        self._win = torch.tensor([[i * self.window, self.window] for i in range(nw)], dtype=torch.int64, device='cuda')
+        self._vh = torch.empty((nw, self.params), dtype=torch.float64, device='cuda')
+        self._rh = torch.empty((nw, self.params), dtype=torch.float64, device='cuda')
+        nb = _lib.lib.vb_rhat_workspace_bytes(self.chains, self.params, nw)
+        self._ws = torch.zeros(nb, dtype=torch.uint8, device='cuda')
+        self._pin = None
+
+    def _diagnose(self, hist):
+        r = self.fn.compute_R_hat_adaptive_numpy(hist, window_size=self.window)
+        h = self.fn.compute_R_hat(hist, warmup=self.iters // 2)[1]
+        dev = hist if hasattr(hist, 'is_cuda') else None
+        avgs = []
+        if dev is not None:
+            for o in range(self.chains):
+                avgs.append(self.fn.stochastic_iterate_averaging(dev[o], self.iters - 500)[1])
+        return r, h, avgs
+
+    def step_device(self):
+        return self._diagnose(self.hist)
+
+    def step_e2e(self):
+        if self._pin is None:
+            self._pin = self.torch.empty(self.hist.shape, dtype=self.torch.float64, pin_memory=True)
+            self._pin.copy_(self.hist)
+        dev = self._pin.to('cuda', non_blocking=True)                  # the history is uploaded once per step
+        r, h, avgs = self._diagnose(dev)
+        return r.cpu(), h.cpu(), [a.cpu() for a in avgs]
+
+    def kernel_only(self):
+        from viabel_b200._device import stream_ptr
+        p = self._ptr
+        self.lib.check(self.lib.lib.vb_rhat_windows(p(self.hist), self.chains, self.iters, self.params, p(self._win),
+                                                    self._win.shape[0], p(self._vh), p(self._rh), p(self._ws),
+                                                    self._ws.numel(), stream_ptr()))
+
+    def roofline(self, ms_kernel, hbm_gbs, bf16_tflops):
+        b = 8 * self.units_per_step      # every iterate value read once (the second pass about the mean hits L2)
+        ach = b / (ms_kernel * 1e-3) / 1e9
+        return {'bound': 'hbm', 'achieved': ach, 'peak': hbm_gbs, 'unit': 'GB/s', 'frac': ach / hbm_gbs,
+                'traffic': None, 'kernel': 'rhat_halfchain_kernel + rhat_finish_kernel (vb_rhat_windows, 8 windows)',
+                'ms_per_launch': ms_kernel, 'algorithmic_bytes_per_launch': b,
+                'note': 'two-pass variance as the reference computes it: a CTA re-reads its 125 x 256 B slab from L2'}
+
+    def config(self):
+        return {'workload': self.config_name(), 'chains': self.chains, 'iterates': self.iters, 'params': self.params,
+                'l2': 'history (4.2 GB) larger than L2', 'parallelism': 'replicas x%d' % self.world}
+
+    def config_name(self):
+        return ('n4r: windowed + halfway split R-hat and iterate averages of a 2 x 2000 x 131840 fp64 iterate '
+                'history (C3 parameter count)')
+
+    def _cpu(self, params):
+        from oracle import functions_np as ofn
+        rs = np.random.RandomState(5)
+        hist = rs.randn(self.chains, self.iters, params) + np.linspace(1.0, 0.0, self.iters)[None, :, None] ** 4
+        t0 = time.perf_counter()
+        ofn.compute_R_hat_adaptive_numpy(hist, window_size=self.window)
+        ofn.compute_R_hat(hist, warmup=self.iters // 2)
+        for o in range(self.chains):
+            ofn.stochastic_iterate_averaging(hist[o], self.iters - 500)
+        return self.chains * self.iters * params / (time.perf_counter() - t0)
+
+    def cpu_baseline(self):
+        rate = self._cpu(self.cpu_params)
+        return {'value': rate, 'unit': self.unit, 'cores': 1, 'kind': 'port',
+                'sample': 'oracle diagnostics on %d of the %d parameters, single-threaded numpy'
+                          % (self.cpu_params, self.params)}
+
+    def reference_arm(self, steps, warmup):
+        k = max(1, min(steps, 3))
+        t0 = time.perf_counter()
+        rates = [self._cpu(self.cpu_params) for _ in range(k)]
+        dt = (time.perf_counter() - t0) / k
+        rate = float(np.mean(rates))
+        cb = {'value': rate, 'unit': self.unit, 'cores': 1, 'kind': 'port',
+              'sample': 'oracle diagnostics on %d parameters x %d x %d iterates per step' % (self.cpu_params, self.chains, self.iters)}
+        return {'metric': self.metric, 'value': rate, 'unit': self.unit, 'ms_per_step': dt * 1e3, 'dtype': 'f64',
+                'config': {'workload': self.config_name()}, 'cpu_baseline': cb,
+                'e2e': {'value': rate, 'unit': self.unit, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+
+
+WORKLOADS = {'c1': C1, 'c4': C4, 'c5': C5, 'n3': N3, 'n4r': N4R}
 
 
 

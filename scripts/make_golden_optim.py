@@ -4,16 +4,13 @@ REFERENCE's own viabel/vb.py and viabel/functions.py in the build container.
 `autograd` and `paragami` are not installed here.  The optimisers (`adagrad_optimize`,
 `rmsprop_IA_optimize_with_rhat`, `adam_IA_optimize_with_rhat`, `learning_rate_schedule`) and the diagnostics
 (`compute_R_hat*`, `stochastic_iterate_averaging`) only use the numpy namespace those packages re-export, so the
-modules are imported with thin stand-ins: `autograd.numpy` IS numpy, the differentiation entry points and the
-paragami patterns are placeholders that raise when called (nothing here calls them).  The reference sources are
-executed where they lie (read-only); only outputs are stored.
+modules are imported with the stand-ins of scripts/ref_stand_ins.py (`autograd.numpy` forwards to numpy; nothing
+here differentiates).  The reference sources are executed where they lie (read-only); only outputs are stored.
 
 Run:  python scripts/make_golden_optim.py      ->  tests/golden/optimizers.npz
 """
-import importlib
 import os
 import sys
-import types
 import warnings
 
 import numpy as np
@@ -21,56 +18,11 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, 'tests'))
+sys.path.insert(0, os.path.join(ROOT, 'scripts'))
 sys.dont_write_bytecode = True
 import golden_inputs as gi   # noqa: E402
 
-REF = os.environ.get('VIABEL_REFERENCE', '/root/reference')
-
-
-def _unavailable(*a, **k):
-    raise RuntimeError('autograd / paragami are not installed: this entry point is a placeholder')
-
-
-def install_stand_ins():
-    import scipy.linalg
-    import scipy.special
-    import scipy.stats
-
-    def mod(name, **attrs):
-        m = types.ModuleType(name)
-        m.__dict__.update(attrs)
-        sys.modules[name] = m
-        return m
-
-    def primitive(f):
-        f.defvjp = lambda *a, **k: None
-        return f
-
-    ag = mod('autograd', value_and_grad=_unavailable, vector_jacobian_product=_unavailable)
-    ag.extend = mod('autograd.extend', primitive=primitive, defvjp=lambda *a, **k: None)
-    sys.modules['autograd.numpy'] = np
-    sys.modules['autograd.numpy.random'] = np.random
-    ag.numpy = np
-    sc = mod('autograd.scipy')
-    st = mod('autograd.scipy.stats')
-    sys.modules['autograd.scipy.stats.multivariate_normal'] = scipy.stats.multivariate_normal
-    sys.modules['autograd.scipy.stats.t'] = scipy.stats.t
-    st.multivariate_normal, st.t = scipy.stats.multivariate_normal, scipy.stats.t
-    sc.stats = st
-    sc.linalg = mod('autograd.scipy.linalg', sqrtm=scipy.linalg.sqrtm)
-    sc.special = scipy.special
-    sys.modules['autograd.scipy.special'] = scipy.special
-    ag.scipy = sc
-    mod('paragami', PatternDict=_unavailable, NumericVectorPattern=_unavailable,
-        PSDSymmetricMatrixPattern=_unavailable, FlattenFunctionInput=_unavailable)
-
-
-def load_reference():
-    install_stand_ins()
-    sys.path.insert(0, REF)
-    vb = importlib.import_module('viabel.vb')
-    fn = importlib.import_module('viabel.functions')
-    return vb, fn
+from ref_stand_ins import load_reference   # noqa: E402
 
 
 def main():

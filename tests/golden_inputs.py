@@ -202,3 +202,38 @@ def optim_case(name):
                                     'tail_avg_iters': 120, 'learning_rate': .05, 'learning_rate_end': .01,
                                     'r_mean_threshold': 1.6, 'r_sigma_threshold': 1.7}, 46
     raise KeyError(name)
+
+
+# ------------------------------------------------------------------------------------------ vb.py objectives
+# Log densities handed to the REFERENCE's black_box_klvi / black_box_chivi by scripts/make_golden_vb.py: plain numpy
+# (so they also accept the complex arguments of the complex-step differentiation stand-in); the tests check that
+# they equal the oracle's model plugins at real arguments.
+def funnel_logp(x, a=1.35):
+    mu, ls = x[:, 0], x[:, 1]
+    return (-0.5 * np.log(2 * np.pi) - np.log(a) - 0.5 * (ls / a) ** 2) \
+        + (-0.5 * np.log(2 * np.pi) - ls - 0.5 * mu * mu * np.exp(-2 * ls))
+
+
+SCHOOLS_Y = np.array([28., 8., -3., 7., -1., 1., 18., 12.])
+SCHOOLS_SIGMA = np.array([15., 10., 16., 11., 9., 11., 10., 18.])
+
+
+def eight_schools_logp(u):
+    mu, lt, th = u[:, 0], u[:, 1], u[:, 2:]
+    tau = np.exp(lt)
+    r = (SCHOOLS_Y[None, :] - mu[:, None] - tau[:, None] * th) / SCHOOLS_SIGMA[None, :]
+    return -mu * mu / 50 - np.log1p(tau * tau / 25) + lt - 0.5 * np.sum(th * th, axis=1) - 0.5 * np.sum(r * r, axis=1)
+
+
+VB_CASES = ['gauss_funnel', 't_schools']
+
+
+def vb_case(name):
+    """(family kind, dim, df, log density name, var_param, n_samples)."""
+    if name == 'gauss_funnel':
+        return 'mf_gauss', 2, None, 'funnel', np.array([0.1, -0.2, 0.3, -0.1]), 64
+    if name == 't_schools':
+        rs = np.random.RandomState(51)
+        lam = np.concatenate([[4.0, 0.8], 0.2 * rs.randn(8), np.log([3.2, 0.73]), -0.05 + 0.02 * rs.randn(8)])
+        return 'mf_t', 10, 7.0, 'eight_schools', lam, 48
+    raise KeyError(name)

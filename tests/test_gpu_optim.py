@@ -1,6 +1,6 @@
 """R-hat diagnostics (csrc/rhat.cu behind viabel_b200.functions) and the R-hat-monitored optimisers against the
 golden vectors of the REFERENCE's own functions (tests/golden/optimizers.npz, scripts/make_golden_optim.py)
-and against the oracle on larger seeded histories.  Tolerance: the device sums the iterations in 32 stripes, the
+and against the oracle on larger seeded histories.  Tolerance: the device sums the iterations in 8 stripes, the
 reference row by row -> rtol 1e-10 on var_hat / R-hat; the iterate averages use numpy's order -> exact."""
 import os
 import sys

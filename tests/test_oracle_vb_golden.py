@@ -1,0 +1,74 @@
+"""The oracle's mean-field families and KLVI / CHIVI objectives against golden vectors produced by the REFERENCE's
+own viabel/vb.py (scripts/make_golden_vb.py: the reference code run in the build container, autograd's
+value_and_grad / vector_jacobian_product stood in by complex-step differentiation of the reference's own objective
+functions, exact to rounding).  This pins `oracle/vb_np.py` for the mean-field families: random streams, entropy,
+log density, moments, objective values and gradients."""
+import os
+
+import numpy as np
+import pytest
+
+import golden_inputs as gi
+from oracle import models_np as mm
+from oracle import vb_np
+
+GOLD = np.load(os.path.join(os.path.dirname(__file__), 'golden', 'vb_reference.npz'))
+RTOL = 1e-12
+
+
+def oracle_family(kind, dim, df):
+    return vb_np.mean_field_gaussian_variational_family(dim) if kind == 'mf_gauss' \
+        else vb_np.mean_field_t_variational_family(dim, df)
+
+
+def oracle_model(name):
+    return mm.Funnel(1.35) if name == 'funnel' else mm.EightSchoolsNCP()
+
+
+@pytest.mark.parametrize('name', gi.VB_CASES)
+def test_log_density_inputs_equal_the_oracle_models(name):
+    kind, dim, df, logp_name, lam, n = gi.vb_case(name)
+    x = np.random.RandomState(3).randn(20, dim)
+    np.testing.assert_allclose(getattr(gi, logp_name + '_logp')(x), oracle_model(logp_name).logp_and_grad(x)[0],
+                               rtol=1e-14)
+
+
+@pytest.mark.parametrize('name', gi.VB_CASES)
+def test_family_closures(name):
+    kind, dim, df, logp_name, lam, n = gi.vb_case(name)
+    g = lambda k: GOLD['vb/%s/%s' % (name, k)]      # noqa: E731
+    fam = oracle_family(kind, dim, df)
+    assert fam.var_param_dim == int(g('var_param_dim'))
+    np.testing.assert_allclose(fam.sample(lam, 5), g('sample_1'), rtol=RTOL)
+    np.testing.assert_allclose(fam.sample(lam, 5), g('sample_2'), rtol=RTOL)
+    x = fam.sample(lam, 6, seed=11)
+    np.testing.assert_allclose(x, g('sample_seed11'), rtol=RTOL)
+    np.testing.assert_allclose(fam.entropy(lam), g('entropy'), rtol=RTOL)
+    np.testing.assert_allclose(fam.logdensity(x, lam), g('logdensity'), rtol=RTOL)
+    m, c = fam.mean_and_cov(lam)
+    np.testing.assert_allclose(m, g('mean'), rtol=RTOL)
+    np.testing.assert_allclose(c, g('cov'), rtol=RTOL)
+    for p in (2, 4):
+        np.testing.assert_allclose(fam.pth_moment(p, lam), g('pth_moment_%d' % p), rtol=RTOL)
+
+
+@pytest.mark.parametrize('name', gi.VB_CASES)
+def test_klvi_objective_and_grad(name):
+    kind, dim, df, logp_name, lam, n = gi.vb_case(name)
+    obj = vb_np.black_box_klvi(oracle_family(kind, dim, df), oracle_model(logp_name), n)
+    for call in (1, 2):
+        v, grad = obj(lam)
+        np.testing.assert_allclose(v, GOLD['vb/%s/klvi_value_%d' % (name, call)], rtol=RTOL)
+        np.testing.assert_allclose(grad, GOLD['vb/%s/klvi_grad_%d' % (name, call)], rtol=1e-11, atol=1e-13)
+
+
+@pytest.mark.parametrize('alpha', [2.0, 1.5])
+@pytest.mark.parametrize('name', gi.VB_CASES)
+def test_chivi_objective_and_grad(name, alpha):
+    kind, dim, df, logp_name, lam, n = gi.vb_case(name)
+    np.random.seed(123)                                   # the per-call seed comes from the global stream, vb.py:258
+    obj = vb_np.black_box_chivi(alpha, oracle_family(kind, dim, df), oracle_model(logp_name), n)
+    for call in (1, 2):
+        v, grad = obj(lam)[:2]
+        np.testing.assert_allclose(v, GOLD['vb/%s/chivi%g_value_%d' % (name, alpha, call)], rtol=RTOL)
+        np.testing.assert_allclose(grad, GOLD['vb/%s/chivi%g_grad_%d' % (name, alpha, call)], rtol=1e-11, atol=1e-13)

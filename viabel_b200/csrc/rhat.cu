@@ -14,7 +14,7 @@ namespace vb {
 namespace {
 
 constexpr int kRhatTX = 32;      // parameters per CTA (one 256-byte row segment per warp load)
-constexpr int kRhatTY = 32;      // iteration stripes per CTA
+constexpr int kRhatTY = 8;       // iteration stripes per CTA (256 threads: 8 CTAs per SM overlap their load / reduce phases)
 
 // ws layout: mean[n_windows][2C][K], s2[n_windows][2C][K]
 __global__ void __launch_bounds__(kRhatTX * kRhatTY)
@@ -33,8 +33,10 @@ rhat_halfchain_kernel(const double* __restrict__ chains, int n_chains, long long
     const bool live = p < K;
     // pass 1: mean
     double s = 0.0;
-    if (live)
+    if (live) {
+#pragma unroll 8
         for (long long t = ty; t < n; t += kRhatTY) s += base[(size_t)t * K + p];
+    }
     red[ty][tx] = s;
     __syncthreads();
     if (ty == 0) {
@@ -48,11 +50,13 @@ rhat_halfchain_kernel(const double* __restrict__ chains, int n_chains, long long
     __syncthreads();
     // pass 2: squared deviations about the mean (functions.py:25)
     double q = 0.0;
-    if (live)
+    if (live) {
+#pragma unroll 8
         for (long long t = ty; t < n; t += kRhatTY) {
-            const double d = base[(size_t)t * K + p] - mean;
+            const double d = base[(size_t)t * K + p] - mean;        // second read: L1 / L2 hit (the CTA's own slab)
             q = fma(d, d, q);
         }
+    }
     red[ty][tx] = q;
     __syncthreads();
     if (ty == 0 && live) {
