@@ -21,10 +21,23 @@ Contents (every function cites the reference ``file:line`` it restates; citation
 * ``vb_autograd``– literal torch-CPU-fp64-autograd transcription of ``viabel/vb.py`` /
   ``viabel/_distributions.py`` (autograd → torch.autograd); used to validate ``vb_np``.
 
-PARITY STATUS of the VI path (``vb_np`` / ``vb_autograd``): **parity unpinned**.
-``viabel/vb.py`` cannot be imported anywhere we can run (its dependencies ``autograd``,
-``paragami`` and ``pystan`` are absent and there is no network) and the reference ships no
-test, fixture or golden vector for it (``README.md:66``).  What *is* pinned: family
-``logdensity`` against ``scipy.stats`` (the arithmetic ``autograd.scipy`` wraps), and the
-closed-form gradients against torch autograd of the literal transcription.
+* ``functions_np`` – numpy restatement of ``viabel/functions.py`` (R-hat family, iterate
+  averaging) and of the RMSProp / Adam R-hat optimisers of ``viabel/vb.py:392-712``.   PINNED:
+  golden outputs of the reference's own functions (``tests/golden/optimizers.npz``, generator
+  ``scripts/make_golden_optim.py``), which also pin ``vb_np.adagrad_optimize`` and
+  ``vb_np.learning_rate_schedule``.
+
+PARITY STATUS of the VI path (``vb_np`` / ``vb_autograd``):
+* mean-field families, KLVI and CHIVI ``objective_and_grad``: **PINNED** on golden vectors made
+  by running the reference's own ``viabel/vb.py`` in the build container
+  (``tests/golden/vb_reference.npz``, generator ``scripts/make_golden_vb.py``): ``autograd`` is
+  absent, so its ``value_and_grad`` / ``vector_jacobian_product`` are stood in by complex-step
+  differentiation of the reference's own objective functions (exact to rounding), see
+  ``scripts/ref_stand_ins.py``.
+* full-rank Student-t family: pinned on golden vectors of the reference's own
+  ``t_variational_family`` / ``multivariate_t_logpdf`` / ``black_box_*`` (same file and
+  generator): values, samples, log density and moments at 1e-11; gradients through a 4-point
+  central difference of the reference's objective (``eigh`` / ``sqrtm`` are not complex-analytic
+  as called), tolerance 1e-7, observed 1e-11.  NOT pinned: ``paragami``'s flattening layout --
+  the package is absent and its three patterns are stood in from its documentation.
 """

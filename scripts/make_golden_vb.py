@@ -17,7 +17,7 @@ sys.path.insert(0, os.path.join(ROOT, 'tests'))
 sys.path.insert(0, os.path.join(ROOT, 'scripts'))
 sys.dont_write_bytecode = True
 import golden_inputs as gi   # noqa: E402
-from ref_stand_ins import load_reference   # noqa: E402
+from ref_stand_ins import load_reference, set_mode   # noqa: E402
 
 
 def main():
@@ -59,6 +59,36 @@ def main():
                     v, g = obj(lam)
                     out[pre + 'chivi%g_value_%d' % (alpha, call)] = np.float64(v)
                     out[pre + 'chivi%g_grad_%d' % (alpha, call)] = g
+        # ---- full-rank Student-t family: finite-difference gradients (see ref_stand_ins.py)
+        set_mode('fd')
+        for name in gi.VB_FR_CASES:
+            dim, df, logp_name, lam, n = gi.vb_fr_case(name)
+            logp = getattr(gi, logp_name + '_logp')
+            fam = vb.t_variational_family(dim, df)
+            pre = 'vb/%s/' % name
+            out[pre + 'var_param_dim'] = np.int64(fam.var_param_dim)
+            out[pre + 'sample_1'] = fam.sample(lam, 5)
+            out[pre + 'sample_2'] = fam.sample(lam, 5)
+            x = fam.sample(lam, 6, seed=11)
+            out[pre + 'sample_seed11'] = x
+            out[pre + 'entropy'] = np.float64(fam.entropy(lam))
+            out[pre + 'logdensity'] = np.asarray(fam.logdensity(x, lam))
+            m, c = fam.mean_and_cov(lam)
+            out[pre + 'mean'], out[pre + 'cov'] = np.asarray(m), np.asarray(c)
+            for p in (2, 4):
+                out[pre + 'pth_moment_%d' % p] = np.float64(fam.pth_moment(p, lam))
+            obj = vb.black_box_klvi(vb.t_variational_family(dim, df), logp, n)
+            for call in (1, 2):
+                v, g = obj(lam)
+                out[pre + 'klvi_value_%d' % call], out[pre + 'klvi_grad_%d' % call] = np.float64(v), g
+            for alpha in (2.0,):
+                np.random.seed(123)
+                obj = vb.black_box_chivi(alpha, vb.t_variational_family(dim, df), logp, n)
+                for call in (1, 2):
+                    v, g = obj(lam)
+                    out[pre + 'chivi%g_value_%d' % (alpha, call)] = np.float64(v)
+                    out[pre + 'chivi%g_grad_%d' % (alpha, call)] = g
+        set_mode('complex')
     path = os.path.join(ROOT, 'tests', 'golden', 'vb_reference.npz')
     np.savez_compressed(path, **out)
     print('wrote %s: %d arrays, %.1f kB' % (path, len(out), os.path.getsize(path) / 1e3))

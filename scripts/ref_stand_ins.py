@@ -13,8 +13,13 @@ What stands in for what:
   * `autograd.scipy.stats.multivariate_normal.logpdf`, `autograd.scipy.stats.t.logpdf` -> the textbook formulas
     in plain numpy (so that they accept complex arguments); `check_stand_ins()` verifies them against
     scipy.stats at real arguments to 1e-13.
-  * `paragami`, `autograd.scipy.linalg.sqrtm`, `autograd.extend` -> placeholders (the full-rank family is not
-    exercised through these stand-ins: eigh / sqrtm are not complex-analytic as called).
+  * full-rank family only (`set_mode('fd')`): `eigh` / `sqrtm` as the reference calls them are not
+    complex-analytic, so differentiation falls back to a 4-point central difference (h = 2e-3, truncation
+    O(h^4): about 1e-10 relative on these smooth objectives) -- a weaker pin than the complex step, stated as such
+    in the tests' tolerances.  `paragami` is stood in by a minimal restatement of the three patterns the
+    reference uses, following paragami's documented free parameterisation (vector: identity; PSD matrix: row-major
+    lower triangle of the Cholesky factor with the diagonal logged; PatternDict: concatenation in insertion
+    order).  That layout is the one thing of the full-rank path this cannot pin.
 """
 import importlib
 import os
@@ -29,6 +34,29 @@ import scipy.stats
 REF = os.environ.get('VIABEL_REFERENCE', '/root/reference')
 _STREAMS = []            # every RandomState the reference creates
 _H = 1e-30
+_MODE = 'complex'
+_FD_H = 2e-3
+
+
+def set_mode(mode):
+    global _MODE
+    assert mode in ('complex', 'fd')
+    _MODE = mode
+
+
+def _partial(f, x, j, args, before, weight=None):
+    """d/dx_j of f (scalar, or weight . f for a vector f) on the replayed random streams."""
+    def scal(v):
+        _restore(before)
+        out = f(v, *args)
+        return out if weight is None else np.sum(weight * out)
+    if _MODE == 'complex':
+        xc = x.astype(complex)
+        xc[j] += 1j * _H
+        return np.imag(scal(xc)) / _H
+    e = np.zeros_like(x)
+    e[j] = _FD_H
+    return (8.0 * (scal(x + e) - scal(x - e)) - (scal(x + 2 * e) - scal(x - 2 * e))) / (12.0 * _FD_H)
 
 
 class TrackedRandomState(np.random.RandomState):
@@ -53,12 +81,7 @@ def value_and_grad(f):
         before = _states()
         value = f(x, *args)
         after = _states()
-        grad = np.empty_like(x)
-        for j in range(x.size):
-            _restore(before)
-            xc = x.astype(complex)
-            xc[j] += 1j * _H
-            grad[j] = np.imag(f(xc, *args)) / _H
+        grad = np.array([_partial(f, x, j, args, before) for j in range(x.size)])
         _restore(after)
         return float(np.real(value)), grad
     return vg
@@ -71,12 +94,7 @@ def vector_jacobian_product(f):
         before = _states()
         f(x, *args)
         after = _states()
-        out = np.empty_like(x)
-        for j in range(x.size):
-            _restore(before)
-            xc = x.astype(complex)
-            xc[j] += 1j * _H
-            out[j] = np.sum(np.real(g) * np.imag(f(xc, *args))) / _H
+        out = np.array([_partial(f, x, j, args, before, weight=np.real(g)) for j in range(x.size)])
         _restore(after)
         return out
     return vjp
@@ -107,6 +125,63 @@ def check_stand_ins():
     # complex step against a closed form: d/dx sum log1p(x^2) = 2x / (1 + x^2)
     g = value_and_grad(lambda v: np.sum(np.log1p(v * v)))(m)[1]
     np.testing.assert_allclose(g, 2 * m / (1 + m * m), rtol=1e-15)
+    set_mode('fd')
+    g = value_and_grad(lambda v: np.sum(np.log1p(v * v)))(m)[1]
+    set_mode('complex')
+    np.testing.assert_allclose(g, 2 * m / (1 + m * m), rtol=1e-9)
+
+
+class NumericVectorPattern:
+    def __init__(self, length):
+        self.length = length
+
+    def flat_length(self, free=None):
+        return self.length
+
+    def fold(self, flat, free=None):
+        return np.asarray(flat)
+
+
+class PSDSymmetricMatrixPattern:
+    def __init__(self, size):
+        self.size = size
+
+    def flat_length(self, free=None):
+        return self.size * (self.size + 1) // 2
+
+    def fold(self, flat, free=None):
+        L = np.zeros((self.size, self.size), dtype=np.asarray(flat).dtype)
+        L[np.tril_indices(self.size)] = flat
+        L[np.diag_indices(self.size)] = np.exp(np.diag(L))
+        return L @ L.T
+
+
+class PatternDict:
+    def __init__(self, free_default=None):
+        self.free_default = free_default
+        self.patterns = {}
+
+    def __setitem__(self, name, pattern):
+        self.patterns[name] = pattern
+
+    def flat_length(self, free=None):
+        return sum(p.flat_length(free) for p in self.patterns.values())
+
+    def fold(self, flat, free=None):
+        out, at = {}, 0
+        for name, p in self.patterns.items():
+            k = p.flat_length(free)
+            out[name] = p.fold(flat[at:at + k], free)
+            at += k
+        return out
+
+
+def FlattenFunctionInput(original_fun, patterns, free, argnums):
+    def wrapped(*args):
+        args = list(args)
+        args[argnums] = patterns.fold(args[argnums], free)
+        return original_fun(*args)
+    return wrapped
 
 
 def _unavailable(*a, **k):
@@ -142,8 +217,8 @@ def install():
     sc.special = scipy.special
     sys.modules['autograd.scipy.special'] = scipy.special
     ag.scipy = sc
-    mod('paragami', PatternDict=_unavailable, NumericVectorPattern=_unavailable,
-        PSDSymmetricMatrixPattern=_unavailable, FlattenFunctionInput=_unavailable)
+    mod('paragami', PatternDict=PatternDict, NumericVectorPattern=NumericVectorPattern,
+        PSDSymmetricMatrixPattern=PSDSymmetricMatrixPattern, FlattenFunctionInput=FlattenFunctionInput)
 
 
 def load_reference():

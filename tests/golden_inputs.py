@@ -237,3 +237,23 @@ def vb_case(name):
         lam = np.concatenate([[4.0, 0.8], 0.2 * rs.randn(8), np.log([3.2, 0.73]), -0.05 + 0.02 * rs.randn(8)])
         return 'mf_t', 10, 7.0, 'eight_schools', lam, 48
     raise KeyError(name)
+
+
+# full-rank Student-t family (vb.py:192-233): gradients of these goldens come from a 4-point central difference of
+# the reference's own objective (scripts/ref_stand_ins.py, mode 'fd'), not from the complex step
+VB_FR_CASES = ['fr_t_gauss3']
+_FR_MEAN = np.array([0.5, -1.0, 0.25])
+_FR_PREC = np.array([[2.0, 0.6, -0.3], [0.6, 1.5, 0.2], [-0.3, 0.2, 1.0]])
+
+
+def gauss3_logp(x):
+    r = x - _FR_MEAN
+    return -0.5 * np.sum((r @ _FR_PREC) * r, axis=1)
+
+
+def vb_fr_case(name):
+    """(dim, df, log density name, var_param [mu, free Sigma], n_samples)."""
+    if name == 'fr_t_gauss3':
+        rs = np.random.RandomState(61)
+        return 3, 9.0, 'gauss3', np.concatenate([0.3 * rs.randn(3), 0.25 * rs.randn(6)]), 40
+    raise KeyError(name)

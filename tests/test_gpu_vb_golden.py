@@ -1,0 +1,118 @@
+"""The CUDA mean-field path against golden vectors of the REFERENCE's own viabel/vb.py
+(tests/golden/vb_reference.npz, scripts/make_golden_vb.py).  The product draws from Philox, the reference from
+numpy's RandomState: the reference's base draws are regenerated here from the same seeds and handed to the CUDA
+objective through `base_draws=`, so values and gradients are compared on identical samples (fp64, rtol 1e-10).
+The deterministic closures (entropy, logdensity, mean_and_cov, pth_moment) are compared directly."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+import golden_inputs as gi   # noqa: E402
+
+pytestmark = pytest.mark.gpu
+GOLD = np.load(os.path.join(os.path.dirname(__file__), 'golden', 'vb_reference.npz'))
+RTOL = 1e-10
+
+
+def family(kind, dim, df):
+    from viabel_b200 import vb
+    return vb.mean_field_gaussian_variational_family(dim) if kind == 'mf_gauss' \
+        else vb.mean_field_t_variational_family(dim, df)
+
+
+def model(name):
+    from viabel_b200 import models
+    return models.Funnel(1.35) if name == 'funnel' else models.EightSchoolsNCP()
+
+
+def reference_draws(rs, kind, df, n, dim):
+    """The base draw of the reference's `sample` (vb.py:57 / :151)."""
+    return rs.randn(n, dim) if kind == 'mf_gauss' else rs.standard_t(df, size=(n, dim))
+
+
+@pytest.mark.parametrize('name', gi.VB_CASES)
+def test_family_closures_golden(name):
+    kind, dim, df, logp_name, lam, n = gi.vb_case(name)
+    g = lambda k: GOLD['vb/%s/%s' % (name, k)]      # noqa: E731
+    fam = family(kind, dim, df)
+    assert fam.var_param_dim == int(g('var_param_dim'))
+    np.testing.assert_allclose(fam.entropy(lam), g('entropy'), rtol=RTOL)
+    np.testing.assert_allclose(fam.logdensity(g('sample_seed11'), lam), g('logdensity'), rtol=RTOL)
+    m, c = fam.mean_and_cov(lam)
+    np.testing.assert_allclose(m, g('mean'), rtol=RTOL)
+    np.testing.assert_allclose(c, g('cov'), rtol=RTOL)
+    for p in (2, 4):
+        np.testing.assert_allclose(fam.pth_moment(p, lam), g('pth_moment_%d' % p), rtol=RTOL)
+    # the model plugin on the reference's samples equals the log density the reference was given
+    x = g('sample_seed11')
+    np.testing.assert_allclose(model(logp_name)(x), getattr(gi, logp_name + '_logp')(x), rtol=RTOL)
+
+
+@pytest.mark.parametrize('name', gi.VB_CASES)
+def test_klvi_golden(name):
+    from viabel_b200 import vb
+    kind, dim, df, logp_name, lam, n = gi.vb_case(name)
+    obj = vb.black_box_klvi(family(kind, dim, df), model(logp_name), n, group=False)
+    rs = np.random.RandomState(0)                          # the family's persistent stream, vb.py:49 / :143
+    for call in (1, 2):
+        eps = reference_draws(rs, kind, df, n, dim)
+        v, grad = obj(lam, base_draws={'eps': eps})
+        np.testing.assert_allclose(v, GOLD['vb/%s/klvi_value_%d' % (name, call)], rtol=RTOL)
+        np.testing.assert_allclose(grad, GOLD['vb/%s/klvi_grad_%d' % (name, call)], rtol=RTOL, atol=1e-12)
+
+
+@pytest.mark.parametrize('alpha', [2.0, 1.5])
+@pytest.mark.parametrize('name', gi.VB_CASES)
+def test_chivi_golden(name, alpha):
+    from viabel_b200 import vb
+    kind, dim, df, logp_name, lam, n = gi.vb_case(name)
+    obj = vb.black_box_chivi(alpha, family(kind, dim, df), model(logp_name), n, group=False)
+    seeds = np.random.RandomState(123)                     # np.random.seed(123); npr.randint(2**32) per call, vb.py:258
+    for call in (1, 2):
+        eps = reference_draws(np.random.RandomState(seeds.randint(2 ** 32)), kind, df, n, dim)
+        v, grad = obj(lam, base_draws={'eps': eps})[:2]
+        np.testing.assert_allclose(v, GOLD['vb/%s/chivi%g_value_%d' % (name, alpha, call)], rtol=RTOL)
+        np.testing.assert_allclose(grad, GOLD['vb/%s/chivi%g_grad_%d' % (name, alpha, call)], rtol=RTOL, atol=1e-12)
+
+
+# ------------------------------------------------------------------------------------------ full-rank Student-t
+# fp64 CUDA chain (eigh-based symmetric square root, GEMMs, weighted Gram matrix) against the reference's own
+# sqrtm / eigh / multivariate_t_logpdf code.  The golden gradients are 4-point central differences of the
+# reference's objective (good to ~1e-10), so gradients are compared at 1e-7; everything else at 1e-10.
+def fr_base(rs, df, n, dim):
+    """Draw order of the reference's `sample` (vb.py:204-206): the chi-square scales first, then the normals."""
+    chi2 = rs.chisquare(df, n)
+    return {'chi2': chi2, 'z': rs.randn(n, dim)}
+
+
+@pytest.mark.parametrize('name', gi.VB_FR_CASES)
+def test_full_rank_golden(name):
+    from viabel_b200 import models, vb
+    dim, df, logp_name, lam, n = gi.vb_fr_case(name)
+    g = lambda k: GOLD['vb/%s/%s' % (name, k)]      # noqa: E731
+    fam = vb.t_variational_family(dim, df)
+    mdl = models.CorrelatedGaussian(gi._FR_MEAN, gi._FR_PREC)
+    assert fam.var_param_dim == int(g('var_param_dim'))
+    np.testing.assert_allclose(fam.entropy(lam), g('entropy'), rtol=RTOL)
+    np.testing.assert_allclose(fam.logdensity(g('sample_seed11'), lam), g('logdensity'), rtol=RTOL)
+    m, c = fam.mean_and_cov(lam)
+    np.testing.assert_allclose(m, g('mean'), rtol=RTOL)
+    np.testing.assert_allclose(c, g('cov'), rtol=RTOL)
+    for p in (2, 4):
+        np.testing.assert_allclose(fam.pth_moment(p, lam), g('pth_moment_%d' % p), rtol=RTOL)
+    obj = vb.black_box_klvi(vb.t_variational_family(dim, df), mdl, n, group=False)
+    rs = np.random.RandomState(0)
+    for call in (1, 2):
+        v, grad = obj(lam, base_draws=fr_base(rs, df, n, dim))
+        np.testing.assert_allclose(v, g('klvi_value_%d' % call), rtol=RTOL)
+        np.testing.assert_allclose(grad, g('klvi_grad_%d' % call), rtol=1e-7, atol=1e-8)
+    obj = vb.black_box_chivi(2.0, vb.t_variational_family(dim, df), mdl, n, group=False)
+    seeds = np.random.RandomState(123)
+    for call in (1, 2):
+        base = fr_base(np.random.RandomState(seeds.randint(2 ** 32)), df, n, dim)
+        v, grad = obj(lam, base_draws=base)[:2]
+        np.testing.assert_allclose(v, g('chivi2_value_%d' % call), rtol=RTOL)
+        np.testing.assert_allclose(grad, g('chivi2_grad_%d' % call), rtol=1e-7, atol=1e-8)

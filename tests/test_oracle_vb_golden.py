@@ -72,3 +72,53 @@ def test_chivi_objective_and_grad(name, alpha):
         v, grad = obj(lam)[:2]
         np.testing.assert_allclose(v, GOLD['vb/%s/chivi%g_value_%d' % (name, alpha, call)], rtol=RTOL)
         np.testing.assert_allclose(grad, GOLD['vb/%s/chivi%g_grad_%d' % (name, alpha, call)], rtol=1e-11, atol=1e-13)
+
+
+# ------------------------------------------------------------------------------------------ full-rank Student-t
+# Values, samples, entropy, log density and moments come from the reference's own code (sqrtm, eigh, its
+# multivariate_t_logpdf) and are compared at 1e-11; its gradients were taken by a 4-point central difference of the
+# reference's objective (truncation ~1e-10 relative), hence the looser gradient tolerance.  paragami's flattening
+# layout is a stand-in written from its documentation (scripts/ref_stand_ins.py): that layout stays unpinned.
+FR_GRAD_RTOL, FR_GRAD_ATOL = 1e-7, 1e-8
+
+
+def fr_model(name):
+    assert name == 'gauss3'
+    return mm.CorrelatedGaussian(gi._FR_MEAN, gi._FR_PREC)
+
+
+@pytest.mark.parametrize('name', gi.VB_FR_CASES)
+def test_full_rank_family_closures(name):
+    dim, df, logp_name, lam, n = gi.vb_fr_case(name)
+    g = lambda k: GOLD['vb/%s/%s' % (name, k)]      # noqa: E731
+    x = np.random.RandomState(3).randn(20, dim)
+    np.testing.assert_allclose(getattr(gi, logp_name + '_logp')(x), fr_model(logp_name).logp_and_grad(x)[0], rtol=1e-13)
+    fam = vb_np.t_variational_family(dim, df)
+    assert fam.var_param_dim == int(g('var_param_dim'))
+    np.testing.assert_allclose(fam.sample(lam, 5), g('sample_1'), rtol=1e-11)
+    np.testing.assert_allclose(fam.sample(lam, 5), g('sample_2'), rtol=1e-11)
+    xs = fam.sample(lam, 6, seed=11)
+    np.testing.assert_allclose(xs, g('sample_seed11'), rtol=1e-11)
+    np.testing.assert_allclose(fam.entropy(lam), g('entropy'), rtol=1e-11)
+    np.testing.assert_allclose(fam.logdensity(xs, lam), g('logdensity'), rtol=1e-11)
+    m, c = fam.mean_and_cov(lam)
+    np.testing.assert_allclose(m, g('mean'), rtol=1e-11)
+    np.testing.assert_allclose(c, g('cov'), rtol=1e-11)
+    for p in (2, 4):
+        np.testing.assert_allclose(fam.pth_moment(p, lam), g('pth_moment_%d' % p), rtol=1e-11)
+
+
+@pytest.mark.parametrize('name', gi.VB_FR_CASES)
+def test_full_rank_objectives(name):
+    dim, df, logp_name, lam, n = gi.vb_fr_case(name)
+    obj = vb_np.black_box_klvi(vb_np.t_variational_family(dim, df), fr_model(logp_name), n)
+    for call in (1, 2):
+        v, grad = obj(lam)
+        np.testing.assert_allclose(v, GOLD['vb/%s/klvi_value_%d' % (name, call)], rtol=1e-11)
+        np.testing.assert_allclose(grad, GOLD['vb/%s/klvi_grad_%d' % (name, call)], rtol=FR_GRAD_RTOL, atol=FR_GRAD_ATOL)
+    np.random.seed(123)
+    obj = vb_np.black_box_chivi(2.0, vb_np.t_variational_family(dim, df), fr_model(logp_name), n)
+    for call in (1, 2):
+        v, grad = obj(lam)[:2]
+        np.testing.assert_allclose(v, GOLD['vb/%s/chivi2_value_%d' % (name, call)], rtol=1e-11)
+        np.testing.assert_allclose(grad, GOLD['vb/%s/chivi2_grad_%d' % (name, call)], rtol=FR_GRAD_RTOL, atol=FR_GRAD_ATOL)
