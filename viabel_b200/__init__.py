@@ -3,7 +3,7 @@
 ``from viabel_b200 import all_bounds, error_bounds, wasserstein_bounds, divergence_bound``
 mirrors ``viabel/__init__.py:1``; ``viabel_b200.vb`` mirrors ``viabel/vb.py``'s kept surface;
 ``viabel_b200.psis`` mirrors ``notebooks/psis.py``; ``viabel_b200.models`` holds the model plugins.
-Importing needs the compiled ``libviabel_b200.so`` (``python -m viabel_b200.build``): there is no
+Importing needs the compiled ``libviabel_b200.so`` (``python viabel_b200/build.py``): there is no
 CPU fallback.
 """
 from .bounds import *          # noqa: F401,F403

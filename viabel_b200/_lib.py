@@ -107,7 +107,7 @@ class ViabelB200Error(RuntimeError):
 def _load():
     if not os.path.exists(LIB_PATH):
         raise ImportError(
-            'viabel_b200: %s not found. Build it with `python -m viabel_b200.build` '
+            'viabel_b200: %s not found. Build it with `python viabel_b200/build.py` '
             '(nvcc, sm_100a). There is no CPU fallback.' % LIB_PATH)
     lib = C.CDLL(LIB_PATH)
     for name, (res, args) in SIGNATURES.items():
