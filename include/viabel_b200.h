@@ -35,7 +35,9 @@ extern "C" {
 
 enum { VB_F32 = 0, VB_F64 = 1 };
 enum { VB_FAMILY_MF_GAUSS = 0, VB_FAMILY_MF_T = 1, VB_FAMILY_FR_T = 2 };
-enum { VB_OBJ_KLVI = 0, VB_OBJ_CHIVI = 1 };
+/* VB_OBJ_KLVI_PD: black_box_klvi_pd / _pd2 (viabel/vb.py:268-296): value -(mean log p - mean log q(x; lambda)) on the
+ * drawn samples instead of the analytic entropy; same gradient as VB_OBJ_KLVI. */
+enum { VB_OBJ_KLVI = 0, VB_OBJ_CHIVI = 1, VB_OBJ_KLVI_PD = 2 };
 enum { VB_MODEL_FUNNEL = 0, VB_MODEL_MIXTURE = 1, VB_MODEL_EIGHT_SCHOOLS = 2,
        VB_MODEL_REGRESSION = 3, VB_MODEL_GAUSS = 4 };
 

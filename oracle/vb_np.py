@@ -13,7 +13,7 @@ from scipy.special import gammaln
 
 __all__ = ['VariationalFamily', 'mean_field_gaussian_variational_family',
            'mean_field_t_variational_family', 't_variational_family',
-           'black_box_klvi', 'black_box_chivi', 'adagrad_optimize',
+           'black_box_klvi', 'black_box_klvi_pd', 'black_box_klvi_pd2', 'black_box_chivi', 'adagrad_optimize',
            'learning_rate_schedule', 'klvi_value_and_grad', 'chivi_value_and_grad']
 
 _Fields = namedtuple('VariationalFamily',                      # vb.py:42-45
@@ -294,6 +294,27 @@ def black_box_klvi(var_family, logdensity, n_samples):
         base = impl.draw_base(impl.rs, n_samples)       # persistent stream, vb.py:239
         return klvi_value_and_grad(impl, logdensity, var_param, base)
     return objective_and_grad
+
+
+def klvi_pd_value_and_grad(impl, model, lam, base):
+    """vb.py:268-278 with the base draw made explicit: value -(mean log p - mean log q(x(lam); lam)); along the
+    reparameterised sample log q depends on lam only through -entropy, so the gradient equals KLVI's."""
+    lam = np.asarray(lam, dtype=float)
+    x = impl.transform(lam, base)
+    lp = model.logp_and_grad(x)[0]
+    return -(np.mean(lp) - np.mean(impl.logq_of_base(lam, base))), klvi_value_and_grad(impl, model, lam, base)[1]
+
+
+def black_box_klvi_pd(var_family, logdensity, n_samples):
+    impl = var_family.impl
+
+    def objective_and_grad(var_param):
+        base = impl.draw_base(impl.rs, n_samples)       # persistent stream, vb.py:271
+        return klvi_pd_value_and_grad(impl, logdensity, var_param, base)
+    return objective_and_grad
+
+
+black_box_klvi_pd2 = black_box_klvi_pd                  # vb.py:281-296: the same function through functools.partial
 
 
 def black_box_chivi(alpha, var_family, logdensity, n_samples):

@@ -51,6 +51,11 @@ def main():
             for call in (1, 2):
                 v, g = obj(lam)
                 out[pre + 'klvi_value_%d' % call], out[pre + 'klvi_grad_%d' % call] = np.float64(v), g
+            for tag, make in (('klvipd', vb.black_box_klvi_pd), ('klvipd2', vb.black_box_klvi_pd2)):
+                obj = make(family(), logp, n)
+                for call in (1, 2):
+                    v, g = obj(lam)
+                    out[pre + '%s_value_%d' % (tag, call)], out[pre + '%s_grad_%d' % (tag, call)] = np.float64(v), g
             # CHIVI: the seed of every call comes from the GLOBAL numpy stream (vb.py:258)
             for alpha in (2.0, 1.5):
                 np.random.seed(123)
@@ -81,6 +86,13 @@ def main():
             for call in (1, 2):
                 v, g = obj(lam)
                 out[pre + 'klvi_value_%d' % call], out[pre + 'klvi_grad_%d' % call] = np.float64(v), g
+            # (black_box_klvi_pd2 passes var_param by keyword, which the full-rank family's flattened logdensity
+            # does not accept in the reference either: only the _pd form exists for this family)
+            for tag, make in (('klvipd', vb.black_box_klvi_pd),):
+                obj = make(vb.t_variational_family(dim, df), logp, n)
+                for call in (1, 2):
+                    v, g = obj(lam)
+                    out[pre + '%s_value_%d' % (tag, call)], out[pre + '%s_grad_%d' % (tag, call)] = np.float64(v), g
             for alpha in (2.0,):
                 np.random.seed(123)
                 obj = vb.black_box_chivi(alpha, vb.t_variational_family(dim, df), logp, n)

@@ -116,3 +116,65 @@ def test_full_rank_golden(name):
         v, grad = obj(lam, base_draws=base)[:2]
         np.testing.assert_allclose(v, g('chivi2_value_%d' % call), rtol=RTOL)
         np.testing.assert_allclose(grad, g('chivi2_grad_%d' % call), rtol=1e-7, atol=1e-8)
+
+
+# ------------------------------------------------------------------------------------------ path-derivative KLVI
+@pytest.mark.parametrize('name', gi.VB_CASES)
+def test_klvi_pd_golden(name):
+    from viabel_b200 import vb
+    kind, dim, df, logp_name, lam, n = gi.vb_case(name)
+    for tag, make in (('klvipd', vb.black_box_klvi_pd), ('klvipd2', vb.black_box_klvi_pd2)):
+        obj = make(family(kind, dim, df), model(logp_name), n, group=False)
+        rs = np.random.RandomState(0)
+        for call in (1, 2):
+            v, grad = obj(lam, base_draws={'eps': reference_draws(rs, kind, df, n, dim)})
+            np.testing.assert_allclose(v, GOLD['vb/%s/%s_value_%d' % (name, tag, call)], rtol=RTOL)
+            np.testing.assert_allclose(grad, GOLD['vb/%s/%s_grad_%d' % (name, tag, call)], rtol=RTOL, atol=1e-12)
+
+
+@pytest.mark.parametrize('name', gi.VB_FR_CASES)
+def test_klvi_pd_full_rank_golden(name):
+    from viabel_b200 import models, vb
+    dim, df, logp_name, lam, n = gi.vb_fr_case(name)
+    obj = vb.black_box_klvi_pd(vb.t_variational_family(dim, df), models.CorrelatedGaussian(gi._FR_MEAN, gi._FR_PREC),
+                               n, group=False)
+    rs = np.random.RandomState(0)
+    for call in (1, 2):
+        v, grad = obj(lam, base_draws=fr_base(rs, df, n, dim))
+        np.testing.assert_allclose(v, GOLD['vb/%s/klvipd_value_%d' % (name, call)], rtol=RTOL)
+        np.testing.assert_allclose(grad, GOLD['vb/%s/klvipd_grad_%d' % (name, call)], rtol=1e-7, atol=1e-8)
+
+
+@pytest.mark.parametrize('n', [1, 257, 5000, 70001])
+def test_klvi_pd_matches_oracle_fused_philox_and_dense(n):
+    """Beyond the golden sizes: fused plugins (external draws and in-kernel Philox, which must equal the KLVI launch
+    on the same stream in its gradient), and the dense regression plugin (vb_model_logp_grad + vb_mf_reduce)."""
+    from oracle import models_np as mm
+    from oracle import vb_np
+    from viabel_b200 import models, vb
+    d = 10
+    lam = np.concatenate([0.3 * np.random.RandomState(1).randn(d), np.full(d, -0.2)])
+    ofam = vb_np.mean_field_t_variational_family(d, 40)
+    base = ofam.impl.draw_base(np.random.RandomState(n), n)
+    v, g = vb.black_box_klvi_pd(vb.mean_field_t_variational_family(d, 40), models.EightSchoolsNCP(), n,
+                                group=False)(lam, base_draws=base)
+    ov, og = vb_np.klvi_pd_value_and_grad(ofam.impl, mm.EightSchoolsNCP(), lam, base)
+    np.testing.assert_allclose(v, ov, rtol=RTOL)
+    np.testing.assert_allclose(g, og, rtol=RTOL, atol=1e-12)
+    # Philox: same stream position for both objectives -> identical draws -> identical gradient
+    v1, g1 = vb.black_box_klvi_pd(vb.mean_field_t_variational_family(d, 40), models.EightSchoolsNCP(), n, group=False)(lam)
+    v2, g2 = vb.black_box_klvi(vb.mean_field_t_variational_family(d, 40), models.EightSchoolsNCP(), n, group=False)(lam)
+    np.testing.assert_allclose(g1, g2, rtol=1e-12, atol=1e-14)
+    assert np.isfinite(v1) and v1 != v2
+    if n <= 5000:
+        rs = np.random.RandomState(5)
+        N, dd = 300, 8
+        X, y = rs.randn(N, dd) / np.sqrt(dd), rs.randn(N)
+        lam8 = np.concatenate([0.1 * rs.randn(dd), np.full(dd, -1.0)])
+        ofam8 = vb_np.mean_field_gaussian_variational_family(dd)
+        base8 = ofam8.impl.draw_base(np.random.RandomState(n), n)
+        v, g = vb.black_box_klvi_pd(vb.mean_field_gaussian_variational_family(dd), models.StudentTRegression(X, y, df=40.0),
+                                    n, group=False)(lam8, base_draws=base8)
+        ov, og = vb_np.klvi_pd_value_and_grad(ofam8.impl, mm.StudentTRegression(X, y, 40.0), lam8, base8)
+        np.testing.assert_allclose(v, ov, rtol=RTOL)
+        np.testing.assert_allclose(g, og, rtol=RTOL, atol=1e-12)

@@ -122,3 +122,29 @@ def test_full_rank_objectives(name):
         v, grad = obj(lam)[:2]
         np.testing.assert_allclose(v, GOLD['vb/%s/chivi2_value_%d' % (name, call)], rtol=1e-11)
         np.testing.assert_allclose(grad, GOLD['vb/%s/chivi2_grad_%d' % (name, call)], rtol=FR_GRAD_RTOL, atol=FR_GRAD_ATOL)
+
+
+# ------------------------------------------------------------------------------------------ path-derivative KLVI
+@pytest.mark.parametrize('name', gi.VB_CASES + gi.VB_FR_CASES)
+def test_klvi_pd_objective_and_grad(name):
+    """black_box_klvi_pd / _pd2 (vb.py:268-296).  The goldens themselves show that the reference's gradient equals
+    KLVI's and that _pd2 is the same function as _pd."""
+    fr = name in gi.VB_FR_CASES
+    if fr:
+        dim, df, logp_name, lam, n = gi.vb_fr_case(name)
+        fam, model = (lambda: vb_np.t_variational_family(dim, df)), fr_model(logp_name)
+    else:
+        kind, dim, df, logp_name, lam, n = gi.vb_case(name)
+        fam, model = (lambda: oracle_family(kind, dim, df)), oracle_model(logp_name)
+    gtol = dict(rtol=FR_GRAD_RTOL, atol=FR_GRAD_ATOL) if fr else dict(rtol=1e-11, atol=1e-13)
+    for tag, make in (('klvipd', vb_np.black_box_klvi_pd), ('klvipd2', vb_np.black_box_klvi_pd2)):
+        if fr and tag == 'klvipd2':
+            continue                       # not callable with the full-rank family in the reference either
+        obj = make(fam(), model, n)
+        for call in (1, 2):
+            v, grad = obj(lam)
+            np.testing.assert_allclose(v, GOLD['vb/%s/%s_value_%d' % (name, tag, call)], rtol=1e-11)
+            np.testing.assert_allclose(grad, GOLD['vb/%s/%s_grad_%d' % (name, tag, call)], **gtol)
+    if not fr:
+        np.testing.assert_array_equal(GOLD['vb/%s/klvipd_grad_1' % name], GOLD['vb/%s/klvi_grad_1' % name])
+        np.testing.assert_array_equal(GOLD['vb/%s/klvipd_grad_1' % name], GOLD['vb/%s/klvipd2_grad_1' % name])

@@ -10,7 +10,7 @@ LIB_PATH = os.path.join(_HERE, 'libviabel_b200.so')
 
 F32, F64 = 0, 1
 FAMILY_MF_GAUSS, FAMILY_MF_T, FAMILY_FR_T = 0, 1, 2
-OBJ_KLVI, OBJ_CHIVI = 0, 1
+OBJ_KLVI, OBJ_CHIVI, OBJ_KLVI_PD = 0, 1, 2
 MODEL_FUNNEL, MODEL_MIXTURE, MODEL_EIGHT_SCHOOLS, MODEL_REGRESSION, MODEL_GAUSS = range(5)
 
 _p, _i, _ll, _d, _sz = C.c_void_p, C.c_int, C.c_longlong, C.c_double, C.c_size_t

@@ -192,7 +192,7 @@ __global__ void mf_reduce_finish_kernel(int family, int objective, double alpha,
     const int NP = 2 * D + 4;
     for (int j = threadIdx.x; j < NP; j += blockDim.x) {
         double v = 0.0;
-        if (j == 0) v = (objective == VB_OBJ_CHIVI) ? *M_ptr : 0.0;
+        if (j == 0) v = (objective != VB_OBJ_KLVI) ? *M_ptr : 0.0;
         else if (j == 1) { for (int b = 0; b < n_wblocks; ++b) v += wblocks[2 * b]; }
         else if (j == 2) { for (int b = 0; b < n_wblocks; ++b) v += wblocks[2 * b + 1]; }
         else if (j == 3) v = (double)n;
@@ -210,7 +210,7 @@ __global__ void mf_reduce_finish_kernel(int family, int objective, double alpha,
         if (j < D) {
             const double sig = exp(var_param[D + j]);
             const double gm = merged_dyn[4 + j], gl = merged_dyn[4 + D + j] * sig;
-            if (objective == VB_OBJ_KLVI) {
+            if (objective == VB_OBJ_KLVI || objective == VB_OBJ_KLVI_PD) {
                 out_grad[j] = -gm / n_total;
                 out_grad[D + j] = -(1.0 + gl / n_total);
             } else {
@@ -224,6 +224,8 @@ __global__ void mf_reduce_finish_kernel(int family, int objective, double alpha,
                 for (int k = 0; k < D; ++k) H += var_param[D + k];
                 if (family == VB_FAMILY_MF_GAUSS) H += 0.5 * D * (1.0 + 1.8378770664093453);
                 *out_value = -(H + merged_dyn[2] / n_total);
+            } else if (objective == VB_OBJ_KLVI_PD) {
+                *out_value = -(merged_dyn[2] / n_total);          // -(mean log p - mean log q), vb.py:268-278
             } else {
                 *out_value = log(merged_dyn[1] / n_total) / alpha + merged_dyn[0];
             }
@@ -270,13 +272,16 @@ static int run_mf_reduce(int family, double df, int objective, double alpha, con
     double* bmax = (double*)(ws + p.off_bmax);
     double* wb = (double*)(ws + p.off_wb);
     double* col = (double*)(ws + p.off_col);
-    if (objective == VB_OBJ_CHIVI) {
+    // path-derivative KLVI = the CHIVI passes with alpha = 0 (unit weights, sum of lw), finalised as KLVI
+    const int pass_obj = (objective == VB_OBJ_KLVI_PD) ? (int)VB_OBJ_CHIVI : objective;
+    const double pass_alpha = (objective == VB_OBJ_KLVI_PD) ? 0.0 : alpha;
+    if (pass_obj == VB_OBJ_CHIVI) {
         mf_rows_kernel<T><<<p.g_rows, 256, 0, st>>>(family, df, var_param, n, D, eps, logp, lw, bmax);
         VB_LAUNCH_CHECK();
         max_finish_kernel<<<1, 256, 0, st>>>(bmax, p.g_rows, M_ptr);
         VB_LAUNCH_CHECK();
     }
-    weights_kernel<<<p.g_w, 256, 0, st>>>(objective, alpha, n, lw, objective == VB_OBJ_CHIVI ? lw : logp, M_ptr,
+    weights_kernel<<<p.g_w, 256, 0, st>>>(pass_obj, pass_alpha, n, lw, pass_obj == VB_OBJ_CHIVI ? lw : logp, M_ptr,
                                          w, wb);
     VB_LAUNCH_CHECK();
     weighted_colsum_kernel<T><<<dim3(p.col_tiles, p.chunks), dim3(32, 8), 0, st>>>(n, D, grad, eps, w,

@@ -95,6 +95,7 @@ struct MfArgs {
     const MfDynStream* dyn;    // or null: Philox (seed, offset) read from device memory (device-resident optimiser)
     const AdagradArgs* opt;    // or null: AdaGrad update applied by the last CTA after the finalise (fused iteration)
     int iters;                 // > 1 (single-CTA Philox launches with opt): optimiser iterations run inside this launch
+    int pd;                    // VB_OBJ_KLVI_PD: the CHIVI pass with alpha = 0 (unit weights, sum of lw), finalised as KLVI
 };
 
 // log q(x(lambda); lambda) = D*c0 - sum(l) + core(eps); this returns core(eps).
@@ -127,7 +128,7 @@ __device__ __forceinline__ void mf_finalize_thread(int family, int objective, do
     if (j < D) {
         const double sig = exp(var_param[D + j]);
         const double gm = part[4 + j], gl = part[4 + D + j] * sig;
-        if (objective == VB_OBJ_KLVI) {
+        if (objective == VB_OBJ_KLVI || objective == VB_OBJ_KLVI_PD) {
             out_grad[j] = -gm / n_total;
             out_grad[D + j] = -(1.0 + gl / n_total);
         } else {
@@ -141,6 +142,10 @@ __device__ __forceinline__ void mf_finalize_thread(int family, int objective, do
             for (int k = 0; k < D; ++k) H += var_param[D + k];
             if (family == VB_FAMILY_MF_GAUSS) H += 0.5 * D * (1.0 + 1.8378770664093453);
             *out_value = -(H + s2 / n_total);
+        } else if (objective == VB_OBJ_KLVI_PD) {
+            // vb.py:268-278: -(mean log p - mean log q(x(lambda); lambda)); s2 = sum of lw in the CHIVI pass.  The
+            // total derivative of log q along the reparameterised sample is that of -entropy, so the gradient is KLVI's.
+            *out_value = -(s2 / n_total);
         } else {
             *out_value = log(sw / n_total) / alpha + M;
         }
@@ -378,7 +383,7 @@ mf_step_kernel(const __grid_constant__ MfArgs<Model> a) {
     }
     __syncthreads();
     if (a.out_value != nullptr && tid < NP)
-        mf_finalize_thread(FAM, OBJ, a.alpha, a.var_param, D, merged, merged[3], a.out_value, a.out_grad, tid);
+        mf_finalize_thread(FAM, a.pd ? (int)VB_OBJ_KLVI_PD : OBJ, a.alpha, a.var_param, D, merged, merged[3], a.out_value, a.out_grad, tid);
     if (a.opt != nullptr) {            // every other CTA has retired its reads of var_param (ticket order)
         __syncthreads();
         adagrad_update_block(*a.opt);
@@ -409,6 +414,7 @@ struct MfCall {
     const MfDynStream* dyn = nullptr;
     const AdagradArgs* opt = nullptr;
     int iters = 1;
+    int pd = 0;
 };
 
 template <typename T, int FAM, class Model, int OBJ, bool PHILOX>
@@ -457,6 +463,7 @@ static int launch_mf(const MfCall& c, const typename Model::P& mp) {
     a.out_grad = c.out_grad;
     a.use_bulk = (c.base != nullptr) && ((reinterpret_cast<uintptr_t>(c.base) & 15u) == 0) &&
                  (c.dyn == nullptr || ((size_t)c.n * D * sizeof(T)) % 16 == 0);
+    a.pd = c.pd;
     a.dyn = c.dyn;
     a.opt = c.opt;
     a.iters = (PHILOX && c.opt != nullptr && grid == 1 && c.iters > 1) ? c.iters : 1;
@@ -474,6 +481,14 @@ static int dispatch_obj(const MfCall& c, const typename Model::P& mp) {
     if (c.objective == VB_OBJ_CHIVI)
         return philox ? launch_mf<T, FAM, Model, VB_OBJ_CHIVI, true>(c, mp)
                       : launch_mf<T, FAM, Model, VB_OBJ_CHIVI, false>(c, mp);
+    if (c.objective == VB_OBJ_KLVI_PD) {       // same kernels as CHIVI: alpha = 0 makes every weight exactly 1
+        MfCall c2 = c;
+        c2.objective = VB_OBJ_CHIVI;
+        c2.alpha = 0.0;
+        c2.pd = 1;
+        return philox ? launch_mf<T, FAM, Model, VB_OBJ_CHIVI, true>(c2, mp)
+                      : launch_mf<T, FAM, Model, VB_OBJ_CHIVI, false>(c2, mp);
+    }
     return VB_ERR_ARG;
 }
 
@@ -582,12 +597,15 @@ __global__ void mf_finalize_kernel(int family, int objective, double alpha, cons
     extern __shared__ double merged_dyn[];
     const int NP = 2 * D + 4;
     double M = 0.0;
-    if (objective == VB_OBJ_CHIVI) {
+    // path-derivative KLVI partials come from the CHIVI pass with alpha = 0: merged like CHIVI (all factors are 1)
+    const int merge_obj = (objective == VB_OBJ_KLVI_PD) ? (int)VB_OBJ_CHIVI : objective;
+    const double merge_alpha = (objective == VB_OBJ_KLVI_PD) ? 0.0 : alpha;
+    if (merge_obj == VB_OBJ_CHIVI) {
         M = -INFINITY;
         for (int r = 0; r < R; ++r) M = fmax(M, parts[(size_t)r * NP]);
     }
     for (int j = threadIdx.x; j < NP; j += blockDim.x)
-        merged_dyn[j] = mf_merge_component(parts, R, NP, objective, alpha, M, j);
+        merged_dyn[j] = mf_merge_component(parts, R, NP, merge_obj, merge_alpha, M, j);
     __syncthreads();
     for (int j = threadIdx.x; j < NP; j += blockDim.x)
         mf_finalize_thread(family, objective, alpha, var_param, D, merged_dyn, merged_dyn[3], out_value, out_grad, j);

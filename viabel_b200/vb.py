@@ -33,6 +33,8 @@ __all__ = [
     'mean_field_t_variational_family',
     't_variational_family',
     'black_box_klvi',
+    'black_box_klvi_pd',
+    'black_box_klvi_pd2',
     'black_box_chivi',
     'adagrad_optimize',
     'rmsprop_IA_optimize_with_rhat',
@@ -418,7 +420,9 @@ class _Objective:
         w = torch.empty(n, dtype=torch.float64, device=vp.device)
         rows = torch.empty(4, dtype=torch.float64, device=vp.device)
         ws = self.ws.get('fr_rows', _lib.lib.vb_fr_rows_workspace_bytes(n))
-        _lib.check(_lib.lib.vb_fr_rows(self.obj, self.alpha, impl.df, impl.code, n, d, ptr(base['z']),
+        # path-derivative KLVI: unit weights like KLVI; its value uses the sum of lw that vb_fr_rows also returns
+        rows_obj = _lib.OBJ_CHIVI if self.obj == _lib.OBJ_CHIVI else _lib.OBJ_KLVI
+        _lib.check(_lib.lib.vb_fr_rows(rows_obj, self.alpha, impl.df, impl.code, n, d, ptr(base['z']),
                                        ptr(base['chi2']), ptr(logp), float(const) - float(entropy),
                                        ptr(lw), ptr(w), ptr(rows), ptr(ws), ws.numel(), stream_ptr()), 'vb_fr_rows')
         if world > 1 and self.obj == _lib.OBJ_CHIVI:
@@ -447,8 +451,9 @@ class _Objective:
         _, _, diag_pos = impl.tri()
         out = torch.empty(1 + self.P, dtype=torch.float64, device=vp.device)
         nt = float(n_total)
-        if self.obj == _lib.OBJ_KLVI:
-            out[0] = -(entropy + rows[2] / nt)
+        if self.obj != _lib.OBJ_CHIVI:
+            # KLVI: analytic entropy (vb.py:240); path-derivative form: -(mean log p - mean log q) (vb.py:272)
+            out[0] = -(entropy + rows[2] / nt) if self.obj == _lib.OBJ_KLVI else -(rows[3] / nt)
             out[1:1 + d] = -g_mu / nt
             phi = -phi / nt
             phi[diag_pos] -= 1.0
@@ -477,7 +482,7 @@ class _Objective:
             n_total = n_local * world if world > 1 else n_local
         else:
             base = None
-            if self.obj == _lib.OBJ_KLVI:
+            if self.obj != _lib.OBJ_CHIVI:
                 seed, off = impl.next_stream(None)
             else:
                 seed, off = int(np.random.randint(2 ** 32)), 0
@@ -508,6 +513,20 @@ def black_box_klvi(var_family, logdensity, n_samples, group=None):
     value ``-(entropy + mean log p)``.  ``group``: torch.distributed group to shard the sample
     axis over (default: the world group when torch.distributed is initialised; ``False``: never)."""
     return _Objective(_lib.OBJ_KLVI, 1.0, var_family, logdensity, n_samples, group)
+
+
+def black_box_klvi_pd(var_family, logdensity, n_samples, group=None):
+    """``vb.py:268-278``: KLVI whose value is ``-(mean log p(x) - mean log q(x; var_param))`` on the drawn samples
+    (a Monte Carlo entropy instead of the analytic one).  Differentiated as the reference does (through the samples
+    AND the explicit parameter) the gradient is KLVI's: along a reparameterised sample ``log q`` depends on the
+    parameter only through ``-entropy``.  One fused launch: the CHIVI pass with unit weights."""
+    return _Objective(_lib.OBJ_KLVI_PD, 1.0, var_family, logdensity, n_samples, group)
+
+
+def black_box_klvi_pd2(var_family, logdensity, n_samples, group=None):
+    """``vb.py:281-296``: the same function as ``black_box_klvi_pd`` written with ``functools.partial``; autograd
+    still traces ``var_param`` through the partial, so value and gradient are identical."""
+    return _Objective(_lib.OBJ_KLVI_PD, 1.0, var_family, logdensity, n_samples, group)
 
 
 def black_box_chivi(alpha, var_family, logdensity, n_samples, group=None):
@@ -565,7 +584,7 @@ def _adagrad_device(n_iters, o, init_param, window, learning_rate, epsilon, lear
         seeds, offsets = np.zeros(n_iters, dtype=np.uint64), np.zeros(n_iters, dtype=np.uint32)
     else:
         base, n_samples = None, o.n
-        if o.obj == _lib.OBJ_KLVI:                      # the family's persistent stream, one call offset per step
+        if o.obj != _lib.OBJ_CHIVI:                     # the family's persistent stream, one call offset per step
             seeds = np.full(n_iters, impl.seed0, dtype=np.uint64)
             offsets = (impl.offset + np.arange(n_iters)).astype(np.uint32)
             impl.offset += n_iters
