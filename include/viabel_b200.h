@@ -166,6 +166,21 @@ int vb_mf_adagrad_create(int family, double df, const vb_model* model, int objec
                          double* d_param_history, void* d_state, size_t state_bytes,
                          void* d_ws, size_t ws_bytes, int graph_iters, int fused, void* stream,
                          vb_adagrad_plan** out_plan);
+/* The fork's RMSProp / Adam update rules (viabel/vb.py:448-462, 616-629) on the same device-resident loop:
+ * rule = VB_OPT_RMSPROP or VB_OPT_ADAM.  d_param_history (n_iters, 2*dim) receives the PRE-update iterate of every
+ * iteration (vb.py:464), d_value_history the objective values; d_bias1 / d_bias2 (Adam) = 1 - beta^(i+2) for
+ * i = 0 .. n_iters-1 with beta1 = 0.9, beta2 = 0.999, made on the host.  d_state: vb_mf_adagrad_state_bytes(dim, 2)
+ * bytes, zero-filled.  Run and destroy with vb_mf_adagrad_run / vb_mf_adagrad_destroy. */
+enum { VB_OPT_ADAGRAD = 0, VB_OPT_RMSPROP = 1, VB_OPT_ADAM = 2 };
+int vb_mf_optimizer_create(int rule, int family, double df, const vb_model* model, int objective,
+                           double alpha, int dtype, double* d_var_param, long long n_samples,
+                           const void* d_base_or_null, int n_iters, double epsilon,
+                           const double* d_rates, const unsigned long long* d_seeds,
+                           const unsigned int* d_offsets, const double* d_bias1_or_null,
+                           const double* d_bias2_or_null, double* d_value_history,
+                           double* d_param_history, void* d_state, size_t state_bytes,
+                           void* d_ws, size_t ws_bytes, int graph_iters, int fused, void* stream,
+                           vb_adagrad_plan** out_plan);
 int vb_mf_adagrad_run(vb_adagrad_plan* plan, int n_steps, void* stream);
 int vb_mf_adagrad_destroy(vb_adagrad_plan* plan);
 

@@ -111,3 +111,47 @@ def test_optimisers_on_the_cuda_objective(rule):
         np.testing.assert_allclose(mine[6][k], theirs[6][k], rtol=1e-9, err_msg=k)
     for a, b in zip(mine[2] + mine[3], theirs[2] + theirs[3]):
         np.testing.assert_allclose(a, b, rtol=1e-12)
+
+
+@pytest.mark.parametrize('objective', ['klvi', 'chivi', 'klvi_pd'])
+@pytest.mark.parametrize('n', [500, 5000])
+@pytest.mark.parametrize('rule', ['rmsprop', 'adam'])
+def test_device_loop_is_bit_identical_to_the_host_loop(rule, n, objective):
+    """vb_mf_optimizer_create: every restart on the device (n = 500: many iterations inside one single-CTA launch;
+    n = 5000: one fused launch per iteration replayed from a CUDA graph) against the reference-shaped host loop over
+    the same CUDA objective -- same Philox streams, same rounding: array_equal on every iterate and value."""
+    from viabel_b200 import models, vb
+
+    def make():
+        fam = vb.mean_field_t_variational_family(10, 40)
+        if objective == 'klvi':
+            return vb.black_box_klvi(fam, models.EightSchoolsNCP(), n)
+        if objective == 'klvi_pd':
+            return vb.black_box_klvi_pd(fam, models.EightSchoolsNCP(), n)
+        return vb.black_box_chivi(2.0, fam, models.EightSchoolsNCP(), n)
+    init = np.concatenate([np.zeros(10), np.full(10, -1.0)])
+    kw = dict(rhat_window=50, tail_avg_iters=100, learning_rate=.03, learning_rate_end=.005, n_optimisers=2, window=2)
+    f = getattr(vb, rule + '_IA_optimize_with_rhat')
+    dev = f(260, make(), init, 10, device_loop=True, **kw)
+    host = f(260, make(), init, 10, device_loop=False, **kw)
+    assert dev[1].shape == host[1].shape == (2, 200, 20)            # history capped at 100 * window
+    np.testing.assert_array_equal(dev[1], host[1])
+    np.testing.assert_array_equal(dev[0], host[0])
+    np.testing.assert_array_equal(dev[4], host[4])
+    for a, b in zip(dev[2] + dev[3], host[2] + host[3]):
+        np.testing.assert_array_equal(a, b)
+    for k in host[6]:
+        np.testing.assert_array_equal(dev[6][k], host[6][k])
+
+
+def test_device_loop_validation():
+    from viabel_b200 import models, vb
+    fam = vb.mean_field_gaussian_variational_family(2)
+    obj = vb.black_box_klvi(fam, models.Funnel(1.35), 100)
+    init = np.array([0., -1., 1., 1.])
+    with pytest.raises(TypeError):
+        vb.rmsprop_IA_optimize_with_rhat(100, obj, init, 2, avg_grad_norm=True, device_loop=True)
+    with pytest.raises(TypeError):
+        vb.adam_IA_optimize_with_rhat(100, gi.NoisyQuadratic(4, 1), init, 2, device_loop=True)
+    with pytest.raises(ValueError):
+        vb.adam_IA_optimize_with_rhat(100, obj, init, 2, learning_rate=-1.0)

@@ -11,6 +11,7 @@ LIB_PATH = os.path.join(_HERE, 'libviabel_b200.so')
 F32, F64 = 0, 1
 FAMILY_MF_GAUSS, FAMILY_MF_T, FAMILY_FR_T = 0, 1, 2
 OBJ_KLVI, OBJ_CHIVI, OBJ_KLVI_PD = 0, 1, 2
+OPT_ADAGRAD, OPT_RMSPROP, OPT_ADAM = 0, 1, 2
 MODEL_FUNNEL, MODEL_MIXTURE, MODEL_EIGHT_SCHOOLS, MODEL_REGRESSION, MODEL_GAUSS = range(5)
 
 _p, _i, _ll, _d, _sz = C.c_void_p, C.c_int, C.c_longlong, C.c_double, C.c_size_t
@@ -38,6 +39,8 @@ SIGNATURES = {
     'vb_mf_adagrad_state_bytes': (_sz, [_i, _i]),
     'vb_mf_adagrad_create': (_i, [_i, _d, _p, _i, _d, _i, _p, _ll, _p, _i, _i, _d, _p, _p, _p, _p, _p, _p, _sz,
                                   _p, _sz, _i, _i, _p, C.POINTER(_p)]),
+    'vb_mf_optimizer_create': (_i, [_i, _i, _d, _p, _i, _d, _i, _p, _ll, _p, _i, _d, _p, _p, _p, _p, _p, _p, _p, _p, _sz,
+                                    _p, _sz, _i, _i, _p, C.POINTER(_p)]),
     'vb_mf_adagrad_run': (_i, [_p, _i, _p]),
     'vb_mf_adagrad_destroy': (_i, [_p]),
     'vb_mf_finalize': (_i, [_i, _i, _d, _p, _i, _p, _i, _p, _p, _p]),

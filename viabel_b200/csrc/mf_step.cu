@@ -40,6 +40,14 @@ struct AdagradArgs {
     double* value_history;      // [n_iters]
     double* param_history;      // [n_iters - keep_from][P]
     MfDynStream* dyn;
+    // update rule: VB_OPT_ADAGRAD (windowed, vb.py:368-376), VB_OPT_RMSPROP (vb.py:448-462), VB_OPT_ADAM
+    // (vb.py:616-629).  The latter two keep their moment vectors in ring[0..P) (second) and ring[P..2P) (first),
+    // record the PRE-update iterate of every iteration (keep_from = 0) and read the bias corrections
+    // 1 - beta^(i+2) from host-made tables so that no pow() is evaluated on the device.
+    int rule = 0;
+    double c0 = 0.0, c1 = 0.0, c2 = 0.0, c3 = 0.0;   // rmsprop: decay, 1-decay; adam: beta1, 1-beta1, beta2, 1-beta2
+    const double* bias1 = nullptr;                   // adam: 1 - beta1^(i+2), [n_iters]
+    const double* bias2 = nullptr;                   // adam: 1 - beta2^(i+2), [n_iters]
 };
 
 // One AdaGrad update by one CTA (vb.py:368-376): called from the last CTA of a fused step launch, or from the
@@ -52,6 +60,36 @@ __device__ __noinline__ void adagrad_update_block(const AdagradArgs& g) {
     const int cnt = (int)min(step + 1u, (unsigned int)W);
     const unsigned int oldest = step + 1u - (unsigned int)cnt;
     const double rate = g.rates[step];
+    if (g.rule != VB_OPT_ADAGRAD) {
+        // every product / sum individually rounded, in the order numpy evaluates the reference's expressions
+        for (int j = threadIdx.x; j < P; j += blockDim.x) {
+            const double gr = g.out[1 + j];
+            const double g2 = __dmul_rn(gr, gr);
+            double stepv;
+            if (g.rule == VB_OPT_RMSPROP) {
+                const double second = (step == 0u) ? g2 : __dadd_rn(__dmul_rn(g.ring[j], g.c0), __dmul_rn(g.c1, g2));
+                g.ring[j] = second;
+                stepv = __ddiv_rn(__dmul_rn(rate, gr), __dsqrt_rn(__dadd_rn(g.epsilon, second)));
+            } else {
+                double second, first;
+                if (step == 0u) {
+                    second = __dmul_rn(0.9, g2);                     // vb.py:617-618
+                    first = __dmul_rn(0.9, gr);
+                } else {
+                    second = __dadd_rn(__dmul_rn(g.ring[j], g.c2), __dmul_rn(g.c3, g2));
+                    first = __dadd_rn(__dmul_rn(g.ring[P + j], g.c0), __dmul_rn(g.c1, gr));
+                }
+                g.ring[j] = second;
+                g.ring[P + j] = first;
+                const double m_hat = __ddiv_rn(first, g.bias1[step]);
+                const double v_hat = __ddiv_rn(second, g.bias2[step]);
+                stepv = __ddiv_rn(__dmul_rn(rate, m_hat), __dsqrt_rn(__dadd_rn(g.epsilon, v_hat)));
+            }
+            const double old = g.var_param[j];
+            g.param_history[(size_t)step * P + j] = old;             // pre-update iterate, vb.py:464
+            g.var_param[j] = __dsub_rn(old, stepv);
+        }
+    } else
     for (int j = threadIdx.x; j < P; j += blockDim.x) {
         const double gr = g.out[1 + j];
         g.ring[(size_t)(step % W) * P + j] = gr;
@@ -740,14 +778,15 @@ extern "C" size_t vb_mf_adagrad_state_bytes(int dim, int window) {
     return adagrad_state_layout(dim, window, &a, &b, &c);
 }
 
-extern "C" int vb_mf_adagrad_create(int family, double df, const vb_model* model, int objective, double alpha,
-                                    int dtype, double* d_var_param, long long n_samples,
-                                    const void* d_base_or_null, int n_iters, int window, double epsilon,
-                                    const double* d_rates, const unsigned long long* d_seeds,
-                                    const unsigned int* d_offsets, double* d_value_history,
-                                    double* d_param_history, void* d_state, size_t state_bytes,
-                                    void* d_ws, size_t ws_bytes, int graph_iters, int fused, void* stream,
-                                    vb_adagrad_plan** out_plan) {
+static int optimizer_plan_create(int rule, const double* d_bias1, const double* d_bias2,
+                                 int family, double df, const vb_model* model, int objective, double alpha,
+                                 int dtype, double* d_var_param, long long n_samples,
+                                 const void* d_base_or_null, int n_iters, int window, double epsilon,
+                                 const double* d_rates, const unsigned long long* d_seeds,
+                                 const unsigned int* d_offsets, double* d_value_history,
+                                 double* d_param_history, void* d_state, size_t state_bytes,
+                                 void* d_ws, size_t ws_bytes, int graph_iters, int fused, void* stream,
+                                 vb_adagrad_plan** out_plan) {
     if (!model || !d_var_param || !d_rates || !d_seeds || !d_offsets || !d_value_history || !d_param_history ||
         !d_state || !d_ws || !out_plan || n_samples < 1 || n_iters < 1 || window < 1 || graph_iters < 0)
         return VB_ERR_ARG;
@@ -771,6 +810,15 @@ extern "C" int vb_mf_adagrad_create(int family, double df, const vb_model* model
     p->upd = AdagradArgs{2 * dim, window, n_iters, 3 * n_iters / 4, epsilon, d_var_param, out,
                          reinterpret_cast<double*>(st + off_ring), d_rates, d_seeds, d_offsets, d_value_history,
                          d_param_history, dyn};
+    if (rule != VB_OPT_ADAGRAD) {
+        p->upd.rule = rule;
+        p->upd.keep_from = 0;
+        p->upd.bias1 = d_bias1;
+        p->upd.bias2 = d_bias2;
+        // the constants as Python evaluates them (1. - 0.9 is not 0.1)
+        if (rule == VB_OPT_RMSPROP) { p->upd.c0 = 0.9; p->upd.c1 = 1.0 - 0.9; }
+        else { p->upd.c0 = 0.9; p->upd.c1 = 1.0 - 0.9; p->upd.c2 = 0.999; p->upd.c3 = 1.0 - 0.999; }
+    }
     p->graph_iters = graph_iters;
     p->fused = fused != 0;
     p->graph = nullptr;
@@ -807,6 +855,38 @@ extern "C" int vb_mf_adagrad_create(int family, double df, const vb_model* model
     }
     *out_plan = p;
     return VB_OK;
+}
+
+extern "C" int vb_mf_adagrad_create(int family, double df, const vb_model* model, int objective, double alpha,
+                                    int dtype, double* d_var_param, long long n_samples,
+                                    const void* d_base_or_null, int n_iters, int window, double epsilon,
+                                    const double* d_rates, const unsigned long long* d_seeds,
+                                    const unsigned int* d_offsets, double* d_value_history,
+                                    double* d_param_history, void* d_state, size_t state_bytes,
+                                    void* d_ws, size_t ws_bytes, int graph_iters, int fused, void* stream,
+                                    vb_adagrad_plan** out_plan) {
+    return optimizer_plan_create(VB_OPT_ADAGRAD, nullptr, nullptr, family, df, model, objective, alpha, dtype,
+                                 d_var_param, n_samples, d_base_or_null, n_iters, window, epsilon, d_rates, d_seeds,
+                                 d_offsets, d_value_history, d_param_history, d_state, state_bytes, d_ws, ws_bytes,
+                                 graph_iters, fused, stream, out_plan);
+}
+
+extern "C" int vb_mf_optimizer_create(int rule, int family, double df, const vb_model* model, int objective,
+                                      double alpha, int dtype, double* d_var_param, long long n_samples,
+                                      const void* d_base_or_null, int n_iters, double epsilon,
+                                      const double* d_rates, const unsigned long long* d_seeds,
+                                      const unsigned int* d_offsets, const double* d_bias1_or_null,
+                                      const double* d_bias2_or_null, double* d_value_history,
+                                      double* d_param_history, void* d_state, size_t state_bytes,
+                                      void* d_ws, size_t ws_bytes, int graph_iters, int fused, void* stream,
+                                      vb_adagrad_plan** out_plan) {
+    if (rule != VB_OPT_RMSPROP && rule != VB_OPT_ADAM) return VB_ERR_ARG;
+    if (rule == VB_OPT_ADAM && (!d_bias1_or_null || !d_bias2_or_null)) return VB_ERR_ARG;
+    // the two moment vectors live where AdaGrad keeps its gradient window: a "window" of 2 rows
+    return optimizer_plan_create(rule, d_bias1_or_null, d_bias2_or_null, family, df, model, objective, alpha, dtype,
+                                 d_var_param, n_samples, d_base_or_null, n_iters, 2, epsilon, d_rates, d_seeds,
+                                 d_offsets, d_value_history, d_param_history, d_state, state_bytes, d_ws, ws_bytes,
+                                 graph_iters, fused, stream, out_plan);
 }
 
 extern "C" int vb_mf_adagrad_run(vb_adagrad_plan* plan, int n_steps, void* stream) {

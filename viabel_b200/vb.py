@@ -704,9 +704,64 @@ def _first_converged_window(rhat_windows, threshold, rhat_window, default):
     return default
 
 
+def _restart_device(rule, n_iters, o, param0, learning_rate, epsilon, learning_rate_end, progress, graph_iters=None):
+    """One restart of the RMSProp / Adam loop on the device (``vb_mf_optimizer_create``): step, finalise and update
+    in one launch per iteration (or many iterations per launch for n <= 2048 samples), moments / iterate / histories
+    in HBM.  Returns (final param, pre-update iterates (n_iters, P), values (n_iters,)), bit-identical to the host
+    loop over the same objective: same Philox streams, every operation of the update individually rounded in
+    numpy's order, bias corrections ``1 - beta**(i + 2)`` tabulated by numpy itself."""
+    impl, d = o.impl, o.impl.dim
+    P = 2 * d
+    rates = np.fromiter(learning_rate_schedule(n_iters, learning_rate, learning_rate_end), dtype=np.float64,
+                        count=n_iters)
+    if o.obj != _lib.OBJ_CHIVI:
+        seeds = np.full(n_iters, impl.seed0, dtype=np.uint64)
+        offsets = (impl.offset + np.arange(n_iters)).astype(np.uint32)
+        impl.offset += n_iters
+    else:
+        seeds = np.array([np.random.randint(2 ** 32) for _ in range(n_iters)], dtype=np.uint64)
+        offsets = np.zeros(n_iters, dtype=np.uint32)
+    if graph_iters is None:
+        graph_iters = 50 if n_iters >= 100 else 0
+    dev = device()
+    steps = np.arange(n_iters)
+    d_bias1 = torch.from_numpy(1 - np.power(0.9, steps + 2)).to(dev)
+    d_bias2 = torch.from_numpy(1 - np.power(0.999, steps + 2)).to(dev)
+    param = torch.from_numpy(np.array(param0, dtype=np.float64, copy=True)).to(dev)
+    d_rates = torch.from_numpy(rates).to(dev)
+    d_seeds = torch.from_numpy(seeds.view(np.int64)).to(dev)
+    d_offsets = torch.from_numpy(offsets.view(np.int32)).to(dev)
+    values = torch.zeros(n_iters, dtype=torch.float64, device=dev)
+    history = torch.zeros((n_iters, P), dtype=torch.float64, device=dev)
+    state = torch.zeros(_lib.lib.vb_mf_adagrad_state_bytes(d, 2), dtype=torch.uint8, device=dev)
+    ws = torch.zeros(_lib.lib.vb_mf_step_workspace_bytes(d), dtype=torch.uint8, device=dev)
+    plan = ctypes.c_void_p()
+    _lib.check(_lib.lib.vb_mf_optimizer_create(
+        _lib.OPT_RMSPROP if rule == 'rmsprop' else _lib.OPT_ADAM, impl.kind, impl.df, o.model.handle, o.obj, o.alpha,
+        impl.code, ptr(param), o.n, 0, n_iters, float(epsilon), ptr(d_rates), ptr(d_seeds), ptr(d_offsets),
+        ptr(d_bias1), ptr(d_bias2), ptr(values), ptr(history), ptr(state), state.numel(), ptr(ws), ws.numel(),
+        int(graph_iters), 1, stream_ptr(), ctypes.byref(plan)), 'vb_mf_optimizer_create')
+    try:
+        group = max(int(graph_iters), 1) * max(1, 500 // max(int(graph_iters), 1))
+        done = 0
+        while done < n_iters:
+            k = min(group, n_iters - done)
+            _lib.check(_lib.lib.vb_mf_adagrad_run(plan, k, stream_ptr()), 'vb_mf_adagrad_run')
+            done += k
+            if progress is not None:
+                i = (done - 1) // 100 * 100
+                progress.update(k)
+                progress.set_description('Average Loss = {:,.6g}'.format(
+                    np.mean(values[max(0, i - 1000):i + 1].cpu().numpy())))
+        return param.cpu().numpy(), history.cpu().numpy(), values.cpu().numpy()
+    finally:
+        torch.cuda.current_stream().synchronize()
+        _lib.lib.vb_mf_adagrad_destroy(plan)
+
+
 def _optimize_with_rhat(rule, n_iters, objective_and_grad, init_param, K, has_log_norm, window, learning_rate,
                         epsilon, rhat_window, n_optimisers, r_mean_threshold, r_sigma_threshold, tail_avg_iters,
-                        avg_grad_norm, learning_rate_end):
+                        avg_grad_norm, learning_rate_end, device_loop=None):
     """Shared body of ``rmsprop_IA_optimize_with_rhat`` (``vb.py:392-548``) and ``adam_IA_optimize_with_rhat``
     (``vb.py:554-712``): n_optimisers restarts of the update rule, the iterate history of every restart, then the
     windowed / halfway split R-hat of that history and the iterate averages from the first converged window on.
@@ -720,11 +775,29 @@ def _optimize_with_rhat(rule, n_iters, objective_and_grad, init_param, K, has_lo
     values, norms, chains = [], [], []
     decay, beta1, beta2 = 0.9, 0.9, 0.999
     spread = 0.5 if rule == 'rmsprop' else 0.2                       # vb.py:425, :592
+    on_device = _device_loop_ok(objective_and_grad, has_log_norm) and not avg_grad_norm
+    if device_loop is None:
+        device_loop = on_device
+    elif device_loop and not on_device:
+        raise TypeError('device_loop=True needs a single-rank fused mean-field objective of viabel_b200.vb, '
+                        'has_log_norm=False and avg_grad_norm=False')
     for o in range(n_optimisers):
         history = []
         np.random.seed(seed=o)                                       # the reference reseeds the GLOBAL numpy stream
         if o >= 1:
             param = init_param + stats.norm.rvs(size=len(init_param)) * (o + 1) * spread
+        if device_loop:
+            learning_rate_schedule(1, learning_rate, learning_rate_end).__next__()   # rate errors before the bar opens
+            with tqdm.trange(n_iters) as progress:
+                try:
+                    param, hist, vals = _restart_device(rule, n_iters, objective_and_grad, param, learning_rate,
+                                                        epsilon, learning_rate_end, progress)
+                finally:
+                    progress.close()
+            values.extend(vals.tolist())
+            norms.extend([0] * n_iters)
+            chains.append(hist[-100 * window:] if n_iters > 100 * window else hist)
+            continue
         with tqdm.trange(n_iters) as progress:
             try:
                 rates = learning_rate_schedule(n_iters, learning_rate, learning_rate_end)
@@ -786,23 +859,27 @@ def rmsprop_IA_optimize_with_rhat(n_iters, objective_and_grad, init_param, K,
                                   has_log_norm=False, window=500, learning_rate=.01,
                                   epsilon=.000001, rhat_window=500, averaging=True, n_optimisers=1,
                                   r_mean_threshold=1.15, r_sigma_threshold=1.20, tail_avg_iters=2000,
-                                  avg_grad_norm=False, learning_rate_end=None):
+                                  avg_grad_norm=False, learning_rate_end=None, device_loop=None):
     """RMSProp with iterate averaging started where the windowed split R-hat says the iterates are stationary
     (``vb.py:392-548``).  ``K`` = number of location parameters (the first K entries of the variational parameter;
     the rest are log scales).  Returns ``(param, history (n_optimisers, kept, P), averaged means per optimiser,
-    averaged log scales per optimiser, value_history, log_norm_history, optimisation_log)``."""
+    averaged log scales per optimiser, value_history, log_norm_history, optimisation_log)``.
+
+    ``device_loop`` (extension, as in ``adagrad_optimize``): ``None`` runs every restart on the device when the
+    objective is a single-rank fused mean-field objective of this package (bit-identical iterates), ``False`` forces
+    the reference's host loop, ``True`` raises if the device loop does not apply."""
     return _optimize_with_rhat('rmsprop', n_iters, objective_and_grad, init_param, K, has_log_norm, window,
                                learning_rate, epsilon, rhat_window, n_optimisers, r_mean_threshold,
-                               r_sigma_threshold, tail_avg_iters, avg_grad_norm, learning_rate_end)
+                               r_sigma_threshold, tail_avg_iters, avg_grad_norm, learning_rate_end, device_loop)
 
 
 def adam_IA_optimize_with_rhat(n_iters, objective_and_grad, init_param, K,
                                has_log_norm=False, window=500, learning_rate=.01,
                                epsilon=.000001, rhat_window=500, averaging=True, n_optimisers=1,
                                r_mean_threshold=1.15, r_sigma_threshold=1.20, tail_avg_iters=2000,
-                               learning_rate_end=None):
+                               learning_rate_end=None, device_loop=None):
     """Adam (bias correction with exponent i + 2, first step seeded with 0.9 g, as ``vb.py:617-629``) with the same
     R-hat-triggered iterate averaging (``vb.py:554-712``); same return tuple as the RMSProp variant."""
     return _optimize_with_rhat('adam', n_iters, objective_and_grad, init_param, K, has_log_norm, window,
                                learning_rate, epsilon, rhat_window, n_optimisers, r_mean_threshold,
-                               r_sigma_threshold, tail_avg_iters, False, learning_rate_end)
+                               r_sigma_threshold, tail_avg_iters, False, learning_rate_end, device_loop)
