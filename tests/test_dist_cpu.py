@@ -32,6 +32,8 @@ def mf_partials(impl, model, objective, alpha, lam, base):
     lp, g = model.logp_and_grad(x)
     eps = base['eps']
     out = np.zeros(2 * d + 4)
+    if objective == 'klvi_pd':                        # VB_OBJ_KLVI_PD: the CHIVI pass with alpha = 0 (unit weights)
+        objective, alpha = 'chivi', 0.0
     if objective == 'klvi':
         w = np.ones(len(lp))
         out[0], out[2] = 0.0, lp.sum()
@@ -50,6 +52,9 @@ def mf_finalize(kind, objective, alpha, lam, parts):
     """numpy restatement of vb_mf_finalize: rescale to the global max, sum in rank order, Appendix A.1."""
     parts = np.asarray(parts)
     d = (parts.shape[1] - 4) // 2
+    pd = objective == 'klvi_pd'
+    if pd:
+        objective, alpha = 'chivi', 0.0
     M = parts[:, 0].max() if objective == 'chivi' else 0.0
     tot = np.zeros(parts.shape[1])
     for p in parts:
@@ -60,6 +65,8 @@ def mf_finalize(kind, objective, alpha, lam, parts):
     n = tot[3]
     sig = np.exp(lam[d:])
     gm, gl = tot[4:4 + d], tot[4 + d:] * sig
+    if pd:                                            # value from the summed log weights, gradient as KLVI
+        return -(tot[2] / n), np.concatenate([-gm / n, -(1 + gl / n)])
     if objective == 'klvi':
         H = lam[d:].sum() + (0.5 * d * (1 + np.log(2 * np.pi)) if kind == 'mf_gauss' else 0.0)
         return -(H + tot[2] / n), np.concatenate([-gm / n, -(1 + gl / n)])
@@ -85,7 +92,7 @@ def _worker(rank, world, port, ret):
         full = fam.impl.draw_base(np.random.RandomState(1), n)          # every rank can regenerate it
         mine = {'eps': full['eps'][start:start + count]}
         results = {}
-        for objective, alpha in (('klvi', 1.0), ('chivi', 2.0)):
+        for objective, alpha in (('klvi', 1.0), ('chivi', 2.0), ('klvi_pd', 1.0)):
             part = torch.from_numpy(mf_partials(fam.impl, model, objective, alpha, lam, mine))
             gathered = all_gather_rows(part, world)        # the product's own exchange helper
             results[objective] = mf_finalize('mf_t', objective, alpha, lam, gathered.numpy())
@@ -99,6 +106,7 @@ def _worker(rank, world, port, ret):
         results['div'] = gathered.numpy().copy()
         if rank == 0:
             ret['klvi'], ret['chivi'], ret['div'] = results['klvi'], results['chivi'], results['div']
+            ret['klvi_pd'] = results['klvi_pd']
             ret['lam'], ret['lw'] = lam, lw
     finally:
         dist.destroy_process_group()
@@ -130,6 +138,9 @@ def test_two_rank_gloo_merge_equals_unsharded():
     v, g = vb_np.chivi_value_and_grad(fam.impl, model, 2.0, lam, base)
     np.testing.assert_allclose(ret['chivi'][0], v, rtol=1e-13)
     np.testing.assert_allclose(ret['chivi'][1], g, rtol=1e-12, atol=1e-14)
+    v, g = vb_np.klvi_pd_value_and_grad(fam.impl, model, lam, base)
+    np.testing.assert_allclose(ret['klvi_pd'][0], v, rtol=1e-13)
+    np.testing.assert_allclose(ret['klvi_pd'][1], g, rtol=1e-12, atol=1e-14)
     # Chan merge of (count, mean, M2) + max-rescaled weight sums reproduce the unsharded statistics
     parts, lw = ret['div'], ret['lw']
     M = parts[:, 0].max()
