@@ -155,3 +155,13 @@ def test_device_loop_validation():
         vb.adam_IA_optimize_with_rhat(100, gi.NoisyQuadratic(4, 1), init, 2, device_loop=True)
     with pytest.raises(ValueError):
         vb.adam_IA_optimize_with_rhat(100, obj, init, 2, learning_rate=-1.0)
+
+
+def test_custom_ops_forward_to_the_same_entry_points(fn):
+    chains, window, interval, start = gi.rhat_window_case('c2_t600_p8')
+    dev = torch.from_numpy(chains).cuda()
+    win = torch.tensor([[i * window, window] for i in range(chains.shape[1] // window)], dtype=torch.int64, device='cuda')
+    vh, rh = torch.ops.viabel_b200.rhat_windows(dev, win)
+    np.testing.assert_array_equal(rh.cpu().numpy(), fn.compute_R_hat_adaptive_numpy(chains, window_size=window))
+    avg = torch.ops.viabel_b200.iterate_average(dev[0], 100)
+    np.testing.assert_array_equal(avg.cpu().numpy(), fn.stochastic_iterate_averaging(chains[0], 100)[0])

@@ -24,6 +24,8 @@ _lib_def.define('psis_smooth_columns(Tensor lw_cols, float reff, bool want_loo) 
 _lib_def.define('mf_adagrad(int family, float df, int model, int objective, float alpha, Tensor init_param, int n, '
                 'Tensor rates, Tensor seeds, Tensor offsets, int window, float epsilon) -> (Tensor, Tensor, Tensor)')
 _lib_def.define('logsumexp(Tensor x) -> Tensor')
+_lib_def.define('rhat_windows(Tensor chains, Tensor windows) -> (Tensor, Tensor)')
+_lib_def.define('iterate_average(Tensor estimate, int start) -> Tensor')
 _lib_def.define('gemm_tf32x3(Tensor a, Tensor b) -> Tensor')
 
 
@@ -130,6 +132,28 @@ def _logsumexp(x):
     return out
 
 
+def _rhat_windows(chains, windows):
+    """(var_hat, R-hat), each (n_windows, K): split R-hat of the iteration windows [(begin, even length)] (int64,
+    (n_windows, 2), on the device) of a contiguous (n_chains, n_iters, K) float64 history (vb_rhat_windows)."""
+    n_chains, n_iters, K = chains.shape
+    nw = windows.shape[0]
+    var_hat = torch.empty((nw, K), dtype=torch.float64, device=chains.device)
+    rhat = torch.empty((nw, K), dtype=torch.float64, device=chains.device)
+    ws = _WS.get('rhat', _lib.lib.vb_rhat_workspace_bytes(n_chains, K, nw))
+    _lib.check(_lib.lib.vb_rhat_windows(ptr(chains), n_chains, n_iters, K, ptr(windows), nw, ptr(var_hat), ptr(rhat),
+                                        ptr(ws), ws.numel(), stream_ptr()), 'vb_rhat_windows')
+    return var_hat, rhat
+
+
+def _iterate_average(estimate, start):
+    """Running mean of estimate[start:] along dim 0 (vb_iterate_average); estimate (N, K) float64, unit column stride."""
+    N, K = estimate.shape
+    out = torch.empty((N - start, K), dtype=torch.float64, device=estimate.device)
+    _lib.check(_lib.lib.vb_iterate_average(ptr(estimate), N, K, estimate.stride(0), start, ptr(out), stream_ptr()),
+               'vb_iterate_average')
+    return out
+
+
 def _gemm_tf32x3(a, b):
     """C (m, n) fp32 = a (m, k) @ b (k, n) with 3xTF32 tcgen05 arithmetic (vb_gemm, dtype f32)."""
     m, k = a.shape
@@ -144,8 +168,9 @@ def _gemm_tf32x3(a, b):
 for _name, _fn in (('mf_step', _mf_step), ('mf_finalize', _mf_finalize), ('model_logp_grad', _model_logp_grad),
                    ('bounds_divergence', _bounds_divergence), ('psis_smooth', _psis_smooth),
                    ('psis_smooth_columns', _psis_smooth_columns), ('mf_adagrad', _mf_adagrad),
-                   ('logsumexp', _logsumexp), ('gemm_tf32x3', _gemm_tf32x3)):
+                   ('logsumexp', _logsumexp), ('gemm_tf32x3', _gemm_tf32x3), ('rhat_windows', _rhat_windows),
+                   ('iterate_average', _iterate_average)):
     _lib_def.impl(_name, _fn, 'CUDA')
 
 OPS = ('mf_step', 'mf_finalize', 'model_logp_grad', 'bounds_divergence', 'psis_smooth', 'psis_smooth_columns',
-       'mf_adagrad', 'logsumexp', 'gemm_tf32x3')
+       'mf_adagrad', 'logsumexp', 'gemm_tf32x3', 'rhat_windows', 'iterate_average')
