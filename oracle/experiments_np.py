@@ -2,8 +2,9 @@
 ``get_samples_and_log_weights`` / ``psis_correction`` / ``improve_with_psis`` of
 ``notebooks/experiments.py:60-89``, on the oracle families of ``oracle/vb_np.py`` with externally
 supplied base draws (the reference draws from the family's RandomState; parity tests hand both
-sides the same draws).  parity unpinned: ``notebooks/experiments.py`` imports ``viabel.vb`` (autograd)
-and matplotlib / seaborn, none of which are installed here."""
+sides the same draws).  PINNED: golden outputs of the reference's own ``notebooks/experiments.py`` run in the build
+container (``tests/golden/experiments_reference.npz``, generator ``scripts/make_golden_experiments.py``; matplotlib /
+seaborn and autograd stood in, see ``scripts/ref_stand_ins.py``), ``tests/test_oracle_experiments_golden.py``."""
 import numpy as np
 
 from . import psis_np

@@ -257,3 +257,16 @@ def vb_fr_case(name):
         rs = np.random.RandomState(61)
         return 3, 9.0, 'gauss3', np.concatenate([0.3 * rs.randn(3), 0.25 * rs.randn(6)]), 40
     raise KeyError(name)
+
+
+# ------------------------------------------------------------------------------------------ notebooks/experiments.py
+EXPERIMENT_CASES = ['gauss_funnel', 't_schools']
+EXPERIMENT_N = 3000
+
+
+def experiment_truth(name):
+    """(true_mean, true_cov) handed to improve_with_psis / check_accuracy (any fixed SPD matrix will do)."""
+    kind, dim, df, logp_name, lam, n = vb_case(name)
+    rs = np.random.RandomState(71)
+    a = rs.randn(dim, dim)
+    return 0.1 * rs.randn(dim), a @ a.T / dim + np.eye(dim)

@@ -178,3 +178,36 @@ def test_klvi_pd_matches_oracle_fused_philox_and_dense(n):
         ov, og = vb_np.klvi_pd_value_and_grad(ofam8.impl, mm.StudentTRegression(X, y, 40.0), lam8, base8)
         np.testing.assert_allclose(v, ov, rtol=RTOL)
         np.testing.assert_allclose(g, og, rtol=RTOL, atol=1e-12)
+
+
+# ------------------------------------------------------------------------------------------ notebooks/experiments.py
+EXP_GOLD = np.load(os.path.join(os.path.dirname(__file__), 'golden', 'experiments_reference.npz'))
+
+
+@pytest.mark.parametrize('name', gi.EXPERIMENT_CASES)
+def test_experiments_helpers_golden(name):
+    """get_samples_and_log_weights / psis_correction / improve_with_psis / check_approx_accuracy on the reference's
+    draws (first call on a fresh family's RandomState(0)) against outputs of the reference's own
+    notebooks/experiments.py."""
+    from viabel_b200 import experiments as ex
+    kind, dim, df, logp_name, lam, _ = gi.vb_case(name)
+    n = gi.EXPERIMENT_N
+    g = lambda k: EXP_GOLD['exp/%s/%s' % (name, k)]      # noqa: E731
+    base = {'eps': reference_draws(np.random.RandomState(0), kind, df, n, dim)}
+    x, lw = ex.get_samples_and_log_weights(model(logp_name), family(kind, dim, df), lam, n, base_draws=base)
+    np.testing.assert_allclose(x[::97], g('samples_probe'), rtol=1e-12)
+    np.testing.assert_allclose(lw, g('log_weights'), rtol=RTOL, atol=1e-11)
+    xt, slw, khat = ex.psis_correction(model(logp_name), family(kind, dim, df), lam, n, base_draws=base)
+    assert xt.shape == (dim, n)
+    np.testing.assert_allclose(slw, g('smoothed_log_weights'), rtol=1e-9, atol=1e-10)
+    np.testing.assert_allclose(khat, g('khat'), rtol=1e-9)
+    tm, tc = gi.experiment_truth(name)
+    res, am, ac = ex.improve_with_psis(model(logp_name), family(kind, dim, df), lam, n, tm, tc, base_draws=base)
+    np.testing.assert_allclose(am, g('approx_mean'), rtol=1e-9, atol=1e-11)
+    np.testing.assert_allclose(ac, g('approx_cov'), rtol=1e-9, atol=1e-11)
+    for k in ('mean_error', 'cov_error_2', 'cov_norm_2', 'cov_error_nuc', 'cov_norm_nuc', 'std_error', 'rel_std_error',
+              'khat'):
+        np.testing.assert_allclose(res[k], g('res/' + k), rtol=1e-8, err_msg=k)
+    res2 = ex.check_approx_accuracy(family(kind, dim, df), lam, tm, tc)
+    for k in ('mean_error', 'cov_error_2', 'cov_error_nuc', 'std_error', 'rel_std_error'):
+        np.testing.assert_allclose(res2[k], g('approx_res/' + k), rtol=1e-10, err_msg=k)

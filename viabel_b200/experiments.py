@@ -14,7 +14,7 @@ from ._device import WS, like_input, ptr, stream_ptr, to_dev, torch_dtype, devic
 from .models import Model
 from .psis import psislw
 
-__all__ = ['get_samples_and_log_weights', 'psis_correction', 'improve_with_psis', 'check_accuracy',
+__all__ = ['get_samples_and_log_weights', 'psis_correction', 'improve_with_psis', 'check_accuracy', 'check_approx_accuracy',
            'weighted_mean_and_cov']
 
 
@@ -54,9 +54,9 @@ def get_samples_and_log_weights(logdensity, var_family, var_param, n_samples, de
     return like_input(x, var_param), like_input(lw, var_param)
 
 
-def psis_correction(logdensity, var_family, var_param, n_samples, device=False):
+def psis_correction(logdensity, var_family, var_param, n_samples, device=False, base_draws=None):
     """``notebooks/experiments.py:66-70``: ``(samples.T, smoothed_log_weights, khat)``."""
-    x, lw = _samples_and_log_weights_device(logdensity, var_family, var_param, n_samples)
+    x, lw = _samples_and_log_weights_device(logdensity, var_family, var_param, n_samples, base_draws)
     slw, khat = psislw(lw)
     if device:
         return x.t(), slw, khat
@@ -107,11 +107,16 @@ def check_accuracy(true_mean, true_cov, approx_mean, approx_cov, verbose=False, 
     return results
 
 
+def check_approx_accuracy(var_family, var_param, true_mean, true_cov, verbose=False, name=None):
+    """``notebooks/experiments.py:51-55``: accuracy of the family's own mean and covariance."""
+    return check_accuracy(true_mean, true_cov, *var_family.mean_and_cov(var_param), verbose, name)
+
+
 def improve_with_psis(logdensity, var_family, var_param, n_samples, true_mean, true_cov, transform=None,
-                      verbose=False):
+                      verbose=False, base_draws=None):
     """``notebooks/experiments.py:73-89``: PSIS-corrected mean / covariance estimates and their errors.
     ``transform`` (if given) is applied to the ``(d, n)`` samples on the host, like the reference does."""
-    x, lw = _samples_and_log_weights_device(logdensity, var_family, var_param, n_samples)
+    x, lw = _samples_and_log_weights_device(logdensity, var_family, var_param, n_samples, base_draws)
     slw, khat = psislw(lw)
     if verbose:
         print('khat = {:.3g}'.format(khat))
