@@ -326,7 +326,9 @@ class C5(Workload):
         return {'bound': 'hbm', 'achieved': ach, 'peak': hbm_gbs, 'unit': 'GB/s', 'frac': ach / hbm_gbs,
                 'traffic': None, 'kernel': 'vb_psis_smooth (all passes: max, prefilter, normalise + tail work)',
                 'ms_per_launch': ms_kernel, 'algorithmic_bytes_per_launch': b,
-                'note': 'this implementation makes 3 reads + 1 write (32 B/weight): frac <= 0.75 by construction'}
+                'note': 'two streaming passes (filter: 1 read; normalise: 1 read + 1 write) = the algorithmic 24 B/weight, '
+                        'measured DRAM traffic 2.95 GB; the exp of the filter pass is instruction-bound (DESIGN 6) and '
+                        '~0.28 ms of small dependent tail kernels sit between the passes'}
 
     def config(self):
         return {'workload': 'c5: psislw + all_bounds on 1.25e8 fp64 log weights per GPU (GPD k=0.5 tail)',
