@@ -2,7 +2,7 @@
 // rmsprop_IA_optimize_with_rhat / adam_IA_optimize_with_rhat, viabel/vb.py:486-522).
 //
 //   vb_rhat_windows      split R-hat of any number of iteration windows of a (n_chains, n_iters, K) fp64 history
-//                        in one pass of two launches: every (window, half-chain, 32-parameter tile) is one CTA
+//                        in one pass of two launches: every (window, half-chain, 32- or 64-parameter tile) is one CTA
 //   vb_iterate_average   running mean of the iterates from `start` on (stochastic_iterate_averaging)
 //
 // Both are streaming reductions over the parameter history (HBM bound when the history is large: C3 keeps
@@ -17,54 +17,79 @@ constexpr int kRhatTX = 32;      // parameters per CTA (one 256-byte row segment
 constexpr int kRhatTY = 8;       // iteration stripes per CTA (256 threads: 8 CTAs per SM overlap their load / reduce phases)
 
 // ws layout: mean[n_windows][2C][K], s2[n_windows][2C][K]
+// VEC = 2: two adjacent parameters per thread through 16-byte loads (K even, 16-byte aligned history): a warp
+// reads 512 contiguous bytes per iteration instead of 256.
+template <int VEC>
 __global__ void __launch_bounds__(kRhatTX * kRhatTY)
 rhat_halfchain_kernel(const double* __restrict__ chains, int n_chains, long long n_iters, long long K,
                       const long long* __restrict__ windows, double* __restrict__ out_mean,
                       double* __restrict__ out_s2) {
-    __shared__ double red[kRhatTY][kRhatTX + 1];
+    __shared__ double red[VEC][kRhatTY][kRhatTX + 1];
     const int tx = threadIdx.x, ty = threadIdx.y;
-    const long long p = (long long)blockIdx.x * kRhatTX + tx;
+    const long long p = ((long long)blockIdx.x * kRhatTX + tx) * VEC;
     const int hc = blockIdx.y;                                  // half-chain 2c + h, as the reference's reshape orders them
     const int w = blockIdx.z;
     const long long begin = windows[2 * w], len = windows[2 * w + 1];
     const long long n = len / 2;                                // iterations per half-chain
     const int c = hc >> 1, h = hc & 1;
     const double* base = chains + ((size_t)c * n_iters + begin + (long long)h * n) * K;
-    const bool live = p < K;
+    const bool live = p < K;                                    // VEC = 2 implies K even: p + 1 < K as well
+    auto load = [&](long long t, double (&v)[VEC]) {
+        if (VEC == 2) {
+            const double2 d2 = *reinterpret_cast<const double2*>(base + (size_t)t * K + p);
+            v[0] = d2.x; v[VEC - 1] = d2.y;
+        } else {
+            v[0] = base[(size_t)t * K + p];
+        }
+    };
     // pass 1: mean
-    double s = 0.0;
-    if (live) {
-#pragma unroll 8
-        for (long long t = ty; t < n; t += kRhatTY) s += base[(size_t)t * K + p];
-    }
-    red[ty][tx] = s;
-    __syncthreads();
-    if (ty == 0) {
-        double a = 0.0;
-#pragma unroll
-        for (int j = 0; j < kRhatTY; ++j) a += red[j][tx];      // fixed order
-        red[0][tx] = a / (double)n;
-    }
-    __syncthreads();
-    const double mean = red[0][tx];
-    __syncthreads();
-    // pass 2: squared deviations about the mean (functions.py:25)
-    double q = 0.0;
+    double s[VEC] = {};
     if (live) {
 #pragma unroll 8
         for (long long t = ty; t < n; t += kRhatTY) {
-            const double d = base[(size_t)t * K + p] - mean;        // second read: L1 / L2 hit (the CTA's own slab)
-            q = fma(d, d, q);
+            double v[VEC];
+            load(t, v);
+#pragma unroll
+            for (int e = 0; e < VEC; ++e) s[e] += v[e];
         }
     }
-    red[ty][tx] = q;
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) red[e][ty][tx] = s[e];
     __syncthreads();
-    if (ty == 0 && live) {
+    if (ty < VEC) {
         double a = 0.0;
 #pragma unroll
-        for (int j = 0; j < kRhatTY; ++j) a += red[j][tx];
-        const size_t o = ((size_t)w * (2 * n_chains) + hc) * K + p;
-        out_mean[o] = mean;
+        for (int j = 0; j < kRhatTY; ++j) a += red[ty][j][tx];  // fixed order
+        red[ty][0][tx] = a / (double)n;
+    }
+    __syncthreads();
+    double mean[VEC];
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) mean[e] = red[e][0][tx];
+    __syncthreads();
+    // pass 2: squared deviations about the mean (functions.py:25); the second read is an L1 / L2 hit
+    double q[VEC] = {};
+    if (live) {
+#pragma unroll 8
+        for (long long t = ty; t < n; t += kRhatTY) {
+            double v[VEC];
+            load(t, v);
+#pragma unroll
+            for (int e = 0; e < VEC; ++e) {
+                const double d = v[e] - mean[e];
+                q[e] = fma(d, d, q[e]);
+            }
+        }
+    }
+#pragma unroll
+    for (int e = 0; e < VEC; ++e) red[e][ty][tx] = q[e];
+    __syncthreads();
+    if (ty < VEC && live) {
+        double a = 0.0;
+#pragma unroll
+        for (int j = 0; j < kRhatTY; ++j) a += red[ty][j][tx];
+        const size_t o = ((size_t)w * (2 * n_chains) + hc) * K + p + ty;
+        out_mean[o] = mean[ty];
         out_s2[o] = a / (double)(n - 1);                        // n = 1: 0/0 = NaN, dropped by the nanmean below
     }
 }
@@ -106,7 +131,18 @@ __global__ void iterate_average_kernel(const double* __restrict__ est, long long
     for (long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x; p < K;
          p += (long long)gridDim.x * blockDim.x) {
         double s = 0.0;
-        for (long long t = start; t < N; ++t) {
+        long long t = start;
+        for (; t + 8 <= N; t += 8) {                 // eight independent loads in flight, the adds stay in order
+            double v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v[u] = est[(size_t)(t + u) * ld + p];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                s += v[u];
+                out[(size_t)(t + u - start) * K + p] = s / (double)(t + u - start + 1);
+            }
+        }
+        for (; t < N; ++t) {
             s += est[(size_t)t * ld + p];
             out[(size_t)(t - start) * K + p] = s / (double)(t - start + 1);
         }
@@ -132,9 +168,15 @@ extern "C" int vb_rhat_windows(const double* d_chains, int n_chains, long long n
     cudaStream_t st = (cudaStream_t)stream;
     double* mean = (double*)(((uintptr_t)d_ws + 255) & ~(uintptr_t)255);
     double* s2 = mean + (size_t)n_windows * 2 * n_chains * n_params;
-    const dim3 grid((unsigned)((n_params + kRhatTX - 1) / kRhatTX), (unsigned)(2 * n_chains), (unsigned)n_windows);
-    rhat_halfchain_kernel<<<grid, dim3(kRhatTX, kRhatTY), 0, st>>>(d_chains, n_chains, n_iters, n_params, d_windows,
-                                                                 mean, s2);
+    const bool vec2 = (n_params % 2 == 0) && ((reinterpret_cast<uintptr_t>(d_chains) & 15u) == 0);
+    const long long per_cta = (long long)kRhatTX * (vec2 ? 2 : 1);
+    const dim3 grid((unsigned)((n_params + per_cta - 1) / per_cta), (unsigned)(2 * n_chains), (unsigned)n_windows);
+    if (vec2)
+        rhat_halfchain_kernel<2><<<grid, dim3(kRhatTX, kRhatTY), 0, st>>>(d_chains, n_chains, n_iters, n_params,
+                                                                        d_windows, mean, s2);
+    else
+        rhat_halfchain_kernel<1><<<grid, dim3(kRhatTX, kRhatTY), 0, st>>>(d_chains, n_chains, n_iters, n_params,
+                                                                        d_windows, mean, s2);
     VB_LAUNCH_CHECK();
     const long long total = (long long)n_windows * n_params;
     long long blocks = (total + 255) / 256;
