@@ -64,6 +64,12 @@ def main():
                     v, g = obj(lam)
                     out[pre + 'chivi%g_value_%d' % (alpha, call)] = np.float64(v)
                     out[pre + 'chivi%g_grad_%d' % (alpha, call)] = g
+        # ---- config C1 end to end on the reference's own streams: family + black_box_klvi + adagrad_optimize
+        init = np.array([0., -1., 1., 1.])                                   # funnel-distribution.ipynb:241-243
+        obj = vb.black_box_klvi(vb.mean_field_gaussian_variational_family(2), gi.funnel_logp, gi.C1_GOLDEN_N)
+        res = vb.adagrad_optimize(gi.C1_GOLDEN_ITERS, obj, init, learning_rate=.01, learning_rate_end=.001)
+        for k, v in zip(['param', 'param_history', 'value_history'], res[:3]):
+            out['vb/c1_adagrad/' + k] = np.asarray(v)
         # ---- full-rank Student-t family: finite-difference gradients (see ref_stand_ins.py)
         set_mode('fd')
         for name in gi.VB_FR_CASES:

@@ -270,3 +270,7 @@ def experiment_truth(name):
     rs = np.random.RandomState(71)
     a = rs.randn(dim, dim)
     return 0.1 * rs.randn(dim), a @ a.T / dim + np.eye(dim)
+
+
+# config C1 (funnel, MF-Gaussian, AdaGrad .01 -> .001) end to end at a size the reference finishes in seconds
+C1_GOLDEN_N, C1_GOLDEN_ITERS = 100, 240

@@ -211,3 +211,20 @@ def test_experiments_helpers_golden(name):
     res2 = ex.check_approx_accuracy(family(kind, dim, df), lam, tm, tc)
     for k in ('mean_error', 'cov_error_2', 'cov_error_nuc', 'std_error', 'rel_std_error'):
         np.testing.assert_allclose(res2[k], g('approx_res/' + k), rtol=1e-10, err_msg=k)
+
+
+@pytest.mark.parametrize('device_loop', [False, True])
+def test_c1_pipeline_end_to_end_golden(device_loop):
+    """Config C1 at a small size against the reference's own run (its family stream, black_box_klvi and
+    adagrad_optimize): the CUDA objective is fed the reference's draws iteration by iteration, through the host loop
+    and through the device-resident loop."""
+    from viabel_b200 import models, vb
+    n, iters = gi.C1_GOLDEN_N, gi.C1_GOLDEN_ITERS
+    rs = np.random.RandomState(0)
+    draws = np.stack([rs.randn(n, 2) for _ in range(iters)])
+    obj = vb.black_box_klvi(vb.mean_field_gaussian_variational_family(2), models.Funnel(1.35), n, group=False)
+    res = vb.adagrad_optimize(iters, obj, np.array([0., -1., 1., 1.]), learning_rate=.01, learning_rate_end=.001,
+                              device_loop=device_loop, base_draws=draws)
+    np.testing.assert_allclose(res[2], GOLD['vb/c1_adagrad/value_history'], rtol=1e-8)
+    np.testing.assert_allclose(res[1], GOLD['vb/c1_adagrad/param_history'], rtol=1e-8, atol=1e-10)
+    np.testing.assert_allclose(res[0], GOLD['vb/c1_adagrad/param'], rtol=1e-8, atol=1e-10)

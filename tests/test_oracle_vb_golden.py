@@ -148,3 +148,14 @@ def test_klvi_pd_objective_and_grad(name):
     if not fr:
         np.testing.assert_array_equal(GOLD['vb/%s/klvipd_grad_1' % name], GOLD['vb/%s/klvi_grad_1' % name])
         np.testing.assert_array_equal(GOLD['vb/%s/klvipd_grad_1' % name], GOLD['vb/%s/klvipd2_grad_1' % name])
+
+
+def test_c1_pipeline_end_to_end():
+    """Config C1 at a small size, entirely in the reference's code (family stream -> KLVI -> AdaGrad with a decaying
+    rate): the oracle follows all 240 iterates."""
+    obj = vb_np.black_box_klvi(vb_np.mean_field_gaussian_variational_family(2), mm.Funnel(1.35), gi.C1_GOLDEN_N)
+    res = vb_np.adagrad_optimize(gi.C1_GOLDEN_ITERS, obj, np.array([0., -1., 1., 1.]), learning_rate=.01,
+                                 learning_rate_end=.001)
+    np.testing.assert_allclose(res[2], GOLD['vb/c1_adagrad/value_history'], rtol=1e-9)
+    np.testing.assert_allclose(res[1], GOLD['vb/c1_adagrad/param_history'], rtol=1e-9, atol=1e-11)
+    np.testing.assert_allclose(res[0], GOLD['vb/c1_adagrad/param'], rtol=1e-9, atol=1e-11)
