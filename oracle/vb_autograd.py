@@ -7,8 +7,8 @@ operation — dense-covariance ``mvn.logpdf`` (vb.py:65), per-coordinate ``t.log
 (vb.py:162), ``sqrtm`` with autograd's Sylvester VJP (vb.py:207), the eigh-based
 ``multivariate_t_logpdf`` (``viabel/_distributions.py:8-38``), paragami's free PSD folding
 (vb.py:185-189) and CHIVI evaluated as forward → weights → VJP (vb.py:257-264).  Its only
-job is to validate the closed-form gradients in ``oracle/vb_np.py``.  **parity unpinned**
-(see ``oracle/__init__.py``).
+job is to validate the closed-form gradients in ``oracle/vb_np.py``, which is itself pinned on
+golden vectors of the reference (see ``oracle/__init__.py``).
 """
 import math
 

@@ -2,9 +2,12 @@
 
 Test infrastructure only.  The reference differentiates with ``autograd``; here every
 gradient is written out analytically and is cross-checked against a
-literal torch-autograd transcription in ``oracle/vb_autograd.py``.  **parity unpinned**:
-the reference has no test or golden vector for this file and cannot be imported here
-(see ``oracle/__init__.py``).  Citations are ``/root/reference/viabel/vb.py:<line>``.
+literal torch-autograd transcription in ``oracle/vb_autograd.py``.  PINNED on golden vectors
+made by running the reference's own ``viabel/vb.py`` in the build container with stand-ins for
+the absent ``autograd`` / ``paragami`` (``tests/golden/vb_reference.npz``,
+``tests/golden/optimizers.npz``; what exactly is pinned, and the one thing that is not --
+paragami's flattening layout -- is stated in ``oracle/__init__.py``).
+Citations are ``/root/reference/viabel/vb.py:<line>``.
 """
 from collections import namedtuple
 

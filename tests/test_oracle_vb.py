@@ -1,7 +1,7 @@
 """The closed-form VI oracle (oracle/vb_np.py) against (a) scipy.stats for the family log
 densities (the arithmetic autograd.scipy wraps), (b) the literal torch-autograd transcription
-of viabel/vb.py (oracle/vb_autograd.py).  The VI path is "parity unpinned" against the real
-reference (autograd/paragami/pystan absent): these tests are what defines it."""
+of viabel/vb.py (oracle/vb_autograd.py).  The pin against the real reference (golden vectors made by running its
+own vb.py here) is tests/test_oracle_vb_golden.py; these tests cover sizes and cases beyond the golden ones."""
 import numpy as np
 import pytest
 from scipy import stats
