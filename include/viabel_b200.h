@@ -32,6 +32,7 @@ extern "C" {
 #define VB_ERR_UNSUPPORTED (-2)
 #define VB_ERR_WORKSPACE   (-3)
 #define VB_ERR_ALIGN       (-4)
+#define VB_ERR_TOO_LARGE   (-5)   /* problem size beyond the stated maximum of a fixed-scratch entry point */
 
 enum { VB_F32 = 0, VB_F64 = 1 };
 enum { VB_FAMILY_MF_GAUSS = 0, VB_FAMILY_MF_T = 1, VB_FAMILY_FR_T = 2 };
@@ -303,6 +304,22 @@ int vb_bounds_divergence_partials(const double* d_lw, long long n, double alpha,
                                   void* stream);
 int vb_bounds_divergence_merge(const double* d_partials, int n_ranks, double alpha,
                                double* d_out, void* stream);
+
+/* vb_bounds_divergence_static: NO COUNTERPART IN THE REFERENCE -- added
+ * for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  Same result as vb_bounds_divergence (same two kernels, same d_out[8]); the scratch
+ * (per-CTA partials, 1184 x 6 doubles = 56 832 bytes) is a file-scope `static __device__` array of the library
+ * instead of a caller workspace, so the call allocates nothing (no cudaMalloc / cudaFree / allocating library
+ * routine) and takes no workspace arguments.  Every GPU that loads the library holds those 56 832 bytes until the
+ * process exits.  Limit: n <= VB_BOUNDS_DIVERGENCE_STATIC_MAX_N (2^31 weights), larger n returns
+ * VB_ERR_TOO_LARGE ("problem larger than the fixed scratch of this entry point allows").  All calls on one
+ * device share the array and it keeps the last call's contents (nothing has to start at zero: each call
+ * overwrites every slot it reads).  Calls that OVERLAP on the GPU (two streams, two host threads) race on it:
+ * serialise them or use vb_bounds_divergence with separate workspaces. */
+#define VB_BOUNDS_DIVERGENCE_STATIC_MAX_N 2147483648LL
+long long vb_bounds_divergence_static_max_n(void);
+int vb_bounds_divergence_static(const double* d_lw, long long n, double alpha, double* d_out,
+                                void* stream);
 
 size_t vb_bounds_moments_workspace_bytes(long long n, int dim);
 int vb_bounds_colsum(int dtype, const void* d_x, long long n, int dim, double* d_out_sum,

@@ -66,6 +66,8 @@ SIGNATURES = {
     'vb_gemm_tf32x3_split': (_i, [_i, _i, _ll, _ll, _ll, _p, _p, _p, _ll, _p]),
     'vb_bounds_divergence_workspace_bytes': (_sz, [_ll]),
     'vb_bounds_divergence': (_i, [_p, _ll, _d, _p, _p, _sz, _p]),
+    'vb_bounds_divergence_static_max_n': (_ll, []),
+    'vb_bounds_divergence_static': (_i, [_p, _ll, _d, _p, _p]),
     'vb_bounds_divergence_partials': (_i, [_p, _ll, _d, _p, _p, _sz, _p]),
     'vb_bounds_divergence_merge': (_i, [_p, _i, _d, _p, _p]),
     'vb_bounds_moments_workspace_bytes': (_sz, [_ll, _i]),

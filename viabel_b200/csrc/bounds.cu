@@ -5,6 +5,7 @@
 //     2nd/4th moments and the scatter matrix in a second pass.
 // HBM-bound: 8 B/weight, 16 d B/sample.  All cross-block merges are in fixed order.
 #include <cstdlib>
+#include <mutex>
 #include "common.cuh"
 #include "gemm_f64.cuh"
 
@@ -356,6 +357,51 @@ extern "C" int vb_bounds_divergence_merge(const double* d_partials, int n_ranks,
                                           double* d_out, void* stream) {
     if (!d_partials || !d_out || n_ranks < 1) return VB_ERR_ARG;
     divergence_merge_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(d_partials, n_ranks, alpha, d_out);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+
+// ------------------------------------------------------------------------------------------ no-allocation variant
+// vb_bounds_divergence with its scratch (the per-CTA partials) in a file-scope device array instead of a caller
+// workspace: for callers that cannot allocate (CUDA graph capture, serving loops).  The array is part of the
+// library image: every GPU that loads the library holds its 56 832 bytes until the process exits.  In host code
+// the symbol below is only a stand-in; its device address is resolved once per device with cudaGetSymbolAddress.
+constexpr int kDivStaticBlocks = kNumSMs * 8;                    // the grid cap of run_divergence
+static __device__ __align__(256) double g_div_static_scratch[kDivStaticBlocks * 6];
+constexpr int kDivStaticMaxDevices = 64;
+static double* g_div_static_ptr[kDivStaticMaxDevices];
+static std::mutex g_div_static_mutex;
+
+static int div_static_scratch(double** out) {
+    int dev = -1;
+    VB_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kDivStaticMaxDevices) return VB_ERR_UNSUPPORTED;
+    std::lock_guard<std::mutex> lock(g_div_static_mutex);
+    if (!g_div_static_ptr[dev]) {
+        void* p = nullptr;
+        VB_CUDA_TRY(cudaGetSymbolAddress(&p, g_div_static_scratch));      // device `dev` is current
+        if (!p) return VB_ERR_UNSUPPORTED;
+        g_div_static_ptr[dev] = (double*)p;
+    }
+    *out = g_div_static_ptr[dev];
+    return VB_OK;
+}
+
+extern "C" long long vb_bounds_divergence_static_max_n(void) { return VB_BOUNDS_DIVERGENCE_STATIC_MAX_N; }
+
+extern "C" int vb_bounds_divergence_static(const double* d_lw, long long n, double alpha, double* d_out, void* stream) {
+    if (!d_lw || !d_out || n < 1 || !(alpha > 0.0)) return VB_ERR_ARG;
+    if (n > VB_BOUNDS_DIVERGENCE_STATIC_MAX_N) return VB_ERR_TOO_LARGE;
+    double* scratch = nullptr;
+    const int rc = div_static_scratch(&scratch);
+    if (rc != VB_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int grid = grid_for((n + 1) / 2, kDivThreads, kDivStaticBlocks);
+    // nothing to clear: the first kernel overwrites all six doubles of each of its `grid` slots and the second
+    // reads exactly those slots; what an earlier call left beyond them is never read
+    divergence_blocks_kernel<0><<<grid, kDivThreads, 0, st>>>(d_lw, n, alpha, scratch);
+    VB_LAUNCH_CHECK();
+    divergence_finish_kernel<<<1, 256, 0, st>>>(d_lw, scratch, grid, alpha, nullptr, d_out);
     VB_LAUNCH_CHECK();
     return VB_OK;
 }
