@@ -68,7 +68,7 @@ class C4(Workload):
         self.torch, self.lib = torch, _lib
         self.fam = vb.mean_field_t_variational_family(self.d, 40)
         self.model = models.EightSchoolsNCP()
-        self.obj = vb.black_box_klvi(self.fam, self.model, self.n * self.world)
+        self.obj = vb.black_box_klvi(self.fam, self.model, self.n * self.world, group=self.world > 1)
         # resident base draws for the streaming (HBM-roofline) mode: this rank's slice of the stream
         start = self.rank * self.n
         self.eps = self.fam.impl.base_draws(self.n, 0, 0, index0=start)['eps']
@@ -599,7 +599,7 @@ class C3(Workload):
         mp, Pp, lam = c3_problem(self.d)
         self.model = models.CorrelatedGaussian(mp, Pp)
         self.fam = vb.t_variational_family(self.d, 40, dtype='f32', scale=self.scale)
-        self.obj = vb.black_box_chivi(2.0, self.fam, self.model, self.n * self.world)
+        self.obj = vb.black_box_chivi(2.0, self.fam, self.model, self.n * self.world, group=self.world > 1)
         self.base = self.fam.impl.base_draws(self.n, 0, 0, index0=self.rank * self.n)
         self.lam_host = lam
         self.lam_dev = torch.from_numpy(lam).cuda()
@@ -717,7 +717,7 @@ class C2(Workload):
         X, y, lam = c2_problem(self.N, self.d)
         self.model = models.StudentTRegression(X, y, df=40.0, dtype='f32')
         self.fam = vb.mean_field_t_variational_family(self.d, 40, dtype=self.compute)
-        self.obj = vb.black_box_klvi(self.fam, self.model, self.n * self.world)
+        self.obj = vb.black_box_klvi(self.fam, self.model, self.n * self.world, group=self.world > 1)
         self.eps = self.fam.impl.base_draws(self.n, 0, 0, index0=self.rank * self.n)['eps']
         self.lam_host = lam
         self.lam_dev = torch.from_numpy(lam).cuda()

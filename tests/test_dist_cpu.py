@@ -80,9 +80,10 @@ def _worker(rank, world, port, ret):
     try:
         from viabel_b200 import vb
         from viabel_b200._device import all_gather_rows
-        r, w, g = vb._dist_info(None)
+        r, w, g = vb._dist_info(True)
         assert (r, w) == (rank, world)
-        assert vb._dist_info(False)[:2] == (0, 1)
+        # sharding is opt-in: an initialised process group alone never splits the sample axis
+        assert vb._dist_info(False)[:2] == (0, 1) and vb._dist_info(None)[:2] == (0, 1)
         n = 1001
         start, count = vb._shard(n, rank, world)
         d = 10
@@ -207,3 +208,69 @@ def test_two_rank_gloo_sharded_psis_equals_unsharded(n):
         np.testing.assert_array_equal(ret[r][2], odet['tailinds'][odet['tail_order']])
         np.testing.assert_allclose(ret[r][1], ok, rtol=1e-10)
     np.testing.assert_allclose(out, oout, rtol=1e-10, atol=1e-10)
+
+
+# ----------------------------------------------------------------------------------------- sharded full-rank CHIVI
+def _fr_worker(rank, world, port, ret):
+    """Each rank: local partials of the full-rank CHIVI step in numpy (what vb_fr_rows / vb_fr_weighted return on
+    the GPU), then the product's own exchange code (viabel_b200.vb.fr_exchange_max / fr_exchange_sums) over gloo."""
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        from viabel_b200 import vb
+        d, n, alpha = 6, 1003, 2.0
+        rs = np.random.RandomState(3)
+        A = rs.randn(d, d)
+        model = mm.CorrelatedGaussian(rs.randn(d), np.linalg.inv(A @ A.T / d + np.eye(d)))
+        fam = vb_np.t_variational_family(d, 9)
+        impl = fam.impl
+        lam = 0.2 * rs.randn(impl.n_param)
+        full = impl.draw_base(np.random.RandomState(4), n)
+        start, count = vb._shard(n, rank, world)
+        mine = {k: v[start:start + count] for k, v in full.items()}
+        x = impl.transform(lam, mine)
+        lp, g = model.logp_and_grad(x)
+        lw = lp - impl.logq_of_base(lam, mine)
+        M = lw.max()
+        w = np.exp(alpha * (lw - M))                       # relative to the LOCAL max, like vb_fr_rows
+        rows = torch.tensor([M, w.sum(), lp.sum(), lw.sum()])
+        w_t, rows = vb.fr_exchange_max(rows, torch.from_numpy(w), alpha, None)
+        wn = w_t.numpy()
+        zt = impl.ztilde(mine)
+        g_mu, G_S = wn @ g, zt.T @ (wn[:, None] * g)      # vb_fr_weighted with the rescaled weights
+        rows, g_mu_t, G_S_t = vb.fr_exchange_sums(rows, torch.from_numpy(g_mu), torch.from_numpy(G_S), world, None)
+        if rank == 0:
+            ret['rows'], ret['g_mu'], ret['G_S'] = rows.numpy(), g_mu_t.numpy(), G_S_t.numpy()
+            ret['lam'], ret['n'] = lam, n
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_gloo_full_rank_chivi_exchange_equals_unsharded():
+    import torch.multiprocessing as mp
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_fr_worker, args=(2, _free_port(), ret), nprocs=2, join=True)
+    d, n, alpha = 6, ret['n'], 2.0
+    rs = np.random.RandomState(3)
+    A = rs.randn(d, d)
+    model = mm.CorrelatedGaussian(rs.randn(d), np.linalg.inv(A @ A.T / d + np.eye(d)))
+    impl = vb_np.t_variational_family(d, 9).impl
+    lam = ret['lam']
+    full = impl.draw_base(np.random.RandomState(4), n)
+    ov, og = vb_np.chivi_value_and_grad(impl, model, alpha, lam, full)
+    rows, g_mu, G_S = ret['rows'], ret['g_mu'], ret['G_S']
+    # finish exactly as _Objective._fr does after the exchange (viabel_b200/vb.py)
+    value = np.log(rows[1] / n) / alpha + rows[0]
+    mu, L, Sigma = impl.fold(lam)
+    S, lamb, V = impl.sqrt_sigma(Sigma)
+    r = np.sqrt(lamb)
+    Y = V @ ((V.T @ G_S @ V) / (r[:, None] + r[None, :])) @ V.T
+    G_L = (Y + Y.T) @ L
+    phi = G_L[impl.tri].copy()
+    phi[impl.diag_pos] *= np.diag(L)
+    phi[impl.diag_pos] += rows[1]
+    grad = np.concatenate([alpha * g_mu / n, alpha * phi / n])
+    np.testing.assert_allclose(value, ov, rtol=1e-12)
+    np.testing.assert_allclose(grad, og, rtol=1e-10, atol=1e-13)

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <math.h>
+#include <atomic>
 #include "../../include/viabel_b200.h"
 #include "log_table.cuh"
 
@@ -24,6 +25,43 @@ constexpr int kNumSMs = 148;       // B200: 2 dies x 74 SMs
 constexpr int kWarp = 32;
 
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// ---------------------------------------------------------------------------- per-device host-side caches
+// cudaFuncSetAttribute and the SM count are PER DEVICE: a process that moves to another GPU after first use must
+// configure the kernels there too.  One bit per device ordinal, set after the configuration succeeded; safe to
+// race (two threads may both configure, which is idempotent).
+constexpr int kMaxDevices = 64;
+static inline int current_device() {
+    int d = -1;
+    return cudaGetDevice(&d) == cudaSuccess ? d : -1;
+}
+struct DeviceOnce {
+    std::atomic<unsigned long long> bits{0};
+    bool pending(int dev) const {
+        return dev < 0 || dev >= kMaxDevices || !((bits.load(std::memory_order_acquire) >> dev) & 1ull);
+    }
+    void done(int dev) {
+        if (dev >= 0 && dev < kMaxDevices) bits.fetch_or(1ull << dev, std::memory_order_release);
+    }
+};
+// largest dynamic shared-memory size configured so far, per device (kernels whose request grows with the problem)
+struct DeviceMaxSize {
+    std::atomic<size_t> v[kMaxDevices];
+    bool covers(int dev, size_t bytes) const { return dev >= 0 && dev < kMaxDevices && v[dev].load(std::memory_order_acquire) >= bytes; }
+    void set(int dev, size_t bytes) { if (dev >= 0 && dev < kMaxDevices) v[dev].store(bytes, std::memory_order_release); }
+};
+static inline int device_sm_count() {
+    static std::atomic<int> cache[kMaxDevices];
+    const int dev = current_device();
+    if (dev >= 0 && dev < kMaxDevices) {
+        const int c = cache[dev].load(std::memory_order_relaxed);
+        if (c > 0) return c;
+    }
+    int v = 0;
+    if (dev < 0 || cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) return kNumSMs;
+    if (dev < kMaxDevices) cache[dev].store(v, std::memory_order_relaxed);
+    return v;
+}
 
 // ---------------------------------------------------------------------------- math traits
 template <typename T> struct Math;

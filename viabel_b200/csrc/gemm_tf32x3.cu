@@ -26,18 +26,7 @@ EncodeTiledFn get_encode_tiled() {
     return fn;
 }
 
-int tf32x3_num_sms() {
-    static int n = 0;
-    if (n == 0) {
-        int dev = 0, v = 0;
-        if (cudaGetDevice(&dev) == cudaSuccess &&
-            cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0)
-            n = v;
-        else
-            n = kNumSMs;
-    }
-    return n;
-}
+int tf32x3_num_sms() { return device_sm_count(); }
 
 int make_split_tmap(CUtensorMap* out, const float* base, long long rows, long long cols, long long ld,
                     long long plane_stride_elems, int box_rows, bool mn_major) {

@@ -473,10 +473,11 @@ static int launch_tf32x3(const SplitMat& A, const SplitMat& B, const GemmShape& 
                : make_split_tmap(&tb, B.base, B.rows, B.cols, B.ld, B.plane_stride, B_MN ? kTBK : kTBN, B_MN);
     if (rc != VB_OK) return rc;
     auto kern = gemm_tf32x3_kernel<A_MN, B_MN, Epi, EW, A_RES, A_RAW, B_RAW>;
-    static bool configured = false;
-    if (!configured) {
+    static DeviceOnce configured;                          // per template instantiation, per device
+    const int dev = current_device();
+    if (configured.pending(dev)) {
         VB_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::kSmemBytes));
-        configured = true;
+        configured.done(dev);
     }
     const long long total = ((shape.M + kTBM - 1) / kTBM) * ((shape.N + kTBN - 1) / kTBN) * shape.splits;
     long long grid = tf32x3_num_sms();

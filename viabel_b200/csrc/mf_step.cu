@@ -430,18 +430,7 @@ mf_step_kernel(const __grid_constant__ MfArgs<Model> a) {
 }
 
 // ------------------------------------------------------------------------------------------ dispatch
-static int g_num_sms_cached = 0;
-static int num_sms() {
-    if (g_num_sms_cached == 0) {
-        int dev = 0, v = 0;
-        if (cudaGetDevice(&dev) == cudaSuccess &&
-            cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0)
-            g_num_sms_cached = v;
-        else
-            g_num_sms_cached = kNumSMs;
-    }
-    return g_num_sms_cached;
-}
+static int num_sms() { return device_sm_count(); }
 
 struct MfCall {
     int family; double df; int objective; double alpha; int dtype;
@@ -461,16 +450,19 @@ static int launch_mf(const MfCall& c, const typename Model::P& mp) {
     constexpr int NP = 2 * D + 4;
     auto kern = mf_step_kernel<T, FAM, Model, OBJ, PHILOX>;
     const size_t smem = PHILOX ? 0 : (size_t)kMfStages * kMfThreads * D * sizeof(T);
-    static bool configured = false;      // per template instantiation
-    static int blocks_per_sm = 1;
-    if (!configured) {
+    static DeviceOnce configured;        // per template instantiation, per device
+    static std::atomic<int> blocks_per_sm_cached{1};
+    const int dev = current_device();
+    int blocks_per_sm = blocks_per_sm_cached.load(std::memory_order_relaxed);
+    if (configured.pending(dev)) {
         VB_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         if (smem > 0)
             VB_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,
                                              (int)cudaSharedmemCarveoutMaxShared));
         VB_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern, kMfThreads, smem));
         if (blocks_per_sm < 1) blocks_per_sm = 1;
-        configured = true;
+        blocks_per_sm_cached.store(blocks_per_sm, std::memory_order_relaxed);      // same on every B200 of the box
+        configured.done(dev);
     }
     const long long n_tiles = (c.n + kMfThreads - 1) / kMfThreads;
     long long grid = (long long)num_sms() * blocks_per_sm;

@@ -118,14 +118,15 @@ static long long pad_pow2(long long count) {
     return p;
 }
 
-static bool g_sort_attr_set = false;
+static DeviceOnce g_sort_attr_set;
 // ascending sort of data[0..n_pad) (n_pad a power of two >= kSortChunk; caller padded the end)
 static int bitonic_sort(Cand* data, long long n_pad, cudaStream_t st) {
     const size_t smem = (size_t)kSortChunk * sizeof(Cand);
-    if (!g_sort_attr_set) {
+    const int dev = current_device();
+    if (g_sort_attr_set.pending(dev)) {
         VB_CUDA_TRY(cudaFuncSetAttribute(bitonic_chunk_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         VB_CUDA_TRY(cudaFuncSetAttribute(bitonic_chunk_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        g_sort_attr_set = true;
+        g_sort_attr_set.done(dev);
     }
     const int chunks = (int)(n_pad / kSortChunk);
     bitonic_chunk_sort_kernel<<<chunks, kSortThreads, smem, st>>>(data);
@@ -926,11 +927,12 @@ extern "C" int vb_psis_filter(const double* d_lw, long long n_local, long long i
     const bool aligned = (reinterpret_cast<uintptr_t>(d_lw) & 15u) == 0;
 #define VB_FILTER_LAUNCH(AL, MX, MB)                                                                              \
     do {                                                                                                          \
-        static bool attr = false;                                                                                 \
-        if (!attr) {                                                                                              \
+        static DeviceOnce attr;                                                                                   \
+        const int dev_ = current_device();                                                                        \
+        if (attr.pending(dev_)) {                                                                                 \
             VB_CUDA_TRY(cudaFuncSetAttribute(filter_kernel<AL, MX, MB>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                              (int)kFSmem));                                                       \
-            attr = true;                                                                                          \
+            attr.done(dev_);                                                                                      \
         }                                                                                                         \
         filter_kernel<AL, MX, MB><<<G, kFThreads, kFSmem, st>>>(d_lw, n_local, index0, d_pivot_x, fo);            \
     } while (0)
@@ -1669,16 +1671,17 @@ extern "C" int vb_psis_smooth_columns(const double* d_lw_cols, double* d_out_col
         return ((sizeof(ColSmem) + 15) & ~(size_t)15) + (size_t)cap * 8 + (size_t)(K1 > 0 ? K1 : 1) * sizeof(double) +
                (size_t)cap * 2;
     };
-    static size_t configured[2] = {0, 0};
+    static DeviceMaxSize configured[2];
+    const int dev = current_device();
     // selection mode when it can pay: the column is longer than the candidate buffer and the expected candidate
     // count (3 (K1 + 1) + 64) fits it with room to spare; d_status (m ints) is required for it
     static const bool no_select = getenv("VB_PSIS_COLUMNS_FULL") != nullptr && atoi(getenv("VB_PSIS_COLUMNS_FULL")) != 0;
     const bool select = !no_select && d_status != nullptr && n > kColSelCap && 3 * (K1 + 1) + 64 <= kColSelCap / 2;
     if (select) {
         const size_t smem = smem_for(kColSelCap);
-        if (smem > configured[1]) {
+        if (!configured[1].covers(dev, smem)) {
             VB_CUDA_TRY(cudaFuncSetAttribute(psis_columns_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            configured[1] = smem;
+            configured[1].set(dev, smem);
         }
         VB_CUDA_TRY(cudaMemsetAsync(d_status, 0, (size_t)m * sizeof(int), st));
         psis_columns_kernel<true><<<(unsigned)m, kColThreads, smem, st>>>(
@@ -1686,9 +1689,9 @@ extern "C" int vb_psis_smooth_columns(const double* d_lw_cols, double* d_out_col
         VB_LAUNCH_CHECK();
     }
     const size_t smem = smem_for(n_pad);
-    if (smem > configured[0]) {
+    if (!configured[0].covers(dev, smem)) {
         VB_CUDA_TRY(cudaFuncSetAttribute(psis_columns_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured[0] = smem;
+        configured[0].set(dev, smem);
     }
     // FULL mode: every column, or (after a selection launch) only the flagged ones -- the other CTAs exit at once
     psis_columns_kernel<false><<<(unsigned)m, kColThreads, smem, st>>>(

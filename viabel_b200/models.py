@@ -36,6 +36,7 @@ class Model:
     def __init__(self):
         self._handle = C.c_void_p()
         self._keep = []        # device tensors the C handle points into
+        self._ws = None        # scratch of logp_and_grad_device: owned by the model, freed with it
 
     def __del__(self):
         h = getattr(self, '_handle', None)
@@ -59,7 +60,10 @@ class Model:
         logp = torch.empty(n, dtype=torch.float64, device=x_dev.device)
         grad = torch.empty_like(x_dev) if want_grad else None
         nbytes = _lib.lib.vb_model_logp_grad_workspace_bytes(self._handle, n, code)
-        ws = WS.get(('model', id(self)), nbytes)
+        if self._ws is None:
+            from ._device import Workspace
+            self._ws = Workspace()
+        ws = self._ws.get('logp_grad', nbytes)
         _lib.check(_lib.lib.vb_model_logp_grad(self._handle, code, ptr(x_dev), n, ptr(logp), ptr(grad),
                                                ptr(ws), ws.numel(), stream_ptr()), 'vb_model_logp_grad')
         return logp, grad

@@ -337,11 +337,12 @@ def _require_plugin(logdensity):
 
 
 def _dist_info(group):
-    """(rank, world) of the sample-sharding group, (0, 1) when not distributed."""
+    """(rank, world, group) of the sample-sharding group; (0, 1, None) when not sharded.  Sharding is opt-in, as in
+    bounds.py and psis.py: ``group=None`` / ``False`` never shards, ``True`` is the world group."""
     import torch.distributed as dist
-    if group is False or not dist.is_available() or not dist.is_initialized():
+    if group is None or group is False or not dist.is_available() or not dist.is_initialized():
         return 0, 1, None
-    g = None if group in (None, True) else group
+    g = None if group is True else group
     return dist.get_rank(g), dist.get_world_size(g), g
 
 
@@ -351,6 +352,30 @@ def _shard(n, rank, world):
     count = base + (1 if rank < rem else 0)
     start = rank * base + min(rank, rem)
     return start, count
+
+
+# --------------------------------------------------------------------------- full-rank multi-rank exchange
+# (CHIVI row).  Device-agnostic torch code: the world-2 gloo test drives these two functions with CPU
+# tensors, the NCCL check (scripts/check_multi_gpu.py) with the real kernels around them.
+def fr_exchange_max(rows, w, alpha, group):
+    """rows = [local max lw, sum w (relative to the local max), sum log p, sum lw]; w (n_local,) relative to the
+    local max.  All-reduce the maximum and rescale to the GLOBAL one: s_i = exp(alpha (lw_i - max)) (vb.py:259-260)."""
+    import torch.distributed as dist
+    gm = rows[0:1].clone()
+    dist.all_reduce(gm, op=dist.ReduceOp.MAX, group=group)
+    scale = torch.exp(alpha * (rows[0] - gm[0]))
+    return w * scale, torch.stack([gm[0], rows[1] * scale, rows[2], rows[3]])
+
+
+def fr_exchange_sums(rows, g_mu, G_S, world, group):
+    """One all-gather of [sum w, sum log p, sum lw, g_mu (d), G_S (d*d)], summed in rank order (deterministic)."""
+    d = g_mu.numel()
+    pack = torch.cat([rows[1:4], g_mu, G_S.reshape(-1)])
+    gathered = all_gather_rows(pack, world, group)
+    tot = gathered[0].clone()
+    for r in range(1, world):
+        tot += gathered[r]
+    return torch.cat([rows[0:1], tot[0:3]]), tot[3:3 + d].contiguous(), tot[3 + d:].reshape(d, d).contiguous()
 
 
 class _Objective:
@@ -426,12 +451,7 @@ class _Objective:
                                        ptr(base['chi2']), ptr(logp), float(const) - float(entropy),
                                        ptr(lw), ptr(w), ptr(rows), ptr(ws), ws.numel(), stream_ptr()), 'vb_fr_rows')
         if world > 1 and self.obj == _lib.OBJ_CHIVI:
-            # weights must be relative to the GLOBAL max: exchange the local maxima first
-            gm = rows[0:1].clone()
-            dist.all_reduce(gm, op=dist.ReduceOp.MAX, group=g)
-            scale = torch.exp(self.alpha * (rows[0] - gm[0]))
-            w = w * scale
-            rows = torch.stack([gm[0], rows[1] * scale, rows[2], rows[3]])
+            w, rows = fr_exchange_max(rows, w, self.alpha, g)
         g_mu = torch.empty(d, dtype=torch.float64, device=vp.device)
         G_S = torch.empty((d, d), dtype=torch.float64, device=vp.device)
         ws2 = self.ws.get('fr_weighted', _lib.lib.vb_fr_weighted_workspace_bytes(n, d))
@@ -439,14 +459,7 @@ class _Objective:
                                            ptr(grad), ptr(g_mu), ptr(G_S), ptr(ws2), ws2.numel(), stream_ptr()),
                    'vb_fr_weighted')
         if world > 1:
-            # one exchange: [sum w, sum logp, sum lw, g_mu (d), G_S (d*d)] gathered and summed in rank order
-            pack = torch.cat([rows[1:4], g_mu, G_S.reshape(-1)])
-            gathered = all_gather_rows(pack, world, g)
-            tot = gathered[0].clone()
-            for r in range(1, world):
-                tot += gathered[r]
-            rows = torch.cat([rows[0:1], tot[0:3]])
-            g_mu, G_S = tot[3:3 + d].contiguous(), tot[3 + d:].reshape(d, d).contiguous()
+            rows, g_mu, G_S = fr_exchange_sums(rows, g_mu, G_S, world, g)
         phi = impl.pack_grad(ch, G_S)
         _, _, diag_pos = impl.tri()
         out = torch.empty(1 + self.P, dtype=torch.float64, device=vp.device)
@@ -511,7 +524,8 @@ class _Objective:
 def black_box_klvi(var_family, logdensity, n_samples, group=None):
     """``vb.py:236-245``.  Returns ``objective_and_grad(var_param) -> (value, grad)`` with
     value ``-(entropy + mean log p)``.  ``group``: torch.distributed group to shard the sample
-    axis over (default: the world group when torch.distributed is initialised; ``False``: never)."""
+    axis over (``True``: the world group; default ``None`` / ``False``: not sharded, every rank runs the whole
+    objective -- the same convention as ``bounds`` and ``psis``)."""
     return _Objective(_lib.OBJ_KLVI, 1.0, var_family, logdensity, n_samples, group)
 
 
