@@ -492,7 +492,13 @@ class _Objective:
             base = impl.coerce_base(base_draws)
             n_local = (base['eps'] if 'eps' in base else base['z']).shape[0]
             seed = off = index0 = 0
-            n_total = n_local * world if world > 1 else n_local
+            n_total = n_local
+            if world > 1:
+                # external shards may be uneven: the global sample count is the sum of the local ones
+                import torch.distributed as dist
+                cnt = torch.tensor([n_local], dtype=torch.int64, device=vp.device)
+                dist.all_reduce(cnt, group=g)
+                n_total = int(cnt.item())
         else:
             base = None
             if self.obj != _lib.OBJ_CHIVI:
