@@ -25,17 +25,91 @@ def _pool_sum(fn, jobs, procs):
         return pool.map(fn, jobs)
 
 
+def blas_threads(n):
+    """Context manager pinning the BLAS / OpenMP pools to n threads (torchrun exports OMP_NUM_THREADS=1, which
+    would silently change the CPU denominator)."""
+    from threadpoolctl import threadpool_limits
+    return threadpool_limits(limits=int(n))
+
+
 class Workload:
     default_steps, default_warmup = 20, 3
     metric, unit, dtype = METRIC, 'samples/s', 'f64'
     h2d_bytes = d2h_bytes = 0
     launches_per_step = 1
+    kernel_launches_per_step = 1   # how often the roofline kernel (the unit kernel_only times) runs in one step
+    # ---- CPU legs (oracle port on the host cores).  A workload states how many of its units one CPU step
+    # processes; the rate is MEASURED on that bounded sample (units / seconds), never scaled from a different shape.
+    cpu_probe_units = 0            # tiny step used to calibrate the sample size
+    cpu_max_units = 0              # the full config (per GPU)
+    cpu_round = 1                  # sample sizes are multiples of this
+    cpu_cores = 1                  # threads the port actually uses
 
     def __init__(self, rank, world, n_gpus):
         self.rank, self.world, self.n_gpus = rank, world, n_gpus
 
     def extra(self):
         return {}
+
+    # subclasses: cpu_prepare() builds host inputs once; cpu_step(units) runs the oracle on `units` units;
+    # cpu_literal_step(units) (optional) the literal torch-autograd transcription; cpu_sample_desc(units) says what ran
+    def cpu_prepare(self):
+        pass
+
+    def cpu_literal_step(self, units):
+        return None
+
+    def _cpu_pick_units(self, n_steps, budget_s):
+        """Sample size so that n_steps CPU steps take about budget_s: calibrated on a small probe step."""
+        self.cpu_prepare()
+        self.cpu_step(self.cpu_probe_units)                      # warm caches / thread pools
+        t0 = time.perf_counter()
+        self.cpu_step(self.cpu_probe_units)
+        per_unit = (time.perf_counter() - t0) / self.cpu_probe_units
+        units = int(budget_s / max(n_steps, 1) / max(per_unit, 1e-12))
+        units = max(self.cpu_probe_units, min(self.cpu_max_units, units // self.cpu_round * self.cpu_round))
+        return units
+
+    def _cpu_time(self, fn, units, k):
+        t0 = time.perf_counter()
+        for _ in range(k):
+            fn(units)
+        return (time.perf_counter() - t0) / k
+
+    def cpu_baseline(self, budget_s=12.0, k=2):
+        """The oracle port timed on this box's host cores on a bounded sample of the same workload."""
+        with blas_threads(self.cpu_cores):
+            units = self._cpu_pick_units(k, budget_s)
+            dt = self._cpu_time(self.cpu_step, units, k)
+        return {'value': units / dt, 'unit': self.unit, 'cores': self.cpu_cores, 'kind': 'port',
+                'sample': self.cpu_sample_desc(units) + '; %d steps of %.2f s' % (k, dt)}
+
+    def reference_arm(self, steps, warmup, budget_s=75.0):
+        """bench.py --impl reference: the oracle port (the reference itself is pure Python and viabel.vb cannot be
+        imported here) on all host threads it can use.  Runs EXACTLY `steps` timed steps after `warmup` untimed ones;
+        each step is a bounded sample of the workload (stated in cpu_baseline.sample) sized by a probe so that the
+        whole run ends within a few minutes.  `value` = units processed / seconds, measured, not extrapolated."""
+        with blas_threads(self.cpu_cores):
+            units = self._cpu_pick_units(steps + warmup, budget_s)
+            for _ in range(warmup):
+                self.cpu_step(units)
+            dt = self._cpu_time(self.cpu_step, units, steps)
+            rate = units / dt
+            arms = {'closed_form': rate}
+            # the literal transcription (forward under a tape + backward, CHIVI forward twice) is what the
+            # reference's autograd does; the FASTER of the two is the denominator (BASELINE.md section 3)
+            lit_units = max(self.cpu_probe_units, min(units, 4 * self.cpu_probe_units))
+            t0 = time.perf_counter()
+            if self.cpu_literal_step(lit_units) is not None:
+                arms['literal_autograd'] = lit_units / (time.perf_counter() - t0)
+        best = max(arms, key=arms.get)
+        cb = {'value': arms[best], 'unit': self.unit, 'cores': self.cpu_cores, 'kind': 'port', 'arm': best,
+              'arms': arms, 'sample': self.cpu_sample_desc(units) + '; %d timed steps of %.2f s after %d warm-up steps'
+              % (steps, dt, warmup)}
+        ms = dt * 1e3 if best == 'closed_form' else units / arms[best] * 1e3
+        return {'metric': self.metric, 'value': arms[best], 'unit': self.unit, 'ms_per_step': ms, 'dtype': 'f64',
+                'config': self.config(), 'units_per_step': units, 'cpu_baseline': cb,
+                'e2e': {'value': arms[best], 'unit': self.unit, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
 
 
 # ======================================================================================= C4
@@ -60,7 +134,6 @@ class C4(Workload):
     n = 1 << 22
     d = 10
     default_steps, default_warmup = 50, 5
-    cpu_sample = 1 << 19
 
     def setup(self):
         import torch
@@ -88,12 +161,14 @@ class C4(Workload):
                       ptr(self._ws), self._ws.numel())
 
     def step_device(self):
-        return self.obj(self.lam_dev, base_draws=self.eps)
+        # the draw is part of the step (vb.py:239 -> :151): Philox + Marsaglia-Tsang inside the fused kernel
+        return self.obj(self.lam_dev)
 
     def step_e2e(self):
-        return self.obj(self.lam_host)            # Philox draws inside the fused kernel, host in / host out
+        return self.obj(self.lam_host)            # same, host var_param in / host (value, grad) out
 
     def kernel_only(self):
+        # roofline instrument: the same kernel in streaming mode (fp64 base draws resident in HBM, read once)
         from viabel_b200._device import stream_ptr
         self.lib.check(self.lib.lib.vb_mf_step(*self._args, stream_ptr()))
 
@@ -106,38 +181,39 @@ class C4(Workload):
 
     def config(self):
         return {'workload': 'c4: eight-schools ncp (d=10), mean-field Student-t(df=40) KLVI, 2^22 samples/step/GPU',
-                'samples_per_step_per_gpu': self.n, 'value_mode': 'streaming: fp64 base draws resident in HBM',
-                'e2e_mode': 'Philox draws fused in-kernel, host var_param in, host (value, grad) out',
-                'l2': 'inputs (335 MB/step) larger than L2 (126 MB)', 'parallelism': 'sample-sharded x%d' % self.world}
+                'samples_per_step_per_gpu': self.n,
+                'value_mode': 'Philox + Marsaglia-Tsang draws fused in-kernel (no HBM input: issue-bound, HBM fraction '
+                              'undefined), device var_param',
+                'e2e_mode': 'same kernel, host var_param in, host (value, grad) out',
+                'roofline_mode': 'streaming instrument: the same kernel fed 335 MB of resident fp64 base draws',
+                'l2': 'streaming inputs (335 MB/launch) larger than L2 (126 MB); Philox mode reads no input', 'parallelism': 'sample-sharded x%d' % self.world}
 
-    def _cpu(self, n, procs):
-        per = max(n // max(procs, 1), 1)
-        jobs = [(1000 + i, per) for i in range(max(procs, 1))]
-        t0 = time.perf_counter()
-        _pool_sum(_c4_cpu_job, jobs, procs)
-        return per * len(jobs) / (time.perf_counter() - t0)
+    # ---- CPU legs: fork pool, one oracle KLVI step shard per process (draws its own standard-t base draws)
+    cpu_probe_units, cpu_max_units, cpu_round = 1 << 15, 1 << 22, 1 << 12
 
-    def cpu_baseline(self):
-        rate = self._cpu(self.cpu_sample, 1)
-        return {'value': rate, 'unit': self.unit, 'cores': 1, 'kind': 'port',
-                'sample': 'oracle vb_np KLVI step incl. standard_t draws on %d samples, 1 process' % self.cpu_sample}
+    @property
+    def cpu_cores(self):
+        return host_cores()
 
-    def reference_arm(self, steps, warmup):
+    def cpu_step(self, units):
         procs = host_cores()
-        n = self.cpu_sample * min(procs, 8)
-        for _ in range(min(warmup, 1)):
-            self._cpu(n, procs)
-        k = max(1, min(steps, 3))
-        t0 = time.perf_counter()
-        for _ in range(k):
-            self._cpu(n, procs)
-        dt = (time.perf_counter() - t0) / k
-        rate = n / dt
-        sample = 'oracle vb_np KLVI step (draws + log p + grad) on %d samples/step, fork pool of %d processes' % (n, procs)
-        return {'metric': self.metric, 'value': rate, 'unit': self.unit, 'ms_per_step': dt * 1e3, 'dtype': 'f64',
-                'config': {'workload': self.config_name()},
-                'cpu_baseline': {'value': rate, 'unit': self.unit, 'cores': procs, 'kind': 'port', 'sample': sample},
-                'e2e': {'value': rate, 'unit': self.unit, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+        per = max(units // procs, 1)
+        with blas_threads(1):
+            _pool_sum(_c4_cpu_job, [(1000 + i, per) for i in range(procs)], procs)
+
+    def cpu_literal_step(self, units):
+        import torch
+        from oracle import vb_autograd as va, vb_np
+        fam = vb_np.mean_field_t_variational_family(10, 40)
+        base = fam.impl.draw_base(np.random.RandomState(1), units)
+        y = [28., 8., -3., 7., -1., 1., 18., 12.]
+        sg = [15., 10., 16., 11., 9., 11., 10., 18.]
+        torch.set_num_threads(host_cores())
+        return va.klvi('mf_t', lambda x: va.eight_schools_logp(x, y, sg), EIGHT_SCHOOLS_LAM, base, 10, 40)
+
+    def cpu_sample_desc(self, units):
+        return ('oracle vb_np KLVI step (standard_t draws + log p + closed-form grad) on %d of the 2^22 samples, '
+                'fork pool of %d processes' % (units, host_cores()))
 
     def config_name(self):
         return 'c4: eight-schools ncp (d=10), mean-field Student-t(df=40) KLVI, 2^22 samples/step/GPU'
@@ -232,7 +308,7 @@ class C1(Workload):
         return ('c1: funnel d=2, mean-field Gaussian KLVI, 1000 samples/iteration, adagrad_optimize '
                 '(%d iterations per bench step)' % C1_ITERS)
 
-    def cpu_baseline(self):
+    def cpu_baseline(self, budget_s=12.0, k=2):
         t0 = time.perf_counter()
         _c1_cpu_job((0, 3000))
         rate = 3000 * self.n / (time.perf_counter() - t0)
@@ -240,8 +316,9 @@ class C1(Workload):
                 'sample': '3000 oracle adagrad_optimize iterations of 1000 samples (randn + funnel log p + '
                           'closed-form grad + windowed update)'}
 
-    def reference_arm(self, steps, warmup):
-        k = max(steps, 2) * C1_ITERS
+    def reference_arm(self, steps, warmup, budget_s=75.0):
+        k = steps * C1_ITERS                                    # exactly `steps` bench steps of 500 iterations
+        _c1_cpu_job((0, max(warmup, 1) * 50))
         t0 = time.perf_counter()
         _c1_cpu_job((0, k))
         dt = time.perf_counter() - t0
@@ -249,7 +326,7 @@ class C1(Workload):
         cb = {'value': rate, 'unit': self.unit, 'cores': 1, 'kind': 'port',
               'sample': '%d sequential oracle adagrad_optimize iterations (the optimiser loop is sequential: 1 process)' % k}
         return {'metric': self.metric, 'value': rate, 'unit': self.unit, 'ms_per_step': dt / k * C1_ITERS * 1e3,
-                'dtype': 'f64', 'config': {'workload': self.config_name()}, 'cpu_baseline': cb,
+                'dtype': 'f64', 'config': self.config(), 'cpu_baseline': cb,
                 'e2e': {'value': rate, 'unit': self.unit, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
 
 
@@ -266,7 +343,6 @@ class C5(Workload):
     n = 125_000_000
     unit = 'weights/s'
     default_steps, default_warmup = 5, 3
-    cpu_sample = 10_000_000
 
     def setup(self):
         import torch
@@ -337,34 +413,29 @@ class C5(Workload):
 
     config_name = lambda self: self.config()['workload']      # noqa: E731
 
-    def _cpu(self, n):
+    # ---- CPU legs: the reference algorithm is one argsort + numpy ufunc passes, single-threaded
+    cpu_probe_units, cpu_max_units, cpu_round, cpu_cores = 1_000_000, 125_000_000, 1_000_000, 1
+
+    def cpu_prepare(self):
+        if getattr(self, '_cpu_lw', None) is None:
+            self._cpu_lw = c5_log_weights_host(40_000_000)      # 0.3 GB; a step uses a prefix of it
+
+    def cpu_step(self, units):
         import warnings
         from oracle import bounds_np, psis_np
-        lw = c5_log_weights_host(n)
-        t0 = time.perf_counter()
+        units = min(units, self._cpu_lw.size)
+        lw = self._cpu_lw[:units]
         with warnings.catch_warnings():
             warnings.simplefilter('ignore')
             psis_np.psislw(lw)
             bounds_np.all_bounds(lw, moment_bound_fn=lambda p: 3.0 if p == 2 else 27.0, q_var=1.0)
-        return n / (time.perf_counter() - t0)
 
-    def cpu_baseline(self):
-        rate = self._cpu(self.cpu_sample)
-        return {'value': rate, 'unit': self.unit, 'cores': 1, 'kind': 'port',
-                'sample': 'oracle psislw + all_bounds on %d weights (np.argsort is single-threaded)' % self.cpu_sample}
+    def _cpu_pick_units(self, n_steps, budget_s):
+        return min(Workload._cpu_pick_units(self, n_steps, budget_s), 40_000_000)
 
-    def reference_arm(self, steps, warmup):
-        k = max(1, min(steps, 2))
-        t0 = time.perf_counter()
-        rates = [self._cpu(self.cpu_sample) for _ in range(k)]
-        dt = (time.perf_counter() - t0) / k
-        rate = float(np.mean(rates))
-        cb = {'value': rate, 'unit': self.unit, 'cores': 1, 'kind': 'port',
-              'sample': 'oracle psislw + all_bounds on %d weights per step; the reference algorithm is one '
-                        'argsort + numpy ufunc passes, single-threaded' % self.cpu_sample}
-        return {'metric': self.metric, 'value': rate, 'unit': self.unit, 'ms_per_step': dt * 1e3, 'dtype': 'f64',
-                'config': {'workload': self.config_name()}, 'cpu_baseline': cb,
-                'e2e': {'value': rate, 'unit': self.unit, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+    def cpu_sample_desc(self, units):
+        return ('oracle psislw + all_bounds (restatement of notebooks/psis.py + viabel/bounds.py: full argsort + numpy '
+                'passes, single-threaded as numpy is) on %d of the 1.25e8 weights per GPU' % units)
 
 
 # ======================================================================================= N3
@@ -588,7 +659,6 @@ class C3(Workload):
     n, d = 1 << 16, 512
     dtype = 'f32 storage, 3xTF32 tensor-core products, fp64 accumulation of reductions'
     default_steps, default_warmup = 10, 3
-    cpu_sample = 1 << 13
     scale = 'sqrtm'
 
     def setup(self):
@@ -649,36 +719,39 @@ class C3(Workload):
     def config_name(self):
         return 'c3: CHIVI alpha=2, full-rank Student-t(df=40) d=512, correlated-Gaussian target, 2^16 samples/step/GPU'
 
-    def _cpu(self, n):
-        from oracle import models_np, vb_np
-        mp, Pp, lam = c3_problem(self.d)
-        fam = vb_np.t_variational_family(self.d, 40, scale=self.scale)
-        model = models_np.CorrelatedGaussian(mp, Pp)
-        t0 = time.perf_counter()
-        base = fam.impl.draw_base(np.random.RandomState(1), n)
+    # ---- CPU legs: closed-form oracle CHIVI step (numpy + multithreaded BLAS), O(d^3) chain included once per step
+    cpu_probe_units, cpu_max_units, cpu_round = 1 << 11, 1 << 16, 1 << 10
+
+    @property
+    def cpu_cores(self):
+        return host_cores()
+
+    def cpu_prepare(self):
+        if getattr(self, '_cpu_in', None) is None:
+            from oracle import models_np, vb_np
+            mp, Pp, lam = c3_problem(self.d)
+            fam = vb_np.t_variational_family(self.d, 40, scale=self.scale)
+            self._cpu_in = (fam, models_np.CorrelatedGaussian(mp, Pp), lam, mp, Pp)
+
+    def cpu_step(self, units):
+        from oracle import vb_np
+        fam, model, lam, _, _ = self._cpu_in
+        base = fam.impl.draw_base(np.random.RandomState(1), units)      # the draw is part of the step (vb.py:204-206)
         vb_np.chivi_value_and_grad(fam.impl, model, 2.0, lam, base)
-        return n / (time.perf_counter() - t0)
 
-    def cpu_baseline(self):
-        rate = self._cpu(self.cpu_sample)
-        return {'value': rate, 'unit': self.unit, 'cores': host_cores(), 'kind': 'port',
-                'sample': 'oracle closed-form CHIVI step on %d samples (numpy + multithreaded BLAS; includes the '
-                          'O(d^3) eigh/sqrtm chain once)' % self.cpu_sample}
+    def cpu_literal_step(self, units):
+        if self.scale != 'sqrtm':
+            return None
+        import torch
+        from oracle import vb_autograd as va
+        fam, _, lam, mp, Pp = self._cpu_in
+        base = fam.impl.draw_base(np.random.RandomState(1), units)
+        torch.set_num_threads(host_cores())
+        return va.chivi('fr_t', lambda x: va.gauss_logp(x, mp, Pp), 2.0, lam, base, self.d, 40)
 
-    def reference_arm(self, steps, warmup):
-        n = self.cpu_sample * 2
-        self._cpu(1 << 10)
-        k = max(1, min(steps, 3))
-        t0 = time.perf_counter()
-        for _ in range(k):
-            self._cpu(n)
-        dt = (time.perf_counter() - t0) / k
-        rate = n / dt
-        cb = {'value': rate, 'unit': self.unit, 'cores': host_cores(), 'kind': 'port',
-              'sample': 'oracle closed-form CHIVI step on %d samples/step, numpy with BLAS threads on all cores' % n}
-        return {'metric': self.metric, 'value': rate, 'unit': self.unit, 'ms_per_step': dt * 1e3, 'dtype': 'f64',
-                'config': {'workload': self.config_name()}, 'cpu_baseline': cb,
-                'e2e': {'value': rate, 'unit': self.unit, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+    def cpu_sample_desc(self, units):
+        return ('oracle closed-form CHIVI step (chi2 + normal draws, z S, log p + grad, weighted outer product, eigh / '
+                'Sylvester chain) on %d of the 2^16 samples, numpy with %d BLAS threads' % (units, host_cores()))
 
 
 class C3Chol(C3):
@@ -708,7 +781,6 @@ class C2(Workload):
     dtype = 'f32 storage, 3xTF32 tensor-core products, fp64 accumulation across row chunks'
     compute = 'f32'
     default_steps, default_warmup = 5, 3
-    cpu_rows = 1 << 16
 
     def setup(self):
         import torch
@@ -763,37 +835,39 @@ class C2(Workload):
     def config_name(self):
         return 'c2: Student-t regression N=2^20 rows d=128, KLVI mean-field Student-t(df=40), 4096 samples/step/GPU'
 
-    def _cpu(self, rows):
-        """Full 4096 samples over a bounded number of design-matrix rows; samples/s scaled to N rows."""
-        from oracle import models_np, vb_np
-        X, y, lam = c2_problem(rows, self.d)
-        model = models_np.StudentTRegression(X.astype(np.float64), y.astype(np.float64), 40.0, row_block=1 << 12)
-        fam = vb_np.mean_field_t_variational_family(self.d, 40)
-        base = fam.impl.draw_base(np.random.RandomState(1), self.n)
-        t0 = time.perf_counter()
+    # ---- CPU legs: closed-form oracle KLVI step on a bounded number of the 4096 MC samples over ALL 2^20 rows, so
+    # that samples/s is measured directly (the per-sample cost 4 N d flop does not depend on the batch)
+    cpu_probe_units, cpu_max_units, cpu_round = 16, 4096, 16
+
+    @property
+    def cpu_cores(self):
+        return host_cores()
+
+    def cpu_prepare(self):
+        if getattr(self, '_cpu_in', None) is None:
+            from oracle import models_np, vb_np
+            X, y, lam = c2_problem(self.N, self.d)
+            model = models_np.StudentTRegression(X.astype(np.float64), y.astype(np.float64), 40.0, row_block=1 << 13)
+            self._cpu_in = (vb_np.mean_field_t_variational_family(self.d, 40), model, lam)
+
+    def cpu_step(self, units):
+        from oracle import vb_np
+        fam, model, lam = self._cpu_in
+        base = fam.impl.draw_base(np.random.RandomState(1), units)
         vb_np.klvi_value_and_grad(fam.impl, model, lam, base)
-        dt = time.perf_counter() - t0
-        return self.n / (dt * self.N / rows)
 
-    def cpu_baseline(self):
-        rate = self._cpu(self.cpu_rows)
-        return {'value': rate, 'unit': self.unit, 'cores': host_cores(), 'kind': 'port',
-                'sample': 'oracle KLVI step, 4096 samples x %d of the 2^20 rows (time scaled x%d); numpy + BLAS threads'
-                          % (self.cpu_rows, self.N // self.cpu_rows)}
+    def cpu_literal_step(self, units):
+        import torch
+        from oracle import vb_autograd as va
+        fam, model, lam = self._cpu_in
+        base = fam.impl.draw_base(np.random.RandomState(1), units)
+        torch.set_num_threads(host_cores())
+        Xt, yt = torch.from_numpy(model.X), torch.from_numpy(model.y)
+        return va.klvi('mf_t', lambda b: va.regression_logp(b, Xt, yt, 40.0), lam, base, self.d, 40)
 
-    def reference_arm(self, steps, warmup):
-        self._cpu(1 << 12)
-        k = max(1, min(steps, 2))
-        t0 = time.perf_counter()
-        rates = [self._cpu(self.cpu_rows) for _ in range(k)]
-        dt = (time.perf_counter() - t0) / k
-        rate = float(np.mean(rates))
-        cb = {'value': rate, 'unit': self.unit, 'cores': host_cores(), 'kind': 'port',
-              'sample': 'oracle KLVI step, 4096 samples x %d of 2^20 rows per step (time scaled x%d), BLAS on all cores'
-                        % (self.cpu_rows, self.N // self.cpu_rows)}
-        return {'metric': self.metric, 'value': rate, 'unit': self.unit, 'ms_per_step': dt * 1e3, 'dtype': 'f64',
-                'config': {'workload': self.config_name()}, 'cpu_baseline': cb,
-                'e2e': {'value': rate, 'unit': self.unit, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+    def cpu_sample_desc(self, units):
+        return ('oracle closed-form KLVI step on %d of the 4096 MC samples x all 2^20 rows (standard_t draws, X b, psi, '
+                "X' psi in fp64), numpy with %d BLAS threads" % (units, host_cores()))
 
 
 class C2F64(C2):
