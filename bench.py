@@ -244,8 +244,6 @@ def run_workload(wl_cls, args, steps, warmup, rank, world, local_rank, want_cpu,
         }
         if stages is not None:
             out['stage_times_ms_per_step'] = stages
-        if want_cpu:
-            out['cpu_baseline'] = wl.cpu_baseline(budget_s=args.cpu_budget)
         out.update(wl.extra())
     del wl
     torch.cuda.empty_cache()
@@ -312,6 +310,13 @@ def main():
         sub = run_workload(cls, args, k, w, rank, world, local_rank, want_cpu, args.stage_times)
         if sub is not None:
             subs[name] = sub
+    if rank == 0 and head is not None and want_cpu:
+        # CPU baselines AFTER every GPU timing: their thread pools / fork pools would otherwise perturb the
+        # host-synchronising steps (c5) of the workloads timed after them
+        head['cpu_baseline'] = wl_cls(rank=0, world=1, n_gpus=args.gpus).cpu_baseline(budget_s=args.cpu_budget)
+        for name in subs:
+            subs[name]['cpu_baseline'] = W.WORKLOADS[name](rank=0, world=1, n_gpus=args.gpus).cpu_baseline(
+                budget_s=args.cpu_budget / 2)
     if rank == 0 and head is not None:
         line = {'metric': W.METRIC, 'value': head.pop('value'), 'unit': head.pop('unit'), 'n_gpus': world,
                 'steps': steps, 'warmup': warmup, 'ms_per_step': head.pop('ms_per_step'), 'higher_is_better': True,
