@@ -72,6 +72,16 @@ int  vb_model_create_regression(const void* d_X, const void* d_y, long long n_ro
  * model, so that the fp32 / 3xTF32 path (vb_model_logp_grad, dtype VB_F32) does not re-split X on every call
  * and its workspace shrinks by that amount.  NULL detaches.  fp32 data only. */
 int  vb_model_regression_attach_split(vb_model* model, const float* d_X_planes);
+/* Fused regression kernel (one persistent tcgen05 launch, "fp16 x 3" arithmetic: every fp32 operand as an fp16
+ * (hi, lo) pair after an exact power-of-two scaling, fp32 accumulation; same 22 significant bits as 3xTF32).
+ * vb_split_f16 writes the scaled planes of a (rows, cols) fp32 matrix plus a 256-byte header (the scale) into
+ * vb_split_f16_bytes(rows, cols) bytes (256-byte aligned, must outlive the model); a regression model of
+ * dim <= 128 with such planes attached evaluates vb_model_logp_grad(dtype f32) through the fused kernel.
+ * Replaces the per-sample Stan log_prob / grad_log_prob loop of viabel/vb.py:301-321. */
+size_t vb_split_f16_bytes(long long rows, long long cols);
+int  vb_split_f16(const float* d_src, long long rows, long long cols, long long ld, void* d_dst_planes,
+                  void* stream);
+int  vb_model_regression_attach_split_f16(vb_model* model, const void* d_X_planes16);
 /* d_mean (dim) and d_precision (dim, dim) symmetric, float64. */
 int  vb_model_create_gauss(const double* d_mean, const double* d_precision, int dim,
                            vb_model** out);

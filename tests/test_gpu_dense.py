@@ -97,6 +97,7 @@ def test_regression_tensor_path_raw_operand_variants(raw, monkeypatch):
     (converter warps; GEMM1 bit 0, GEMM2 bit 1).  Same stated tolerance as the default pre-split path."""
     from viabel_b200 import models
     monkeypatch.setenv('VB_REG_RAW', raw)
+    monkeypatch.setenv('VB_REG_PATH', '1')          # the two-GEMM 3xTF32 pipeline (the fused fp16x3 kernel is the default)
     N, d, n = 5000, 64, 200
     X, y, bt = _regression(N, d)
     X32, y32 = X.astype(np.float32), y.astype(np.float32)

@@ -27,6 +27,9 @@ SIGNATURES = {
     'vb_model_create_eight_schools': (_i, [C.POINTER(_d), C.POINTER(_d), _i, C.POINTER(_p)]),
     'vb_model_create_regression': (_i, [_p, _p, _ll, _i, _d, _d, _i, C.POINTER(_p)]),
     'vb_model_regression_attach_split': (_i, [_p, _p]),
+    'vb_split_f16_bytes': (_sz, [_ll, _ll]),
+    'vb_split_f16': (_i, [_p, _ll, _ll, _ll, _p, _p]),
+    'vb_model_regression_attach_split_f16': (_i, [_p, _p]),
     'vb_model_create_gauss': (_i, [_p, _p, _i, C.POINTER(_p)]),
     'vb_model_kind': (_i, [_p]),
     'vb_model_dim': (_i, [_p]),

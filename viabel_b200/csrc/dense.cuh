@@ -30,4 +30,10 @@ size_t regression_tf32_workspace_bytes(long long n, long long n_rows, int dim, b
 int regression_logp_grad_tf32(const ModelHost* m, const float* b, long long n, double* out_logp,
                               float* out_grad_or_null, void* ws, size_t ws_bytes, cudaStream_t st);
 
+// Fused fp16x3 kernel (reg_fused.cu): needs the scaled fp16 planes of X attached to the model and dim <= 128
+bool regression_fused_ok(const ModelHost* m);
+size_t regression_fused_workspace_bytes(long long n, long long n_rows);
+int regression_logp_grad_fused(const ModelHost* m, const float* b, long long n, double* out_logp,
+                               float* out_grad_or_null, void* ws, size_t ws_bytes, cudaStream_t st);
+
 }  // namespace vb

@@ -60,6 +60,21 @@ int make_raw_tmap(CUtensorMap* out, const float* base, long long rows, long long
     return r == CUDA_SUCCESS ? VB_OK : VB_ERR_ARG;
 }
 
+int make_f16_planes_tmap(CUtensorMap* out, const void* base, long long rows, long long cols, long long ld,
+                         long long plane_stride_elems, int box_rows) {
+    EncodeTiledFn enc = get_encode_tiled();
+    if (!enc) return VB_ERR_UNSUPPORTED;
+    if ((reinterpret_cast<uintptr_t>(base) & 15u) || (ld % 8) || (plane_stride_elems % 8)) return VB_ERR_ALIGN;
+    const cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)rows, 2};
+    const cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)plane_stride_elems * 2};
+    const cuuint32_t box[3] = {64, (cuuint32_t)box_rows, 2};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                           CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? VB_OK : VB_ERR_ARG;
+}
+
 // ------------------------------------------------------------------------------------------ operand splitting
 // src (rows, cols) with leading dimension lds -> dst planes (rows, ldd): hi at dst, lo at dst + plane
 __global__ void split_kernel(const float* __restrict__ src, long long rows, long long cols, long long lds,

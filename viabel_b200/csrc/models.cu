@@ -242,6 +242,16 @@ extern "C" int vb_model_create_regression(const void* d_X, const void* d_y, long
     if (rc) return rc;
     m->d_X = d_X; m->d_y = d_y; m->n_rows = n_rows; m->df = df; m->prior_sd = prior_sd; m->data_dtype = dtype;
     m->d_X_planes = nullptr;
+    m->d_X_planes16 = nullptr;
+    return VB_OK;
+}
+
+extern "C" int vb_model_regression_attach_split_f16(vb_model* model, const void* d_X_planes16) {
+    if (!model) return VB_ERR_ARG;
+    ModelHost* m = reinterpret_cast<ModelHost*>(model);
+    if (m->kind != VB_MODEL_REGRESSION || m->data_dtype != VB_F32) return VB_ERR_UNSUPPORTED;
+    if (reinterpret_cast<uintptr_t>(d_X_planes16) & 255u) return VB_ERR_ALIGN;
+    m->d_X_planes16 = d_X_planes16;
     return VB_OK;
 }
 
@@ -270,6 +280,8 @@ extern "C" size_t vb_model_logp_grad_workspace_bytes(const vb_model* model, long
     if (!model || n < 1) return 0;
     const ModelHost* m = reinterpret_cast<const ModelHost*>(model);
     if (m->kind == VB_MODEL_REGRESSION) {
+        if (dtype == VB_F32 && m->data_dtype == VB_F32 && regression_fused_ok(m))
+            return regression_fused_workspace_bytes(n, m->n_rows);
         if (dtype == VB_F32 && m->data_dtype == VB_F32)
             return regression_tf32_workspace_bytes(n, m->n_rows, m->dim, m->d_X_planes != nullptr);
         const long long chunk = regression_chunk_rows(n, m->n_rows);
@@ -324,6 +336,9 @@ extern "C" int vb_model_logp_grad(const vb_model* model, int dtype, const void* 
         case VB_MODEL_REGRESSION: {
             const size_t need = vb_model_logp_grad_workspace_bytes(model, n, dtype);
             if (!d_ws || ws_bytes < need) return VB_ERR_WORKSPACE;
+            if (dtype == VB_F32 && m->data_dtype == VB_F32 && regression_fused_ok(m))
+                return regression_logp_grad_fused(m, (const float*)d_x, n, d_out_logp, (float*)d_out_grad_or_null,
+                                                  d_ws, ws_bytes, st);
             if (dtype == VB_F32 && m->data_dtype == VB_F32)
                 return regression_logp_grad_tf32(m, (const float*)d_x, n, d_out_logp, (float*)d_out_grad_or_null,
                                                  d_ws, ws_bytes, st);

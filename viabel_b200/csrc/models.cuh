@@ -25,6 +25,7 @@ struct ModelHost {
     double prior_sd;
     int data_dtype;
     const float* d_X_planes;   // or null: tf32 hi/lo planes of X made once by vb_split_f32 (vb_model_regression_attach_split)
+    const void* d_X_planes16;  // or null: scaled fp16 hi/lo planes + header made once by vb_split_f16 (..._attach_split_f16)
     // gauss
     const double* d_mean;
     const double* d_prec;

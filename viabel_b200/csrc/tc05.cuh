@@ -174,6 +174,64 @@ __device__ __forceinline__ void mma_commit(uint64_t* bar) {
                  :: "r"(smem_u32(bar)) : "memory");
 }
 
+// ---------------------------------------------------------------------------- kind::f16 (fp16 operands, fp32 accumulate)
+// Instruction descriptor: bits 4-5 D format (1 = F32) | 7-9 A format (0 = F16) | 10-12 B format (0 = F16)
+//   bit 15 A major (1 = MN) | bit 16 B major (1 = MN) | 17-22 N >> 3 | 24-28 M >> 4.   UMMA_K = 16.
+__host__ __device__ constexpr uint32_t idesc_f16(int M, int N, bool a_mn_major, bool b_mn_major) {
+    return (1u << 4) | ((a_mn_major ? 1u : 0u) << 15) | ((b_mn_major ? 1u : 0u) << 16) |
+           ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+// A from tensor memory (lane = row; a 32-bit column holds TWO consecutive K elements, low half first), B from
+// shared memory; warp-collective form (all 32 lanes converged, one elected lane issues)
+__device__ __forceinline__ void mma_f16_ts_warp(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                                bool accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p, e;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "elect.sync _|e, 0xffffffff;\n"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n"
+        "}\n"
+        :: "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"((uint32_t)accumulate) : "memory");
+}
+// 32 lanes x 16 columns of 32-bit, registers -> TMEM
+__device__ __forceinline__ void tmem_st_32x16(uint32_t taddr, const uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+        :: "r"(taddr),
+           "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+           "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+        : "memory");
+}
+// TMEM -> registers without the wait (issue several loads, then tmem_ld_wait once)
+__device__ __forceinline__ void tmem_ld_32x32_nowait(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// two fp32 -> packed f16x2 (round to nearest even); `lo16` lands in the low half
+__device__ __forceinline__ uint32_t pack_f16x2(float lo16, float hi16) {
+    uint32_t r;
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi16), "f"(lo16));
+    return r;
+}
+// fp16 hi / lo split of a pair: hi = x rounded to 11 significant bits (integer add + mask: exact in fp16 when
+// normal), lo = x - hi (exact in fp32), both packed as f16x2.  22 significant bits in total, like tf32 hi / lo.
+__device__ __forceinline__ void split_f16_pair(float a, float b, uint32_t& hi2, uint32_t& lo2) {
+    const float ah = __uint_as_float((__float_as_uint(a) + 0x1000u) & 0xffffe000u);
+    const float bh = __uint_as_float((__float_as_uint(b) + 0x1000u) & 0xffffe000u);
+    hi2 = pack_f16x2(ah, bh);
+    lo2 = pack_f16x2(a - ah, b - bh);
+}
+
 // round-to-nearest fp32 -> tf32 (low 13 mantissa bits cleared)
 __device__ __forceinline__ float to_tf32(float x) {
     uint32_t r;
@@ -213,5 +271,9 @@ int make_split_tmap(CUtensorMap* out, const float* base, long long rows, long lo
 // the same map stores (32 x box_rows) tiles staged in shared memory.
 int make_raw_tmap(CUtensorMap* out, const float* base, long long rows, long long cols, long long ld, int box_rows,
                   bool atom32 = false);
+// fp16 hi / lo planes of a (rows, cols) matrix, leading dimension ld (elements, multiple of 8), plane 1 following
+// plane 0 at plane_stride elements: 3-D map (cols, rows, 2), box (64, box_rows, 2), 128-byte swizzle.
+int make_f16_planes_tmap(CUtensorMap* out, const void* base, long long rows, long long cols, long long ld,
+                         long long plane_stride_elems, int box_rows);
 
 }  // namespace vb

@@ -144,6 +144,13 @@ class StudentTRegression(Model):
             _lib.check(_lib.lib.vb_split_f32(ptr(Xd), N, d, d, ptr(planes), stream_ptr()), 'vb_split_f32')
             _lib.check(_lib.lib.vb_model_regression_attach_split(self._handle, ptr(planes)), 'attach_split')
             self._keep.append(planes)
+        if code == _lib.F32 and Xd.shape[1] <= 128:
+            # fused kernel: X as scaled fp16 (hi, lo) planes, made once (model data)
+            N, d = Xd.shape
+            p16 = torch.empty(_lib.lib.vb_split_f16_bytes(N, d), dtype=torch.uint8, device=Xd.device)
+            _lib.check(_lib.lib.vb_split_f16(ptr(Xd), N, d, d, ptr(p16), stream_ptr()), 'vb_split_f16')
+            _lib.check(_lib.lib.vb_model_regression_attach_split_f16(self._handle, ptr(p16)), 'attach_split_f16')
+            self._keep.append(p16)
 
 
 class CorrelatedGaussian(Model):
