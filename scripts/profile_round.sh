@@ -10,7 +10,7 @@ WLS=${@:-"c4 c5 c3 c2"}
 OUT=gpurun_out/$TAG
 mkdir -p $OUT
 declare -A KREGEX=( [c4]="mf_step_kernel" [c1]="mf_step_kernel" [c5]="filter_kernel|normalise_kernel|divergence_blocks"
-                    [c3]="gemm_tf32x3_kernel" [c3chol]="gemm_tf32x3_kernel" [c2]="gemm_tf32x3_kernel" [n3]="psis_columns_kernel" [n4r]="rhat_halfchain_kernel" )
+                    [c3]="gemm_tf32x3_kernel" [c3chol]="gemm_tf32x3_kernel" [c2]="reg_fused_kernel" [n3]="psis_columns_kernel" [n4r]="rhat_halfchain_kernel" )
 for w in $WLS; do
   echo "== $w: launch list"
   python bench.py --workload $w --profile-step --steps 2 --warmup 3 > $OUT/plain_step_$w.log 2>&1 &&

@@ -31,8 +31,12 @@ constexpr int kFD = 128;                 // max dimension (K of GEMM1, N of GEMM
 constexpr int kFStages = 5;              // X ring depth
 constexpr uint32_t kFXBytes = 2u * 2u * kFR * 64 * 2;         // [col block 2][plane 2][64 rows][64 halves] = 32 KB
 constexpr uint32_t kFStageBytes = kFXBytes + 256;             // + the tile's 64 y values
-constexpr int kFThreads = 384;           // warp 0 TMA, warp 1 MMA, warps 2-3 idle, warps 4-11 epilogue
-constexpr int kFEpiThreads = 256;
+constexpr int kFEW = 16;                 // epilogue warps: warp (q, h) = TMEM lane quarter q, columns 16 h .. 16 h + 15
+constexpr int kFThreads = 128 + 32 * kFEW;                    // warp 0 TMA, warp 1 MMA, warps 2-3 idle, then the epilogue
+constexpr int kFEpiThreads = 32 * kFEW;
+constexpr int kFG = kFEW / 4;            // column groups per lane quarter
+constexpr int kFC = kFR / kFG;           // columns of a row tile per epilogue thread (16)
+static_assert(kFC == 16 && kFD / kFG == 32, "epilogue register tiling assumes 16 epilogue warps");
 // tensor-memory columns
 constexpr uint32_t kTG = 0, kTAcc = 128, kTBhi = 256, kTBlo = 320, kTPsi = 384;
 constexpr size_t kFSmemBytes = (size_t)kFStages * kFStageBytes + 512 + 1024;
@@ -112,42 +116,43 @@ __device__ __forceinline__ float2 log_ge1_x2f(float2 p) {
 __device__ __noinline__ float log1p_sum4_slow_f(float r0, float r1, float r2, float r3, float inv_df) {
     return (log1pf(r0 * r0 * inv_df) + log1pf(r1 * r1 * inv_df)) + (log1pf(r2 * r2 * inv_df) + log1pf(r3 * r3 * inv_df));
 }
-// eight residuals: accumulates sum log(1 + r^2/df) (one packed log per eight: two products of four) and returns
-// psi / c * psi_scale as four fp16 (hi, lo) register pairs
-__device__ __forceinline__ void psi_oct(const float* acc, const float* yv, float neg_inv_ab, float inv_df, float psi_scale,
-                                        float2& lsum, uint32_t* hi2, uint32_t* lo2) {
-    const float2 nia = make_float2(neg_inv_ab, neg_inv_ab), one = make_float2(1.f, 1.f), idf = make_float2(inv_df, inv_df);
+// eight residuals, everything in register PAIRS (packed fp32x2 arithmetic needs aligned pairs; unpaired operands cost
+// a move each): acc = tensor-memory accumulator pairs, ys = psi_scale * y pairs.
+//   r' = psi_scale r = fma(acc, c1, ys),  c1 = -psi_scale / (draw scale * X scale)
+//   u  = 1 + r^2/df = fma(r' r', idf, 1), idf = 1 / (df psi_scale^2)
+//   sum log u: one packed log per eight (two products of four);   psi' = psi_scale psi / c = r' / u -> fp16 (hi, lo)
+__device__ __forceinline__ void psi_oct(const float2 (&acc)[4], const float2 (&ys)[4], float c1, float idf, float inv_df,
+                                        float inv_ps, float2& lsum, uint32_t* hi2, uint32_t* lo2) {
+    const float2 c1v = make_float2(c1, c1), one = make_float2(1.f, 1.f), idfv = make_float2(idf, idf);
     float2 r[4], u[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        r[i] = __ffma2_rn(make_float2(acc[2 * i], acc[2 * i + 1]), nia, make_float2(yv[2 * i], yv[2 * i + 1]));
-        u[i] = __ffma2_rn(__fmul2_rn(r[i], r[i]), idf, one);
+        r[i] = __ffma2_rn(acc[i], c1v, ys[i]);
+        u[i] = __ffma2_rn(__fmul2_rn(r[i], r[i]), idfv, one);
     }
     const float2 pa = __fmul2_rn(u[0], u[1]), pb = __fmul2_rn(u[2], u[3]);
-    const float2 p = __fmul2_rn(make_float2(pa.x, pb.x), make_float2(pa.y, pb.y));
+    const float2 p = __fmul2_rn(pa, pb);                       // (u0 u2 u4 u6, u1 u3 u5 u7): the pairing is irrelevant
     if (p.x < 3.0e38f && p.y < 3.0e38f) {
         lsum = __fadd2_rn(lsum, log_ge1_x2f(p));
-    } else {
-        lsum.x += log1p_sum4_slow_f(r[0].x, r[0].y, r[1].x, r[1].y, inv_df);
-        lsum.y += log1p_sum4_slow_f(r[2].x, r[2].y, r[3].x, r[3].y, inv_df);
+    } else {                                                   // rare: a product of four overflowed
+        lsum.x += log1p_sum4_slow_f(r[0].x * inv_ps, r[1].x * inv_ps, r[2].x * inv_ps, r[3].x * inv_ps, inv_df);
+        lsum.y += log1p_sum4_slow_f(r[0].y * inv_ps, r[1].y * inv_ps, r[2].y * inv_ps, r[3].y * inv_ps, inv_df);
     }
-    const float2 ps = make_float2(psi_scale, psi_scale);
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        float ix, iy;
-        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ix) : "f"(u[i].x));
-        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(iy) : "f"(u[i].y));
-        const float2 o = __fmul2_rn(__fmul2_rn(r[i], ps), make_float2(ix, iy));
-        tc::split_f16_pair(o.x, o.y, hi2[i], lo2[i]);
+        float2 iv;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(iv.x) : "f"(u[i].x));
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(iv.y) : "f"(u[i].y));
+        tc::split_f16_pair_rz(__fmul2_rn(r[i], iv), hi2[i], lo2[i]);
     }
 }
 
 struct FusedArgs {
     const float* b;            // (S, D) fp32 draws
-    const float* y;            // (N)
+    const float* ys;           // (N padded to 64) psi_scale * y, zero past N (made per call by reg_fused_prep_kernel)
     const F16Header* xhdr;     // scale of the X planes
     float* gpart;              // [R][S_pad][128] fp32 partial gradients (scaled by psi_scale * x_scale)
-    double* lpart;             // [R][2][S_pad] partial sums of log(1 + r^2/df)
+    double* lpart;             // [R][kFG][S_pad] partial sums of log(1 + r^2/df)
     long long S, S_pad, N;
     int D, n_dt, DG, R, flush_tiles;
     float inv_df, psi_scale;
@@ -209,13 +214,10 @@ reg_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const FusedArgs a) 
                 if (lane == 0) {
                     unsigned char* dst = smem + (size_t)s * kFStageBytes;
                     const long long r0 = t * kFR;
-                    long long nv = a.N - r0;
-                    if (nv > kFR) nv = kFR;
-                    const uint32_t ybytes = (uint32_t)(nv / 4) * 16;
-                    mbar_expect_tx(&full[s], kFXBytes + ybytes);
-                    tc::tma_load_3d(dst, &tmap_x, &full[s], 0, (int)r0, 0);
+                    mbar_expect_tx(&full[s], kFXBytes + 256);
+                    tc::tma_load_3d(dst, &tmap_x, &full[s], 0, (int)r0, 0);          // rows past N: zero-filled
                     tc::tma_load_3d(dst + 16384, &tmap_x, &full[s], 64, (int)r0, 0);
-                    if (ybytes) bulk_g2s(dst + kFXBytes, a.y + r0, ybytes, &full[s]);
+                    bulk_g2s(dst + kFXBytes, a.ys + r0, 256, &full[s]);
                 }
                 __syncwarp();
             }
@@ -255,42 +257,50 @@ reg_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const FusedArgs a) 
                 ++flushes;
             }
         };
+        // GEMM1 runs kLook tiles ahead of GEMM2: the epilogue of tile t (TMEM load, ~250 instructions per thread,
+        // TMEM store) takes longer than one GEMM1, so with a look-ahead of one the tensor pipe idled on psi_full
+        constexpr int kLook = 2;
         for (int p = 0; p < n_pass; ++p) {
             mbar_wait(b_full, (uint32_t)(p & 1));
-            for (long long t = 0; t < nt; ++t, ++it) {
-                const int s = (int)(it % kFStages), ab = (int)(it & 1);
-                mbar_wait(&full[s], (uint32_t)((it / kFStages) & 1));
-                mbar_wait(&acc_empty[ab], (uint32_t)(((it >> 1) & 1) ^ 1));
-                tc::fence_after_sync();
-                const uint32_t xs = smem_u + (uint32_t)s * kFStageBytes;
-                const uint32_t d1 = tm + kTAcc + (uint32_t)ab * kFR;
+            const long long it0 = it;
+            for (long long t = 0; t < nt + kLook; ++t) {
+                if (t < nt) {
+                    const int s = (int)(it % kFStages), ab = (int)(it & 1);
+                    mbar_wait(&full[s], (uint32_t)((it / kFStages) & 1));
+                    mbar_wait(&acc_empty[ab], (uint32_t)(((it >> 1) & 1) ^ 1));
+                    tc::fence_after_sync();
+                    const uint32_t xs = smem_u + (uint32_t)s * kFStageBytes;
+                    const uint32_t d1 = tm + kTAcc + (uint32_t)ab * kFR;
 #pragma unroll
-                for (int k = 0; k < kFD / 16; ++k) {
-                    // K-major: col block (k / 4) at +16384, 16 dims = 32 bytes inside the 128-byte line; 8 rows = 1024 B
-                    const uint32_t off = (uint32_t)(k >> 2) * 16384 + (uint32_t)(k & 3) * 32;
-                    const uint64_t x_hi = tc::smem_desc_sw128(xs + off, 16, 1024, 2);
-                    const uint64_t x_lo = tc::smem_desc_sw128(xs + 8192 + off, 16, 1024, 2);
-                    tc::mma_f16_ts_warp(d1, tm + kTBlo + k * 8, x_hi, idesc1, k != 0);
-                    tc::mma_f16_ts_warp(d1, tm + kTBhi + k * 8, x_lo, idesc1, true);
-                    tc::mma_f16_ts_warp(d1, tm + kTBhi + k * 8, x_hi, idesc1, true);
+                    for (int k = 0; k < kFD / 16; ++k) {
+                        // K-major: col block (k / 4) at +16384, 16 dims = 32 bytes inside the 128-byte line; 8 rows = 1024 B
+                        const uint32_t off = (uint32_t)(k >> 2) * 16384 + (uint32_t)(k & 3) * 32;
+                        const uint64_t x_hi = tc::smem_desc_sw128(xs + off, 16, 1024, 2);
+                        const uint64_t x_lo = tc::smem_desc_sw128(xs + 8192 + off, 16, 1024, 2);
+                        tc::mma_f16_ts_warp(d1, tm + kTBlo + k * 8, x_hi, idesc1, k != 0);
+                        tc::mma_f16_ts_warp(d1, tm + kTBhi + k * 8, x_lo, idesc1, true);
+                        tc::mma_f16_ts_warp(d1, tm + kTBhi + k * 8, x_hi, idesc1, true);
+                    }
+                    tc::mma_commit_warp(bars_u + (uint32_t)(16 + ab) * 8);        // acc_full[ab]
+                    if (t == nt - 1) tc::mma_commit_warp(bars_u + 25 * 8);        // b_empty: last GEMM1 on this draw tile
+                    ++it;
                 }
-                tc::mma_commit_warp(bars_u + (uint32_t)(16 + ab) * 8);        // acc_full[ab]
-                if (t == nt - 1) tc::mma_commit_warp(bars_u + 25 * 8);        // b_empty: last GEMM1 on this draw tile
-                if (t > 0) gemm2(it - 1, false);
+                if (t >= kLook) gemm2(it0 + t - kLook, t - kLook == nt - 1);
             }
-            gemm2(it - 1, true);
         }
     } else if (warp >= 4) {
-        // ===================================================== epilogue warps: thread = draw row (TMEM lane)
-        const int q = warp & 3, h = (warp - 4) >> 2;
+        // ===================================================== epilogue warps: thread = draw row (TMEM lane) x 16 columns
+        const int q = warp & 3, h = (warp - 4) >> 2;                  // lane quarter, column group
         const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
         const float x_inv = a.xhdr->inv_scale;
+        const float idf = a.inv_df / (a.psi_scale * a.psi_scale), inv_ps = 1.f / a.psi_scale;
         long long it = 0;
         uint32_t flushes = 0;
         for (int p = 0; p < n_pass; ++p) {
             const int dt = dg + p * a.DG;
             const long long row = (long long)dt * kFM + q * 32 + lane;
-            // ---- this pass's draws -> tensor memory (fp16 hi / lo, per-row power-of-two scale)
+            // ---- this pass's draws -> tensor memory (fp16 hi / lo, per-row power-of-two scale); this thread converts
+            // dims 32 h .. 32 h + 31 of its row
             if (p > 0) { mbar_wait(b_empty, (uint32_t)((p - 1) & 1)); tc::fence_after_sync(); }
             float b_scale = 1.f;
             {
@@ -303,104 +313,98 @@ reg_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const FusedArgs a) 
                         if (bb < 0x7f800000u && bb > mx) mx = bb;
                     }
                 b_scale = pow2_scale_for(mx);
-#pragma unroll 1
-                for (int blk = 0; blk < 2; ++blk) {                  // 32 dims per block -> 16 packed columns
-                    uint32_t hi2[16], lo2[16];
+                uint32_t hi2[16], lo2[16];
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        const int c = h * 64 + blk * 32 + 2 * j;
-                        const float v0 = (live && c < a.D) ? b_scale * __ldg(src + c) : 0.f;
-                        const float v1 = (live && c + 1 < a.D) ? b_scale * __ldg(src + c + 1) : 0.f;
-                        tc::split_f16_pair(v0, v1, hi2[j], lo2[j]);
-                    }
-                    tc::tmem_st_32x16(lane_addr + kTBhi + h * 32 + blk * 16, hi2);
-                    tc::tmem_st_32x16(lane_addr + kTBlo + h * 32 + blk * 16, lo2);
+                for (int j = 0; j < 16; ++j) {
+                    const int c = h * 32 + 2 * j;
+                    const float v0 = (live && c < a.D) ? b_scale * __ldg(src + c) : 0.f;
+                    const float v1 = (live && c + 1 < a.D) ? b_scale * __ldg(src + c + 1) : 0.f;
+                    tc::split_f16_pair(v0, v1, hi2[j], lo2[j]);
                 }
+                tc::tmem_st_32x16(lane_addr + kTBhi + h * 16, hi2);
+                tc::tmem_st_32x16(lane_addr + kTBlo + h * 16, lo2);
                 tc::tmem_st_wait();
                 tc::fence_before_sync();
                 mbar_arrive(b_full);
             }
-            const float neg_inv_ab = -(x_inv / b_scale);
+            const float c1 = -(a.psi_scale * x_inv) / b_scale;
             double lsum = 0.0;
+            float lc = 0.f, lcomp = 0.f;            // per-chain log-sum in compensated fp32 (the fp64 pipe is too slow per tile)
             int chain = 0;
             bool first_flush = true;
             for (long long t = 0; t < nt; ++t, ++it) {
                 const int s = (int)(it % kFStages), ab = (int)(it & 1);
-                const long long r0 = (rt0 + t) * kFR;
-                long long nv = a.N - r0;
-                if (nv > kFR) nv = kFR;
                 mbar_wait(&acc_full[ab], (uint32_t)((it >> 1) & 1));
                 mbar_wait(&full[s], (uint32_t)((it / kFStages) & 1));          // y segment of the slot (already complete)
                 tc::fence_after_sync();
-                uint32_t raw[32];
-                tc::tmem_ld_32x32_nowait(lane_addr + kTAcc + ab * kFR + h * 32, raw);
+                uint32_t raw[16];
+                tc::tmem_ld_32x16_nowait(lane_addr + kTAcc + ab * kFR + h * kFC, raw);
+                const float4* ysm = reinterpret_cast<const float4*>(smem + (size_t)s * kFStageBytes + kFXBytes) + h * (kFC / 4);
+                const float4 y0 = ysm[0], y1 = ysm[1], y2 = ysm[2], y3 = ysm[3];
                 tc::tmem_ld_wait();
                 tc::fence_before_sync();
                 mbar_arrive(&acc_empty[ab]);
-                const float* ysm = reinterpret_cast<const float*>(smem + (size_t)s * kFStageBytes + kFXBytes) + h * 32;
-                uint32_t hi2[16], lo2[16];
+                uint32_t hi2[8], lo2[8];
                 float2 ls = make_float2(0.f, 0.f);
-                if (nv == kFR) {
-#pragma unroll
-                    for (int o = 0; o < 4; ++o) {
-                        const float4 t0 = *reinterpret_cast<const float4*>(ysm + 8 * o);
-                        const float4 t1 = *reinterpret_cast<const float4*>(ysm + 8 * o + 4);
-                        const float yy[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
-                        float av[8];
-#pragma unroll
-                        for (int e = 0; e < 8; ++e) av[e] = __uint_as_float(raw[8 * o + e]);
-                        psi_oct(av, yy, neg_inv_ab, a.inv_df, a.psi_scale, ls, hi2 + 4 * o, lo2 + 4 * o);
-                    }
-                } else {
-#pragma unroll
-                    for (int o = 0; o < 4; ++o) {
-                        float yy[8], av[8];
-#pragma unroll
-                        for (int e = 0; e < 8; ++e) {      // rows past the end: r = 0 -> u = 1 -> no log term, psi = 0
-                            const int c = h * 32 + 8 * o + e;
-                            const bool on = c < nv;
-                            yy[e] = on ? __ldg(a.y + r0 + c) : 0.f;
-                            av[e] = on ? __uint_as_float(raw[8 * o + e]) : 0.f;
-                        }
-                        psi_oct(av, yy, neg_inv_ab, a.inv_df, a.psi_scale, ls, hi2 + 4 * o, lo2 + 4 * o);
-                    }
+                {
+                    const float2 av[4] = {make_float2(__uint_as_float(raw[0]), __uint_as_float(raw[1])),
+                                          make_float2(__uint_as_float(raw[2]), __uint_as_float(raw[3])),
+                                          make_float2(__uint_as_float(raw[4]), __uint_as_float(raw[5])),
+                                          make_float2(__uint_as_float(raw[6]), __uint_as_float(raw[7]))};
+                    const float2 yv[4] = {make_float2(y0.x, y0.y), make_float2(y0.z, y0.w),
+                                          make_float2(y1.x, y1.y), make_float2(y1.z, y1.w)};
+                    psi_oct(av, yv, c1, idf, a.inv_df, inv_ps, ls, hi2, lo2);
                 }
-                lsum += (double)(ls.x + ls.y);
+                {
+                    const float2 av[4] = {make_float2(__uint_as_float(raw[8]), __uint_as_float(raw[9])),
+                                          make_float2(__uint_as_float(raw[10]), __uint_as_float(raw[11])),
+                                          make_float2(__uint_as_float(raw[12]), __uint_as_float(raw[13])),
+                                          make_float2(__uint_as_float(raw[14]), __uint_as_float(raw[15]))};
+                    const float2 yv[4] = {make_float2(y2.x, y2.y), make_float2(y2.z, y2.w),
+                                          make_float2(y3.x, y3.y), make_float2(y3.z, y3.w)};
+                    psi_oct(av, yv, c1, idf, a.inv_df, inv_ps, ls, hi2 + 4, lo2 + 4);
+                }
+                {
+                    const float v = (ls.x + ls.y) - lcomp;       // Kahan
+                    const float tsum = lc + v;
+                    lcomp = (tsum - lc) - v;
+                    lc = tsum;
+                }
                 mbar_wait(&psi_empty[ab], (uint32_t)(((it >> 1) & 1) ^ 1));
                 tc::fence_after_sync();
-                tc::tmem_st_32x16(lane_addr + kTPsi + ab * 64 + h * 16, hi2);
-                tc::tmem_st_32x16(lane_addr + kTPsi + ab * 64 + 32 + h * 16, lo2);
+                // packed fp16 pairs: tile rows 16 h + 2 j, 16 h + 2 j + 1 -> column 8 h + j of the hi / lo block
+                tc::tmem_st_32x8(lane_addr + kTPsi + ab * 64 + h * 8, hi2);
+                tc::tmem_st_32x8(lane_addr + kTPsi + ab * 64 + 32 + h * 8, lo2);
                 tc::tmem_st_wait();
                 tc::fence_before_sync();
                 mbar_arrive(&psi_full[ab]);
                 ++chain;
                 if (chain == a.flush_tiles || t == nt - 1) {
-                    // ---- chain complete: G (this thread: one row, 64 dims) -> fp32 partial of (row range, draw tile)
+                    // ---- chain complete: G (this thread: one row, 32 dims) -> fp32 partial of (row range, draw tile)
                     mbar_wait(g_full, flushes & 1);
                     tc::fence_after_sync();
-                    float* dst = a.gpart + ((size_t)rr * a.S_pad + row) * kFD + h * 64;
-#pragma unroll 1
-                    for (int blk = 0; blk < 2; ++blk) {
-                        uint32_t g[32];
-                        tc::tmem_ld_32x32_nowait(lane_addr + kTG + h * 64 + blk * 32, g);
-                        tc::tmem_ld_wait();
-                        float4* d4 = reinterpret_cast<float4*>(dst + blk * 32);
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            float4 v = make_float4(__uint_as_float(g[4 * j]), __uint_as_float(g[4 * j + 1]),
-                                                   __uint_as_float(g[4 * j + 2]), __uint_as_float(g[4 * j + 3]));
-                            if (!first_flush) { const float4 o = d4[j]; v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w; }
-                            d4[j] = v;
-                        }
-                    }
+                    float* dst = a.gpart + ((size_t)rr * a.S_pad + row) * kFD + h * 32;
+                    uint32_t g[32];
+                    tc::tmem_ld_32x32_nowait(lane_addr + kTG + h * 32, g);
+                    tc::tmem_ld_wait();
                     tc::fence_before_sync();
-                    mbar_arrive(g_empty);
+                    mbar_arrive(g_empty);                           // G is in registers: the next chain may start
+                    float4* d4 = reinterpret_cast<float4*>(dst);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        float4 v = make_float4(__uint_as_float(g[4 * j]), __uint_as_float(g[4 * j + 1]),
+                                               __uint_as_float(g[4 * j + 2]), __uint_as_float(g[4 * j + 3]));
+                        if (!first_flush) { const float4 o = d4[j]; v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w; }
+                        d4[j] = v;
+                    }
                     ++flushes;
                     chain = 0;
                     first_flush = false;
+                    lsum += (double)lc - (double)lcomp;
+                    lc = 0.f; lcomp = 0.f;
                 }
             }
-            a.lpart[((size_t)rr * 2 + h) * a.S_pad + row] = lsum;
+            a.lpart[((size_t)rr * kFG + h) * a.S_pad + row] = lsum;
         }
     }
     tc::fence_before_sync();
@@ -429,13 +433,20 @@ __global__ void reg_fused_final_kernel(const FusedArgs a, double inv_var, double
         bb = warp_sum(bb);
         if (lane == 0) {
             double l = 0.0;
-            for (int r = 0; r < 2 * a.R; ++r) l += a.lpart[(size_t)r * a.S_pad + s];
+            for (int r = 0; r < kFG * a.R; ++r) l += a.lpart[(size_t)r * a.S_pad + s];
             logp[s] = -0.5 * bb * inv_var - half_dfp1 * l;
         }
     }
 }
 
-struct FusedPlan { int n_dt, DG, R; long long S_pad; size_t off_g, off_l, total; };
+// ys[r] = psi_scale * y[r] for r < N, 0 up to the next multiple of 64 (+ one spare tile)
+__global__ void reg_fused_prep_kernel(const float* __restrict__ y, long long N, long long n_pad, float psi_scale,
+                                      float* __restrict__ ys) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n_pad; i += (long long)gridDim.x * blockDim.x)
+        ys[i] = i < N ? psi_scale * y[i] : 0.f;
+}
+
+struct FusedPlan { int n_dt, DG, R; long long S_pad, n_pad; size_t off_g, off_l, off_y, total; };
 static FusedPlan fused_plan(long long S, long long N) {
     FusedPlan p;
     p.n_dt = (int)((S + kFM - 1) / kFM);
@@ -465,7 +476,9 @@ static FusedPlan fused_plan(long long S, long long N) {
     p.R = (int)R;
     p.off_g = 0;
     p.off_l = align_up((size_t)p.R * p.S_pad * kFD * 4, 256);
-    p.total = p.off_l + align_up((size_t)p.R * 2 * p.S_pad * 8, 256);
+    p.off_y = p.off_l + align_up((size_t)p.R * kFG * p.S_pad * 8, 256);
+    p.n_pad = T * kFR;
+    p.total = p.off_y + align_up((size_t)p.n_pad * 4, 256);
     return p;
 }
 
@@ -488,7 +501,7 @@ int regression_logp_grad_fused(const ModelHost* m, const float* b, long long S, 
     int rc = make_f16_planes_tmap(&tx, m->d_X_planes16, N, D, ldp, N * ldp, kFR);
     if (rc != VB_OK) return rc;
     FusedArgs a;
-    a.b = b; a.y = (const float*)m->d_y; a.xhdr = f16_header(m->d_X_planes16, N, D);
+    a.b = b; a.ys = (const float*)(w + p.off_y); a.xhdr = f16_header(m->d_X_planes16, N, D);
     a.gpart = (float*)(w + p.off_g); a.lpart = (double*)(w + p.off_l);
     a.S = S; a.S_pad = p.S_pad; a.N = N; a.D = D; a.n_dt = p.n_dt; a.DG = p.DG; a.R = p.R;
     a.flush_tiles = 128;                         // 8192 rows per TMEM accumulation chain (DESIGN: truncating accumulate)
@@ -504,6 +517,9 @@ int regression_logp_grad_fused(const ModelHost* m, const float* b, long long S, 
         VB_CUDA_TRY(cudaFuncSetAttribute(reg_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFSmemBytes));
         configured.done(dev);
     }
+    reg_fused_prep_kernel<<<grid_for_f(p.n_pad, 256, kNumSMs * 8), 256, 0, st>>>((const float*)m->d_y, N, p.n_pad, a.psi_scale,
+                                                                                 (float*)(w + p.off_y));
+    VB_LAUNCH_CHECK();
     reg_fused_kernel<<<(unsigned)(p.R * p.DG), kFThreads, kFSmemBytes, st>>>(tx, a);
     VB_LAUNCH_CHECK();
     const double inv_var = 1.0 / (m->prior_sd * m->prior_sd);

@@ -216,12 +216,37 @@ __device__ __forceinline__ void tmem_ld_32x32_nowait(uint32_t taddr, uint32_t (&
           "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
         : "r"(taddr) : "memory");
 }
+__device__ __forceinline__ void tmem_ld_32x16_nowait(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_st_32x8(uint32_t taddr, const uint32_t (&v)[8]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+        :: "r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+        : "memory");
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 // two fp32 -> packed f16x2 (round to nearest even); `lo16` lands in the low half
 __device__ __forceinline__ uint32_t pack_f16x2(float lo16, float hi16) {
     uint32_t r;
     asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi16), "f"(lo16));
     return r;
+}
+// Cheap fp16 hi / lo split of a pair for streaming epilogues: hi = x TRUNCATED to 11 significant bits (one
+// round-toward-zero pack), lo = fp16_rn(x - hi) with x - hi exact in fp32 (|lo| < 2^-10 |x|).  The truncation is
+// not an error source: lo carries the remainder, so x = hi + lo up to the unbiased rounding of lo, 2^-21 |x|.
+__device__ __forceinline__ void split_f16_pair_rz(float2 x, uint32_t& hi2, uint32_t& lo2) {
+    asm("cvt.rz.f16x2.f32 %0, %1, %2;" : "=r"(hi2) : "f"(x.y), "f"(x.x));
+    float2 nh;                                              // -hi as fp32: mask the low 13 mantissa bits, flip the sign
+    nh.x = __uint_as_float((__float_as_uint(x.x) & 0xffffe000u) ^ 0x80000000u);
+    nh.y = __uint_as_float((__float_as_uint(x.y) & 0xffffe000u) ^ 0x80000000u);
+    const float2 l = __fadd2_rn(x, nh);
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(lo2) : "f"(l.y), "f"(l.x));
 }
 // fp16 hi / lo split of a pair: hi = x rounded to 11 significant bits (integer add + mask: exact in fp16 when
 // normal), lo = x - hi (exact in fp32), both packed as f16x2.  22 significant bits in total, like tf32 hi / lo.
