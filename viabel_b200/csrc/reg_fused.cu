@@ -116,30 +116,33 @@ __device__ __forceinline__ float2 log_ge1_x2f(float2 p) {
 __device__ __noinline__ float log1p_sum4_slow_f(float r0, float r1, float r2, float r3, float inv_df) {
     return (log1pf(r0 * r0 * inv_df) + log1pf(r1 * r1 * inv_df)) + (log1pf(r2 * r2 * inv_df) + log1pf(r3 * r3 * inv_df));
 }
-// eight residuals, everything in register PAIRS (packed fp32x2 arithmetic needs aligned pairs; unpaired operands cost
-// a move each): acc = tensor-memory accumulator pairs, ys = psi_scale * y pairs.
+// sixteen residuals, everything in register PAIRS (packed fp32x2 arithmetic needs aligned pairs; unpaired operands
+// cost a move each): acc = tensor-memory accumulator pairs, ys = psi_scale * y pairs.
 //   r' = psi_scale r = fma(acc, c1, ys),  c1 = -psi_scale / (draw scale * X scale)
 //   u  = 1 + r^2/df = fma(r' r', idf, 1), idf = 1 / (df psi_scale^2)
-//   sum log u: one packed log per eight (two products of four);   psi' = psi_scale psi / c = r' / u -> fp16 (hi, lo)
-__device__ __forceinline__ void psi_oct(const float2 (&acc)[4], const float2 (&ys)[4], float c1, float idf, float inv_df,
-                                        float inv_ps, float2& lsum, uint32_t* hi2, uint32_t* lo2) {
+//   sum log u: ONE packed log per sixteen (two products of eight; a product overflows only for |r| > ~1600 sqrt(df/40):
+//   then the slow path);   psi' = psi_scale psi / c = r' / u -> fp16 (hi, lo)
+__device__ __forceinline__ void psi_hex(const float2 (&acc)[8], const float2 (&ys)[8], float c1, float idf, float inv_df,
+                                        float inv_ps, float2& lsum, uint32_t (&hi2)[8], uint32_t (&lo2)[8]) {
     const float2 c1v = make_float2(c1, c1), one = make_float2(1.f, 1.f), idfv = make_float2(idf, idf);
-    float2 r[4], u[4];
+    float2 r[8], u[8];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < 8; ++i) {
         r[i] = __ffma2_rn(acc[i], c1v, ys[i]);
         u[i] = __ffma2_rn(__fmul2_rn(r[i], r[i]), idfv, one);
     }
-    const float2 pa = __fmul2_rn(u[0], u[1]), pb = __fmul2_rn(u[2], u[3]);
-    const float2 p = __fmul2_rn(pa, pb);                       // (u0 u2 u4 u6, u1 u3 u5 u7): the pairing is irrelevant
+    const float2 p = __fmul2_rn(__fmul2_rn(__fmul2_rn(u[0], u[1]), __fmul2_rn(u[2], u[3])),
+                                __fmul2_rn(__fmul2_rn(u[4], u[5]), __fmul2_rn(u[6], u[7])));
     if (p.x < 3.0e38f && p.y < 3.0e38f) {
         lsum = __fadd2_rn(lsum, log_ge1_x2f(p));
-    } else {                                                   // rare: a product of four overflowed
-        lsum.x += log1p_sum4_slow_f(r[0].x * inv_ps, r[1].x * inv_ps, r[2].x * inv_ps, r[3].x * inv_ps, inv_df);
-        lsum.y += log1p_sum4_slow_f(r[0].y * inv_ps, r[1].y * inv_ps, r[2].y * inv_ps, r[3].y * inv_ps, inv_df);
+    } else {                                                   // rare: a product of eight overflowed
+#pragma unroll
+        for (int i = 0; i < 8; i += 2) {
+            lsum.x += log1p_sum4_slow_f(r[i].x * inv_ps, r[i].y * inv_ps, r[i + 1].x * inv_ps, r[i + 1].y * inv_ps, inv_df);
+        }
     }
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < 8; ++i) {
         float2 iv;
         asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(iv.x) : "f"(u[i].x));
         asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(iv.y) : "f"(u[i].y));
@@ -206,11 +209,11 @@ reg_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const FusedArgs a) 
 
     if (warp == 0) {
         // ===================================================== TMA producer
-        long long it = 0;
+        int s = 0;
+        uint32_t ph = 0;
         for (int p = 0; p < n_pass; ++p) {
-            for (long long t = rt0; t < rt1; ++t, ++it) {
-                const int s = (int)(it % kFStages);
-                mbar_wait(&empty[s], (uint32_t)(((it / kFStages) & 1) ^ 1));
+            for (long long t = rt0; t < rt1; ++t) {
+                mbar_wait(&empty[s], ph ^ 1);
                 if (lane == 0) {
                     unsigned char* dst = smem + (size_t)s * kFStageBytes;
                     const long long r0 = t * kFR;
@@ -220,6 +223,7 @@ reg_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const FusedArgs a) 
                     bulk_g2s(dst + kFXBytes, a.ys + r0, 256, &full[s]);
                 }
                 __syncwarp();
+                if (++s == kFStages) { s = 0; ph ^= 1; }
             }
         }
     } else if (warp == 1) {
@@ -232,8 +236,11 @@ reg_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const FusedArgs a) 
         long long it = 0;
         int chain = 0;
         uint32_t flushes = 0;
+        int s1 = 0, s2 = 0;                           // X ring slots of the next GEMM1 / GEMM2 tile
+        uint32_t ph1 = 0;
         auto gemm2 = [&](long long j, bool last_of_pass) {
-            const int s = (int)(j % kFStages), pb = (int)(j & 1);
+            const int s = s2, pb = (int)(j & 1);
+            if (++s2 == kFStages) s2 = 0;
             mbar_wait(&psi_full[pb], (uint32_t)((j >> 1) & 1));
             if (chain == 0) mbar_wait(g_empty, (flushes & 1) ^ 1);
             tc::fence_after_sync();
@@ -265,8 +272,9 @@ reg_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const FusedArgs a) 
             const long long it0 = it;
             for (long long t = 0; t < nt + kLook; ++t) {
                 if (t < nt) {
-                    const int s = (int)(it % kFStages), ab = (int)(it & 1);
-                    mbar_wait(&full[s], (uint32_t)((it / kFStages) & 1));
+                    const int s = s1, ab = (int)(it & 1);
+                    mbar_wait(&full[s], ph1);
+                    if (++s1 == kFStages) { s1 = 0; ph1 ^= 1; }
                     mbar_wait(&acc_empty[ab], (uint32_t)(((it >> 1) & 1) ^ 1));
                     tc::fence_after_sync();
                     const uint32_t xs = smem_u + (uint32_t)s * kFStageBytes;
@@ -296,6 +304,9 @@ reg_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const FusedArgs a) 
         const float idf = a.inv_df / (a.psi_scale * a.psi_scale), inv_ps = 1.f / a.psi_scale;
         long long it = 0;
         uint32_t flushes = 0;
+        int st = 0;                                  // X ring slot / phase of tile `it`, kept incrementally
+        uint32_t st_ph = 0;
+        const uint32_t smem_sa = smem_u32(smem);
         for (int p = 0; p < n_pass; ++p) {
             const int dt = dg + p * a.DG;
             const long long row = (long long)dt * kFM + q * 32 + lane;
@@ -331,38 +342,31 @@ reg_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const FusedArgs a) 
             double lsum = 0.0;
             float lc = 0.f, lcomp = 0.f;            // per-chain log-sum in compensated fp32 (the fp64 pipe is too slow per tile)
             int chain = 0;
-            bool first_flush = true;
+            bool first_flush = true, pending = false;
             for (long long t = 0; t < nt; ++t, ++it) {
-                const int s = (int)(it % kFStages), ab = (int)(it & 1);
-                mbar_wait(&acc_full[ab], (uint32_t)((it >> 1) & 1));
-                mbar_wait(&full[s], (uint32_t)((it / kFStages) & 1));          // y segment of the slot (already complete)
+                const int ab = (int)(it & 1);
+                const uint32_t ph2 = (uint32_t)((it >> 1) & 1);
+                mbar_wait(&acc_full[ab], ph2);
+                mbar_wait(&full[st], st_ph);                                   // y segment of the slot (already complete)
                 tc::fence_after_sync();
                 uint32_t raw[16];
                 tc::tmem_ld_32x16_nowait(lane_addr + kTAcc + ab * kFR + h * kFC, raw);
-                const float4* ysm = reinterpret_cast<const float4*>(smem + (size_t)s * kFStageBytes + kFXBytes) + h * (kFC / 4);
-                const float4 y0 = ysm[0], y1 = ysm[1], y2 = ysm[2], y3 = ysm[3];
+                const uint32_t ya = smem_sa + (uint32_t)st * kFStageBytes + kFXBytes + (uint32_t)h * (kFC * 4);
+                const float4 y0 = tc::lds128(ya), y1 = tc::lds128(ya + 16), y2 = tc::lds128(ya + 32), y3 = tc::lds128(ya + 48);
+                if (++st == kFStages) { st = 0; st_ph ^= 1; }
                 tc::tmem_ld_wait();
                 tc::fence_before_sync();
                 mbar_arrive(&acc_empty[ab]);
                 uint32_t hi2[8], lo2[8];
                 float2 ls = make_float2(0.f, 0.f);
                 {
-                    const float2 av[4] = {make_float2(__uint_as_float(raw[0]), __uint_as_float(raw[1])),
-                                          make_float2(__uint_as_float(raw[2]), __uint_as_float(raw[3])),
-                                          make_float2(__uint_as_float(raw[4]), __uint_as_float(raw[5])),
-                                          make_float2(__uint_as_float(raw[6]), __uint_as_float(raw[7]))};
-                    const float2 yv[4] = {make_float2(y0.x, y0.y), make_float2(y0.z, y0.w),
-                                          make_float2(y1.x, y1.y), make_float2(y1.z, y1.w)};
-                    psi_oct(av, yv, c1, idf, a.inv_df, inv_ps, ls, hi2, lo2);
-                }
-                {
-                    const float2 av[4] = {make_float2(__uint_as_float(raw[8]), __uint_as_float(raw[9])),
-                                          make_float2(__uint_as_float(raw[10]), __uint_as_float(raw[11])),
-                                          make_float2(__uint_as_float(raw[12]), __uint_as_float(raw[13])),
-                                          make_float2(__uint_as_float(raw[14]), __uint_as_float(raw[15]))};
-                    const float2 yv[4] = {make_float2(y2.x, y2.y), make_float2(y2.z, y2.w),
+                    float2 av[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) av[i] = make_float2(__uint_as_float(raw[2 * i]), __uint_as_float(raw[2 * i + 1]));
+                    const float2 yv[8] = {make_float2(y0.x, y0.y), make_float2(y0.z, y0.w), make_float2(y1.x, y1.y),
+                                          make_float2(y1.z, y1.w), make_float2(y2.x, y2.y), make_float2(y2.z, y2.w),
                                           make_float2(y3.x, y3.y), make_float2(y3.z, y3.w)};
-                    psi_oct(av, yv, c1, idf, a.inv_df, inv_ps, ls, hi2 + 4, lo2 + 4);
+                    psi_hex(av, yv, c1, idf, a.inv_df, inv_ps, ls, hi2, lo2);
                 }
                 {
                     const float v = (ls.x + ls.y) - lcomp;       // Kahan
@@ -370,7 +374,7 @@ reg_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const FusedArgs a) 
                     lcomp = (tsum - lc) - v;
                     lc = tsum;
                 }
-                mbar_wait(&psi_empty[ab], (uint32_t)(((it >> 1) & 1) ^ 1));
+                mbar_wait(&psi_empty[ab], ph2 ^ 1);
                 tc::fence_after_sync();
                 // packed fp16 pairs: tile rows 16 h + 2 j, 16 h + 2 j + 1 -> column 8 h + j of the hi / lo block
                 tc::tmem_st_32x8(lane_addr + kTPsi + ab * 64 + h * 8, hi2);
@@ -379,8 +383,10 @@ reg_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const FusedArgs a) 
                 tc::fence_before_sync();
                 mbar_arrive(&psi_full[ab]);
                 ++chain;
-                if (chain == a.flush_tiles || t == nt - 1) {
-                    // ---- chain complete: G (this thread: one row, 32 dims) -> fp32 partial of (row range, draw tile)
+                // ---- chain complete: G (this thread: one row, 32 dims) -> fp32 partial of (row range, draw tile).  The
+                // drain is deferred by one tile (the epilogue works on tile t + 1 while the chain's last GEMM2 retires)
+                // except at the end of a pass.
+                auto drain = [&]() {
                     mbar_wait(g_full, flushes & 1);
                     tc::fence_after_sync();
                     float* dst = a.gpart + ((size_t)rr * a.S_pad + row) * kFD + h * 32;
@@ -398,10 +404,14 @@ reg_fused_kernel(const __grid_constant__ CUtensorMap tmap_x, const FusedArgs a) 
                         d4[j] = v;
                     }
                     ++flushes;
-                    chain = 0;
                     first_flush = false;
+                };
+                if (pending) { drain(); pending = false; }
+                if (chain == a.flush_tiles || t == nt - 1) {
+                    chain = 0;
                     lsum += (double)lc - (double)lcomp;
                     lc = 0.f; lcomp = 0.f;
+                    if (t == nt - 1) drain(); else pending = true;
                 }
             }
             a.lpart[((size_t)rr * kFG + h) * a.S_pad + row] = lsum;

@@ -242,11 +242,17 @@ __device__ __forceinline__ uint32_t pack_f16x2(float lo16, float hi16) {
 // not an error source: lo carries the remainder, so x = hi + lo up to the unbiased rounding of lo, 2^-21 |x|.
 __device__ __forceinline__ void split_f16_pair_rz(float2 x, uint32_t& hi2, uint32_t& lo2) {
     asm("cvt.rz.f16x2.f32 %0, %1, %2;" : "=r"(hi2) : "f"(x.y), "f"(x.x));
-    float2 nh;                                              // -hi as fp32: mask the low 13 mantissa bits, flip the sign
-    nh.x = __uint_as_float((__float_as_uint(x.x) & 0xffffe000u) ^ 0x80000000u);
-    nh.y = __uint_as_float((__float_as_uint(x.y) & 0xffffe000u) ^ 0x80000000u);
-    const float2 l = __fadd2_rn(x, nh);
+    float2 h;                                               // hi as fp32: the low 13 mantissa bits masked off
+    h.x = __uint_as_float(__float_as_uint(x.x) & 0xffffe000u);
+    h.y = __uint_as_float(__float_as_uint(x.y) & 0xffffe000u);
+    const float2 l = __ffma2_rn(h, make_float2(-1.f, -1.f), x);     // x - hi, exact
     asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(lo2) : "f"(l.y), "f"(l.x));
+}
+// 16-byte shared-memory load through a 32-bit shared address (a generic pointer makes the compiler emit LD.E)
+__device__ __forceinline__ float4 lds128(uint32_t saddr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(saddr));
+    return v;
 }
 // fp16 hi / lo split of a pair: hi = x rounded to 11 significant bits (integer add + mask: exact in fp16 when
 // normal), lo = x - hi (exact in fp32), both packed as f16x2.  22 significant bits in total, like tf32 hi / lo.
