@@ -434,6 +434,16 @@ int vb_psis_tail(const void* d_cands, long long count, long long K1, const doubl
 int vb_psis_write(const double* d_lw, double* d_out, long long n_local, long long index0,
                   const double* d_M, long long count, long long K1, const void* d_tail_ws,
                   void* stream);
+/* S6 / the single-GPU composite with the one-pass statistics of divergence_bound(alpha = 2) (bounds.py:169-176) of the
+ * RAW weights taken in the same final pass (the pass is HBM-bound and knows the maximum, so all_bounds after psislw
+ * costs no third read of the weights): d_out_div_partials[6] has the layout of vb_bounds_divergence_partials. */
+size_t vb_psis_div_workspace_bytes(void);
+int vb_psis_write_div(const double* d_lw, double* d_out, long long n_local, long long index0,
+                      const double* d_M, long long count, long long K1, const void* d_tail_ws,
+                      double* d_out_div_partials, void* d_ws, size_t ws_bytes, void* stream);
+int vb_psis_smooth_div(const double* d_lw_in, double* d_lw_out, long long n, double reff,
+                       double* d_out_diag, long long* d_out_tail_idx_or_null,
+                       double* d_out_div_partials_or_null, void* d_ws, size_t ws_bytes, void* stream);
 
 size_t vb_gpd_fit_workspace_bytes(long long n);
 int vb_gpd_fit(const double* d_x_sorted, long long n, double* d_out_k_sigma,

@@ -302,3 +302,36 @@ def test_gpdfit_gpinv_sumlogs(golden, name):
                                    equal_nan=True)
     x = np.random.RandomState(0).randn(100001) * 30
     np.testing.assert_allclose(psis.sumlogs(x), psis_np.sumlogs(x), rtol=1e-13)
+
+
+def test_all_bounds_after_psislw_reuses_the_final_pass_and_matches_the_standalone_kernel():
+    """psislw's normalise pass also takes the alpha = 2 divergence statistics of the raw weights
+    (vb_psis_smooth_div); all_bounds on the same unmodified CUDA tensor must then give what the standalone one-pass
+    kernel gives, and any in-place change of the tensor (or another tensor) must bypass the cached statistics."""
+    import warnings
+    import torch
+    import viabel_b200
+    from viabel_b200 import psis
+    from viabel_b200.psis import _DivCache
+    rs = np.random.RandomState(5)
+    u = rs.rand(300_001)
+    lw = torch.from_numpy(np.log(np.expm1(-0.4 * np.log1p(-u)) / 0.4) - 3.0).cuda()
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        ref = viabel_b200.all_bounds(lw.clone(), moment_bound_fn=lambda p: 3.0 if p == 2 else 27.0, q_var=1.0)
+        assert _DivCache.lookup(lw, 1) is None
+        psis.psislw(lw)
+        assert _DivCache.lookup(lw, 1) is not None
+        got = viabel_b200.all_bounds(lw, moment_bound_fn=lambda p: 3.0 if p == 2 else 27.0, q_var=1.0)
+        for k in ref:
+            np.testing.assert_allclose(got[k], ref[k], rtol=1e-10, err_msg=k)
+        oracle = bounds_np.all_bounds(lw.cpu().numpy(), moment_bound_fn=lambda p: 3.0 if p == 2 else 27.0, q_var=1.0)
+        for k in ref:
+            np.testing.assert_allclose(got[k], oracle[k], rtol=1e-9, err_msg=k)
+        # alpha != 2 never uses it; a modified tensor never uses it
+        d15 = viabel_b200.divergence_bound(lw, alpha=1.5)
+        np.testing.assert_allclose(d15, bounds_np.divergence_bound(lw.cpu().numpy(), alpha=1.5), rtol=1e-10)
+        lw.add_(0.25)
+        assert _DivCache.lookup(lw, 1) is None
+        d2 = viabel_b200.divergence_bound(lw, alpha=2.0)
+        np.testing.assert_allclose(d2, bounds_np.divergence_bound(lw.cpu().numpy(), alpha=2.0), rtol=1e-10)

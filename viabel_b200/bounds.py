@@ -33,14 +33,23 @@ def _divergence_stats(log_weights, alpha, group=None):
     out = torch.empty(8, dtype=torch.float64, device=lw.device)
     ws = WS.get('bounds_div', _lib.lib.vb_bounds_divergence_workspace_bytes(n))
     world, g = _dist_world(group)
-    if world == 1:
+    # statistics psislw's final pass already took over this very tensor (alpha = 2 only): no further pass
+    from .psis import _DivCache
+    cached = _DivCache.lookup(log_weights, world) if (alpha == 2.0 and isinstance(log_weights, torch.Tensor)) else None
+    if world == 1 and cached is not None:
+        _lib.check(_lib.lib.vb_bounds_divergence_merge(ptr(cached), 1, float(alpha), ptr(out), stream_ptr()),
+                   'vb_bounds_divergence_merge')
+    elif world == 1:
         _lib.check(_lib.lib.vb_bounds_divergence(ptr(lw), n, float(alpha), ptr(out), ptr(ws), ws.numel(),
                                                  stream_ptr()), 'vb_bounds_divergence')
     else:
         import torch.distributed as dist
-        part = torch.empty(6, dtype=torch.float64, device=lw.device)
-        _lib.check(_lib.lib.vb_bounds_divergence_partials(ptr(lw), n, float(alpha), ptr(part), ptr(ws), ws.numel(),
-                                                          stream_ptr()), 'vb_bounds_divergence_partials')
+        if cached is not None:
+            part = cached
+        else:
+            part = torch.empty(6, dtype=torch.float64, device=lw.device)
+            _lib.check(_lib.lib.vb_bounds_divergence_partials(ptr(lw), n, float(alpha), ptr(part), ptr(ws), ws.numel(),
+                                                              stream_ptr()), 'vb_bounds_divergence_partials')
         gathered = all_gather_rows(part, world, g)
         _lib.check(_lib.lib.vb_bounds_divergence_merge(ptr(gathered), world, float(alpha), ptr(out), stream_ptr()),
                    'vb_bounds_divergence_merge')

@@ -802,6 +802,97 @@ normalise_kernel(const double* __restrict__ lw, double* __restrict__ out, long l
         for (long long i = gtid; i < n; i += gthreads) out[i] = (lw[i] - M) - lse;
     }
 }
+// P3 + divergence statistics: the normalise pass is HBM-bound with idle issue slots and knows the exact maximum M,
+// so the one-pass statistics of divergence_bound(alpha = 2) (bounds.py:169-176) ride along instead of costing a
+// third read of the weights: per element e = exp(x - M) <= 1, sums of e^2 (= w), e^4 (= w^2), (x - K), (x - K)^2
+// with K = lw[0] as the shift of the variance sums.  Block partials, merged in fixed order by the finish kernel.
+constexpr int kNDThreads = 256;
+__global__ void __launch_bounds__(kNDThreads, 3)
+normalise_div_kernel(const double* __restrict__ lw, double* __restrict__ out, long long n, const double* __restrict__ M_ptr,
+                     const double* __restrict__ lse_ptr, double* __restrict__ block_out /* [grid][4] */) {
+    __shared__ double s_table[64];
+    __shared__ double scratch[32];
+    if (threadIdx.x < 64) s_table[threadIdx.x] = kExp2Table[threadIdx.x];
+    __syncthreads();
+    const double M = *M_ptr, lse = *lse_ptr, K = lw[0];
+    const long long gtid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    const long long gthreads = (long long)gridDim.x * blockDim.x;
+    double a2 = 0.0, a4 = 0.0, b2 = 0.0, b4 = 0.0, sx = 0.0, sxx = 0.0, tx = 0.0, txx = 0.0;
+    auto one = [&](double x, double& s2, double& s4, double& s1, double& s11) -> double {
+        const double d = x - M;
+        const double e = exp_nonpos_flush(d, s_table);
+        const double w = e * e;
+        s2 += w;
+        s4 = fma(w, w, s4);
+        const double c = x - K;
+        s1 += c;
+        s11 = fma(c, c, s11);
+        return d - lse;
+    };
+    if (((reinterpret_cast<uintptr_t>(lw) | reinterpret_cast<uintptr_t>(out)) & 15u) == 0) {
+        const long long n2 = n >> 1;
+        const double2* p = reinterpret_cast<const double2*>(lw);
+        double2* q = reinterpret_cast<double2*>(out);
+        long long i = gtid;
+        // software pipeline: the next round's four 16-byte loads are in flight while this round's eight exponentials
+        // are evaluated (without it the pass alternates between a memory phase and a compute phase)
+        double2 v0, v1, v2, v3;
+        bool have = i + 3 * gthreads < n2;
+        if (have) {
+            v0 = ld_stream2(p + i); v1 = ld_stream2(p + i + gthreads);
+            v2 = ld_stream2(p + i + 2 * gthreads); v3 = ld_stream2(p + i + 3 * gthreads);
+        }
+        while (have) {
+            const long long nx = i + 4 * gthreads;
+            const bool more = nx + 3 * gthreads < n2;
+            double2 w0, w1, w2, w3;
+            if (more) {
+                w0 = ld_stream2(p + nx); w1 = ld_stream2(p + nx + gthreads);
+                w2 = ld_stream2(p + nx + 2 * gthreads); w3 = ld_stream2(p + nx + 3 * gthreads);
+            }
+            v0.x = one(v0.x, a2, a4, sx, sxx); v0.y = one(v0.y, b2, b4, tx, txx);
+            v1.x = one(v1.x, a2, a4, sx, sxx); v1.y = one(v1.y, b2, b4, tx, txx);
+            v2.x = one(v2.x, a2, a4, sx, sxx); v2.y = one(v2.y, b2, b4, tx, txx);
+            v3.x = one(v3.x, a2, a4, sx, sxx); v3.y = one(v3.y, b2, b4, tx, txx);
+            q[i] = v0; q[i + gthreads] = v1; q[i + 2 * gthreads] = v2; q[i + 3 * gthreads] = v3;
+            i = nx;
+            have = more;
+            if (more) { v0 = w0; v1 = w1; v2 = w2; v3 = w3; }
+        }
+        for (; i < n2; i += gthreads) {
+            double2 v = ld_stream2(p + i);
+            v.x = one(v.x, a2, a4, sx, sxx); v.y = one(v.y, b2, b4, tx, txx);
+            q[i] = v;
+        }
+        if ((n & 1) && gtid == 0) out[n - 1] = one(lw[n - 1], a2, a4, sx, sxx);
+    } else {
+        for (long long i = gtid; i < n; i += gthreads) out[i] = one(lw[i], a2, a4, sx, sxx);
+    }
+    double r[4] = {a2 + b2, a4 + b4, sx + tx, sxx + txx};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) r[k] = block_sum(r[k], scratch);
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) block_out[(size_t)blockIdx.x * 4 + k] = r[k];
+    }
+}
+// partials[6] in the layout of vb_bounds_divergence_partials: max, sum w, sum w^2, count, mean lw, M2 lw
+__global__ void __launch_bounds__(256)
+normalise_div_finish_kernel(const double* __restrict__ lw, const double* __restrict__ blocks, int G, long long n,
+                            const double* __restrict__ M_ptr, double* __restrict__ out) {
+    __shared__ double scratch[32];
+    double acc[4] = {0, 0, 0, 0};
+    for (int b = threadIdx.x; b < G; b += blockDim.x)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) acc[k] += blocks[(size_t)b * 4 + k];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) acc[k] = block_sum(acc[k], scratch);
+    if (threadIdx.x != 0) return;
+    const double cnt = (double)n;
+    out[0] = *M_ptr; out[1] = acc[0]; out[2] = acc[1]; out[3] = cnt;
+    out[4] = lw[0] + acc[2] / cnt;
+    out[5] = acc[3] - acc[2] * acc[2] / cnt;
+}
 __global__ void tail_scatter_kernel(const Cand* __restrict__ sorted, const long long* __restrict__ counts,
                                     const double* __restrict__ tail_new, const double* __restrict__ state,
                                     double* __restrict__ out, long long index0, long long n_local) {
@@ -1219,11 +1310,36 @@ extern "C" int vb_psis_write(const double* d_lw, double* d_out, long long n_loca
     return VB_OK;
 }
 
+// S6 with the alpha = 2 divergence partials of the RAW weights of this shard (relative to the global maximum M)
+extern "C" size_t vb_psis_div_workspace_bytes(void) { return (size_t)kNumSMs * 8 * 4 * sizeof(double) + 256; }
+extern "C" int vb_psis_write_div(const double* d_lw, double* d_out, long long n_local, long long index0,
+                                 const double* d_M, long long count, long long K1, const void* d_tail_ws,
+                                 double* d_out_div_partials, void* d_ws, size_t ws_bytes, void* stream) {
+    if (!d_lw || !d_out || !d_M || !d_tail_ws || !d_out_div_partials || !d_ws || n_local < 1 || d_lw == d_out) return VB_ERR_ARG;
+    if (ws_bytes < vb_psis_div_workspace_bytes()) return VB_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    const TailLayout L = tail_layout(count, K1);
+    const char* ws = (const char*)(((uintptr_t)d_tail_ws + 255) & ~(uintptr_t)255);
+    const double* state = (const double*)(ws + L.off_state);
+    const long long* counts = (const long long*)(ws + L.off_counts);
+    const Cand* sort_buf = (const Cand*)(ws + L.off_sort);
+    const double* tail_new = (const double*)(ws + L.off_tailnew);
+    double* blocks = (double*)(((uintptr_t)d_ws + 255) & ~(uintptr_t)255);
+    const int G = grid_for((n_local + 1) / 2, kNDThreads, kNumSMs * 8);
+    normalise_div_kernel<<<G, kNDThreads, 0, st>>>(d_lw, d_out, n_local, d_M, state + 5, blocks);
+    VB_LAUNCH_CHECK();
+    normalise_div_finish_kernel<<<1, 256, 0, st>>>(d_lw, blocks, G, n_local, d_M, d_out_div_partials);
+    VB_LAUNCH_CHECK();
+    tail_scatter_kernel<<<kSmallGrid, 256, 0, st>>>(sort_buf, counts, tail_new, state, d_out, index0, n_local);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+
 // ---- single-GPU composite: psislw for one column
 namespace vb {
 struct SmoothLayout {
     long long cap1;
-    size_t off_sample, off_pivot, off_count, off_bodymax, off_terms, off_filter, off_cand1, off_tail, total;
+    size_t off_sample, off_pivot, off_count, off_bodymax, off_terms, off_filter, off_cand1, off_tail, off_div, total;
 };
 static SmoothLayout smooth_layout(long long n, double reff) {
     SmoothLayout L;
@@ -1242,6 +1358,7 @@ static SmoothLayout smooth_layout(long long n, double reff) {
     L.off_filter = take(vb_psis_filter_workspace_bytes(n));
     L.off_cand1 = take((size_t)L.cap1 * sizeof(Cand));
     L.off_tail = take(vb_psis_tail_workspace_bytes(L.cap1, K1));
+    L.off_div = take(vb_psis_div_workspace_bytes());
     L.total = o;
     return L;
 }
@@ -1252,9 +1369,19 @@ extern "C" size_t vb_psis_smooth_workspace_bytes(long long n, double reff) {
     return smooth_layout(n, reff).total + 256;
 }
 
+extern "C" int vb_psis_smooth_div(const double* d_lw_in, double* d_lw_out, long long n, double reff,
+                                  double* d_out_diag, long long* d_out_tail_idx_or_null,
+                                  double* d_out_div_partials_or_null, void* d_ws, size_t ws_bytes, void* stream);
 extern "C" int vb_psis_smooth(const double* d_lw_in, double* d_lw_out, long long n, double reff,
                               double* d_out_diag, long long* d_out_tail_idx_or_null,
                               void* d_ws, size_t ws_bytes, void* stream) {
+    return vb_psis_smooth_div(d_lw_in, d_lw_out, n, reff, d_out_diag, d_out_tail_idx_or_null, nullptr, d_ws, ws_bytes, stream);
+}
+// vb_psis_smooth that also returns, from the same final pass over the weights, the one-pass statistics
+// divergence_bound(alpha = 2) needs (layout of vb_bounds_divergence_partials; finalise with vb_bounds_divergence_merge)
+extern "C" int vb_psis_smooth_div(const double* d_lw_in, double* d_lw_out, long long n, double reff,
+                                  double* d_out_diag, long long* d_out_tail_idx_or_null,
+                                  double* d_out_div_partials_or_null, void* d_ws, size_t ws_bytes, void* stream) {
     if (!d_lw_in || !d_lw_out || !d_out_diag || !d_ws || !(reff > 0.0)) return VB_ERR_ARG;
     if (n <= 1) return VB_ERR_ARG;                                    // psis.py:143-144
     if (d_lw_in == d_lw_out) return VB_ERR_ARG;                       // streaming loads assume no aliasing
@@ -1306,6 +1433,9 @@ extern "C" int vb_psis_smooth(const double* d_lw_in, double* d_lw_out, long long
     rc = vb_psis_tail(cand1, C1, K1, M_ptr, pivot_x, terms, 1, d_out_diag, d_out_tail_idx_or_null,
                       ws + L.off_tail, vb_psis_tail_workspace_bytes(L.cap1, K1), stream);
     if (rc != VB_OK) return rc;
+    if (d_out_div_partials_or_null)
+        return vb_psis_write_div(d_lw_in, d_lw_out, n, 0, M_ptr, C1, K1, ws + L.off_tail, d_out_div_partials_or_null,
+                                 ws + L.off_div, vb_psis_div_workspace_bytes(), stream);
     return vb_psis_write(d_lw_in, d_lw_out, n, 0, M_ptr, C1, K1, ws + L.off_tail, stream);
 }
 

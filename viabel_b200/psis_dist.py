@@ -114,10 +114,16 @@ class CudaStages:
         return diag, tail_idx, (ws, count, K1)
 
     def write(self, lw, index0, M, handle):
+        """S6; also leaves this shard's divergence partials (alpha = 2, relative to the global maximum) in
+        ``self.last_div``: taken in the same pass over the weights."""
         ws, count, K1 = handle
         out = torch.empty_like(lw)
-        _lib.check(_lib.lib.vb_psis_write(self._p(lw), self._p(out), lw.numel(), index0, self._p(M), count, K1,
-                                          self._p(ws), self._stream()), 'vb_psis_write')
+        part = self.empty((6,), torch.float64)
+        dws = self.ws.get('div', _lib.lib.vb_psis_div_workspace_bytes())
+        _lib.check(_lib.lib.vb_psis_write_div(self._p(lw), self._p(out), lw.numel(), index0, self._p(M), count, K1,
+                                              self._p(ws), self._p(part), self._p(dws), dws.numel(), self._stream()),
+                   'vb_psis_write_div')
+        self.last_div = part
         return out
 
 
@@ -147,7 +153,7 @@ class DistComm:
         return t
 
 
-def psislw_sharded(lw_local, Reff=1.0, group=None, stages=None, want_detail=False, comm=None):
+def psislw_sharded(lw_local, Reff=1.0, group=None, stages=None, want_detail=False, comm=None, src=None):
     """Sharded ``psislw`` (``psis.py:112-208``) of one weight column.
 
     ``lw_local``: this rank's contiguous slice (float64, on the stages' device).  Returns
@@ -167,7 +173,7 @@ def psislw_sharded(lw_local, Reff=1.0, group=None, stages=None, want_detail=Fals
             sizes = [int(v) for v in comm.all_gather(torch.tensor([n_local], dtype=torch.int64, device=dev)).cpu().view(-1).tolist()]
             if key is not None:
                 _SIZES[key] = sizes
-        res = _sharded_with_sizes(st, comm, lw_local, Reff, sizes, want_detail)
+        res = _sharded_with_sizes(st, comm, lw_local, Reff, sizes, want_detail, src)
         if res is not None:
             return res
         sizes = None                       # some rank's shard changed since the sizes were cached
@@ -179,7 +185,7 @@ def psislw_sharded(lw_local, Reff=1.0, group=None, stages=None, want_detail=Fals
 _SIZES = {}
 
 
-def _sharded_with_sizes(st, comm, lw_local, Reff, sizes, want_detail):
+def _sharded_with_sizes(st, comm, lw_local, Reff, sizes, want_detail, src=None):
     world, rank = comm.world, comm.rank
     n_local = int(lw_local.numel())
     dev = lw_local.device
@@ -253,6 +259,9 @@ def _sharded_with_sizes(st, comm, lw_local, Reff, sizes, want_detail):
     total2 = sum(counts)
     diag, tail_idx, handle = st.tail(all_cands, total2, K1, M, pivot, all_terms, want_tail_idx=want_detail)
     out = st.write(lw_local, index0, M, handle)
+    if src is not None and getattr(st, 'last_div', None) is not None:
+        from .psis import _DivCache                      # the caller's tensor: all_bounds(lw, group=...) reuses the pass
+        _DivCache.store(src, st.last_div, world)
     n = sum(sizes)
     d = diag.cpu().numpy()
     if not want_detail:
