@@ -437,6 +437,33 @@ int vb_psis_write(const double* d_lw, double* d_out, long long n_local, long lon
 /* S6 / the single-GPU composite with the one-pass statistics of divergence_bound(alpha = 2) (bounds.py:169-176) of the
  * RAW weights taken in the same final pass (the pass is HBM-bound and knows the maximum, so all_bounds after psislw
  * costs no third read of the weights): d_out_div_partials[6] has the layout of vb_bounds_divergence_partials. */
+/* S5 with the candidate count in device memory (at most `cap` entries in d_cands): no host read between the
+ * stages.  d_count1 / cap1 (optional): count and capacity of the filter pass that produced the candidates, checked
+ * on the device too.  When a precondition fails (fewer than K1 + 1 candidates, a buffer overflow, a refinement bin
+ * too large for the per-warp ranking) the remaining kernels are inert and d_out_diag[7] = -(status code): run the
+ * host-driven vb_psis_tail then.  Workspace: vb_psis_tail_workspace_bytes(cap, K1). */
+int vb_psis_tail_dev(const void* d_cands, long long cap, const unsigned long long* d_count, long long K1,
+                     const double* d_M, const double* d_pivot_x, const double* d_terms, int n_terms,
+                     const unsigned long long* d_count1, long long cap1, const int* d_status_in_or_null,
+                     double* d_out_diag, long long* d_out_tail_idx_or_null,
+                     void* d_ws, size_t ws_bytes, void* stream);
+/* Device-driven stages of the SHARDED protocol (no rank waits on a host read; replaces the count exchanges around
+ * notebooks/psis.py:165-200).  vb_psis_prepare_hist_dev = S4 + this rank's refinement histogram with the candidate
+ * count in device memory; vb_psis_refine_select_dev cuts at the global threshold straight into a fixed-capacity
+ * exchange slot of capx + 3 rows of 16 bytes: candidates | (term0, term1) | (kept count, flags) | (shard size,
+ * filter count); vb_psis_gather_compact turns the all-gathered slots (world, capx + 3) into the dense candidate
+ * list in rank order, the body terms in rank order, the total and a status (any rank's flag, a changed shard size,
+ * a total beyond capx) that vb_psis_tail_dev takes as d_status_in. */
+int vb_psis_prepare_hist_dev(void* d_cand, long long cap, const unsigned long long* d_count, const double* d_M,
+                             const double* d_pivot_x, const double* d_body_pre, double* d_out_term0,
+                             unsigned int* d_hist, void* d_ws, size_t ws_bytes, void* stream);
+int vb_psis_refine_select_dev(const void* d_cand, long long cap, const unsigned long long* d_count,
+                              const double* d_M, const double* d_pivot_x, const unsigned int* d_hist_global,
+                              long long keep_global, void* d_send, long long capx, double* d_terms,
+                              long long n_local, void* d_ws, size_t ws_bytes, void* stream);
+int vb_psis_gather_compact(const void* d_recv, int world, long long capx, const long long* d_sizes_or_null,
+                           void* d_out_cands, unsigned long long* d_out_total, double* d_out_terms,
+                           int* d_out_status, void* stream);
 size_t vb_psis_div_workspace_bytes(void);
 int vb_psis_write_div(const double* d_lw, double* d_out, long long n_local, long long index0,
                       const double* d_M, long long count, long long K1, const void* d_tail_ws,

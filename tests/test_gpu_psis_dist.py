@@ -113,3 +113,33 @@ def test_sharded_matches_single_gpu_path_bitwise_on_indices():
     np.testing.assert_array_equal(dets[2]['tail_idx_sorted'], det1['tail_idx_sorted'])
     np.testing.assert_allclose(kh, k1, rtol=1e-12)
     np.testing.assert_allclose(out, out1, rtol=1e-11, atol=1e-11)
+
+
+def test_device_driven_protocol_is_taken_and_falls_back_on_ties(monkeypatch):
+    """The device-driven protocol (no host read between stages) runs for large tie-free inputs; heavy ties in one
+    refinement bin make its on-device check fail and the call falls back to the host-driven protocol; VB_PSIS_HOST=1
+    forces the host-driven one.  All three give the oracle's result."""
+    from viabel_b200 import psis_dist
+    lw = gpd_lw(2_000_000, 0.5, 5)
+    oout, ok, odet = _quiet(psis_np.psislw_detail, lw, sort_kind='stable')
+    out, kh, dets = run_virtual(lw, 8)
+    assert psis_dist.PATH_TAKEN[0] == 'dev'
+    np.testing.assert_array_equal(dets[5]['tail_idx_sorted'], odet['tailinds'][odet['tail_order']])
+    np.testing.assert_allclose(out, oout, rtol=1e-9, atol=1e-9)
+    monkeypatch.setenv('VB_PSIS_HOST', '1')
+    out_h, kh_h, dets_h = run_virtual(lw, 8)
+    assert psis_dist.PATH_TAKEN[0] == 'host'
+    np.testing.assert_array_equal(dets_h[0]['tail_idx_sorted'], dets[0]['tail_idx_sorted'])
+    np.testing.assert_allclose(out_h, out, rtol=1e-12, atol=1e-12)
+    np.testing.assert_allclose(kh_h, kh, rtol=1e-12)
+    monkeypatch.delenv('VB_PSIS_HOST')
+    tied = np.round(gpd_lw(400000, 0.6, 11), 2)
+    out_t, kh_t, dets_t = run_virtual(tied, 3)               # ties, but no refinement bin above 512 entries
+    oout_t, ok_t, odet_t = _quiet(psis_np.psislw_detail, tied, sort_kind='stable')
+    np.testing.assert_array_equal(dets_t[0]['tail_idx_sorted'], odet_t['tailinds'][odet_t['tail_order']])
+    tied[np.random.RandomState(1).randint(0, len(tied), 1000)] = tied.max()      # 1000 copies of the maximum: one bin overflows
+    out_t, kh_t, dets_t = run_virtual(tied, 3)
+    assert psis_dist.PATH_TAKEN[0] == 'dev->host'
+    oout_t, ok_t, odet_t = _quiet(psis_np.psislw_detail, tied, sort_kind='stable')
+    np.testing.assert_array_equal(dets_t[0]['tail_idx_sorted'], odet_t['tailinds'][odet_t['tail_order']])
+    np.testing.assert_allclose(out_t, oout_t, rtol=1e-9, atol=1e-9)

@@ -92,6 +92,10 @@ SIGNATURES = {
     'vb_psis_tail_workspace_bytes': (_sz, [_ll, _ll]),
     'vb_psis_tail': (_i, [_p, _ll, _ll, _p, _p, _p, _i, _p, _p, _p, _sz, _p]),
     'vb_psis_write': (_i, [_p, _p, _ll, _ll, _p, _ll, _ll, _p, _p]),
+    'vb_psis_tail_dev': (_i, [_p, _ll, _p, _ll, _p, _p, _p, _i, _p, _ll, _p, _p, _p, _p, _sz, _p]),
+    'vb_psis_prepare_hist_dev': (_i, [_p, _ll, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    'vb_psis_refine_select_dev': (_i, [_p, _ll, _p, _p, _p, _p, _ll, _p, _ll, _p, _ll, _p, _sz, _p]),
+    'vb_psis_gather_compact': (_i, [_p, _i, _ll, _p, _p, _p, _p, _p, _p]),
     'vb_psis_div_workspace_bytes': (_sz, []),
     'vb_psis_write_div': (_i, [_p, _p, _ll, _ll, _p, _ll, _ll, _p, _p, _p, _sz, _p]),
     'vb_psis_smooth_div': (_i, [_p, _p, _ll, _d, _p, _p, _p, _p, _sz, _p]),

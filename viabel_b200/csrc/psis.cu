@@ -341,9 +341,19 @@ filter_finish_kernel(const double* __restrict__ block_body, const double* __rest
     m = block_max(m, scratch);
     if (threadIdx.x == 0) { *out_body = s; *out_max = m; }
 }
+// Device-driven counts: a kernel given `cnt_ptr` takes the element count from device memory (clamped to the buffer
+// capacity passed as `count`), so that no host read sits between the stages; null = the host value.
+__device__ __forceinline__ long long dev_count(long long count, const unsigned long long* cnt_ptr) {
+    if (!cnt_ptr) return count;
+    const unsigned long long c = *cnt_ptr;
+    return c < (unsigned long long)count ? (long long)c : count;
+}
+
 // Once the (global) maximum M is known: candidate keys become ~bits(M - x) (the reference sorts the
 // SHIFTED weights, psis.py:165-167), pivot_u = M - pivot_x, and the body sum is rescaled to M.
-__global__ void rekey_kernel(Cand* __restrict__ cand, long long count, const double* __restrict__ M_ptr) {
+__global__ void rekey_kernel(Cand* __restrict__ cand, long long count, const double* __restrict__ M_ptr,
+                             const unsigned long long* __restrict__ cnt_ptr = nullptr) {
+    count = dev_count(count, cnt_ptr);
     const double M = *M_ptr;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < count;
          i += (long long)gridDim.x * blockDim.x)
@@ -362,7 +372,8 @@ __global__ void derive_kernel(const double* __restrict__ M_ptr, const double* __
 // ------------------------------------------------------------------------------------------ refinement histogram
 __global__ void __launch_bounds__(512)
 hist_kernel(const Cand* __restrict__ cand, long long count, const double* __restrict__ pivot_ptr,
-            unsigned int* __restrict__ hist) {
+            unsigned int* __restrict__ hist, const unsigned long long* __restrict__ cnt_ptr = nullptr) {
+    count = dev_count(count, cnt_ptr);
     __shared__ unsigned int sh[kHistBins];
     for (int b = threadIdx.x; b < kHistBins; b += blockDim.x) sh[b] = 0;
     __syncthreads();
@@ -423,8 +434,10 @@ hist_scan_kernel(const unsigned int* __restrict__ hist, long long target, long l
 __global__ void __launch_bounds__(256)
 compact2_kernel(const Cand* __restrict__ cand, long long count, const double* __restrict__ pivot_ptr,
                 const long long* __restrict__ bstar_ptr, Cand* __restrict__ out, unsigned long long* __restrict__ counter,
-                double* __restrict__ block_body) {
+                double* __restrict__ block_body, const unsigned long long* __restrict__ cnt_ptr = nullptr,
+                long long out_cap = 0x7fffffffffffffffll) {
     __shared__ double scratch[32];
+    count = dev_count(count, cnt_ptr);
     const double pivot = *pivot_ptr;
     const double scale = (pivot > 0.0 && isfinite(pivot)) ? (double)kHistBins / pivot : 0.0;
     const long long bstar = *bstar_ptr;
@@ -452,7 +465,8 @@ compact2_kernel(const Cand* __restrict__ cand, long long count, const double* __
             unsigned long long basepos = 0;
             if (lane == leader) basepos = atomicAdd(counter, (unsigned long long)__popc(mask));
             basepos = __shfl_sync(0xffffffffu, basepos, leader);
-            if (keep) out[basepos + __popc(mask & ((1u << lane) - 1))] = c;
+            const unsigned long long pos = basepos + __popc(mask & ((1u << lane) - 1));
+            if (keep && (long long)pos < out_cap) out[pos] = c;      // the counter still counts what did not fit
         }
     }
     body = block_sum(body, scratch);
@@ -516,6 +530,24 @@ bin_scan_kernel(const unsigned int* __restrict__ hist, const long long* __restri
         run += c[b];
     }
 }
+// Preconditions of the device-driven tail (the host-driven path decides these from three host reads):
+//   K1 + 1 <= C1 <= cap1 (the filter pass found enough candidates and they fit), K1 + 1 <= C2 (kept by the
+//   refinement), every kept bin small enough for the per-warp ranking, histogram total == kept count.
+__global__ void psis_check_kernel(const unsigned long long* __restrict__ c1_ptr, long long cap1,
+                                  const unsigned long long* __restrict__ c2_ptr, const long long* __restrict__ meta,
+                                  long long K1, int max_bin, int* __restrict__ status,
+                                  const int* __restrict__ status_in = nullptr) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const unsigned long long c1 = *c1_ptr, c2 = *c2_ptr;
+    int st = 0;
+    if (status_in && *status_in) st = *status_in;              // raised by an earlier stage (any rank)
+    else if (c1 < (unsigned long long)(K1 + 1)) st = 1;
+    else if (c1 > (unsigned long long)cap1) st = 2;
+    else if (c2 < (unsigned long long)(K1 + 1) || c2 > c1) st = 3;
+    else if (meta[0] > max_bin) st = 4;
+    else if ((unsigned long long)meta[1] != c2) st = 5;
+    *status = st;
+}
 __device__ __forceinline__ int cand_bin(const Cand& c, double scale) {
     long long b = (long long)(key_to_u(c.key) * scale);         // same expression as hist_kernel
     return (int)(b > kHistBins - 1 ? kHistBins - 1 : b);
@@ -523,7 +555,9 @@ __device__ __forceinline__ int cand_bin(const Cand& c, double scale) {
 // dst[total - offsets[b + 1] + slot]: bins in descending order, arbitrary order inside a bin
 __global__ void __launch_bounds__(256)
 bin_scatter_kernel(const Cand* __restrict__ src, const long long* __restrict__ meta, const double* __restrict__ pivot_ptr,
-                   const unsigned int* __restrict__ offsets, unsigned int* __restrict__ cursor, Cand* __restrict__ dst) {
+                   const unsigned int* __restrict__ offsets, unsigned int* __restrict__ cursor, Cand* __restrict__ dst,
+                   const int* __restrict__ status = nullptr) {
+    if (status && *status) return;
     const double pivot = *pivot_ptr;
     const double scale = (pivot > 0.0 && isfinite(pivot)) ? (double)kHistBins / pivot : 0.0;
     const long long total = meta[1];
@@ -538,7 +572,8 @@ bin_scatter_kernel(const Cand* __restrict__ src, const long long* __restrict__ m
 // one warp per bin: rank of every element among the bin's elements by (key, index)
 __global__ void __launch_bounds__(256)
 bin_rank_kernel(const Cand* __restrict__ src, const long long* __restrict__ meta, const long long* __restrict__ bstar_ptr,
-                const unsigned int* __restrict__ offsets, Cand* __restrict__ dst) {
+                const unsigned int* __restrict__ offsets, Cand* __restrict__ dst, const int* __restrict__ status = nullptr) {
+    if (status && *status) return;
     const long long total = meta[1];
     const int n_bins = (int)((bstar_ptr ? *bstar_ptr : (long long)kHistBins - 1) + 1);
     const int lane = threadIdx.x & 31;
@@ -563,8 +598,15 @@ bin_rank_kernel(const Cand* __restrict__ src, const long long* __restrict__ meta
 // counts[] (long long): [0] n2  [1] first tail position p in the sorted candidates  [2] m (quadrature points)
 //                       [3] 1 when the GPD fit runs (psislw: n2 > 4, psis.py:177)
 __global__ void tail_bounds_kernel(const Cand* __restrict__ sorted, long long count, long long K1,
-                                   double* __restrict__ state, long long* __restrict__ counts) {
+                                   double* __restrict__ state, long long* __restrict__ counts,
+                                   const unsigned long long* __restrict__ cnt_ptr = nullptr,
+                                   const int* __restrict__ status = nullptr) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    if (status && *status) {                       // device-driven path found its preconditions violated: inert state
+        state[0] = 0.0; state[1] = 1.0; counts[0] = 0; counts[1] = 0; counts[2] = 30; counts[3] = 0;
+        return;
+    }
+    count = dev_count(count, cnt_ptr);
     // (K1+1)-th largest shifted weight == (K1+1)-th smallest u == sorted[count-1-K1]   (psis.py:157,169)
     const double u_cut = key_to_u(sorted[count - 1 - K1].key);
     const double xcut = fmax(-u_cut, -kNegLogTiny);                  // psis.py:169-172
@@ -755,8 +797,11 @@ struct SumList { const double* p[4]; int n[4]; };
 __global__ void __launch_bounds__(256)
 psis_finish_kernel(SumList lists, const double* __restrict__ M_ptr, const long long* __restrict__ counts,
                                    long long n_cand, double* __restrict__ state, double* __restrict__ diag,
-                                   double* __restrict__ lse_partial_or_null) {
+                                   double* __restrict__ lse_partial_or_null,
+                                   const unsigned long long* __restrict__ cnt_ptr = nullptr,
+                                   const int* __restrict__ status = nullptr) {
     __shared__ double scratch[32];
+    n_cand = dev_count(n_cand, cnt_ptr);
     double total = 0.0;
     for (int l = 0; l < 4; ++l) {                  // fixed tree per list, lists added in order
         double part = 0.0;
@@ -770,6 +815,7 @@ psis_finish_kernel(SumList lists, const double* __restrict__ M_ptr, const long l
     if (diag) {
         diag[0] = state[2]; diag[1] = state[3]; diag[2] = state[0]; diag[3] = (double)counts[0];
         diag[4] = state[4]; diag[5] = *M_ptr; diag[6] = lse; diag[7] = (double)n_cand;
+        if (status && *status) diag[7] = -(double)*status;       // device-driven path: the caller must take the host-driven one
     }
 }
 
@@ -1069,17 +1115,18 @@ __global__ void pivot_u_kernel(const double* M, const double* px, double* out) {
 }
 // keep the ~`keep` largest of `count` re-keyed candidates (histogram of u); the dropped ones add exp(-u) to *out_term
 static int refine_to(const Cand* in, long long count, const double* d_M, const double* d_pivot_x, long long keep,
-                     Cand* out, unsigned long long* d_out_count, double* d_out_term, char* ws, cudaStream_t st) {
+                     Cand* out, unsigned long long* d_out_count, double* d_out_term, char* ws, cudaStream_t st,
+                     const unsigned long long* cnt_ptr = nullptr) {
     const RefineWs r = refine_ws(ws);
     pivot_u_kernel<<<1, 1, 0, st>>>(d_M, d_pivot_x, r.pivot_u);
     VB_LAUNCH_CHECK();
     VB_CUDA_TRY(cudaMemsetAsync(r.hist, 0, (size_t)kHistBins * 4, st));
     VB_CUDA_TRY(cudaMemsetAsync(d_out_count, 0, 8, st));
-    hist_kernel<<<grid_for(count, 512 * 8, kNumSMs), 512, 0, st>>>(in, count, r.pivot_u, r.hist);
+    hist_kernel<<<grid_for(count, 512 * 8, kNumSMs), 512, 0, st>>>(in, count, r.pivot_u, r.hist, cnt_ptr);
     VB_LAUNCH_CHECK();
     hist_scan_kernel<<<1, 1024, 0, st>>>(r.hist, keep, r.counts2);
     VB_LAUNCH_CHECK();
-    compact2_kernel<<<kSmallGrid, 256, 0, st>>>(in, count, r.pivot_u, r.counts2, out, d_out_count, r.blk);
+    compact2_kernel<<<kSmallGrid, 256, 0, st>>>(in, count, r.pivot_u, r.counts2, out, d_out_count, r.blk, cnt_ptr);
     VB_LAUNCH_CHECK();
     sum_blocks_kernel<<<1, 256, 0, st>>>(r.blk, kSmallGrid, d_out_term);
     VB_LAUNCH_CHECK();
@@ -1147,6 +1194,107 @@ extern "C" int vb_psis_refine_select(const void* d_cand, long long count, const 
                                                 d_out_count, r.blk);
     VB_LAUNCH_CHECK();
     sum_blocks_kernel<<<1, 256, 0, st>>>(r.blk, kSmallGrid, d_out_term);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+
+// ---- S4 / S4b with the candidate count in device memory (sharded, device-driven protocol: viabel_b200/psis_dist.py)
+// prepare + local histogram: keys relative to the global maximum, term0, this rank's 8192 bin counters
+extern "C" int vb_psis_prepare_hist_dev(void* d_cand, long long cap, const unsigned long long* d_count, const double* d_M,
+                                        const double* d_pivot_x, const double* d_body_pre, double* d_out_term0,
+                                        unsigned int* d_hist, void* d_ws, size_t ws_bytes, void* stream) {
+    if (!d_cand || !d_count || !d_M || !d_pivot_x || !d_body_pre || !d_out_term0 || !d_hist || !d_ws || cap < 1) return VB_ERR_ARG;
+    if (ws_bytes < vb_psis_refine_workspace_bytes()) return VB_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    const RefineWs r = refine_ws((char*)d_ws);
+    rekey_kernel<<<grid_for(cap, 256, kNumSMs * 4), 256, 0, st>>>((Cand*)d_cand, cap, d_M, d_count);
+    VB_LAUNCH_CHECK();
+    derive_kernel<<<1, 1, 0, st>>>(d_M, d_pivot_x, d_body_pre, r.pivot_u, d_out_term0);
+    VB_LAUNCH_CHECK();
+    VB_CUDA_TRY(cudaMemsetAsync(d_hist, 0, (size_t)kHistBins * 4, st));
+    hist_kernel<<<grid_for(cap, 512 * 8, kNumSMs), 512, 0, st>>>((const Cand*)d_cand, cap, r.pivot_u, d_hist, d_count);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+// send buffer layout (rows of two 64-bit words): [0, capx) kept candidates | row capx: (term0, term1) |
+// row capx + 1: (kept count, flags << 32 | 0) | row capx + 2: (shard size, filter count)
+__global__ void send_header_kernel(Cand* __restrict__ send, long long capx, const double* __restrict__ terms,
+                                   const unsigned long long* __restrict__ kept, const unsigned long long* __restrict__ c1,
+                                   long long cap1, long long n_local) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    unsigned long long flags = 0;
+    if (*c1 > (unsigned long long)cap1) flags = 2;                   // the filter pass overflowed this rank's buffer
+    else if (*kept > (unsigned long long)capx) flags = 7;            // kept more than the exchange slot holds
+    send[capx].key = (unsigned long long)__double_as_longlong(terms[0]);
+    send[capx].idx = (unsigned long long)__double_as_longlong(terms[1]);
+    send[capx + 1].key = *kept;
+    send[capx + 1].idx = flags;
+    send[capx + 2].key = (unsigned long long)n_local;
+    send[capx + 2].idx = *c1;
+}
+extern "C" int vb_psis_refine_select_dev(const void* d_cand, long long cap, const unsigned long long* d_count,
+                                         const double* d_M, const double* d_pivot_x, const unsigned int* d_hist_global,
+                                         long long keep_global, void* d_send, long long capx, double* d_terms,
+                                         long long n_local, void* d_ws, size_t ws_bytes, void* stream) {
+    if (!d_cand || !d_count || !d_M || !d_pivot_x || !d_hist_global || !d_send || !d_terms || !d_ws || cap < 1 || capx < 1 ||
+        keep_global < 1)
+        return VB_ERR_ARG;
+    if (ws_bytes < vb_psis_refine_workspace_bytes()) return VB_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    const RefineWs r = refine_ws((char*)d_ws);
+    unsigned long long* kept = (unsigned long long*)(r.counts2 + 8);          // spare words of the 256-byte counts2 block
+    VB_CUDA_TRY(cudaMemsetAsync(kept, 0, 8, st));
+    hist_scan_kernel<<<1, 1024, 0, st>>>(d_hist_global, keep_global, r.counts2);
+    VB_LAUNCH_CHECK();
+    compact2_kernel<<<kSmallGrid, 256, 0, st>>>((const Cand*)d_cand, cap, r.pivot_u, r.counts2, (Cand*)d_send, kept, r.blk,
+                                                d_count, capx);
+    VB_LAUNCH_CHECK();
+    sum_blocks_kernel<<<1, 256, 0, st>>>(r.blk, kSmallGrid, d_terms + 1);
+    VB_LAUNCH_CHECK();
+    send_header_kernel<<<1, 1, 0, st>>>((Cand*)d_send, capx, d_terms, kept, d_count, cap, n_local);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+// recv (world, capx + 3, 2 words) -> dense candidate list in rank order, the 2 * world body terms in rank order, the
+// total count and a status: any rank's flag, a shard size that differs from the expected one, or a total that does
+// not fit capx
+__global__ void __launch_bounds__(256)
+gather_compact_kernel(const Cand* __restrict__ recv, int world, long long capx, const long long* __restrict__ sizes,
+                      Cand* __restrict__ out, unsigned long long* __restrict__ total_out, double* __restrict__ terms_out,
+                      int* __restrict__ status_out) {
+    const long long row = capx + 3;
+    long long total = 0;
+    int st = 0;
+    for (int r = 0; r < world; ++r) {
+        const Cand h = recv[r * row + capx + 1];
+        if (h.idx && !st) st = (int)h.idx;
+        if (sizes && (long long)recv[r * row + capx + 2].key != sizes[r] && !st) st = 9;
+        total += (long long)h.key;
+    }
+    if (total > capx && !st) st = 8;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        *total_out = st ? 0ull : (unsigned long long)total;
+        *status_out = st;
+        for (int r = 0; r < world; ++r) {
+            terms_out[2 * r] = __longlong_as_double((long long)recv[r * row + capx].key);
+            terms_out[2 * r + 1] = __longlong_as_double((long long)recv[r * row + capx].idx);
+        }
+    }
+    if (st) return;
+    long long base = 0;
+    for (int r = 0; r < world; ++r) {
+        const long long c = (long long)recv[r * row + capx + 1].key;
+        for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < c; i += (long long)gridDim.x * blockDim.x)
+            out[base + i] = recv[r * row + i];
+        base += c;
+    }
+}
+extern "C" int vb_psis_gather_compact(const void* d_recv, int world, long long capx, const long long* d_sizes_or_null,
+                                      void* d_out_cands, unsigned long long* d_out_total, double* d_out_terms,
+                                      int* d_out_status, void* stream) {
+    if (!d_recv || !d_out_cands || !d_out_total || !d_out_terms || !d_out_status || world < 1 || capx < 1) return VB_ERR_ARG;
+    gather_compact_kernel<<<kSmallGrid, 256, 0, (cudaStream_t)stream>>>((const Cand*)d_recv, world, capx, d_sizes_or_null,
+                                                                      (Cand*)d_out_cands, d_out_total, d_out_terms, d_out_status);
     VB_LAUNCH_CHECK();
     return VB_OK;
 }
@@ -1292,6 +1440,74 @@ extern "C" int vb_psis_tail(const void* d_cands, long long count, long long K1, 
     return VB_OK;
 }
 
+// ---- S5, device-driven: the candidate count stays in device memory (d_count, at most `cap` entries in d_cands) and
+// the decisions the host-driven path takes after reading counts back are replaced by psis_check_kernel: when a
+// precondition fails the remaining kernels turn inert and d_out_diag[7] = -(status) tells the caller to run the
+// host-driven path.  No host read, no synchronisation: ~25 dependent launches go out back to back.
+static int* tail_status_ptr(char* ws, const vb::TailLayout& L) { return (int*)(ws + L.off_meta + 64); }
+extern "C" int vb_psis_tail_dev(const void* d_cands, long long cap, const unsigned long long* d_count, long long K1,
+                                const double* d_M, const double* d_pivot_x, const double* d_terms, int n_terms,
+                                const unsigned long long* d_count1, long long cap1, const int* d_status_in_or_null,
+                                double* d_out_diag, long long* d_out_tail_idx_or_null,
+                                void* d_ws, size_t ws_bytes, void* stream) {
+    if (!d_cands || !d_count || !d_M || !d_pivot_x || !d_terms || !d_out_diag || !d_ws || n_terms < 1 || K1 < 0) return VB_ERR_ARG;
+    if (cap < K1 + 1) return VB_ERR_ARG;
+    if (ws_bytes < vb_psis_tail_workspace_bytes(cap, K1)) return VB_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    const TailLayout L = tail_layout(cap, K1);
+    char* ws = (char*)(((uintptr_t)d_ws + 255) & ~(uintptr_t)255);
+    double* state = (double*)(ws + L.off_state);
+    long long* counts = (long long*)(ws + L.off_counts);
+    unsigned long long* cnt2 = (unsigned long long*)(ws + L.off_cnt2);
+    double* term_ref = (double*)(ws + L.off_term);
+    Cand* sort_buf = (Cand*)(ws + L.off_sort);
+    double* x2 = (double*)(ws + L.off_x2);
+    double* tail_new = (double*)(ws + L.off_tailnew);
+    double* bs = (double*)(ws + L.off_bs);
+    double* Lq = (double*)(ws + L.off_L);
+    double* wq = (double*)(ws + L.off_w);
+    double* blk3 = (double*)(ws + L.off_blk3);
+    double* blk4 = (double*)(ws + L.off_blk4);
+    double* blk5 = (double*)(ws + L.off_blk5);
+    Cand* sort2 = (Cand*)(ws + L.off_sort2);
+    unsigned int* binoff = (unsigned int*)(ws + L.off_binoff);
+    unsigned int* cursor = (unsigned int*)(ws + L.off_cursor);
+    long long* meta = (long long*)(ws + L.off_meta);
+    int* status = tail_status_ptr(ws, L);
+    const RefineWs rw = refine_ws(ws + L.off_refine);
+    int rc = refine_to((const Cand*)d_cands, cap, d_M, d_pivot_x, K1 + 1, sort_buf, cnt2, term_ref, ws + L.off_refine, st,
+                       d_count);
+    if (rc != VB_OK) return rc;
+    bin_scan_kernel<<<1, 1024, 0, st>>>(rw.hist, rw.counts2, binoff, meta);
+    VB_LAUNCH_CHECK();
+    psis_check_kernel<<<1, 1, 0, st>>>(d_count1 ? d_count1 : d_count, d_count1 ? cap1 : cap, cnt2, meta, K1, kBinSortMax, status,
+                                       d_status_in_or_null);
+    VB_LAUNCH_CHECK();
+    VB_CUDA_TRY(cudaMemsetAsync(cursor, 0, (size_t)kHistBins * 4, st));
+    bin_scatter_kernel<<<grid_for(cap, 256, kNumSMs * 4), 256, 0, st>>>(sort_buf, meta, rw.pivot_u, binoff, cursor, sort2, status);
+    VB_LAUNCH_CHECK();
+    bin_rank_kernel<<<kNumSMs * 4, 256, 0, st>>>(sort2, meta, rw.counts2, binoff, sort_buf, status);
+    VB_LAUNCH_CHECK();
+    tail_bounds_kernel<<<1, 1, 0, st>>>(sort_buf, cap, K1, state, counts, cnt2, status);
+    VB_LAUNCH_CHECK();
+    tail_excess_kernel<<<kSmallGrid, 256, 0, st>>>(sort_buf, state, counts, x2);
+    VB_LAUNCH_CHECK();
+    rc = run_gpd_fit(x2, counts, K1 + 1, bs, Lq, wq, blk3, kSmallGrid, state, st);
+    if (rc != VB_OK) return rc;
+    tail_smooth_kernel<<<kSmallGrid, 256, 0, st>>>(sort_buf, state, counts, tail_new, d_out_tail_idx_or_null, blk4);
+    VB_LAUNCH_CHECK();
+    cand_body_kernel<<<kSmallGrid, 256, 0, st>>>(sort_buf, counts, 0, 0x7fffffffffffffffll, blk5);
+    VB_LAUNCH_CHECK();
+    SumList lists;
+    lists.p[0] = d_terms;  lists.n[0] = n_terms;
+    lists.p[1] = term_ref; lists.n[1] = 1;
+    lists.p[2] = blk5;     lists.n[2] = kSmallGrid;
+    lists.p[3] = blk4;     lists.n[3] = kSmallGrid;
+    psis_finish_kernel<<<1, 256, 0, st>>>(lists, d_M, counts, cap, state, d_out_diag, nullptr, cnt2, status);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+
 // ---- S6: out = (x - M) - lse over this shard, then the smoothed tail entries it owns
 extern "C" int vb_psis_write(const double* d_lw, double* d_out, long long n_local, long long index0,
                              const double* d_M, long long count, long long K1, const void* d_tail_ws, void* stream) {
@@ -1401,6 +1617,41 @@ extern "C" int vb_psis_smooth_div(const double* d_lw_in, double* d_lw_out, long 
     if (!direct) {
         rc = vb_psis_sample(d_lw_in, n, 0, sample, stream);
         if (rc != VB_OK) return rc;
+    }
+    // Device-driven attempt: every stage is enqueued without reading a count back; ONE status word is read at the
+    // end (the caller reads the diagnostics then anyway).  Falls through to the host-driven sequence below when a
+    // precondition failed (too few candidates for the first pivot, heavy ties, tiny problems).
+    static const bool host_only = getenv("VB_PSIS_HOST") != nullptr && atoi(getenv("VB_PSIS_HOST")) != 0;
+    if (!direct && !host_only) {
+        double frac0 = 4.0 * (double)(K1 + 1) / (double)n;
+        if (frac0 < 0.01) frac0 = 0.01;
+        rc = vb_psis_pivot(sample, kSampleSize, kSampleSize, frac0, pivot_x, stream);
+        if (rc != VB_OK) return rc;
+        rc = vb_psis_filter(d_lw_in, n, 0, pivot_x, cand1, L.cap1, count, body_max, ws + L.off_filter,
+                            vb_psis_filter_workspace_bytes(n), stream);
+        if (rc != VB_OK) return rc;
+        const double* M_dev = body_max + 1;
+        rekey_kernel<<<grid_for(L.cap1, 256, kNumSMs * 4), 256, 0, st>>>(cand1, L.cap1, M_dev, count);
+        VB_LAUNCH_CHECK();
+        derive_kernel<<<1, 1, 0, st>>>(M_dev, pivot_x, body_max, nullptr, terms);
+        VB_LAUNCH_CHECK();
+        rc = vb_psis_tail_dev(cand1, L.cap1, count, K1, M_dev, pivot_x, terms, 1, nullptr, 0, nullptr, d_out_diag,
+                              d_out_tail_idx_or_null, ws + L.off_tail, vb_psis_tail_workspace_bytes(L.cap1, K1), stream);
+        if (rc != VB_OK) return rc;
+        if (d_out_div_partials_or_null)
+            rc = vb_psis_write_div(d_lw_in, d_lw_out, n, 0, M_dev, L.cap1, K1, ws + L.off_tail, d_out_div_partials_or_null,
+                                   ws + L.off_div, vb_psis_div_workspace_bytes(), stream);
+        else
+            rc = vb_psis_write(d_lw_in, d_lw_out, n, 0, M_dev, L.cap1, K1, ws + L.off_tail, stream);
+        if (rc != VB_OK) return rc;
+        int h_status = 0;
+        {
+            const TailLayout TL = tail_layout(L.cap1, K1);
+            char* tws = (char*)(((uintptr_t)(ws + L.off_tail) + 255) & ~(uintptr_t)255);
+            VB_CUDA_TRY(cudaMemcpyAsync(&h_status, tail_status_ptr(tws, TL), sizeof(int), cudaMemcpyDeviceToHost, st));
+            VB_CUDA_TRY(cudaStreamSynchronize(st));
+        }
+        if (h_status == 0) return VB_OK;
     }
     // filter pass, widening the sample quantile until the candidates hold the K1+1 largest
     long long C1 = 0;

@@ -113,6 +113,45 @@ class CudaStages:
                                          self._stream()), 'vb_psis_tail')
         return diag, tail_idx, (ws, count, K1)
 
+    # ---- device-driven variants: counts stay in device memory, nothing is read back between the stages
+    def prepare_hist_dev(self, cand, count_t, M, pivot, body_max, terms):
+        hist = self.empty((int(_lib.lib.vb_psis_hist_bins()),), torch.int32)
+        ws = self.ws.get('refine', _lib.lib.vb_psis_refine_workspace_bytes())
+        _lib.check(_lib.lib.vb_psis_prepare_hist_dev(self._p(cand), cand.shape[0], self._p(count_t), self._p(M), self._p(pivot),
+                                                     self._p(body_max), self._p(terms), self._p(hist), self._p(ws),
+                                                     ws.numel(), self._stream()), 'vb_psis_prepare_hist_dev')
+        return hist
+
+    def refine_select_dev(self, cand, count_t, M, pivot, hist_global, keep, capx, terms, n_local):
+        send = self.empty((capx + 3, 2), torch.int64)
+        ws = self.ws.get('refine', _lib.lib.vb_psis_refine_workspace_bytes())
+        _lib.check(_lib.lib.vb_psis_refine_select_dev(self._p(cand), cand.shape[0], self._p(count_t), self._p(M),
+                                                      self._p(pivot), self._p(hist_global), keep, self._p(send), capx,
+                                                      self._p(terms), n_local, self._p(ws), ws.numel(), self._stream()),
+                   'vb_psis_refine_select_dev')
+        return send
+
+    def gather_compact(self, recv, world, capx, sizes_t):
+        cands = self.empty((capx, 2), torch.int64)
+        total = self.empty((1,), torch.int64)
+        terms = self.empty((2 * world,), torch.float64)
+        status = self.empty((1,), torch.int32)
+        _lib.check(_lib.lib.vb_psis_gather_compact(self._p(recv), world, capx, self._p(sizes_t), self._p(cands),
+                                                   self._p(total), self._p(terms), self._p(status), self._stream()),
+                   'vb_psis_gather_compact')
+        return cands, total, terms, status
+
+    def tail_dev(self, cands, total_t, K1, M, pivot, terms, status_t, want_tail_idx=False):
+        cap = cands.shape[0]
+        diag = self.empty((8,), torch.float64)
+        tail_idx = torch.full((K1 + 1,), -1, dtype=torch.int64, device=self.device) if want_tail_idx else None
+        ws = self.ws.get('tail', _lib.lib.vb_psis_tail_workspace_bytes(cap, K1))
+        _lib.check(_lib.lib.vb_psis_tail_dev(self._p(cands), cap, self._p(total_t), K1, self._p(M), self._p(pivot),
+                                             self._p(terms), terms.numel(), 0, 0, self._p(status_t), self._p(diag),
+                                             self._p(tail_idx), self._p(ws), ws.numel(), self._stream()),
+                   'vb_psis_tail_dev')
+        return diag, tail_idx, (ws, cap, K1)
+
     def write(self, lw, index0, M, handle):
         """S6; also leaves this shard's divergence partials (alpha = 2, relative to the global maximum) in
         ``self.last_div``: taken in the same pass over the weights."""
@@ -152,6 +191,10 @@ class DistComm:
         self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX, group=self.group)
         return t
 
+    def all_reduce_sum(self, t):
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM, group=self.group)
+        return t
+
 
 def psislw_sharded(lw_local, Reff=1.0, group=None, stages=None, want_detail=False, comm=None, src=None):
     """Sharded ``psislw`` (``psis.py:112-208``) of one weight column.
@@ -173,7 +216,14 @@ def psislw_sharded(lw_local, Reff=1.0, group=None, stages=None, want_detail=Fals
             sizes = [int(v) for v in comm.all_gather(torch.tensor([n_local], dtype=torch.int64, device=dev)).cpu().view(-1).tolist()]
             if key is not None:
                 _SIZES[key] = sizes
-        res = _sharded_with_sizes(st, comm, lw_local, Reff, sizes, want_detail, src)
+        res = None
+        if _round == 0 and _dev_path_ok(st, comm, sum(sizes)):
+            res = _sharded_dev(st, comm, lw_local, Reff, sizes, want_detail, src)     # None: take the host-driven path
+            PATH_TAKEN[0] = 'dev' if res is not None else 'dev->host'
+        else:
+            PATH_TAKEN[0] = 'host'
+        if res is None:
+            res = _sharded_with_sizes(st, comm, lw_local, Reff, sizes, want_detail, src)
         if res is not None:
             return res
         sizes = None                       # some rank's shard changed since the sizes were cached
@@ -183,6 +233,71 @@ def psislw_sharded(lw_local, Reff=1.0, group=None, stages=None, want_detail=Fals
 
 
 _SIZES = {}
+_SIZES_DEV = {}
+PATH_TAKEN = [None]          # which protocol the last call ran: 'dev', 'dev->host' (fallback) or 'host' (tests)
+
+
+def _dev_path_ok(st, comm, n):
+    import os
+    return (hasattr(st, 'tail_dev') and hasattr(comm, 'all_reduce_sum') and n > DIRECT_MAX
+            and os.environ.get('VB_PSIS_HOST', '0') in ('', '0'))
+
+
+def exchange_capacity(K1):
+    """Rows of the fixed-capacity candidate slot every rank sends: the global refinement keeps K1 + 1 candidates plus
+    the rest of the threshold bin in TOTAL, whatever the number of ranks, and one rank may hold all of them."""
+    return (K1 + 1) + (K1 + 1) // 4 + 8192
+
+
+def _sharded_dev(st, comm, lw_local, Reff, sizes, want_detail, src):
+    """Device-driven protocol: four collectives (samples, maximum, histogram, candidate slots), no host read until
+    the diagnostics come back at the end.  Counts, capacities and the refinement threshold stay in device memory;
+    the gathers have a fixed capacity (``exchange_capacity``), so no rank needs a host-side count.  Returns None when
+    the on-device checks failed (too few candidates for the first pivot, an overflowing buffer, heavy ties, a changed
+    shard size): the caller then runs the host-driven protocol, which handles those cases."""
+    world, rank = comm.world, comm.rank
+    n_local = int(lw_local.numel())
+    n = sum(sizes)
+    index0 = sum(sizes[:rank])
+    K1 = psis_tail_count(n, Reff)
+    capx = exchange_capacity(K1)
+    key = (getattr(comm, 'cache_key', None), tuple(sizes), str(lw_local.device))
+    sizes_t = _SIZES_DEV.get(key)
+    if sizes_t is None:
+        sizes_t = torch.tensor(sizes, dtype=torch.int64, device=lw_local.device)
+        _SIZES_DEV.clear()
+        _SIZES_DEV[key] = sizes_t
+    pivot = st.empty((1,), torch.float64)
+    mine = st.sample(lw_local, index0)
+    cap_s = _pow2_at_least(world * SAMPLE)
+    sample_all = st.empty((cap_s, 2), torch.int64)
+    sample_all[:world * SAMPLE] = comm.all_gather(mine).view(world * SAMPLE, 2)
+    cap = min(n_local, max(1 << 21, n_local // 16))
+    frac = max(0.01, 4.0 * (K1 + 1) / n)
+    st.pivot(sample_all, world * SAMPLE, frac, pivot)
+    cand, count_t, body_max = st.filter(lw_local, index0, pivot, cap)
+    M = body_max[1:2].clone()
+    comm.all_reduce_max(M)
+    terms = st.empty((2,), torch.float64)
+    hist = st.prepare_hist_dev(cand, count_t, M, pivot, body_max, terms)
+    comm.all_reduce_sum(hist)                                            # 32 KB: one global threshold
+    send = st.refine_select_dev(cand, count_t, M, pivot, hist, K1 + 1, capx, terms, n_local)
+    recv = comm.all_gather(send)                                         # (world, capx + 3, 2)
+    all_cands, total_t, all_terms, status_t = st.gather_compact(recv, world, capx, sizes_t)
+    diag, tail_idx, handle = st.tail_dev(all_cands, total_t, K1, M, pivot, all_terms, status_t, want_tail_idx=want_detail)
+    out = st.write(lw_local, index0, M, handle)
+    d = diag.cpu().numpy()                                               # the one host read of the call
+    if d[7] < 0:
+        return None
+    if src is not None and getattr(st, 'last_div', None) is not None:
+        from .psis import _DivCache
+        _DivCache.store(src, st.last_div, world)
+    if not want_detail:
+        return out, d[0]
+    n2 = int(d[3])
+    detail = dict(k=d[0], sigma=d[1], xcutoff=d[2], n2=n2, smoothed=bool(d[4]), max=d[5], lse=d[6],
+                  n_candidates=int(d[7]), tail_idx_sorted=tail_idx[:n2].cpu().numpy(), index0=index0, n=n)
+    return out, d[0], detail
 
 
 def _sharded_with_sizes(st, comm, lw_local, Reff, sizes, want_detail, src=None):
