@@ -295,6 +295,25 @@ int vb_gemm_tf32x3_split(int a_mn_major, int b_mn_major, long long m, long long 
                          float* d_C, long long ldc, void* stream);
 
 /* ------------------------------------------------------------------------------------
+ * O(d^3) parameter chain of the full-rank Student-t family as two persistent cooperative kernels (csrc/fr_chain.cu):
+ * no eigendecomposition, no library call.  Replaces paragami's fold + scipy sqrtm (viabel/vb.py:185-189, 207) and
+ * autograd's sqrtm VJP (solve_sylvester) + the assembly of value_and_grad's result (vb.py:236-266).
+ *   vb_fr_chain_forward   var_param -> L (d, d), S (d, d) = sqrtm(L L') [scale_mode 0] or L' [1: x = mu + L ztilde],
+ *                         optional fp32 copy of S, d_out_scal[2] = (sum of the log-diagonal = entropy, |L|_F^2)
+ *   vb_fr_chain_backward  G_S = Ztilde' diag(w) G, g_mu = sum w g, rows = [max lw, sum w, sum log p, sum lw]
+ *                         -> d_out[1 + P] = (value, gradient) of KLVI (objective 0), CHIVI (1), path-derivative KLVI (2)
+ *   vb_fr_chain_info      iteration counts and status of the last calls on a workspace (synchronises)
+ * ---------------------------------------------------------------------------------- */
+size_t vb_fr_chain_workspace_bytes(int dim);
+int vb_fr_chain_forward(const double* d_var_param, int dim, int scale_mode, double* d_out_L, double* d_out_S,
+                        float* d_out_S32_or_null, double* d_out_scal, void* d_ws, size_t ws_bytes, void* stream);
+int vb_fr_chain_backward(int dim, int scale_mode, int objective, double alpha, double n_total,
+                         const double* d_L, const double* d_S, const double* d_GS, const double* d_gmu,
+                         const double* d_rows, const double* d_scal, double* d_out, void* d_ws, size_t ws_bytes,
+                         void* stream);
+int vb_fr_chain_info(const void* d_ws, int dim, int* h_out4, void* stream);
+
+/* ------------------------------------------------------------------------------------
  * Bounds (viabel/bounds.py).
  *   vb_bounds_divergence  one streaming pass over lw (n):  max, sum exp(alpha (lw - max)),
  *                         its second moment, mean/variance of lw.   bounds.py:142-192

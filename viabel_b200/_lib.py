@@ -58,6 +58,10 @@ SIGNATURES = {
     'vb_fr_sample': (_i, [_i, _p, _p, _d, _ll, _i, _p, _p, _p, _p, _sz, _p]),
     'vb_fr_logdensity_workspace_bytes': (_sz, [_ll, _i]),
     'vb_fr_logdensity': (_i, [_i, _p, _p, _d, _d, _ll, _i, _p, _p, _p, _sz, _p]),
+    'vb_fr_chain_workspace_bytes': (_sz, [_i]),
+    'vb_fr_chain_forward': (_i, [_p, _i, _i, _p, _p, _p, _p, _p, _sz, _p]),
+    'vb_fr_chain_backward': (_i, [_i, _i, _i, _d, _d, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    'vb_fr_chain_info': (_i, [_p, _i, C.POINTER(_i), _p]),
     'vb_fr_rows_workspace_bytes': (_sz, [_ll]),
     'vb_fr_rows': (_i, [_i, _d, _d, _i, _ll, _i, _p, _p, _p, _d, _p, _p, _p, _p, _sz, _p]),
     'vb_fr_weighted_workspace_bytes': (_sz, [_ll, _i]),

@@ -1,0 +1,538 @@
+// The O(d^3) parameter chain of the full-rank Student-t family (kernel K7) as TWO persistent
+// cooperative kernels, with no eigendecomposition and no library call:
+//   forward   phi -> L (paragami free PSD pattern, viabel/vb.py:185-189) -> S = sqrtm(L L')      (vb.py:207)
+//   backward  G_S -> Y solving S Y + Y S = G_S (autograd's sqrtm VJP) -> G_L = (Y + Y') L -> d/dphi, and the assembly
+//             of the KLVI / CHIVI (value, gradient) vector                                       (vb.py:236-266)
+// Everything is fp64 GEMMs on the fp64 tensor cores (mma.sync m8n8k4) inside one launch, separated by grid barriers:
+//   * S is the symmetric polar factor of L (L = S Q, Q orthogonal): Q by a Newton-Schulz iteration on X0 = L / |L|_F
+//     (a few steps of the quintic a X + X (b A + c A^2), A = X'X, lift the small singular values at 3.44x per step,
+//     then the cubic 1.5 X - 0.5 X A converges quadratically), S = sym(L Q').
+//   * Sylvester by squared-Smith doubling: with M = S + mu I, A0 = (S - mu I) M^-1, Y0 = 2 mu M^-1 G M^-1,
+//     Y = sum_j A0^j Y0 A0^j:  Y <- Y + A Y A, A <- A^2;  M^-1 by Newton-Schulz (X <- 2 X - X M X).
+// Every iteration's stopping test is a Frobenius norm summed in fixed order from per-CTA partials, so all CTAs take
+// the same decision and repeated runs are bit-identical.  Accuracy vs the eigh formulation: S 4e-15, Y 5e-13
+// (config C3, kappa(L) = 216); 87 GEMMs of 512^3 instead of cuSOLVER syevd + 5 GEMMs.
+#include <cstdlib>
+#include "common.cuh"
+
+namespace vb {
+
+constexpr int kCT = 256;                   // threads per CTA: two groups of 4 warps, each takes half of every k slab
+constexpr int kCM = 64, kCN = 32, kCK = 32;    // CTA tile (k slab 32: half as many exposed L2 round trips as 16)
+constexpr int kCMaxGrid = 148;
+constexpr int kCAld = kCM + 4, kCBld = kCN + 4;   // leading dimensions = 4 (mod 16): conflict-free fragment loads
+
+struct ChainBarrier { unsigned int count; };
+
+// all CTAs of the (cooperative: co-resident) grid; `phase` counts the barriers this thread block has passed
+__device__ __forceinline__ void grid_barrier(unsigned int* counter, unsigned int& phase) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned int target = (phase + 1) * gridDim.x;
+        atomicAdd(counter, 1u);
+        unsigned int v;
+        do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
+        } while (v < target);
+        __threadfence();
+    }
+    ++phase;
+    __syncthreads();
+}
+
+__device__ __forceinline__ void dmma(double (&c)[2], double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+                 : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
+}
+
+// C (d x d, ld = d) = alpha op(A) op(B) + beta E + gamma I, every CTA of the grid takes tiles t = blockIdx.x, + gridDim.x ..
+// norm_mode: 0 none, 1 partial of |C - I|_F^2, 2 partial of |C|_F^2  -> returned (this CTA's sum, valid in every thread)
+// sym_mode:  the A operand is read as (A + A') (used for (Y + Y') L)
+struct GemmSmem { double As[2][kCK][kCAld]; double Bs[2][kCK][kCBld]; double red[kCT / 32]; };     // 53 KB: dynamic
+
+__device__ double chain_gemm(GemmSmem& sm, int d, bool ta, const double* __restrict__ A, bool tb, const double* __restrict__ B,
+                             double alpha, double beta, const double* E, double gamma, double* __restrict__ C,
+                             int norm_mode, bool sym_a = false) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int grp = warp >> 2;                                      // k-split group of this warp
+    const int wm = (warp & 1) * 32, wn = ((warp >> 1) & 1) * 16;
+    const int tiles_m = (d + kCM - 1) / kCM, tiles_n = (d + kCN - 1) / kCN;
+    double nrm = 0.0;
+    for (int t = blockIdx.x; t < tiles_m * tiles_n; t += gridDim.x) {
+        const int i0 = (t / tiles_n) * kCM, j0 = (t % tiles_n) * kCN;
+        double acc[4][2][2];
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 2; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+        double ra[kCM * kCK / kCT], rb[kCN * kCK / kCT];
+        auto load = [&](int k0) {
+#pragma unroll
+            for (int e = 0; e < kCM * kCK / kCT; ++e) {
+                const int idx = tid + e * kCT;
+                int m, k;
+                if (!ta) { m = idx / kCK; k = idx % kCK; } else { m = idx % kCM; k = idx / kCM; }   // contiguous index fastest
+                const int gm = i0 + m, gk = k0 + k;
+                double v = 0.0;
+                if (gm < d && gk < d) {
+                    v = ta ? A[(size_t)gk * d + gm] : A[(size_t)gm * d + gk];
+                    if (sym_a) v += ta ? A[(size_t)gm * d + gk] : A[(size_t)gk * d + gm];
+                }
+                ra[e] = v;
+            }
+#pragma unroll
+            for (int e = 0; e < kCN * kCK / kCT; ++e) {
+                const int idx = tid + e * kCT;
+                int n, k;
+                if (!tb) { n = idx % kCN; k = idx / kCN; } else { n = idx / kCK; k = idx % kCK; }
+                const int gn = j0 + n, gk = k0 + k;
+                rb[e] = (gn < d && gk < d) ? (tb ? B[(size_t)gn * d + gk] : B[(size_t)gk * d + gn]) : 0.0;
+            }
+        };
+        auto store = [&](int buf) {
+#pragma unroll
+            for (int e = 0; e < kCM * kCK / kCT; ++e) {
+                const int idx = tid + e * kCT;
+                int m, k;
+                if (!ta) { m = idx / kCK; k = idx % kCK; } else { m = idx % kCM; k = idx / kCM; }
+                sm.As[buf][k][m] = ra[e];
+            }
+#pragma unroll
+            for (int e = 0; e < kCN * kCK / kCT; ++e) {
+                const int idx = tid + e * kCT;
+                int n, k;
+                if (!tb) { n = idx % kCN; k = idx / kCN; } else { n = idx / kCK; k = idx % kCK; }
+                sm.Bs[buf][k][n] = rb[e];
+            }
+        };
+        load(0);
+        store(0);
+        __syncthreads();
+        int buf = 0;
+        for (int k0 = 0; k0 < d; k0 += kCK) {
+            const bool more = k0 + kCK < d;
+            if (more) load(k0 + kCK);
+#pragma unroll
+            for (int kk = grp * 4; kk < kCK; kk += 8) {
+                double af[4], bf[2];
+#pragma unroll
+                for (int a = 0; a < 4; ++a) af[a] = sm.As[buf][kk + (lane & 3)][wm + a * 8 + (lane >> 2)];
+#pragma unroll
+                for (int b = 0; b < 2; ++b) bf[b] = sm.Bs[buf][kk + (lane & 3)][wn + b * 8 + (lane >> 2)];
+#pragma unroll
+                for (int a = 0; a < 4; ++a)
+#pragma unroll
+                    for (int b = 0; b < 2; ++b) dmma(acc[a][b], af[a], bf[b]);
+            }
+            if (more) store(buf ^ 1);
+            __syncthreads();
+            buf ^= 1;
+        }
+        // the two k-split groups meet in shared memory (the operand buffers are free after the last slab)
+        {
+            double* xch = &sm.As[0][0][0];
+            if (grp == 1) {
+#pragma unroll
+                for (int a = 0; a < 4; ++a)
+#pragma unroll
+                    for (int b = 0; b < 2; ++b)
+#pragma unroll
+                        for (int c = 0; c < 2; ++c) xch[((a * 2 + b) * 2 + c) * 128 + (tid - 128)] = acc[a][b][c];
+            }
+            __syncthreads();
+            if (grp == 0) {
+#pragma unroll
+                for (int a = 0; a < 4; ++a)
+#pragma unroll
+                    for (int b = 0; b < 2; ++b)
+#pragma unroll
+                        for (int c = 0; c < 2; ++c) acc[a][b][c] += xch[((a * 2 + b) * 2 + c) * 128 + tid];
+            }
+            __syncthreads();
+        }
+        // epilogue (group 0): thread holds C(row = lane / 4, cols = 2 (lane % 4), + 1) of each 8 x 8 block
+        if (grp == 0)
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 2; ++b)
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    const int gi = i0 + wm + a * 8 + (lane >> 2), gj = j0 + wn + b * 8 + 2 * (lane & 3) + c;
+                    if (gi < d && gj < d) {
+                        double v = alpha * acc[a][b][c];
+                        if (beta != 0.0) v = fma(beta, E[(size_t)gi * d + gj], v);
+                        if (gi == gj) v += gamma;
+                        C[(size_t)gi * d + gj] = v;
+                        if (norm_mode) {
+                            const double r = (norm_mode == 1 && gi == gj) ? v - 1.0 : v;
+                            nrm = fma(r, r, nrm);
+                        }
+                    }
+                }
+    }
+    if (!norm_mode) return 0.0;
+    nrm = warp_sum(nrm);
+    __syncthreads();
+    if (lane == 0) sm.red[warp] = nrm;
+    __syncthreads();
+    double s = 0.0;
+#pragma unroll
+    for (int w = 0; w < kCT / 32; ++w) s += sm.red[w];
+    return s;
+}
+
+// sum of the per-CTA partials in fixed order (every thread of every CTA gets the same value)
+__device__ __forceinline__ double sum_partials(const volatile double* parts) {
+    // lane l adds parts[l], parts[l + 32], ... then a fixed butterfly: the same tree in every warp of every CTA
+    double s = 0.0;
+    for (unsigned int b = threadIdx.x & 31; b < gridDim.x; b += 32) s += parts[b];
+    return warp_sum(s);
+}
+
+struct ChainWs {
+    double *X0, *X1, *T0, *T1, *T2, *T3;        // six d x d scratch matrices
+    double* parts;                              // [3][grid] norm partials (rotating: a slot is rewritten two barriers later)
+    unsigned int* barrier;
+    int* info;                                  // [0] polar iterations [1] inverse iterations [2] smith iterations [3] status
+};
+
+// ------------------------------------------------------------------------------------------ forward
+struct FwdArgs {
+    const double* vp;          // (d + d (d + 1) / 2) variational parameters
+    int d, mode;               // mode 0 = sqrtm (reference), 1 = chol (x = mu + L ztilde)
+    double* L;                 // out (d, d)
+    double* S;                 // out (d, d) fp64: row-form scale matrix (x = mu + ztilde S): sqrtm(Sigma) or L'
+    float* S32;                // out (d, d) fp32 copy or null
+    double* scal;              // out [0] entropy = sum phi_ii  [1] |L|_F^2
+    ChainWs ws;
+};
+
+__global__ void __launch_bounds__(kCT)
+fr_chain_forward_kernel(const FwdArgs a) {
+    extern __shared__ __align__(16) unsigned char chain_smem[];
+    GemmSmem& sm = *reinterpret_cast<GemmSmem*>(chain_smem);
+    const int d = a.d;
+    const long long dd = (long long)d * d;
+    const long long gtid = blockIdx.x * (long long)blockDim.x + threadIdx.x, gth = (long long)gridDim.x * blockDim.x;
+    unsigned int phase = 0;
+    double* parts = a.ws.parts;
+    int slot = 0;
+    auto next_slot = [&]() { double* p = parts + (size_t)slot * gridDim.x; slot = (slot + 1) % 3; return p; };
+    // ---- fold: L = unvec_tril_rowmajor(phi) with exp on the diagonal; partial sums of |L|_F^2 and of the log diagonal
+    double f2 = 0.0, ent = 0.0;
+    for (long long e = gtid; e < dd; e += gth) {
+        const int r = (int)(e / d), c = (int)(e - (long long)r * d);
+        double v = 0.0;
+        if (c <= r) {
+            v = a.vp[d + (long long)r * (r + 1) / 2 + c];
+            if (c == r) { ent += v; v = exp(v); }
+        }
+        a.L[e] = v;
+        f2 = fma(v, v, f2);
+    }
+    {
+        f2 = warp_sum(f2); ent = warp_sum(ent);
+        __syncthreads();
+        if ((threadIdx.x & 31) == 0) { sm.red[threadIdx.x >> 5] = f2; sm.As[0][0][threadIdx.x >> 5] = ent; }
+        __syncthreads();
+        double s = 0.0, t = 0.0;
+        for (int w = 0; w < kCT / 32; ++w) { s += sm.red[w]; t += sm.As[0][0][w]; }
+        __syncthreads();
+        double* p = next_slot();
+        double* p2 = next_slot();
+        if (threadIdx.x == 0) { p[blockIdx.x] = s; p2[blockIdx.x] = t; }
+        grid_barrier(a.ws.barrier, phase);
+        f2 = sum_partials(p);
+        ent = sum_partials(p2);
+        if (gtid == 0) { a.scal[0] = ent; a.scal[1] = f2; }
+    }
+    if (a.mode == 1) {                                   // chol: S = L' (row form), no iteration
+        for (long long e = gtid; e < dd; e += gth) {
+            const int r = (int)(e / d), c = (int)(e - (long long)r * d);
+            const double v = a.L[(size_t)c * d + r];
+            a.S[e] = v;
+            if (a.S32) a.S32[e] = (float)v;
+        }
+        if (gtid == 0) { a.ws.info[0] = 0; a.ws.info[3] = 0; }
+        return;
+    }
+    // ---- polar factor of L: X0 = L / |L|_F
+    const double inv_f = 1.0 / sqrt(f2);
+    double* X = a.ws.X0;
+    double* Xn = a.ws.X1;
+    for (long long e = gtid; e < dd; e += gth) X[e] = a.L[e] * inv_f;
+    grid_barrier(a.ws.barrier, phase);
+    const double tol2 = 16.0 * (double)d * 1e-28;        // |X'X - I|_F < 4 sqrt(d) 1e-14
+    int its = 0, status = 1;
+    bool lifting = true;
+    for (int it = 0; it < 60; ++it) {
+        double* p = next_slot();
+        const double part = chain_gemm(sm, d, true, X, false, X, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 1);      // A = X'X
+        if (threadIdx.x == 0) p[blockIdx.x] = part;
+        grid_barrier(a.ws.barrier, phase);
+        const double err2 = sum_partials(p);
+        if (err2 < tol2) { status = 0; break; }
+        if (lifting && (err2 < 0.25 || it >= 8)) lifting = false;
+        if (lifting) {
+            // quintic lift: X <- a X + X (b A + c A^2)
+            chain_gemm(sm, d, false, a.ws.T0, false, a.ws.T0, 2.0315, -4.7750, a.ws.T0, 0.0, a.ws.T1, 0);  // B = c A A + b A
+            grid_barrier(a.ws.barrier, phase);
+            chain_gemm(sm, d, false, X, false, a.ws.T1, 1.0, 3.4445, X, 0.0, Xn, 0);
+        } else {
+            chain_gemm(sm, d, false, X, false, a.ws.T0, -0.5, 1.5, X, 0.0, Xn, 0);                          // 1.5 X - 0.5 X A
+        }
+        grid_barrier(a.ws.barrier, phase);
+        double* t = X; X = Xn; Xn = t;
+        ++its;
+    }
+    // ---- S = sym(L Q'), Q = X
+    chain_gemm(sm, d, false, a.L, true, X, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 0);
+    grid_barrier(a.ws.barrier, phase);
+    for (long long e = gtid; e < dd; e += gth) {
+        const int r = (int)(e / d), c = (int)(e - (long long)r * d);
+        const double v = 0.5 * (a.ws.T0[e] + a.ws.T0[(size_t)c * d + r]);
+        a.S[e] = v;
+        if (a.S32) a.S32[e] = (float)v;
+    }
+    if (gtid == 0) { a.ws.info[0] = its; a.ws.info[3] = status; }
+}
+
+// ------------------------------------------------------------------------------------------ backward
+struct BwdArgs {
+    int d, mode, objective;    // objective: 0 KLVI, 1 CHIVI, 2 KLVI path-derivative value
+    double alpha, n_total;
+    const double* L;           // (d, d)
+    const double* S;           // (d, d)
+    const double* GS;          // (d, d) G_S = Ztilde' diag(w) G
+    const double* gmu;         // (d)    sum_i w_i g_i
+    const double* rows;        // [max lw, sum w, sum log p, sum lw]
+    const double* scal;        // forward scalars: [0] entropy, [1] |L|_F^2
+    double* out;               // (1 + P): value, gradient
+    ChainWs ws;
+};
+
+__global__ void __launch_bounds__(kCT)
+fr_chain_backward_kernel(const BwdArgs a) {
+    extern __shared__ __align__(16) unsigned char chain_smem[];
+    GemmSmem& sm = *reinterpret_cast<GemmSmem*>(chain_smem);
+    const int d = a.d;
+    const long long dd = (long long)d * d;
+    const long long gtid = blockIdx.x * (long long)blockDim.x + threadIdx.x, gth = (long long)gridDim.x * blockDim.x;
+    unsigned int phase = 0;
+    double* parts = a.ws.parts;
+    int slot = 0;
+    auto next_slot = [&]() { double* p = parts + (size_t)slot * gridDim.x; slot = (slot + 1) % 3; return p; };
+    const double* GL = nullptr;          // d f / d L as (d, d) row-major
+    bool gl_transposed = false;
+    int inv_its = 0, smith_its = 0, status = 0;
+    if (a.mode == 1) {
+        GL = a.GS;                       // chol: G_L = G_S' (x = mu + L ztilde)
+        gl_transposed = true;
+    } else {
+        // ---- M^-1, M = S + mu I, mu = rms eigenvalue of S = sqrt(|L|_F^2 / d);  X0 = I / |M|_1
+        const double mu = sqrt(a.scal[1] / (double)d);
+        double* Mx = a.ws.T3;            // M
+        double colmax = 0.0;
+        for (long long e = gtid; e < dd; e += gth) {
+            const int r = (int)(e / d), c = (int)(e - (long long)r * d);
+            Mx[e] = a.S[e] + (r == c ? mu : 0.0);
+        }
+        // |M|_1 = max column sum (M symmetric: row sums); one warp per row
+        {
+            const int lane = threadIdx.x & 31;
+            const long long gw = gtid >> 5, nw = gth >> 5;
+            for (long long r = gw; r < d; r += nw) {
+                double s = 0.0;
+                for (int c = lane; c < d; c += 32) s += fabs(a.S[(size_t)r * d + c] + (r == c ? mu : 0.0));
+                s = warp_sum(s);
+                colmax = fmax(colmax, s);
+            }
+            colmax = warp_max(colmax);
+            __syncthreads();
+            if (lane == 0) sm.red[threadIdx.x >> 5] = colmax;
+            __syncthreads();
+            double m = 0.0;
+            for (int w = 0; w < kCT / 32; ++w) m = fmax(m, sm.red[w]);
+            __syncthreads();
+            double* p = next_slot();
+            if (threadIdx.x == 0) p[blockIdx.x] = m;
+            grid_barrier(a.ws.barrier, phase);
+            colmax = 0.0;
+            for (unsigned int b = 0; b < gridDim.x; ++b) colmax = fmax(colmax, ((const volatile double*)p)[b]);
+        }
+        double* X = a.ws.X0;
+        double* Xn = a.ws.X1;
+        const double x0 = 1.0 / colmax;
+        for (long long e = gtid; e < dd; e += gth) {
+            const int r = (int)(e / d), c = (int)(e - (long long)r * d);
+            X[e] = (r == c) ? x0 : 0.0;
+        }
+        grid_barrier(a.ws.barrier, phase);
+        const double tol2 = 16.0 * (double)d * 1e-28;
+        status = 2;
+        for (int it = 0; it < 60; ++it) {
+            double* p = next_slot();
+            const double part = chain_gemm(sm, d, false, Mx, false, X, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 1);   // R = M X
+            if (threadIdx.x == 0) p[blockIdx.x] = part;
+            grid_barrier(a.ws.barrier, phase);
+            if (sum_partials(p) < tol2) { status = 0; break; }
+            chain_gemm(sm, d, false, X, false, a.ws.T0, -1.0, 2.0, X, 0.0, Xn, 0);                           // 2 X - X R
+            grid_barrier(a.ws.barrier, phase);
+            double* t = X; X = Xn; Xn = t;
+            ++inv_its;
+        }
+        // ---- A0 = S M^-1 - mu M^-1,  Y0 = 2 mu M^-1 G M^-1
+        double* Aq = a.ws.T1;
+        double* Aq2 = a.ws.T3;           // M is no longer needed after A0
+        double* Y = a.ws.T2;
+        double* Yn = Xn;                 // the spare inverse buffer
+        chain_gemm(sm, d, false, X, false, a.GS, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 0);                        // T = M^-1 G
+        grid_barrier(a.ws.barrier, phase);
+        chain_gemm(sm, d, false, a.ws.T0, false, X, 2.0 * mu, 0.0, nullptr, 0.0, Y, 0);                      // Y0
+        {
+            double* p = next_slot();
+            const double part = chain_gemm(sm, d, false, a.S, false, X, 1.0, -mu, X, 0.0, Aq, 2);            // A0, |A0|_F^2
+            if (threadIdx.x == 0) p[blockIdx.x] = part;
+            grid_barrier(a.ws.barrier, phase);
+            double na2 = sum_partials(p);
+            // ---- doubling: Y <- Y + A Y A, A <- A^2 until |A|_F is negligible
+            for (int it = 0; it < 60 && na2 > 1e-34; ++it) {
+                chain_gemm(sm, d, false, Aq, false, Y, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 0);                  // T = A Y
+                double* p2 = next_slot();
+                const double part2 = chain_gemm(sm, d, false, Aq, false, Aq, 1.0, 0.0, nullptr, 0.0, Aq2, 2);   // A^2 (independent)
+                if (threadIdx.x == 0) p2[blockIdx.x] = part2;
+                grid_barrier(a.ws.barrier, phase);
+                chain_gemm(sm, d, false, a.ws.T0, false, Aq, 1.0, 1.0, Y, 0.0, Yn, 0);                       // Y + T A
+                grid_barrier(a.ws.barrier, phase);
+                na2 = sum_partials(p2);
+                double* t = Aq; Aq = Aq2; Aq2 = t;
+                t = Y; Y = Yn; Yn = t;
+                ++smith_its;
+            }
+            if (na2 > 1e-34 && status == 0) status = 3;
+        }
+        // ---- G_L = (Y + Y') L
+        chain_gemm(sm, d, false, Y, false, a.L, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 0, true);
+        grid_barrier(a.ws.barrier, phase);
+        GL = a.ws.T0;
+    }
+    // ---- assemble (value, gradient): vb.py:240-243 (KLVI), :261-264 (CHIVI)
+    const double nt = a.n_total;
+    const double entropy = a.scal[0];
+    const double sw = a.rows[1];
+    const bool chivi = a.objective == 1;
+    const double gscale = chivi ? a.alpha / nt : -1.0 / nt;
+    if (gtid == 0) {
+        double v;
+        if (chivi) v = log(sw / nt) / a.alpha + a.rows[0];
+        else if (a.objective == 0) v = -(entropy + a.rows[2] / nt);
+        else v = -(a.rows[3] / nt);
+        a.out[0] = v;
+        a.ws.info[1] = inv_its; a.ws.info[2] = smith_its;
+        if (status) a.ws.info[3] = status;
+    }
+    for (long long j = gtid; j < d; j += gth) a.out[1 + j] = gscale * a.gmu[j];
+    const long long ntri = (long long)d * (d + 1) / 2;
+    for (long long e = gtid; e < ntri; e += gth) {
+        // row-major lower triangle: e -> (r, c)
+        long long r = (long long)((sqrt(8.0 * (double)e + 1.0) - 1.0) * 0.5);
+        while (r * (r + 1) / 2 > e) --r;
+        while ((r + 1) * (r + 2) / 2 <= e) ++r;
+        const long long c = e - r * (r + 1) / 2;
+        double g = gl_transposed ? GL[(size_t)c * d + r] : GL[(size_t)r * d + c];
+        if (r == c) {
+            g *= a.L[(size_t)r * d + r];                     // chain through exp on the diagonal
+            g += chivi ? sw : (double)nt;                    // -log q term: + sum w (CHIVI), -1 after the KLVI scaling
+        }
+        a.out[1 + d + e] = gscale * g;
+    }
+}
+
+static cudaError_t chain_configure() {
+    static DeviceOnce once;
+    const int dev = current_device();
+    if (!once.pending(dev)) return cudaSuccess;
+    cudaError_t e = cudaFuncSetAttribute(fr_chain_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(GemmSmem));
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(fr_chain_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(GemmSmem));
+    if (e == cudaSuccess) once.done(dev);
+    return e;
+}
+static int chain_grid(int d) {
+    const int tiles = ((d + kCM - 1) / kCM) * ((d + kCN - 1) / kCN);
+    int g = device_sm_count();
+    if (g > kCMaxGrid) g = kCMaxGrid;
+    if (tiles < g) g = tiles < 8 ? 8 : tiles;              // a few CTAs even for tiny d (elementwise phases)
+    if (g > device_sm_count()) g = device_sm_count();
+    return g;
+}
+static size_t chain_ws_bytes(int d) {
+    return align_up((size_t)6 * d * d * 8, 256) + align_up((size_t)3 * kCMaxGrid * 8, 256) + 256 + 256;
+}
+static ChainWs chain_ws(void* ws, int d) {
+    char* p = (char*)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
+    const size_t m = (size_t)d * d * 8;
+    ChainWs w;
+    w.X0 = (double*)p; w.X1 = (double*)(p + m); w.T0 = (double*)(p + 2 * m); w.T1 = (double*)(p + 3 * m);
+    w.T2 = (double*)(p + 4 * m); w.T3 = (double*)(p + 5 * m);
+    p += align_up(6 * m, 256);
+    w.parts = (double*)p; p += align_up((size_t)3 * kCMaxGrid * 8, 256);
+    w.barrier = (unsigned int*)p; p += 256;
+    w.info = (int*)p;
+    return w;
+}
+
+}  // namespace vb
+
+using namespace vb;
+
+extern "C" size_t vb_fr_chain_workspace_bytes(int dim) { return dim < 1 ? 0 : chain_ws_bytes(dim) + 256; }
+
+extern "C" int vb_fr_chain_forward(const double* d_var_param, int dim, int scale_mode, double* d_out_L, double* d_out_S,
+                                   float* d_out_S32_or_null, double* d_out_scal, void* d_ws, size_t ws_bytes, void* stream) {
+    if (!d_var_param || !d_out_L || !d_out_S || !d_out_scal || !d_ws || dim < 1 || (scale_mode != 0 && scale_mode != 1))
+        return VB_ERR_ARG;
+    if (ws_bytes < vb_fr_chain_workspace_bytes(dim)) return VB_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    FwdArgs a;
+    a.vp = d_var_param; a.d = dim; a.mode = scale_mode; a.L = d_out_L; a.S = d_out_S; a.S32 = d_out_S32_or_null;
+    a.scal = d_out_scal; a.ws = chain_ws(d_ws, dim);
+    VB_CUDA_TRY(cudaMemsetAsync(a.ws.barrier, 0, 256 + 256, st));
+    void* args[] = {(void*)&a};
+    VB_CUDA_TRY(chain_configure());
+    VB_CUDA_TRY(cudaLaunchCooperativeKernel((const void*)fr_chain_forward_kernel, dim3(chain_grid(dim)), dim3(kCT), args,
+                                            sizeof(GemmSmem), st));
+    return VB_OK;
+}
+
+extern "C" int vb_fr_chain_backward(int dim, int scale_mode, int objective, double alpha, double n_total,
+                                    const double* d_L, const double* d_S, const double* d_GS, const double* d_gmu,
+                                    const double* d_rows, const double* d_scal, double* d_out, void* d_ws, size_t ws_bytes,
+                                    void* stream) {
+    if (!d_L || !d_S || !d_GS || !d_gmu || !d_rows || !d_scal || !d_out || !d_ws || dim < 1) return VB_ERR_ARG;
+    if (scale_mode != 0 && scale_mode != 1) return VB_ERR_ARG;
+    if (objective < 0 || objective > 2 || !(n_total > 0.0)) return VB_ERR_ARG;
+    if (ws_bytes < vb_fr_chain_workspace_bytes(dim)) return VB_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    BwdArgs a;
+    a.d = dim; a.mode = scale_mode; a.objective = objective; a.alpha = alpha; a.n_total = n_total;
+    a.L = d_L; a.S = d_S; a.GS = d_GS; a.gmu = d_gmu; a.rows = d_rows; a.scal = d_scal; a.out = d_out;
+    a.ws = chain_ws(d_ws, dim);
+    VB_CUDA_TRY(cudaMemsetAsync(a.ws.barrier, 0, 256, st));
+    void* args[] = {(void*)&a};
+    VB_CUDA_TRY(chain_configure());
+    VB_CUDA_TRY(cudaLaunchCooperativeKernel((const void*)fr_chain_backward_kernel, dim3(chain_grid(dim)), dim3(kCT), args,
+                                            sizeof(GemmSmem), st));
+    return VB_OK;
+}
+
+// iteration counts and status of the last forward / backward on this workspace: [polar, inverse, smith, status]
+extern "C" int vb_fr_chain_info(const void* d_ws, int dim, int* h_out4, void* stream) {
+    if (!d_ws || !h_out4 || dim < 1) return VB_ERR_ARG;
+    const ChainWs w = chain_ws(const_cast<void*>(d_ws), dim);
+    VB_CUDA_TRY(cudaMemcpyAsync(h_out4, w.info, 4 * sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    VB_CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
+    return VB_OK;
+}

@@ -218,8 +218,35 @@ class _FullRank(_FamilyImpl):
         L.diagonal().exp_()
         return vp[:d].contiguous(), L, self.gemm(L, L, transb=True)
 
+    def use_eigh(self):
+        import os
+        return os.environ.get('VB_FR_EIGH', '0') not in ('', '0')
+
+    def chain_kernel(self, vp):
+        """Forward half of the O(d^3) chain in ONE cooperative launch (csrc/fr_chain.cu): fold, then the symmetric
+        square root as the polar factor of L by Newton-Schulz -- no eigendecomposition."""
+        d = self.dim
+        dev = vp.device
+        L = torch.empty((d, d), dtype=torch.float64, device=dev)
+        S = torch.empty((d, d), dtype=torch.float64, device=dev)
+        S32 = torch.empty((d, d), dtype=torch.float32, device=dev) if self.code != _lib.F64 else None
+        scal = torch.empty(2, dtype=torch.float64, device=dev)
+        ws = self.ws.get('chain', _lib.lib.vb_fr_chain_workspace_bytes(d))
+        _lib.check(_lib.lib.vb_fr_chain_forward(ptr(vp), d, 0 if self.scale == 'sqrtm' else 1, ptr(L), ptr(S), ptr(S32),
+                                                ptr(scal), ptr(ws), ws.numel(), stream_ptr()), 'vb_fr_chain_forward')
+        return {'mu': vp[:d], 'L': L, 'S': S, 'S32': S32, 'scal': scal, 'kernel': True}
+
+    def chain_info(self):
+        """[polar, inverse, smith iterations, status] of the last chain kernels (synchronises)."""
+        out = (ctypes.c_int * 4)()
+        ws = self.ws.get('chain', _lib.lib.vb_fr_chain_workspace_bytes(self.dim))
+        _lib.check(_lib.lib.vb_fr_chain_info(ptr(ws), self.dim, out, stream_ptr()), 'vb_fr_chain_info')
+        return list(out)
+
     def chain(self, vp):
         """Everything of O(d^3) that a step needs."""
+        if not self.use_eigh():
+            return self.chain_kernel(vp)
         mu, L, Sigma = self.fold(vp)
         out = {'mu': mu, 'L': L, 'Sigma': Sigma}
         if self.scale == 'sqrtm':
@@ -234,7 +261,9 @@ class _FullRank(_FamilyImpl):
 
     def scale_matrix(self, ch):
         S = ch['S']
-        return S if self.code == _lib.F64 else S.to(torch.float32)
+        if self.code == _lib.F64:
+            return S
+        return ch['S32'] if ch.get('S32') is not None else S.to(torch.float32)
 
     def pack_grad(self, ch, G_S):
         """d/dphi of sum_i w_i log p(x_i) from G_S = Ztilde' diag(w) G  (SURVEY Appendix A.2)."""
@@ -432,7 +461,7 @@ class _Objective:
         return out
 
     # ------------------------------------------------------------------ full rank
-    def _fr(self, vp, base, n_total, rank, world, g):
+    def _fr(self, vp, base, n_total, rank, world, g, entropy_host=None):
         import torch.distributed as dist
         impl, d = self.impl, self.impl.dim
         n = base['z'].shape[0]
@@ -440,7 +469,12 @@ class _Objective:
         logp, grad = self.model.logp_and_grad_device(x, impl.code, True)
         const = (math.lgamma(0.5 * (impl.df + d)) - math.lgamma(0.5 * impl.df)
                  - 0.5 * d * math.log(math.pi * impl.df))
-        entropy = ch['L'].diagonal().log().sum()
+        if ch.get('kernel'):
+            # sum of the log-diagonal = 1/2 log det Sigma (vb.py:213): from the host copy of var_param when there is one
+            # (no device read-back), else from the forward kernel's scalar
+            entropy = entropy_host if entropy_host is not None else ch['scal'][0]
+        else:
+            entropy = ch['L'].diagonal().log().sum()
         lw = torch.empty(n, dtype=torch.float64, device=vp.device)
         w = torch.empty(n, dtype=torch.float64, device=vp.device)
         rows = torch.empty(4, dtype=torch.float64, device=vp.device)
@@ -460,6 +494,16 @@ class _Objective:
                    'vb_fr_weighted')
         if world > 1:
             rows, g_mu, G_S = fr_exchange_sums(rows, g_mu, G_S, world, g)
+        self.last_log_weights = lw
+        if ch.get('kernel'):
+            # backward half of the chain + assembly of (value, gradient) in ONE cooperative launch
+            out = torch.empty(1 + self.P, dtype=torch.float64, device=vp.device)
+            cws = impl.ws.get('chain', _lib.lib.vb_fr_chain_workspace_bytes(d))
+            _lib.check(_lib.lib.vb_fr_chain_backward(d, 0 if impl.scale == 'sqrtm' else 1, self.obj, self.alpha,
+                                                     float(n_total), ptr(ch['L']), ptr(ch['S']), ptr(G_S), ptr(g_mu),
+                                                     ptr(rows.contiguous()), ptr(ch['scal']), ptr(out), ptr(cws),
+                                                     cws.numel(), stream_ptr()), 'vb_fr_chain_backward')
+            return out
         phi = impl.pack_grad(ch, G_S)
         _, _, diag_pos = impl.tri()
         out = torch.empty(1 + self.P, dtype=torch.float64, device=vp.device)
@@ -515,7 +559,11 @@ class _Objective:
         if impl.kind == _lib.FAMILY_FR_T:
             if base is None:
                 base = impl.base_draws(n_local, seed, off, index0)
-            out = self._fr(vp, base, n_total, rank, world, g)
+            entropy_host = None
+            if is_host(var_param):
+                lam_h = _host_param(var_param)
+                entropy_host = float(np.sum(lam_h[impl.dim:][np.cumsum(np.arange(1, impl.dim + 1)) - 1]))
+            out = self._fr(vp, base, n_total, rank, world, g, entropy_host)
         else:
             out, partials = self._mf(vp, base, seed, off, index0, n_local, finalize=(world == 1))
             self.last_partials = partials
