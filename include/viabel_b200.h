@@ -85,6 +85,10 @@ int  vb_model_regression_attach_split_f16(vb_model* model, const void* d_X_plane
 /* d_mean (dim) and d_precision (dim, dim) symmetric, float64. */
 int  vb_model_create_gauss(const double* d_mean, const double* d_precision, int dim,
                            vb_model** out);
+/* Constants of the correlated-Gaussian plugin's fp32 tensor path (tf32 planes of float(P), bias = mean' P), made
+ * once into vb_model_gauss_cache_bytes(dim) bytes (256-byte aligned, must outlive the model) instead of per call. */
+size_t vb_model_gauss_cache_bytes(int dim);
+int  vb_model_gauss_attach_cache(vb_model* model, float* d_cache, void* stream);
 int  vb_model_kind(const vb_model* m);
 int  vb_model_dim(const vb_model* m);
 void vb_model_destroy(vb_model* m);

@@ -31,6 +31,8 @@ SIGNATURES = {
     'vb_split_f16': (_i, [_p, _ll, _ll, _ll, _p, _p]),
     'vb_model_regression_attach_split_f16': (_i, [_p, _p]),
     'vb_model_create_gauss': (_i, [_p, _p, _i, C.POINTER(_p)]),
+    'vb_model_gauss_cache_bytes': (_sz, [_i]),
+    'vb_model_gauss_attach_cache': (_i, [_p, _p, _p]),
     'vb_model_kind': (_i, [_p]),
     'vb_model_dim': (_i, [_p]),
     'vb_model_destroy': (None, [_p]),

@@ -66,10 +66,13 @@ __device__ double chain_gemm(GemmSmem& sm, int d, bool ta, const double* __restr
         for (int a = 0; a < 4; ++a)
 #pragma unroll
             for (int b = 0; b < 2; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
-        double ra[kCM * kCK / kCT], rb[kCN * kCK / kCT];
-        auto load = [&](int k0) {
+        constexpr int kNA = kCM * kCK / kCT, kNB = kCN * kCK / kCT;
+        // two register sets: slab k + 2 is requested while slab k is multiplied, so every global (L2) load has two
+        // slabs of tensor work to land (one slab, ~0.5 us, does not cover the ~0.8 us round trip)
+        double ra[2][kNA], rb[2][kNB];
+        auto load = [&](int k0, double (&qa)[kNA], double (&qb)[kNB]) {
 #pragma unroll
-            for (int e = 0; e < kCM * kCK / kCT; ++e) {
+            for (int e = 0; e < kNA; ++e) {
                 const int idx = tid + e * kCT;
                 int m, k;
                 if (!ta) { m = idx / kCK; k = idx % kCK; } else { m = idx % kCM; k = idx / kCM; }   // contiguous index fastest
@@ -79,40 +82,34 @@ __device__ double chain_gemm(GemmSmem& sm, int d, bool ta, const double* __restr
                     v = ta ? A[(size_t)gk * d + gm] : A[(size_t)gm * d + gk];
                     if (sym_a) v += ta ? A[(size_t)gm * d + gk] : A[(size_t)gk * d + gm];
                 }
-                ra[e] = v;
+                qa[e] = v;
             }
 #pragma unroll
-            for (int e = 0; e < kCN * kCK / kCT; ++e) {
+            for (int e = 0; e < kNB; ++e) {
                 const int idx = tid + e * kCT;
                 int n, k;
                 if (!tb) { n = idx % kCN; k = idx / kCN; } else { n = idx / kCK; k = idx % kCK; }
                 const int gn = j0 + n, gk = k0 + k;
-                rb[e] = (gn < d && gk < d) ? (tb ? B[(size_t)gn * d + gk] : B[(size_t)gk * d + gn]) : 0.0;
+                qb[e] = (gn < d && gk < d) ? (tb ? B[(size_t)gn * d + gk] : B[(size_t)gk * d + gn]) : 0.0;
             }
         };
-        auto store = [&](int buf) {
+        auto store = [&](int buf, const double (&qa)[kNA], const double (&qb)[kNB]) {
 #pragma unroll
-            for (int e = 0; e < kCM * kCK / kCT; ++e) {
+            for (int e = 0; e < kNA; ++e) {
                 const int idx = tid + e * kCT;
                 int m, k;
                 if (!ta) { m = idx / kCK; k = idx % kCK; } else { m = idx % kCM; k = idx / kCM; }
-                sm.As[buf][k][m] = ra[e];
+                sm.As[buf][k][m] = qa[e];
             }
 #pragma unroll
-            for (int e = 0; e < kCN * kCK / kCT; ++e) {
+            for (int e = 0; e < kNB; ++e) {
                 const int idx = tid + e * kCT;
                 int n, k;
                 if (!tb) { n = idx % kCN; k = idx / kCN; } else { n = idx / kCK; k = idx % kCK; }
-                sm.Bs[buf][k][n] = rb[e];
+                sm.Bs[buf][k][n] = qb[e];
             }
         };
-        load(0);
-        store(0);
-        __syncthreads();
-        int buf = 0;
-        for (int k0 = 0; k0 < d; k0 += kCK) {
-            const bool more = k0 + kCK < d;
-            if (more) load(k0 + kCK);
+        auto multiply = [&](int buf) {
 #pragma unroll
             for (int kk = grp * 4; kk < kCK; kk += 8) {
                 double af[4], bf[2];
@@ -125,9 +122,25 @@ __device__ double chain_gemm(GemmSmem& sm, int d, bool ta, const double* __restr
 #pragma unroll
                     for (int b = 0; b < 2; ++b) dmma(acc[a][b], af[a], bf[b]);
             }
-            if (more) store(buf ^ 1);
+        };
+        // prologue: slab 0 -> smem buffer 0, slab 1 -> register set 1
+        load(0, ra[0], rb[0]);
+        store(0, ra[0], rb[0]);
+        if (kCK < d) load(kCK, ra[1], rb[1]);
+        __syncthreads();
+        // slab s lives in smem buffer s & 1; register set s & 1 carries slab s on its way to shared memory
+        for (int k0 = 0; k0 < d; k0 += 2 * kCK) {
+            // even slab (buffer 0): request slab + 2 into set 0, multiply, move slab + 1 (set 1) into buffer 1
+            if (k0 + 2 * kCK < d) load(k0 + 2 * kCK, ra[0], rb[0]);
+            multiply(0);
+            if (k0 + kCK < d) store(1, ra[1], rb[1]);
             __syncthreads();
-            buf ^= 1;
+            if (k0 + kCK >= d) break;
+            // odd slab (buffer 1)
+            if (k0 + 3 * kCK < d) load(k0 + 3 * kCK, ra[1], rb[1]);
+            multiply(1);
+            if (k0 + 2 * kCK < d) store(0, ra[0], rb[0]);
+            __syncthreads();
         }
         // the two k-split groups meet in shared memory (the operand buffers are free after the last slab)
         {

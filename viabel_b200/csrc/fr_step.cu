@@ -78,9 +78,12 @@ __global__ void fr_weights_kernel(int objective, double alpha, long long n, cons
 }
 __global__ void fr_rows_finish_kernel(const double* __restrict__ M_ptr, const double* __restrict__ blocks, int G,
                                       double* __restrict__ out) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    // one warp, lane-strided partial sums + a fixed butterfly (a serial loop over ~1000 blocks cost 30 us)
+    if (blockIdx.x != 0 || threadIdx.x >= 32) return;
     double sw = 0, slp = 0, slw = 0;
-    for (int g = 0; g < G; ++g) { sw += blocks[3 * g]; slp += blocks[3 * g + 1]; slw += blocks[3 * g + 2]; }
+    for (int g = threadIdx.x; g < G; g += 32) { sw += blocks[3 * g]; slp += blocks[3 * g + 1]; slw += blocks[3 * g + 2]; }
+    sw = warp_sum(sw); slp = warp_sum(slp); slw = warp_sum(slw);
+    if (threadIdx.x != 0) return;
     out[0] = *M_ptr; out[1] = sw; out[2] = slp; out[3] = slw;
 }
 
@@ -236,7 +239,7 @@ extern "C" int vb_fr_rows(int objective, double alpha, double df, int dtype, lon
     VB_LAUNCH_CHECK();
     fr_weights_kernel<<<g_w, 256, 0, st>>>(objective, alpha, n, d_out_lw, d_logp, M_ptr, d_out_w, wb);
     VB_LAUNCH_CHECK();
-    fr_rows_finish_kernel<<<1, 1, 0, st>>>(M_ptr, wb, g_w, d_out_rows);
+    fr_rows_finish_kernel<<<1, 32, 0, st>>>(M_ptr, wb, g_w, d_out_rows);
     VB_LAUNCH_CHECK();
     return VB_OK;
 }
@@ -273,9 +276,11 @@ extern "C" int vb_fr_weighted(int dtype, double df, long long n, int dim, const 
     } else {
         // fp32 storage: G_S on the tensor path (3xTF32, split-K), g_mu by the fp64-accumulating column sum
         double* colparts32 = (double*)((char*)d_ws + ((fr_weighted_tf32_workspace_bytes(n, dim) + 255) & ~(size_t)255));
+        const bool fused = fr_weighted_colsum_fused(n, dim);
         rc = fr_weighted_GS_tf32(df, n, dim, (const float*)d_z, (const float*)d_chi2, d_w, (const float*)d_grad,
-                                 d_out_GS, d_ws, fr_weighted_tf32_workspace_bytes(n, dim), st);
+                                 d_out_GS, d_ws, fr_weighted_tf32_workspace_bytes(n, dim), st, fused ? d_out_gmu : nullptr);
         if (rc != VB_OK) return rc;
+        if (fused) return VB_OK;
         fr_wcolsum_kernel<float><<<dim3((dim + 31) / 32, chunks), dim3(32, 8), 0, st>>>(n, dim, (const float*)d_grad,
                                                                                       d_w, rpc, colparts32);
         VB_LAUNCH_CHECK();

@@ -288,8 +288,21 @@ size_t gauss_f32_workspace_bytes(long long n, int dim) {
            (((size_t)n * dim * 4 + 255) & ~(size_t)255) + 512;
 }
 
+size_t gauss_cache_bytes(int dim) { return split_bytes(dim, dim) + (((size_t)dim * 4 + 255) & ~(size_t)255) + (((size_t)dim * dim * 4 + 255) & ~(size_t)255); }
+// model constants of the fp32 path, made once: tf32 planes of float(P), bias = mean' P, (scratch: float(P))
+int gauss_fill_cache(const double* mean, const double* prec, int dim, float* cache, cudaStream_t st) {
+    char* w = (char*)cache;
+    float* planes = (float*)w;                  w += split_bytes(dim, dim);
+    float* bias = (float*)w;                    w += ((size_t)dim * 4 + 255) & ~(size_t)255;
+    float* p32 = (float*)w;
+    gauss_prep_kernel<<<grid_for((long long)dim * dim, 256, kNumSMs * 2), 256, 0, st>>>(mean, prec, dim, p32, bias);
+    VB_LAUNCH_CHECK();
+    SplitMat ps;
+    return split_into(p32, dim, dim, dim, planes, st, &ps);
+}
 int gauss_logp_grad_f32(const double* mean, const double* prec, int dim, const float* x, long long n,
-                        double* out_logp, float* out_grad_or_null, void* ws, size_t ws_bytes, cudaStream_t st) {
+                        double* out_logp, float* out_grad_or_null, void* ws, size_t ws_bytes, cudaStream_t st,
+                        const float* cache) {
     if (!ws || ws_bytes < gauss_f32_workspace_bytes(n, dim)) return VB_ERR_WORKSPACE;
     const int chunks = (dim + 31) / 32;
     char* w = (char*)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
@@ -299,11 +312,18 @@ int gauss_logp_grad_f32(const double* mean, const double* prec, int dim, const f
     float* bias = (float*)w;                    w += ((size_t)dim * 4 + 255) & ~(size_t)255;
     float* rowpart = (float*)w;                 w += ((size_t)n * chunks * 4 + 255) & ~(size_t)255;
     float* g = out_grad_or_null ? out_grad_or_null : (float*)w;
-    gauss_prep_kernel<<<grid_for((long long)dim * dim, 256, kNumSMs * 2), 256, 0, st>>>(mean, prec, dim, p32, bias);
-    VB_LAUNCH_CHECK();
     SplitMat xs, ps;
-    int rc = split_into(p32, dim, dim, dim, ps_buf, st, &ps);
-    if (rc != VB_OK) return rc;
+    int rc = VB_OK;
+    if (cache) {
+        const long long ldd = pad4(dim);
+        ps = SplitMat{cache, dim, dim, ldd, (long long)dim * ldd};
+        bias = const_cast<float*>(cache) + split_bytes(dim, dim) / 4;
+    } else {
+        gauss_prep_kernel<<<grid_for((long long)dim * dim, 256, kNumSMs * 2), 256, 0, st>>>(mean, prec, dim, p32, bias);
+        VB_LAUNCH_CHECK();
+        rc = split_into(p32, dim, dim, dim, ps_buf, st, &ps);
+        if (rc != VB_OK) return rc;
+    }
     const GemmShape shape = plan_gemm(n, dim, dim, 1);
     const GaussEpi epi{g, dim, bias, x, mean, rowpart, chunks};
     if (dim % 4 == 0 && (reinterpret_cast<uintptr_t>(x) & 15u) == 0) {  // x read as plain fp32, split on chip into TMEM
@@ -322,20 +342,42 @@ int gauss_logp_grad_f32(const double* mean, const double* prec, int dim, const f
 // ------------------------------------------------------------------------------------------ G_S = Ztilde' diag(w) G
 // A(a, i) = z[i, a] (MN-major), B(i, b) = (w_i / s_i) g[i, b] (MN-major), K = n, split-K partials in fp32,
 // reduced in fp64.
+// Also returns the weighted column sums sum_i w_i g[i, c] (the gradient w.r.t. the mean) when `colparts` is given:
+// the launch then has a thread count that is a multiple of ldd, so a thread always meets the same column and keeps
+// its sum in a register; colparts[block][thread] are merged in fixed order by colparts_sum_kernel.
 __global__ void split_rowscaled_kernel(const float* __restrict__ src, long long rows, long long cols,
                                        const double* __restrict__ w, const float* __restrict__ chi2, float df,
-                                       float* __restrict__ dst, long long ldd, long long plane) {
+                                       float* __restrict__ dst, long long ldd, long long plane,
+                                       double* __restrict__ colparts) {
     const long long total = rows * ldd;
+    double acc = 0.0;
     for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
          e += (long long)gridDim.x * blockDim.x) {
         const long long r = e / ldd, c = e - r * ldd;
         float hi = 0.f, lo = 0.f;
         if (c < cols) {
-            const float sc = (float)(w[r] / sqrt((double)chi2[r] / (double)df));
-            tc::split_tf32(sc * src[r * cols + c], hi, lo);
+            const double wr = w[r];
+            const float gv = src[r * cols + c];
+            const float sc = (float)(wr / sqrt((double)chi2[r] / (double)df));
+            tc::split_tf32(sc * gv, hi, lo);
+            acc = fma(wr, (double)gv, acc);
         }
         dst[e] = hi;
         dst[e + plane] = lo;
+    }
+    if (colparts) colparts[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = acc;
+}
+// out[c] = sum over the threads t with (t mod ldd) == c of colparts[t], ascending t (fixed order)
+__global__ void colparts_sum_kernel(const double* __restrict__ colparts, long long n_threads, long long ldd, int cols,
+                                    double* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const long long warp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long c = warp; c < cols; c += nwarps) {
+        double s = 0.0;
+        for (long long t = c + (long long)lane * ldd; t < n_threads; t += 32 * ldd) s += colparts[t];
+        s = warp_sum(s);
+        if (lane == 0) out[c] = s;
     }
 }
 struct SplitKEpi {
@@ -378,11 +420,17 @@ __global__ void splitk_sum_f64_kernel(const float* __restrict__ parts, int split
 
 size_t fr_weighted_tf32_workspace_bytes(long long n, int dim) {
     const int splits = plan_gemm(dim, dim, n, auto_splits(dim, dim, n)).splits;
-    return 2 * split_bytes(n, dim) + (((size_t)splits * dim * dim * 4 + 255) & ~(size_t)255) + 512;
+    return 2 * split_bytes(n, dim) + (((size_t)splits * dim * dim * 4 + 255) & ~(size_t)255) +
+           (size_t)kNumSMs * 8 * 256 * 8 + 512;                    // + per-thread column-sum partials
+}
+bool fr_weighted_colsum_fused(long long n, int dim) {
+    const long long ldd = pad4(dim);
+    return ((long long)grid_for(n * ldd, 256, kNumSMs * 8) * 256) % ldd == 0;
 }
 
 int fr_weighted_GS_tf32(double df, long long n, int dim, const float* z, const float* chi2, const double* w,
-                        const float* grad, double* out_GS, void* ws, size_t ws_bytes, cudaStream_t st) {
+                        const float* grad, double* out_GS, void* ws, size_t ws_bytes, cudaStream_t st,
+                        double* out_gmu_or_null) {
     if (!ws || ws_bytes < fr_weighted_tf32_workspace_bytes(n, dim)) return VB_ERR_WORKSPACE;
     char* wp = (char*)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
     float* zs_buf = (float*)wp;     wp += split_bytes(n, dim);
@@ -392,9 +440,17 @@ int fr_weighted_GS_tf32(double df, long long n, int dim, const float* z, const f
     int rc = split_into(z, n, dim, dim, zs_buf, st, &zs);
     if (rc != VB_OK) return rc;
     const long long ldd = pad4(dim);
-    split_rowscaled_kernel<<<grid_for(n * ldd, 256, kNumSMs * 8), 256, 0, st>>>(grad, n, dim, w, chi2, (float)df,
-                                                                               gs_buf, ldd, n * ldd);
+    // the weighted column sums ride along when the thread count is a multiple of the padded row length
+    const int sgrid = grid_for(n * ldd, 256, kNumSMs * 8);
+    const long long sthreads = (long long)sgrid * 256;
+    const bool fuse = out_gmu_or_null != nullptr && sthreads % ldd == 0;
+    double* colparts = fuse ? (double*)(wp + (((size_t)plan_gemm(dim, dim, n, auto_splits(dim, dim, n)).splits * dim * dim * 4 + 255) & ~(size_t)255)) : nullptr;
+    split_rowscaled_kernel<<<sgrid, 256, 0, st>>>(grad, n, dim, w, chi2, (float)df, gs_buf, ldd, n * ldd, colparts);
     VB_LAUNCH_CHECK();
+    if (fuse) {
+        colparts_sum_kernel<<<grid_for((long long)dim * 32, 256, kNumSMs), 256, 0, st>>>(colparts, sthreads, ldd, dim, out_gmu_or_null);
+        VB_LAUNCH_CHECK();
+    }
     const SplitMat gs{gs_buf, n, dim, ldd, n * ldd};
     const GemmShape shape = plan_gemm(dim, dim, n, auto_splits(dim, dim, n));
     const long long mn = (long long)dim * dim;

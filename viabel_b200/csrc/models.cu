@@ -269,6 +269,18 @@ extern "C" int vb_model_create_gauss(const double* d_mean, const double* d_preci
     int rc = new_model(VB_MODEL_GAUSS, dim, out, &m);
     if (rc) return rc;
     m->d_mean = d_mean; m->d_prec = d_precision;
+    m->d_gauss_cache = nullptr;
+    return VB_OK;
+}
+extern "C" size_t vb_model_gauss_cache_bytes(int dim) { return dim < 1 ? 0 : gauss_cache_bytes(dim); }
+extern "C" int vb_model_gauss_attach_cache(vb_model* model, float* d_cache, void* stream) {
+    if (!model || !d_cache) return VB_ERR_ARG;
+    ModelHost* m = reinterpret_cast<ModelHost*>(model);
+    if (m->kind != VB_MODEL_GAUSS) return VB_ERR_UNSUPPORTED;
+    if (reinterpret_cast<uintptr_t>(d_cache) & 255u) return VB_ERR_ALIGN;
+    const int rc = gauss_fill_cache(m->d_mean, m->d_prec, m->dim, d_cache, (cudaStream_t)stream);
+    if (rc != VB_OK) return rc;
+    m->d_gauss_cache = d_cache;
     return VB_OK;
 }
 
@@ -331,7 +343,7 @@ extern "C" int vb_model_logp_grad(const vb_model* model, int dtype, const void* 
                 return VB_OK;
             }
             return gauss_logp_grad_f32(m->d_mean, m->d_prec, D, (const float*)d_x, n, d_out_logp,
-                                       (float*)d_out_grad_or_null, d_ws, ws_bytes, st);
+                                       (float*)d_out_grad_or_null, d_ws, ws_bytes, st, m->d_gauss_cache);
         }
         case VB_MODEL_REGRESSION: {
             const size_t need = vb_model_logp_grad_workspace_bytes(model, n, dtype);

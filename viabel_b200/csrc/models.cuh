@@ -29,6 +29,7 @@ struct ModelHost {
     // gauss
     const double* d_mean;
     const double* d_prec;
+    const float* d_gauss_cache;   // or null: [tf32 hi/lo planes of float(P) | bias = mean' P (fp32)] made once (vb_model_gauss_attach_cache)
 };
 
 struct Funnel {

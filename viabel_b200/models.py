@@ -163,3 +163,8 @@ class CorrelatedGaussian(Model):
             raise ValueError('mean must be (d,) and precision (d, d)')
         self._keep = [md, Pd]
         _lib.check(_lib.lib.vb_model_create_gauss(ptr(md), ptr(Pd), Pd.shape[0], C.byref(self._handle)), 'gauss')
+        # constants of the fp32 tensor path (tf32 planes of P, bias mean' P): model data, made once
+        import torch
+        cache = torch.empty(int(_lib.lib.vb_model_gauss_cache_bytes(Pd.shape[0])), dtype=torch.uint8, device=Pd.device)
+        _lib.check(_lib.lib.vb_model_gauss_attach_cache(self._handle, ptr(cache), stream_ptr()), 'gauss_attach_cache')
+        self._keep.append(cache)
