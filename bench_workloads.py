@@ -676,7 +676,7 @@ class C3(Workload):
         self.units_per_step = self.n
         self.h2d_bytes = lam.nbytes
         self.d2h_bytes = 8 * (1 + lam.size)
-        self.launches_per_step = 40
+        self.launches_per_step = 20
         # pre-split operands for the kernel-only timing: X (n, d) = Z (n, d) S (d, d)
         lib = _lib.lib
         z = self.base['z']
@@ -687,6 +687,12 @@ class C3(Workload):
         _lib.check(lib.vb_split_f32(ptr(S), self.d, self.d, self.d, ptr(self._ss), 0))
         self._c = torch.empty((self.n, self.d), dtype=torch.float32, device='cuda')
         self._ptr = ptr
+        g = torch.Generator(device='cuda')
+        g.manual_seed(3)
+        self._GS = torch.randn((self.d, self.d), dtype=torch.float64, device='cuda', generator=g)
+        self._gmu = torch.randn(self.d, dtype=torch.float64, device='cuda', generator=g)
+        self._rows = torch.tensor([0.0, float(self.n) / 8, -1.0, -2.0], dtype=torch.float64, device='cuda')
+        self._out = torch.empty(1 + lam.size, dtype=torch.float64, device='cuda')
 
     def step_device(self):
         return self.obj(self.lam_dev, base_draws=self.base)
@@ -695,20 +701,35 @@ class C3(Workload):
         return self.obj(self.lam_host)
 
     def kernel_only(self):
+        """The step's dominant kernels: the O(d^3) chain pair (fr_chain_forward_kernel + fr_chain_backward_kernel)."""
         from viabel_b200._device import stream_ptr
-        p = self._ptr
-        self.lib.check(self.lib.lib.vb_gemm_tf32x3_split(0, 1, self.n, self.d, self.d, p(self._zs), p(self._ss),
-                                                         p(self._c), self.d, stream_ptr()))
+        impl, lib, p, d = self.fam.impl, self.lib.lib, self._ptr, self.d
+        ch = impl.chain_kernel(self.lam_dev)
+        ws = impl.ws.get('chain', lib.vb_fr_chain_workspace_bytes(d))
+        self.lib.check(lib.vb_fr_chain_backward(d, 0 if self.scale == 'sqrtm' else 1, 1, 2.0, float(self.n), p(ch['L']),
+                                                p(ch['S']), p(self._GS), p(self._gmu), p(self._rows), p(ch['scal']),
+                                                p(self._out), p(ws), ws.numel(), stream_ptr()), 'vb_fr_chain_backward')
 
     def roofline(self, ms_kernel, hbm_gbs, bf16_tflops):
-        flops = 2.0 * self.n * self.d * self.d                # algorithmic: counted once, the 3x split is overhead
-        ach = flops / (ms_kernel * 1e-3) / 1e12
-        peak = bf16_tflops / 2.0
-        return {'bound': 'tensor', 'achieved': ach, 'peak': peak, 'unit': 'TFLOP/s', 'frac': ach / peak,
-                'traffic': None, 'kernel': 'gemm_tf32x3_kernel<K-major A, MN-major B> (z S product, 65536x512x512)',
-                'ms_per_launch': ms_kernel, 'algorithmic_flops_per_launch': flops,
-                'note': 'peak = measured dense bf16 / 2 (tf32 runs at half the bf16 rate); three tf32 MMAs are issued '
-                        'per algorithmic product, so frac <= 1/3 by construction; tensor-pipe rate = 3 x achieved'}
+        info = self.fam.impl.chain_info()                     # [polar, inverse, smith iterations, status]
+        # GEMMs executed by the pair: polar (A = X'X + update; the first steps are the 3-GEMM quintic), S = L Q',
+        # inverse (2 per step + 1), A0 / Y0 (3), Smith (3 per step), (Y + Y') L
+        lift = min(info[0], 6)
+        gemms = (3 * lift + 2 * (info[0] - lift) + 1) + 1 + (2 * info[1] + 1) + 3 + 3 * info[2] + 1 if self.scale == 'sqrtm' else 0
+        flops = gemms * 2.0 * self.d ** 3
+        ach = flops / (ms_kernel * 1e-3) / 1e12 if ms_kernel > 0 else 0.0
+        peak = 40.0
+        return {'bound': 'tensor', 'achieved': ach, 'peak': peak, 'unit': 'TFLOP/s', 'frac': ach / peak, 'traffic': None,
+                'peak_kind': 'f64', 'peak_source': 'nominal B200 fp64 tensor rate (40 TFLOP/s); MEASURED_PEAKS.json has no fp64 figure',
+                'kernel': 'fr_chain_forward_kernel + fr_chain_backward_kernel (O(d^3) chain: polar Newton-Schulz sqrtm, '
+                          'squared-Smith Sylvester solve, packing; fp64 mma.sync m8n8k4)',
+                'ms_per_launch': ms_kernel, 'executed_gemms': gemms, 'iterations': info,
+                'executed_flops_per_launch': flops,
+                'note': 'the chain pair is the dominant kernel of the step (see share_of_step); `achieved` counts the '
+                        'EXECUTED fp64 GEMM flops (%d GEMMs of 512^3), not an algorithmic minimum: the iteration trades '
+                        'flops for having no eigendecomposition (cuSOLVER syevd took 4.7 ms here).  The per-sample products '
+                        '(z S, (x - mu_p) P_p, Z\' diag(w) G: 6 d^2 flop per sample) run on tcgen05 3xTF32 at 0.14 / 0.19 / '
+                        '0.14 ms per launch (profiles/r2k_launches_c3.txt)' % gemms}
 
     def config(self):
         return {'workload': self.config_name(), 'samples_per_step_per_gpu': self.n, 'scale': self.scale,

@@ -498,6 +498,13 @@ int vb_psis_smooth_div(const double* d_lw_in, double* d_lw_out, long long n, dou
 size_t vb_gpd_fit_workspace_bytes(long long n);
 int vb_gpd_fit(const double* d_x_sorted, long long n, double* d_out_k_sigma,
                void* d_ws, size_t ws_bytes, void* stream);
+/* ascending sort of a float64 array (gpdfitnew(sort=True), psis.py:254-265) */
+size_t vb_sort_f64_workspace_bytes(long long n);
+int vb_sort_f64(const double* d_x, long long n, double* d_out, void* d_ws, size_t ws_bytes, void* stream);
+/* gpdfitnew(return_quadrature=True) (psis.py:314-331): also the m = 30 + floor(sqrt(n)) quadrature points ks (weak
+ * prior applied) and their unnormalised weights; the caller drops weights below 10 eps and normalises (psis.py:300-305). */
+int vb_gpd_fit_quadrature(const double* d_x_sorted, long long n, double* d_out_k_sigma, double* d_out_ks,
+                          double* d_out_w, void* d_ws, size_t ws_bytes, void* stream);
 int vb_gpd_inv(const double* d_p, long long n, double k, double sigma, double* d_out,
                void* stream);
 size_t vb_logsumexp_workspace_bytes(long long n);

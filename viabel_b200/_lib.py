@@ -109,6 +109,9 @@ SIGNATURES = {
     'vb_psis_smooth_columns': (_i, [_p, _p, _ll, _ll, _d, _p, _p, _p, _p]),
     'vb_gpd_fit_workspace_bytes': (_sz, [_ll]),
     'vb_gpd_fit': (_i, [_p, _ll, _p, _p, _sz, _p]),
+    'vb_sort_f64_workspace_bytes': (_sz, [_ll]),
+    'vb_sort_f64': (_i, [_p, _ll, _p, _p, _sz, _p]),
+    'vb_gpd_fit_quadrature': (_i, [_p, _ll, _p, _p, _p, _p, _sz, _p]),
     'vb_gpd_inv': (_i, [_p, _ll, _d, _d, _p, _p]),
     'vb_logsumexp_workspace_bytes': (_sz, [_ll]),
     'vb_logsumexp': (_i, [_p, _ll, _p, _p, _sz, _p]),

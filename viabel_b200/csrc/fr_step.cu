@@ -151,7 +151,8 @@ __global__ void fr_logdensity_rows_kernel(long long n, int D, const double* __re
         double s = 0.0;
         for (int j = lane; j < D; j += 32) { const double v = Y[i * D + j]; s = fma(v, v, s); }
         s = warp_sum(s);
-        if (lane == 0) out[i] = c_total - 0.5 * (df + D) * log(1.0 + s / df);
+        // df = inf: the multivariate normal (_distributions.py:24-25), c_total carries its constant
+        if (lane == 0) out[i] = isinf(df) ? c_total - 0.5 * s : c_total - 0.5 * (df + D) * log(1.0 + s / df);
     }
 }
 
@@ -342,8 +343,9 @@ extern "C" int vb_fr_logdensity(int dtype, const double* d_mu, const double* d_U
         return VB_ERR_ARG;
     if (rc != VB_OK) return rc;
     // lgamma((df+d)/2) - lgamma(df/2) - d/2 log(pi df) - 1/2 log pdet      (_distributions.py:33-34)
-    const double c_total = lgamma(0.5 * (df + dim)) - lgamma(0.5 * df) - 0.5 * dim * log(3.14159265358979323846 * df)
-                           - 0.5 * log_pdet;
+    const double c_total = isinf(df)
+        ? -0.5 * dim * 1.8378770664093453 - 0.5 * log_pdet                       // mvn.logpdf: -d/2 log(2 pi) - 1/2 log pdet
+        : lgamma(0.5 * (df + dim)) - lgamma(0.5 * df) - 0.5 * dim * log(3.14159265358979323846 * df) - 0.5 * log_pdet;
     fr_logdensity_rows_kernel<<<grid_for(n * 32, 256, kNumSMs * 8), 256, 0, st>>>(n, dim, Y, c_total, df, d_out_logq);
     VB_LAUNCH_CHECK();
     return VB_OK;

@@ -1721,6 +1721,68 @@ extern "C" int vb_gpd_fit(const double* d_x_sorted, long long n, double* d_out_k
     return VB_OK;
 }
 
+// ascending sort of a float64 array (gpdfitnew(sort=True), psis.py:254-265): monotone keys + the bitonic network
+namespace vb {
+__global__ void sort_fill_kernel(const double* __restrict__ x, long long n, long long n_pad, Cand* __restrict__ c) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n_pad; i += (long long)gridDim.x * blockDim.x) {
+        Cand e;
+        e.key = i < n ? f64_to_key(x[i]) : 0xffffffffffffffffull;
+        e.idx = (unsigned long long)i;
+        c[i] = e;
+    }
+}
+__global__ void sort_unpack_kernel(const Cand* __restrict__ c, long long n, double* __restrict__ out) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        out[i] = key_to_f64(c[i].key);
+}
+}  // namespace vb
+extern "C" size_t vb_sort_f64_workspace_bytes(long long n) { return n < 1 ? 0 : (size_t)pad_pow2(n) * sizeof(Cand) + 256; }
+extern "C" int vb_sort_f64(const double* d_x, long long n, double* d_out, void* d_ws, size_t ws_bytes, void* stream) {
+    if (!d_x || !d_out || !d_ws || n < 1) return VB_ERR_ARG;
+    if (ws_bytes < vb_sort_f64_workspace_bytes(n)) return VB_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    Cand* c = (Cand*)(((uintptr_t)d_ws + 255) & ~(uintptr_t)255);
+    const long long n_pad = pad_pow2(n);
+    sort_fill_kernel<<<grid_for(n_pad, 256, kNumSMs * 4), 256, 0, st>>>(d_x, n, n_pad, c);
+    VB_LAUNCH_CHECK();
+    const int rc = bitonic_sort(c, n_pad, st);
+    if (rc != VB_OK) return rc;
+    sort_unpack_kernel<<<grid_for(n, 256, kNumSMs * 4), 256, 0, st>>>(c, n, d_out);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+
+// gpdfitnew(return_quadrature=True) (psis.py:314-331): the quadrature points ks_j = mean_r log1p(-b_j x_r) with the
+// weak prior applied, and the UNNORMALISED weights w_j = 1 / sum_i exp(L_i - L_j) of all m points (the caller drops
+// the negligible ones, psis.py:300-305, and normalises: output formatting of <= a few hundred numbers)
+namespace vb {
+__global__ void gpd_quadrature_kernel(const double* __restrict__ parts, const double* __restrict__ wq, long long n,
+                                      long long m, double* __restrict__ ks, double* __restrict__ w) {
+    for (long long j = blockIdx.x * (long long)blockDim.x + threadIdx.x; j < m; j += (long long)gridDim.x * blockDim.x) {
+        double s = 0.0;
+        for (int k = 0; k < kGpdSplit; ++k) s += parts[j * kGpdSplit + k];
+        const double a = 10.0;
+        ks[j] = (s / (double)n) * (double)n / ((double)n + a) + a * 0.5 / ((double)n + a);
+        w[j] = wq[j];
+    }
+}
+}  // namespace vb
+extern "C" int vb_gpd_fit_quadrature(const double* d_x_sorted, long long n, double* d_out_k_sigma, double* d_out_ks,
+                                     double* d_out_w, void* d_ws, size_t ws_bytes, void* stream) {
+    if (!d_out_ks || !d_out_w) return VB_ERR_ARG;
+    const int rc = vb_gpd_fit(d_x_sorted, n, d_out_k_sigma, d_ws, ws_bytes, stream);
+    if (rc != VB_OK) return rc;
+    char* ws = (char*)d_ws;
+    const long long m_max = 30 + (long long)sqrt((double)n) + 1;
+    const size_t mb = align_up((size_t)m_max * 8, 256);
+    const double* Lq = (const double*)(ws + 512 + mb);
+    const double* wq = (const double*)(ws + 512 + (2 + kGpdSplit) * mb);
+    const long long m = 30 + (long long)sqrt((double)n);
+    gpd_quadrature_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(Lq + m_max, wq, n, m, d_out_ks, d_out_w);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+
 namespace vb {
 __global__ void gpd_inv_kernel(const double* __restrict__ p, long long n, double k, double sigma, double* __restrict__ out) {
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {

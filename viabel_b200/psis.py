@@ -177,29 +177,50 @@ def psislw_detail(lw, Reff=1.0):
 
 
 def gpdfitnew(x, sort=True, sort_in_place=False, return_quadrature=False):
-    """Zhang–Stephens GPD fit (``psis.py:211-331``): returns ``(k, sigma)``."""
+    """Zhang–Stephens GPD fit (``psis.py:211-331``): returns ``(k, sigma)`` or, with ``return_quadrature``,
+    ``(k, sigma, ks, w)`` (quadrature points and weights of the marginal posterior of k)."""
     if x.ndim != 1 or len(x) <= 1:
         raise ValueError("Invalid input array.")
-    if return_quadrature:
-        raise NotImplementedError('return_quadrature is not part of the CUDA path')
     dev = to_dev(x, _lib.F64)
     if sort is False:
         xs = dev.contiguous()
     elif sort is True:
-        xs = torch.sort(dev).values
-        if sort_in_place and isinstance(x, np.ndarray):
-            x.sort()
+        xs = _sorted_1d(dev)
+        if sort_in_place:                                 # psis.py:255-257
+            if isinstance(x, np.ndarray):
+                x[...] = xs.cpu().numpy()
+            elif isinstance(x, torch.Tensor):
+                x.copy_(xs)
     else:
         idx = torch.as_tensor(np.asarray(sort) if not isinstance(sort, torch.Tensor) else sort, device=dev.device)
         xs = dev[idx.long()].contiguous()
     n = xs.numel()
-    if n <= 4:
-        raise NotImplementedError('the CUDA GPD fit needs more than 4 points (psislw never calls it with fewer)')
     out = torch.empty(2, dtype=torch.float64, device=xs.device)
     ws = WS.get('gpdfit', _lib.lib.vb_gpd_fit_workspace_bytes(n))
-    _lib.check(_lib.lib.vb_gpd_fit(ptr(xs), n, ptr(out), ptr(ws), ws.numel(), stream_ptr()), 'vb_gpd_fit')
+    if not return_quadrature:
+        _lib.check(_lib.lib.vb_gpd_fit(ptr(xs), n, ptr(out), ptr(ws), ws.numel(), stream_ptr()), 'vb_gpd_fit')
+        k, sigma = out.cpu().numpy()
+        return k, sigma
+    m = 30 + int(np.sqrt(n))                              # psis.py:268
+    ks = torch.empty(m, dtype=torch.float64, device=xs.device)
+    w = torch.empty(m, dtype=torch.float64, device=xs.device)
+    _lib.check(_lib.lib.vb_gpd_fit_quadrature(ptr(xs), n, ptr(out), ptr(ks), ptr(w), ptr(ws), ws.numel(), stream_ptr()),
+               'vb_gpd_fit_quadrature')
     k, sigma = out.cpu().numpy()
-    return k, sigma
+    ks, w = ks.cpu().numpy(), w.cpu().numpy()
+    keep = w >= 10 * np.finfo(float).eps                  # psis.py:300-305: drop negligible weights, normalise
+    ks, w = ks[keep], w[keep]
+    return k, sigma, ks, w / w.sum()
+
+
+def _sorted_1d(dev):
+    """Ascending sort of a 1-D device array with the library's own bitonic network (``vb_sort_f64``)."""
+    v = dev.contiguous()
+    n = v.numel()
+    out = torch.empty_like(v)
+    ws = WS.get('sort', _lib.lib.vb_sort_f64_workspace_bytes(n))
+    _lib.check(_lib.lib.vb_sort_f64(ptr(v), n, ptr(out), ptr(ws), ws.numel(), stream_ptr()), 'vb_sort_f64')
+    return out
 
 
 def gpinv(p, k, sigma):
@@ -213,10 +234,8 @@ def gpinv(p, k, sigma):
 
 
 def sumlogs(x, axis=None, out=None):
-    """``log(sum(exp(x)))`` (``psis.py:379-395``).  ``axis`` may be None (all elements) or 0 of a
-    2-D array (one value per column)."""
-    if out is not None:
-        raise NotImplementedError('out= is not supported')
+    """``log(sum(exp(x)))`` (``psis.py:379-395``).  ``axis``: None (all elements) or an axis of a 2-D array;
+    ``out``: array that receives the result (returned), as in the reference."""
     dev = to_dev(x, _lib.F64)
 
     def one(v):
@@ -229,8 +248,17 @@ def sumlogs(x, axis=None, out=None):
 
     if axis is None or dev.ndim == 1:
         r = one(dev)
-        return float(r.item()) if is_host(x) else r[0]
-    if axis == 0 and dev.ndim == 2:
-        r = torch.cat([one(dev[:, j]) for j in range(dev.shape[1])])
-        return like_input(r, x)
-    raise NotImplementedError('sumlogs supports axis=None or axis=0')
+        res = float(r.item()) if is_host(x) else r[0]
+    elif dev.ndim == 2 and axis in (0, 1, -1, -2):
+        cols = dev if axis in (0, -2) else dev.t()
+        r = torch.cat([one(cols[:, j]) for j in range(cols.shape[1])])
+        res = like_input(r, x)
+    else:
+        raise ValueError('sumlogs: axis must be None or an axis of a 1-D / 2-D array')
+    if out is not None:
+        if isinstance(out, np.ndarray):
+            out[...] = res if not isinstance(res, torch.Tensor) else res.cpu().numpy()
+        else:
+            out.copy_(res if isinstance(res, torch.Tensor) else torch.as_tensor(res))
+        return out
+    return res

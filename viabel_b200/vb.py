@@ -40,6 +40,7 @@ __all__ = [
     'rmsprop_IA_optimize_with_rhat',
     'adam_IA_optimize_with_rhat',
     'learning_rate_schedule',
+    'multivariate_t_logpdf',
 ]
 
 _Fields = namedtuple('VariationalFamily',
@@ -281,6 +282,31 @@ class _FullRank(_FamilyImpl):
         return phi
 
 
+def multivariate_t_logpdf(x, m, S, df=np.inf, _impl=None):
+    """``viabel/_distributions.py:8-38``: log density of the multivariate Student t (any positive semidefinite
+    ``S``: pseudo-inverse and pseudo-determinant through ``eigh``, eigenvalues with ``abs(s) <= 1e-10`` dropped,
+    ``:27-31``).  ``x``: (n, d) or (d,) numpy / CUDA tensor; returns (n,) of the same kind.  ``df = inf`` is the
+    multivariate normal (``:24-25``)."""
+    host = is_host(x)
+    code = (_impl.code if _impl is not None else _lib.F64) if host else dtype_code(x.dtype)
+    xd = to_dev(x, code)
+    if xd.ndim == 1:
+        xd = xd[None, :]
+    xd = xd.contiguous()
+    n, d = xd.shape
+    mu, Sigma = to_dev(m, _lib.F64).contiguous(), to_dev(S, _lib.F64).contiguous()
+    s, u = torch.linalg.eigh(Sigma)                                      # _distributions.py:27 (off the step path)
+    s_pinv = torch.where(s.abs() <= 1e-10, torch.zeros_like(s), 1.0 / s)
+    U = (u * s_pinv.sqrt()).contiguous()
+    log_pdet = float(torch.log(s).sum())
+    out = torch.empty(n, dtype=torch.float64, device=xd.device)
+    ws_owner = _impl.ws if _impl is not None else WS
+    ws = ws_owner.get('logdensity', _lib.lib.vb_fr_logdensity_workspace_bytes(n, d))
+    _lib.check(_lib.lib.vb_fr_logdensity(dtype_code(xd.dtype), ptr(mu), ptr(U), log_pdet, float(df), n, d, ptr(xd),
+                                         ptr(out), ptr(ws), ws.numel(), stream_ptr()), 'vb_fr_logdensity')
+    return like_input(out, x)
+
+
 def t_variational_family(dim, df, dtype='f64', scale='sqrtm'):
     if df <= 2:
         raise ValueError('df must be greater than 2')
@@ -316,24 +342,9 @@ def t_variational_family(dim, df, dtype='f64', scale='sqrtm'):
         return lam[:dim], L @ L.T
 
     def logdensity(x, var_param):
-        host = is_host(x)
-        xd = to_dev(x, impl.code if host else dtype_code(x.dtype))
-        code = dtype_code(xd.dtype)
-        if xd.ndim == 1:
-            xd = xd[None, :]
-        xd = xd.contiguous()
         vp = to_dev(var_param, _lib.F64)
         mu, _, Sigma = impl.fold(vp)
-        s, u = torch.linalg.eigh(Sigma)                                  # _distributions.py:27
-        s_pinv = torch.where(s.abs() <= 1e-10, torch.zeros_like(s), 1.0 / s)
-        U = (u * s_pinv.sqrt()).contiguous()
-        log_pdet = float(torch.log(s).sum())
-        n = xd.shape[0]
-        out = torch.empty(n, dtype=torch.float64, device=xd.device)
-        ws = impl.ws.get('logdensity', _lib.lib.vb_fr_logdensity_workspace_bytes(n, dim))
-        _lib.check(_lib.lib.vb_fr_logdensity(code, ptr(mu), ptr(U), log_pdet, impl.df, n, dim, ptr(xd), ptr(out),
-                                             ptr(ws), ws.numel(), stream_ptr()), 'vb_fr_logdensity')
-        return like_input(out, x)
+        return multivariate_t_logpdf(x, mu, Sigma, df, _impl=impl)
 
     def mean_and_cov(var_param):
         mu, Sigma = _fold_host(var_param)
