@@ -112,6 +112,53 @@ class Workload:
                 'e2e': {'value': arms[best], 'unit': self.unit, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
 
 
+class MeanFieldStages:
+    """--stage-times for the sample-sharded mean-field objectives: CUDA-event time of (i) the local step (draws, model,
+    reductions -> this rank's partial vector), (ii) the one all-gather of the partial vectors, (iii) the finalise
+    kernel, each over `steps` back-to-back repetitions; bench.py reports max and min over ranks, which separates the
+    collective's cost from rank skew."""
+
+    def stage_times(self, steps):
+        import torch
+        import torch.distributed as dist
+        from viabel_b200 import _lib
+        from viabel_b200._device import all_gather_rows
+        obj = self.obj
+        vp = self.lam_dev
+        impl = obj.impl
+        base = getattr(self, '_stage_base', None)
+        n_local = self.n
+        index0 = self.rank * self.n
+
+        def timed(fn):
+            torch.cuda.synchronize()
+            if self.world > 1:
+                dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(steps):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1) / steps
+
+        state = {}
+
+        def local():
+            state['out'], state['partials'] = obj._mf(vp, base, 0, 0, index0, n_local, finalize=(self.world == 1))
+        t_local = timed(local)
+        out = {'local_step': t_local}
+        if self.world > 1:
+            def gather():
+                state['g'] = all_gather_rows(state['partials'], self.world, None)
+            out['all_gather'] = timed(gather)
+
+            def fin():
+                obj._mf_merge(vp, state['partials'], self.world, None)
+            out['all_gather_plus_finalize'] = timed(fin)
+        return out
+
+
 # ======================================================================================= C4
 EIGHT_SCHOOLS_LAM = np.array(
     [4.4, 0.8, 0.3, 0.1, -0.1, 0.1, -0.2, -0.1, 0.35, 0.06] +
@@ -128,7 +175,7 @@ def _c4_cpu_job(job):
     return v, g
 
 
-class C4(Workload):
+class C4(MeanFieldStages, Workload):
     """eight-schools non-centred, mean-field t (df 40), KLVI, 2^22 samples per step per GPU."""
     name = 'c4'
     n = 1 << 22
@@ -795,7 +842,7 @@ def c2_problem(N=1 << 20, d=128):
     return X, y, lam
 
 
-class C2(Workload):
+class C2(MeanFieldStages, Workload):
     """Student-t robust regression N = 2^20 rows, d = 128; KLVI, mean-field Student-t (df 40), 4096 samples/step."""
     name = 'c2'
     n, N, d = 4096, 1 << 20, 128
