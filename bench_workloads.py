@@ -758,11 +758,8 @@ class C3(Workload):
                                                 p(self._out), p(ws), ws.numel(), stream_ptr()), 'vb_fr_chain_backward')
 
     def roofline(self, ms_kernel, hbm_gbs, bf16_tflops):
-        info = self.fam.impl.chain_info()                     # [polar, inverse, smith iterations, status]
-        # GEMMs executed by the pair: polar (A = X'X + update; the first steps are the 3-GEMM quintic), S = L Q',
-        # inverse (2 per step + 1), A0 / Y0 (3), Smith (3 per step), (Y + Y') L
-        lift = min(info[0], 6)
-        gemms = (3 * lift + 2 * (info[0] - lift) + 1) + 1 + (2 * info[1] + 1) + 3 + 3 * info[2] + 1 if self.scale == 'sqrtm' else 0
+        info = self.fam.impl.chain_info()       # [polar, inverse, smith iterations, status, forward GEMMs, backward GEMMs]
+        gemms = info[4] + info[5]               # counted by the kernels themselves
         flops = gemms * 2.0 * self.d ** 3
         ach = flops / (ms_kernel * 1e-3) / 1e12 if ms_kernel > 0 else 0.0
         peak = 40.0

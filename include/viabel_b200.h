@@ -303,10 +303,12 @@ int vb_gemm_tf32x3_split(int a_mn_major, int b_mn_major, long long m, long long 
  * no eigendecomposition, no library call.  Replaces paragami's fold + scipy sqrtm (viabel/vb.py:185-189, 207) and
  * autograd's sqrtm VJP (solve_sylvester) + the assembly of value_and_grad's result (vb.py:236-266).
  *   vb_fr_chain_forward   var_param -> L (d, d), S (d, d) = sqrtm(L L') [scale_mode 0] or L' [1: x = mu + L ztilde],
- *                         optional fp32 copy of S, d_out_scal[2] = (sum of the log-diagonal = entropy, |L|_F^2)
+ *                         optional fp32 copy of S, d_out_scal[4] = (sum of the log-diagonal = entropy, |L|_F^2,
+ *                         an upper bound of sigma_max(L) that the backward's inverse iteration starts from, reserved)
  *   vb_fr_chain_backward  G_S = Ztilde' diag(w) G, g_mu = sum w g, rows = [max lw, sum w, sum log p, sum lw]
  *                         -> d_out[1 + P] = (value, gradient) of KLVI (objective 0), CHIVI (1), path-derivative KLVI (2)
- *   vb_fr_chain_info      iteration counts and status of the last calls on a workspace (synchronises)
+ *   vb_fr_chain_info      h_out6 = [polar, inverse, Smith iterations, status (0 = every iteration met its tolerance),
+ *                         GEMMs executed by the forward, by the backward] of the last calls on a workspace (synchronises)
  * ---------------------------------------------------------------------------------- */
 size_t vb_fr_chain_workspace_bytes(int dim);
 int vb_fr_chain_forward(const double* d_var_param, int dim, int scale_mode, double* d_out_L, double* d_out_S,
@@ -315,7 +317,7 @@ int vb_fr_chain_backward(int dim, int scale_mode, int objective, double alpha, d
                          const double* d_L, const double* d_S, const double* d_GS, const double* d_gmu,
                          const double* d_rows, const double* d_scal, double* d_out, void* d_ws, size_t ws_bytes,
                          void* stream);
-int vb_fr_chain_info(const void* d_ws, int dim, int* h_out4, void* stream);
+int vb_fr_chain_info(const void* d_ws, int dim, int* h_out6, void* stream);
 
 /* ------------------------------------------------------------------------------------
  * Bounds (viabel/bounds.py).

@@ -209,6 +209,36 @@ def test_full_rank_t(scale, d, n):
     assert rel(g, og) < 1e-9
 
 
+@pytest.mark.parametrize('span', [1.5, 3.0, 4.5])
+def test_full_rank_chain_ill_conditioned(span):
+    """The chain kernels on scale factors whose spectrum reaches cond(L) = 11, 2e2, 1.1e5 (cond(Sigma) = 1.3e10: beyond that the oracle's own eigh of Sigma has no digits left): the polar schedule is built
+    for sigma_min / sigma_max >= 1e-3 and re-enters in cycles below that; the Smith doubling and the inverse iteration
+    count up with the condition number.  Tolerance scales with cond(L) (the Sylvester solve is that ill-conditioned:
+    the eigh formulation of the oracle loses the same digits)."""
+    from viabel_b200 import models, vb
+    d, n = 40, 2000
+    mp, Pp = _gauss(d)
+    model, omodel = models.CorrelatedGaussian(mp, Pp), mm.CorrelatedGaussian(mp, Pp)
+    fam, ofam = vb.t_variational_family(d, 40), vb_np.t_variational_family(d, 40)
+    rs = np.random.RandomState(8)
+    lam = 0.05 * rs.randn(fam.var_param_dim)
+    mu_, L, _ = ofam.impl.fold(lam)
+    r, c = np.tril_indices(d)
+    diag_pos = d + np.flatnonzero(r == c)
+    lam[diag_pos] = np.linspace(-span, 0.5, d)[rs.permutation(d)]
+    mu_, L, _ = ofam.impl.fold(lam)
+    cond = np.linalg.cond(L)
+    base = ofam.impl.draw_base(np.random.RandomState(5), n)
+    v, g = vb.black_box_chivi(2.0, fam, model, n, group=False)(lam, base_draws=base)
+    info = fam.impl.chain_info()
+    assert info[3] == 0, info
+    ov, og = vb_np.chivi_value_and_grad(ofam.impl, omodel, 2.0, lam, base)
+    np.testing.assert_allclose(v, ov, rtol=1e-13 * max(cond, 100.0))
+    assert rel(g, og) < 1e-14 * cond + 1e-12, (rel(g, og), cond, info)      # measured 7e-15, 1e-13, 4e-11
+    if span > 4:
+        assert info[0] > 8, info          # the spectrum reaches below 1e-3: the schedule re-entered
+
+
 def test_full_rank_family_closures():
     import torch
     from viabel_b200 import vb

@@ -204,11 +204,19 @@ __device__ __forceinline__ double sum_partials(const volatile double* parts) {
     return warp_sum(s);
 }
 
+// Minimax odd quintics a x + b x^3 + c x^5 for the polar iteration: polynomial k is the best approximation of 1 on the
+// image [1 - t, 1 + t] of its predecessor, starting from [1e-3, 1] (scripts/polar_schedule.py; errors t = 0.9915,
+// 0.9646, 0.8598, 0.5459, 0.1134, 9.2e-4).
+__constant__ double kPolarSched[6][3] = {
+    {8.470329, -25.108079, 18.629279}, {4.182834, -3.108701, 0.580607}, {3.961856, -2.954063, 0.562976},
+    {3.286584, -2.464719, 0.507358},   {2.273748, -1.644659, 0.416191}, {1.888716, -1.265157, 0.376519}};
+
 struct ChainWs {
     double *X0, *X1, *T0, *T1, *T2, *T3;        // six d x d scratch matrices
     double* parts;                              // [3][grid] norm partials (rotating: a slot is rewritten two barriers later)
     unsigned int* barrier;
     int* info;                                  // [0] polar iterations [1] inverse iterations [2] smith iterations [3] status
+                                                // [4] GEMMs executed by the forward [5] by the backward
 };
 
 // ------------------------------------------------------------------------------------------ forward
@@ -218,7 +226,7 @@ struct FwdArgs {
     double* L;                 // out (d, d)
     double* S;                 // out (d, d) fp64: row-form scale matrix (x = mu + ztilde S): sqrtm(Sigma) or L'
     float* S32;                // out (d, d) fp32 copy or null
-    double* scal;              // out [0] entropy = sum phi_ii  [1] |L|_F^2
+    double* scal;              // out [0] entropy = sum phi_ii  [1] |L|_F^2  [2] upper bound of sigma_max(L) (sqrtm mode)
     ChainWs ws;
 };
 
@@ -268,40 +276,60 @@ fr_chain_forward_kernel(const FwdArgs a) {
             a.S[e] = v;
             if (a.S32) a.S32[e] = (float)v;
         }
-        if (gtid == 0) { a.ws.info[0] = 0; a.ws.info[3] = 0; }
+        if (gtid == 0) { a.ws.info[0] = 0; a.ws.info[3] = 0; a.ws.info[4] = 0; a.scal[2] = 0.0; }
         return;
     }
-    // ---- polar factor of L: X0 = L / |L|_F
+    // ---- polar factor of L: X0 = L / |L|_F, then X0 / s with s^2 = |X0'X0|_F >= sigma_max(X0)^2 (Frobenius alone
+    // leaves the spectrum a factor ~sqrt(d) below 1; this bound, free with the first product, leaves d^(1/4))
     const double inv_f = 1.0 / sqrt(f2);
     double* X = a.ws.X0;
     double* Xn = a.ws.X1;
     for (long long e = gtid; e < dd; e += gth) X[e] = a.L[e] * inv_f;
     grid_barrier(a.ws.barrier, phase);
     const double tol2 = 16.0 * (double)d * 1e-28;        // |X'X - I|_F < 4 sqrt(d) 1e-14
-    int its = 0, status = 1;
-    bool lifting = true;
-    for (int it = 0; it < 60; ++it) {
+    int its = 0, status = 1, ng = 0;
+    double ps = 1.0;                                     // pending scale: the iterate is X / ps, its Gram matrix T0 / ps^2
+    double err2 = INFINITY;
+    bool finishing = false;
+    for (int it = 0; it < 80; ++it) {
         double* p = next_slot();
-        const double part = chain_gemm(sm, d, true, X, false, X, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 1);      // A = X'X
+        const double part = chain_gemm(sm, d, true, X, false, X, 1.0, 0.0, nullptr, 0.0, a.ws.T0, it == 0 ? 2 : 1);   // A = X'X
+        ++ng;
         if (threadIdx.x == 0) p[blockIdx.x] = part;
         grid_barrier(a.ws.barrier, phase);
-        const double err2 = sum_partials(p);
-        if (err2 < tol2) { status = 0; break; }
-        if (lifting && (err2 < 0.25 || it >= 8)) lifting = false;
-        if (lifting) {
-            // quintic lift: X <- a X + X (b A + c A^2)
-            chain_gemm(sm, d, false, a.ws.T0, false, a.ws.T0, 2.0315, -4.7750, a.ws.T0, 0.0, a.ws.T1, 0);  // B = c A A + b A
+        if (it == 0) {
+            ps = sqrt(sqrt(sum_partials(p)) * (1.0 + 1e-12));
+            if (gtid == 0) a.scal[2] = ps * sqrt(f2);    // >= sigma_max(L) = lambda_max(S): the backward's inverse starts from it
+        } else {
+            err2 = sum_partials(p);
+            if (err2 < tol2) { status = 0; break; }
+        }
+        // Schedule: six minimax quintics (kPolarSched: [l, 1] -> 1 +- 9e-4 for l = 1e-3), then the cubic Newton-Schulz
+        // step; a spectrum reaching below 1e-3 re-enters the schedule at its second polynomial (valid on [0, 1.99]) in
+        // cycles of five (x234 per cycle) until the error seen at a cycle boundary is small.
+        if (it >= 6 && (it - 6) % 5 == 0 && err2 <= 0.25) finishing = true;
+        if (err2 <= 0.0025) finishing = true;
+        if (!finishing) {
+            const double* q = kPolarSched[it < 6 ? it : 1 + (it - 6) % 5];
+            const double i2 = 1.0 / (ps * ps);
+            // B = c A^2 + b A, X <- a X + X B with the pending scale folded into the coefficients
+            chain_gemm(sm, d, false, a.ws.T0, false, a.ws.T0, q[2] * i2 * i2, q[1] * i2, a.ws.T0, 0.0, a.ws.T1, 0);
             grid_barrier(a.ws.barrier, phase);
-            chain_gemm(sm, d, false, X, false, a.ws.T1, 1.0, 3.4445, X, 0.0, Xn, 0);
+            chain_gemm(sm, d, false, X, false, a.ws.T1, 1.0 / ps, q[0] / ps, X, 0.0, Xn, 0);
+            ng += 2;
         } else {
             chain_gemm(sm, d, false, X, false, a.ws.T0, -0.5, 1.5, X, 0.0, Xn, 0);                          // 1.5 X - 0.5 X A
+            ++ng;
         }
+        ps = 1.0;
         grid_barrier(a.ws.barrier, phase);
         double* t = X; X = Xn; Xn = t;
         ++its;
+        if (finishing && err2 < 1e-14) { status = 0; break; }   // quadratic: the next error is ~err^2 < 1e-14, no product spent on seeing it
     }
     // ---- S = sym(L Q'), Q = X
     chain_gemm(sm, d, false, a.L, true, X, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 0);
+    ++ng;
     grid_barrier(a.ws.barrier, phase);
     for (long long e = gtid; e < dd; e += gth) {
         const int r = (int)(e / d), c = (int)(e - (long long)r * d);
@@ -309,7 +337,7 @@ fr_chain_forward_kernel(const FwdArgs a) {
         a.S[e] = v;
         if (a.S32) a.S32[e] = (float)v;
     }
-    if (gtid == 0) { a.ws.info[0] = its; a.ws.info[3] = status; }
+    if (gtid == 0) { a.ws.info[0] = its; a.ws.info[3] = status; a.ws.info[4] = ng; }
 }
 
 // ------------------------------------------------------------------------------------------ backward
@@ -339,47 +367,23 @@ fr_chain_backward_kernel(const BwdArgs a) {
     auto next_slot = [&]() { double* p = parts + (size_t)slot * gridDim.x; slot = (slot + 1) % 3; return p; };
     const double* GL = nullptr;          // d f / d L as (d, d) row-major
     bool gl_transposed = false;
-    int inv_its = 0, smith_its = 0, status = 0;
+    int inv_its = 0, smith_its = 0, status = 0, ng = 0;
     if (a.mode == 1) {
         GL = a.GS;                       // chol: G_L = G_S' (x = mu + L ztilde)
         gl_transposed = true;
     } else {
-        // ---- M^-1, M = S + mu I, mu = rms eigenvalue of S = sqrt(|L|_F^2 / d);  X0 = I / |M|_1
+        // ---- M^-1, M = S + mu I, mu = rms eigenvalue of S = sqrt(|L|_F^2 / d).  S is positive semi-definite and the
+        // forward left ub >= lambda_max(S) in scal[2], so spec(M) lies in [mu, ub + mu] and X0 = 2 / (ub + 2 mu) I
+        // starts Newton-Schulz at |I - M X0|_2 <= ub / (ub + 2 mu) < 1 (the classic I / |M|_1 start cost two more steps)
         const double mu = sqrt(a.scal[1] / (double)d);
         double* Mx = a.ws.T3;            // M
-        double colmax = 0.0;
+        const double ub = a.scal[2];
+        double* X = a.ws.X0;
+        double* Xn = a.ws.X1;
+        const double x0 = 2.0 / (ub + 2.0 * mu);
         for (long long e = gtid; e < dd; e += gth) {
             const int r = (int)(e / d), c = (int)(e - (long long)r * d);
             Mx[e] = a.S[e] + (r == c ? mu : 0.0);
-        }
-        // |M|_1 = max column sum (M symmetric: row sums); one warp per row
-        {
-            const int lane = threadIdx.x & 31;
-            const long long gw = gtid >> 5, nw = gth >> 5;
-            for (long long r = gw; r < d; r += nw) {
-                double s = 0.0;
-                for (int c = lane; c < d; c += 32) s += fabs(a.S[(size_t)r * d + c] + (r == c ? mu : 0.0));
-                s = warp_sum(s);
-                colmax = fmax(colmax, s);
-            }
-            colmax = warp_max(colmax);
-            __syncthreads();
-            if (lane == 0) sm.red[threadIdx.x >> 5] = colmax;
-            __syncthreads();
-            double m = 0.0;
-            for (int w = 0; w < kCT / 32; ++w) m = fmax(m, sm.red[w]);
-            __syncthreads();
-            double* p = next_slot();
-            if (threadIdx.x == 0) p[blockIdx.x] = m;
-            grid_barrier(a.ws.barrier, phase);
-            colmax = 0.0;
-            for (unsigned int b = 0; b < gridDim.x; ++b) colmax = fmax(colmax, ((const volatile double*)p)[b]);
-        }
-        double* X = a.ws.X0;
-        double* Xn = a.ws.X1;
-        const double x0 = 1.0 / colmax;
-        for (long long e = gtid; e < dd; e += gth) {
-            const int r = (int)(e / d), c = (int)(e - (long long)r * d);
             X[e] = (r == c) ? x0 : 0.0;
         }
         grid_barrier(a.ws.barrier, phase);
@@ -388,13 +392,17 @@ fr_chain_backward_kernel(const BwdArgs a) {
         for (int it = 0; it < 60; ++it) {
             double* p = next_slot();
             const double part = chain_gemm(sm, d, false, Mx, false, X, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 1);   // R = M X
+            ++ng;
             if (threadIdx.x == 0) p[blockIdx.x] = part;
             grid_barrier(a.ws.barrier, phase);
-            if (sum_partials(p) < tol2) { status = 0; break; }
+            const double err2 = sum_partials(p);
+            if (err2 < tol2) { status = 0; break; }
             chain_gemm(sm, d, false, X, false, a.ws.T0, -1.0, 2.0, X, 0.0, Xn, 0);                           // 2 X - X R
+            ++ng;
             grid_barrier(a.ws.barrier, phase);
             double* t = X; X = Xn; Xn = t;
             ++inv_its;
+            if (err2 < 1e-14) { status = 0; break; }     // the residual squares: now < 1e-14, no product spent on seeing it
         }
         // ---- A0 = S M^-1 - mu M^-1,  Y0 = 2 mu M^-1 G M^-1
         double* Aq = a.ws.T1;
@@ -404,14 +412,16 @@ fr_chain_backward_kernel(const BwdArgs a) {
         chain_gemm(sm, d, false, X, false, a.GS, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 0);                        // T = M^-1 G
         grid_barrier(a.ws.barrier, phase);
         chain_gemm(sm, d, false, a.ws.T0, false, X, 2.0 * mu, 0.0, nullptr, 0.0, Y, 0);                      // Y0
+        ng += 3;
         {
             double* p = next_slot();
             const double part = chain_gemm(sm, d, false, a.S, false, X, 1.0, -mu, X, 0.0, Aq, 2);            // A0, |A0|_F^2
             if (threadIdx.x == 0) p[blockIdx.x] = part;
             grid_barrier(a.ws.barrier, phase);
             double na2 = sum_partials(p);
-            // ---- doubling: Y <- Y + A Y A, A <- A^2 until |A|_F is negligible
-            for (int it = 0; it < 60 && na2 > 1e-34; ++it) {
+            // ---- doubling: Y <- Y + A Y A, A <- A^2.  What is still missing after a step is A_new Y A_new, relatively
+            // |A_new|_2^2 <= |A_new|_F^2: stop once that is below 1e-17
+            for (int it = 0; it < 60 && na2 > 1e-17; ++it) {
                 chain_gemm(sm, d, false, Aq, false, Y, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 0);                  // T = A Y
                 double* p2 = next_slot();
                 const double part2 = chain_gemm(sm, d, false, Aq, false, Aq, 1.0, 0.0, nullptr, 0.0, Aq2, 2);   // A^2 (independent)
@@ -423,11 +433,13 @@ fr_chain_backward_kernel(const BwdArgs a) {
                 double* t = Aq; Aq = Aq2; Aq2 = t;
                 t = Y; Y = Yn; Yn = t;
                 ++smith_its;
+                ng += 3;
             }
-            if (na2 > 1e-34 && status == 0) status = 3;
+            if (na2 > 1e-17 && status == 0) status = 3;
         }
         // ---- G_L = (Y + Y') L
         chain_gemm(sm, d, false, Y, false, a.L, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 0, true);
+        ++ng;
         grid_barrier(a.ws.barrier, phase);
         GL = a.ws.T0;
     }
@@ -443,7 +455,7 @@ fr_chain_backward_kernel(const BwdArgs a) {
         else if (a.objective == 0) v = -(entropy + a.rows[2] / nt);
         else v = -(a.rows[3] / nt);
         a.out[0] = v;
-        a.ws.info[1] = inv_its; a.ws.info[2] = smith_its;
+        a.ws.info[1] = inv_its; a.ws.info[2] = smith_its; a.ws.info[5] = ng;
         if (status) a.ws.info[3] = status;
     }
     for (long long j = gtid; j < d; j += gth) a.out[1 + j] = gscale * a.gmu[j];
@@ -541,11 +553,12 @@ extern "C" int vb_fr_chain_backward(int dim, int scale_mode, int objective, doub
     return VB_OK;
 }
 
-// iteration counts and status of the last forward / backward on this workspace: [polar, inverse, smith, status]
-extern "C" int vb_fr_chain_info(const void* d_ws, int dim, int* h_out4, void* stream) {
-    if (!d_ws || !h_out4 || dim < 1) return VB_ERR_ARG;
+// iteration counts and status of the last forward / backward on this workspace:
+// [polar, inverse, smith, status, GEMMs of the forward, GEMMs of the backward]
+extern "C" int vb_fr_chain_info(const void* d_ws, int dim, int* h_out6, void* stream) {
+    if (!d_ws || !h_out6 || dim < 1) return VB_ERR_ARG;
     const ChainWs w = chain_ws(const_cast<void*>(d_ws), dim);
-    VB_CUDA_TRY(cudaMemcpyAsync(h_out4, w.info, 4 * sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    VB_CUDA_TRY(cudaMemcpyAsync(h_out6, w.info, 6 * sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     VB_CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
     return VB_OK;
 }

@@ -231,15 +231,16 @@ class _FullRank(_FamilyImpl):
         L = torch.empty((d, d), dtype=torch.float64, device=dev)
         S = torch.empty((d, d), dtype=torch.float64, device=dev)
         S32 = torch.empty((d, d), dtype=torch.float32, device=dev) if self.code != _lib.F64 else None
-        scal = torch.empty(2, dtype=torch.float64, device=dev)
+        scal = torch.empty(4, dtype=torch.float64, device=dev)
         ws = self.ws.get('chain', _lib.lib.vb_fr_chain_workspace_bytes(d))
         _lib.check(_lib.lib.vb_fr_chain_forward(ptr(vp), d, 0 if self.scale == 'sqrtm' else 1, ptr(L), ptr(S), ptr(S32),
                                                 ptr(scal), ptr(ws), ws.numel(), stream_ptr()), 'vb_fr_chain_forward')
         return {'mu': vp[:d], 'L': L, 'S': S, 'S32': S32, 'scal': scal, 'kernel': True}
 
     def chain_info(self):
-        """[polar, inverse, smith iterations, status] of the last chain kernels (synchronises)."""
-        out = (ctypes.c_int * 4)()
+        """[polar, inverse, smith iterations, status, forward GEMMs, backward GEMMs] of the last chain kernels
+        (synchronises)."""
+        out = (ctypes.c_int * 6)()
         ws = self.ws.get('chain', _lib.lib.vb_fr_chain_workspace_bytes(self.dim))
         _lib.check(_lib.lib.vb_fr_chain_info(ptr(ws), self.dim, out, stream_ptr()), 'vb_fr_chain_info')
         return list(out)
