@@ -17,12 +17,12 @@
 
 namespace vb {
 
-constexpr int kCT = 256;                   // threads per CTA: two groups of 4 warps, each takes half of every k slab
-constexpr int kCM = 64, kCN = 32, kCK = 32;    // CTA tile (k slab 32: half as many exposed L2 round trips as 16)
+constexpr int kCConsumers = 256;           // MMA warps: two groups of 4 warps, each takes half of every k slab
+constexpr int kCGroups = kCConsumers / 128;
+constexpr int kCProducers = 128;           // copy warps: issue the cp.async of the operand slabs, nothing else
+constexpr int kCT = kCConsumers + kCProducers;
+constexpr int kCM = 64, kCN = 32, kCK = 32;    // CTA tile and k slab
 constexpr int kCMaxGrid = 148;
-constexpr int kCAld = kCM + 4, kCBld = kCN + 4;   // leading dimensions = 4 (mod 16): conflict-free fragment loads
-
-struct ChainBarrier { unsigned int count; };
 
 // all CTAs of the (cooperative: co-resident) grid; `phase` counts the barriers this thread block has passed
 __device__ __forceinline__ void grid_barrier(unsigned int* counter, unsigned int& phase) {
@@ -48,142 +48,178 @@ __device__ __forceinline__ void dmma(double (&c)[2], double a, double b) {
 
 // C (d x d, ld = d) = alpha op(A) op(B) + beta E + gamma I, every CTA of the grid takes tiles t = blockIdx.x, + gridDim.x ..
 // norm_mode: 0 none, 1 partial of |C - I|_F^2, 2 partial of |C|_F^2  -> returned (this CTA's sum, valid in every thread)
-// sym_mode:  the A operand is read as (A + A') (used for (Y + Y') L)
-struct GemmSmem { double As[2][kCK][kCAld]; double Bs[2][kCK][kCBld]; double red[kCT / 32]; };     // 53 KB: dynamic
+//
+// Operand slabs (k = 32) travel global (L2) -> shared memory by cp.async into a ring of kCStages buffers, in their
+// GLOBAL layout (no transposing store: the m8n8k4 fragments are 8-byte scalar loads, so either orientation is read in
+// place; row pitches = 4 mod 16 doubles keep both conflict-free).  The copies are issued by four PRODUCER warps and
+// complete on a per-stage mbarrier (cp.async.mbarrier.arrive); the eight MMA warps only wait on it, load fragments and
+// issue DMMAs, and hand the stage back through a second mbarrier: no __syncthreads in the k loop.  The operand
+// orientations are template parameters, so that every fragment offset is an immediate of its shared-memory load (as
+// run-time strides they cost an integer multiply-add per load and 20 % of the kernel).  `ring` counts the slabs a CTA
+// has consumed since the kernel began: stage and mbarrier parity follow from it, across tiles and across GEMMs.
+constexpr int kCStages = 5;
+constexpr int kCPitchK = kCK + 4;          // rows of k-values (A not transposed, B transposed)
+constexpr int kCPitchM = kCM + 4;          // rows of m-values (A transposed)
+constexpr int kCPitchN = kCN + 4;          // rows of n-values (B not transposed)
+constexpr int kCABytes = (kCM * kCPitchK > kCK * kCPitchM ? kCM * kCPitchK : kCK * kCPitchM) * 8;
+constexpr int kCBBytes = (kCN * kCPitchK > kCK * kCPitchN ? kCN * kCPitchK : kCK * kCPitchN) * 8;
+struct GemmSmem {
+    unsigned char stage[kCStages][kCABytes + kCBBytes];
+    double xch[(kCGroups - 1) * 16 * 128];             // k-split exchange
+    double red[kCT / 32];
+    unsigned long long full[kCStages], empty[kCStages];
+};                                                     // 151 KB: dynamic
 
-__device__ double chain_gemm(GemmSmem& sm, int d, bool ta, const double* __restrict__ A, bool tb, const double* __restrict__ B,
-                             double alpha, double beta, const double* E, double gamma, double* __restrict__ C,
-                             int norm_mode, bool sym_a = false) {
+__device__ __forceinline__ void chain_smem_init(GemmSmem& sm) {
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kCStages; ++s) {
+            mbar_init(reinterpret_cast<uint64_t*>(&sm.full[s]), kCProducers);
+            mbar_init(reinterpret_cast<uint64_t*>(&sm.empty[s]), kCConsumers / 32);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+}
+template <int BYTES>
+__device__ __forceinline__ void cp_async(void* smem_dst, const void* gsrc, bool valid) {
+    const unsigned int dst = (unsigned int)__cvta_generic_to_shared(smem_dst);
+    const int sz = valid ? BYTES : 0;                  // src-size 0: the destination is zero-filled
+    if (BYTES == 16)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(gsrc), "r"(sz) : "memory");
+    else
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(dst), "l"(gsrc), "r"(sz) : "memory");
+}
+// the executing thread's earlier cp.async copies arrive on `bar` when they have landed (counted in the expected arrivals)
+__device__ __forceinline__ void cp_async_arrive(unsigned long long* bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kCConsumers) : "memory"); }
+
+// VEC = doubles per copy: 2 when d is even (every row start is 16-byte aligned), else 1
+template <int VEC, bool ta, bool tb>
+__device__ __noinline__ double chain_gemm_impl(GemmSmem& sm, unsigned int& ring, int d, const double* __restrict__ A,
+                                               const double* __restrict__ B, double alpha, double beta,
+                                               const double* E, double gamma, double* __restrict__ C, int norm_mode) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int grp = warp >> 2;                                      // k-split group of this warp
-    const int wm = (warp & 1) * 32, wn = ((warp >> 1) & 1) * 16;
     const int tiles_m = (d + kCM - 1) / kCM, tiles_n = (d + kCN - 1) / kCN;
+    const int nslab = (d + kCK - 1) / kCK;
     double nrm = 0.0;
-    for (int t = blockIdx.x; t < tiles_m * tiles_n; t += gridDim.x) {
-        const int i0 = (t / tiles_n) * kCM, j0 = (t % tiles_n) * kCN;
-        double acc[4][2][2];
+    if (tid >= kCConsumers) {
+        // ---------------------------------------------------------------- producer warps
+        const int ptid = tid - kCConsumers;
+        for (int t = blockIdx.x; t < tiles_m * tiles_n; t += gridDim.x) {
+            const int i0 = (t / tiles_n) * kCM, j0 = (t % tiles_n) * kCN;
+            for (int slab = 0; slab < nslab; ++slab, ++ring) {
+                const int st = ring % kCStages;
+                mbar_wait(reinterpret_cast<uint64_t*>(&sm.empty[st]), ((ring / kCStages) & 1) ^ 1);
+                const int k0 = slab * kCK;
+                double* as = reinterpret_cast<double*>(sm.stage[st]);
+                double* bs = reinterpret_cast<double*>(sm.stage[st] + kCABytes);
+                constexpr int kChunksA = kCM * kCK / VEC, kChunksB = kCN * kCK / VEC;
 #pragma unroll
-        for (int a = 0; a < 4; ++a)
-#pragma unroll
-            for (int b = 0; b < 2; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
-        constexpr int kNA = kCM * kCK / kCT, kNB = kCN * kCK / kCT;
-        // two register sets: slab k + 2 is requested while slab k is multiplied, so every global (L2) load has two
-        // slabs of tensor work to land (one slab, ~0.5 us, does not cover the ~0.8 us round trip)
-        double ra[2][kNA], rb[2][kNB];
-        auto load = [&](int k0, double (&qa)[kNA], double (&qb)[kNB]) {
-#pragma unroll
-            for (int e = 0; e < kNA; ++e) {
-                const int idx = tid + e * kCT;
-                int m, k;
-                if (!ta) { m = idx / kCK; k = idx % kCK; } else { m = idx % kCM; k = idx / kCM; }   // contiguous index fastest
-                const int gm = i0 + m, gk = k0 + k;
-                double v = 0.0;
-                if (gm < d && gk < d) {
-                    v = ta ? A[(size_t)gk * d + gm] : A[(size_t)gm * d + gk];
-                    if (sym_a) v += ta ? A[(size_t)gm * d + gk] : A[(size_t)gk * d + gm];
+                for (int c = ptid; c < kChunksA; c += kCProducers) {
+                    // rows of the global layout: (m, k..) when not transposed, (k, m..) when transposed
+                    int row, col;
+                    if (!ta) { row = c / (kCK / VEC); col = (c % (kCK / VEC)) * VEC; }
+                    else { row = c / (kCM / VEC); col = (c % (kCM / VEC)) * VEC; }
+                    const int gr = (ta ? k0 : i0) + row, gc = (ta ? i0 : k0) + col;
+                    const bool ok = gr < d && gc < d;
+                    cp_async<VEC * 8>(as + row * (ta ? kCPitchM : kCPitchK) + col, ok ? A + (size_t)gr * d + gc : A, ok);
                 }
-                qa[e] = v;
+#pragma unroll
+                for (int c = ptid; c < kChunksB; c += kCProducers) {
+                    int row, col;                        // (k, n..) or (n, k..)
+                    if (!tb) { row = c / (kCN / VEC); col = (c % (kCN / VEC)) * VEC; }
+                    else { row = c / (kCK / VEC); col = (c % (kCK / VEC)) * VEC; }
+                    const int gr = (tb ? j0 : k0) + row, gc = (tb ? k0 : j0) + col;
+                    const bool ok = gr < d && gc < d;
+                    cp_async<VEC * 8>(bs + row * (tb ? kCPitchK : kCPitchN) + col, ok ? B + (size_t)gr * d + gc : B, ok);
+                }
+                cp_async_arrive(&sm.full[st]);
             }
-#pragma unroll
-            for (int e = 0; e < kNB; ++e) {
-                const int idx = tid + e * kCT;
-                int n, k;
-                if (!tb) { n = idx % kCN; k = idx / kCN; } else { n = idx / kCK; k = idx % kCK; }
-                const int gn = j0 + n, gk = k0 + k;
-                qb[e] = (gn < d && gk < d) ? (tb ? B[(size_t)gn * d + gk] : B[(size_t)gk * d + gn]) : 0.0;
-            }
-        };
-        auto store = [&](int buf, const double (&qa)[kNA], const double (&qb)[kNB]) {
-#pragma unroll
-            for (int e = 0; e < kNA; ++e) {
-                const int idx = tid + e * kCT;
-                int m, k;
-                if (!ta) { m = idx / kCK; k = idx % kCK; } else { m = idx % kCM; k = idx / kCM; }
-                sm.As[buf][k][m] = qa[e];
-            }
-#pragma unroll
-            for (int e = 0; e < kNB; ++e) {
-                const int idx = tid + e * kCT;
-                int n, k;
-                if (!tb) { n = idx % kCN; k = idx / kCN; } else { n = idx / kCK; k = idx % kCK; }
-                sm.Bs[buf][k][n] = qb[e];
-            }
-        };
-        auto multiply = [&](int buf) {
-#pragma unroll
-            for (int kk = grp * 4; kk < kCK; kk += 8) {
-                double af[4], bf[2];
-#pragma unroll
-                for (int a = 0; a < 4; ++a) af[a] = sm.As[buf][kk + (lane & 3)][wm + a * 8 + (lane >> 2)];
-#pragma unroll
-                for (int b = 0; b < 2; ++b) bf[b] = sm.Bs[buf][kk + (lane & 3)][wn + b * 8 + (lane >> 2)];
-#pragma unroll
-                for (int a = 0; a < 4; ++a)
-#pragma unroll
-                    for (int b = 0; b < 2; ++b) dmma(acc[a][b], af[a], bf[b]);
-            }
-        };
-        // prologue: slab 0 -> smem buffer 0, slab 1 -> register set 1
-        load(0, ra[0], rb[0]);
-        store(0, ra[0], rb[0]);
-        if (kCK < d) load(kCK, ra[1], rb[1]);
-        __syncthreads();
-        // slab s lives in smem buffer s & 1; register set s & 1 carries slab s on its way to shared memory
-        for (int k0 = 0; k0 < d; k0 += 2 * kCK) {
-            // even slab (buffer 0): request slab + 2 into set 0, multiply, move slab + 1 (set 1) into buffer 1
-            if (k0 + 2 * kCK < d) load(k0 + 2 * kCK, ra[0], rb[0]);
-            multiply(0);
-            if (k0 + kCK < d) store(1, ra[1], rb[1]);
-            __syncthreads();
-            if (k0 + kCK >= d) break;
-            // odd slab (buffer 1)
-            if (k0 + 3 * kCK < d) load(k0 + 3 * kCK, ra[1], rb[1]);
-            multiply(1);
-            if (k0 + 2 * kCK < d) store(0, ra[0], rb[0]);
-            __syncthreads();
         }
-        // the two k-split groups meet in shared memory (the operand buffers are free after the last slab)
-        {
-            double* xch = &sm.As[0][0][0];
-            if (grp == 1) {
+    } else {
+        // ---------------------------------------------------------------- MMA warps
+        const int grp = warp >> 2;                                      // k-split group of this warp
+        const int wm = (warp & 1) * 32, wn = ((warp >> 1) & 1) * 16;
+        // fragment addressing: A(m, k) at m * sa_m + k * sa_k, B(k, n) at k * sb_k + n * sb_n (doubles within a stage)
+        constexpr int sa_m = ta ? 1 : kCPitchK, sa_k = ta ? kCPitchM : 1;
+        constexpr int sb_k = tb ? 1 : kCPitchN, sb_n = tb ? kCPitchK : 1;
+        const int a_off = (wm + (lane >> 2)) * sa_m + (lane & 3) * sa_k;
+        const int b_off = (lane & 3) * sb_k + (wn + (lane >> 2)) * sb_n;
+        for (int t = blockIdx.x; t < tiles_m * tiles_n; t += gridDim.x) {
+            const int i0 = (t / tiles_n) * kCM, j0 = (t % tiles_n) * kCN;
+            double acc[4][2][2];
 #pragma unroll
-                for (int a = 0; a < 4; ++a)
+            for (int a = 0; a < 4; ++a)
 #pragma unroll
-                    for (int b = 0; b < 2; ++b)
+                for (int b = 0; b < 2; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+            for (int slab = 0; slab < nslab; ++slab, ++ring) {
+                const int st = ring % kCStages;
+                mbar_wait(reinterpret_cast<uint64_t*>(&sm.full[st]), (ring / kCStages) & 1);
+                const double* as = reinterpret_cast<const double*>(sm.stage[st]) + a_off;
+                const double* bs = reinterpret_cast<const double*>(sm.stage[st] + kCABytes) + b_off;
 #pragma unroll
-                        for (int c = 0; c < 2; ++c) xch[((a * 2 + b) * 2 + c) * 128 + (tid - 128)] = acc[a][b][c];
+                for (int kk = grp * 4; kk < kCK; kk += 4 * kCGroups) {
+                    double af[4], bf[2];
+#pragma unroll
+                    for (int a = 0; a < 4; ++a) af[a] = as[kk * sa_k + a * 8 * sa_m];
+#pragma unroll
+                    for (int b = 0; b < 2; ++b) bf[b] = bs[kk * sb_k + b * 8 * sb_n];
+#pragma unroll
+                    for (int a = 0; a < 4; ++a)
+#pragma unroll
+                        for (int b = 0; b < 2; ++b) dmma(acc[a][b], af[a], bf[b]);
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(reinterpret_cast<uint64_t*>(&sm.empty[st]));
             }
-            __syncthreads();
-            if (grp == 0) {
+            // the k-split groups meet in shared memory; group 0 adds in fixed order
+            {
+                const int t128 = tid & 127;
+                if (grp != 0) {
 #pragma unroll
-                for (int a = 0; a < 4; ++a)
+                    for (int a = 0; a < 4; ++a)
 #pragma unroll
-                    for (int b = 0; b < 2; ++b)
+                        for (int b = 0; b < 2; ++b)
 #pragma unroll
-                        for (int c = 0; c < 2; ++c) acc[a][b][c] += xch[((a * 2 + b) * 2 + c) * 128 + tid];
+                            for (int c = 0; c < 2; ++c)
+                                sm.xch[((grp - 1) * 16 + (a * 2 + b) * 2 + c) * 128 + t128] = acc[a][b][c];
+                }
+                consumer_sync();
+                if (grp == 0) {
+#pragma unroll
+                    for (int g = 0; g < kCGroups - 1; ++g)
+#pragma unroll
+                        for (int a = 0; a < 4; ++a)
+#pragma unroll
+                            for (int b = 0; b < 2; ++b)
+#pragma unroll
+                                for (int c = 0; c < 2; ++c) acc[a][b][c] += sm.xch[(g * 16 + (a * 2 + b) * 2 + c) * 128 + t128];
+                }
+                consumer_sync();
             }
-            __syncthreads();
-        }
-        // epilogue (group 0): thread holds C(row = lane / 4, cols = 2 (lane % 4), + 1) of each 8 x 8 block
-        if (grp == 0)
+            // epilogue (group 0): thread holds C(row = lane / 4, cols = 2 (lane % 4), + 1) of each 8 x 8 block
+            if (grp == 0)
 #pragma unroll
-        for (int a = 0; a < 4; ++a)
+            for (int a = 0; a < 4; ++a)
 #pragma unroll
-            for (int b = 0; b < 2; ++b)
+                for (int b = 0; b < 2; ++b)
 #pragma unroll
-                for (int c = 0; c < 2; ++c) {
-                    const int gi = i0 + wm + a * 8 + (lane >> 2), gj = j0 + wn + b * 8 + 2 * (lane & 3) + c;
-                    if (gi < d && gj < d) {
-                        double v = alpha * acc[a][b][c];
-                        if (beta != 0.0) v = fma(beta, E[(size_t)gi * d + gj], v);
-                        if (gi == gj) v += gamma;
-                        C[(size_t)gi * d + gj] = v;
-                        if (norm_mode) {
-                            const double r = (norm_mode == 1 && gi == gj) ? v - 1.0 : v;
-                            nrm = fma(r, r, nrm);
+                    for (int c = 0; c < 2; ++c) {
+                        const int gi = i0 + wm + a * 8 + (lane >> 2), gj = j0 + wn + b * 8 + 2 * (lane & 3) + c;
+                        if (gi < d && gj < d) {
+                            double v = alpha * acc[a][b][c];
+                            if (beta != 0.0) v = fma(beta, E[(size_t)gi * d + gj], v);
+                            if (gi == gj) v += gamma;
+                            C[(size_t)gi * d + gj] = v;
+                            if (norm_mode) {
+                                const double r = (norm_mode == 1 && gi == gj) ? v - 1.0 : v;
+                                nrm = fma(r, r, nrm);
+                            }
                         }
                     }
-                }
+        }
     }
     if (!norm_mode) return 0.0;
     nrm = warp_sum(nrm);
@@ -194,6 +230,22 @@ __device__ double chain_gemm(GemmSmem& sm, int d, bool ta, const double* __restr
 #pragma unroll
     for (int w = 0; w < kCT / 32; ++w) s += sm.red[w];
     return s;
+}
+
+template <int VEC>
+__device__ __forceinline__ double chain_gemm_v(GemmSmem& sm, unsigned int& ring, int d, bool ta, const double* __restrict__ A,
+                                               bool tb, const double* __restrict__ B, double alpha, double beta,
+                                               const double* E, double gamma, double* __restrict__ C, int norm_mode) {
+    if (!ta && !tb) return chain_gemm_impl<VEC, false, false>(sm, ring, d, A, B, alpha, beta, E, gamma, C, norm_mode);
+    if (ta && !tb) return chain_gemm_impl<VEC, true, false>(sm, ring, d, A, B, alpha, beta, E, gamma, C, norm_mode);
+    if (!ta && tb) return chain_gemm_impl<VEC, false, true>(sm, ring, d, A, B, alpha, beta, E, gamma, C, norm_mode);
+    return chain_gemm_impl<VEC, true, true>(sm, ring, d, A, B, alpha, beta, E, gamma, C, norm_mode);
+}
+__device__ __forceinline__ double chain_gemm(GemmSmem& sm, unsigned int& ring, int d, bool ta, const double* __restrict__ A,
+                                             bool tb, const double* __restrict__ B, double alpha, double beta,
+                                             const double* E, double gamma, double* __restrict__ C, int norm_mode) {
+    if ((d & 1) == 0) return chain_gemm_v<2>(sm, ring, d, ta, A, tb, B, alpha, beta, E, gamma, C, norm_mode);
+    return chain_gemm_v<1>(sm, ring, d, ta, A, tb, B, alpha, beta, E, gamma, C, norm_mode);
 }
 
 // sum of the per-CTA partials in fixed order (every thread of every CTA gets the same value)
@@ -237,7 +289,8 @@ fr_chain_forward_kernel(const FwdArgs a) {
     const int d = a.d;
     const long long dd = (long long)d * d;
     const long long gtid = blockIdx.x * (long long)blockDim.x + threadIdx.x, gth = (long long)gridDim.x * blockDim.x;
-    unsigned int phase = 0;
+    unsigned int phase = 0, ring = 0;
+    chain_smem_init(sm);
     double* parts = a.ws.parts;
     int slot = 0;
     auto next_slot = [&]() { double* p = parts + (size_t)slot * gridDim.x; slot = (slot + 1) % 3; return p; };
@@ -256,10 +309,11 @@ fr_chain_forward_kernel(const FwdArgs a) {
     {
         f2 = warp_sum(f2); ent = warp_sum(ent);
         __syncthreads();
-        if ((threadIdx.x & 31) == 0) { sm.red[threadIdx.x >> 5] = f2; sm.As[0][0][threadIdx.x >> 5] = ent; }
+        double* red2 = sm.xch;
+        if ((threadIdx.x & 31) == 0) { sm.red[threadIdx.x >> 5] = f2; red2[threadIdx.x >> 5] = ent; }
         __syncthreads();
         double s = 0.0, t = 0.0;
-        for (int w = 0; w < kCT / 32; ++w) { s += sm.red[w]; t += sm.As[0][0][w]; }
+        for (int w = 0; w < kCT / 32; ++w) { s += sm.red[w]; t += red2[w]; }
         __syncthreads();
         double* p = next_slot();
         double* p2 = next_slot();
@@ -293,7 +347,7 @@ fr_chain_forward_kernel(const FwdArgs a) {
     bool finishing = false;
     for (int it = 0; it < 80; ++it) {
         double* p = next_slot();
-        const double part = chain_gemm(sm, d, true, X, false, X, 1.0, 0.0, nullptr, 0.0, a.ws.T0, it == 0 ? 2 : 1);   // A = X'X
+        const double part = chain_gemm(sm, ring, d, true, X, false, X, 1.0, 0.0, nullptr, 0.0, a.ws.T0, it == 0 ? 2 : 1);   // A = X'X
         ++ng;
         if (threadIdx.x == 0) p[blockIdx.x] = part;
         grid_barrier(a.ws.barrier, phase);
@@ -313,12 +367,12 @@ fr_chain_forward_kernel(const FwdArgs a) {
             const double* q = kPolarSched[it < 6 ? it : 1 + (it - 6) % 5];
             const double i2 = 1.0 / (ps * ps);
             // B = c A^2 + b A, X <- a X + X B with the pending scale folded into the coefficients
-            chain_gemm(sm, d, false, a.ws.T0, false, a.ws.T0, q[2] * i2 * i2, q[1] * i2, a.ws.T0, 0.0, a.ws.T1, 0);
+            chain_gemm(sm, ring, d, false, a.ws.T0, false, a.ws.T0, q[2] * i2 * i2, q[1] * i2, a.ws.T0, 0.0, a.ws.T1, 0);
             grid_barrier(a.ws.barrier, phase);
-            chain_gemm(sm, d, false, X, false, a.ws.T1, 1.0 / ps, q[0] / ps, X, 0.0, Xn, 0);
+            chain_gemm(sm, ring, d, false, X, false, a.ws.T1, 1.0 / ps, q[0] / ps, X, 0.0, Xn, 0);
             ng += 2;
         } else {
-            chain_gemm(sm, d, false, X, false, a.ws.T0, -0.5, 1.5, X, 0.0, Xn, 0);                          // 1.5 X - 0.5 X A
+            chain_gemm(sm, ring, d, false, X, false, a.ws.T0, -0.5, 1.5, X, 0.0, Xn, 0);                          // 1.5 X - 0.5 X A
             ++ng;
         }
         ps = 1.0;
@@ -328,7 +382,7 @@ fr_chain_forward_kernel(const FwdArgs a) {
         if (finishing && err2 < 1e-14) { status = 0; break; }   // quadratic: the next error is ~err^2 < 1e-14, no product spent on seeing it
     }
     // ---- S = sym(L Q'), Q = X
-    chain_gemm(sm, d, false, a.L, true, X, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 0);
+    chain_gemm(sm, ring, d, false, a.L, true, X, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 0);
     ++ng;
     grid_barrier(a.ws.barrier, phase);
     for (long long e = gtid; e < dd; e += gth) {
@@ -361,7 +415,8 @@ fr_chain_backward_kernel(const BwdArgs a) {
     const int d = a.d;
     const long long dd = (long long)d * d;
     const long long gtid = blockIdx.x * (long long)blockDim.x + threadIdx.x, gth = (long long)gridDim.x * blockDim.x;
-    unsigned int phase = 0;
+    unsigned int phase = 0, ring = 0;
+    chain_smem_init(sm);
     double* parts = a.ws.parts;
     int slot = 0;
     auto next_slot = [&]() { double* p = parts + (size_t)slot * gridDim.x; slot = (slot + 1) % 3; return p; };
@@ -391,13 +446,13 @@ fr_chain_backward_kernel(const BwdArgs a) {
         status = 2;
         for (int it = 0; it < 60; ++it) {
             double* p = next_slot();
-            const double part = chain_gemm(sm, d, false, Mx, false, X, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 1);   // R = M X
+            const double part = chain_gemm(sm, ring, d, false, Mx, false, X, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 1);   // R = M X
             ++ng;
             if (threadIdx.x == 0) p[blockIdx.x] = part;
             grid_barrier(a.ws.barrier, phase);
             const double err2 = sum_partials(p);
             if (err2 < tol2) { status = 0; break; }
-            chain_gemm(sm, d, false, X, false, a.ws.T0, -1.0, 2.0, X, 0.0, Xn, 0);                           // 2 X - X R
+            chain_gemm(sm, ring, d, false, X, false, a.ws.T0, -1.0, 2.0, X, 0.0, Xn, 0);                           // 2 X - X R
             ++ng;
             grid_barrier(a.ws.barrier, phase);
             double* t = X; X = Xn; Xn = t;
@@ -409,25 +464,25 @@ fr_chain_backward_kernel(const BwdArgs a) {
         double* Aq2 = a.ws.T3;           // M is no longer needed after A0
         double* Y = a.ws.T2;
         double* Yn = Xn;                 // the spare inverse buffer
-        chain_gemm(sm, d, false, X, false, a.GS, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 0);                        // T = M^-1 G
+        chain_gemm(sm, ring, d, false, X, false, a.GS, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 0);                        // T = M^-1 G
         grid_barrier(a.ws.barrier, phase);
-        chain_gemm(sm, d, false, a.ws.T0, false, X, 2.0 * mu, 0.0, nullptr, 0.0, Y, 0);                      // Y0
+        chain_gemm(sm, ring, d, false, a.ws.T0, false, X, 2.0 * mu, 0.0, nullptr, 0.0, Y, 0);                      // Y0
         ng += 3;
         {
             double* p = next_slot();
-            const double part = chain_gemm(sm, d, false, a.S, false, X, 1.0, -mu, X, 0.0, Aq, 2);            // A0, |A0|_F^2
+            const double part = chain_gemm(sm, ring, d, false, a.S, false, X, 1.0, -mu, X, 0.0, Aq, 2);            // A0, |A0|_F^2
             if (threadIdx.x == 0) p[blockIdx.x] = part;
             grid_barrier(a.ws.barrier, phase);
             double na2 = sum_partials(p);
             // ---- doubling: Y <- Y + A Y A, A <- A^2.  What is still missing after a step is A_new Y A_new, relatively
             // |A_new|_2^2 <= |A_new|_F^2: stop once that is below 1e-17
             for (int it = 0; it < 60 && na2 > 1e-17; ++it) {
-                chain_gemm(sm, d, false, Aq, false, Y, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 0);                  // T = A Y
+                chain_gemm(sm, ring, d, false, Aq, false, Y, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 0);                  // T = A Y
                 double* p2 = next_slot();
-                const double part2 = chain_gemm(sm, d, false, Aq, false, Aq, 1.0, 0.0, nullptr, 0.0, Aq2, 2);   // A^2 (independent)
+                const double part2 = chain_gemm(sm, ring, d, false, Aq, false, Aq, 1.0, 0.0, nullptr, 0.0, Aq2, 2);   // A^2 (independent)
                 if (threadIdx.x == 0) p2[blockIdx.x] = part2;
                 grid_barrier(a.ws.barrier, phase);
-                chain_gemm(sm, d, false, a.ws.T0, false, Aq, 1.0, 1.0, Y, 0.0, Yn, 0);                       // Y + T A
+                chain_gemm(sm, ring, d, false, a.ws.T0, false, Aq, 1.0, 1.0, Y, 0.0, Yn, 0);                       // Y + T A
                 grid_barrier(a.ws.barrier, phase);
                 na2 = sum_partials(p2);
                 double* t = Aq; Aq = Aq2; Aq2 = t;
@@ -438,7 +493,12 @@ fr_chain_backward_kernel(const BwdArgs a) {
             if (na2 > 1e-17 && status == 0) status = 3;
         }
         // ---- G_L = (Y + Y') L
-        chain_gemm(sm, d, false, Y, false, a.L, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 0, true);
+        for (long long e = gtid; e < dd; e += gth) {
+            const int r = (int)(e / d), c = (int)(e - (long long)r * d);
+            Yn[e] = Y[e] + Y[(size_t)c * d + r];
+        }
+        grid_barrier(a.ws.barrier, phase);
+        chain_gemm(sm, ring, d, false, Yn, false, a.L, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 0);
         ++ng;
         grid_barrier(a.ws.barrier, phase);
         GL = a.ws.T0;
