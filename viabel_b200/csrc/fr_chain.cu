@@ -24,21 +24,36 @@ constexpr int kCT = kCConsumers + kCProducers;
 constexpr int kCM = 64, kCN = 32, kCK = 32;    // CTA tile and k slab
 constexpr int kCMaxGrid = 148;
 
+#ifdef VB_CHAIN_TRACE
+// debug build only: CTA 0 / thread 0 records (SM clock, tag) pairs; dumped by vb_fr_chain_trace_dump
+__device__ unsigned long long g_chain_trace[8192];
+__device__ unsigned int g_chain_trace_n;
+#define CHAIN_TRACE(tag)                                                                           \
+    do {                                                                                           \
+        if (blockIdx.x == 0 && threadIdx.x == 0) {                                                 \
+            const unsigned int n_ = g_chain_trace_n++;                                             \
+            if (n_ < 8192) g_chain_trace[n_] = ((unsigned long long)clock64() << 8) | (tag);       \
+        }                                                                                          \
+    } while (0)
+#else
+#define CHAIN_TRACE(tag) do { } while (0)
+#endif
+
 // all CTAs of the (cooperative: co-resident) grid; `phase` counts the barriers this thread block has passed
 __device__ __forceinline__ void grid_barrier(unsigned int* counter, unsigned int& phase) {
     __syncthreads();
     if (threadIdx.x == 0) {
-        __threadfence();
         const unsigned int target = (phase + 1) * gridDim.x;
-        atomicAdd(counter, 1u);
+        // release: the CTA's writes (ordered before this thread by the bar.sync above) are visible before the count
+        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(counter) : "memory");
         unsigned int v;
         do {
             asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
         } while (v < target);
-        __threadfence();
     }
     ++phase;
     __syncthreads();
+    CHAIN_TRACE(6);
 }
 
 __device__ __forceinline__ void dmma(double (&c)[2], double a, double b) {
@@ -154,9 +169,11 @@ __device__ __noinline__ double chain_gemm_impl(GemmSmem& sm, unsigned int& ring,
             for (int a = 0; a < 4; ++a)
 #pragma unroll
                 for (int b = 0; b < 2; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+            CHAIN_TRACE(1);
             for (int slab = 0; slab < nslab; ++slab, ++ring) {
                 const int st = ring % kCStages;
                 mbar_wait(reinterpret_cast<uint64_t*>(&sm.full[st]), (ring / kCStages) & 1);
+                if (slab == 0) CHAIN_TRACE(2);
                 const double* as = reinterpret_cast<const double*>(sm.stage[st]) + a_off;
                 const double* bs = reinterpret_cast<const double*>(sm.stage[st] + kCABytes) + b_off;
 #pragma unroll
@@ -174,6 +191,7 @@ __device__ __noinline__ double chain_gemm_impl(GemmSmem& sm, unsigned int& ring,
                 __syncwarp();
                 if (lane == 0) mbar_arrive(reinterpret_cast<uint64_t*>(&sm.empty[st]));
             }
+            CHAIN_TRACE(3);
             // the k-split groups meet in shared memory; group 0 adds in fixed order
             {
                 const int t128 = tid & 127;
@@ -199,28 +217,59 @@ __device__ __noinline__ double chain_gemm_impl(GemmSmem& sm, unsigned int& ring,
                 }
                 consumer_sync();
             }
-            // epilogue (group 0): thread holds C(row = lane / 4, cols = 2 (lane % 4), + 1) of each 8 x 8 block
-            if (grp == 0)
+            CHAIN_TRACE(4);
+            // epilogue (group 0): thread holds C(row = lane / 4, cols = 2 (lane % 4), + 1) of each 8 x 8 block.  All E
+            // values are requested before the first store (E may alias nothing the compiler can prove: interleaved,
+            // the 16 load -> store pairs ran as a chain of L2 round trips, 3.7 K cycles per GEMM)
+            if (grp == 0) {
+                double ev[4][2][2];
+                const bool use_e = beta != 0.0;
 #pragma unroll
-            for (int a = 0; a < 4; ++a)
+                for (int a = 0; a < 4; ++a)
 #pragma unroll
-                for (int b = 0; b < 2; ++b)
-#pragma unroll
-                    for (int c = 0; c < 2; ++c) {
-                        const int gi = i0 + wm + a * 8 + (lane >> 2), gj = j0 + wn + b * 8 + 2 * (lane & 3) + c;
-                        if (gi < d && gj < d) {
-                            double v = alpha * acc[a][b][c];
-                            if (beta != 0.0) v = fma(beta, E[(size_t)gi * d + gj], v);
-                            if (gi == gj) v += gamma;
-                            C[(size_t)gi * d + gj] = v;
-                            if (norm_mode) {
-                                const double r = (norm_mode == 1 && gi == gj) ? v - 1.0 : v;
-                                nrm = fma(r, r, nrm);
+                    for (int b = 0; b < 2; ++b) {
+                        const int gi = i0 + wm + a * 8 + (lane >> 2), gj = j0 + wn + b * 8 + 2 * (lane & 3);
+                        ev[a][b][0] = ev[a][b][1] = 0.0;
+                        if (use_e && gi < d) {
+                            if (VEC == 2) {
+                                if (gj < d) {
+                                    const double2 q = *reinterpret_cast<const double2*>(E + (size_t)gi * d + gj);
+                                    ev[a][b][0] = q.x; ev[a][b][1] = q.y;
+                                }
+                            } else {
+                                if (gj < d) ev[a][b][0] = E[(size_t)gi * d + gj];
+                                if (gj + 1 < d) ev[a][b][1] = E[(size_t)gi * d + gj + 1];
                             }
                         }
                     }
+#pragma unroll
+                for (int a = 0; a < 4; ++a)
+#pragma unroll
+                    for (int b = 0; b < 2; ++b) {
+                        const int gi = i0 + wm + a * 8 + (lane >> 2), gj = j0 + wn + b * 8 + 2 * (lane & 3);
+                        double v[2];
+#pragma unroll
+                        for (int c = 0; c < 2; ++c) {
+                            v[c] = fma(beta, ev[a][b][c], alpha * acc[a][b][c]);
+                            if (gi == gj + c) v[c] += gamma;
+                            if (norm_mode && gi < d && gj + c < d) {
+                                const double r = (norm_mode == 1 && gi == gj + c) ? v[c] - 1.0 : v[c];
+                                nrm = fma(r, r, nrm);
+                            }
+                        }
+                        if (gi < d) {
+                            if (VEC == 2) {
+                                if (gj < d) *reinterpret_cast<double2*>(C + (size_t)gi * d + gj) = make_double2(v[0], v[1]);
+                            } else {
+                                if (gj < d) C[(size_t)gi * d + gj] = v[0];
+                                if (gj + 1 < d) C[(size_t)gi * d + gj + 1] = v[1];
+                            }
+                        }
+                    }
+            }
         }
     }
+    CHAIN_TRACE(5);
     if (!norm_mode) return 0.0;
     nrm = warp_sum(nrm);
     __syncthreads();
@@ -572,6 +621,19 @@ static ChainWs chain_ws(void* ws, int d) {
 }  // namespace vb
 
 using namespace vb;
+
+#ifdef VB_CHAIN_TRACE
+extern "C" int vb_fr_chain_trace_dump(unsigned long long* h_out, int cap, int reset) {
+    unsigned int n = 0;
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(&n, g_chain_trace_n, sizeof(n));
+    if ((int)n > cap) n = cap;
+    if (n > 8192) n = 8192;
+    cudaMemcpyFromSymbol(h_out, g_chain_trace, (size_t)n * 8);
+    if (reset) { const unsigned int z = 0; cudaMemcpyToSymbol(g_chain_trace_n, &z, sizeof(z)); }
+    return (int)n;
+}
+#endif
 
 extern "C" size_t vb_fr_chain_workspace_bytes(int dim) { return dim < 1 ? 0 : chain_ws_bytes(dim) + 256; }
 
