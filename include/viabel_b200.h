@@ -496,6 +496,13 @@ int vb_psis_write_div(const double* d_lw, double* d_out, long long n_local, long
 int vb_psis_smooth_div(const double* d_lw_in, double* d_lw_out, long long n, double reff,
                        double* d_out_diag, long long* d_out_tail_idx_or_null,
                        double* d_out_div_partials_or_null, void* d_ws, size_t ws_bytes, void* stream);
+/* vb_psis_smooth_div whose small results also reach the HOST in the one synchronisation the call has anyway:
+ * h_out18 = [diag (8) | the alpha = 2 statistics as vb_bounds_divergence writes them (8; zeros when no partials were
+ * requested) | path taken: 0 device-driven, 1 host-driven | reserved].  Serves psislw followed by all_bounds on the
+ * same weights (notebooks/experiments.py:69,159-166) without a second device read. */
+int vb_psis_smooth_host(const double* d_lw_in, double* d_lw_out, long long n, double reff,
+                        double* d_out_diag, long long* d_out_tail_idx_or_null,
+                        double* d_out_div_partials_or_null, double* h_out18, void* d_ws, size_t ws_bytes, void* stream);
 
 size_t vb_gpd_fit_workspace_bytes(long long n);
 int vb_gpd_fit(const double* d_x_sorted, long long n, double* d_out_k_sigma,

@@ -105,6 +105,7 @@ SIGNATURES = {
     'vb_psis_div_workspace_bytes': (_sz, []),
     'vb_psis_write_div': (_i, [_p, _p, _ll, _ll, _p, _ll, _ll, _p, _p, _p, _sz, _p]),
     'vb_psis_smooth_div': (_i, [_p, _p, _ll, _d, _p, _p, _p, _p, _sz, _p]),
+    'vb_psis_smooth_host': (_i, [_p, _p, _ll, _d, _p, _p, _p, _p, _p, _sz, _p]),
     'vb_psis_columns_max_n': (_ll, []),
     'vb_psis_smooth_columns': (_i, [_p, _p, _ll, _ll, _d, _p, _p, _p, _p]),
     'vb_gpd_fit_workspace_bytes': (_sz, [_ll]),

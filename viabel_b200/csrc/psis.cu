@@ -1556,7 +1556,7 @@ extern "C" int vb_psis_write_div(const double* d_lw, double* d_out, long long n_
 namespace vb {
 struct SmoothLayout {
     long long cap1;
-    size_t off_sample, off_pivot, off_count, off_bodymax, off_terms, off_filter, off_cand1, off_tail, off_div, total;
+    size_t off_sample, off_pivot, off_count, off_bodymax, off_terms, off_filter, off_cand1, off_tail, off_div, off_pack, total;
 };
 static SmoothLayout smooth_layout(long long n, double reff) {
     SmoothLayout L;
@@ -1576,6 +1576,7 @@ static SmoothLayout smooth_layout(long long n, double reff) {
     L.off_cand1 = take((size_t)L.cap1 * sizeof(Cand));
     L.off_tail = take(vb_psis_tail_workspace_bytes(L.cap1, K1));
     L.off_div = take(vb_psis_div_workspace_bytes());
+    L.off_pack = take(24 * sizeof(double));
     L.total = o;
     return L;
 }
@@ -1586,19 +1587,49 @@ extern "C" size_t vb_psis_smooth_workspace_bytes(long long n, double reff) {
     return smooth_layout(n, reff).total + 256;
 }
 
-extern "C" int vb_psis_smooth_div(const double* d_lw_in, double* d_lw_out, long long n, double reff,
-                                  double* d_out_diag, long long* d_out_tail_idx_or_null,
-                                  double* d_out_div_partials_or_null, void* d_ws, size_t ws_bytes, void* stream);
-extern "C" int vb_psis_smooth(const double* d_lw_in, double* d_lw_out, long long n, double reff,
-                              double* d_out_diag, long long* d_out_tail_idx_or_null,
-                              void* d_ws, size_t ws_bytes, void* stream) {
-    return vb_psis_smooth_div(d_lw_in, d_lw_out, n, reff, d_out_diag, d_out_tail_idx_or_null, nullptr, d_ws, ws_bytes, stream);
+namespace vb {
+// packed host result of vb_psis_smooth_host: [0..7] diag, [8..15] divergence statistics (alpha = 2), [16] status word
+// ([8..15] are written in place by the divergence merge kernel)
+__global__ void smooth_pack_kernel(const double* __restrict__ diag, const int* __restrict__ status_or_null,
+                                   double* __restrict__ pack) {
+    const int t = threadIdx.x;
+    if (t < 8) pack[t] = diag[t];
+    else if (t == 16) pack[16] = status_or_null ? (double)*status_or_null : 0.0;
 }
-// vb_psis_smooth that also returns, from the same final pass over the weights, the one-pass statistics
-// divergence_bound(alpha = 2) needs (layout of vb_bounds_divergence_partials; finalise with vb_bounds_divergence_merge)
+static int smooth_impl(const double* d_lw_in, double* d_lw_out, long long n, double reff,
+                       double* d_out_diag, long long* d_out_tail_idx_or_null,
+                       double* d_out_div_partials_or_null, double* h_out18_or_null, void* d_ws, size_t ws_bytes, void* stream);
+}  // namespace vb
+extern "C" int vb_bounds_divergence_merge(const double* d_partials, int n_ranks, double alpha, double* d_out, void* stream);
+
 extern "C" int vb_psis_smooth_div(const double* d_lw_in, double* d_lw_out, long long n, double reff,
                                   double* d_out_diag, long long* d_out_tail_idx_or_null,
                                   double* d_out_div_partials_or_null, void* d_ws, size_t ws_bytes, void* stream) {
+    return smooth_impl(d_lw_in, d_lw_out, n, reff, d_out_diag, d_out_tail_idx_or_null, d_out_div_partials_or_null, nullptr,
+                       d_ws, ws_bytes, stream);
+}
+extern "C" int vb_psis_smooth(const double* d_lw_in, double* d_lw_out, long long n, double reff,
+                              double* d_out_diag, long long* d_out_tail_idx_or_null,
+                              void* d_ws, size_t ws_bytes, void* stream) {
+    return smooth_impl(d_lw_in, d_lw_out, n, reff, d_out_diag, d_out_tail_idx_or_null, nullptr, nullptr, d_ws, ws_bytes, stream);
+}
+// vb_psis_smooth_div that also hands the small results to the HOST in the one synchronisation the call has anyway:
+// h_out18 = [diag (8) | divergence_bound(alpha = 2) statistics as vb_bounds_divergence writes them (8; zeros when no
+// partials were requested) | path: 0 device-driven, 1 host-driven | reserved].  A caller that wants k-hat and the
+// bounds as host numbers (viabel.all_bounds does) then needs no further device read.
+extern "C" int vb_psis_smooth_host(const double* d_lw_in, double* d_lw_out, long long n, double reff,
+                                   double* d_out_diag, long long* d_out_tail_idx_or_null,
+                                   double* d_out_div_partials_or_null, double* h_out18, void* d_ws, size_t ws_bytes,
+                                   void* stream) {
+    if (!h_out18) return VB_ERR_ARG;
+    return smooth_impl(d_lw_in, d_lw_out, n, reff, d_out_diag, d_out_tail_idx_or_null, d_out_div_partials_or_null, h_out18,
+                       d_ws, ws_bytes, stream);
+}
+// the one-pass statistics divergence_bound(alpha = 2) needs come from the same final pass over the weights
+// (layout of vb_bounds_divergence_partials; finalise with vb_bounds_divergence_merge)
+static int vb::smooth_impl(const double* d_lw_in, double* d_lw_out, long long n, double reff,
+                           double* d_out_diag, long long* d_out_tail_idx_or_null,
+                           double* d_out_div_partials_or_null, double* h_out, void* d_ws, size_t ws_bytes, void* stream) {
     if (!d_lw_in || !d_lw_out || !d_out_diag || !d_ws || !(reff > 0.0)) return VB_ERR_ARG;
     if (n <= 1) return VB_ERR_ARG;                                    // psis.py:143-144
     if (d_lw_in == d_lw_out) return VB_ERR_ARG;                       // streaming loads assume no aliasing
@@ -1653,8 +1684,23 @@ extern "C" int vb_psis_smooth_div(const double* d_lw_in, double* d_lw_out, long 
         {
             const TailLayout TL = tail_layout(L.cap1, K1);
             char* tws = (char*)(((uintptr_t)(ws + L.off_tail) + 255) & ~(uintptr_t)255);
-            VB_CUDA_TRY(cudaMemcpyAsync(&h_status, tail_status_ptr(tws, TL), sizeof(int), cudaMemcpyDeviceToHost, st));
-            VB_CUDA_TRY(cudaStreamSynchronize(st));
+            if (h_out) {
+                double* pack = (double*)(ws + L.off_pack);
+                if (d_out_div_partials_or_null) {
+                    rc = vb_bounds_divergence_merge(d_out_div_partials_or_null, 1, 2.0, pack + 8, stream);
+                    if (rc != VB_OK) return rc;
+                }
+                smooth_pack_kernel<<<1, 32, 0, st>>>(d_out_diag, (const int*)tail_status_ptr(tws, TL), pack);
+                VB_LAUNCH_CHECK();
+                VB_CUDA_TRY(cudaMemcpyAsync(h_out, pack, 17 * sizeof(double), cudaMemcpyDeviceToHost, st));
+                VB_CUDA_TRY(cudaStreamSynchronize(st));
+                h_status = (int)h_out[16];
+                h_out[16] = 0.0; h_out[17] = 0.0;
+                if (!d_out_div_partials_or_null) for (int i = 8; i < 16; ++i) h_out[i] = 0.0;
+            } else {
+                VB_CUDA_TRY(cudaMemcpyAsync(&h_status, tail_status_ptr(tws, TL), sizeof(int), cudaMemcpyDeviceToHost, st));
+                VB_CUDA_TRY(cudaStreamSynchronize(st));
+            }
         }
         if (h_status == 0) return VB_OK;
     }
@@ -1690,9 +1736,23 @@ extern "C" int vb_psis_smooth_div(const double* d_lw_in, double* d_lw_out, long 
                       ws + L.off_tail, vb_psis_tail_workspace_bytes(L.cap1, K1), stream);
     if (rc != VB_OK) return rc;
     if (d_out_div_partials_or_null)
-        return vb_psis_write_div(d_lw_in, d_lw_out, n, 0, M_ptr, C1, K1, ws + L.off_tail, d_out_div_partials_or_null,
-                                 ws + L.off_div, vb_psis_div_workspace_bytes(), stream);
-    return vb_psis_write(d_lw_in, d_lw_out, n, 0, M_ptr, C1, K1, ws + L.off_tail, stream);
+        rc = vb_psis_write_div(d_lw_in, d_lw_out, n, 0, M_ptr, C1, K1, ws + L.off_tail, d_out_div_partials_or_null,
+                               ws + L.off_div, vb_psis_div_workspace_bytes(), stream);
+    else
+        rc = vb_psis_write(d_lw_in, d_lw_out, n, 0, M_ptr, C1, K1, ws + L.off_tail, stream);
+    if (rc != VB_OK || !h_out) return rc;
+    double* pack = (double*)(ws + L.off_pack);
+    if (d_out_div_partials_or_null) {
+        rc = vb_bounds_divergence_merge(d_out_div_partials_or_null, 1, 2.0, pack + 8, stream);
+        if (rc != VB_OK) return rc;
+    }
+    smooth_pack_kernel<<<1, 32, 0, st>>>(d_out_diag, nullptr, pack);
+    VB_LAUNCH_CHECK();
+    VB_CUDA_TRY(cudaMemcpyAsync(h_out, pack, 17 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    VB_CUDA_TRY(cudaStreamSynchronize(st));
+    h_out[16] = 1.0; h_out[17] = 0.0;
+    if (!d_out_div_partials_or_null) for (int i = 8; i < 16; ++i) h_out[i] = 0.0;
+    return VB_OK;
 }
 
 // ------------------------------------------------------------------------------------------ standalone ops

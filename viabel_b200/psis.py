@@ -23,11 +23,17 @@ class _DivCache:
     ref = None
     key = None
     partials = None
+    host = None          # the merged statistics as host numbers (single-GPU call: they came back with k-hat)
 
     @classmethod
-    def store(cls, t, partials, world):
+    def store(cls, t, partials, world, host=None):
         import weakref
         cls.ref, cls.key, cls.partials = weakref.ref(t), (t.data_ptr(), t.numel(), t._version, world), partials
+        cls.host = host
+
+    @classmethod
+    def lookup_host(cls, t, world):
+        return cls.host if cls.lookup(t, world) is not None else None
 
     @classmethod
     def lookup(cls, t, world):
@@ -50,11 +56,14 @@ def _smooth_1d(col, Reff, want_tail=False, src=None):
         tail = torch.full((cap,), -1, dtype=torch.int64, device=col.device)
     ws = WS.get('psis', _lib.lib.vb_psis_smooth_workspace_bytes(n, float(Reff)))
     part = torch.empty(6, dtype=torch.float64, device=col.device) if src is not None else None
-    _lib.check(_lib.lib.vb_psis_smooth_div(ptr(col), ptr(out), n, float(Reff), ptr(diag), ptr(tail), ptr(part), ptr(ws),
-                                           ws.numel(), stream_ptr()), 'vb_psis_smooth_div')
+    # k-hat, the other diagnostics and the alpha = 2 divergence statistics come back to the host in the call's one
+    # synchronisation (no further device read here or in all_bounds)
+    host = np.empty(18)
+    _lib.check(_lib.lib.vb_psis_smooth_host(ptr(col), ptr(out), n, float(Reff), ptr(diag), ptr(tail), ptr(part),
+                                            host.ctypes.data, ptr(ws), ws.numel(), stream_ptr()), 'vb_psis_smooth_host')
     if src is not None:
-        _DivCache.store(src, part, 1)
-    return out, diag.cpu().numpy(), tail
+        _DivCache.store(src, part, 1, host=host[8:16].copy())
+    return out, host[:8].copy(), tail
 
 
 def _smooth_columns(cols, Reff, want_loo=False):
