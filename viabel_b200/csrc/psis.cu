@@ -165,9 +165,10 @@ __global__ void pivot_kernel(const Cand* __restrict__ sorted_sample, long long c
 __global__ void __launch_bounds__(1024)
 radix_select_kernel(const Cand* __restrict__ sample, int count, int rank, double* __restrict__ out_pivot_x) {
     __shared__ unsigned int hist[256];
+    __shared__ unsigned int wtot[8];
     __shared__ unsigned long long s_prefix;
     __shared__ int s_rank;
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) { s_prefix = 0ull; s_rank = rank; }
     unsigned long long mask = 0ull;
     for (int shift = 56; shift >= 0; shift -= 8) {
@@ -180,10 +181,24 @@ radix_select_kernel(const Cand* __restrict__ sample, int count, int rank, double
             if ((k & mask) == prefix) atomicAdd(&hist[(unsigned)(k >> shift) & 255u], 1u);
         }
         __syncthreads();
+        // above[d] = number of keys with a larger digit: suffix sums by warp shuffles (a serial walk over up to 255
+        // counters per thread made this kernel 18 us)
+        unsigned int h = 0, v = 0;
         if (tid < 256) {
-            unsigned int above = 0;
-            for (int d = tid + 1; d < 256; ++d) above += hist[d];
-            if ((int)above <= r && r < (int)(above + hist[tid])) {       // exactly one digit owns rank r
+            h = hist[tid];
+            v = h;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned int t = __shfl_down_sync(0xffffffffu, v, o);
+                if (lane + o < 32) v += t;
+            }
+            if (lane == 0) wtot[warp] = v;
+        }
+        __syncthreads();
+        if (tid < 256) {
+            unsigned int above = v - h;
+            for (int w = warp + 1; w < 8; ++w) above += wtot[w];
+            if ((int)above <= r && r < (int)(above + h)) {               // exactly one digit owns rank r
                 s_prefix = prefix | ((unsigned long long)tid << shift);
                 s_rank = r - (int)above;
             }
@@ -663,39 +678,53 @@ gpd_profile_kernel(const double* __restrict__ x, const long long* __restrict__ c
     s = block_sum(s, scratch);
     if (threadIdx.x == 0) parts[j * kGpdSplit + blockIdx.y] = s;
 }
-// single CTA: profile log-likelihood L_j = n (log(-(b_j/ks_j)) - ks_j - 1), quadrature weights
-// w_j = 1 / sum_i exp(L_i - L_j) (one warp per j), posterior mean of b (psis.py:287-308)
-__global__ void __launch_bounds__(1024)
-gpd_weights_kernel(const double* __restrict__ x, const long long* __restrict__ counts, const double* __restrict__ parts,
-                   double* __restrict__ bs, double* __restrict__ L, double* __restrict__ w_scratch,
-                   double* __restrict__ state) {
-    __shared__ double scratch[32];
+// profile log-likelihood L_j = n (log(-(b_j/ks_j)) - ks_j - 1) (psis.py:287-289)
+__global__ void __launch_bounds__(256)
+gpd_loglik_kernel(const double* __restrict__ x, const long long* __restrict__ counts, const double* __restrict__ parts,
+                  double* __restrict__ bs, double* __restrict__ L) {
     const long long n = counts[0], m = counts[2];
     if (counts[3] == 0) return;
+    const long long j = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (j >= m) return;
     const double x_q = x[(long long)((double)n / 4.0 + 0.5) - 1];
     const double x_max = x[n - 1];
-    for (long long j = threadIdx.x; j < m; j += blockDim.x) {
-        double s = 0.0;
-        for (int k = 0; k < kGpdSplit; ++k) s += parts[j * kGpdSplit + k];      // fixed order
-        const double ks = s / (double)n;
-        const double b = gpd_b(j, m, x_q, x_max);
-        bs[j] = b;
-        L[j] = (double)n * (log(-(b / ks)) - ks - 1.0);
-    }
-    __syncthreads();
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
-    for (long long j = warp; j < m; j += nw) {
+    double s = 0.0;
+    for (int k = 0; k < kGpdSplit; ++k) s += parts[j * kGpdSplit + k];          // fixed order
+    const double ks = s / (double)n;
+    const double b = gpd_b(j, m, x_q, x_max);
+    bs[j] = b;
+    L[j] = (double)n * (log(-(b / ks)) - ks - 1.0);
+}
+// quadrature weights w_j = 1 / sum_i exp(L_i - L_j), one WARP per j over a grid of CTAs (as one CTA this was a chain of
+// ~50 dependent fp64 exponentials per lane, 26 us at m = 213); the CTA that finishes last (ticket) takes the posterior
+// mean of b in fixed order (psis.py:293-308)
+constexpr int kGpdWWarps = 8;
+__global__ void __launch_bounds__(kGpdWWarps * 32)
+gpd_weights_kernel(const long long* __restrict__ counts, const double* __restrict__ bs, const double* __restrict__ L,
+                   double* __restrict__ w_out, double* __restrict__ state, unsigned int* __restrict__ ticket) {
+    __shared__ double scratch[32];
+    __shared__ bool s_last;
+    const long long m = counts[2];
+    if (counts[3] == 0) return;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long long j = blockIdx.x * (long long)kGpdWWarps + warp;
+    if (j < m) {
         double s = 0.0;
         const double Lj = L[j];
         for (long long i = lane; i < m; i += 32) s += exp(L[i] - Lj);
         s = warp_sum(s);
-        if (lane == 0) w_scratch[j] = 1.0 / s;
+        if (lane == 0) w_out[j] = 1.0 / s;
     }
+    __threadfence();
     __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
     double sw = 0.0, sbw = 0.0;
-    for (long long j = threadIdx.x; j < m; j += blockDim.x) {
-        const double w = w_scratch[j];
-        if (w >= 10.0 * DBL_EPSILON) { sw += w; sbw += bs[j] * w; }      // psis.py:300-305
+    for (long long i = threadIdx.x; i < m; i += blockDim.x) {
+        const double w = __ldcg(w_out + i);
+        if (w >= 10.0 * DBL_EPSILON) { sw += w; sbw += bs[i] * w; }      // psis.py:300-305
     }
     sw = block_sum(sw, scratch);
     sbw = block_sum(sbw, scratch);
@@ -965,7 +994,12 @@ static int run_gpd_fit(const double* x2, const long long* counts, long long n2_u
     double* parts = Lq + m_max;                     // the L region holds L[m_max] then parts[m_max][kGpdSplit]
     gpd_profile_kernel<<<dim3((unsigned)m_max, kGpdSplit), 256, 0, st>>>(x2, counts, parts);
     VB_LAUNCH_CHECK();
-    gpd_weights_kernel<<<1, 1024, 0, st>>>(x2, counts, parts, bs, Lq, wq, state);
+    gpd_loglik_kernel<<<(unsigned)((m_max + 255) / 256), 256, 0, st>>>(x2, counts, parts, bs, Lq);
+    VB_LAUNCH_CHECK();
+    unsigned int* ticket = (unsigned int*)blk;      // blk is written by gpd_k_blocks_kernel only after this
+    VB_CUDA_TRY(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), st));
+    gpd_weights_kernel<<<(unsigned)((m_max + kGpdWWarps - 1) / kGpdWWarps), kGpdWWarps * 32, 0, st>>>(counts, bs, Lq, wq, state,
+                                                                                                    ticket);
     VB_LAUNCH_CHECK();
     gpd_k_blocks_kernel<<<g_small, 256, 0, st>>>(x2, counts, state, blk);
     VB_LAUNCH_CHECK();
