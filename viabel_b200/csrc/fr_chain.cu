@@ -281,20 +281,203 @@ __device__ __noinline__ double chain_gemm_impl(GemmSmem& sm, unsigned int& ring,
     return s;
 }
 
+// The same product when the RESULT is symmetric (X'X, A A, products of commuting symmetric matrices, A Y A): only the
+// 32 x 32 blocks on and below the diagonal are computed (nb (nb + 1) / 2 tiles: 136 at d = 512, one wave) and each
+// off-diagonal block is also stored transposed.  E, if given, must be symmetric too (it is read at the lower position).
+// Where symmetry holds only mathematically (M X with X a polynomial in M, A Y A) the mirror replaces an O(eps) rounding
+// asymmetry.  Same ring, barriers and fragment scheme as above with 16 x 16 warp tiles.
+constexpr int kCSym = 32;                  // block size of the symmetric variant (kCSym == kCK: all slab pitches are 36)
+static_assert(kCSym == kCK && kCSym == kCN, "symmetric tiles reuse the B-slab geometry");
+template <int VEC, bool ta, bool tb>
+__device__ __noinline__ double chain_gemm_sym_impl(GemmSmem& sm, unsigned int& ring, int d, const double* __restrict__ A,
+                                                   const double* __restrict__ B, double alpha, double beta,
+                                                   const double* E, double gamma, double* __restrict__ C, int norm_mode) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nb = (d + kCSym - 1) / kCSym;
+    const int ntiles = nb * (nb + 1) / 2;
+    const int nslab = (d + kCK - 1) / kCK;
+    constexpr int P = kCSym + 4;
+    auto tile_of = [&](int t, int& bi, int& bj) {        // row-major lower triangle: t -> (bi, bj <= bi)
+        bi = (int)((sqrtf(8.0f * (float)t + 1.0f) - 1.0f) * 0.5f);
+        while (bi * (bi + 1) / 2 > t) --bi;
+        while ((bi + 1) * (bi + 2) / 2 <= t) ++bi;
+        bj = t - bi * (bi + 1) / 2;
+    };
+    double nrm = 0.0;
+    if (tid >= kCConsumers) {
+        const int ptid = tid - kCConsumers;
+        for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+            int bi, bj;
+            tile_of(t, bi, bj);
+            const int i0 = bi * kCSym, j0 = bj * kCSym;
+            for (int slab = 0; slab < nslab; ++slab, ++ring) {
+                const int st = ring % kCStages;
+                mbar_wait(reinterpret_cast<uint64_t*>(&sm.empty[st]), ((ring / kCStages) & 1) ^ 1);
+                const int k0 = slab * kCK;
+                double* as = reinterpret_cast<double*>(sm.stage[st]);
+                double* bs = reinterpret_cast<double*>(sm.stage[st] + kCABytes);
+                constexpr int kChunks = kCSym * kCK / VEC;
+#pragma unroll
+                for (int c = ptid; c < kChunks; c += kCProducers) {
+                    const int row = c / (kCSym / VEC), col = (c % (kCSym / VEC)) * VEC;
+                    {   // A: rows (m, k..) or (k, m..)
+                        const int gr = (ta ? k0 : i0) + row, gc = (ta ? i0 : k0) + col;
+                        const bool ok = gr < d && gc < d;
+                        cp_async<VEC * 8>(as + row * P + col, ok ? A + (size_t)gr * d + gc : A, ok);
+                    }
+                    {   // B: rows (k, n..) or (n, k..)
+                        const int gr = (tb ? j0 : k0) + row, gc = (tb ? k0 : j0) + col;
+                        const bool ok = gr < d && gc < d;
+                        cp_async<VEC * 8>(bs + row * P + col, ok ? B + (size_t)gr * d + gc : B, ok);
+                    }
+                }
+                cp_async_arrive(&sm.full[st]);
+            }
+        }
+    } else {
+        const int grp = warp >> 2;
+        const int wm = (warp & 1) * 16, wn = ((warp >> 1) & 1) * 16;
+        constexpr int sa_m = ta ? 1 : P, sa_k = ta ? P : 1;
+        constexpr int sb_k = tb ? 1 : P, sb_n = tb ? P : 1;
+        const int a_off = (wm + (lane >> 2)) * sa_m + (lane & 3) * sa_k;
+        const int b_off = (lane & 3) * sb_k + (wn + (lane >> 2)) * sb_n;
+        for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+            int bi, bj;
+            tile_of(t, bi, bj);
+            const int i0 = bi * kCSym, j0 = bj * kCSym;
+            double acc[2][2][2];
+#pragma unroll
+            for (int a = 0; a < 2; ++a)
+#pragma unroll
+                for (int b = 0; b < 2; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+            for (int slab = 0; slab < nslab; ++slab, ++ring) {
+                const int st = ring % kCStages;
+                mbar_wait(reinterpret_cast<uint64_t*>(&sm.full[st]), (ring / kCStages) & 1);
+                const double* as = reinterpret_cast<const double*>(sm.stage[st]) + a_off;
+                const double* bs = reinterpret_cast<const double*>(sm.stage[st] + kCABytes) + b_off;
+#pragma unroll
+                for (int kk = grp * 4; kk < kCK; kk += 4 * kCGroups) {
+                    double af[2], bf[2];
+#pragma unroll
+                    for (int a = 0; a < 2; ++a) af[a] = as[kk * sa_k + a * 8 * sa_m];
+#pragma unroll
+                    for (int b = 0; b < 2; ++b) bf[b] = bs[kk * sb_k + b * 8 * sb_n];
+#pragma unroll
+                    for (int a = 0; a < 2; ++a)
+#pragma unroll
+                        for (int b = 0; b < 2; ++b) dmma(acc[a][b], af[a], bf[b]);
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(reinterpret_cast<uint64_t*>(&sm.empty[st]));
+            }
+            {
+                const int t128 = tid & 127;
+                if (grp != 0) {
+#pragma unroll
+                    for (int a = 0; a < 2; ++a)
+#pragma unroll
+                        for (int b = 0; b < 2; ++b)
+#pragma unroll
+                            for (int c = 0; c < 2; ++c)
+                                sm.xch[((grp - 1) * 8 + (a * 2 + b) * 2 + c) * 128 + t128] = acc[a][b][c];
+                }
+                consumer_sync();
+                if (grp == 0) {
+#pragma unroll
+                    for (int g = 0; g < kCGroups - 1; ++g)
+#pragma unroll
+                        for (int a = 0; a < 2; ++a)
+#pragma unroll
+                            for (int b = 0; b < 2; ++b)
+#pragma unroll
+                                for (int c = 0; c < 2; ++c) acc[a][b][c] += sm.xch[(g * 8 + (a * 2 + b) * 2 + c) * 128 + t128];
+                }
+                consumer_sync();
+            }
+            if (grp == 0) {
+                const bool offdiag = bi != bj;
+                double ev[2][2][2];
+                const bool use_e = beta != 0.0;
+#pragma unroll
+                for (int a = 0; a < 2; ++a)
+#pragma unroll
+                    for (int b = 0; b < 2; ++b) {
+                        const int gi = i0 + wm + a * 8 + (lane >> 2), gj = j0 + wn + b * 8 + 2 * (lane & 3);
+                        ev[a][b][0] = ev[a][b][1] = 0.0;
+                        if (use_e && gi < d) {
+                            if (VEC == 2) {
+                                if (gj < d) {
+                                    const double2 q = *reinterpret_cast<const double2*>(E + (size_t)gi * d + gj);
+                                    ev[a][b][0] = q.x; ev[a][b][1] = q.y;
+                                }
+                            } else {
+                                if (gj < d) ev[a][b][0] = E[(size_t)gi * d + gj];
+                                if (gj + 1 < d) ev[a][b][1] = E[(size_t)gi * d + gj + 1];
+                            }
+                        }
+                    }
+#pragma unroll
+                for (int a = 0; a < 2; ++a)
+#pragma unroll
+                    for (int b = 0; b < 2; ++b) {
+                        const int gi = i0 + wm + a * 8 + (lane >> 2), gj = j0 + wn + b * 8 + 2 * (lane & 3);
+                        double v[2];
+#pragma unroll
+                        for (int c = 0; c < 2; ++c) {
+                            v[c] = fma(beta, ev[a][b][c], alpha * acc[a][b][c]);
+                            if (gi == gj + c) v[c] += gamma;
+                            if (norm_mode && gi < d && gj + c < d) {
+                                const double r = (norm_mode == 1 && gi == gj + c) ? v[c] - 1.0 : v[c];
+                                nrm = fma(offdiag ? 2.0 * r : r, r, nrm);
+                            }
+                        }
+                        if (gi < d) {
+                            if (VEC == 2) {
+                                if (gj < d) *reinterpret_cast<double2*>(C + (size_t)gi * d + gj) = make_double2(v[0], v[1]);
+                            } else {
+                                if (gj < d) C[(size_t)gi * d + gj] = v[0];
+                                if (gj + 1 < d) C[(size_t)gi * d + gj + 1] = v[1];
+                            }
+                            if (offdiag) {
+                                if (gj < d) C[(size_t)gj * d + gi] = v[0];
+                                if (gj + 1 < d) C[(size_t)(gj + 1) * d + gi] = v[1];
+                            }
+                        }
+                    }
+            }
+        }
+    }
+    if (!norm_mode) return 0.0;
+    nrm = warp_sum(nrm);
+    __syncthreads();
+    if (lane == 0) sm.red[warp] = nrm;
+    __syncthreads();
+    double s = 0.0;
+#pragma unroll
+    for (int w = 0; w < kCT / 32; ++w) s += sm.red[w];
+    return s;
+}
+
 template <int VEC>
 __device__ __forceinline__ double chain_gemm_v(GemmSmem& sm, unsigned int& ring, int d, bool ta, const double* __restrict__ A,
                                                bool tb, const double* __restrict__ B, double alpha, double beta,
-                                               const double* E, double gamma, double* __restrict__ C, int norm_mode) {
+                                               const double* E, double gamma, double* __restrict__ C, int norm_mode, bool sym) {
+    if (sym) {
+        if (!ta && !tb) return chain_gemm_sym_impl<VEC, false, false>(sm, ring, d, A, B, alpha, beta, E, gamma, C, norm_mode);
+        if (ta && !tb) return chain_gemm_sym_impl<VEC, true, false>(sm, ring, d, A, B, alpha, beta, E, gamma, C, norm_mode);
+    }
     if (!ta && !tb) return chain_gemm_impl<VEC, false, false>(sm, ring, d, A, B, alpha, beta, E, gamma, C, norm_mode);
     if (ta && !tb) return chain_gemm_impl<VEC, true, false>(sm, ring, d, A, B, alpha, beta, E, gamma, C, norm_mode);
     if (!ta && tb) return chain_gemm_impl<VEC, false, true>(sm, ring, d, A, B, alpha, beta, E, gamma, C, norm_mode);
     return chain_gemm_impl<VEC, true, true>(sm, ring, d, A, B, alpha, beta, E, gamma, C, norm_mode);
 }
+// sym: the caller asserts that the result is symmetric (see chain_gemm_sym_impl)
 __device__ __forceinline__ double chain_gemm(GemmSmem& sm, unsigned int& ring, int d, bool ta, const double* __restrict__ A,
                                              bool tb, const double* __restrict__ B, double alpha, double beta,
-                                             const double* E, double gamma, double* __restrict__ C, int norm_mode) {
-    if ((d & 1) == 0) return chain_gemm_v<2>(sm, ring, d, ta, A, tb, B, alpha, beta, E, gamma, C, norm_mode);
-    return chain_gemm_v<1>(sm, ring, d, ta, A, tb, B, alpha, beta, E, gamma, C, norm_mode);
+                                             const double* E, double gamma, double* __restrict__ C, int norm_mode,
+                                             bool sym = false) {
+    if ((d & 1) == 0) return chain_gemm_v<2>(sm, ring, d, ta, A, tb, B, alpha, beta, E, gamma, C, norm_mode, sym);
+    return chain_gemm_v<1>(sm, ring, d, ta, A, tb, B, alpha, beta, E, gamma, C, norm_mode, sym);
 }
 
 // sum of the per-CTA partials in fixed order (every thread of every CTA gets the same value)
@@ -396,7 +579,7 @@ fr_chain_forward_kernel(const FwdArgs a) {
     bool finishing = false;
     for (int it = 0; it < 80; ++it) {
         double* p = next_slot();
-        const double part = chain_gemm(sm, ring, d, true, X, false, X, 1.0, 0.0, nullptr, 0.0, a.ws.T0, it == 0 ? 2 : 1);   // A = X'X
+        const double part = chain_gemm(sm, ring, d, true, X, false, X, 1.0, 0.0, nullptr, 0.0, a.ws.T0, it == 0 ? 2 : 1, true);   // A = X'X
         ++ng;
         if (threadIdx.x == 0) p[blockIdx.x] = part;
         grid_barrier(a.ws.barrier, phase);
@@ -416,7 +599,7 @@ fr_chain_forward_kernel(const FwdArgs a) {
             const double* q = kPolarSched[it < 6 ? it : 1 + (it - 6) % 5];
             const double i2 = 1.0 / (ps * ps);
             // B = c A^2 + b A, X <- a X + X B with the pending scale folded into the coefficients
-            chain_gemm(sm, ring, d, false, a.ws.T0, false, a.ws.T0, q[2] * i2 * i2, q[1] * i2, a.ws.T0, 0.0, a.ws.T1, 0);
+            chain_gemm(sm, ring, d, false, a.ws.T0, false, a.ws.T0, q[2] * i2 * i2, q[1] * i2, a.ws.T0, 0.0, a.ws.T1, 0, true);
             grid_barrier(a.ws.barrier, phase);
             chain_gemm(sm, ring, d, false, X, false, a.ws.T1, 1.0 / ps, q[0] / ps, X, 0.0, Xn, 0);
             ng += 2;
@@ -489,19 +672,22 @@ fr_chain_backward_kernel(const BwdArgs a) {
             const int r = (int)(e / d), c = (int)(e - (long long)r * d);
             Mx[e] = a.S[e] + (r == c ? mu : 0.0);
             X[e] = (r == c) ? x0 : 0.0;
+            // only Y + Y' is used below and the equation is linear: solve for the symmetric part of G, then every
+            // product of the doubling except A Y is symmetric
+            a.ws.T2[e] = 0.5 * (a.GS[e] + a.GS[(size_t)c * d + r]);
         }
         grid_barrier(a.ws.barrier, phase);
         const double tol2 = 16.0 * (double)d * 1e-28;
         status = 2;
         for (int it = 0; it < 60; ++it) {
             double* p = next_slot();
-            const double part = chain_gemm(sm, ring, d, false, Mx, false, X, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 1);   // R = M X
+            const double part = chain_gemm(sm, ring, d, false, Mx, false, X, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 1, true);   // R = M X
             ++ng;
             if (threadIdx.x == 0) p[blockIdx.x] = part;
             grid_barrier(a.ws.barrier, phase);
             const double err2 = sum_partials(p);
             if (err2 < tol2) { status = 0; break; }
-            chain_gemm(sm, ring, d, false, X, false, a.ws.T0, -1.0, 2.0, X, 0.0, Xn, 0);                           // 2 X - X R
+            chain_gemm(sm, ring, d, false, X, false, a.ws.T0, -1.0, 2.0, X, 0.0, Xn, 0, true);                     // 2 X - X R
             ++ng;
             grid_barrier(a.ws.barrier, phase);
             double* t = X; X = Xn; Xn = t;
@@ -513,13 +699,13 @@ fr_chain_backward_kernel(const BwdArgs a) {
         double* Aq2 = a.ws.T3;           // M is no longer needed after A0
         double* Y = a.ws.T2;
         double* Yn = Xn;                 // the spare inverse buffer
-        chain_gemm(sm, ring, d, false, X, false, a.GS, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 0);                        // T = M^-1 G
+        chain_gemm(sm, ring, d, false, X, false, a.ws.T2, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 0);                     // T = M^-1 sym(G)
         grid_barrier(a.ws.barrier, phase);
-        chain_gemm(sm, ring, d, false, a.ws.T0, false, X, 2.0 * mu, 0.0, nullptr, 0.0, Y, 0);                      // Y0
+        chain_gemm(sm, ring, d, false, a.ws.T0, false, X, 2.0 * mu, 0.0, nullptr, 0.0, Y, 0, true);                // Y0
         ng += 3;
         {
             double* p = next_slot();
-            const double part = chain_gemm(sm, ring, d, false, a.S, false, X, 1.0, -mu, X, 0.0, Aq, 2);            // A0, |A0|_F^2
+            const double part = chain_gemm(sm, ring, d, false, a.S, false, X, 1.0, -mu, X, 0.0, Aq, 2, true);      // A0, |A0|_F^2
             if (threadIdx.x == 0) p[blockIdx.x] = part;
             grid_barrier(a.ws.barrier, phase);
             double na2 = sum_partials(p);
@@ -528,10 +714,10 @@ fr_chain_backward_kernel(const BwdArgs a) {
             for (int it = 0; it < 60 && na2 > 1e-17; ++it) {
                 chain_gemm(sm, ring, d, false, Aq, false, Y, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 0);                  // T = A Y
                 double* p2 = next_slot();
-                const double part2 = chain_gemm(sm, ring, d, false, Aq, false, Aq, 1.0, 0.0, nullptr, 0.0, Aq2, 2);   // A^2 (independent)
+                const double part2 = chain_gemm(sm, ring, d, false, Aq, false, Aq, 1.0, 0.0, nullptr, 0.0, Aq2, 2, true);   // A^2 (independent)
                 if (threadIdx.x == 0) p2[blockIdx.x] = part2;
                 grid_barrier(a.ws.barrier, phase);
-                chain_gemm(sm, ring, d, false, a.ws.T0, false, Aq, 1.0, 1.0, Y, 0.0, Yn, 0);                       // Y + T A
+                chain_gemm(sm, ring, d, false, a.ws.T0, false, Aq, 1.0, 1.0, Y, 0.0, Yn, 0, true);                 // Y + T A
                 grid_barrier(a.ws.barrier, phase);
                 na2 = sum_partials(p2);
                 double* t = Aq; Aq = Aq2; Aq2 = t;
@@ -541,13 +727,8 @@ fr_chain_backward_kernel(const BwdArgs a) {
             }
             if (na2 > 1e-17 && status == 0) status = 3;
         }
-        // ---- G_L = (Y + Y') L
-        for (long long e = gtid; e < dd; e += gth) {
-            const int r = (int)(e / d), c = (int)(e - (long long)r * d);
-            Yn[e] = Y[e] + Y[(size_t)c * d + r];
-        }
-        grid_barrier(a.ws.barrier, phase);
-        chain_gemm(sm, ring, d, false, Yn, false, a.L, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 0);
+        // ---- G_L = (Y + Y') L = 2 Y L
+        chain_gemm(sm, ring, d, false, Y, false, a.L, 2.0, 0.0, nullptr, 0.0, a.ws.T0, 0);      // Y is symmetric: Y + Y' = 2 Y
         ++ng;
         grid_barrier(a.ws.barrier, phase);
         GL = a.ws.T0;
@@ -595,7 +776,9 @@ static cudaError_t chain_configure() {
     return e;
 }
 static int chain_grid(int d) {
-    const int tiles = ((d + kCM - 1) / kCM) * ((d + kCN - 1) / kCN);
+    int tiles = ((d + kCM - 1) / kCM) * ((d + kCN - 1) / kCN);
+    const int nb = (d + kCSym - 1) / kCSym;
+    if (nb * (nb + 1) / 2 > tiles) tiles = nb * (nb + 1) / 2;     // the symmetric products' tile count
     int g = device_sm_count();
     if (g > kCMaxGrid) g = kCMaxGrid;
     if (tiles < g) g = tiles < 8 ? 8 : tiles;              // a few CTAs even for tiny d (elementwise phases)

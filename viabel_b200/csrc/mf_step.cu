@@ -18,6 +18,13 @@ namespace vb {
 
 constexpr int kMfThreads = 256;
 constexpr int kMfStages = 3;
+#ifndef VB_MF_CTAS_STREAM
+#define VB_MF_CTAS_STREAM 2
+#endif
+#ifndef VB_MF_CTAS_PHILOX
+#define VB_MF_CTAS_PHILOX 2
+#endif
+constexpr int kMfMinCtasStream = VB_MF_CTAS_STREAM, kMfMinCtasPhilox = VB_MF_CTAS_PHILOX;
 constexpr long long kMfSingleCtaMax = 2048;   // samples: at most 8 tiles on one CTA
 
 // Philox stream record kept in device memory by the device-resident optimiser loop: every launch of an
@@ -204,7 +211,7 @@ __device__ __forceinline__ double mf_merge_component(const double* parts, int R,
 }
 
 template <typename T, int FAM, class Model, int OBJ, bool PHILOX>
-__global__ void __launch_bounds__(kMfThreads, 2)
+__global__ void __launch_bounds__(kMfThreads, PHILOX ? kMfMinCtasPhilox : kMfMinCtasStream)
 mf_step_kernel(const __grid_constant__ MfArgs<Model> a) {
     constexpr int D = Model::D;
     constexpr int NP = 2 * D + 4;
