@@ -759,21 +759,33 @@ class C3(Workload):
 
     def roofline(self, ms_kernel, hbm_gbs, bf16_tflops):
         info = self.fam.impl.chain_info()       # [polar, inverse, smith iterations, status, forward GEMMs, backward GEMMs]
-        gemms = info[4] + info[5]               # counted by the kernels themselves
-        flops = gemms * 2.0 * self.d ** 3
+        gemms, sym = info[4] + info[5], info[6] + info[7]      # counted by the kernels themselves
+        nb = (self.d + 31) // 32
+        sym_frac = (nb * (nb + 1) / 2) / float(nb * nb)          # a symmetric product computes the lower-triangular blocks
+        flops = ((gemms - sym) + sym * sym_frac) * 2.0 * self.d ** 3
         ach = flops / (ms_kernel * 1e-3) / 1e12 if ms_kernel > 0 else 0.0
-        peak = 40.0
+        # fp64 MMA peak of THIS GPU, measured live by the library's own microbenchmark (DMMA.8x8x4 on register operands)
+        import ctypes
+        import torch
+        pk = ctypes.c_double(0.0)
+        nb = self.lib.lib.vb_measure_dmma_peak_workspace_bytes()
+        pws = torch.empty(nb, dtype=torch.uint8, device='cuda')
+        self.lib.check(self.lib.lib.vb_measure_dmma_peak(ctypes.byref(pk), pws.data_ptr(), nb, None), 'vb_measure_dmma_peak')
+        peak = pk.value
+        del pws
         return {'bound': 'tensor', 'achieved': ach, 'peak': peak, 'unit': 'TFLOP/s', 'frac': ach / peak, 'traffic': None,
-                'peak_kind': 'f64', 'peak_source': 'nominal B200 fp64 tensor rate (40 TFLOP/s); MEASURED_PEAKS.json has no fp64 figure',
+                'peak_kind': 'f64', 'peak_source': 'measured live: vb_measure_dmma_peak (back-to-back DMMA.8x8x4, all SMs, '
+                                                   'best of 4; nominal 40 TFLOP/s); MEASURED_PEAKS.json has no fp64 figure',
                 'kernel': 'fr_chain_forward_kernel + fr_chain_backward_kernel (O(d^3) chain: polar Newton-Schulz sqrtm, '
                           'squared-Smith Sylvester solve, packing; fp64 mma.sync m8n8k4)',
-                'ms_per_launch': ms_kernel, 'executed_gemms': gemms, 'iterations': info,
+                'ms_per_launch': ms_kernel, 'executed_gemms': gemms, 'symmetric_gemms': sym, 'iterations': info[:4],
                 'executed_flops_per_launch': flops,
                 'note': 'the chain pair is the dominant kernel of the step (see share_of_step); `achieved` counts the '
                         'EXECUTED fp64 GEMM flops (%d GEMMs of 512^3), not an algorithmic minimum: the iteration trades '
                         'flops for having no eigendecomposition (cuSOLVER syevd took 4.7 ms here).  The per-sample products '
                         '(z S, (x - mu_p) P_p, Z\' diag(w) G: 6 d^2 flop per sample) run on tcgen05 3xTF32 at 0.14 / 0.19 / '
-                        '0.14 ms per launch (profiles/r2k_launches_c3.txt)' % gemms}
+                        '0.14 ms per launch (profiles/r2u_launches_c3.txt); symmetric products (52 of 73 at C3) execute half of 2 d^3 and '
+                        'are counted as executed' % gemms}
 
     def config(self):
         return {'workload': self.config_name(), 'samples_per_step_per_gpu': self.n, 'scale': self.scale,

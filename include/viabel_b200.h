@@ -46,6 +46,11 @@ enum { VB_MODEL_FUNNEL = 0, VB_MODEL_MIXTURE = 1, VB_MODEL_EIGHT_SCHOOLS = 2,
 int vb_abi_version(void);
 int vb_compiled_sm(void);
 const char* vb_error_string(int status);
+/* Measured fp64 tensor-core peak of the current device in TFLOP/s (back-to-back DMMA.8x8x4 on register operands, every
+ * SM, best of 4 launches of ~2 ms): the roofline denominator bench.py quotes the full-rank chain kernels against.  No
+ * reference counterpart (measurement aid). */
+size_t vb_measure_dmma_peak_workspace_bytes(void);
+int vb_measure_dmma_peak(double* h_out_tflops, void* d_ws, size_t ws_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------
  * Model plugins: log p(x) and grad log p(x) on the unconstrained space.
@@ -307,8 +312,9 @@ int vb_gemm_tf32x3_split(int a_mn_major, int b_mn_major, long long m, long long 
  *                         an upper bound of sigma_max(L) that the backward's inverse iteration starts from, reserved)
  *   vb_fr_chain_backward  G_S = Ztilde' diag(w) G, g_mu = sum w g, rows = [max lw, sum w, sum log p, sum lw]
  *                         -> d_out[1 + P] = (value, gradient) of KLVI (objective 0), CHIVI (1), path-derivative KLVI (2)
- *   vb_fr_chain_info      h_out6 = [polar, inverse, Smith iterations, status (0 = every iteration met its tolerance),
- *                         GEMMs executed by the forward, by the backward] of the last calls on a workspace (synchronises)
+ *   vb_fr_chain_info      h_out8 = [polar, inverse, Smith iterations, status (0 = every iteration met its tolerance),
+ *                         GEMMs executed by the forward, by the backward, symmetric (half-work) GEMMs among them:
+ *                         forward, backward] of the last calls on a workspace (synchronises)
  * ---------------------------------------------------------------------------------- */
 size_t vb_fr_chain_workspace_bytes(int dim);
 int vb_fr_chain_forward(const double* d_var_param, int dim, int scale_mode, double* d_out_L, double* d_out_S,
@@ -317,7 +323,7 @@ int vb_fr_chain_backward(int dim, int scale_mode, int objective, double alpha, d
                          const double* d_L, const double* d_S, const double* d_GS, const double* d_gmu,
                          const double* d_rows, const double* d_scal, double* d_out, void* d_ws, size_t ws_bytes,
                          void* stream);
-int vb_fr_chain_info(const void* d_ws, int dim, int* h_out6, void* stream);
+int vb_fr_chain_info(const void* d_ws, int dim, int* h_out8, void* stream);
 
 /* ------------------------------------------------------------------------------------
  * Bounds (viabel/bounds.py).

@@ -22,6 +22,8 @@ SIGNATURES = {
     'vb_abi_version': (_i, []),
     'vb_compiled_sm': (_i, []),
     'vb_error_string': (C.c_char_p, [_i]),
+    'vb_measure_dmma_peak_workspace_bytes': (_sz, []),
+    'vb_measure_dmma_peak': (_i, [C.POINTER(_d), _p, _sz, _p]),
     'vb_model_create_funnel': (_i, [_d, C.POINTER(_p)]),
     'vb_model_create_mixture': (_i, [_d, C.POINTER(_p)]),
     'vb_model_create_eight_schools': (_i, [C.POINTER(_d), C.POINTER(_d), _i, C.POINTER(_p)]),

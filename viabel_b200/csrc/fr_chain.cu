@@ -500,7 +500,7 @@ struct ChainWs {
     double* parts;                              // [3][grid] norm partials (rotating: a slot is rewritten two barriers later)
     unsigned int* barrier;
     int* info;                                  // [0] polar iterations [1] inverse iterations [2] smith iterations [3] status
-                                                // [4] GEMMs executed by the forward [5] by the backward
+                                                // [4] GEMMs executed by the forward [5] by the backward [6], [7] symmetric ones among them
 };
 
 // ------------------------------------------------------------------------------------------ forward
@@ -562,7 +562,7 @@ fr_chain_forward_kernel(const FwdArgs a) {
             a.S[e] = v;
             if (a.S32) a.S32[e] = (float)v;
         }
-        if (gtid == 0) { a.ws.info[0] = 0; a.ws.info[3] = 0; a.ws.info[4] = 0; a.scal[2] = 0.0; }
+        if (gtid == 0) { a.ws.info[0] = 0; a.ws.info[3] = 0; a.ws.info[4] = 0; a.ws.info[6] = 0; a.scal[2] = 0.0; }
         return;
     }
     // ---- polar factor of L: X0 = L / |L|_F, then X0 / s with s^2 = |X0'X0|_F >= sigma_max(X0)^2 (Frobenius alone
@@ -573,14 +573,14 @@ fr_chain_forward_kernel(const FwdArgs a) {
     for (long long e = gtid; e < dd; e += gth) X[e] = a.L[e] * inv_f;
     grid_barrier(a.ws.barrier, phase);
     const double tol2 = 16.0 * (double)d * 1e-28;        // |X'X - I|_F < 4 sqrt(d) 1e-14
-    int its = 0, status = 1, ng = 0;
+    int its = 0, status = 1, ng = 0, nsym = 0;
     double ps = 1.0;                                     // pending scale: the iterate is X / ps, its Gram matrix T0 / ps^2
     double err2 = INFINITY;
     bool finishing = false;
     for (int it = 0; it < 80; ++it) {
         double* p = next_slot();
         const double part = chain_gemm(sm, ring, d, true, X, false, X, 1.0, 0.0, nullptr, 0.0, a.ws.T0, it == 0 ? 2 : 1, true);   // A = X'X
-        ++ng;
+        ++ng; ++nsym;
         if (threadIdx.x == 0) p[blockIdx.x] = part;
         grid_barrier(a.ws.barrier, phase);
         if (it == 0) {
@@ -602,7 +602,7 @@ fr_chain_forward_kernel(const FwdArgs a) {
             chain_gemm(sm, ring, d, false, a.ws.T0, false, a.ws.T0, q[2] * i2 * i2, q[1] * i2, a.ws.T0, 0.0, a.ws.T1, 0, true);
             grid_barrier(a.ws.barrier, phase);
             chain_gemm(sm, ring, d, false, X, false, a.ws.T1, 1.0 / ps, q[0] / ps, X, 0.0, Xn, 0);
-            ng += 2;
+            ng += 2; ++nsym;
         } else {
             chain_gemm(sm, ring, d, false, X, false, a.ws.T0, -0.5, 1.5, X, 0.0, Xn, 0);                          // 1.5 X - 0.5 X A
             ++ng;
@@ -623,7 +623,7 @@ fr_chain_forward_kernel(const FwdArgs a) {
         a.S[e] = v;
         if (a.S32) a.S32[e] = (float)v;
     }
-    if (gtid == 0) { a.ws.info[0] = its; a.ws.info[3] = status; a.ws.info[4] = ng; }
+    if (gtid == 0) { a.ws.info[0] = its; a.ws.info[3] = status; a.ws.info[4] = ng; a.ws.info[6] = nsym; }
 }
 
 // ------------------------------------------------------------------------------------------ backward
@@ -654,7 +654,7 @@ fr_chain_backward_kernel(const BwdArgs a) {
     auto next_slot = [&]() { double* p = parts + (size_t)slot * gridDim.x; slot = (slot + 1) % 3; return p; };
     const double* GL = nullptr;          // d f / d L as (d, d) row-major
     bool gl_transposed = false;
-    int inv_its = 0, smith_its = 0, status = 0, ng = 0;
+    int inv_its = 0, smith_its = 0, status = 0, ng = 0, nsym = 0;
     if (a.mode == 1) {
         GL = a.GS;                       // chol: G_L = G_S' (x = mu + L ztilde)
         gl_transposed = true;
@@ -682,13 +682,13 @@ fr_chain_backward_kernel(const BwdArgs a) {
         for (int it = 0; it < 60; ++it) {
             double* p = next_slot();
             const double part = chain_gemm(sm, ring, d, false, Mx, false, X, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 1, true);   // R = M X
-            ++ng;
+            ++ng; ++nsym;
             if (threadIdx.x == 0) p[blockIdx.x] = part;
             grid_barrier(a.ws.barrier, phase);
             const double err2 = sum_partials(p);
             if (err2 < tol2) { status = 0; break; }
             chain_gemm(sm, ring, d, false, X, false, a.ws.T0, -1.0, 2.0, X, 0.0, Xn, 0, true);                     // 2 X - X R
-            ++ng;
+            ++ng; ++nsym;
             grid_barrier(a.ws.barrier, phase);
             double* t = X; X = Xn; Xn = t;
             ++inv_its;
@@ -702,7 +702,7 @@ fr_chain_backward_kernel(const BwdArgs a) {
         chain_gemm(sm, ring, d, false, X, false, a.ws.T2, 1.0, 0.0, nullptr, 0.0, a.ws.T0, 0);                     // T = M^-1 sym(G)
         grid_barrier(a.ws.barrier, phase);
         chain_gemm(sm, ring, d, false, a.ws.T0, false, X, 2.0 * mu, 0.0, nullptr, 0.0, Y, 0, true);                // Y0
-        ng += 3;
+        ng += 3; nsym += 2;
         {
             double* p = next_slot();
             const double part = chain_gemm(sm, ring, d, false, a.S, false, X, 1.0, -mu, X, 0.0, Aq, 2, true);      // A0, |A0|_F^2
@@ -723,7 +723,7 @@ fr_chain_backward_kernel(const BwdArgs a) {
                 double* t = Aq; Aq = Aq2; Aq2 = t;
                 t = Y; Y = Yn; Yn = t;
                 ++smith_its;
-                ng += 3;
+                ng += 3; nsym += 2;
             }
             if (na2 > 1e-17 && status == 0) status = 3;
         }
@@ -745,7 +745,7 @@ fr_chain_backward_kernel(const BwdArgs a) {
         else if (a.objective == 0) v = -(entropy + a.rows[2] / nt);
         else v = -(a.rows[3] / nt);
         a.out[0] = v;
-        a.ws.info[1] = inv_its; a.ws.info[2] = smith_its; a.ws.info[5] = ng;
+        a.ws.info[1] = inv_its; a.ws.info[2] = smith_its; a.ws.info[5] = ng; a.ws.info[7] = nsym;
         if (status) a.ws.info[3] = status;
     }
     for (long long j = gtid; j < d; j += gth) a.out[1 + j] = gscale * a.gmu[j];
@@ -859,11 +859,11 @@ extern "C" int vb_fr_chain_backward(int dim, int scale_mode, int objective, doub
 }
 
 // iteration counts and status of the last forward / backward on this workspace:
-// [polar, inverse, smith, status, GEMMs of the forward, GEMMs of the backward]
-extern "C" int vb_fr_chain_info(const void* d_ws, int dim, int* h_out6, void* stream) {
-    if (!d_ws || !h_out6 || dim < 1) return VB_ERR_ARG;
+// [polar, inverse, smith, status, GEMMs of the forward, GEMMs of the backward, symmetric (half-work) ones among them: forward, backward]
+extern "C" int vb_fr_chain_info(const void* d_ws, int dim, int* h_out8, void* stream) {
+    if (!d_ws || !h_out8 || dim < 1) return VB_ERR_ARG;
     const ChainWs w = chain_ws(const_cast<void*>(d_ws), dim);
-    VB_CUDA_TRY(cudaMemcpyAsync(h_out6, w.info, 6 * sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    VB_CUDA_TRY(cudaMemcpyAsync(h_out8, w.info, 8 * sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     VB_CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
     return VB_OK;
 }

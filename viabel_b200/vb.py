@@ -238,9 +238,9 @@ class _FullRank(_FamilyImpl):
         return {'mu': vp[:d], 'L': L, 'S': S, 'S32': S32, 'scal': scal, 'kernel': True}
 
     def chain_info(self):
-        """[polar, inverse, smith iterations, status, forward GEMMs, backward GEMMs] of the last chain kernels
-        (synchronises)."""
-        out = (ctypes.c_int * 6)()
+        """[polar, inverse, smith iterations, status, forward GEMMs, backward GEMMs, symmetric GEMMs among them: forward,
+        backward] of the last chain kernels (synchronises)."""
+        out = (ctypes.c_int * 8)()
         ws = self.ws.get('chain', _lib.lib.vb_fr_chain_workspace_bytes(self.dim))
         _lib.check(_lib.lib.vb_fr_chain_info(ptr(ws), self.dim, out, stream_ptr()), 'vb_fr_chain_info')
         return list(out)
