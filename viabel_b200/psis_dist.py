@@ -273,7 +273,11 @@ def _sharded_dev(st, comm, lw_local, Reff, sizes, want_detail, src):
     sample_all = st.empty((cap_s, 2), torch.int64)
     sample_all[:world * SAMPLE] = comm.all_gather(mine).view(world * SAMPLE, 2)
     cap = min(n_local, max(1 << 21, n_local // 16))
-    frac = max(0.01, 4.0 * (K1 + 1) / n)
+    # First pivot: 8x the tail fraction, at least sample rank 10 of the world * 4096 sampled weights.  Fewer than K1 + 1
+    # true values above it needs >= rank sample hits where rank / 8 are expected (P < 1e-9); the status word catches it
+    # and the host-driven protocol redoes the call from its 1 % pivot.  At 8 x 1.25e8 weights this stages 13x fewer
+    # candidates per rank than the 1 % pivot.
+    frac = min(1.0, max(8.0 * (K1 + 1) / n, 10.0 / (world * SAMPLE)))
     st.pivot(sample_all, world * SAMPLE, frac, pivot)
     cand, count_t, body_max = st.filter(lw_local, index0, pivot, cap)
     M = body_max[1:2].clone()
