@@ -36,8 +36,8 @@ def _divergence_stats(log_weights, alpha, group=None):
     # statistics psislw's final pass already took over this very tensor (alpha = 2 only): no further pass
     from .psis import _DivCache
     cached = _DivCache.lookup(log_weights, world) if (alpha == 2.0 and isinstance(log_weights, torch.Tensor)) else None
-    if world == 1 and cached is not None and _DivCache.lookup_host(log_weights, world) is not None:
-        return _DivCache.lookup_host(log_weights, world).copy()
+    if cached is not None and _DivCache.lookup_host(log_weights, world) is not None:
+        return _DivCache.lookup_host(log_weights, world).copy()      # merged over the group by psislw already
     if world == 1 and cached is not None:
         _lib.check(_lib.lib.vb_bounds_divergence_merge(ptr(cached), 1, float(alpha), ptr(out), stream_ptr()),
                    'vb_bounds_divergence_merge')

@@ -152,6 +152,13 @@ class CudaStages:
                    'vb_psis_tail_dev')
         return diag, tail_idx, (ws, cap, K1)
 
+    def merge_div(self, gathered, world):
+        """(world, 6) divergence partials -> the 8 statistics of divergence_bound(alpha = 2) (device)."""
+        out = self.empty((8,), torch.float64)
+        _lib.check(_lib.lib.vb_bounds_divergence_merge(self._p(gathered), int(world), 2.0, self._p(out), self._stream()),
+                   'vb_bounds_divergence_merge')
+        return out
+
     def write(self, lw, index0, M, handle):
         """S6; also leaves this shard's divergence partials (alpha = 2, relative to the global maximum) in
         ``self.last_div``: taken in the same pass over the weights."""
@@ -182,10 +189,6 @@ class DistComm:
         out = torch.empty(self.world * flat.numel(), dtype=t.dtype, device=t.device)
         self.dist.all_gather_into_tensor(out, flat, group=self.group)
         return out.view((self.world,) + tuple(t.shape))
-
-    def all_reduce_sum(self, t):
-        self.dist.all_reduce(t, group=self.group)
-        return t
 
     def all_reduce_max(self, t):
         self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX, group=self.group)
@@ -290,12 +293,20 @@ def _sharded_dev(st, comm, lw_local, Reff, sizes, want_detail, src):
     all_cands, total_t, all_terms, status_t = st.gather_compact(recv, world, capx, sizes_t)
     diag, tail_idx, handle = st.tail_dev(all_cands, total_t, K1, M, pivot, all_terms, status_t, want_tail_idx=want_detail)
     out = st.write(lw_local, index0, M, handle)
-    d = diag.cpu().numpy()                                               # the one host read of the call
+    host_stats = None
+    if src is not None and getattr(st, 'last_div', None) is not None and hasattr(st, 'merge_div'):
+        # the caller's own tensor: all_bounds(lw) usually follows (experiments.py:69,159-166).  Its alpha = 2 statistics
+        # are merged here (one small all-gather) and come back with the diagnostics in the same host read
+        stats = st.merge_div(comm.all_gather(st.last_div), world)
+        both = torch.cat([diag, stats]).cpu().numpy()                    # the one host read of the call
+        d, host_stats = both[:8], both[8:16].copy()
+    else:
+        d = diag.cpu().numpy()                                           # the one host read of the call
     if d[7] < 0:
         return None
     if src is not None and getattr(st, 'last_div', None) is not None:
         from .psis import _DivCache
-        _DivCache.store(src, st.last_div, world)
+        _DivCache.store(src, st.last_div, world, host=host_stats)
     if not want_detail:
         return out, d[0]
     n2 = int(d[3])
