@@ -310,7 +310,9 @@ int vb_gemm_tf32x3_split(int a_mn_major, int b_mn_major, long long m, long long 
  *   vb_fr_chain_forward   var_param -> L (d, d), S (d, d) = sqrtm(L L') [scale_mode 0] or L' [1: x = mu + L ztilde],
  *                         optional fp32 copy of S, d_out_scal[4] = (sum of the log-diagonal = entropy, |L|_F^2,
  *                         an upper bound of sigma_max(L) that the backward's inverse iteration starts from, reserved)
- *   vb_fr_chain_backward  G_S = Ztilde' diag(w) G, g_mu = sum w g, rows = [max lw, sum w, sum log p, sum lw]
+ *   vb_fr_chain_backward  G_S = Ztilde' diag(w) G, g_mu = sum w g, rows = [max lw, sum w, sum log p, sum lw]; with
+ *                         n_total = 0 the global sample count is read from rows[4] on the device (sharded callers
+ *                         whose count travelled with the exchange of the sums)
  *                         -> d_out[1 + P] = (value, gradient) of KLVI (objective 0), CHIVI (1), path-derivative KLVI (2)
  *   vb_fr_chain_info      h_out8 = [polar, inverse, Smith iterations, status (0 = every iteration met its tolerance),
  *                         GEMMs executed by the forward, by the backward, symmetric (half-work) GEMMs among them:

@@ -239,7 +239,8 @@ def _fr_worker(rank, world, port, ret):
         wn = w_t.numpy()
         zt = impl.ztilde(mine)
         g_mu, G_S = wn @ g, zt.T @ (wn[:, None] * g)      # vb_fr_weighted with the rescaled weights
-        rows, g_mu_t, G_S_t = vb.fr_exchange_sums(rows, torch.from_numpy(g_mu), torch.from_numpy(G_S), world, None)
+        rows, g_mu_t, G_S_t = vb.fr_exchange_sums(rows, torch.from_numpy(g_mu), torch.from_numpy(G_S), world, None, count)
+        assert rows.numel() == 5 and float(rows[4]) == n        # the global sample count travels with the sums
         if rank == 0:
             ret['rows'], ret['g_mu'], ret['G_S'] = rows.numpy(), g_mu_t.numpy(), G_S_t.numpy()
             ret['lam'], ret['n'] = lam, n

@@ -634,7 +634,7 @@ struct BwdArgs {
     const double* S;           // (d, d)
     const double* GS;          // (d, d) G_S = Ztilde' diag(w) G
     const double* gmu;         // (d)    sum_i w_i g_i
-    const double* rows;        // [max lw, sum w, sum log p, sum lw]
+    const double* rows;        // [max lw, sum w, sum log p, sum lw] (+ [4] global sample count, read when n_total == 0)
     const double* scal;        // forward scalars: [0] entropy, [1] |L|_F^2
     double* out;               // (1 + P): value, gradient
     ChainWs ws;
@@ -734,7 +734,7 @@ fr_chain_backward_kernel(const BwdArgs a) {
         GL = a.ws.T0;
     }
     // ---- assemble (value, gradient): vb.py:240-243 (KLVI), :261-264 (CHIVI)
-    const double nt = a.n_total;
+    const double nt = a.n_total > 0.0 ? a.n_total : a.rows[4];      // 0: the global count travelled with the sums (rows[4])
     const double entropy = a.scal[0];
     const double sw = a.rows[1];
     const bool chivi = a.objective == 1;
@@ -843,7 +843,7 @@ extern "C" int vb_fr_chain_backward(int dim, int scale_mode, int objective, doub
                                     void* stream) {
     if (!d_L || !d_S || !d_GS || !d_gmu || !d_rows || !d_scal || !d_out || !d_ws || dim < 1) return VB_ERR_ARG;
     if (scale_mode != 0 && scale_mode != 1) return VB_ERR_ARG;
-    if (objective < 0 || objective > 2 || !(n_total > 0.0)) return VB_ERR_ARG;
+    if (objective < 0 || objective > 2 || !(n_total >= 0.0)) return VB_ERR_ARG;
     if (ws_bytes < vb_fr_chain_workspace_bytes(dim)) return VB_ERR_WORKSPACE;
     cudaStream_t st = (cudaStream_t)stream;
     BwdArgs a;

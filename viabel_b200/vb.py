@@ -408,15 +408,16 @@ def fr_exchange_max(rows, w, alpha, group):
     return w * scale, torch.stack([gm[0], rows[1] * scale, rows[2], rows[3]])
 
 
-def fr_exchange_sums(rows, g_mu, G_S, world, group):
-    """One all-gather of [sum w, sum log p, sum lw, g_mu (d), G_S (d*d)], summed in rank order (deterministic)."""
+def fr_exchange_sums(rows, g_mu, G_S, world, group, n_local=None):
+    """One all-gather of [sum w, sum log p, sum lw, local sample count, g_mu (d), G_S (d*d)], summed over the ranks in
+    one fixed-order reduction (every rank computes the same bits).  Returns rows (5,) = [max lw, sum w, sum log p,
+    sum lw, global sample count], g_mu, G_S.  The count rides along so that uneven external shards need no separate
+    collective and no host read."""
     d = g_mu.numel()
-    pack = torch.cat([rows[1:4], g_mu, G_S.reshape(-1)])
-    gathered = all_gather_rows(pack, world, group)
-    tot = gathered[0].clone()
-    for r in range(1, world):
-        tot += gathered[r]
-    return torch.cat([rows[0:1], tot[0:3]]), tot[3:3 + d].contiguous(), tot[3 + d:].reshape(d, d).contiguous()
+    cnt = torch.full((1,), float(n_local if n_local is not None else 0), dtype=torch.float64, device=rows.device)
+    pack = torch.cat([rows[1:4], cnt, g_mu, G_S.reshape(-1)])
+    tot = all_gather_rows(pack, world, group).sum(dim=0)
+    return torch.cat([rows[0:1], tot[0:4]]), tot[4:4 + d], tot[4 + d:].view(d, d)
 
 
 class _Objective:
@@ -505,14 +506,16 @@ class _Objective:
                                            ptr(grad), ptr(g_mu), ptr(G_S), ptr(ws2), ws2.numel(), stream_ptr()),
                    'vb_fr_weighted')
         if world > 1:
-            rows, g_mu, G_S = fr_exchange_sums(rows, g_mu, G_S, world, g)
+            rows, g_mu, G_S = fr_exchange_sums(rows, g_mu, G_S, world, g, n)
         self.last_log_weights = lw
         if ch.get('kernel'):
             # backward half of the chain + assembly of (value, gradient) in ONE cooperative launch
             out = torch.empty(1 + self.P, dtype=torch.float64, device=vp.device)
             cws = impl.ws.get('chain', _lib.lib.vb_fr_chain_workspace_bytes(d))
+            # n_total None: the global count is rows[4] on the device (0.0 tells the kernel to read it there)
             _lib.check(_lib.lib.vb_fr_chain_backward(d, 0 if impl.scale == 'sqrtm' else 1, self.obj, self.alpha,
-                                                     float(n_total), ptr(ch['L']), ptr(ch['S']), ptr(G_S), ptr(g_mu),
+                                                     0.0 if n_total is None else float(n_total), ptr(ch['L']),
+                                                     ptr(ch['S']), ptr(G_S.contiguous()), ptr(g_mu.contiguous()),
                                                      ptr(rows.contiguous()), ptr(ch['scal']), ptr(out), ptr(cws),
                                                      cws.numel(), stream_ptr()), 'vb_fr_chain_backward')
             return out
@@ -549,8 +552,11 @@ class _Objective:
             n_local = (base['eps'] if 'eps' in base else base['z']).shape[0]
             seed = off = index0 = 0
             n_total = n_local
-            if world > 1:
-                # external shards may be uneven: the global sample count is the sum of the local ones
+            if world > 1 and impl.kind == _lib.FAMILY_FR_T and not impl.use_eigh():
+                # external shards may be uneven: the global sample count is the sum of the local ones.  It travels
+                # with the step's one exchange of sums and stays on the device (no extra collective, no host read)
+                n_total = None
+            elif world > 1:
                 import torch.distributed as dist
                 cnt = torch.tensor([n_local], dtype=torch.int64, device=vp.device)
                 dist.all_reduce(cnt, group=g)
