@@ -308,8 +308,7 @@ mf_step_kernel(const __grid_constant__ MfArgs<Model> a) {
                             if (4 * q + k < D) eps[4 * q + k] = (T)z[k];
                     }
                 } else {
-#pragma unroll
-                    for (int j = 0; j < D; ++j) eps[j] = (T)draw_student_t(rng, gi, (uint32_t)j, (float)a.df);
+                    draw_student_t_row<D, T>(rng, gi, (float)a.df, eps);
                 }
             }
         } else if (bulk && full_tile) {
@@ -576,8 +575,7 @@ mf_samples_lw_kernel(const __grid_constant__ MfArgs<Model> a, T* __restrict__ ou
                         if (4 * q + k < D) eps[4 * q + k] = (T)z[k];
                 }
             } else {
-#pragma unroll
-                for (int j = 0; j < D; ++j) eps[j] = (T)draw_student_t(a.rng, gi, (uint32_t)j, (float)a.df);
+                draw_student_t_row<D, T>(a.rng, gi, (float)a.df, eps);
             }
         } else {
 #pragma unroll

@@ -92,6 +92,51 @@ __device__ __forceinline__ float draw_student_t(const PhiloxStream& s, uint64_t 
     return z * rsqrtf(2.0f * g / df);
 }
 
+// All D coordinates of one sample: the same variates as D calls of draw_student_t, bit for bit (same counters, same
+// arithmetic), but the Marsaglia-Tsang retries of the whole row are gathered into ONE loop per thread.  A first
+// attempt is rejected with probability ~5 %: written per coordinate, 80 % of the warps ran the retry body (a Philox
+// block, a Box-Muller pair, two acceptance tests) for one or two lanes after EVERY coordinate; gathered, a warp runs
+// it max-over-lanes times per row (2 - 3 instead of ~8 for D = 10), and the body exists once in the instruction
+// stream instead of D times.
+template <int D, typename T>
+__device__ __forceinline__ void draw_student_t_row(const PhiloxStream& s, uint64_t sample, float df, T (&eps)[D]) {
+    const float shape = 0.5f * df;
+    const float d = shape - 1.0f / 3.0f;
+    const float c = rsqrtf(9.0f * d);
+    float zs[D];
+    uint32_t pending = 0;
+#pragma unroll
+    for (int j = 0; j < D; ++j) {
+        const Philox4 r = philox_at(s, sample, (uint32_t)j);
+        float xn, g;
+        box_muller(r.x, r.y, zs[j], xn);
+        if (mt_accept(d, c, xn, u01(r.z), g)) zs[j] = zs[j] * rsqrtf(2.0f * g / df);
+        else pending |= 1u << j;
+    }
+    int a = 1;
+#pragma unroll 1
+    while (pending) {
+        const int j = __ffs((int)pending) - 1;
+        const Philox4 r = philox_at(s, sample, (uint32_t)j | ((uint32_t)a << 24));
+        float x0, x1, g;
+        box_muller(r.x, r.y, x0, x1);
+        bool ok = mt_accept(d, c, x0, u01(r.z), g);
+        if (!ok) ok = mt_accept(d, c, x1, u01(r.w), g);
+        ++a;
+        if (ok || a >= kGammaAttempts) {
+            if (!ok) g = d;                              // probability < 1e-15; keeps the draw finite
+            const float sc = rsqrtf(2.0f * g / df);
+#pragma unroll
+            for (int jj = 0; jj < D; ++jj)
+                if (jj == j) zs[jj] = zs[jj] * sc;       // (static indices: the row stays in registers)
+            pending &= pending - 1;
+            a = 1;
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < D; ++j) eps[j] = (T)zs[j];
+}
+
 // chisquare(df) for one sample (full-rank family, drawn "first": its own lane space).
 __device__ __forceinline__ float draw_chi2(const PhiloxStream& s, uint64_t sample, float df) {
     const float shape = 0.5f * df;
