@@ -742,7 +742,8 @@ class C3(Workload):
         self._out = torch.empty(1 + lam.size, dtype=torch.float64, device='cuda')
 
     def step_device(self):
-        return self.obj(self.lam_dev, base_draws=self.base)
+        # the draw is part of the step (vb.py:258 -> :203-208): Philox chi-square + normals generated on the device
+        return self.obj(self.lam_dev)
 
     def step_e2e(self):
         return self.obj(self.lam_host)

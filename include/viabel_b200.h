@@ -119,6 +119,11 @@ int vb_base_draws(int family, double df, int dtype, long long n, int dim,
                   unsigned long long seed, unsigned int call_offset,
                   unsigned long long sample_index0,
                   void* d_out_eps, void* d_out_chi2_or_null, void* stream);
+/* vb_base_draws for the full-rank family in fp32 storage that also writes the 3xTF32 operand planes of the normals
+ * (viabel/vb.py:203-206 draws; the planes feed vb_fr_weighted_split). */
+int vb_base_draws_fr_split(double df, long long n, int dim, unsigned long long seed, unsigned int call_offset,
+                           unsigned long long sample_index0, float* d_out_z, float* d_out_chi2,
+                           float* d_out_z_planes, void* stream);
 
 /* ------------------------------------------------------------------------------------
  * Fused mean-field step: draw/load eps -> x = m + exp(l) eps -> log p, grad log p ->
@@ -282,6 +287,12 @@ int vb_fr_weighted(int dtype, double df, long long n, int dim, const void* d_z,
                    const void* d_chi2, const double* d_w, const void* d_grad,
                    double* d_out_gmu, double* d_out_GS, void* d_ws, size_t ws_bytes,
                    void* stream);
+/* The same with the 3xTF32 operand planes of z (vb_split_bytes(n, dim) bytes, layout of vb_split_f32) supplied by the
+ * caller -- vb_base_draws_fr_split writes them together with the draws -- so that no split pass over z is made.
+ * fp32 storage only. */
+int vb_fr_weighted_split(double df, long long n, int dim, const float* d_z, const float* d_z_planes,
+                         const float* d_chi2, const double* d_w, const float* d_grad,
+                         double* d_out_gmu, double* d_out_GS, void* d_ws, size_t ws_bytes, void* stream);
 
 /* Dense helper: C (m, n) = alpha * op(A) op(B) + beta * C, row-major, float64 (SIMT) or
  * float32 storage with 3xTF32 tcgen05 arithmetic.  transa/transb: 0 = as stored, 1 = transposed. */

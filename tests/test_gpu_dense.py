@@ -239,6 +239,32 @@ def test_full_rank_chain_ill_conditioned(span):
         assert info[0] > 8, info          # the spectrum reaches below 1e-3: the schedule re-entered
 
 
+def test_full_rank_draws_carry_the_operand_planes():
+    """fp32 storage: base_draws() writes the 3xTF32 planes of z with the draws (vb_base_draws_fr_split) and the step's
+    weighted outer product consumes them (vb_fr_weighted_split).  Bit-identical to the separate draw / split passes."""
+    import torch
+    from viabel_b200 import _lib, models, vb
+    from viabel_b200._device import ptr, stream_ptr
+    d, n = 96, 5001
+    fam = vb.t_variational_family(d, 40, dtype='f32')
+    b = fam.impl.base_draws(n, 7, 3, index0=11)
+    assert b['z_planes'].numel() * 4 == _lib.lib.vb_split_bytes(n, d)
+    z2 = torch.empty_like(b['z'])
+    c2 = torch.empty_like(b['chi2'])
+    _lib.check(_lib.lib.vb_base_draws(_lib.FAMILY_FR_T, 40.0, _lib.F32, n, d, 7, 3, 11, ptr(z2), ptr(c2), stream_ptr()))
+    assert torch.equal(z2, b['z']) and torch.equal(c2, b['chi2'])
+    ref = torch.empty_like(b['z_planes'])
+    _lib.check(_lib.lib.vb_split_f32(ptr(b['z']), n, d, d, ptr(ref), stream_ptr()))
+    assert torch.equal(ref, b['z_planes'])
+    mp, Pp = _gauss(d)
+    lam = 0.1 * np.random.RandomState(6).randn(fam.var_param_dim)
+    for make in (lambda: vb.black_box_klvi(fam, models.CorrelatedGaussian(mp, Pp), n, group=False),
+                 lambda: vb.black_box_chivi(2.0, fam, models.CorrelatedGaussian(mp, Pp), n, group=False)):
+        v1, g1 = make()(lam, base_draws=b)                                       # planes used
+        v2, g2 = make()(lam, base_draws={'z': b['z'], 'chi2': b['chi2']})        # z split by the step
+        assert v1 == v2 and np.array_equal(g1, g2)
+
+
 def test_full_rank_family_closures():
     import torch
     from viabel_b200 import vb

@@ -41,6 +41,7 @@ SIGNATURES = {
     'vb_model_logp_grad_workspace_bytes': (_sz, [_p, _ll, _i]),
     'vb_model_logp_grad': (_i, [_p, _i, _p, _ll, _p, _p, _p, _sz, _p]),
     'vb_base_draws': (_i, [_i, _d, _i, _ll, _i, _ull, _u, _ull, _p, _p, _p]),
+    'vb_base_draws_fr_split': (_i, [_d, _ll, _i, _ull, _u, _ull, _p, _p, _p, _p]),
     'vb_mf_step_workspace_bytes': (_sz, [_i]),
     'vb_mf_step': (_i, [_i, _d, _p, _i, _d, _i, _p, _ll, _p, _ull, _u, _ull, _p, _p, _p, _p, _sz, _p]),
     'vb_mf_adagrad_state_bytes': (_sz, [_i, _i]),
@@ -70,6 +71,7 @@ SIGNATURES = {
     'vb_fr_rows': (_i, [_i, _d, _d, _i, _ll, _i, _p, _p, _p, _d, _p, _p, _p, _p, _sz, _p]),
     'vb_fr_weighted_workspace_bytes': (_sz, [_ll, _i]),
     'vb_fr_weighted': (_i, [_i, _d, _ll, _i, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    'vb_fr_weighted_split': (_i, [_d, _ll, _i, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     'vb_gemm_workspace_bytes': (_sz, [_i, _ll, _ll, _ll]),
     'vb_gemm': (_i, [_i, _i, _i, _ll, _ll, _ll, _d, _p, _ll, _p, _ll, _d, _p, _ll, _p, _sz, _p]),
     'vb_split_bytes': (_sz, [_ll, _ll]),

@@ -28,7 +28,7 @@ size_t fr_weighted_tf32_workspace_bytes(long long n, int dim);
 // G_S (dim, dim) fp64 = sum_i (w_i / sqrt(chi2_i/df)) z_i' g_i on the tensor path (split-K, fp64 cross-split sum)
 int fr_weighted_GS_tf32(double df, long long n, int dim, const float* z, const float* chi2, const double* w,
                         const float* grad, double* out_GS, void* ws, size_t ws_bytes, cudaStream_t st,
-                        double* out_gmu_or_null = nullptr);
+                        double* out_gmu_or_null = nullptr, const float* z_planes_or_null = nullptr);
 // true when fr_weighted_GS_tf32 also returns g_mu = sum_i w_i g_i (its row-scaling pass carries the column sums)
 bool fr_weighted_colsum_fused(long long n, int dim);
 

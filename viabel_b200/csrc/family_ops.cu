@@ -3,6 +3,7 @@
 // Reference: viabel/vb.py:54-65, 148-162, 202-208.
 #include "common.cuh"
 #include "philox.cuh"
+#include "tc05.cuh"
 
 namespace vb {
 
@@ -37,6 +38,38 @@ __global__ void base_draws_kernel(int family, float df, long long n, int D, Phil
 #pragma unroll
             for (int k = 0; k < 4; ++k)
                 if (4 * q + k < D) out[i * D + 4 * q + k] = (T)z[k];
+        }
+    }
+}
+
+// Standard normals of the full-rank family (fp32) written together with their 3xTF32 operand planes (hi, lo; row pitch
+// pad4(D), the layout of split_kernel / vb_split_f32): the weighted outer product Z' diag(w) G then needs no split pass
+// over z (134 MB read + 268 MB written per step at C3).  Same variates and same split as the two separate kernels.
+__global__ void base_draws_split_kernel(long long n, int D, PhiloxStream rng, unsigned long long index0,
+                                        float* __restrict__ out, float* __restrict__ planes, long long ldd, long long plane) {
+    const int Q = (D + 3) / 4;
+    const long long total = n * Q;
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
+         e += (long long)gridDim.x * blockDim.x) {
+        const long long i = e / Q;
+        const int q = (int)(e - i * Q);
+        float z[4], hi[4], lo[4];
+        draw_normal_pair(rng, index0 + (uint64_t)i, (uint32_t)q, z[0], z[1], z[2], z[3]);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            hi[k] = lo[k] = 0.f;
+            if (4 * q + k < D) tc::split_tf32(z[k], hi[k], lo[k]);
+        }
+        // 4 q + k < ldd always (Q = ldd / 4): padding columns of the planes get zeros; 16-byte stores where aligned
+        float* ph = planes + i * ldd + 4 * q;
+        *reinterpret_cast<float4*>(ph) = make_float4(hi[0], hi[1], hi[2], hi[3]);
+        *reinterpret_cast<float4*>(ph + plane) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+        if ((D & 3) == 0) {
+            *reinterpret_cast<float4*>(out + i * D + 4 * q) = make_float4(z[0], z[1], z[2], z[3]);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (4 * q + k < D) out[i * D + 4 * q + k] = z[k];
         }
     }
 }
@@ -323,6 +356,25 @@ extern "C" int vb_base_draws(int family, double df, int dtype, long long n, int 
             base_draws_chi2_kernel<float><<<g2, 256, 0, st>>>((float)df, n, rng, sample_index0, (float*)d_out_chi2_or_null);
         VB_LAUNCH_CHECK();
     }
+    return VB_OK;
+}
+
+// vb_base_draws for the full-rank family in fp32 storage that also writes the 3xTF32 operand planes of z
+// (vb_split_bytes(n, dim) bytes; consumed by vb_fr_weighted_split)
+extern "C" int vb_base_draws_fr_split(double df, long long n, int dim, unsigned long long seed, unsigned int call_offset,
+                                      unsigned long long sample_index0, float* d_out_z, float* d_out_chi2,
+                                      float* d_out_z_planes, void* stream) {
+    if (!d_out_z || !d_out_chi2 || !d_out_z_planes || n < 1 || dim < 1 || !(df > 2.0)) return VB_ERR_ARG;
+    if ((reinterpret_cast<uintptr_t>(d_out_z_planes) & 15u) || ((dim & 3) == 0 && (reinterpret_cast<uintptr_t>(d_out_z) & 15u)))
+        return VB_ERR_ALIGN;
+    PhiloxStream rng{(uint32_t)seed, (uint32_t)(seed >> 32), call_offset};
+    cudaStream_t st = (cudaStream_t)stream;
+    const long long ldd = ((long long)dim + 3) / 4 * 4;
+    base_draws_split_kernel<<<grid_for(n * (ldd / 4), 256, kNumSMs * 8), 256, 0, st>>>(n, dim, rng, sample_index0, d_out_z,
+                                                                                     d_out_z_planes, ldd, n * ldd);
+    VB_LAUNCH_CHECK();
+    base_draws_chi2_kernel<float><<<grid_for(n, 256, kNumSMs * 8), 256, 0, st>>>((float)df, n, rng, sample_index0, d_out_chi2);
+    VB_LAUNCH_CHECK();
     return VB_OK;
 }
 

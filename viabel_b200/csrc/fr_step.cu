@@ -253,9 +253,26 @@ extern "C" size_t vb_fr_weighted_workspace_bytes(long long n, int dim) {
     return (a + b + 512) > t ? (a + b + 512) : t;
 }
 
+static int fr_weighted_impl(int dtype, double df, long long n, int dim, const void* d_z, const float* d_z_planes_or_null,
+                            const void* d_chi2, const double* d_w, const void* d_grad,
+                            double* d_out_gmu, double* d_out_GS, void* d_ws, size_t ws_bytes, void* stream);
 extern "C" int vb_fr_weighted(int dtype, double df, long long n, int dim, const void* d_z,
                               const void* d_chi2, const double* d_w, const void* d_grad,
                               double* d_out_gmu, double* d_out_GS, void* d_ws, size_t ws_bytes, void* stream) {
+    return fr_weighted_impl(dtype, df, n, dim, d_z, nullptr, d_chi2, d_w, d_grad, d_out_gmu, d_out_GS, d_ws, ws_bytes, stream);
+}
+// fp32 storage with the 3xTF32 operand planes of z already made (vb_base_draws_fr_split, or vb_split_f32 of z): the
+// product reads them instead of splitting z again
+extern "C" int vb_fr_weighted_split(double df, long long n, int dim, const float* d_z, const float* d_z_planes,
+                                    const float* d_chi2, const double* d_w, const float* d_grad,
+                                    double* d_out_gmu, double* d_out_GS, void* d_ws, size_t ws_bytes, void* stream) {
+    if (!d_z_planes) return VB_ERR_ARG;
+    if (reinterpret_cast<uintptr_t>(d_z_planes) & 15u) return VB_ERR_ALIGN;
+    return fr_weighted_impl(VB_F32, df, n, dim, d_z, d_z_planes, d_chi2, d_w, d_grad, d_out_gmu, d_out_GS, d_ws, ws_bytes, stream);
+}
+static int fr_weighted_impl(int dtype, double df, long long n, int dim, const void* d_z, const float* d_z_planes_or_null,
+                            const void* d_chi2, const double* d_w, const void* d_grad,
+                            double* d_out_gmu, double* d_out_GS, void* d_ws, size_t ws_bytes, void* stream) {
     if (!d_z || !d_chi2 || !d_w || !d_grad || !d_out_gmu || !d_out_GS || !d_ws || n < 1 || dim < 1) return VB_ERR_ARG;
     if (dtype != VB_F32 && dtype != VB_F64) return VB_ERR_ARG;
     if (ws_bytes < vb_fr_weighted_workspace_bytes(n, dim)) return VB_ERR_WORKSPACE;
@@ -279,7 +296,8 @@ extern "C" int vb_fr_weighted(int dtype, double df, long long n, int dim, const 
         double* colparts32 = (double*)((char*)d_ws + ((fr_weighted_tf32_workspace_bytes(n, dim) + 255) & ~(size_t)255));
         const bool fused = fr_weighted_colsum_fused(n, dim);
         rc = fr_weighted_GS_tf32(df, n, dim, (const float*)d_z, (const float*)d_chi2, d_w, (const float*)d_grad,
-                                 d_out_GS, d_ws, fr_weighted_tf32_workspace_bytes(n, dim), st, fused ? d_out_gmu : nullptr);
+                                 d_out_GS, d_ws, fr_weighted_tf32_workspace_bytes(n, dim), st, fused ? d_out_gmu : nullptr,
+                                 d_z_planes_or_null);
         if (rc != VB_OK) return rc;
         if (fused) return VB_OK;
         fr_wcolsum_kernel<float><<<dim3((dim + 31) / 32, chunks), dim3(32, 8), 0, st>>>(n, dim, (const float*)d_grad,

@@ -466,16 +466,21 @@ bool fr_weighted_colsum_fused(long long n, int dim) {
 
 int fr_weighted_GS_tf32(double df, long long n, int dim, const float* z, const float* chi2, const double* w,
                         const float* grad, double* out_GS, void* ws, size_t ws_bytes, cudaStream_t st,
-                        double* out_gmu_or_null) {
+                        double* out_gmu_or_null, const float* z_planes_or_null) {
     if (!ws || ws_bytes < fr_weighted_tf32_workspace_bytes(n, dim)) return VB_ERR_WORKSPACE;
     char* wp = (char*)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
     float* zs_buf = (float*)wp;     wp += split_bytes(n, dim);
     float* gs_buf = (float*)wp;     wp += split_bytes(n, dim);
     float* parts = (float*)wp;
     SplitMat zs;
-    int rc = split_into(z, n, dim, dim, zs_buf, st, &zs);
-    if (rc != VB_OK) return rc;
+    int rc = VB_OK;
     const long long ldd = pad4(dim);
+    if (z_planes_or_null) {                              // made with the draws (vb_base_draws_fr_split): no split pass
+        zs = SplitMat{z_planes_or_null, n, dim, ldd, n * ldd};
+    } else {
+        rc = split_into(z, n, dim, dim, zs_buf, st, &zs);
+        if (rc != VB_OK) return rc;
+    }
     // the weighted column sums ride along when the thread count is a multiple of the padded row length
     const int sgrid = grid_for(n * ldd, 256, kNumSMs * 8);
     const long long sthreads = (long long)sgrid * 256;

@@ -83,6 +83,13 @@ class _FamilyImpl:
         dt = torch_dtype(self.code)
         eps = torch.empty((n, self.dim), dtype=dt, device=device())
         chi2 = torch.empty(n, dtype=dt, device=device()) if self.kind == _lib.FAMILY_FR_T else None
+        if self.kind == _lib.FAMILY_FR_T and self.code == _lib.F32:
+            # fp32 storage: the draw kernel also writes the 3xTF32 operand planes of z that the weighted outer product
+            # of the step consumes (no separate split pass over z)
+            planes = torch.empty(_lib.lib.vb_split_bytes(n, self.dim) // 4, dtype=torch.float32, device=device())
+            _lib.check(_lib.lib.vb_base_draws_fr_split(self.df, n, self.dim, seed, offset, index0, ptr(eps), ptr(chi2),
+                                                       ptr(planes), stream_ptr()), 'vb_base_draws_fr_split')
+            return {'z': eps, 'chi2': chi2, 'z_planes': planes}
         _lib.check(_lib.lib.vb_base_draws(self.kind, self.df, self.code, n, self.dim, seed, offset, index0,
                                           ptr(eps), ptr(chi2), stream_ptr()), 'vb_base_draws')
         if self.kind == _lib.FAMILY_FR_T:
@@ -95,7 +102,12 @@ class _FamilyImpl:
             z, c = to_dev(base['z'], self.code), to_dev(base['chi2'], self.code)
             if z.ndim != 2 or z.shape[1] != self.dim or c.shape != (z.shape[0],):
                 raise ValueError('base draws must be z (n, dim) and chi2 (n,)')
-            return {'z': z, 'chi2': c}
+            out = {'z': z, 'chi2': c}
+            planes = base.get('z_planes') if isinstance(base, dict) else None
+            if (planes is not None and self.code == _lib.F32 and isinstance(planes, torch.Tensor) and planes.is_cuda
+                    and z is base['z'] and planes.numel() * 4 == _lib.lib.vb_split_bytes(z.shape[0], self.dim)):
+                out['z_planes'] = planes                 # made by base_draws() together with this very z
+            return out
         eps = base['eps'] if isinstance(base, dict) else base
         eps = to_dev(eps, self.code)
         if eps.ndim != 2 or eps.shape[1] != self.dim:
@@ -502,9 +514,14 @@ class _Objective:
         g_mu = torch.empty(d, dtype=torch.float64, device=vp.device)
         G_S = torch.empty((d, d), dtype=torch.float64, device=vp.device)
         ws2 = self.ws.get('fr_weighted', _lib.lib.vb_fr_weighted_workspace_bytes(n, d))
-        _lib.check(_lib.lib.vb_fr_weighted(impl.code, impl.df, n, d, ptr(base['z']), ptr(base['chi2']), ptr(w),
-                                           ptr(grad), ptr(g_mu), ptr(G_S), ptr(ws2), ws2.numel(), stream_ptr()),
-                   'vb_fr_weighted')
+        if base.get('z_planes') is not None:
+            _lib.check(_lib.lib.vb_fr_weighted_split(impl.df, n, d, ptr(base['z']), ptr(base['z_planes']), ptr(base['chi2']),
+                                                     ptr(w), ptr(grad), ptr(g_mu), ptr(G_S), ptr(ws2), ws2.numel(),
+                                                     stream_ptr()), 'vb_fr_weighted_split')
+        else:
+            _lib.check(_lib.lib.vb_fr_weighted(impl.code, impl.df, n, d, ptr(base['z']), ptr(base['chi2']), ptr(w),
+                                               ptr(grad), ptr(g_mu), ptr(G_S), ptr(ws2), ws2.numel(), stream_ptr()),
+                       'vb_fr_weighted')
         if world > 1:
             rows, g_mu, G_S = fr_exchange_sums(rows, g_mu, G_S, world, g, n)
         self.last_log_weights = lw
@@ -566,12 +583,19 @@ class _Objective:
             if self.obj != _lib.OBJ_CHIVI:
                 seed, off = impl.next_stream(None)
             else:
-                seed, off = int(np.random.randint(2 ** 32)), 0
+                seed, off = int(np.random.randint(2 ** 32)), 0          # every rank consumes one draw per call (vb.py:258)
                 if world > 1:
-                    import torch.distributed as dist
-                    st = torch.tensor([seed], dtype=torch.int64, device=vp.device)
-                    dist.broadcast(st, src=dist.get_global_rank(g, 0) if g is not None else 0, group=g)
-                    seed = int(st.item())
+                    # the ranks need ONE seed per call.  Rank 0's first draw is broadcast once per objective (one host
+                    # read, first call only); call k then uses base + k * golden-ratio increment (mod 2^64), so the
+                    # steady state has no collective and no host read for the seed.  Every rank must make the same
+                    # sequence of calls -- which the step's own collectives require anyway.
+                    if getattr(self, '_shard_seed', None) is None:
+                        import torch.distributed as dist
+                        st = torch.tensor([seed], dtype=torch.int64, device=vp.device)
+                        dist.broadcast(st, src=dist.get_global_rank(g, 0) if g is not None else 0, group=g)
+                        self._shard_seed, self._shard_calls = int(st.item()), 0
+                    seed = (self._shard_seed + 0x9E3779B97F4A7C15 * self._shard_calls) & 0xFFFFFFFFFFFFFFFF
+                    self._shard_calls += 1
             index0, n_local = _shard(self.n, rank, world)
             n_total = self.n
         if impl.kind == _lib.FAMILY_FR_T:
