@@ -406,7 +406,7 @@ class C5(Workload):
         self.units_per_step = self.n
         self.h2d_bytes = 2 * self.n * 8        # psislw(lw_host) and all_bounds(lw_host) each upload the weights
         self.d2h_bytes = self.n * 8
-        self.launches_per_step = 60
+        self.launches_per_step = 30       # profiles/r3d_launches_c5.txt (psislw; all_bounds launches nothing on a cache hit)
         self._out = torch.empty_like(self.lw)
         self._diag = torch.empty(8, dtype=torch.float64, device='cuda')
         nb = _lib.lib.vb_psis_smooth_workspace_bytes(self.n, 1.0)
@@ -723,7 +723,7 @@ class C3(Workload):
         self.units_per_step = self.n
         self.h2d_bytes = lam.nbytes
         self.d2h_bytes = 8 * (1 + lam.size)
-        self.launches_per_step = 20
+        self.launches_per_step = 17       # profiles/r3g_launches_c3.txt: 2 draws, 2 chain, 3 GEMMs + 10 small kernels per step
         # pre-split operands for the kernel-only timing: X (n, d) = Z (n, d) S (d, d)
         lib = _lib.lib
         z = self.base['z']
@@ -873,13 +873,14 @@ class C2(MeanFieldStages, Workload):
         self.lam_dev = torch.from_numpy(lam).cuda()
         self.units_per_step = self.n
         self.h2d_bytes, self.d2h_bytes = lam.nbytes, 8 * (1 + lam.size)
-        self.launches_per_step = 7        # mf_sample, y prescale, fused kernel, final reduce, weights, colsum, finish
+        self.launches_per_step = 8        # base draws, mf_sample, y prescale, fused kernel, final reduce, weights, colsum, finish
         self._x = torch.from_numpy(np.tile(lam[:self.d], (self.n, 1))).cuda()
         if self.compute == 'f32':
             self._x = self._x.float()
 
     def step_device(self):
-        return self.obj(self.lam_dev, base_draws=self.eps)
+        # the draw is part of the step (vb.py:239 -> :54-57): Philox normals generated on the device
+        return self.obj(self.lam_dev)
 
     def step_e2e(self):
         return self.obj(self.lam_host)
