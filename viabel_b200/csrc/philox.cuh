@@ -41,18 +41,23 @@ __device__ __forceinline__ Philox4 philox_at(const PhiloxStream& s, uint64_t sam
     return philox4x32_10((uint32_t)sample, (uint32_t)(sample >> 32), lane, s.offset, s.k0, s.k1);
 }
 
+// Every arithmetic step below is written with explicit round-to-nearest intrinsics: the same source inlined into
+// different kernels must give the same bits (left to the compiler, a*b+c contracts to an FMA in one kernel and not in
+// another, and a Marsaglia-Tsang acceptance that sits on the boundary then flips: 1 draw in ~1e7 differed between the
+// stand-alone draw kernel and the fused step).
+
 // (0,1) open interval, 2^-32 resolution before fp32 rounding; never 0, may round to 1-2^-24.
 __device__ __forceinline__ float u01(uint32_t u) {
-    return fminf(((float)u + 0.5f) * 2.3283064365386963e-10f, 0.99999994f);
+    return fminf(__fmul_rn(__fadd_rn((float)u, 0.5f), 2.3283064365386963e-10f), 0.99999994f);
 }
 
 // Two independent standard normals from two words.
 __device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& n0, float& n1) {
-    const float r = sqrtf(-2.0f * __logf(u01(a)));
+    const float r = __fsqrt_rn(__fmul_rn(-2.0f, __logf(u01(a))));
     float s, c;
-    __sincosf(6.2831853071795865f * ((float)b * 2.3283064365386963e-10f), &s, &c);
-    n0 = r * c;
-    n1 = r * s;
+    __sincosf(__fmul_rn(6.2831853071795865f, __fmul_rn((float)b, 2.3283064365386963e-10f)), &s, &c);
+    n0 = __fmul_rn(r, c);
+    n1 = __fmul_rn(r, s);
 }
 
 // Lane numbering: coordinates use lanes [0, 2^30); rejection retries use lane | (attempt << 30)... kept
@@ -62,18 +67,20 @@ constexpr int kGammaAttempts = 6;   // acceptance >= 0.95 per attempt for shape 
 
 // Marsaglia-Tsang acceptance test for Gamma(shape, 1), shape >= 1, given a normal and a uniform.
 __device__ __forceinline__ bool mt_accept(float d, float c, float xn, float un, float& out) {
-    const float t = 1.0f + c * xn;
-    const float v = t * t * t;
-    out = d * v;
-    return (t > 0.0f) && (__logf(un) < 0.5f * xn * xn + d - d * v + d * __logf(v));
+    const float t = __fmaf_rn(c, xn, 1.0f);
+    const float v = __fmul_rn(__fmul_rn(t, t), t);
+    out = __fmul_rn(d, v);
+    // log(u) < x^2 / 2 + d - d v + d log(v)
+    const float rhs = __fmaf_rn(d, __logf(v), __fadd_rn(__fmaf_rn(__fmul_rn(0.5f, xn), xn, d), -out));
+    return (t > 0.0f) && (__logf(un) < rhs);
 }
 
 // standard_t(df) variate for (sample, coord): z / sqrt(chi2/df), chi2 = 2 Gamma(df/2).
 __device__ __forceinline__ float draw_student_t(const PhiloxStream& s, uint64_t sample, uint32_t coord,
                                                 float df) {
-    const float shape = 0.5f * df;
-    const float d = shape - 1.0f / 3.0f;
-    const float c = rsqrtf(9.0f * d);
+    const float shape = __fmul_rn(0.5f, df);
+    const float d = __fadd_rn(shape, -(1.0f / 3.0f));
+    const float c = rsqrtf(__fmul_rn(9.0f, d));
     Philox4 r = philox_at(s, sample, coord);
     float z, xn;
     box_muller(r.x, r.y, z, xn);
@@ -89,7 +96,7 @@ __device__ __forceinline__ float draw_student_t(const PhiloxStream& s, uint64_t 
     }
     if (!ok) g = d;   // probability < 1e-15; keeps the draw finite
     // chi2/df = 2 g / df
-    return z * rsqrtf(2.0f * g / df);
+    return __fmul_rn(z, rsqrtf(__fdiv_rn(__fmul_rn(2.0f, g), df)));
 }
 
 // All D coordinates of one sample: the same variates as D calls of draw_student_t, bit for bit (same counters, same
@@ -100,9 +107,9 @@ __device__ __forceinline__ float draw_student_t(const PhiloxStream& s, uint64_t 
 // stream instead of D times.
 template <int D, typename T>
 __device__ __forceinline__ void draw_student_t_row(const PhiloxStream& s, uint64_t sample, float df, T (&eps)[D]) {
-    const float shape = 0.5f * df;
-    const float d = shape - 1.0f / 3.0f;
-    const float c = rsqrtf(9.0f * d);
+    const float shape = __fmul_rn(0.5f, df);
+    const float d = __fadd_rn(shape, -(1.0f / 3.0f));
+    const float c = rsqrtf(__fmul_rn(9.0f, d));
     float zs[D];
     uint32_t pending = 0;
 #pragma unroll
@@ -110,7 +117,7 @@ __device__ __forceinline__ void draw_student_t_row(const PhiloxStream& s, uint64
         const Philox4 r = philox_at(s, sample, (uint32_t)j);
         float xn, g;
         box_muller(r.x, r.y, zs[j], xn);
-        if (mt_accept(d, c, xn, u01(r.z), g)) zs[j] = zs[j] * rsqrtf(2.0f * g / df);
+        if (mt_accept(d, c, xn, u01(r.z), g)) zs[j] = __fmul_rn(zs[j], rsqrtf(__fdiv_rn(__fmul_rn(2.0f, g), df)));
         else pending |= 1u << j;
     }
     int a = 1;
@@ -125,10 +132,10 @@ __device__ __forceinline__ void draw_student_t_row(const PhiloxStream& s, uint64
         ++a;
         if (ok || a >= kGammaAttempts) {
             if (!ok) g = d;                              // probability < 1e-15; keeps the draw finite
-            const float sc = rsqrtf(2.0f * g / df);
+            const float sc = rsqrtf(__fdiv_rn(__fmul_rn(2.0f, g), df));
 #pragma unroll
             for (int jj = 0; jj < D; ++jj)
-                if (jj == j) zs[jj] = zs[jj] * sc;       // (static indices: the row stays in registers)
+                if (jj == j) zs[jj] = __fmul_rn(zs[jj], sc);       // (static indices: the row stays in registers)
             pending &= pending - 1;
             a = 1;
         }
@@ -139,9 +146,9 @@ __device__ __forceinline__ void draw_student_t_row(const PhiloxStream& s, uint64
 
 // chisquare(df) for one sample (full-rank family, drawn "first": its own lane space).
 __device__ __forceinline__ float draw_chi2(const PhiloxStream& s, uint64_t sample, float df) {
-    const float shape = 0.5f * df;
-    const float d = shape - 1.0f / 3.0f;
-    const float c = rsqrtf(9.0f * d);
+    const float shape = __fmul_rn(0.5f, df);
+    const float d = __fadd_rn(shape, -(1.0f / 3.0f));
+    const float c = rsqrtf(__fmul_rn(9.0f, d));
     float g = d;
     bool ok = false;
 #pragma unroll 1
@@ -153,7 +160,7 @@ __device__ __forceinline__ float draw_chi2(const PhiloxStream& s, uint64_t sampl
         if (!ok) ok = mt_accept(d, c, x1, u01(r.w), g);
     }
     if (!ok) g = d;
-    return 2.0f * g;
+    return __fmul_rn(2.0f, g);
 }
 
 // Two standard normals for coordinates (2*pair, 2*pair+1) of a sample.
