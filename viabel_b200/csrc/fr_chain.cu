@@ -1,17 +1,20 @@
 // The O(d^3) parameter chain of the full-rank Student-t family (kernel K7) as TWO persistent
 // cooperative kernels, with no eigendecomposition and no library call:
 //   forward   phi -> L (paragami free PSD pattern, viabel/vb.py:185-189) -> S = sqrtm(L L')      (vb.py:207)
-//   backward  G_S -> Y solving S Y + Y S = G_S (autograd's sqrtm VJP) -> G_L = (Y + Y') L -> d/dphi, and the assembly
-//             of the KLVI / CHIVI (value, gradient) vector                                       (vb.py:236-266)
+//   backward  G_S -> Y solving S Y + Y S = sym(G_S) (autograd's sqrtm VJP; only Y + Y' is used) -> G_L = 2 Y L ->
+//             d/dphi, and the assembly of the KLVI / CHIVI (value, gradient) vector                (vb.py:236-266)
 // Everything is fp64 GEMMs on the fp64 tensor cores (mma.sync m8n8k4) inside one launch, separated by grid barriers:
-//   * S is the symmetric polar factor of L (L = S Q, Q orthogonal): Q by a Newton-Schulz iteration on X0 = L / |L|_F
-//     (a few steps of the quintic a X + X (b A + c A^2), A = X'X, lift the small singular values at 3.44x per step,
-//     then the cubic 1.5 X - 0.5 X A converges quadratically), S = sym(L Q').
+//   * S is the symmetric polar factor of L (L = S Q, Q orthogonal): Q by a polynomial iteration on
+//     X0 = L / (|L|_F |X0'X0|_F^1/2): six minimax quintics a X + X (b A + c A^2), A = X'X (kPolarSched: built for
+//     sigma_min / sigma_max >= 1e-3, re-entered in cycles below that), then the cubic 1.5 X - 0.5 X A, which converges
+//     quadratically; S = sym(L Q').
 //   * Sylvester by squared-Smith doubling: with M = S + mu I, A0 = (S - mu I) M^-1, Y0 = 2 mu M^-1 G M^-1,
-//     Y = sum_j A0^j Y0 A0^j:  Y <- Y + A Y A, A <- A^2;  M^-1 by Newton-Schulz (X <- 2 X - X M X).
+//     Y = sum_j A0^j Y0 A0^j:  Y <- Y + A Y A, A <- A^2;  M^-1 by Newton-Schulz (X <- 2 X - X M X) from
+//     2 / (ub + 2 mu) I, ub >= lambda_max(S) left by the forward.
+//   * Products whose result is symmetric (52 of 73 at C3) compute only the lower-triangular 32 x 32 blocks.
 // Every iteration's stopping test is a Frobenius norm summed in fixed order from per-CTA partials, so all CTAs take
-// the same decision and repeated runs are bit-identical.  Accuracy vs the eigh formulation: S 4e-15, Y 5e-13
-// (config C3, kappa(L) = 216); 87 GEMMs of 512^3 instead of cuSOLVER syevd + 5 GEMMs.
+// the same decision and repeated runs are bit-identical.  Accuracy vs the eigh formulation: S 5e-15, Y 4e-13
+// (config C3, cond(L) = 216); 73 GEMMs of 512^3 (9 + 7 + 10 iterations) instead of cuSOLVER syevd + 5 GEMMs.
 #include <cstdlib>
 #include "common.cuh"
 
