@@ -561,13 +561,13 @@ class N3(Workload):
             psis_np.psisloo(ll)
         return self.n * cols / (time.perf_counter() - t0)
 
-    def cpu_baseline(self):
+    def cpu_baseline(self, budget_s=None, k=None):       # fixed sample (a few seconds); the budget arguments are accepted
         rate = self._cpu(self.cpu_cols)
         return {'value': rate, 'unit': self.unit, 'cores': 1, 'kind': 'port',
                 'sample': 'oracle psisloo on %d of the %d columns (4000 draws each), single-threaded numpy'
                           % (self.cpu_cols, self.m)}
 
-    def reference_arm(self, steps, warmup):
+    def reference_arm(self, steps, warmup, budget_s=None):
         k = max(1, min(steps, 3))
         t0 = time.perf_counter()
         rates = [self._cpu(self.cpu_cols) for _ in range(k)]
@@ -667,13 +667,13 @@ class N4R(Workload):
             ofn.stochastic_iterate_averaging(hist[o], self.iters - 500)
         return self.chains * self.iters * params / (time.perf_counter() - t0)
 
-    def cpu_baseline(self):
+    def cpu_baseline(self, budget_s=None, k=None):
         rate = self._cpu(self.cpu_params)
         return {'value': rate, 'unit': self.unit, 'cores': 1, 'kind': 'port',
                 'sample': 'oracle diagnostics on %d of the %d parameters, single-threaded numpy'
                           % (self.cpu_params, self.params)}
 
-    def reference_arm(self, steps, warmup):
+    def reference_arm(self, steps, warmup, budget_s=None):
         k = max(1, min(steps, 3))
         t0 = time.perf_counter()
         rates = [self._cpu(self.cpu_params) for _ in range(k)]

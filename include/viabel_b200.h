@@ -535,6 +535,9 @@ int vb_gpd_fit_quadrature(const double* d_x_sorted, long long n, double* d_out_k
                           double* d_out_w, void* d_ws, size_t ws_bytes, void* stream);
 int vb_gpd_inv(const double* d_p, long long n, double k, double sigma, double* d_out,
                void* stream);
+/* d_dst (cols, rows) = scale * transpose of d_src (rows, cols): the layout change of psislw / psisloo for 2-D input
+ * (psis.py:101 negates: scale = -1). */
+int vb_transpose_scale_f64(const double* d_src, long long rows, long long cols, double scale, double* d_dst, void* stream);
 size_t vb_logsumexp_workspace_bytes(long long n);
 int vb_logsumexp(const double* d_x, long long n, double* d_out, void* d_ws, size_t ws_bytes,
                  void* stream);

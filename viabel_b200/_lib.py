@@ -118,6 +118,7 @@ SIGNATURES = {
     'vb_sort_f64': (_i, [_p, _ll, _p, _p, _sz, _p]),
     'vb_gpd_fit_quadrature': (_i, [_p, _ll, _p, _p, _p, _p, _sz, _p]),
     'vb_gpd_inv': (_i, [_p, _ll, _d, _d, _p, _p]),
+    'vb_transpose_scale_f64': (_i, [_p, _ll, _ll, _d, _p, _p]),
     'vb_logsumexp_workspace_bytes': (_sz, [_ll]),
     'vb_logsumexp': (_i, [_p, _ll, _p, _p, _sz, _p]),
     'vb_psis_normalise': (_i, [_p, _ll, _d, _p]),

@@ -1928,6 +1928,41 @@ extern "C" size_t vb_logsumexp_workspace_bytes(long long n) {
     return 256 + (size_t)kNumSMs * 8 * 8 + 256 + vb_max_workspace_bytes(n);
 }
 
+// dst (cols, rows) = scale * src (rows, cols)': the layout change psislw / psisloo make for 2-D input (one contiguous
+// row per weight set; psisloo also negates: lw = -log_lik, psis.py:101), through 32 x 33 shared-memory tiles so that
+// both the reads and the writes are coalesced.
+namespace vb {
+__global__ void __launch_bounds__(256)
+transpose_scale_kernel(const double* __restrict__ src, long long rows, long long cols, double scale, double* __restrict__ dst) {
+    __shared__ double tile[32][33];
+    const long long tiles_c = (cols + 31) / 32, tiles_r = (rows + 31) / 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;          // 32 x 8 threads
+    for (long long t = blockIdx.x; t < tiles_r * tiles_c; t += gridDim.x) {
+        const long long r0 = (t / tiles_c) * 32, c0 = (t % tiles_c) * 32;
+#pragma unroll
+        for (int k = 0; k < 32; k += 8) {
+            const long long r = r0 + ty + k, c = c0 + tx;
+            tile[ty + k][tx] = (r < rows && c < cols) ? scale * src[r * cols + c] : 0.0;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < 32; k += 8) {
+            const long long c = c0 + ty + k, r = r0 + tx;
+            if (c < cols && r < rows) dst[c * rows + r] = tile[tx][ty + k];
+        }
+        __syncthreads();
+    }
+}
+}  // namespace vb
+extern "C" int vb_transpose_scale_f64(const double* d_src, long long rows, long long cols, double scale, double* d_dst,
+                                      void* stream) {
+    if (!d_src || !d_dst || rows < 1 || cols < 1 || d_src == d_dst) return VB_ERR_ARG;
+    const long long tiles = ((rows + 31) / 32) * ((cols + 31) / 32);
+    transpose_scale_kernel<<<grid_for(tiles, 1, kNumSMs * 8), 256, 0, (cudaStream_t)stream>>>(d_src, rows, cols, scale, d_dst);
+    VB_LAUNCH_CHECK();
+    return VB_OK;
+}
+
 extern "C" int vb_logsumexp(const double* d_x, long long n, double* d_out, void* d_ws, size_t ws_bytes, void* stream) {
     if (!d_x || !d_out || !d_ws || n < 1) return VB_ERR_ARG;
     if (ws_bytes < vb_logsumexp_workspace_bytes(n)) return VB_ERR_WORKSPACE;

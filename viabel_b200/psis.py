@@ -44,6 +44,16 @@ class _DivCache:
         return cls.partials
 
 
+def _transposed(x, scale):
+    """(rows, cols) CUDA f64 -> contiguous (cols, rows) = scale * x' in one pass (``vb_transpose_scale_f64``)."""
+    x = x.contiguous()
+    rows, cols = x.shape
+    out = torch.empty((cols, rows), dtype=torch.float64, device=x.device)
+    _lib.check(_lib.lib.vb_transpose_scale_f64(ptr(x), rows, cols, float(scale), ptr(out), stream_ptr()),
+               'vb_transpose_scale_f64')
+    return out
+
+
 def _smooth_1d(col, Reff, want_tail=False, src=None):
     """col: CUDA f64 (n,) contiguous -> (smoothed (n,), diag (8,) numpy, tail idx or None).
     ``src``: the caller's tensor when ``col`` is it (no copy / cast happened): its divergence partials are kept."""
@@ -101,7 +111,7 @@ def psisloo(log_lik, **kwargs):
         raise TypeError('unexpected keyword arguments: %s' % sorted(kwargs))
     if log_lik.shape[0] <= 1:
         raise ValueError("More than one log-weight needed.")
-    cols = (-to_dev(log_lik, _lib.F64)).t().contiguous()            # lw = -log_lik, one column per row
+    cols = _transposed(to_dev(log_lik, _lib.F64), -1.0)             # lw = -log_lik, one column per row
     _, ks, loos = _smooth_columns(cols, Reff, want_loo=True)
     loo = loos.sum()
     if is_host(log_lik):
@@ -144,10 +154,10 @@ def psislw(lw, Reff=1.0, overwrite_lw=False, group=None, out=None):
         out, diag, _ = _smooth_1d(col, Reff, src=lw if col is lw else None)
         kss = diag[0]
     else:
-        cols = dev.t().contiguous()                      # (m, n): one contiguous row per weight set
+        cols = _transposed(dev, 1.0)                     # (m, n): one contiguous row per weight set
         out_cols, ks_dev, _ = _smooth_columns(cols, Reff)
         kss = ks_dev.cpu().numpy()
-        out = out_cols.t().contiguous()
+        out = _transposed(out_cols, 1.0)
     if is_host(lw):
         if out_host is not None:
             if lw.ndim != 1 or not isinstance(out_host, np.ndarray) or out_host.dtype != np.float64 \
