@@ -313,13 +313,19 @@ filter_kernel(const double* __restrict__ lw, long long n, long long index0, cons
             }
 #pragma unroll
             for (int q = 0; q < kFPerThread / 2; ++q) {
-                // branch-free main path: candidates add e^-700 (nothing); NaN poisons the sum
+                // every element is exponentiated (the evaluation is exact for the small positive arguments of the
+                // candidates too), the add is predicated: no select in front of the exp.  NaN: not a candidate (the
+                // compare is false), poisons the sum
                 const bool c0 = v[q].x >= pivot, c1 = v[q].y >= pivot;
-                body += exp_nonpos_flush_v<MIXED>(c0 ? -INFINITY : v[q].x - pivot, s_table);
-                body2 += exp_nonpos_flush_v<MIXED>(c1 ? -INFINITY : v[q].y - pivot, s_table);
-                const long long i = base + 2 * (tid + q * kFThreads);
-                stage(c0, v[q].x, i);
-                stage(c1, v[q].y, i + 1);
+                const double e0 = exp_nonpos_flush_v<MIXED>(v[q].x - pivot, s_table);
+                const double e1 = exp_nonpos_flush_v<MIXED>(v[q].y - pivot, s_table);
+                if (!c0) body += e0;
+                if (!c1) body2 += e1;
+                if (__any_sync(0xffffffffu, c0 || c1)) {   // 0.25 % candidates: one vote per pair of slots skips most stagings
+                    const long long i = base + 2 * (tid + q * kFThreads);
+                    stage(c0, v[q].x, i);
+                    stage(c1, v[q].y, i + 1);
+                }
             }
 #pragma unroll
             for (int q = 0; q < kFPerThread / 2; ++q) v[q] = nv[q];
