@@ -267,6 +267,25 @@ def test_full_rank_draws_carry_the_operand_planes(d, n):
         assert v1 == v2 and np.array_equal(g1, g2)
 
 
+@pytest.mark.parametrize('d', [600, 777])
+def test_full_rank_chain_beyond_one_tile_per_cta(d):
+    """d > 512: more output tiles than CTAs (every CTA walks several tiles through the same shared-memory ring and
+    mbarrier phases), d = 777 odd (8-byte copies, ragged edge tiles of both the full and the symmetric products)."""
+    from viabel_b200 import models, vb
+    rs = np.random.RandomState(d)
+    A = rs.randn(d, d)
+    mp, Pp = rs.randn(d), np.linalg.inv(A @ A.T / d + np.eye(d))
+    fam, ofam = vb.t_variational_family(d, 40), vb_np.t_variational_family(d, 40)
+    lam = 0.02 * rs.randn(fam.var_param_dim)
+    n = 300
+    base = ofam.impl.draw_base(np.random.RandomState(5), n)
+    v, g = vb.black_box_chivi(2.0, fam, models.CorrelatedGaussian(mp, Pp), n, group=False)(lam, base_draws=base)
+    assert fam.impl.chain_info()[3] == 0
+    ov, og = vb_np.chivi_value_and_grad(ofam.impl, mm.CorrelatedGaussian(mp, Pp), 2.0, lam, base)
+    np.testing.assert_allclose(v, ov, rtol=1e-12)
+    assert rel(g, og) < 1e-11
+
+
 def test_full_rank_family_closures():
     import torch
     from viabel_b200 import vb
